@@ -1,0 +1,169 @@
+// oracle/ref_harness.cpp — TEST INFRASTRUCTURE, not product.
+//
+// Driver around the UNMODIFIED reference (linked from oracle/_ref/<variant>/libnemoref.so, built by
+// oracle/Makefile from /root/reference). It calls only the reference's public API
+//   nemo_init_with_backend            (/root/reference/src/nemo-ggml.h:259)
+//   nemo_stream_init / _process_incremental / _finalize / _free   (src/nemo-stream.h:271-326)
+//   nemo_preprocessor_init_from_data / _process                   (src/preprocessor.h:16-49)
+// and reads the public struct fields sctx->encoder_graph.encoder_out, sctx->tokens,
+// sctx->{encoder,decoder,transfer}_seconds to dump what the parity tests compare against.
+//
+//   ref_harness stream <gguf> <pcm.s16le> <right_context> <threads> <out_prefix|-> [max_seconds]
+//       feeds shift*160 samples per call (=> at most one encoder chunk per call), then finalize.
+//       writes <prefix>.mel.f32 [frames,128], <prefix>.enc.f32 [chunks,T,d_model] (all T frames of
+//       every chunk, before the valid_out truncation), <prefix>.tokens.i32, <prefix>.chunk_tokens.i32
+//       (tokens emitted per chunk) and prints one JSON line with timings.
+//   ref_harness mel <gguf> <pcm.s16le> <slice_samples> <out.f32>
+//       preprocessor only, PCM fed in slices of the given size.
+#include "nemo-ggml.h"
+#include "nemo-stream.h"
+#include "preprocessor.h"
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+static std::vector<int16_t> read_pcm(const char* path) {
+    std::vector<int16_t> pcm;
+    FILE* f = fopen(path, "rb");
+    if (!f) { fprintf(stderr, "cannot open %s\n", path); exit(2); }
+    fseek(f, 0, SEEK_END);
+    long n = ftell(f);
+    fseek(f, 0, SEEK_SET);
+    pcm.resize(n / 2);
+    if (fread(pcm.data(), 2, pcm.size(), f) != pcm.size()) { fprintf(stderr, "short read\n"); exit(2); }
+    fclose(f);
+    return pcm;
+}
+
+static void write_file(const std::string& path, const void* data, size_t bytes) {
+    FILE* f = fopen(path.c_str(), "wb");
+    if (!f) { fprintf(stderr, "cannot write %s\n", path.c_str()); exit(2); }
+    fwrite(data, 1, bytes, f);
+    fclose(f);
+}
+
+static double now_s() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+static int run_mel(int argc, char** argv) {
+    if (argc < 6) { fprintf(stderr, "usage: mel <gguf> <pcm> <slice> <out.f32>\n"); return 2; }
+    nemo_context* ctx = nemo_init_with_backend(argv[2], NEMO_BACKEND_CPU);
+    if (!ctx) return 1;
+    std::vector<int16_t> pcm = read_pcm(argv[3]);
+    size_t slice = (size_t)atol(argv[4]);
+    nemo_preprocessor* pp = nemo_preprocessor_init_from_data(
+        ctx->model.preproc_fb_host.data(), ctx->model.preproc_fb_host.size(),
+        ctx->model.preproc_win_host.data(), ctx->model.preproc_win_host.size());
+    std::vector<float> all, mel;
+    for (size_t i = 0; i < pcm.size(); i += slice) {
+        size_t n = std::min(slice, pcm.size() - i);
+        nemo_preprocessor_process(pp, pcm.data() + i, n, mel);
+        all.insert(all.end(), mel.begin(), mel.end());
+    }
+    write_file(argv[5], all.data(), all.size() * sizeof(float));
+    printf("{\"mode\":\"mel\",\"frames\":%zu}\n", all.size() / 128);
+    nemo_preprocessor_free(pp);
+    nemo_free(ctx);
+    return 0;
+}
+
+static int run_stream(int argc, char** argv) {
+    if (argc < 7) { fprintf(stderr, "usage: stream <gguf> <pcm> <rc> <threads> <prefix|-> [max_seconds]\n"); return 2; }
+    const char* gguf = argv[2];
+    std::vector<int16_t> pcm = read_pcm(argv[3]);
+    int rc = atoi(argv[4]);
+    int threads = atoi(argv[5]);
+    std::string prefix = argv[6];
+    bool dump = prefix != "-";
+    double max_seconds = argc > 7 ? atof(argv[7]) : 0.0;
+    if (max_seconds > 0 && pcm.size() > (size_t)(max_seconds * 16000)) pcm.resize((size_t)(max_seconds * 16000));
+
+    double t0 = now_s();
+    nemo_context* ctx = nemo_init_with_backend(gguf, NEMO_BACKEND_CPU);
+    if (!ctx) return 1;
+    if (threads > 0) ggml_backend_cpu_set_n_threads(ctx->model.backend, threads);
+    double t_load = now_s() - t0;
+
+    nemo_cache_config cfg = nemo_cache_config::default_config();
+    cfg.att_right_context = rc;
+    nemo_stream_context* s = nemo_stream_init(ctx, &cfg);
+    if (!s) return 1;
+
+    const size_t feed = s->config.get_shift_mel_frames() * s->config.hop_length;
+    const int d_model = s->config.d_model;
+
+    // mel dump: a second, independent preprocessor instance over the same PCM
+    std::vector<float> mel_all;
+    if (dump) {
+        nemo_preprocessor* pp = nemo_preprocessor_init_from_data(
+            ctx->model.preproc_fb_host.data(), ctx->model.preproc_fb_host.size(),
+            ctx->model.preproc_win_host.data(), ctx->model.preproc_win_host.size());
+        std::vector<float> mel;
+        for (size_t i = 0; i < pcm.size(); i += feed) {
+            nemo_preprocessor_process(pp, pcm.data() + i, std::min(feed, pcm.size() - i), mel);
+            mel_all.insert(mel_all.end(), mel.begin(), mel.end());
+        }
+        nemo_preprocessor_free(pp);
+    }
+
+    std::vector<float> enc_all;
+    std::vector<int32_t> chunk_tokens;
+    int chunks_seen = 0;
+    size_t tokens_seen = 0;
+    int enc_T = 0;
+    auto after_call = [&]() {
+        if (s->total_chunks_processed > chunks_seen) {
+            // by construction at most one chunk per call
+            if (dump) {
+                ggml_tensor* e = s->encoder_graph.encoder_out;
+                enc_T = (int)e->ne[1];
+                std::vector<float> buf(ggml_nelements(e));
+                ggml_backend_tensor_get(e, buf.data(), 0, buf.size() * sizeof(float));
+                enc_all.insert(enc_all.end(), buf.begin(), buf.end());
+            }
+            chunk_tokens.push_back((int32_t)(s->tokens.size() - tokens_seen));
+            tokens_seen = s->tokens.size();
+            chunks_seen = s->total_chunks_processed;
+        }
+    };
+
+    double t1 = now_s();
+    for (size_t i = 0; i < pcm.size(); i += feed) {
+        nemo_stream_process_incremental(s, pcm.data() + i, (int)std::min(feed, pcm.size() - i));
+        after_call();
+    }
+    nemo_stream_finalize(s);
+    after_call();
+    double t_proc = now_s() - t1;
+
+    if (dump) {
+        write_file(prefix + ".mel.f32", mel_all.data(), mel_all.size() * sizeof(float));
+        write_file(prefix + ".enc.f32", enc_all.data(), enc_all.size() * sizeof(float));
+        std::vector<int32_t> tok(s->tokens.begin(), s->tokens.end());
+        write_file(prefix + ".tokens.i32", tok.data(), tok.size() * sizeof(int32_t));
+        write_file(prefix + ".chunk_tokens.i32", chunk_tokens.data(), chunk_tokens.size() * sizeof(int32_t));
+    }
+    double audio_s = (double)pcm.size() / 16000.0;
+    printf("{\"mode\":\"stream\",\"rc\":%d,\"threads\":%d,\"audio_s\":%.4f,\"proc_s\":%.4f,\"load_s\":%.3f,"
+           "\"rtfx\":%.4f,\"chunks\":%d,\"enc_T\":%d,\"d_model\":%d,\"tokens\":%zu,\"decode_iters\":%d,"
+           "\"encoder_s\":%.4f,\"decoder_s\":%.4f,\"transfer_s\":%.4f}\n",
+           rc, threads, audio_s, t_proc, t_load, audio_s / t_proc, chunks_seen, enc_T, d_model,
+           s->tokens.size(), s->total_decode_iterations, s->encoder_seconds, s->decoder_seconds,
+           s->transfer_seconds);
+    nemo_stream_free(s);
+    nemo_free(ctx);
+    return 0;
+}
+
+int main(int argc, char** argv) {
+    if (argc < 2) { fprintf(stderr, "usage: ref_harness stream|mel ...\n"); return 2; }
+    if (!strcmp(argv[1], "mel")) return run_mel(argc, argv);
+    if (!strcmp(argv[1], "stream")) return run_stream(argc, argv);
+    fprintf(stderr, "unknown mode %s\n", argv[1]);
+    return 2;
+}
