@@ -1,0 +1,127 @@
+/* nb200.h — C ABI of libnemob200.so: the B200 (sm_100a) backend for nemotron-asr.cpp's streaming hot path
+ *   s16le PCM -> log-mel -> cache-aware FastConformer encoder -> RNNT LSTM/joint -> greedy tokens.
+ *
+ * This is the drop-in boundary. Every entry point names the reference interface it replaces
+ * (paths relative to the reference repo m1el/nemotron-asr.cpp @ 4a863ff). The reference API is C++ over public
+ * structs; this ABI is plain C (opaque handles, pointers and sizes, int status codes) so it can be bound from the
+ * reference's own sources, from ctypes (nemotron-asr.cpp_b200/nb200.py) or any FFI.
+ *
+ * Threading contract = the reference's (src/nemo-server.cpp:6-10): one thread owns a model and its streams.
+ * Errors: functions return NULL / a negative status and nb200_last_error() holds a message (the reference
+ * returns nullptr/false/"" and prints to stderr). There is NO CPU fallback: without a CUDA device or with a
+ * failed kernel every call fails loudly.
+ */
+#ifndef NB200_H
+#define NB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NB200_OK 0
+#define NB200_ERR (-1)
+
+typedef struct nb200_model nb200_model;   /* replaces struct nemo_context   (src/nemo-ggml.h:236-252) */
+typedef struct nb200_stream nb200_stream; /* replaces struct nemo_stream_context (src/nemo-stream.h:177-262) */
+
+/* model-load flags */
+#define NB200_FLAG_ACT_QUANT_AUTO 0 /* emulate ggml-CPU's Q8_0 activation re-quantisation iff the file has Q8_0 weights */
+#define NB200_FLAG_ACT_QUANT_OFF 1  /* never (weights are still the dequantised Q8_0 values)                       */
+#define NB200_FLAG_ACT_QUANT_ON 2   /* always                                                                      */
+#define NB200_FLAG_GEMM_SIMT 16     /* debug: CUDA-core GEMM instead of the tcgen05 kernel (same operands/epilogues) */
+
+typedef struct nb200_info {
+    int32_t n_mels, d_model, n_heads, d_head, d_ff, n_layers, kernel_size;
+    int32_t vocab_size, blank_token, decoder_dim, joint_dim, subsampling_factor, att_left_context, num_prompts;
+    int32_t weights_quantized; /* 1 if the GGUF holds Q8_0 encoder matrices */
+    int32_t act_quant;         /* 1 if activation re-quantisation is emulated */
+    int32_t max_streams;       /* stream slots allocated in HBM */
+    int32_t device;
+} nb200_info;
+
+typedef struct nb200_stats {
+    int64_t steps;            /* batched steps run                                   */
+    int64_t chunks;           /* stream-chunks processed (sum of batch sizes)        */
+    int64_t frames;           /* encoder frames decoded                              */
+    int64_t tokens;           /* non-blank tokens emitted                            */
+    int64_t decode_rounds;    /* batched joint evaluations                           */
+    int64_t kernel_launches;  /* kernels of this library launched so far             */
+    double audio_seconds;     /* audio consumed by processed chunks                  */
+    double gpu_seconds;       /* device time of all steps (CUDA events on the library's stream) */
+    double last_step_gpu_ms;  /* device time of the last nb200_step                  */
+    double last_frontend_ms, last_encoder_ms, last_decoder_ms; /* split of the last step (events) */
+} nb200_stats;
+
+const char* nb200_last_error(void);
+int nb200_version(void);
+
+/* nemo_init_with_backend(path, backend) — src/nemo-ggml.h:259, src/nemo-ggml.cpp:448-495 (GGUF load :83-442).
+ * device: CUDA ordinal. max_streams: stream slots to reserve (K/V/conv caches live in HBM per slot). */
+nb200_model* nb200_model_load(const char* gguf_path, int device, int max_streams, int flags);
+/* nemo_free — src/nemo-ggml.h:261 */
+void nb200_model_free(nb200_model* m);
+int nb200_model_info(const nb200_model* m, nb200_info* out);
+/* vocabulary piece of a token id (model.vocab, src/nemo-ggml.cpp:149-169); NULL if out of range */
+const char* nb200_model_token(const nb200_model* m, int32_t id);
+/* tokens_to_text — src/nemo-ggml.cpp:1556-1583 (U+2581 -> ' '); returns bytes written (excluding NUL) or <0 */
+int nb200_tokens_to_text(const nb200_model* m, const int32_t* tokens, int n, char* out, int cap);
+
+/* nemo_stream_init(ctx, cfg) with cfg.att_right_context in {0,1,6,13} — src/nemo-stream.h:271, .cpp:696-733 */
+nb200_stream* nb200_stream_create(nb200_model* m, int right_context);
+/* nemo_stream_free — src/nemo-stream.h:324 */
+void nb200_stream_free(nb200_stream* s);
+/* nemo_stream_reset — src/nemo-stream.h:319 (this backend also re-zeroes the conv cache; the reference does not) */
+int nb200_stream_reset(nb200_stream* s);
+
+/* First half of nemo_stream_process_incremental (src/nemo-stream.cpp:1145-1162): buffer PCM. Enqueue only. */
+int nb200_stream_feed(nb200_stream* s, const int16_t* pcm, int n_samples);
+/* nemo_stream_finalize (src/nemo-stream.cpp:1217-1293): mark the stream so the next nb200_step flushes its
+ * zero-padded tail chunk (keeps floor(new_mel/8) frames). */
+int nb200_stream_finalize(nb200_stream* s);
+/* chunks this stream could run right now (full chunks buffered, +1 if a finalize tail is pending) */
+int nb200_stream_ready_chunks(const nb200_stream* s);
+
+/* Second half of nemo_stream_process_incremental (:1174-1199) for ALL streams of the model at once: takes at
+ * most one ready chunk from every stream, runs them as batched kernels (mel, conv subsampling, 24 conformer
+ * layers, joint/LSTM greedy decode) and appends the emitted tokens to each stream. This is what gives
+ * cross-stream batching; the reference runs one stream at a time (src/nemo-server.cpp:192-271).
+ * Returns the number of stream-chunks processed (0 = nothing ready) or <0 on error. */
+int nb200_step(nb200_model* m);
+/* Convenience: nb200_step until no stream has a ready chunk. Returns total stream-chunks processed. */
+int nb200_drain(nb200_model* m);
+
+/* Tokens emitted since the last poll (sctx->tokens, src/nemo-stream.h:231). Returns count copied. */
+int nb200_stream_poll_tokens(nb200_stream* s, int32_t* out, int cap);
+/* nemo_stream_get_tokens — all tokens so far; returns total count, copies min(total, cap) */
+int nb200_stream_get_tokens(const nb200_stream* s, int32_t* out, int cap);
+/* per-chunk token counts (for parity tests); returns number of chunks processed */
+int nb200_stream_chunk_token_counts(const nb200_stream* s, int32_t* out, int cap);
+/* per-chunk smallest top1-top2 logit gap over the chunk's symbol steps (near-tie tracing of token mismatches) */
+int nb200_stream_chunk_margins(const nb200_stream* s, float* out, int cap);
+
+/* Parity taps (the reference reads sctx->encoder_graph.encoder_out, src/nemo-stream.h:156). When enabled the
+ * stream keeps the log-mel frames and every chunk's encoder output [T,1024] on the host. */
+#define NB200_TAP_MEL 1
+#define NB200_TAP_ENC 2
+int nb200_stream_set_taps(nb200_stream* s, int taps);
+/* returns number of floats available; copies min(available, cap) */
+int64_t nb200_stream_fetch_tap(const nb200_stream* s, int tap, float* out, int64_t cap);
+
+int nb200_get_stats(const nb200_model* m, nb200_stats* out);
+
+/* ---- kernel-level entry points (used by the parity tests and bench; same kernels the step uses) -------- */
+/* nemo_preprocessor_process (src/preprocessor.cpp:330-395) for a batch of independent signals, each starting
+ * from a fresh preprocessor: pcm [n_streams][n_samples] int16 (host) -> mel [n_streams][n_frames][128] (host),
+ * n_frames = (256 + n_samples - 512)/160 + 1. Returns n_frames or <0. */
+int nb200_mel_batch(nb200_model* m, const int16_t* pcm, int n_streams, int n_samples, float* mel_out);
+/* Y[M,N] = X[M,K] * W^T with W one of the model's encoder matrices (by GGUF tensor name), using exactly the
+ * operand preparation (activation re-quantisation, fp16 operands) and GEMM kernel of the step. Host buffers. */
+int nb200_debug_matmul(nb200_model* m, const char* tensor_name, const float* x, int M, float* y);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NB200_H */

@@ -1,0 +1,90 @@
+// common.cuh — shared definitions for libnemob200 (sm_100a only).
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <stdexcept>
+#include <string>
+
+namespace nb {
+
+// Architecture constants of nemotron-speech-streaming-0.6B (src/nemo-ggml.h:37-55 in the reference); only
+// n_layers is read from the file, everything else is checked against these at load.
+constexpr int N_MELS = 128, D_MODEL = 1024, N_HEADS = 8, D_HEAD = 128, D_FF = 4096, KERNEL = 9;
+constexpr int VOCAB = 1025, BLANK = 1024, DEC = 640, JOINT = 640, LEFT = 70, CONV_CACHE = 8;
+constexpr int SUB_CH = 256, SUB_F1 = 65, SUB_F2 = 33, SUB_F3 = 17, SUB_FEAT = SUB_CH * SUB_F3;  // 4352
+constexpr int N_FFT = 512, HOP = 160, N_BINS = 257, MEL_OVERLAP = 9;
+constexpr int RING = 84;          // K/V ring capacity: 70 cached + up to 14 new frames
+constexpr int MAX_T = 14;         // encoder frames per chunk at right_context 13
+constexpr int MAX_SYMBOLS = 10;   // src/nemo-stream.cpp:849
+
+struct Error : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+inline void cuda_check(cudaError_t e, const char* what, const char* file, int line) {
+    if (e != cudaSuccess) {
+        char buf[512];
+        snprintf(buf, sizeof buf, "CUDA error %s at %s:%d: %s", what, file, line, cudaGetErrorString(e));
+        throw Error(buf);
+    }
+}
+#define CUDA_CHECK(x) ::nb::cuda_check((x), #x, __FILE__, __LINE__)
+
+extern long long g_launches;  // kernels launched by this library (reported as gpu_launches)
+#define NB_LAUNCHED() (++::nb::g_launches)
+#define NB_KERNEL_CHECK() do { NB_LAUNCHED(); CUDA_CHECK(cudaGetLastError()); } while (0)
+
+template <typename T>
+T* dalloc(size_t n) {
+    T* p = nullptr;
+    CUDA_CHECK(cudaMalloc(&p, n * sizeof(T)));
+    return p;
+}
+
+__host__ __device__ inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// Latency-mode arithmetic (src/nemo-stream.h:65-100)
+struct Mode {
+    int rc;         // att_right_context
+    int T;          // encoder frames per chunk = 1 + rc
+    int shift;      // new mel frames per chunk = 8 * (1 + rc)
+    int chunk_mel;  // 9 + shift
+    int t1, t2, t3; // time extents after each stride-2 stage
+    int npos;       // relative positions used: p in [-(T-1), 70+T-1]
+    explicit Mode(int rc_) : rc(rc_) {
+        T = 1 + rc;
+        shift = 8 * (1 + rc);
+        chunk_mel = MEL_OVERLAP + shift;
+        t1 = chunk_mel / 2 + 1;
+        t2 = t1 / 2 + 1;
+        t3 = t2 / 2 + 1;
+        npos = LEFT + 2 * T - 1;
+    }
+};
+
+// ---- device helpers -------------------------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+// ggml-CPU's Q8_0 activation quantiser applied to a value given its block's amax, returned dequantised:
+// d = fp16(amax/127), q = rne(x * (127/amax))  (ggml/src/ggml-cpu/arch/x86/quants.c:331-346), value = q*d.
+__device__ __forceinline__ float fake_quant(float x, float amax) {
+    if (amax == 0.0f) return 0.0f;
+    float d = __half2float(__float2half_rn(__fdiv_rn(amax, 127.0f)));
+    float id = __fdiv_rn(127.0f, amax);
+    return rintf(__fmul_rn(x, id)) * d;
+}
+
+}  // namespace nb

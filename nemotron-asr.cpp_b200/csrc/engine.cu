@@ -1,0 +1,1027 @@
+// engine.cu — model load, stream sessions, the batched step scheduler and the C ABI (include/nb200.h).
+//
+// Replaces, for the streaming hot path, the reference's nemo_model_load (src/nemo-ggml.cpp:83-442),
+// nemo_stream_context (src/nemo-stream.h:177-262), process_mel_chunk_streaming / nemo_stream_process_incremental /
+// nemo_stream_finalize (src/nemo-stream.cpp:1013-1293). One step runs ONE chunk of EVERY ready stream as batched
+// kernels; per-stream state (K/V ring caches, conv cache, mel overlap, LSTM state) lives in HBM slots.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/nb200.h"
+#include "gemm.cuh"
+#include "gguf_reader.h"
+#include "kernels.cuh"
+
+using namespace nb;
+
+namespace {
+
+thread_local std::string g_error;
+void set_error(const std::string& e) {
+    g_error = e;
+    fprintf(stderr, "nb200: %s\n", e.c_str());
+}
+
+struct F16Matrix {  // fp16 [rows][K] in HBM + TMA descriptors
+    __half* ptr = nullptr;
+    Operand op;
+};
+
+struct LayerW {
+    float *ln_ff1_g, *ln_ff1_b, *ln_att_g, *ln_att_b, *ln_conv_g, *ln_conv_b, *ln_ff2_g, *ln_ff2_b, *ln_out_g, *ln_out_b;
+    float *bn_g, *bn_b, *pos_u, *pos_v, *w_dw;
+    F16Matrix ff1_w1, ff1_w2, wqkv, wpos, wout, pw1, pw2, ff2_w1, ff2_w2;
+};
+
+struct ModeCtx {
+    Mode mode;
+    float* pos_tab = nullptr;  // [L][npos][1024] linear_pos(PE(p)), p = -(T-1) .. 70+T-1
+    explicit ModeCtx(int rc) : mode(rc) {}
+};
+
+template <typename T>
+struct PinnedBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    void reserve(size_t m) {
+        if (m <= n) return;
+        if (p) cudaFreeHost(p);
+        CUDA_CHECK(cudaMallocHost(&p, m * sizeof(T)));
+        n = m;
+    }
+    ~PinnedBuf() {
+        if (p) cudaFreeHost(p);
+    }
+};
+
+}  // namespace
+
+struct nb200_stream {
+    nb200_model* model = nullptr;
+    int slot = -1;
+    int rc = 0;
+    // host-side audio buffer: pcm[i] is absolute sample pcm_base + i
+    std::vector<int16_t> pcm;
+    long long pcm_base = 0;
+    long long samples_total = 0;
+    long long chunks_done = 0;
+    bool finalize_requested = false, finalized = false;
+    int wpos = 0;   // K/V ring write index
+    int valid = 0;  // cache_valid_len
+    std::vector<int32_t> tokens;
+    size_t poll_cursor = 0;
+    std::vector<int32_t> chunk_tokens;
+    std::vector<float> chunk_margins;  // per chunk: smallest top1-top2 logit gap of its symbol steps
+    int taps = 0;
+    std::vector<float> tap_mel, tap_enc;
+};
+
+struct nb200_model {
+    int device = 0;
+    cudaStream_t st = nullptr;
+    nb200_info info{};
+    std::vector<std::string> vocab;
+    bool act_quant = false, simt = false;
+    int n_layers = 0, max_streams = 0;
+
+    std::vector<void*> allocs;  // everything cudaMalloc'ed
+    // weights
+    MelTables mel_tb{};
+    SubWeights sub{};
+    float *sub_b3 = nullptr, *sub_b6 = nullptr, *sub_bout = nullptr;
+    F16Matrix sub_w3, sub_w6, sub_wout;
+    float *joint_enc_w = nullptr, *joint_enc_b = nullptr;  // fp32: the decoder side stays in fp32 like the reference
+    std::vector<LayerW> layers;
+    DecodeWeights dec{};
+    std::map<std::string, F16Matrix*> by_name;
+    // per-slot state
+    float *k_ring = nullptr, *v_ring = nullptr, *conv_cache = nullptr;  // [L][slots][...]
+    float* mel_overlap = nullptr;                                      // [slots][9][128]
+    DecodeState dstate{};
+    std::vector<int> free_slots;
+    std::vector<nb200_stream*> streams;
+    std::map<int, std::unique_ptr<ModeCtx>> modes;
+    // workspace (capacity: cap_B streams x MAX_T frames)
+    int cap_B = 0;
+    float *ws_mel = nullptr, *ws_a3 = nullptr, *ws_x = nullptr, *ws_q = nullptr, *ws_g = nullptr, *ws_e = nullptr;
+    __half *ws_a2h = nullptr, *ws_a5h = nullptr, *ws_a6h = nullptr, *ws_a16 = nullptr, *ws_h16 = nullptr, *ws_pos16 = nullptr;
+    float* ws_posf = nullptr;
+    Operand op_a2h, op_a5h, op_a6h, op_a16, op_h16, op_pos16;
+    int16_t* ws_pcm = nullptr;
+    int pcm_stride = 0;
+    int* ws_meta = nullptr;        // int arrays [8][cap_B]
+    long long* ws_meta64 = nullptr;  // [cap_B]
+    int *ws_fp = nullptr, *ws_sym = nullptr, *ws_tok = nullptr, *ws_tokcnt = nullptr, *ws_unfinished = nullptr;
+    float *ws_hid = nullptr, *ws_logits = nullptr, *ws_lx = nullptr, *ws_gates = nullptr, *ws_hp = nullptr;
+    PinnedBuf<int16_t> h_pcm;
+    PinnedBuf<int> h_meta;
+    PinnedBuf<long long> h_meta64;
+    PinnedBuf<int> h_tok;
+    PinnedBuf<float> h_tap;
+    cudaEvent_t ev[4]{};
+    nb200_stats stats{};
+
+    template <typename T>
+    T* alloc(size_t n, bool zero = true) {
+        T* p = dalloc<T>(n);
+        allocs.push_back(p);
+        if (zero) CUDA_CHECK(cudaMemset(p, 0, n * sizeof(T)));
+        return p;
+    }
+    template <typename T>
+    T* upload(const std::vector<T>& v) {
+        T* p = alloc<T>(v.size(), false);
+        CUDA_CHECK(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+        return p;
+    }
+    ~nb200_model() {
+        for (auto* s : streams) delete s;
+        for (void* p : allocs) cudaFree(p);
+        for (auto& e : ev)
+            if (e) cudaEventDestroy(e);
+        if (st) cudaStreamDestroy(st);
+    }
+};
+
+namespace {
+
+std::vector<float> load_f32(const GgufFile& g, const std::string& name, int64_t expect = -1) {
+    const GgufTensor& t = g.tensor(name);
+    if (expect >= 0 && t.nelements() != expect)
+        throw Error("tensor " + name + " has " + std::to_string(t.nelements()) + " elements, expected " + std::to_string(expect));
+    std::vector<float> v((size_t)t.nelements());
+    dequantize_to_f32(t, v.data());
+    return v;
+}
+
+void make_f16(nb200_model* m, F16Matrix& dst, const std::vector<float>& w, int rows, int K, const std::string& name = "") {
+    std::vector<__half> h((size_t)rows * K);
+    for (size_t i = 0; i < h.size(); i++) h[i] = __float2half_rn(w[i]);
+    dst.ptr = m->upload(h);
+    operand_init(dst.op, dst.ptr, rows, K);
+    if (!name.empty()) m->by_name[name] = &dst;
+}
+
+void load_matrix(nb200_model* m, const GgufFile& g, F16Matrix& dst, const std::string& name, int rows, int K) {
+    make_f16(m, dst, load_f32(g, name, (int64_t)rows * K), rows, K, name);
+}
+
+uint32_t kv_u32(const GgufFile& g, const char* key, uint32_t dflt) {
+    auto it = g.u32.find(key);
+    return it == g.u32.end() ? dflt : it->second;
+}
+
+void build_model(nb200_model* m, const std::string& path, int flags) {
+    GgufFile g;
+    g.open(path);
+    nb200_info& hp = m->info;
+    hp.n_mels = kv_u32(g, "nemo.n_mels", N_MELS);
+    hp.d_model = kv_u32(g, "nemo.d_model", D_MODEL);
+    hp.n_heads = kv_u32(g, "nemo.n_heads", N_HEADS);
+    hp.d_head = kv_u32(g, "nemo.d_head", D_HEAD);
+    hp.d_ff = kv_u32(g, "nemo.d_ff", D_FF);
+    hp.n_layers = kv_u32(g, "nemo.n_layers", 24);
+    hp.vocab_size = kv_u32(g, "nemo.vocab_size", VOCAB);
+    hp.decoder_dim = kv_u32(g, "nemo.decoder_dim", DEC);
+    hp.joint_dim = kv_u32(g, "nemo.joint_dim", JOINT);
+    hp.subsampling_factor = kv_u32(g, "nemo.subsampling_factor", 8);
+    hp.att_left_context = kv_u32(g, "nemo.att_left_context", LEFT);
+    hp.num_prompts = kv_u32(g, "nemo.num_prompts", 0);
+    hp.blank_token = hp.vocab_size - 1;
+    hp.device = m->device;
+    hp.max_streams = m->max_streams;
+    if (hp.n_mels != N_MELS || hp.d_model != D_MODEL || hp.n_heads != N_HEADS || hp.d_head != D_HEAD || hp.d_ff != D_FF ||
+        hp.vocab_size != VOCAB || hp.decoder_dim != DEC || hp.joint_dim != JOINT || hp.subsampling_factor != 8 ||
+        hp.att_left_context != LEFT)
+        throw Error("this backend is built for the nemotron-speech-streaming 0.6B architecture; the GGUF header differs");
+    if (hp.num_prompts != 0) throw Error("multilingual prompt fusion (num_prompts > 0) is not supported by this backend yet");
+    m->n_layers = hp.n_layers;
+    // vocabulary (src/nemo-ggml.cpp:149-169)
+    if (g.str_arr.count("tokenizer.vocab_list")) {
+        m->vocab = g.str_arr["tokenizer.vocab_list"];
+    } else if (g.str.count("tokenizer.vocab")) {
+        const std::string& blob = g.str["tokenizer.vocab"];
+        for (size_t i = 0; i + 8 <= blob.size() && (int)i / 8 < hp.vocab_size - 1; i += 8)
+            m->vocab.emplace_back(blob.data() + i, strnlen(blob.data() + i, 8));
+    } else {
+        throw Error("no vocabulary in GGUF (need tokenizer.vocab_list or tokenizer.vocab)");
+    }
+    const std::string l0 = "encoder.layers.0.";
+    const GgufTensor& dw0 = g.tensor(l0 + "conv.depthwise_conv.weight");
+    hp.kernel_size = dw0.dims.size() > 1 ? (int)dw0.dims[1] : 0;  // inferred like src/nemo-ggml.cpp:357-360
+    if (hp.kernel_size != KERNEL) throw Error("depthwise kernel size must be 9");
+    hp.weights_quantized = g.tensor(l0 + "feed_forward1.linear1.weight").type != GGML_F32 &&
+                           g.tensor(l0 + "feed_forward1.linear1.weight").type != GGML_F16;
+    const int aq = flags & 3;
+    m->act_quant = aq == NB200_FLAG_ACT_QUANT_ON || (aq == NB200_FLAG_ACT_QUANT_AUTO && hp.weights_quantized);
+    hp.act_quant = m->act_quant;
+    m->simt = (flags & NB200_FLAG_GEMM_SIMT) != 0;
+
+    // ---- mel tables (src/preprocessor.cpp:80-110, 270-307) ----
+    {
+        std::vector<float> fb = load_f32(g, "preprocessor.featurizer.fb", (int64_t)N_MELS * N_BINS);
+        std::vector<float> win = load_f32(g, "preprocessor.featurizer.window", 400);
+        std::vector<float> win512(N_FFT, 0.0f), cs(N_FFT), sn(N_FFT), fbT((size_t)N_BINS * N_MELS);
+        std::copy(win.begin(), win.end(), win512.begin() + (N_FFT - 400) / 2);
+        for (int i = 0; i < N_FFT; i++) {
+            float theta = (2.0f * (float)M_PI * i) / N_FFT;
+            sn[i] = sinf(theta);
+            cs[i] = cosf(theta);
+        }
+        std::vector<int2> range(N_MELS);
+        for (int mm = 0; mm < N_MELS; mm++) {
+            int lo = N_BINS, hi = 0;
+            for (int k = 0; k < N_BINS; k++) {
+                float v = fb[(size_t)mm * N_BINS + k];
+                fbT[(size_t)k * N_MELS + mm] = v;
+                if (v != 0.0f) {
+                    lo = std::min(lo, k);
+                    hi = std::max(hi, k + 1);
+                }
+            }
+            if (lo >= hi) lo = hi = 0;
+            range[mm] = make_int2(lo, hi);
+        }
+        m->mel_tb.win512 = m->upload(win512);
+        m->mel_tb.cos_tbl = m->upload(cs);
+        m->mel_tb.sin_tbl = m->upload(sn);
+        m->mel_tb.fbT = m->upload(fbT);
+        m->mel_tb.fb_range = m->upload(range);
+    }
+    // ---- pre_encode (src/nemo-ggml.cpp:296-307) ----
+    {
+        const std::string pe = "encoder.pre_encode.";
+        std::vector<float> w0 = load_f32(g, pe + "conv.0.weight", 256 * 9);
+        for (auto& v : w0) v = __half2float(__float2half_rn(v));  // conv0 runs through an F16 im2col (ggml.c:4658-4680)
+        m->sub.w0 = m->upload(w0);
+        m->sub.b0 = m->upload(load_f32(g, pe + "conv.0.bias", 256));
+        m->sub.w2 = m->upload(load_f32(g, pe + "conv.2.weight", 256 * 9));
+        m->sub.b2 = m->upload(load_f32(g, pe + "conv.2.bias", 256));
+        m->sub.w5 = m->upload(load_f32(g, pe + "conv.5.weight", 256 * 9));
+        m->sub.b5 = m->upload(load_f32(g, pe + "conv.5.bias", 256));
+        load_matrix(m, g, m->sub_w3, pe + "conv.3.weight", 256, 256);
+        m->sub_b3 = m->upload(load_f32(g, pe + "conv.3.bias", 256));
+        load_matrix(m, g, m->sub_w6, pe + "conv.6.weight", 256, 256);
+        m->sub_b6 = m->upload(load_f32(g, pe + "conv.6.bias", 256));
+        // out.weight [1024][c*17+w] -> [1024][w*256+c]: our activations are position-major, channel fastest
+        std::vector<float> wo = load_f32(g, pe + "out.weight", (int64_t)D_MODEL * SUB_FEAT), wp(wo.size());
+        for (int n = 0; n < D_MODEL; n++)
+            for (int c = 0; c < SUB_CH; c++)
+                for (int w = 0; w < SUB_F3; w++) wp[(size_t)n * SUB_FEAT + w * SUB_CH + c] = wo[(size_t)n * SUB_FEAT + c * SUB_F3 + w];
+        make_f16(m, m->sub_wout, wp, D_MODEL, SUB_FEAT);
+        m->sub_bout = m->upload(load_f32(g, pe + "out.bias", D_MODEL));
+    }
+    // ---- conformer layers (src/nemo-ggml.cpp:310-361) ----
+    m->layers.resize(m->n_layers);
+    for (int l = 0; l < m->n_layers; l++) {
+        LayerW& L = m->layers[l];
+        const std::string p = "encoder.layers." + std::to_string(l) + ".";
+        auto vec = [&](const std::string& n, int64_t cnt) { return m->upload(load_f32(g, p + n, cnt)); };
+        L.ln_ff1_g = vec("norm_feed_forward1.weight", D_MODEL); L.ln_ff1_b = vec("norm_feed_forward1.bias", D_MODEL);
+        L.ln_att_g = vec("norm_self_att.weight", D_MODEL);      L.ln_att_b = vec("norm_self_att.bias", D_MODEL);
+        L.ln_conv_g = vec("norm_conv.weight", D_MODEL);         L.ln_conv_b = vec("norm_conv.bias", D_MODEL);
+        L.ln_ff2_g = vec("norm_feed_forward2.weight", D_MODEL); L.ln_ff2_b = vec("norm_feed_forward2.bias", D_MODEL);
+        L.ln_out_g = vec("norm_out.weight", D_MODEL);           L.ln_out_b = vec("norm_out.bias", D_MODEL);
+        L.bn_g = vec("conv.batch_norm.weight", D_MODEL);        L.bn_b = vec("conv.batch_norm.bias", D_MODEL);
+        L.pos_u = vec("self_attn.pos_bias_u", D_MODEL);         L.pos_v = vec("self_attn.pos_bias_v", D_MODEL);
+        L.w_dw = vec("conv.depthwise_conv.weight", (int64_t)KERNEL * D_MODEL);
+        load_matrix(m, g, L.ff1_w1, p + "feed_forward1.linear1.weight", D_FF, D_MODEL);
+        load_matrix(m, g, L.ff1_w2, p + "feed_forward1.linear2.weight", D_MODEL, D_FF);
+        load_matrix(m, g, L.ff2_w1, p + "feed_forward2.linear1.weight", D_FF, D_MODEL);
+        load_matrix(m, g, L.ff2_w2, p + "feed_forward2.linear2.weight", D_MODEL, D_FF);
+        load_matrix(m, g, L.wpos, p + "self_attn.linear_pos.weight", D_MODEL, D_MODEL);
+        load_matrix(m, g, L.wout, p + "self_attn.linear_out.weight", D_MODEL, D_MODEL);
+        load_matrix(m, g, L.pw2, p + "conv.pointwise_conv2.weight", D_MODEL, D_MODEL);
+        {   // q|k|v stacked: one N=3072 GEMM over the same (re-quantised) LN output
+            std::vector<float> w((size_t)3 * D_MODEL * D_MODEL);
+            const char* nm[3] = {"self_attn.linear_q.weight", "self_attn.linear_k.weight", "self_attn.linear_v.weight"};
+            for (int i = 0; i < 3; i++) {
+                std::vector<float> part = load_f32(g, p + nm[i], (int64_t)D_MODEL * D_MODEL);
+                std::copy(part.begin(), part.end(), w.begin() + (size_t)i * D_MODEL * D_MODEL);
+            }
+            make_f16(m, L.wqkv, w, 3 * D_MODEL, D_MODEL);
+        }
+        {   // pointwise_conv1: rows 0..1023 = GLU value, 1024..2047 = gate -> interleave (value_j, gate_j)
+            std::vector<float> w = load_f32(g, p + "conv.pointwise_conv1.weight", (int64_t)2 * D_MODEL * D_MODEL), wi(w.size());
+            for (int j = 0; j < D_MODEL; j++) {
+                std::copy(w.begin() + (size_t)j * D_MODEL, w.begin() + (size_t)(j + 1) * D_MODEL, wi.begin() + (size_t)(2 * j) * D_MODEL);
+                std::copy(w.begin() + (size_t)(D_MODEL + j) * D_MODEL, w.begin() + (size_t)(D_MODEL + j + 1) * D_MODEL,
+                          wi.begin() + (size_t)(2 * j + 1) * D_MODEL);
+            }
+            make_f16(m, L.pw1, wi, 2 * D_MODEL, D_MODEL);
+        }
+    }
+    // ---- decoder + joint (src/nemo-ggml.cpp:369-388), kept fp32 ----
+    {
+        const std::string d = "decoder.prediction.";
+        m->dec.embed = m->upload(load_f32(g, d + "embed.weight", (int64_t)VOCAB * DEC));
+        for (int l = 0; l < 2; l++) {
+            const std::string s = std::to_string(l);
+            std::vector<float> wih = load_f32(g, d + "dec_rnn.lstm.weight_ih_l" + s, (int64_t)4 * DEC * DEC);
+            std::vector<float> whh = load_f32(g, d + "dec_rnn.lstm.weight_hh_l" + s, (int64_t)4 * DEC * DEC);
+            std::vector<float> bih = load_f32(g, d + "dec_rnn.lstm.bias_ih_l" + s, 4 * DEC);
+            std::vector<float> bhh = load_f32(g, d + "dec_rnn.lstm.bias_hh_l" + s, 4 * DEC);
+            std::vector<float> wc((size_t)4 * DEC * 2 * DEC), bc(4 * DEC);
+            for (int r = 0; r < 4 * DEC; r++) {
+                std::copy(wih.begin() + (size_t)r * DEC, wih.begin() + (size_t)(r + 1) * DEC, wc.begin() + (size_t)r * 2 * DEC);
+                std::copy(whh.begin() + (size_t)r * DEC, whh.begin() + (size_t)(r + 1) * DEC, wc.begin() + (size_t)r * 2 * DEC + DEC);
+                bc[r] = bih[r] + bhh[r];
+            }
+            m->dec.wcat[l] = m->upload(wc);
+            m->dec.bcat[l] = m->upload(bc);
+        }
+        m->dec.wpred = m->upload(load_f32(g, "joint.pred.weight", (int64_t)JOINT * DEC));
+        m->dec.bpred = m->upload(load_f32(g, "joint.pred.bias", JOINT));
+        std::vector<float> wo = load_f32(g, "joint.joint_net.2.weight", (int64_t)VOCAB * JOINT), bo = load_f32(g, "joint.joint_net.2.bias", VOCAB);
+        wo.resize((size_t)1088 * JOINT, 0.0f);
+        bo.resize(1088, -INFINITY);
+        m->dec.wout = m->upload(wo);
+        m->dec.bout = m->upload(bo);
+        m->joint_enc_w = m->upload(load_f32(g, "joint.enc.weight", (int64_t)JOINT * D_MODEL));
+        m->joint_enc_b = m->upload(load_f32(g, "joint.enc.bias", JOINT));
+    }
+}
+
+}  // namespace
+
+namespace {
+
+constexpr int META_ROWS = 8;  // int arrays per batch: slot, wpos, valid, nvalid, n_frames, (3 spare)
+
+void alloc_state(nb200_model* m) {
+    const size_t S = (size_t)m->max_streams, L = (size_t)m->n_layers;
+    m->k_ring = m->alloc<float>(L * S * RING * D_MODEL);
+    m->v_ring = m->alloc<float>(L * S * RING * D_MODEL);
+    m->conv_cache = m->alloc<float>(L * S * CONV_CACHE * D_MODEL);
+    m->mel_overlap = m->alloc<float>(S * MEL_OVERLAP * N_MELS);
+    m->dstate.h = m->alloc<float>(S * 2 * DEC);
+    m->dstate.c = m->alloc<float>(S * 2 * DEC);
+    m->dstate.pend_h = m->alloc<float>(S * 2 * DEC);
+    m->dstate.pend_c = m->alloc<float>(S * 2 * DEC);
+    m->dstate.pend_p = m->alloc<float>(S * JOINT);
+    m->dstate.prev = m->alloc<int>(S);
+    for (int i = m->max_streams - 1; i >= 0; i--) m->free_slots.push_back(i);
+
+    const int B = m->cap_B = m->max_streams;
+    const Mode big(13);
+    const size_t rows = (size_t)B * MAX_T;
+    const size_t rows_pad = (rows + 127) / 128 * 128;
+    m->ws_mel = m->alloc<float>((size_t)B * big.chunk_mel * N_MELS);
+    m->ws_a2h = m->alloc<__half>((size_t)B * big.t2 * SUB_F2 * SUB_CH + 128 * SUB_CH);
+    m->ws_a3 = m->alloc<float>((size_t)B * big.t2 * SUB_F2 * SUB_CH);
+    m->ws_a5h = m->alloc<__half>((rows_pad + 128) * SUB_F3 * SUB_CH);
+    m->ws_x = m->alloc<float>(rows_pad * D_MODEL);
+    m->ws_q = m->alloc<float>(rows_pad * D_MODEL);
+    m->ws_g = m->alloc<float>(rows_pad * D_MODEL);
+    m->ws_e = m->alloc<float>(rows_pad * JOINT);
+    m->ws_a16 = m->alloc<__half>(rows_pad * D_MODEL);
+    m->ws_h16 = m->alloc<__half>(rows_pad * D_FF);
+    m->ws_posf = m->alloc<float>((size_t)128 * D_MODEL);
+    m->ws_pos16 = m->alloc<__half>((size_t)128 * D_MODEL);
+    operand_init(m->op_a2h, m->ws_a2h, B * big.t2 * SUB_F2, SUB_CH);
+    operand_init(m->op_a5h, m->ws_a5h, (int)rows * SUB_F3, SUB_CH);
+    m->ws_a6h = m->alloc<__half>((rows_pad + 128) * SUB_FEAT);
+    operand_init(m->op_a6h, m->ws_a6h, (int)rows_pad, SUB_FEAT);
+    operand_init(m->op_a16, m->ws_a16, (int)rows_pad, D_MODEL);
+    operand_init(m->op_h16, m->ws_h16, (int)rows_pad, D_FF);
+    operand_init(m->op_pos16, m->ws_pos16, 128, D_MODEL);
+    m->pcm_stride = HOP * big.shift + 360;
+    m->ws_pcm = m->alloc<int16_t>((size_t)B * m->pcm_stride);
+    m->ws_meta = m->alloc<int>((size_t)META_ROWS * B);
+    m->ws_meta64 = m->alloc<long long>(B);
+    m->ws_fp = m->alloc<int>(B);
+    m->ws_sym = m->alloc<int>(B);
+    m->ws_tok = m->alloc<int>((size_t)B * MAX_T * MAX_SYMBOLS);
+    m->ws_tokcnt = m->alloc<int>((size_t)2 * B);  // [B] counts + [B] margins (as float bits)
+    m->ws_unfinished = m->alloc<int>(1);
+    m->ws_hid = m->alloc<float>((size_t)B * JOINT);
+    m->ws_logits = m->alloc<float>((size_t)B * 1088);
+    m->ws_lx = m->alloc<float>((size_t)B * 2 * DEC);
+    m->ws_gates = m->alloc<float>((size_t)B * 4 * DEC);
+    m->ws_hp = m->alloc<float>((size_t)B * DEC);
+    m->h_pcm.reserve((size_t)B * m->pcm_stride);
+    m->h_meta.reserve((size_t)META_ROWS * B);
+    m->h_meta64.reserve(B);
+    m->h_tok.reserve((size_t)B * (MAX_T * MAX_SYMBOLS + 2) + 1);
+    for (auto& e : m->ev) CUDA_CHECK(cudaEventCreate(&e));
+}
+
+// linear_pos(PE(p)) for every layer: constant per latency mode, so it is computed once here instead of in every layer
+// of every chunk as the reference does (src/nemo-stream.cpp:516). Same arithmetic as any other encoder matmul.
+ModeCtx* get_mode(nb200_model* m, int rc) {
+    auto it = m->modes.find(rc);
+    if (it != m->modes.end()) return it->second.get();
+    auto ctx = std::make_unique<ModeCtx>(rc);
+    const Mode& md = ctx->mode;
+    ctx->pos_tab = m->alloc<float>((size_t)m->n_layers * md.npos * D_MODEL);
+    launch_pos_emb(m->st, m->ws_posf, -(md.T - 1), md.npos);
+    launch_cast_f16(m->st, m->ws_posf, m->ws_pos16, m->act_quant ? 1 : 0, md.npos, D_MODEL);
+    for (int l = 0; l < m->n_layers; l++) {
+        EpiParams ep;
+        ep.kind = EPI_STORE;
+        ep.out_f32 = ctx->pos_tab + (size_t)l * md.npos * D_MODEL;
+        ep.ldo = D_MODEL;
+        gemm(m->st, m->op_pos16, m->layers[l].wpos.op, md.npos, ep, m->simt);
+    }
+    CUDA_CHECK(cudaStreamSynchronize(m->st));
+    ModeCtx* r = ctx.get();
+    m->modes[rc] = std::move(ctx);
+    return r;
+}
+
+DecodeBatch decode_batch(nb200_model* m, int B, int T) {
+    DecodeBatch d{};
+    d.e = m->ws_e;
+    d.slot = m->ws_meta + 0 * m->cap_B;
+    d.nvalid = m->ws_meta + 3 * m->cap_B;
+    d.fp = m->ws_fp;
+    d.sym = m->ws_sym;
+    d.tok_out = m->ws_tok;
+    d.tok_cnt = m->ws_tokcnt;
+    d.min_margin = reinterpret_cast<float*>(m->ws_tokcnt + m->cap_B);
+    d.unfinished = m->ws_unfinished;
+    d.hid = m->ws_hid;
+    d.logits = m->ws_logits;
+    d.x = m->ws_lx;
+    d.gates = m->ws_gates;
+    d.hp = m->ws_hp;
+    d.B = B;
+    d.T = T;
+    return d;
+}
+
+// zero a slot's state and recompute its pending decoder state (prev = blank, h = c = 0)
+void reset_slot(nb200_model* m, int slot) {
+    const size_t S = (size_t)m->max_streams;
+    for (int l = 0; l < m->n_layers; l++) {
+        CUDA_CHECK(cudaMemsetAsync(m->k_ring + ((size_t)l * S + slot) * RING * D_MODEL, 0, sizeof(float) * RING * D_MODEL, m->st));
+        CUDA_CHECK(cudaMemsetAsync(m->v_ring + ((size_t)l * S + slot) * RING * D_MODEL, 0, sizeof(float) * RING * D_MODEL, m->st));
+        CUDA_CHECK(cudaMemsetAsync(m->conv_cache + ((size_t)l * S + slot) * CONV_CACHE * D_MODEL, 0, sizeof(float) * CONV_CACHE * D_MODEL, m->st));
+    }
+    CUDA_CHECK(cudaMemsetAsync(m->mel_overlap + (size_t)slot * MEL_OVERLAP * N_MELS, 0, sizeof(float) * MEL_OVERLAP * N_MELS, m->st));
+    CUDA_CHECK(cudaMemsetAsync(m->dstate.h + (size_t)slot * 2 * DEC, 0, sizeof(float) * 2 * DEC, m->st));
+    CUDA_CHECK(cudaMemsetAsync(m->dstate.c + (size_t)slot * 2 * DEC, 0, sizeof(float) * 2 * DEC, m->st));
+    const int blank = BLANK;
+    CUDA_CHECK(cudaMemcpyAsync(m->dstate.prev + slot, &blank, sizeof(int), cudaMemcpyHostToDevice, m->st));
+    CUDA_CHECK(cudaMemcpyAsync(m->ws_meta, &slot, sizeof(int), cudaMemcpyHostToDevice, m->st));
+    launch_decode_refresh(m->st, m->dec, m->dstate, decode_batch(m, 1, 1));
+    CUDA_CHECK(cudaStreamSynchronize(m->st));
+}
+
+// ---- small copy kernels of the step ---------------------------------------------------------------------
+// chunk[b][0:9] = overlap[slot[b]]; chunk[b][9+n_frames[b] : chunk_mel] = 0 (tail chunk of a finalize)
+__global__ void mel_assemble_kernel(float* chunk, const float* overlap, const int* slot, const int* n_frames, int chunk_mel) {
+    const int b = blockIdx.y, f = blockIdx.x, t = threadIdx.x;  // 128 threads
+    float* dst = chunk + ((size_t)b * chunk_mel + f) * N_MELS + t;
+    if (f < MEL_OVERLAP) *dst = overlap[((size_t)slot[b] * MEL_OVERLAP + f) * N_MELS + t];
+    else if (f >= MEL_OVERLAP + n_frames[b]) *dst = 0.0f;
+}
+// overlap[slot[b]] = chunk[b][shift : shift+9]
+__global__ void mel_save_overlap_kernel(const float* chunk, float* overlap, const int* slot, int chunk_mel, int shift) {
+    const int b = blockIdx.y, f = blockIdx.x, t = threadIdx.x;
+    overlap[((size_t)slot[b] * MEL_OVERLAP + f) * N_MELS + t] = chunk[((size_t)b * chunk_mel + shift + f) * N_MELS + t];
+}
+
+long long frames_available(long long n_samples) {  // src/preprocessor.cpp:320-328 with the 256-sample centre pad
+    return n_samples + 256 < N_FFT ? 0 : (n_samples + 256 - N_FFT) / HOP + 1;
+}
+
+struct BatchItem {
+    nb200_stream* s;
+    int n_frames;  // new mel frames computed for this chunk (shift, or fewer for a finalize tail)
+    int nvalid;    // encoder frames to decode
+};
+
+void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items);
+
+}  // namespace
+
+namespace {
+
+void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
+    const Mode& md = mc->mode;
+    const int B = (int)items.size(), T = md.T, M = B * T, capB = m->cap_B;
+    const int aq = m->act_quant ? 1 : 0;
+    const bool simt = m->simt;
+    cudaStream_t st = m->st;
+    const int stride = HOP * md.shift + 360;
+
+    // ---- host -> pinned staging: metadata + the PCM window of every item ----
+    int* meta = m->h_meta.p;
+    for (int b = 0; b < B; b++) {
+        nb200_stream* s = items[b].s;
+        meta[0 * capB + b] = s->slot;
+        meta[1 * capB + b] = s->wpos;
+        meta[2 * capB + b] = s->valid;
+        meta[3 * capB + b] = items[b].nvalid;
+        meta[4 * capB + b] = items[b].n_frames;
+        m->h_meta64.p[b] = ((long long)b * md.chunk_mel + MEL_OVERLAP) * N_MELS;
+        // element e of the window is absolute sample a0 + e; a0 = first new frame's first sample - 1 (pre-emphasis)
+        const long long a0 = (long long)HOP * md.shift * s->chunks_done - 257;
+        const int count = HOP * items[b].n_frames + 353;
+        int16_t* dst = m->h_pcm.p + (size_t)b * stride;
+        for (int e = 0; e < count; e++) {
+            const long long a = a0 + e, i = a - s->pcm_base;
+            dst[e] = (a >= 0 && i >= 0 && i < (long long)s->pcm.size()) ? s->pcm[(size_t)i] : (int16_t)0;
+        }
+        for (int e = count; e < stride; e++) dst[e] = 0;
+    }
+    CUDA_CHECK(cudaEventRecord(m->ev[0], st));
+    CUDA_CHECK(cudaMemcpyAsync(m->ws_pcm, m->h_pcm.p, (size_t)B * stride * sizeof(int16_t), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(m->ws_meta, meta, (size_t)META_ROWS * capB * sizeof(int), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(m->ws_meta64, m->h_meta64.p, (size_t)B * sizeof(long long), cudaMemcpyHostToDevice, st));
+    const int* d_slot = m->ws_meta + 0 * capB;
+    const int* d_wpos = m->ws_meta + 1 * capB;
+    const int* d_valid = m->ws_meta + 2 * capB;
+    const int* d_nframes = m->ws_meta + 4 * capB;
+
+    // ---- frontend: log-mel of the new samples, then dw-striding subsampling (src/nemo-ggml.cpp:954-1029) ----
+    mel_assemble_kernel<<<dim3(md.chunk_mel, B), N_MELS, 0, st>>>(m->ws_mel, m->mel_overlap, d_slot, d_nframes, md.chunk_mel);
+    NB_KERNEL_CHECK();
+    launch_mel(st, m->mel_tb, m->ws_pcm, stride, d_nframes, m->ws_meta64, m->ws_mel, B, md.shift);
+    for (int b = 0; b < B; b++) {
+        nb200_stream* s = items[b].s;
+        if ((s->taps & NB200_TAP_MEL) && items[b].n_frames > 0) {
+            const size_t n = (size_t)items[b].n_frames * N_MELS, old = s->tap_mel.size();
+            s->tap_mel.resize(old + n);
+            CUDA_CHECK(cudaMemcpyAsync(s->tap_mel.data() + old, m->ws_mel + ((size_t)b * md.chunk_mel + MEL_OVERLAP) * N_MELS,
+                                       n * sizeof(float), cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaStreamSynchronize(st));
+        }
+    }
+    launch_sub_stage1(st, m->sub, m->ws_mel, m->ws_a2h, B, md.chunk_mel, md.t1, md.t2);
+    mel_save_overlap_kernel<<<dim3(MEL_OVERLAP, B), N_MELS, 0, st>>>(m->ws_mel, m->mel_overlap, d_slot, md.chunk_mel, md.shift);
+    NB_KERNEL_CHECK();
+    {
+        EpiParams ep;  // pw3 + bias + ReLU -> fp32 (input of the fp32 depthwise conv5)
+        ep.kind = EPI_STORE; ep.act = ACT_RELU; ep.bias = m->sub_b3; ep.out_f32 = m->ws_a3; ep.ldo = SUB_CH;
+        gemm(st, m->op_a2h, m->sub_w3.op, B * md.t2 * SUB_F2, ep, simt);
+        launch_sub_stage2(st, m->sub, m->ws_a3, m->ws_a5h, B, md.t2, md.t3);
+        EpiParams e6;  // pw6 + bias + ReLU -> fp16 [B*T*17][256], whose rows (b,t) are the K=4352 operand of pre_encode.out
+        e6.kind = EPI_STORE_F16; e6.act = ACT_RELU; e6.bias = m->sub_b6; e6.out_f16 = m->ws_a6h; e6.ldo = SUB_CH; e6.act_quant = 0;
+        gemm(st, m->op_a5h, m->sub_w6.op, M * SUB_F3, e6, simt);
+        EpiParams eo;
+        eo.kind = EPI_STORE; eo.bias = m->sub_bout; eo.out_f32 = m->ws_x; eo.ldo = D_MODEL;
+        gemm(st, m->op_a6h, m->sub_wout.op, M, eo, simt);
+    }
+    CUDA_CHECK(cudaEventRecord(m->ev[1], st));
+
+    // ---- 24 cache-aware conformer layers (src/nemo-stream.cpp:605-690) ----
+    const size_t S = (size_t)m->max_streams;
+    launch_layernorm(st, m->ws_x, m->layers[0].ln_ff1_g, m->layers[0].ln_ff1_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M);
+    for (int l = 0; l < m->n_layers; l++) {
+        LayerW& L = m->layers[l];
+        EpiParams up;  // linear1 + SiLU (+ re-quantise) -> fp16 [M,4096]
+        up.kind = EPI_STORE_F16; up.act = ACT_SILU; up.act_quant = aq; up.out_f16 = m->ws_h16; up.ldo = D_FF;
+        EpiParams half;  // x += 0.5 * linear2(...)
+        half.kind = EPI_RESID; half.alpha = 0.5f; half.out_f32 = m->ws_x; half.ldo = D_MODEL;
+        EpiParams res = half;  // x += ...
+        res.alpha = 1.0f;
+        gemm(st, m->op_a16, L.ff1_w1.op, M, up, simt);
+        gemm(st, m->op_h16, L.ff1_w2.op, M, half, simt);
+        // self-attention
+        launch_layernorm(st, m->ws_x, L.ln_att_g, L.ln_att_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M);
+        float* kr = m->k_ring + (size_t)l * S * RING * D_MODEL;
+        float* vr = m->v_ring + (size_t)l * S * RING * D_MODEL;
+        EpiParams qkv;
+        qkv.kind = EPI_QKV; qkv.out_f32 = m->ws_q; qkv.k_ring = kr; qkv.v_ring = vr; qkv.slot = d_slot; qkv.wpos = d_wpos; qkv.T = T;
+        gemm(st, m->op_a16, L.wqkv.op, M, qkv, simt);
+        AttnArgs at{};
+        at.q = m->ws_q; at.k_ring = kr; at.v_ring = vr; at.pos = mc->pos_tab + (size_t)l * md.npos * D_MODEL;
+        at.bias_u = L.pos_u; at.bias_v = L.pos_v; at.slot = d_slot; at.wpos = d_wpos; at.valid = d_valid;
+        at.out = m->ws_a16; at.B = B; at.T = T; at.act_quant = aq;
+        launch_attention(st, at);
+        gemm(st, m->op_a16, L.wout.op, M, res, simt);
+        // convolution module
+        launch_layernorm(st, m->ws_x, L.ln_conv_g, L.ln_conv_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M);
+        EpiParams glu;
+        glu.kind = EPI_GLU; glu.out_f32 = m->ws_g; glu.ldo = D_MODEL;
+        gemm(st, m->op_a16, L.pw1.op, M, glu, simt);
+        ConvArgs cv{};
+        cv.g = m->ws_g; cv.conv_cache = m->conv_cache + (size_t)l * S * CONV_CACHE * D_MODEL; cv.w_dw = L.w_dw;
+        cv.ln_g = L.bn_g; cv.ln_b = L.bn_b; cv.slot = d_slot; cv.out = m->ws_a16; cv.B = B; cv.T = T; cv.act_quant = aq;
+        launch_dwconv(st, cv);
+        launch_conv_cache_update(st, cv);
+        gemm(st, m->op_a16, L.pw2.op, M, res, simt);
+        // FFN2 and the layer's output norm (fused with the next layer's first norm)
+        launch_layernorm(st, m->ws_x, L.ln_ff2_g, L.ln_ff2_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M);
+        gemm(st, m->op_a16, L.ff2_w1.op, M, up, simt);
+        gemm(st, m->op_h16, L.ff2_w2.op, M, half, simt);
+        if (l + 1 < m->n_layers)
+            launch_layernorm(st, m->ws_x, L.ln_out_g, L.ln_out_b, m->ws_x, m->layers[l + 1].ln_ff1_g, m->layers[l + 1].ln_ff1_b, m->ws_a16, aq, M);
+        else
+            launch_layernorm(st, m->ws_x, L.ln_out_g, L.ln_out_b, m->ws_x, nullptr, nullptr, nullptr, 0, M);
+    }
+    CUDA_CHECK(cudaEventRecord(m->ev[2], st));
+    for (int b = 0; b < B; b++) {
+        nb200_stream* s = items[b].s;
+        if (s->taps & NB200_TAP_ENC) {
+            const size_t n = (size_t)T * D_MODEL, old = s->tap_enc.size();
+            s->tap_enc.resize(old + n);
+            CUDA_CHECK(cudaMemcpyAsync(s->tap_enc.data() + old, m->ws_x + (size_t)b * T * D_MODEL, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaStreamSynchronize(st));
+        }
+    }
+
+    // ---- joint.enc over all frames, then the greedy rounds (src/nemo-stream.cpp:1106-1118, 840-930) ----
+    launch_sgemm(st, m->ws_x, m->joint_enc_w, m->joint_enc_b, m->ws_e, M, JOINT, D_MODEL, JOINT, nullptr);
+    CUDA_CHECK(cudaMemsetAsync(m->ws_fp, 0, sizeof(int) * B, st));
+    CUDA_CHECK(cudaMemsetAsync(m->ws_sym, 0, sizeof(int) * B, st));
+    CUDA_CHECK(cudaMemsetAsync(m->ws_tokcnt, 0, sizeof(int) * B, st));
+    CUDA_CHECK(cudaMemsetAsync(m->ws_tokcnt + capB, 0x7f, sizeof(int) * B, st));  // margins = 3.39e38
+    DecodeBatch db = decode_batch(m, B, T);
+    int max_valid = 0;
+    for (auto& it : items) max_valid = std::max(max_valid, it.nvalid);
+    long long rounds = 0;
+    int* h_unf = m->h_tok.p;  // word 0 of the pinned token buffer
+    int pending = max_valid;  // every stream needs at least nvalid rounds
+    while (pending > 0) {
+        for (int r = 0; r < pending; r++) launch_decode_round(st, m->dec, m->dstate, db);
+        rounds += pending;
+        CUDA_CHECK(cudaMemcpyAsync(h_unf, m->ws_unfinished, sizeof(int), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        pending = (*h_unf > 0) ? 4 : 0;
+        if (rounds > (long long)T * (MAX_SYMBOLS + 1) + 8) throw Error("decode loop did not terminate");
+    }
+    int* h_cnt = m->h_tok.p + 1;
+    int* h_margin = h_cnt + B;
+    int* h_toks = h_margin + B;
+    CUDA_CHECK(cudaMemcpyAsync(h_cnt, m->ws_tokcnt, sizeof(int) * B, cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaMemcpyAsync(h_margin, m->ws_tokcnt + capB, sizeof(int) * B, cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaMemcpyAsync(h_toks, m->ws_tok, sizeof(int) * (size_t)B * T * MAX_SYMBOLS, cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaEventRecord(m->ev[3], st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+
+    // ---- host bookkeeping ----
+    long long frames = 0, toks = 0;
+    for (int b = 0; b < B; b++) {
+        nb200_stream* s = items[b].s;
+        const int n = h_cnt[b];
+        for (int i = 0; i < n; i++) s->tokens.push_back(h_toks[(size_t)b * T * MAX_SYMBOLS + i]);
+        s->chunk_tokens.push_back(n);
+        float mg;
+        memcpy(&mg, &h_margin[b], sizeof(float));
+        s->chunk_margins.push_back(mg);
+        toks += n;
+        frames += items[b].nvalid;
+        s->chunks_done++;
+        s->wpos = (s->wpos + T) % RING;
+        s->valid = std::min(s->valid + T, LEFT);  // src/nemo-stream.cpp:1085
+        const long long keep_from = (long long)HOP * md.shift * s->chunks_done - 257;
+        if (keep_from > s->pcm_base) {
+            const size_t drop = (size_t)std::min<long long>(keep_from - s->pcm_base, (long long)s->pcm.size());
+            s->pcm.erase(s->pcm.begin(), s->pcm.begin() + drop);
+            s->pcm_base += drop;
+        }
+        m->stats.audio_seconds += (double)items[b].n_frames * HOP / 16000.0;
+    }
+    float ms01 = 0, ms12 = 0, ms23 = 0;
+    CUDA_CHECK(cudaEventElapsedTime(&ms01, m->ev[0], m->ev[1]));
+    CUDA_CHECK(cudaEventElapsedTime(&ms12, m->ev[1], m->ev[2]));
+    CUDA_CHECK(cudaEventElapsedTime(&ms23, m->ev[2], m->ev[3]));
+    m->stats.steps++;
+    m->stats.chunks += B;
+    m->stats.frames += frames;
+    m->stats.tokens += toks;
+    m->stats.decode_rounds += rounds;
+    m->stats.last_frontend_ms = ms01;
+    m->stats.last_encoder_ms = ms12;
+    m->stats.last_decoder_ms = ms23;
+    m->stats.last_step_gpu_ms = ms01 + ms12 + ms23;
+    m->stats.gpu_seconds += (ms01 + ms12 + ms23) * 1e-3;
+    m->stats.kernel_launches = g_launches;
+}
+
+}  // namespace
+
+// =====================================================================================================
+// C ABI
+// =====================================================================================================
+#define NB_TRY try {
+#define NB_CATCH(ret)                         \
+    }                                         \
+    catch (const std::exception& e) {         \
+        set_error(e.what());                  \
+        return ret;                           \
+    }
+
+extern "C" {
+
+const char* nb200_last_error(void) { return g_error.c_str(); }
+int nb200_version(void) { return 100; }
+
+nb200_model* nb200_model_load(const char* gguf_path, int device, int max_streams, int flags) {
+    nb200_model* m = nullptr;
+    try {
+        if (!gguf_path) throw Error("null path");
+        if (max_streams <= 0) max_streams = 64;
+        int n_dev = 0;
+        cudaError_t e = cudaGetDeviceCount(&n_dev);
+        if (e != cudaSuccess || n_dev == 0)
+            throw Error(std::string("no CUDA device: this backend has no CPU fallback (") + cudaGetErrorString(e) + ")");
+        if (device < 0 || device >= n_dev) throw Error("CUDA device ordinal out of range");
+        CUDA_CHECK(cudaSetDevice(device));
+        cudaDeviceProp prop;
+        CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+        if (prop.major != 10) throw Error(std::string("this library is built for sm_100a (B200); found ") + prop.name);
+        m = new nb200_model();
+        m->device = device;
+        m->max_streams = max_streams;
+        CUDA_CHECK(cudaStreamCreateWithFlags(&m->st, cudaStreamNonBlocking));
+        build_model(m, gguf_path, flags);
+        alloc_state(m);
+        CUDA_CHECK(cudaStreamSynchronize(m->st));
+        return m;
+    } catch (const std::exception& e) {
+        set_error(e.what());
+        delete m;
+        return nullptr;
+    }
+}
+
+void nb200_model_free(nb200_model* m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    cudaDeviceSynchronize();
+    delete m;
+}
+
+int nb200_model_info(const nb200_model* m, nb200_info* out) {
+    if (!m || !out) return NB200_ERR;
+    *out = m->info;
+    return NB200_OK;
+}
+
+const char* nb200_model_token(const nb200_model* m, int32_t id) {
+    if (!m || id < 0 || id >= (int)m->vocab.size()) return nullptr;
+    return m->vocab[id].c_str();
+}
+
+int nb200_tokens_to_text(const nb200_model* m, const int32_t* tokens, int n, char* out, int cap) {
+    if (!m || (!tokens && n > 0) || !out || cap <= 0) return NB200_ERR;
+    std::string text;
+    for (int i = 0; i < n; i++) {
+        if (tokens[i] < 0 || tokens[i] >= (int)m->vocab.size()) continue;
+        text += m->vocab[tokens[i]];
+    }
+    std::string res;  // U+2581 (E2 96 81) -> space, src/nemo-ggml.cpp:1556-1583
+    for (size_t i = 0; i < text.size();) {
+        if (i + 2 < text.size() && (unsigned char)text[i] == 0xE2 && (unsigned char)text[i + 1] == 0x96 && (unsigned char)text[i + 2] == 0x81) {
+            res += ' ';
+            i += 3;
+        } else {
+            res += text[i++];
+        }
+    }
+    const int w = std::min((int)res.size(), cap - 1);
+    memcpy(out, res.data(), w);
+    out[w] = 0;
+    return w;
+}
+
+nb200_stream* nb200_stream_create(nb200_model* m, int right_context) {
+    NB_TRY
+    if (!m) throw Error("null model");
+    if (right_context != 0 && right_context != 1 && right_context != 6 && right_context != 13)
+        throw Error("right_context must be one of 0, 1, 6, 13 (src/nemo-stream.h:15-20)");
+    if (m->free_slots.empty()) throw Error("no free stream slot (raise max_streams at model load)");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    get_mode(m, right_context);
+    nb200_stream* s = new nb200_stream();
+    s->model = m;
+    s->rc = right_context;
+    s->slot = m->free_slots.back();
+    m->free_slots.pop_back();
+    reset_slot(m, s->slot);
+    m->streams.push_back(s);
+    return s;
+    NB_CATCH(nullptr)
+}
+
+void nb200_stream_free(nb200_stream* s) {
+    if (!s) return;
+    nb200_model* m = s->model;
+    m->free_slots.push_back(s->slot);
+    m->streams.erase(std::remove(m->streams.begin(), m->streams.end(), s), m->streams.end());
+    delete s;
+}
+
+int nb200_stream_reset(nb200_stream* s) {
+    NB_TRY
+    if (!s) throw Error("null stream");
+    CUDA_CHECK(cudaSetDevice(s->model->device));
+    reset_slot(s->model, s->slot);
+    s->pcm.clear();
+    s->pcm_base = s->samples_total = s->chunks_done = 0;
+    s->finalize_requested = s->finalized = false;
+    s->wpos = s->valid = 0;
+    s->tokens.clear();
+    s->poll_cursor = 0;
+    s->chunk_tokens.clear();
+    s->chunk_margins.clear();
+    s->tap_mel.clear();
+    s->tap_enc.clear();
+    return NB200_OK;
+    NB_CATCH(NB200_ERR)
+}
+
+int nb200_stream_feed(nb200_stream* s, const int16_t* pcm, int n_samples) {
+    NB_TRY
+    if (!s) throw Error("null stream");
+    if (n_samples <= 0 || !pcm) return NB200_OK;  // like the reference: nothing to do (src/nemo-stream.cpp:1150)
+    if (s->finalized || s->finalize_requested) throw Error("stream already finalized; reset it first");
+    s->pcm.insert(s->pcm.end(), pcm, pcm + n_samples);
+    s->samples_total += n_samples;
+    return NB200_OK;
+    NB_CATCH(NB200_ERR)
+}
+
+static int full_chunks_ready(const nb200_stream* s) {
+    const Mode md(s->rc);
+    const long long frames = frames_available(s->samples_total);
+    const long long have = frames - (long long)md.shift * s->chunks_done;
+    return have < md.shift ? 0 : (int)(have / md.shift);
+}
+
+static int tail_frames(const nb200_stream* s) {  // new mel frames left for a finalize tail (src/nemo-stream.cpp:1240-1244)
+    const Mode md(s->rc);
+    return (int)(frames_available(s->samples_total) - (long long)md.shift * s->chunks_done);
+}
+
+int nb200_stream_finalize(nb200_stream* s) {
+    if (!s) return NB200_ERR;
+    if (!s->finalized) s->finalize_requested = true;
+    return NB200_OK;
+}
+
+int nb200_stream_ready_chunks(const nb200_stream* s) {
+    if (!s || s->finalized) return 0;
+    int n = full_chunks_ready(s);
+    if (s->finalize_requested) {
+        const Mode md(s->rc);
+        const int rem = tail_frames(s) - n * md.shift;
+        if (rem / 8 > 0) n++;
+    }
+    return n;
+}
+
+int nb200_step(nb200_model* m) {
+    NB_TRY
+    if (!m) throw Error("null model");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    std::map<int, std::vector<BatchItem>> groups;
+    for (nb200_stream* s : m->streams) {
+        if (s->finalized) continue;
+        const Mode md(s->rc);
+        if (full_chunks_ready(s) > 0) {
+            groups[s->rc].push_back({s, md.shift, md.T});
+        } else if (s->finalize_requested) {
+            const int rem = tail_frames(s);
+            const int n_valid = rem / 8;  // floor(real_new / subsampling_factor), src/nemo-stream.cpp:1243
+            if (n_valid > 0) groups[s->rc].push_back({s, rem, n_valid});
+            s->finalized = true;
+            s->finalize_requested = false;
+        }
+    }
+    int total = 0;
+    for (auto& kv : groups) {
+        run_batch(m, get_mode(m, kv.first), kv.second);
+        total += (int)kv.second.size();
+    }
+    return total;
+    NB_CATCH(NB200_ERR)
+}
+
+int nb200_drain(nb200_model* m) {
+    int total = 0;
+    for (;;) {
+        const int n = nb200_step(m);
+        if (n < 0) return n;
+        if (n == 0) return total;
+        total += n;
+    }
+}
+
+int nb200_stream_poll_tokens(nb200_stream* s, int32_t* out, int cap) {
+    if (!s || (!out && cap > 0)) return NB200_ERR;
+    const int n = std::min<int>(cap, (int)(s->tokens.size() - s->poll_cursor));
+    for (int i = 0; i < n; i++) out[i] = s->tokens[s->poll_cursor + i];
+    s->poll_cursor += n;
+    return n;
+}
+
+int nb200_stream_get_tokens(const nb200_stream* s, int32_t* out, int cap) {
+    if (!s) return NB200_ERR;
+    const int n = std::min<int>(cap, (int)s->tokens.size());
+    for (int i = 0; i < n; i++) out[i] = s->tokens[i];
+    return (int)s->tokens.size();
+}
+
+int nb200_stream_chunk_token_counts(const nb200_stream* s, int32_t* out, int cap) {
+    if (!s) return NB200_ERR;
+    const int n = std::min<int>(cap, (int)s->chunk_tokens.size());
+    for (int i = 0; i < n; i++) out[i] = s->chunk_tokens[i];
+    return (int)s->chunk_tokens.size();
+}
+
+int nb200_stream_chunk_margins(const nb200_stream* s, float* out, int cap) {
+    if (!s) return NB200_ERR;
+    const int n = std::min<int>(cap, (int)s->chunk_margins.size());
+    for (int i = 0; i < n; i++) out[i] = s->chunk_margins[i];
+    return (int)s->chunk_margins.size();
+}
+
+int nb200_stream_set_taps(nb200_stream* s, int taps) {
+    if (!s) return NB200_ERR;
+    s->taps = taps;
+    return NB200_OK;
+}
+
+int64_t nb200_stream_fetch_tap(const nb200_stream* s, int tap, float* out, int64_t cap) {
+    if (!s) return NB200_ERR;
+    const std::vector<float>& v = (tap == NB200_TAP_MEL) ? s->tap_mel : s->tap_enc;
+    const int64_t n = std::min<int64_t>(cap, (int64_t)v.size());
+    if (out && n > 0) memcpy(out, v.data(), (size_t)n * sizeof(float));
+    return (int64_t)v.size();
+}
+
+int nb200_get_stats(const nb200_model* m, nb200_stats* out) {
+    if (!m || !out) return NB200_ERR;
+    *out = m->stats;
+    out->kernel_launches = g_launches;
+    return NB200_OK;
+}
+
+int nb200_mel_batch(nb200_model* m, const int16_t* pcm, int n_streams, int n_samples, float* mel_out) {
+    NB_TRY
+    if (!m || !pcm || !mel_out) throw Error("null argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    const int nf = (int)frames_available(n_samples);
+    if (nf <= 0 || n_streams <= 0) return 0;
+    const int stride = HOP * (nf - 1) + N_FFT + 1;
+    std::vector<int16_t> win((size_t)n_streams * stride, 0);
+    for (int b = 0; b < n_streams; b++)
+        for (int e = 0; e < stride; e++) {
+            const long long a = (long long)e - 257;  // a0 = -257: 256 zeros of centre padding + the pre-emphasis sample
+            if (a >= 0 && a < n_samples) win[(size_t)b * stride + e] = pcm[(size_t)b * n_samples + a];
+        }
+    std::vector<int> nfr(n_streams, nf);
+    std::vector<long long> off(n_streams);
+    for (int b = 0; b < n_streams; b++) off[b] = (long long)b * nf * N_MELS;
+    int16_t* d_pcm = dalloc<int16_t>(win.size());
+    int* d_nf = dalloc<int>(n_streams);
+    long long* d_off = dalloc<long long>(n_streams);
+    float* d_mel = dalloc<float>((size_t)n_streams * nf * N_MELS);
+    CUDA_CHECK(cudaMemcpyAsync(d_pcm, win.data(), win.size() * sizeof(int16_t), cudaMemcpyHostToDevice, m->st));
+    CUDA_CHECK(cudaMemcpyAsync(d_nf, nfr.data(), n_streams * sizeof(int), cudaMemcpyHostToDevice, m->st));
+    CUDA_CHECK(cudaMemcpyAsync(d_off, off.data(), n_streams * sizeof(long long), cudaMemcpyHostToDevice, m->st));
+    launch_mel(m->st, m->mel_tb, d_pcm, stride, d_nf, d_off, d_mel, n_streams, nf);
+    CUDA_CHECK(cudaMemcpyAsync(mel_out, d_mel, (size_t)n_streams * nf * N_MELS * sizeof(float), cudaMemcpyDeviceToHost, m->st));
+    CUDA_CHECK(cudaStreamSynchronize(m->st));
+    cudaFree(d_pcm);
+    cudaFree(d_nf);
+    cudaFree(d_off);
+    cudaFree(d_mel);
+    return nf;
+    NB_CATCH(NB200_ERR)
+}
+
+int nb200_debug_matmul(nb200_model* m, const char* tensor_name, const float* x, int M, float* y) {
+    NB_TRY
+    if (!m || !tensor_name || !x || !y || M <= 0) throw Error("bad argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    auto it = m->by_name.find(tensor_name);
+    if (it == m->by_name.end()) throw Error(std::string("no such (unfused) matrix: ") + tensor_name);
+    const Operand& W = it->second->op;
+    const int K = W.K, N = W.rows;
+    if (K % 1024 != 0) throw Error("debug_matmul supports K multiple of 1024");
+    const int Mp = (M + 127) / 128 * 128;
+    float* dx = dalloc<float>((size_t)M * K);
+    __half* dx16 = dalloc<__half>((size_t)Mp * K);
+    float* dy = dalloc<float>((size_t)M * N);
+    CUDA_CHECK(cudaMemsetAsync(dx16, 0, (size_t)Mp * K * sizeof(__half), m->st));
+    CUDA_CHECK(cudaMemcpyAsync(dx, x, (size_t)M * K * sizeof(float), cudaMemcpyHostToDevice, m->st));
+    launch_cast_f16(m->st, dx, dx16, m->act_quant ? 1 : 0, M, K);
+    Operand A;
+    operand_init(A, dx16, Mp, K);
+    EpiParams ep;
+    ep.kind = EPI_STORE;
+    ep.out_f32 = dy;
+    ep.ldo = N;
+    gemm(m->st, A, W, M, ep, m->simt);
+    CUDA_CHECK(cudaMemcpyAsync(y, dy, (size_t)M * N * sizeof(float), cudaMemcpyDeviceToHost, m->st));
+    CUDA_CHECK(cudaStreamSynchronize(m->st));
+    cudaFree(dx);
+    cudaFree(dx16);
+    cudaFree(dy);
+    return NB200_OK;
+    NB_CATCH(NB200_ERR)
+}
+
+}  // extern "C"

@@ -1,0 +1,149 @@
+// frontend.cu — log-mel preprocessor and the direct-convolution stages of the dw-striding subsampling.
+//
+// Mel (reference: src/preprocessor.cpp:330-395): one CTA per (frame, stream). The operation ORDER of the reference is
+// mirrored so that fp32 results agree to an ulp of logf: pre-emphasis (:349-356), window (:184-194), bit-reversed
+// radix-2 DIT FFT with the host libm twiddle table (:113-161), sqrtf then re-square (:200-203,:363-368), sequential
+// mel sum over FFT bins (:374-383). Every multiply/add is an explicit round-to-nearest intrinsic so nvcc cannot
+// contract them into FMAs (the reference binary is built without FMA, Makefile:7). Zero filterbank weights are skipped:
+// adding +0 never changes an fp32 sum, so the result is bit-identical to the dense 257-term loop.
+#include "kernels.cuh"
+
+namespace nb {
+
+__global__ void __launch_bounds__(256) mel_kernel(MelTables tb, const int16_t* __restrict__ pcm, int pcm_stride,
+                                                  const int* __restrict__ n_frames, const long long* __restrict__ out_off,
+                                                  float* __restrict__ mel_out) {
+    const int f = blockIdx.x, b = blockIdx.y;
+    if (f >= n_frames[b]) return;
+    __shared__ float xs[N_FFT + 1];
+    __shared__ float re[N_FFT], im[N_FFT];
+    __shared__ float pw[N_BINS];
+    const int t = threadIdx.x;
+    const int16_t* src = pcm + (size_t)b * pcm_stride + (size_t)f * HOP;
+    for (int i = t; i < N_FFT + 1; i += 256) xs[i] = __fmul_rn((float)src[i], 1.0f / 32768.0f);
+    __syncthreads();
+    for (int i = t; i < N_FFT; i += 256) {
+        float y = __fsub_rn(xs[i + 1], __fmul_rn(0.97f, xs[i]));
+        y = __fmul_rn(y, tb.win512[i]);
+        int r = __brev((unsigned)i) >> 23;  // 9-bit reversal
+        re[r] = y;
+        im[r] = 0.0f;
+    }
+    __syncthreads();
+#pragma unroll 1
+    for (int lg = 1; lg <= 9; lg++) {
+        const int m2 = 1 << (lg - 1);
+        const int j = t & (m2 - 1);
+        const int i1 = ((t >> (lg - 1)) << lg) + j;
+        const int i2 = i1 + m2;
+        const int idx = j << (9 - lg);
+        const float wr = tb.cos_tbl[idx];
+        const float wi = -tb.sin_tbl[idx];
+        const float r2 = re[i2], q2 = im[i2], r1 = re[i1], q1 = im[i1];
+        const float tr = __fsub_rn(__fmul_rn(wr, r2), __fmul_rn(wi, q2));
+        const float ti = __fadd_rn(__fmul_rn(wr, q2), __fmul_rn(wi, r2));
+        re[i2] = __fsub_rn(r1, tr);
+        im[i2] = __fsub_rn(q1, ti);
+        re[i1] = __fadd_rn(r1, tr);
+        im[i1] = __fadd_rn(q1, ti);
+        __syncthreads();
+    }
+    for (int k = t; k < N_BINS; k += 256) {
+        float mag = __fsqrt_rn(__fadd_rn(__fmul_rn(re[k], re[k]), __fmul_rn(im[k], im[k])));
+        pw[k] = __fmul_rn(mag, mag);
+    }
+    __syncthreads();
+    if (t < N_MELS) {
+        const int2 rg = tb.fb_range[t];
+        float sum = 0.0f;
+        for (int k = rg.x; k < rg.y; k++) sum = __fadd_rn(sum, __fmul_rn(tb.fbT[k * N_MELS + t], pw[k]));
+        mel_out[out_off[b] + (long long)f * N_MELS + t] = logf(__fadd_rn(sum, 5.960464477539063e-8f));
+    }
+}
+
+void launch_mel(cudaStream_t st, const MelTables& tb, const int16_t* pcm, int pcm_stride, const int* n_frames,
+                const long long* out_off, float* mel_out, int B, int max_frames) {
+    if (B <= 0 || max_frames <= 0) return;
+    mel_kernel<<<dim3(max_frames, B), 256, 0, st>>>(tb, pcm, pcm_stride, n_frames, out_off, mel_out);
+    NB_KERNEL_CHECK();
+}
+
+// ---- subsampling stage 1: conv0 (1->256, 3x3 s2, fp16-rounded operands) + ReLU + depthwise conv2 (3x3 s2) ----------
+// Causal zero padding (2 before, 1 after) on both axes at every stage (src/nemo-ggml.cpp:905-913). One CTA per
+// (h2, stream): thread = channel; the 7 mel rows feeding this output row sit in shared memory, fp16-rounded.
+__global__ void __launch_bounds__(256) sub_stage1_kernel(SubWeights w, const float* __restrict__ mel, __half* __restrict__ out,
+                                                         int chunk_mel, int t1, int t2) {
+    const int h2 = blockIdx.x, b = blockIdx.y, c = threadIdx.x;
+    __shared__ float ms[7][N_MELS + 4];  // column index = mel bin + 2 (two zero columns on the left, two on the right)
+    const float* msrc = mel + (size_t)b * chunk_mel * N_MELS;
+    for (int i = c; i < 7 * (N_MELS + 4); i += 256) {
+        int r = i / (N_MELS + 4), col = i % (N_MELS + 4);
+        int tt = 4 * h2 - 6 + r, ff = col - 2;
+        float v = 0.0f;
+        if (tt >= 0 && tt < chunk_mel && ff >= 0 && ff < N_MELS) v = __half2float(__float2half_rn(msrc[(size_t)tt * N_MELS + ff]));
+        ms[r][col] = v;
+    }
+    float k0[9], k2[9];
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        k0[i] = w.w0[c * 9 + i];
+        k2[i] = w.w2[c * 9 + i];
+    }
+    const float bias0 = w.b0[c], bias2 = w.b2[c];
+    __syncthreads();
+    __half* orow = out + ((size_t)(b * t2 + h2) * SUB_F2) * SUB_CH + c;
+    for (int w2 = 0; w2 < SUB_F2; w2++) {
+        float acc = bias2;
+#pragma unroll
+        for (int kh = 0; kh < 3; kh++) {
+            const int h1 = 2 * h2 + kh - 2;
+            if (h1 < 0 || h1 >= t1) continue;  // zero padding row of the conv0 output
+#pragma unroll
+            for (int kw = 0; kw < 3; kw++) {
+                const int w1 = 2 * w2 + kw - 2;
+                if (w1 < 0 || w1 >= SUB_F1) continue;
+                // conv0 output at (h1, w1): mel rows 2*h1-2 .. 2*h1 -> smem rows 2*kh .. 2*kh+2; columns 2*w1-2 .. 2*w1
+                float a = 0.0f;
+#pragma unroll
+                for (int i = 0; i < 3; i++)
+#pragma unroll
+                    for (int j = 0; j < 3; j++) a = fmaf(k0[i * 3 + j], ms[2 * kh + i][2 * w1 + j], a);
+                a = fmaxf(a + bias0, 0.0f);
+                acc = fmaf(k2[kh * 3 + kw], a, acc);
+            }
+        }
+        orow[(size_t)w2 * SUB_CH] = __float2half_rn(acc);
+    }
+}
+
+void launch_sub_stage1(cudaStream_t st, const SubWeights& w, const float* mel, __half* out, int B, int chunk_mel, int t1, int t2) {
+    sub_stage1_kernel<<<dim3(t2, B), 256, 0, st>>>(w, mel, out, chunk_mel, t1, t2);
+    NB_KERNEL_CHECK();
+}
+
+// ---- subsampling stage 2: depthwise conv5 over relu(pw3), only the rows that survive the drop of 2 frames ----------
+__global__ void __launch_bounds__(256) sub_stage2_kernel(SubWeights w, const float* __restrict__ a3, __half* __restrict__ out,
+                                                         int t2, int t3) {
+    const int w3 = blockIdx.x, hh = blockIdx.y, b = blockIdx.z, c = threadIdx.x;
+    const int h3 = hh + 2;
+    float acc = w.b5[c];
+#pragma unroll
+    for (int kh = 0; kh < 3; kh++) {
+        const int h2 = 2 * h3 + kh - 2;
+        if (h2 < 0 || h2 >= t2) continue;
+#pragma unroll
+        for (int kw = 0; kw < 3; kw++) {
+            const int w2 = 2 * w3 + kw - 2;
+            if (w2 < 0 || w2 >= SUB_F2) continue;
+            acc = fmaf(w.w5[c * 9 + kh * 3 + kw], a3[((size_t)(b * t2 + h2) * SUB_F2 + w2) * SUB_CH + c], acc);
+        }
+    }
+    out[((size_t)(b * (t3 - 2) + hh) * SUB_F3 + w3) * SUB_CH + c] = __float2half_rn(acc);
+}
+
+void launch_sub_stage2(cudaStream_t st, const SubWeights& w, const float* a3, __half* out, int B, int t2, int t3) {
+    sub_stage2_kernel<<<dim3(SUB_F3, t3 - 2, B), 256, 0, st>>>(w, a3, out, t2, t3);
+    NB_KERNEL_CHECK();
+}
+
+}  // namespace nb

@@ -1,0 +1,324 @@
+// gemm.cu — tcgen05/TMEM/TMA GEMM and its CUDA-core checker. See gemm.cuh.
+#include "gemm.cuh"
+
+#include <cudaTypedefs.h>
+
+namespace nb {
+
+long long g_launches = 0;
+
+// ------------------------------------------------------------------------------------------------
+// PTX wrappers (sm_100a)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(bar), "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
+}
+
+// Shared-memory matrix descriptor for a K-major fp16 tile whose rows are 128 bytes (64 halves), 128B-swizzled:
+// start>>4 | LBO=1 (ignored for swizzled K-major) | SBO = 1024 B between 8-row groups | version 1 | SWIZZLE_128B.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+// Instruction descriptor, kind::f16: D=f32 (bits 4-5 = 1), A=B=f16 (0), both K-major, N>>3 at 17, M>>4 at 24.
+__host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
+    return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ------------------------------------------------------------------------------------------------
+// tcgen05 kernel: one 128 x BN output tile per CTA
+// ------------------------------------------------------------------------------------------------
+constexpr int TC_BM = 128, TC_BK = 64, TC_THREADS = 192;
+
+template <int BN, int STAGES>
+struct TcSmem {
+    static constexpr int A_BYTES = TC_BM * TC_BK * 2;
+    static constexpr int B_BYTES = BN * TC_BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN, int STAGES>
+__global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
+                                                            const __grid_constant__ CUtensorMap map_w, int M, int K,
+                                                            EpiParams epi) {
+    using S = TcSmem<BN, STAGES>;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;  // 128B swizzle atoms need 1024-byte alignment
+    uint8_t* smem = smem_raw + (base - raw);
+    const uint32_t bars = base + STAGES * S::STAGE_BYTES;
+    // barrier layout: full[STAGES], empty[STAGES], accum, then the TMEM base address word
+    auto full_bar = [&](int s) { return bars + 8u * s; };
+    auto empty_bar = [&](int s) { return bars + 8u * (STAGES + s); };
+    const uint32_t accum_bar = bars + 8u * (2 * STAGES);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + STAGES * S::STAGE_BYTES + 8 * (2 * STAGES + 1));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_tile = blockIdx.x, m_tile = blockIdx.y;
+    const int num_k = K / TC_BK;
+    constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(full_bar(s), 1);
+            mbar_init(empty_bar(s), 1);
+        }
+        mbar_init(accum_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {  // ===== TMA producer =====
+            for (int kb = 0; kb < num_k; kb++) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (kb / STAGES) & 1;
+                mbar_wait(empty_bar(s), ph ^ 1);
+                mbar_expect_tx(full_bar(s), S::STAGE_BYTES);
+                const uint32_t a_dst = base + s * S::STAGE_BYTES;
+                tma_load_2d(a_dst, &map_a, full_bar(s), kb * TC_BK, m_tile * TC_BM);
+                tma_load_2d(a_dst + S::A_BYTES, &map_w, full_bar(s), kb * TC_BK, n_tile * BN);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {  // ===== MMA issuer =====
+            constexpr uint32_t idesc = make_idesc_f16(TC_BM, BN);
+            for (int kb = 0; kb < num_k; kb++) {
+                const int s = kb % STAGES;
+                const uint32_t ph = (kb / STAGES) & 1;
+                mbar_wait(full_bar(s), ph);
+                tc_fence_after();
+                const uint32_t a_addr = base + s * S::STAGE_BYTES;
+                const uint64_t adesc = make_smem_desc(a_addr);
+                const uint64_t bdesc = make_smem_desc(a_addr + S::A_BYTES);
+#pragma unroll
+                for (int k = 0; k < TC_BK / 16; k++) {
+                    // advance 16 halves = 32 bytes along K inside the swizzle atom: +2 in the (addr>>4) field
+                    umma_f16(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                }
+                umma_commit(empty_bar(s));  // frees the smem slot when these MMAs retire
+            }
+            umma_commit(accum_bar);  // accumulator complete
+        }
+    } else {  // ===== epilogue warps 2..5: TMEM lanes 32*(warp%4) .. +31 =====
+        const int lane_base = (warp & 3) * 32;
+        mbar_wait(accum_bar, 0);
+        tc_fence_after();
+        const int m = m_tile * TC_BM + lane_base + lane;
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+            float acc[32];
+            tmem_ld32(tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)c, acc);  // warp-collective
+            if (m < M) epilogue_apply(epi, m, n_tile * BN + c, acc);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// CUDA-core checker: 64 x 64 tile, 128 threads, thread = (row, 32-column half)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) gemm_simt_kernel(const __half* __restrict__ A, const __half* __restrict__ W, int M,
+                                                       int N, int K, EpiParams epi) {
+    __shared__ float As[32][64 + 1];
+    __shared__ float Ws[32][64 + 4];
+    const int t = threadIdx.x;
+    const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+    const int row = t & 63, half = t >> 6;
+    float acc[32];
+#pragma unroll
+    for (int j = 0; j < 32; j++) acc[j] = 0.0f;
+    const int lr = t >> 1, lk = (t & 1) * 16;
+    for (int k0 = 0; k0 < K; k0 += 32) {
+        {
+            uint4 u0 = make_uint4(0, 0, 0, 0), u1 = u0;
+            if (m0 + lr < M) {
+                const uint4* src = reinterpret_cast<const uint4*>(A + (size_t)(m0 + lr) * K + k0 + lk);
+                u0 = src[0];
+                u1 = src[1];
+            }
+            const __half* h0 = reinterpret_cast<const __half*>(&u0);
+            const __half* h1 = reinterpret_cast<const __half*>(&u1);
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                As[lk + j][lr] = __half2float(h0[j]);
+                As[lk + 8 + j][lr] = __half2float(h1[j]);
+            }
+            const uint4* wsrc = reinterpret_cast<const uint4*>(W + (size_t)(n0 + lr) * K + k0 + lk);
+            uint4 w0 = wsrc[0], w1 = wsrc[1];
+            const __half* g0 = reinterpret_cast<const __half*>(&w0);
+            const __half* g1 = reinterpret_cast<const __half*>(&w1);
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                Ws[lk + j][lr] = __half2float(g0[j]);
+                Ws[lk + 8 + j][lr] = __half2float(g1[j]);
+            }
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int k = 0; k < 32; k++) {
+            const float a = As[k][row];
+            const float4* wrow = reinterpret_cast<const float4*>(&Ws[k][half * 32]);
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                float4 w = wrow[j];
+                acc[4 * j + 0] = fmaf(a, w.x, acc[4 * j + 0]);
+                acc[4 * j + 1] = fmaf(a, w.y, acc[4 * j + 1]);
+                acc[4 * j + 2] = fmaf(a, w.z, acc[4 * j + 2]);
+                acc[4 * j + 3] = fmaf(a, w.w, acc[4 * j + 3]);
+            }
+        }
+        __syncthreads();
+    }
+    const int m = m0 + row;
+    if (m < M) epilogue_apply(epi, m, n0 + half * 32, acc);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
+    static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+        if (qres != cudaDriverEntryPointSuccess || !p) throw Error("cuTensorMapEncodeTiled not available from the driver");
+        fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+    }
+    return fn;
+}
+
+static void make_map(CUtensorMap* map, const __half* ptr, int rows, int K, int box_rows) {
+    cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    cuuint64_t gstride[1] = {(cuuint64_t)K * 2};
+    cuuint32_t box[2] = {(cuuint32_t)TC_BK, (cuuint32_t)box_rows};
+    cuuint32_t estride[2] = {1, 1};
+    CUresult r = get_encode_fn()(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (void*)ptr, gdim, gstride, box, estride,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) throw Error("cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+}
+
+void operand_init(Operand& op, const __half* ptr, int rows, int K) {
+    if (K % TC_BK != 0) throw Error("GEMM operand K must be a multiple of 64");
+    if (((uintptr_t)ptr & 15) != 0) throw Error("GEMM operand must be 16-byte aligned");
+    op.ptr = ptr;
+    op.rows = rows;
+    op.K = K;
+    make_map(&op.map128, ptr, rows, K, 128);
+    make_map(&op.map64, ptr, rows, K, 64);
+}
+
+template <int BN, int STAGES>
+static void launch_tc(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiParams& epi) {
+    using S = TcSmem<BN, STAGES>;
+    static bool configured = false;
+    if (!configured) {
+        CUDA_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+        configured = true;
+    }
+    dim3 grid(W.rows / BN, cdiv(M, TC_BM));
+    gemm_tc_kernel<BN, STAGES><<<grid, TC_THREADS, S::TOTAL, st>>>(A.map128, BN == 128 ? W.map128 : W.map64, M, A.K, epi);
+    NB_KERNEL_CHECK();
+}
+
+void gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiParams& epi, bool use_simt) {
+    if (M <= 0) return;
+    if (A.K != W.K) throw Error("GEMM: K mismatch");
+    if (M > A.rows) throw Error("GEMM: M exceeds the activation buffer");
+    const int N = W.rows;
+    if (N % 64 != 0) throw Error("GEMM: N must be a multiple of 64");
+    if (use_simt) {
+        dim3 grid(N / 64, cdiv(M, 64));
+        gemm_simt_kernel<<<grid, 128, 0, st>>>(A.ptr, W.ptr, M, N, A.K, epi);
+        NB_KERNEL_CHECK();
+        return;
+    }
+    // Tile width: 128 when that already gives >= 1 wave of CTAs (or N is not a multiple of 128), else 64.
+    const int m_tiles = cdiv(M, TC_BM);
+    if (N % 128 == 0 && (N / 128) * m_tiles >= 148) {
+        launch_tc<128, 3>(st, A, W, M, epi);
+    } else {
+        launch_tc<64, 4>(st, A, W, M, epi);
+    }
+}
+
+}  // namespace nb

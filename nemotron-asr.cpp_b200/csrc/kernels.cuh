@@ -1,0 +1,121 @@
+// kernels.cuh — launchers of the bandwidth-bound kernels (frontend.cu, encoder.cu, decoder.cu).
+#pragma once
+#include "common.cuh"
+
+namespace nb {
+
+// ---- frontend.cu ---------------------------------------------------------------------------------
+struct MelTables {           // device pointers, built once per model from the GGUF filterbank/window
+    const float* win512;     // hann-400 centred in 512 (src/preprocessor.cpp:297-299)
+    const float* cos_tbl;    // host libm cosf/sinf of 2*pi*i/512 (src/preprocessor.cpp:86-89)
+    const float* sin_tbl;
+    const float* fbT;        // filterbank transposed [257][128]
+    const int2* fb_range;    // per mel bin: [first, last+1) FFT bins with non-zero weight
+};
+// pcm: per item a window of samples; item b's window starts at pcm + b*pcm_stride and its element 0 is the sample
+// BEFORE the first frame's first sample (pre-emphasis needs x[i-1]). Frame f uses elements [1+160f, 1+160f+512).
+// out: item b, frame f -> mel_out + out_off[b] + f*128 floats (out_off in floats). n_frames[b] <= max_frames.
+void launch_mel(cudaStream_t st, const MelTables& tb, const int16_t* pcm, int pcm_stride, const int* n_frames,
+                const long long* out_off, float* mel_out, int B, int max_frames);
+
+struct SubWeights {          // encoder.pre_encode.* (src/nemo-ggml.cpp:296-307)
+    const float* w0;         // [256][9] fp16-rounded values (conv0 runs through an F16 im2col in the reference)
+    const float* b0;         // [256]
+    const float* w2;         // [256][9] fp32 depthwise
+    const float* b2;
+    const float* w5;
+    const float* b5;
+};
+// mel chunk [B][chunk_mel][128] -> relu(conv0) -> depthwise conv2 (+bias) -> fp16 [B][t2][33][256]
+void launch_sub_stage1(cudaStream_t st, const SubWeights& w, const float* mel, __half* out, int B, int chunk_mel, int t1, int t2);
+// relu(pw3) fp32 [B][t2][33][256] -> depthwise conv5 (+bias), rows h3 >= 2 only -> fp16 [B][t3-2][17][256]
+void launch_sub_stage2(cudaStream_t st, const SubWeights& w, const float* a3, __half* out, int B, int t2, int t3);
+
+// ---- encoder.cu ----------------------------------------------------------------------------------
+// y = LN(x; g1,b1); if out_f32: out_f32 = y; z = g2 ? LN(y; g2,b2) : y; out_f16 = fp16(fq ? fake_quant(z) : z)
+void launch_layernorm(cudaStream_t st, const float* x, const float* g1, const float* b1, float* out_f32, const float* g2,
+                      const float* b2, __half* out_f16, int act_quant, int M);
+
+struct AttnArgs {
+    const float* q;        // [M][1024] fp32 (row m = b*T + i)
+    const float* k_ring;   // this layer's [slots][RING][1024]
+    const float* v_ring;
+    const float* pos;      // this layer's projected positions [npos][1024], row p + (T-1), p in [-(T-1), 70+T-1]
+    const float* bias_u;   // [8][128]
+    const float* bias_v;
+    const int* slot;       // [B]
+    const int* wpos;       // [B] ring index of this chunk's frame 0
+    const int* valid;      // [B] cache_valid_len before this chunk
+    __half* out;           // [M][1024] fp16 context (fq per 32 features when act_quant)
+    int B, T, act_quant;
+};
+void launch_attention(cudaStream_t st, const AttnArgs& a);
+
+struct ConvArgs {
+    const float* g;        // GLU output [M][1024]
+    float* conv_cache;     // this layer's [slots][8][1024]
+    const float* w_dw;     // [9][1024]
+    const float* ln_g;     // conv.batch_norm (a LayerNorm)
+    const float* ln_b;
+    const int* slot;
+    __half* out;           // [M][1024] fp16 = fq(silu(LN(dwconv)))
+    int B, T, act_quant;
+};
+void launch_dwconv(cudaStream_t st, const ConvArgs& a);        // reads cache, writes out
+void launch_conv_cache_update(cudaStream_t st, const ConvArgs& a);  // cache = last 8 of [cache ; g]
+
+// fp32 [rows][1024] -> fp16 with optional fake-quant per 32 (used to prepare the positional table GEMM input)
+void launch_cast_f16(cudaStream_t st, const float* x, __half* out, int act_quant, int rows, int cols);
+// sinusoid rows for relative positions p0 .. p0+n-1 (src/nemo-ggml.cpp:17-32) -> fp32 [n][1024]
+void launch_pos_emb(cudaStream_t st, float* out, int p0, int n);
+
+}  // namespace nb
+
+// ---- decoder.cu ----------------------------------------------------------------------------------
+namespace nb {
+
+// C[M,N] = A[M,K] * W[N,K]^T + bias, fp32 on CUDA cores (the reference keeps LSTM/joint weights and math in fp32,
+// src/nemo-ggml.cpp:580-619,1186-1224). N % 64 == 0, K % 16 == 0. Row m of C is stored at row out_rows[m] if given.
+void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* bias, float* C, int M, int N, int K,
+                  int ldc, const int* out_rows);
+
+struct DecodeState {           // per stream slot, persistent in HBM
+    float* h;                  // [slots][2][640] committed LSTM hidden state
+    float* c;                  // [slots][2][640]
+    float* pend_h;             // [slots][2][640] LSTM(embed[prev], h, c) — what the next symbol step would commit
+    float* pend_c;
+    float* pend_p;             // [slots][640]    joint.pred(pend_h[1]) + bias
+    int* prev;                 // [slots] previous non-blank token (blank at start)
+};
+struct DecodeBatch {           // per batched step
+    const float* e;            // [B*T][640] joint.enc(enc_out) + bias
+    const int* slot;           // [B]
+    const int* nvalid;         // [B] encoder frames to decode for this chunk
+    int* fp;                   // [B] frame pointer
+    int* sym;                  // [B] symbols emitted at the current frame
+    int* tok_out;              // [B][T*MAX_SYMBOLS]
+    int* tok_cnt;              // [B]
+    int* unfinished;           // [1] streams with fp < nvalid after the last round
+    float* min_margin;         // [B] smallest top1-top2 logit gap over this chunk's symbol steps (near-tie tracing)
+    float* hid;                // [B][640]
+    float* logits;             // [B][1088]
+    float* x;                  // [B][1280] LSTM input rows
+    float* gates;              // [B][2560]
+    float* hp;                 // [B][640]
+    int B, T;
+};
+struct DecodeWeights {
+    const float* embed;        // [1025][640]
+    const float* wcat[2];      // [2560][1280] = [W_ih | W_hh]
+    const float* bcat[2];      // [2560] = b_ih + b_hh
+    const float* wpred;        // [640][640]
+    const float* bpred;
+    const float* wout;         // [1088][640], rows >= 1025 are zero
+    const float* bout;         // [1088], entries >= 1025 are -inf
+};
+// one greedy round for every unfinished stream of the batch (src/nemo-stream.cpp:865-927)
+void launch_decode_round(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& b);
+// recompute the pending LSTM/pred state of the given slots from their committed state (after create/reset)
+void launch_decode_refresh(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& b);
+
+}  // namespace nb

@@ -1,0 +1,250 @@
+"""ctypes binding of libnemob200.so (include/nb200.h) plus a thin host-side mirror of the reference's stream API.
+
+`Model` / `Stream` follow the reference's operator interface for the streaming path
+(/root/reference/src/nemo-stream.h:271-326): `Stream.process_incremental(pcm)` == nemo_stream_process_incremental,
+`Stream.finalize()` == nemo_stream_finalize, `Stream.tokens` == nemo_stream_get_tokens, same argument meaning and
+error behaviour (empty string / exception with the library's message instead of nullptr + stderr).
+The product path is the CUDA library only: importing this module without the built library, or loading a model
+without a B200, raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import numpy as np
+
+_HERE = Path(__file__).resolve().parent
+LIB_PATH = _HERE / "libnemob200.so"
+
+FLAG_ACT_QUANT_AUTO, FLAG_ACT_QUANT_OFF, FLAG_ACT_QUANT_ON, FLAG_GEMM_SIMT = 0, 1, 2, 16
+TAP_MEL, TAP_ENC = 1, 2
+
+
+class Info(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "n_mels", "d_model", "n_heads", "d_head", "d_ff", "n_layers", "kernel_size", "vocab_size", "blank_token",
+        "decoder_dim", "joint_dim", "subsampling_factor", "att_left_context", "num_prompts", "weights_quantized",
+        "act_quant", "max_streams", "device")]
+
+
+class Stats(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in ("steps", "chunks", "frames", "tokens", "decode_rounds", "kernel_launches")] + \
+               [(n, C.c_double) for n in ("audio_seconds", "gpu_seconds", "last_step_gpu_ms", "last_frontend_ms",
+                                          "last_encoder_ms", "last_decoder_ms")]
+
+
+# every symbol include/nb200.h declares: (restype, argtypes)
+_I16P, _I32P, _F32P = C.POINTER(C.c_int16), C.POINTER(C.c_int32), C.POINTER(C.c_float)
+SYMBOLS = {
+    "nb200_last_error": (C.c_char_p, []),
+    "nb200_version": (C.c_int, []),
+    "nb200_model_load": (C.c_void_p, [C.c_char_p, C.c_int, C.c_int, C.c_int]),
+    "nb200_model_free": (None, [C.c_void_p]),
+    "nb200_model_info": (C.c_int, [C.c_void_p, C.POINTER(Info)]),
+    "nb200_model_token": (C.c_char_p, [C.c_void_p, C.c_int32]),
+    "nb200_tokens_to_text": (C.c_int, [C.c_void_p, _I32P, C.c_int, C.c_char_p, C.c_int]),
+    "nb200_stream_create": (C.c_void_p, [C.c_void_p, C.c_int]),
+    "nb200_stream_free": (None, [C.c_void_p]),
+    "nb200_stream_reset": (C.c_int, [C.c_void_p]),
+    "nb200_stream_feed": (C.c_int, [C.c_void_p, _I16P, C.c_int]),
+    "nb200_stream_finalize": (C.c_int, [C.c_void_p]),
+    "nb200_stream_ready_chunks": (C.c_int, [C.c_void_p]),
+    "nb200_step": (C.c_int, [C.c_void_p]),
+    "nb200_drain": (C.c_int, [C.c_void_p]),
+    "nb200_stream_poll_tokens": (C.c_int, [C.c_void_p, _I32P, C.c_int]),
+    "nb200_stream_get_tokens": (C.c_int, [C.c_void_p, _I32P, C.c_int]),
+    "nb200_stream_chunk_token_counts": (C.c_int, [C.c_void_p, _I32P, C.c_int]),
+    "nb200_stream_chunk_margins": (C.c_int, [C.c_void_p, _F32P, C.c_int]),
+    "nb200_stream_set_taps": (C.c_int, [C.c_void_p, C.c_int]),
+    "nb200_stream_fetch_tap": (C.c_int64, [C.c_void_p, C.c_int, _F32P, C.c_int64]),
+    "nb200_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
+    "nb200_mel_batch": (C.c_int, [C.c_void_p, _I16P, C.c_int, C.c_int, _F32P]),
+    "nb200_debug_matmul": (C.c_int, [C.c_void_p, C.c_char_p, _F32P, C.c_int, _F32P]),
+}
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Loads the CUDA library; raises if it has not been built (no fallback of any kind)."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise RuntimeError(f"{LIB_PATH} is missing: build it with `make -C {_HERE}` (python __graft_entry__.py build)")
+        _lib = C.CDLL(str(LIB_PATH))
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(_lib, name)
+            fn.restype, fn.argtypes = res, args
+    return _lib
+
+
+class NB200Error(RuntimeError):
+    pass
+
+
+def _err() -> str:
+    return (lib().nb200_last_error() or b"").decode(errors="replace")
+
+
+def _ptr(a: np.ndarray, typ):
+    return a.ctypes.data_as(typ)
+
+
+class Model:
+    """nemo_context equivalent (src/nemo-ggml.h:236-261)."""
+
+    def __init__(self, gguf_path: str, device: int = 0, max_streams: int = 64, flags: int = 0):
+        self._h = lib().nb200_model_load(os.fsencode(gguf_path), device, max_streams, flags)
+        if not self._h:
+            raise NB200Error(_err())
+        self.info = Info()
+        lib().nb200_model_info(self._h, C.byref(self.info))
+        self._streams: list[Stream] = []
+
+    def close(self):
+        if self._h:
+            lib().nb200_model_free(self._h)
+            self._h = None
+            for s in self._streams:
+                s._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def stream(self, right_context: int = 0) -> "Stream":
+        """nemo_stream_init(ctx, &cfg) with cfg.att_right_context = right_context."""
+        s = Stream(self, right_context)
+        self._streams.append(s)
+        return s
+
+    def step(self) -> int:
+        n = lib().nb200_step(self._h)
+        if n < 0:
+            raise NB200Error(_err())
+        return n
+
+    def drain(self) -> int:
+        n = lib().nb200_drain(self._h)
+        if n < 0:
+            raise NB200Error(_err())
+        return n
+
+    def stats(self) -> Stats:
+        st = Stats()
+        lib().nb200_get_stats(self._h, C.byref(st))
+        return st
+
+    def tokens_to_text(self, tokens) -> str:
+        t = np.ascontiguousarray(tokens, dtype=np.int32)
+        buf = C.create_string_buffer(16 * max(1, t.size) + 16)
+        n = lib().nb200_tokens_to_text(self._h, _ptr(t, _I32P), int(t.size), buf, len(buf))
+        if n < 0:
+            raise NB200Error(_err())
+        return buf.raw[:n].decode("utf-8", errors="replace")
+
+    def mel_batch(self, pcm: np.ndarray) -> np.ndarray:
+        """nemo_preprocessor_process for [n_streams, n_samples] int16 signals, each from a fresh preprocessor."""
+        pcm = np.ascontiguousarray(pcm, dtype=np.int16)
+        ns, n = pcm.shape
+        nf = 0 if n + 256 < 512 else (n + 256 - 512) // 160 + 1
+        out = np.zeros((ns, nf, 128), np.float32)
+        r = lib().nb200_mel_batch(self._h, _ptr(pcm, _I16P), ns, n, _ptr(out, _F32P))
+        if r < 0:
+            raise NB200Error(_err())
+        return out
+
+    def debug_matmul(self, tensor_name: str, x: np.ndarray, n_out: int) -> np.ndarray:
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        y = np.zeros((x.shape[0], n_out), np.float32)
+        if lib().nb200_debug_matmul(self._h, tensor_name.encode(), _ptr(x, _F32P), x.shape[0], _ptr(y, _F32P)) < 0:
+            raise NB200Error(_err())
+        return y
+
+
+class Stream:
+    """nemo_stream_context equivalent (src/nemo-stream.h:177-326)."""
+
+    def __init__(self, model: Model, right_context: int):
+        self.model = model
+        self.right_context = right_context
+        self._h = lib().nb200_stream_create(model._h, right_context)
+        if not self._h:
+            raise NB200Error(_err())
+
+    def free(self):
+        if self._h and self.model._h:
+            lib().nb200_stream_free(self._h)
+        self._h = None
+
+    def reset(self):
+        if lib().nb200_stream_reset(self._h) < 0:
+            raise NB200Error(_err())
+
+    def feed(self, pcm: np.ndarray):
+        pcm = np.ascontiguousarray(pcm, dtype=np.int16)
+        if lib().nb200_stream_feed(self._h, _ptr(pcm, _I16P), int(pcm.size)) < 0:
+            raise NB200Error(_err())
+
+    def set_taps(self, taps: int):
+        lib().nb200_stream_set_taps(self._h, taps)
+
+    def fetch_tap(self, tap: int) -> np.ndarray:
+        n = lib().nb200_stream_fetch_tap(self._h, tap, None, 0)
+        out = np.zeros(max(n, 0), np.float32)
+        if n > 0:
+            lib().nb200_stream_fetch_tap(self._h, tap, _ptr(out, _F32P), n)
+        return out
+
+    def poll_tokens(self) -> list[int]:
+        buf = np.zeros(4096, np.int32)
+        out: list[int] = []
+        while True:
+            n = lib().nb200_stream_poll_tokens(self._h, _ptr(buf, _I32P), buf.size)
+            if n <= 0:
+                return out
+            out.extend(buf[:n].tolist())
+
+    @property
+    def tokens(self) -> list[int]:
+        n = lib().nb200_stream_get_tokens(self._h, None, 0)
+        buf = np.zeros(max(n, 1), np.int32)
+        lib().nb200_stream_get_tokens(self._h, _ptr(buf, _I32P), n)
+        return buf[:n].tolist()
+
+    @property
+    def chunk_token_counts(self) -> list[int]:
+        n = lib().nb200_stream_chunk_token_counts(self._h, None, 0)
+        buf = np.zeros(max(n, 1), np.int32)
+        lib().nb200_stream_chunk_token_counts(self._h, _ptr(buf, _I32P), n)
+        return buf[:n].tolist()
+
+    @property
+    def chunk_margins(self) -> list[float]:
+        n = lib().nb200_stream_chunk_margins(self._h, None, 0)
+        buf = np.zeros(max(n, 1), np.float32)
+        lib().nb200_stream_chunk_margins(self._h, _ptr(buf, _F32P), n)
+        return buf[:n].tolist()
+
+    # ---- the reference's call shapes ---------------------------------------------------------------
+    def process_incremental(self, pcm: np.ndarray) -> str:
+        """nemo_stream_process_incremental (src/nemo-stream.cpp:1145-1206): feed, run every complete chunk of THIS
+        stream, return the newly decoded text."""
+        if pcm is None or len(pcm) == 0:
+            return ""
+        self.feed(pcm)
+        while lib().nb200_stream_ready_chunks(self._h) > 0:
+            self.model.step()
+        return self.model.tokens_to_text(self.poll_tokens())
+
+    def finalize(self) -> str:
+        """nemo_stream_finalize (src/nemo-stream.cpp:1217-1293): flush the zero-padded tail; text added by the flush."""
+        lib().nb200_stream_finalize(self._h)
+        while lib().nb200_stream_ready_chunks(self._h) > 0:
+            self.model.step()
+        self.model.step()  # consumes the finalize mark even when the tail yields no frame
+        return self.model.tokens_to_text(self.poll_tokens())
