@@ -15,6 +15,9 @@
 //       (tokens emitted per chunk) and prints one JSON line with timings.
 //   ref_harness mel <gguf> <pcm.s16le> <slice_samples> <out.f32>
 //       preprocessor only, PCM fed in slices of the given size.
+//   ref_harness matmul <gguf> <tensor_name> <x.f32> <M> <out.f32> [threads]
+//       y[M,N] = ggml_mul_mat(W, x) on the reference's CPU backend for one weight tensor of the file (Q8_0 or F32),
+//       i.e. exactly the kernel the encoder graph runs for that tensor (src/nemo-stream.cpp:593-603).
 #include "nemo-ggml.h"
 #include "nemo-stream.h"
 #include "preprocessor.h"
@@ -160,10 +163,45 @@ static int run_stream(int argc, char** argv) {
     return 0;
 }
 
+static int run_matmul(int argc, char** argv) {
+    if (argc < 7) { fprintf(stderr, "usage: matmul <gguf> <tensor> <x.f32> <M> <out.f32> [threads]\n"); return 2; }
+    nemo_context* ctx = nemo_init_with_backend(argv[2], NEMO_BACKEND_CPU);
+    if (!ctx) return 1;
+    if (argc > 7) ggml_backend_cpu_set_n_threads(ctx->model.backend, atoi(argv[7]));
+    auto it = ctx->model.tensors.find(argv[3]);
+    if (it == ctx->model.tensors.end()) { fprintf(stderr, "no tensor %s\n", argv[3]); return 1; }
+    ggml_tensor* W = it->second;
+    const int M = atoi(argv[5]);
+    const int64_t K = W->ne[0], N = W->ne[1];
+    std::vector<float> x((size_t)M * K);
+    FILE* f = fopen(argv[4], "rb");
+    if (!f || fread(x.data(), sizeof(float), x.size(), f) != x.size()) { fprintf(stderr, "cannot read %s\n", argv[4]); return 2; }
+    fclose(f);
+    ggml_init_params ip = {ggml_tensor_overhead() * 8 + ggml_graph_overhead(), nullptr, true};
+    ggml_context* c = ggml_init(ip);
+    ggml_tensor* X = ggml_new_tensor_2d(c, GGML_TYPE_F32, K, M);
+    ggml_tensor* Y = ggml_mul_mat(c, W, X);
+    ggml_cgraph* g = ggml_new_graph(c);
+    ggml_build_forward_expand(g, Y);
+    ggml_gallocr_t ga = ggml_gallocr_new(ggml_backend_get_default_buffer_type(ctx->model.backend));
+    ggml_gallocr_alloc_graph(ga, g);
+    ggml_backend_tensor_set(X, x.data(), 0, x.size() * sizeof(float));
+    ggml_backend_graph_compute(ctx->model.backend, g);
+    std::vector<float> y((size_t)M * N);
+    ggml_backend_tensor_get(Y, y.data(), 0, y.size() * sizeof(float));
+    write_file(argv[6], y.data(), y.size() * sizeof(float));
+    printf("{\"mode\":\"matmul\",\"M\":%d,\"N\":%lld,\"K\":%lld,\"type\":\"%s\"}\n", M, (long long)N, (long long)K, ggml_type_name(W->type));
+    ggml_gallocr_free(ga);
+    ggml_free(c);
+    nemo_free(ctx);
+    return 0;
+}
+
 int main(int argc, char** argv) {
-    if (argc < 2) { fprintf(stderr, "usage: ref_harness stream|mel ...\n"); return 2; }
+    if (argc < 2) { fprintf(stderr, "usage: ref_harness stream|mel|matmul ...\n"); return 2; }
     if (!strcmp(argv[1], "mel")) return run_mel(argc, argv);
     if (!strcmp(argv[1], "stream")) return run_stream(argc, argv);
+    if (!strcmp(argv[1], "matmul")) return run_matmul(argc, argv);
     fprintf(stderr, "unknown mode %s\n", argv[1]);
     return 2;
 }

@@ -1,0 +1,78 @@
+"""Deterministic input set shared by tests/golden/make_golden.py and the tests.
+
+Everything is a pure function of seeds, so the GPU box regenerates byte-identical GGUFs / PCM (neither travels:
+the 2-layer GGUFs are 108 MB / 256 MB). Files are cached under $NB200_TMP (default /tmp/nb200).
+"""
+from __future__ import annotations
+
+import os
+import sys
+import zlib
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parents[1]
+sys.path.insert(0, str(ROOT / "tools"))
+TMP = Path(os.environ.get("NB200_TMP", "/tmp/nb200"))
+
+SEED = 1234
+TEST_LAYERS = 2  # parity fixtures use a 2-layer model of the real widths: every kernel and both cache paths run
+
+# (tensor name, M) of the single-matmul fixtures
+MATMUL_CASES = (
+    ("encoder.layers.0.feed_forward1.linear1.weight", 1),
+    ("encoder.layers.0.feed_forward1.linear1.weight", 6),
+    ("encoder.layers.0.feed_forward1.linear2.weight", 6),
+    ("encoder.layers.1.conv.pointwise_conv1.weight", 6),
+    ("encoder.layers.1.self_attn.linear_out.weight", 6),
+)
+
+# (variant, right_context, pcm seed, seconds) of the stream fixtures. 8 s at rc=13 wraps the K/V ring (84 frames) and
+# saturates cache_valid_len (70); every run ends with nemo_stream_finalize, so the zero-padded tail chunk is covered.
+STREAM_CASES = (
+    ("q8_0", 0, 11, 3.0),
+    ("q8_0", 13, 11, 4.0),
+    ("f32dq", 0, 11, 3.0),
+    ("f32dq", 13, 11, 8.0),
+    ("f32dq", 1, 12, 2.0),
+    ("f32dq", 6, 12, 2.5),
+)
+
+
+def gguf_path(variant: str, layers: int = TEST_LAYERS) -> str:
+    import make_random_gguf as mg
+    TMP.mkdir(parents=True, exist_ok=True)
+    p = TMP / f"L{layers}_{variant}_s{SEED}.gguf"
+    if not p.exists():
+        tmp = p.with_suffix(f".tmp{os.getpid()}")
+        mg.write_gguf(str(tmp), SEED, layers, variant)
+        os.replace(tmp, p)
+    return str(p)
+
+
+def pcm(seed: int, seconds: float) -> np.ndarray:
+    import make_pcm
+    return make_pcm.make_pcm(seconds, seed)
+
+
+def pcm_path(seed: int, seconds: float) -> str:
+    TMP.mkdir(parents=True, exist_ok=True)
+    p = TMP / f"pcm_s{seed}_{seconds:g}s.pcm"
+    if not p.exists():
+        tmp = p.with_suffix(f".tmp{os.getpid()}")
+        pcm(seed, seconds).tofile(tmp)
+        os.replace(tmp, p)
+    return str(p)
+
+
+def ensure_inputs() -> dict:
+    return {"q8_0": gguf_path("q8_0"), "f32dq": gguf_path("f32dq")}
+
+
+def matmul_input(name: str, M: int, K: int | None = None) -> np.ndarray:
+    """Seeded activations with a realistic spread (a few large entries per 32-block, like LN outputs)."""
+    if K is None:
+        K = 4096 if name.endswith("linear2.weight") else 1024
+    rng = np.random.default_rng([SEED, zlib.crc32(name.encode()), M])
+    return (rng.standard_normal((M, K)) * rng.uniform(0.2, 3.0, (M, 1))).astype(np.float32)
