@@ -1,0 +1,330 @@
+#!/usr/bin/env python3
+"""Benchmark of the streaming-ASR hot path (BASELINE.json): audio-seconds per wall-second (RTFx) over concurrent
+streams, plus per-chunk latency, on N B200s of one node (one process per GPU; streams sharded by id, no collective).
+
+    python bench.py --gpus 1 --steps 20 --warmup 3                         # own arm (CUDA library through its C ABI)
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+    python bench.py --impl reference --steps 20 --warmup 3                 # the reference's ggml-CPU path (oracle/_ref)
+
+Workload at N=1 = BASELINE.json configs[1]: nemotron-speech-streaming 0.6B architecture (24 layers, random-init Q8_0
+GGUF, seed 1234), 64 concurrent streams, 1.12 s chunks (right_context 13). One "step" = one batched chunk of every
+stream (64 x 1.12 s of audio). Weak scaling: 64 streams per GPU.
+
+Legs (all timed with CUDA events on the library's stream, max over ranks):
+  value  K steps with the audio already resident in HBM (fed into the device PCM rings before the timed region)
+  e2e    K steps through the public call sequence feed (pinned host PCM -> H2D) / step / poll tokens (D2H)
+  roofline  per-kernel-family device time from a profiled pass of the same steps (events around every launch)
+  cpu_baseline  the unmodified reference (oracle/_ref ref_harness) on the host cores, bounded sample
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+for _p in (ROOT / "nemotron-asr.cpp_b200", ROOT / "tools", ROOT / "tests"):
+    sys.path.insert(0, str(_p))
+
+METRIC = "audio-sec/sec (RTFx) over concurrent streams"
+UNIT = "audio-s/s"
+HOP, SR = 160, 16000
+BENCH_BLANK_GAIN = 6.3  # see tools/make_random_gguf.py: blank-dominated decode, ~1.05 symbol steps per encoder frame
+
+
+def chunk_samples(rc: int) -> int:
+    return 8 * (1 + rc) * HOP
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return {"hbm_gbs": d["hbm_gbs"], "tflops": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "tflops": 1400.0, "source": "fallback"}
+
+
+def ref_harness_bin():
+    flags = open("/proc/cpuinfo").read()
+    order = (["avx512"] if ("avx512_vnni" in flags or "avx512vnni" in flags) and "avx512bw" in flags else []) + ["avx2"]
+    for v in order:
+        p = ROOT / "oracle" / "_ref" / v / "ref_harness"
+        if p.exists():
+            return str(p), v
+    return None, None
+
+
+def host_threads() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def run_reference(gguf: str, rc: int, chunks: int, threads: int, seed: int = 21) -> dict:
+    """Times the unmodified reference on `chunks` chunks of one stream (it has no cross-stream batching)."""
+    import inputs
+    exe, isa = ref_harness_bin()
+    if exe is None:
+        raise RuntimeError("oracle/_ref/<isa>/ref_harness is missing (built by __graft_entry__.build() where /root/reference exists)")
+    secs = chunks * chunk_samples(rc) / SR
+    pcm = inputs.pcm_path(seed, round(secs + 0.05, 3))
+    r = subprocess.run([exe, "stream", gguf, pcm, str(rc), str(threads), "-", f"{secs:.4f}"], check=True,
+                       stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    d["isa"] = isa
+    return d
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed regions run."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.proc = index, [], None
+
+    def run(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([x.strip() for x in line.split(",")])
+        except Exception:
+            pass
+
+    def stop(self) -> dict:
+        if self.proc:
+            self.proc.terminate()
+        self.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 7 for n, v in zip(names, r[3:7]) if v.lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def build_pcm(n_streams: int, n_samples: int, first_id: int):
+    """[n_streams, n_samples] int16 in pinned host memory; stream s = base signal (s mod 8) rolled by a stream-specific
+    offset and tiled (seeded, see tools/make_pcm.py)."""
+    import torch
+
+    import inputs
+    base = [inputs.pcm(100 + i, 8.0) for i in range(8)]
+    out = torch.empty((n_streams, n_samples), dtype=torch.int16).pin_memory()
+    arr = out.numpy()
+    for s in range(n_streams):
+        g = first_id + s
+        sig = np.roll(base[g % 8], 997 * g)
+        arr[s] = np.tile(sig, n_samples // sig.size + 1)[:n_samples]
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=("b200", "reference"))
+    ap.add_argument("--streams", type=int, default=64, help="concurrent streams per GPU")
+    ap.add_argument("--rc", type=int, default=13, choices=(0, 1, 6, 13))
+    ap.add_argument("--layers", type=int, default=24)
+    ap.add_argument("--variant", default="q8_0", choices=("q8_0", "f32dq"))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    if a.warmup < 3:
+        a.warmup = 3
+    rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    cs, T = chunk_samples(a.rc), 1 + a.rc
+    workload = f"nemotron-speech-streaming-0.6B ({a.layers} layers, random-init {a.variant}), {a.streams} concurrent streams per GPU, " \
+               f"{cs / SR:.2f} s chunks (right_context {a.rc})"
+    config = {"workload": workload, "streams_per_gpu": a.streams, "right_context": a.rc, "chunk_seconds": cs / SR, "layers": a.layers,
+              "weights": a.variant, "l2_policy": "inputs larger than L2: weights 1.2 GB + 0.9 GB of K/V caches are re-read every step"}
+
+    import inputs
+    gguf_done = Path(inputs.TMP) / f".gguf_ready_{a.layers}_{a.variant}"
+    if local == 0:
+        gguf = inputs.gguf_path(a.variant, a.layers, BENCH_BLANK_GAIN)
+        gguf_done.touch()
+    else:
+        while not gguf_done.exists():
+            time.sleep(0.5)
+        gguf = inputs.gguf_path(a.variant, a.layers, BENCH_BLANK_GAIN)
+
+    # ------------------------------------------------------------------------------------------------------
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        threads = host_threads()
+        run_reference(gguf, a.rc, a.warmup, threads)  # warm-up (page cache, thread pool)
+        d = run_reference(gguf, a.rc, a.steps, threads)
+        value = d["audio_s"] / d["proc_s"]
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+                "ms_per_step": d["proc_s"] / max(d["chunks"], 1) * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "int8 x int8 blocks (ggml Q8_0) + f32", "data": "synthetic", "impl": "reference", "config": config,
+                "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "reference",
+                                 "sample": f"1 stream x {d['chunks']} chunks ({d['audio_s']:.1f} s); the reference has no cross-stream batching "
+                                           f"(src/nemo-server.cpp:192-271), so its N-stream RTFx equals its 1-stream RTFx; ggml-CPU {d['isa']} build"},
+                "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "decode_steps_per_frame": d["decode_iters"] / max(d["chunks"] * T, 1)}
+        print(json.dumps(line))
+        return
+
+    # ------------------------------------------------------------------------------------------------------
+    import torch
+    import torch.distributed as dist
+
+    import nb200
+    import shard
+    import __graft_entry__ as ge
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    ge.build_library()
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+
+    n_total_steps = 2 * (a.warmup + a.steps) + 5
+    need = (a.warmup + a.steps + 2) * cs + 1024
+    os.environ["NB200_PCM_RING_LOG2"] = str(max(17, int(np.ceil(np.log2(need)))))
+    my_ids = shard.shard_streams(a.streams * world, world, rank)
+    assert len(my_ids) == a.streams
+    model = nb200.Model(gguf, device=local, max_streams=a.streams)
+    streams = [model.stream(a.rc) for _ in my_ids]
+    pcm = build_pcm(a.streams, n_total_steps * cs, my_ids[0])
+    base_ptr, row_bytes = pcm.data_ptr(), pcm.stride(0) * 2
+    cursor = 0  # samples fed per stream so far
+
+    def feed_chunks(n_chunks: int):
+        nonlocal cursor
+        for i, s in enumerate(streams):
+            s.feed_ptr(base_ptr + i * row_bytes + cursor * 2, n_chunks * cs)
+        cursor += n_chunks * cs
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+
+    # ---- leg 1: device-resident inputs -------------------------------------------------------------------
+    # one chunk more than the steps consume: a centred STFT frame needs 256 samples beyond its hop (preprocessor.cpp:320-328)
+    feed_chunks(a.warmup + a.steps + 1)
+    for _ in range(a.warmup):
+        assert model.step() == a.streams
+    st0 = model.stats()
+    barrier()
+    model.timer_start()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        n = model.step()
+        assert n == a.streams, n
+    ms_dev = model.timer_stop()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    barrier()
+    st1 = model.stats()
+    audio_local = a.steps * a.streams * cs / SR
+    ms_max, audio_all = shard.reduce_timing(max(ms_dev, wall_ms), audio_local, dev)
+    value = audio_all / (ms_max * 1e-3)
+    launches = st1.kernel_launches - st0.kernel_launches
+    frames = st1.frames - st0.frames
+    steps_per_frame = (st1.decode_rounds - st0.decode_rounds) / max(a.steps * T, 1)
+
+    # ---- leg 2: end to end through feed / step / poll ------------------------------------------------------
+    for _ in range(a.warmup):
+        feed_chunks(1)
+        model.step()
+        for s in streams:
+            s.poll_tokens()
+    st2 = model.stats()
+    lat = []
+    barrier()
+    model.timer_start()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        t1 = time.perf_counter()
+        feed_chunks(1)
+        n = model.step()
+        assert n == a.streams, n
+        for s in streams:
+            s.poll_tokens()
+        lat.append((time.perf_counter() - t1) * 1e3)
+    ms_dev2 = model.timer_stop()
+    wall2 = (time.perf_counter() - t0) * 1e3
+    barrier()
+    st3 = model.stats()
+    ms2_max, audio2 = shard.reduce_timing(max(ms_dev2, wall2), audio_local, dev)
+    e2e = {"value": audio2 / (ms2_max * 1e-3), "unit": UNIT, "h2d_bytes_per_step": (st3.h2d_bytes - st2.h2d_bytes) // a.steps,
+           "d2h_bytes_per_step": (st3.d2h_bytes - st2.d2h_bytes) // a.steps, "ms_per_step": ms2_max / a.steps}
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- leg 3: per-kernel device time (profiled pass, outside the timed regions) ---------------------------
+    model.profile(True)
+    for _ in range(2):
+        feed_chunks(1)
+        model.step()
+    prof = model.profile_report()
+    model.profile(False)
+    tot_ms = sum(v["ms"] for v in prof.values()) or 1.0
+    dom = max(prof, key=lambda k: prof[k]["ms"])
+    pk = peaks()
+    d = prof[dom]
+    per_launch_ms = d["ms"] / d["launches"]
+    if dom.startswith("gemm"):
+        ach = d["flops"] / (d["ms"] * 1e-3) / 1e12
+        roofline = {"kernel": dom, "bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"]}
+    else:
+        ach = d["bytes"] / (d["ms"] * 1e-3) / 1e9
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"]}
+    roofline.update({"traffic": None, "peak_source": pk["source"], "share_of_step": d["ms"] / tot_ms, "avg_launch_us": per_launch_ms * 1e3,
+                     "launches_per_step": d["launches"] // 2})
+    kernels = {k: {"share": round(v["ms"] / tot_ms, 4), "launches_per_step": v["launches"] // 2, "avg_us": round(v["ms"] / v["launches"] * 1e3, 2),
+                   "tflops": round(v["flops"] / (v["ms"] * 1e-3) / 1e12, 2), "gbs": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 1)}
+               for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
+
+    for s in streams:
+        s.free()
+    model.close()
+    if world > 1:
+        dist.barrier(device_ids=[local])
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f16 operands, f32 accumulate (Q8_0 weights dequantised; ggml's int8 activation re-quantisation emulated)",
+            "data": "synthetic", "config": config, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "latency_ms": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)), "what": "feed+step+poll of one batched chunk"},
+            "decode_steps_per_frame": steps_per_frame, "frames_decoded": int(frames), "streams_total": a.streams * world,
+            "realtime_streams_supported": value, "roofline": roofline, "kernels": kernels}
+
+    if world == 1 and not a.no_cpu_baseline:
+        try:
+            threads = host_threads()
+            run_reference(gguf, a.rc, 2, threads)
+            r = run_reference(gguf, a.rc, 12, threads)
+            line["cpu_baseline"] = {"value": r["audio_s"] / r["proc_s"], "unit": UNIT, "cores": threads, "kind": "reference",
+                                    "sample": f"unmodified reference (ggml-CPU {r['isa']} build), 1 stream x {r['chunks']} chunks ({r['audio_s']:.1f} s) of the same "
+                                              f"GGUF and latency mode; it has no cross-stream batching, so its N-stream RTFx equals this 1-stream RTFx",
+                                    "ms_per_chunk": r["proc_s"] / max(r["chunks"], 1) * 1e3}
+        except Exception as e:  # the checker binary did not travel / cannot run here
+            line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": host_threads(), "kind": "reference", "sample": f"unavailable: {e}"}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

@@ -49,6 +49,8 @@ typedef struct nb200_stats {
     int64_t tokens;           /* non-blank tokens emitted                            */
     int64_t decode_rounds;    /* batched joint evaluations                           */
     int64_t kernel_launches;  /* kernels of this library launched so far             */
+    int64_t h2d_bytes;        /* bytes copied host->device (audio + per-step metadata)          */
+    int64_t d2h_bytes;        /* bytes copied device->host (tokens, counts, the decode loop's flag) */
     double audio_seconds;     /* audio consumed by processed chunks                  */
     double gpu_seconds;       /* device time of all steps (CUDA events on the library's stream) */
     double last_step_gpu_ms;  /* device time of the last nb200_step                  */
@@ -76,7 +78,9 @@ void nb200_stream_free(nb200_stream* s);
 /* nemo_stream_reset — src/nemo-stream.h:319 (this backend also re-zeroes the conv cache; the reference does not) */
 int nb200_stream_reset(nb200_stream* s);
 
-/* First half of nemo_stream_process_incremental (src/nemo-stream.cpp:1145-1162): buffer PCM. Enqueue only. */
+/* First half of nemo_stream_process_incremental (src/nemo-stream.cpp:1145-1162): buffer PCM. The samples are
+ * uploaded (pinned staging + async copy on the library's stream) into the stream's device-resident PCM ring, so a
+ * later nb200_step starts with its inputs already in HBM. Enqueue only: no kernel runs here. */
 int nb200_stream_feed(nb200_stream* s, const int16_t* pcm, int n_samples);
 /* nemo_stream_finalize (src/nemo-stream.cpp:1217-1293): mark the stream so the next nb200_step flushes its
  * zero-padded tail chunk (keeps floor(new_mel/8) frames). */
@@ -111,6 +115,17 @@ int nb200_stream_set_taps(nb200_stream* s, int taps);
 int64_t nb200_stream_fetch_tap(const nb200_stream* s, int tap, float* out, int64_t cap);
 
 int nb200_get_stats(const nb200_model* m, nb200_stats* out);
+
+/* ---- measurement (the reference has only wall-clock accumulators, src/nemo-stream.h:237-244) ------------- */
+/* CUDA-event stopwatch on the library's own stream: start records an event, stop records a second one, waits for
+ * it and returns the elapsed DEVICE time in ms (covers everything queued on that stream in between). */
+int nb200_timer_start(nb200_model* m);
+int nb200_timer_stop(nb200_model* m, double* ms_out);
+/* Per-kernel-family device timing: while enabled every launch is bracketed by CUDA events on the launching stream.
+ * report() writes a JSON object {"family": {"launches","ms","flops","bytes"}} (algorithmic FLOPs / bytes of the
+ * launches) into json_out, clears the records and returns the string length, or <0 if cap is too small. */
+int nb200_profile_enable(nb200_model* m, int on);
+int nb200_profile_report(nb200_model* m, char* json_out, int cap);
 
 /* ---- kernel-level entry points (used by the parity tests and bench; same kernels the step uses) -------- */
 /* nemo_preprocessor_process (src/preprocessor.cpp:330-395) for a batch of independent signals, each starting

@@ -36,6 +36,23 @@ extern long long g_launches;  // kernels launched by this library (reported as g
 #define NB_LAUNCHED() (++::nb::g_launches)
 #define NB_KERNEL_CHECK() do { NB_LAUNCHED(); CUDA_CHECK(cudaGetLastError()); } while (0)
 
+// Per-kernel-family device timing (nb200_profile_*): when enabled, every launcher brackets its launch with CUDA events
+// on the launching stream and reports the algorithmic FLOPs / bytes of that launch; prof.cu aggregates per family.
+extern bool g_prof_on;
+void prof_begin(cudaStream_t st, const char* family, double flops, double bytes);
+void prof_end(cudaStream_t st);
+std::string prof_report();  // JSON of per-family totals since the last report; clears the records
+struct ProfScope {
+    cudaStream_t st;
+    bool on;
+    ProfScope(cudaStream_t s, const char* family, double flops, double bytes) : st(s), on(g_prof_on) {
+        if (on) prof_begin(st, family, flops, bytes);
+    }
+    ~ProfScope() {
+        if (on) prof_end(st);
+    }
+};
+
 template <typename T>
 T* dalloc(size_t n) {
     T* p = nullptr;

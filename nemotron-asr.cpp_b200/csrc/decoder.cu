@@ -63,6 +63,7 @@ void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* 
                   int ldc, const int* out_rows) {
     if (M <= 0) return;
     if (N % 64 != 0 || K % 16 != 0) throw Error("sgemm: N must be a multiple of 64 and K of 16");
+    ProfScope ps(st, "sgemm_f32", 2.0 * M * (double)N * K, 4.0 * ((double)M * K + (double)N * K + (double)M * N));
     sgemm_nt_kernel<<<dim3(N / 64, cdiv(M, 64)), 256, 0, st>>>(A, W, bias, C, M, N, K, ldc, out_rows);
     NB_KERNEL_CHECK();
 }

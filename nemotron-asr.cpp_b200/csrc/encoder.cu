@@ -71,6 +71,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict_
 void launch_layernorm(cudaStream_t st, const float* x, const float* g1, const float* b1, float* out_f32, const float* g2,
                       const float* b2, __half* out_f16, int act_quant, int M) {
     if (M <= 0) return;
+    ProfScope ps(st, "layernorm", (double)M * D_MODEL * 8, (double)M * D_MODEL * (4 + (out_f32 ? 4 : 0) + (out_f16 ? 2 : 0)));
     layernorm_kernel<<<M, 256, 0, st>>>(x, g1, b1, out_f32, g2, b2, out_f16, act_quant);
     NB_KERNEL_CHECK();
 }
@@ -194,8 +195,13 @@ void launch_attention(cudaStream_t st, const AttnArgs& a) {
         CUDA_CHECK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(MAX_T)));
         configured = true;
     }
-    attention_kernel<<<dim3(N_HEADS, a.B), 256, attn_smem_bytes(a.T), st>>>(a);
-    NB_KERNEL_CHECK();
+    {
+        const double kv = LEFT + a.T;
+        ProfScope ps(st, "attention", 6.0 * a.B * a.T * kv * D_MODEL,
+                     (double)a.B * (2.0 * kv * D_MODEL * 4 + (double)a.T * D_MODEL * 6) + (LEFT + 2.0 * a.T - 1) * D_MODEL * 4);
+        attention_kernel<<<dim3(N_HEADS, a.B), 256, attn_smem_bytes(a.T), st>>>(a);
+        NB_KERNEL_CHECK();
+    }
 }
 
 // ---- cached causal depthwise conv (9 taps) + LayerNorm + SiLU --------------------------------------
@@ -225,6 +231,7 @@ __global__ void __launch_bounds__(256) dwconv_kernel(ConvArgs a) {
 }
 
 void launch_dwconv(cudaStream_t st, const ConvArgs& a) {
+    ProfScope ps(st, "dwconv_ln_silu", (double)a.B * a.T * D_MODEL * 30, (double)a.B * ((a.T + 8.0) * D_MODEL * 4 + (double)a.T * D_MODEL * 2));
     dwconv_kernel<<<dim3(a.T, a.B), 256, 0, st>>>(a);
     NB_KERNEL_CHECK();
 }
@@ -245,6 +252,7 @@ __global__ void __launch_bounds__(256) conv_cache_update_kernel(ConvArgs a) {
 }
 
 void launch_conv_cache_update(cudaStream_t st, const ConvArgs& a) {
+    ProfScope ps(st, "conv_cache_update", 0.0, (double)a.B * 16.0 * D_MODEL * 4);
     conv_cache_update_kernel<<<a.B, 256, 0, st>>>(a);
     NB_KERNEL_CHECK();
 }

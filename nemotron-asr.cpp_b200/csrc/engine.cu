@@ -66,10 +66,11 @@ struct nb200_stream {
     nb200_model* model = nullptr;
     int slot = -1;
     int rc = 0;
-    // host-side audio buffer: pcm[i] is absolute sample pcm_base + i
-    std::vector<int16_t> pcm;
-    long long pcm_base = 0;
-    long long samples_total = 0;
+    // audio: samples [0, fed) have been uploaded into this slot's device PCM ring; `pending` holds samples that did
+    // not fit yet (the ring keeps what unprocessed chunks still need) and is flushed as chunks are consumed.
+    std::vector<int16_t> pending;
+    long long fed = 0;
+    long long samples_total = 0;  // fed + pending.size()
     long long chunks_done = 0;
     bool finalize_requested = false, finalized = false;
     int wpos = 0;   // K/V ring write index
@@ -99,7 +100,12 @@ struct nb200_model {
     float *joint_enc_w = nullptr, *joint_enc_b = nullptr;  // fp32: the decoder side stays in fp32 like the reference
     std::vector<LayerW> layers;
     DecodeWeights dec{};
-    std::map<std::string, F16Matrix*> by_name;
+    struct NamedMatrix {   // GGUF tensor name -> where its rows live in our (possibly fused / interleaved) fp16 storage
+        const __half* ptr;
+        int rows, K;
+        bool glu_interleaved;  // pointwise_conv1: row 2j = value j, row 2j+1 = gate j
+    };
+    std::map<std::string, NamedMatrix> by_name;
     // per-slot state
     float *k_ring = nullptr, *v_ring = nullptr, *conv_cache = nullptr;  // [L][slots][...]
     float* mel_overlap = nullptr;                                      // [slots][9][128]
@@ -113,18 +119,20 @@ struct nb200_model {
     __half *ws_a2h = nullptr, *ws_a5h = nullptr, *ws_a6h = nullptr, *ws_a16 = nullptr, *ws_h16 = nullptr, *ws_pos16 = nullptr;
     float* ws_posf = nullptr;
     Operand op_a2h, op_a5h, op_a6h, op_a16, op_h16, op_pos16;
-    int16_t* ws_pcm = nullptr;
-    int pcm_stride = 0;
+    int16_t* pcm_ring = nullptr;   // [slots][ring_cap] device-resident audio (nb200_stream_feed uploads into it)
+    int ring_cap = 0;              // samples per slot, power of two
     int* ws_meta = nullptr;        // int arrays [8][cap_B]
-    long long* ws_meta64 = nullptr;  // [cap_B]
+    long long* ws_meta64 = nullptr;  // long long arrays [3][cap_B]: out_off, a0, n_avail
     int *ws_fp = nullptr, *ws_sym = nullptr, *ws_tok = nullptr, *ws_tokcnt = nullptr, *ws_unfinished = nullptr;
     float *ws_hid = nullptr, *ws_logits = nullptr, *ws_lx = nullptr, *ws_gates = nullptr, *ws_hp = nullptr;
-    PinnedBuf<int16_t> h_pcm;
+    PinnedBuf<int16_t> h_stage;   // pinned staging of fed audio; offsets reset whenever the stream has been synchronised
+    size_t stage_off = 0;
     PinnedBuf<int> h_meta;
     PinnedBuf<long long> h_meta64;
     PinnedBuf<int> h_tok;
     PinnedBuf<float> h_tap;
     cudaEvent_t ev[4]{};
+    cudaEvent_t tev[2]{};
     nb200_stats stats{};
 
     template <typename T>
@@ -144,6 +152,8 @@ struct nb200_model {
         for (auto* s : streams) delete s;
         for (void* p : allocs) cudaFree(p);
         for (auto& e : ev)
+            if (e) cudaEventDestroy(e);
+        for (auto& e : tev)
             if (e) cudaEventDestroy(e);
         if (st) cudaStreamDestroy(st);
     }
@@ -165,7 +175,7 @@ void make_f16(nb200_model* m, F16Matrix& dst, const std::vector<float>& w, int r
     for (size_t i = 0; i < h.size(); i++) h[i] = __float2half_rn(w[i]);
     dst.ptr = m->upload(h);
     operand_init(dst.op, dst.ptr, rows, K);
-    if (!name.empty()) m->by_name[name] = &dst;
+    if (!name.empty()) m->by_name[name] = {dst.ptr, rows, K, false};
 }
 
 void load_matrix(nb200_model* m, const GgufFile& g, F16Matrix& dst, const std::string& name, int rows, int K) {
@@ -306,6 +316,7 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
                 std::copy(part.begin(), part.end(), w.begin() + (size_t)i * D_MODEL * D_MODEL);
             }
             make_f16(m, L.wqkv, w, 3 * D_MODEL, D_MODEL);
+            for (int i = 0; i < 3; i++) m->by_name[p + nm[i]] = {L.wqkv.ptr + (size_t)i * D_MODEL * D_MODEL, D_MODEL, D_MODEL, false};
         }
         {   // pointwise_conv1: rows 0..1023 = GLU value, 1024..2047 = gate -> interleave (value_j, gate_j)
             std::vector<float> w = load_f32(g, p + "conv.pointwise_conv1.weight", (int64_t)2 * D_MODEL * D_MODEL), wi(w.size());
@@ -315,6 +326,7 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
                           wi.begin() + (size_t)(2 * j + 1) * D_MODEL);
             }
             make_f16(m, L.pw1, wi, 2 * D_MODEL, D_MODEL);
+            m->by_name[p + "conv.pointwise_conv1.weight"] = {L.pw1.ptr, 2 * D_MODEL, D_MODEL, true};
         }
     }
     // ---- decoder + joint (src/nemo-ggml.cpp:369-388), kept fp32 ----
@@ -391,10 +403,14 @@ void alloc_state(nb200_model* m) {
     operand_init(m->op_a16, m->ws_a16, (int)rows_pad, D_MODEL);
     operand_init(m->op_h16, m->ws_h16, (int)rows_pad, D_FF);
     operand_init(m->op_pos16, m->ws_pos16, 128, D_MODEL);
-    m->pcm_stride = HOP * big.shift + 360;
-    m->ws_pcm = m->alloc<int16_t>((size_t)B * m->pcm_stride);
+    {   // device PCM ring per slot: default 2^17 samples (8.2 s); NB200_PCM_RING_LOG2 overrides (15..24)
+        int lg = 17;
+        if (const char* e = getenv("NB200_PCM_RING_LOG2")) lg = std::min(24, std::max(15, atoi(e)));
+        m->ring_cap = 1 << lg;
+        m->pcm_ring = m->alloc<int16_t>(S * (size_t)m->ring_cap);
+    }
     m->ws_meta = m->alloc<int>((size_t)META_ROWS * B);
-    m->ws_meta64 = m->alloc<long long>(B);
+    m->ws_meta64 = m->alloc<long long>((size_t)3 * B);
     m->ws_fp = m->alloc<int>(B);
     m->ws_sym = m->alloc<int>(B);
     m->ws_tok = m->alloc<int>((size_t)B * MAX_T * MAX_SYMBOLS);
@@ -405,11 +421,12 @@ void alloc_state(nb200_model* m) {
     m->ws_lx = m->alloc<float>((size_t)B * 2 * DEC);
     m->ws_gates = m->alloc<float>((size_t)B * 4 * DEC);
     m->ws_hp = m->alloc<float>((size_t)B * DEC);
-    m->h_pcm.reserve((size_t)B * m->pcm_stride);
+    m->h_stage.reserve(std::max<size_t>((size_t)1 << 22, (size_t)B * (HOP * big.shift + 1024)));  // >= one rc=13 chunk per slot
     m->h_meta.reserve((size_t)META_ROWS * B);
-    m->h_meta64.reserve(B);
+    m->h_meta64.reserve((size_t)3 * B);
     m->h_tok.reserve((size_t)B * (MAX_T * MAX_SYMBOLS + 2) + 1);
     for (auto& e : m->ev) CUDA_CHECK(cudaEventCreate(&e));
+    for (auto& e : m->tev) CUDA_CHECK(cudaEventCreate(&e));
 }
 
 // linear_pos(PE(p)) for every layer: constant per latency mode, so it is computed once here instead of in every layer
@@ -492,6 +509,42 @@ long long frames_available(long long n_samples) {  // src/preprocessor.cpp:320-3
     return n_samples + 256 < N_FFT ? 0 : (n_samples + 256 - N_FFT) / HOP + 1;
 }
 
+// oldest absolute sample the stream's next chunk still needs (everything before it may be overwritten in the ring)
+long long keep_from(const nb200_stream* s) {
+    const Mode md(s->rc);
+    return std::max<long long>(0, (long long)HOP * md.shift * s->chunks_done - 257);
+}
+
+// Upload up to n samples into the slot's device ring (pinned staging -> cudaMemcpyAsync on the library's stream, at
+// most two segments when the ring wraps). Returns the number of samples taken (less than n when the ring is full).
+size_t upload_pcm(nb200_model* m, nb200_stream* s, const int16_t* pcm, size_t n) {
+    const long long space = (long long)m->ring_cap - (s->fed - keep_from(s));
+    n = (size_t)std::max<long long>(0, std::min<long long>((long long)n, space));
+    size_t done = 0;
+    while (done < n) {
+        if (m->stage_off >= m->h_stage.n) {  // staging exhausted: wait for the queued copies, then reuse it
+            CUDA_CHECK(cudaStreamSynchronize(m->st));
+            m->stage_off = 0;
+        }
+        const size_t pos = (size_t)(s->fed & (long long)(m->ring_cap - 1));
+        const size_t k = std::min({n - done, m->h_stage.n - m->stage_off, (size_t)m->ring_cap - pos});
+        int16_t* stg = m->h_stage.p + m->stage_off;
+        memcpy(stg, pcm + done, k * sizeof(int16_t));
+        CUDA_CHECK(cudaMemcpyAsync(m->pcm_ring + (size_t)s->slot * m->ring_cap + pos, stg, k * sizeof(int16_t), cudaMemcpyHostToDevice, m->st));
+        m->stage_off += k;
+        s->fed += (long long)k;
+        done += k;
+        m->stats.h2d_bytes += (long long)(k * sizeof(int16_t));
+    }
+    return n;
+}
+
+void flush_pending(nb200_model* m, nb200_stream* s) {
+    if (s->pending.empty()) return;
+    const size_t k = upload_pcm(m, s, s->pending.data(), s->pending.size());
+    s->pending.erase(s->pending.begin(), s->pending.begin() + k);
+}
+
 struct BatchItem {
     nb200_stream* s;
     int n_frames;  // new mel frames computed for this chunk (shift, or fewer for a finalize tail)
@@ -510,10 +563,10 @@ void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
     const int aq = m->act_quant ? 1 : 0;
     const bool simt = m->simt;
     cudaStream_t st = m->st;
-    const int stride = HOP * md.shift + 360;
 
-    // ---- host -> pinned staging: metadata + the PCM window of every item ----
+    // ---- per-item metadata (the audio itself is already resident in the slots' device PCM rings) ----
     int* meta = m->h_meta.p;
+    long long* meta64 = m->h_meta64.p;
     for (int b = 0; b < B; b++) {
         nb200_stream* s = items[b].s;
         meta[0 * capB + b] = s->slot;
@@ -521,21 +574,15 @@ void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
         meta[2 * capB + b] = s->valid;
         meta[3 * capB + b] = items[b].nvalid;
         meta[4 * capB + b] = items[b].n_frames;
-        m->h_meta64.p[b] = ((long long)b * md.chunk_mel + MEL_OVERLAP) * N_MELS;
-        // element e of the window is absolute sample a0 + e; a0 = first new frame's first sample - 1 (pre-emphasis)
-        const long long a0 = (long long)HOP * md.shift * s->chunks_done - 257;
-        const int count = HOP * items[b].n_frames + 353;
-        int16_t* dst = m->h_pcm.p + (size_t)b * stride;
-        for (int e = 0; e < count; e++) {
-            const long long a = a0 + e, i = a - s->pcm_base;
-            dst[e] = (a >= 0 && i >= 0 && i < (long long)s->pcm.size()) ? s->pcm[(size_t)i] : (int16_t)0;
-        }
-        for (int e = count; e < stride; e++) dst[e] = 0;
+        meta64[0 * capB + b] = ((long long)b * md.chunk_mel + MEL_OVERLAP) * N_MELS;
+        // frame f of this chunk covers absolute samples a0 + 160 f + [0, 513): a0 = first new frame's first sample - 1
+        meta64[1 * capB + b] = (long long)HOP * md.shift * s->chunks_done - 257;
+        meta64[2 * capB + b] = s->fed;
     }
     CUDA_CHECK(cudaEventRecord(m->ev[0], st));
-    CUDA_CHECK(cudaMemcpyAsync(m->ws_pcm, m->h_pcm.p, (size_t)B * stride * sizeof(int16_t), cudaMemcpyHostToDevice, st));
     CUDA_CHECK(cudaMemcpyAsync(m->ws_meta, meta, (size_t)META_ROWS * capB * sizeof(int), cudaMemcpyHostToDevice, st));
-    CUDA_CHECK(cudaMemcpyAsync(m->ws_meta64, m->h_meta64.p, (size_t)B * sizeof(long long), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(m->ws_meta64, meta64, (size_t)3 * capB * sizeof(long long), cudaMemcpyHostToDevice, st));
+    m->stats.h2d_bytes += (long long)META_ROWS * capB * sizeof(int) + (long long)3 * capB * sizeof(long long);
     const int* d_slot = m->ws_meta + 0 * capB;
     const int* d_wpos = m->ws_meta + 1 * capB;
     const int* d_valid = m->ws_meta + 2 * capB;
@@ -544,7 +591,10 @@ void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
     // ---- frontend: log-mel of the new samples, then dw-striding subsampling (src/nemo-ggml.cpp:954-1029) ----
     mel_assemble_kernel<<<dim3(md.chunk_mel, B), N_MELS, 0, st>>>(m->ws_mel, m->mel_overlap, d_slot, d_nframes, md.chunk_mel);
     NB_KERNEL_CHECK();
-    launch_mel(st, m->mel_tb, m->ws_pcm, stride, d_nframes, m->ws_meta64, m->ws_mel, B, md.shift);
+    {
+        MelBatch mb{m->pcm_ring, m->ring_cap, d_slot, d_nframes, m->ws_meta64 + 1 * capB, m->ws_meta64 + 2 * capB, m->ws_meta64 + 0 * capB};
+        launch_mel(st, m->mel_tb, mb, m->ws_mel, B, md.shift);
+    }
     for (int b = 0; b < B; b++) {
         nb200_stream* s = items[b].s;
         if ((s->taps & NB200_TAP_MEL) && items[b].n_frames > 0) {
@@ -657,6 +707,8 @@ void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
     CUDA_CHECK(cudaMemcpyAsync(h_toks, m->ws_tok, sizeof(int) * (size_t)B * T * MAX_SYMBOLS, cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaEventRecord(m->ev[3], st));
     CUDA_CHECK(cudaStreamSynchronize(st));
+    m->stage_off = 0;  // every queued audio upload has completed
+    m->stats.d2h_bytes += (long long)sizeof(int) * ((size_t)2 * B + (size_t)B * T * MAX_SYMBOLS) + (long long)rounds / 4 * sizeof(int);
 
     // ---- host bookkeeping ----
     long long frames = 0, toks = 0;
@@ -673,12 +725,6 @@ void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
         s->chunks_done++;
         s->wpos = (s->wpos + T) % RING;
         s->valid = std::min(s->valid + T, LEFT);  // src/nemo-stream.cpp:1085
-        const long long keep_from = (long long)HOP * md.shift * s->chunks_done - 257;
-        if (keep_from > s->pcm_base) {
-            const size_t drop = (size_t)std::min<long long>(keep_from - s->pcm_base, (long long)s->pcm.size());
-            s->pcm.erase(s->pcm.begin(), s->pcm.begin() + drop);
-            s->pcm_base += drop;
-        }
         m->stats.audio_seconds += (double)items[b].n_frames * HOP / 16000.0;
     }
     float ms01 = 0, ms12 = 0, ms23 = 0;
@@ -817,8 +863,8 @@ int nb200_stream_reset(nb200_stream* s) {
     if (!s) throw Error("null stream");
     CUDA_CHECK(cudaSetDevice(s->model->device));
     reset_slot(s->model, s->slot);
-    s->pcm.clear();
-    s->pcm_base = s->samples_total = s->chunks_done = 0;
+    s->pending.clear();
+    s->fed = s->samples_total = s->chunks_done = 0;
     s->finalize_requested = s->finalized = false;
     s->wpos = s->valid = 0;
     s->tokens.clear();
@@ -836,22 +882,26 @@ int nb200_stream_feed(nb200_stream* s, const int16_t* pcm, int n_samples) {
     if (!s) throw Error("null stream");
     if (n_samples <= 0 || !pcm) return NB200_OK;  // like the reference: nothing to do (src/nemo-stream.cpp:1150)
     if (s->finalized || s->finalize_requested) throw Error("stream already finalized; reset it first");
-    s->pcm.insert(s->pcm.end(), pcm, pcm + n_samples);
+    CUDA_CHECK(cudaSetDevice(s->model->device));
+    flush_pending(s->model, s);
+    size_t took = 0;
+    if (s->pending.empty()) took = upload_pcm(s->model, s, pcm, (size_t)n_samples);
+    s->pending.insert(s->pending.end(), pcm + took, pcm + n_samples);
     s->samples_total += n_samples;
     return NB200_OK;
     NB_CATCH(NB200_ERR)
 }
 
-static int full_chunks_ready(const nb200_stream* s) {
+static int full_chunks_ready(const nb200_stream* s) {  // counts device-resident audio only
     const Mode md(s->rc);
-    const long long frames = frames_available(s->samples_total);
+    const long long frames = frames_available(s->fed);
     const long long have = frames - (long long)md.shift * s->chunks_done;
     return have < md.shift ? 0 : (int)(have / md.shift);
 }
 
 static int tail_frames(const nb200_stream* s) {  // new mel frames left for a finalize tail (src/nemo-stream.cpp:1240-1244)
     const Mode md(s->rc);
-    return (int)(frames_available(s->samples_total) - (long long)md.shift * s->chunks_done);
+    return (int)(frames_available(s->fed) - (long long)md.shift * s->chunks_done);
 }
 
 int nb200_stream_finalize(nb200_stream* s) {
@@ -863,6 +913,7 @@ int nb200_stream_finalize(nb200_stream* s) {
 int nb200_stream_ready_chunks(const nb200_stream* s) {
     if (!s || s->finalized) return 0;
     int n = full_chunks_ready(s);
+    if (n == 0 && !s->pending.empty()) return 1;  // the next step uploads the rest of the fed audio
     if (s->finalize_requested) {
         const Mode md(s->rc);
         const int rem = tail_frames(s) - n * md.shift;
@@ -878,10 +929,11 @@ int nb200_step(nb200_model* m) {
     std::map<int, std::vector<BatchItem>> groups;
     for (nb200_stream* s : m->streams) {
         if (s->finalized) continue;
+        flush_pending(m, s);
         const Mode md(s->rc);
         if (full_chunks_ready(s) > 0) {
             groups[s->rc].push_back({s, md.shift, md.T});
-        } else if (s->finalize_requested) {
+        } else if (s->finalize_requested && s->pending.empty()) {
             const int rem = tail_frames(s);
             const int n_valid = rem / 8;  // floor(real_new / subsampling_factor), src/nemo-stream.cpp:1243
             if (n_valid > 0) groups[s->rc].push_back({s, rem, n_valid});
@@ -964,31 +1016,79 @@ int nb200_mel_batch(nb200_model* m, const int16_t* pcm, int n_streams, int n_sam
     CUDA_CHECK(cudaSetDevice(m->device));
     const int nf = (int)frames_available(n_samples);
     if (nf <= 0 || n_streams <= 0) return 0;
-    const int stride = HOP * (nf - 1) + N_FFT + 1;
-    std::vector<int16_t> win((size_t)n_streams * stride, 0);
-    for (int b = 0; b < n_streams; b++)
-        for (int e = 0; e < stride; e++) {
-            const long long a = (long long)e - 257;  // a0 = -257: 256 zeros of centre padding + the pre-emphasis sample
-            if (a >= 0 && a < n_samples) win[(size_t)b * stride + e] = pcm[(size_t)b * n_samples + a];
-        }
-    std::vector<int> nfr(n_streams, nf);
-    std::vector<long long> off(n_streams);
-    for (int b = 0; b < n_streams; b++) off[b] = (long long)b * nf * N_MELS;
-    int16_t* d_pcm = dalloc<int16_t>(win.size());
-    int* d_nf = dalloc<int>(n_streams);
-    long long* d_off = dalloc<long long>(n_streams);
+    int cap = 1;
+    while (cap < n_samples) cap <<= 1;  // a private "ring" that holds each whole signal
+    std::vector<int> slot(n_streams), nfr(n_streams, nf);
+    std::vector<long long> m64((size_t)3 * n_streams);
+    for (int b = 0; b < n_streams; b++) {
+        slot[b] = b;
+        m64[0 * n_streams + b] = (long long)b * nf * N_MELS;  // out_off
+        m64[1 * n_streams + b] = -257;                        // a0: 256 zeros of centre padding + the pre-emphasis sample
+        m64[2 * n_streams + b] = n_samples;                   // n_avail
+    }
+    int16_t* d_pcm = dalloc<int16_t>((size_t)n_streams * cap);
+    int* d_i = dalloc<int>((size_t)2 * n_streams);
+    long long* d_l = dalloc<long long>(m64.size());
     float* d_mel = dalloc<float>((size_t)n_streams * nf * N_MELS);
-    CUDA_CHECK(cudaMemcpyAsync(d_pcm, win.data(), win.size() * sizeof(int16_t), cudaMemcpyHostToDevice, m->st));
-    CUDA_CHECK(cudaMemcpyAsync(d_nf, nfr.data(), n_streams * sizeof(int), cudaMemcpyHostToDevice, m->st));
-    CUDA_CHECK(cudaMemcpyAsync(d_off, off.data(), n_streams * sizeof(long long), cudaMemcpyHostToDevice, m->st));
-    launch_mel(m->st, m->mel_tb, d_pcm, stride, d_nf, d_off, d_mel, n_streams, nf);
+    CUDA_CHECK(cudaMemcpy2DAsync(d_pcm, (size_t)cap * sizeof(int16_t), pcm, (size_t)n_samples * sizeof(int16_t),
+                                 (size_t)n_samples * sizeof(int16_t), n_streams, cudaMemcpyHostToDevice, m->st));
+    CUDA_CHECK(cudaMemcpyAsync(d_i, slot.data(), n_streams * sizeof(int), cudaMemcpyHostToDevice, m->st));
+    CUDA_CHECK(cudaMemcpyAsync(d_i + n_streams, nfr.data(), n_streams * sizeof(int), cudaMemcpyHostToDevice, m->st));
+    CUDA_CHECK(cudaMemcpyAsync(d_l, m64.data(), m64.size() * sizeof(long long), cudaMemcpyHostToDevice, m->st));
+    MelBatch mb{d_pcm, cap, d_i, d_i + n_streams, d_l + n_streams, d_l + 2 * n_streams, d_l};
+    launch_mel(m->st, m->mel_tb, mb, d_mel, n_streams, nf);
     CUDA_CHECK(cudaMemcpyAsync(mel_out, d_mel, (size_t)n_streams * nf * N_MELS * sizeof(float), cudaMemcpyDeviceToHost, m->st));
     CUDA_CHECK(cudaStreamSynchronize(m->st));
     cudaFree(d_pcm);
-    cudaFree(d_nf);
-    cudaFree(d_off);
+    cudaFree(d_i);
+    cudaFree(d_l);
     cudaFree(d_mel);
     return nf;
+    NB_CATCH(NB200_ERR)
+}
+
+int nb200_timer_start(nb200_model* m) {
+    NB_TRY
+    if (!m) throw Error("null model");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    CUDA_CHECK(cudaEventRecord(m->tev[0], m->st));
+    return NB200_OK;
+    NB_CATCH(NB200_ERR)
+}
+
+int nb200_timer_stop(nb200_model* m, double* ms_out) {
+    NB_TRY
+    if (!m || !ms_out) throw Error("null argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    CUDA_CHECK(cudaEventRecord(m->tev[1], m->st));
+    CUDA_CHECK(cudaEventSynchronize(m->tev[1]));
+    float ms = 0;
+    CUDA_CHECK(cudaEventElapsedTime(&ms, m->tev[0], m->tev[1]));
+    *ms_out = ms;
+    return NB200_OK;
+    NB_CATCH(NB200_ERR)
+}
+
+int nb200_profile_enable(nb200_model* m, int on) {
+    NB_TRY
+    if (!m) throw Error("null model");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    CUDA_CHECK(cudaStreamSynchronize(m->st));
+    if (on) prof_report();  // drop stale records
+    g_prof_on = on != 0;
+    return NB200_OK;
+    NB_CATCH(NB200_ERR)
+}
+
+int nb200_profile_report(nb200_model* m, char* json_out, int cap) {
+    NB_TRY
+    if (!m || !json_out || cap <= 0) throw Error("bad argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    CUDA_CHECK(cudaStreamSynchronize(m->st));
+    const std::string r = prof_report();
+    if ((int)r.size() + 1 > cap) throw Error("profile report buffer too small");
+    memcpy(json_out, r.c_str(), r.size() + 1);
+    return (int)r.size();
     NB_CATCH(NB200_ERR)
 }
 
@@ -997,8 +1097,9 @@ int nb200_debug_matmul(nb200_model* m, const char* tensor_name, const float* x, 
     if (!m || !tensor_name || !x || !y || M <= 0) throw Error("bad argument");
     CUDA_CHECK(cudaSetDevice(m->device));
     auto it = m->by_name.find(tensor_name);
-    if (it == m->by_name.end()) throw Error(std::string("no such (unfused) matrix: ") + tensor_name);
-    const Operand& W = it->second->op;
+    if (it == m->by_name.end()) throw Error(std::string("no such encoder matrix: ") + tensor_name);
+    Operand W;
+    operand_init(W, it->second.ptr, it->second.rows, it->second.K);
     const int K = W.K, N = W.rows;
     if (K % 1024 != 0) throw Error("debug_matmul supports K multiple of 1024");
     const int Mp = (M + 127) / 128 * 128;
@@ -1015,7 +1116,18 @@ int nb200_debug_matmul(nb200_model* m, const char* tensor_name, const float* x, 
     ep.out_f32 = dy;
     ep.ldo = N;
     gemm(m->st, A, W, M, ep, m->simt);
-    CUDA_CHECK(cudaMemcpyAsync(y, dy, (size_t)M * N * sizeof(float), cudaMemcpyDeviceToHost, m->st));
+    if (it->second.glu_interleaved) {  // undo the load-time row interleave so y is in the tensor's own row order
+        std::vector<float> tmp((size_t)M * N);
+        CUDA_CHECK(cudaMemcpyAsync(tmp.data(), dy, tmp.size() * sizeof(float), cudaMemcpyDeviceToHost, m->st));
+        CUDA_CHECK(cudaStreamSynchronize(m->st));
+        for (int r = 0; r < M; r++)
+            for (int j = 0; j < N / 2; j++) {
+                y[(size_t)r * N + j] = tmp[(size_t)r * N + 2 * j];
+                y[(size_t)r * N + N / 2 + j] = tmp[(size_t)r * N + 2 * j + 1];
+            }
+    } else {
+        CUDA_CHECK(cudaMemcpyAsync(y, dy, (size_t)M * N * sizeof(float), cudaMemcpyDeviceToHost, m->st));
+    }
     CUDA_CHECK(cudaStreamSynchronize(m->st));
     cudaFree(dx);
     cudaFree(dx16);

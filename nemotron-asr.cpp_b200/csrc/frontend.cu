@@ -10,17 +10,22 @@
 
 namespace nb {
 
-__global__ void __launch_bounds__(256) mel_kernel(MelTables tb, const int16_t* __restrict__ pcm, int pcm_stride,
-                                                  const int* __restrict__ n_frames, const long long* __restrict__ out_off,
-                                                  float* __restrict__ mel_out) {
+__global__ void __launch_bounds__(256) mel_kernel(MelTables tb, MelBatch mb, float* __restrict__ mel_out) {
     const int f = blockIdx.x, b = blockIdx.y;
-    if (f >= n_frames[b]) return;
+    if (f >= mb.n_frames[b]) return;
     __shared__ float xs[N_FFT + 1];
     __shared__ float re[N_FFT], im[N_FFT];
     __shared__ float pw[N_BINS];
     const int t = threadIdx.x;
-    const int16_t* src = pcm + (size_t)b * pcm_stride + (size_t)f * HOP;
-    for (int i = t; i < N_FFT + 1; i += 256) xs[i] = __fmul_rn((float)src[i], 1.0f / 32768.0f);
+    // element i of this frame is absolute sample a0 + 160 f + i; samples before the stream start are the centre
+    // padding (zeros), samples at or beyond n_avail are the zero padding of a finalize tail.
+    const int16_t* ring = mb.ring + (size_t)mb.slot[b] * mb.ring_cap;
+    const long long a_first = mb.a0[b] + (long long)f * HOP, n_avail = mb.n_avail[b];
+    for (int i = t; i < N_FFT + 1; i += 256) {
+        const long long a = a_first + i;
+        const int16_t s = (a >= 0 && a < n_avail) ? ring[a & (long long)(mb.ring_cap - 1)] : (int16_t)0;
+        xs[i] = __fmul_rn((float)s, 1.0f / 32768.0f);
+    }
     __syncthreads();
     for (int i = t; i < N_FFT; i += 256) {
         float y = __fsub_rn(xs[i + 1], __fmul_rn(0.97f, xs[i]));
@@ -57,14 +62,14 @@ __global__ void __launch_bounds__(256) mel_kernel(MelTables tb, const int16_t* _
         const int2 rg = tb.fb_range[t];
         float sum = 0.0f;
         for (int k = rg.x; k < rg.y; k++) sum = __fadd_rn(sum, __fmul_rn(tb.fbT[k * N_MELS + t], pw[k]));
-        mel_out[out_off[b] + (long long)f * N_MELS + t] = logf(__fadd_rn(sum, 5.960464477539063e-8f));
+        mel_out[mb.out_off[b] + (long long)f * N_MELS + t] = logf(__fadd_rn(sum, 5.960464477539063e-8f));
     }
 }
 
-void launch_mel(cudaStream_t st, const MelTables& tb, const int16_t* pcm, int pcm_stride, const int* n_frames,
-                const long long* out_off, float* mel_out, int B, int max_frames) {
+void launch_mel(cudaStream_t st, const MelTables& tb, const MelBatch& mb, float* mel_out, int B, int max_frames) {
     if (B <= 0 || max_frames <= 0) return;
-    mel_kernel<<<dim3(max_frames, B), 256, 0, st>>>(tb, pcm, pcm_stride, n_frames, out_off, mel_out);
+    ProfScope ps(st, "mel", (double)B * max_frames * 2.0e5, (double)B * max_frames * (HOP * 2 + N_MELS * 4));
+    mel_kernel<<<dim3(max_frames, B), 256, 0, st>>>(tb, mb, mel_out);
     NB_KERNEL_CHECK();
 }
 
@@ -117,6 +122,8 @@ __global__ void __launch_bounds__(256) sub_stage1_kernel(SubWeights w, const flo
 }
 
 void launch_sub_stage1(cudaStream_t st, const SubWeights& w, const float* mel, __half* out, int B, int chunk_mel, int t1, int t2) {
+    ProfScope ps(st, "sub_conv0_dw2", (double)B * t2 * SUB_F2 * SUB_CH * 2.0 * 9 * 10,
+                 (double)B * (chunk_mel * N_MELS * 4.0 + (double)t2 * SUB_F2 * SUB_CH * 2));
     sub_stage1_kernel<<<dim3(t2, B), 256, 0, st>>>(w, mel, out, chunk_mel, t1, t2);
     NB_KERNEL_CHECK();
 }
@@ -142,6 +149,8 @@ __global__ void __launch_bounds__(256) sub_stage2_kernel(SubWeights w, const flo
 }
 
 void launch_sub_stage2(cudaStream_t st, const SubWeights& w, const float* a3, __half* out, int B, int t2, int t3) {
+    ProfScope ps(st, "sub_dw5", (double)B * (t3 - 2) * SUB_F3 * SUB_CH * 18.0,
+                 (double)B * ((double)t2 * SUB_F2 * SUB_CH * 4 + (double)(t3 - 2) * SUB_F3 * SUB_CH * 2));
     sub_stage2_kernel<<<dim3(SUB_F3, t3 - 2, B), 256, 0, st>>>(w, a3, out, t2, t3);
     NB_KERNEL_CHECK();
 }

@@ -306,6 +306,12 @@ void gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiP
     if (M > A.rows) throw Error("GEMM: M exceeds the activation buffer");
     const int N = W.rows;
     if (N % 64 != 0) throw Error("GEMM: N must be a multiple of 64");
+    const double flops = 2.0 * M * (double)N * A.K;
+    const double out_b = epi.kind == EPI_RESID ? 8.0 : (epi.kind == EPI_STORE_F16 ? 2.0 : (epi.kind == EPI_GLU ? 2.0 : 4.0));
+    const double bytes = 2.0 * ((double)M * A.K + (double)N * A.K) + out_b * M * (double)N;
+    const int m_tiles = cdiv(M, TC_BM);
+    const bool wide = N % 128 == 0 && (N / 128) * m_tiles >= 148;
+    ProfScope ps(st, use_simt ? "gemm_simt" : (wide ? "gemm_tc_128x128" : "gemm_tc_128x64"), flops, bytes);
     if (use_simt) {
         dim3 grid(N / 64, cdiv(M, 64));
         gemm_simt_kernel<<<grid, 128, 0, st>>>(A.ptr, W.ptr, M, N, A.K, epi);
@@ -313,8 +319,7 @@ void gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiP
         return;
     }
     // Tile width: 128 when that already gives >= 1 wave of CTAs (or N is not a multiple of 128), else 64.
-    const int m_tiles = cdiv(M, TC_BM);
-    if (N % 128 == 0 && (N / 128) * m_tiles >= 148) {
+    if (wide) {
         launch_tc<128, 3>(st, A, W, M, epi);
     } else {
         launch_tc<64, 4>(st, A, W, M, epi);

@@ -12,11 +12,21 @@ struct MelTables {           // device pointers, built once per model from the G
     const float* fbT;        // filterbank transposed [257][128]
     const int2* fb_range;    // per mel bin: [first, last+1) FFT bins with non-zero weight
 };
-// pcm: per item a window of samples; item b's window starts at pcm + b*pcm_stride and its element 0 is the sample
-// BEFORE the first frame's first sample (pre-emphasis needs x[i-1]). Frame f uses elements [1+160f, 1+160f+512).
+// Audio lives in per-slot device rings (int16, ring_cap a power of two): absolute sample a of slot s is
+// ring[s*ring_cap + (a & (ring_cap-1))]. Item b computes n_frames[b] frames; frame f covers absolute samples
+// a0[b] + 160 f + [0, 513): element 0 is the sample BEFORE the frame's first sample (pre-emphasis needs x[i-1]).
+// Samples with a < 0 (the 256-sample centre pad) or a >= n_avail[b] (finalize tail) read as zero.
 // out: item b, frame f -> mel_out + out_off[b] + f*128 floats (out_off in floats). n_frames[b] <= max_frames.
-void launch_mel(cudaStream_t st, const MelTables& tb, const int16_t* pcm, int pcm_stride, const int* n_frames,
-                const long long* out_off, float* mel_out, int B, int max_frames);
+struct MelBatch {
+    const int16_t* ring;
+    int ring_cap;
+    const int* slot;            // [B]
+    const int* n_frames;        // [B]
+    const long long* a0;        // [B]
+    const long long* n_avail;   // [B]
+    const long long* out_off;   // [B]
+};
+void launch_mel(cudaStream_t st, const MelTables& tb, const MelBatch& mb, float* mel_out, int B, int max_frames);
 
 struct SubWeights {          // encoder.pre_encode.* (src/nemo-ggml.cpp:296-307)
     const float* w0;         // [256][9] fp16-rounded values (conv0 runs through an F16 im2col in the reference)

@@ -30,7 +30,8 @@ class Info(C.Structure):
 
 
 class Stats(C.Structure):
-    _fields_ = [(n, C.c_int64) for n in ("steps", "chunks", "frames", "tokens", "decode_rounds", "kernel_launches")] + \
+    _fields_ = [(n, C.c_int64) for n in ("steps", "chunks", "frames", "tokens", "decode_rounds", "kernel_launches",
+                                         "h2d_bytes", "d2h_bytes")] + \
                [(n, C.c_double) for n in ("audio_seconds", "gpu_seconds", "last_step_gpu_ms", "last_frontend_ms",
                                           "last_encoder_ms", "last_decoder_ms")]
 
@@ -60,6 +61,10 @@ SYMBOLS = {
     "nb200_stream_set_taps": (C.c_int, [C.c_void_p, C.c_int]),
     "nb200_stream_fetch_tap": (C.c_int64, [C.c_void_p, C.c_int, _F32P, C.c_int64]),
     "nb200_get_stats": (C.c_int, [C.c_void_p, C.POINTER(Stats)]),
+    "nb200_timer_start": (C.c_int, [C.c_void_p]),
+    "nb200_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "nb200_profile_enable": (C.c_int, [C.c_void_p, C.c_int]),
+    "nb200_profile_report": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
     "nb200_mel_batch": (C.c_int, [C.c_void_p, _I16P, C.c_int, C.c_int, _F32P]),
     "nb200_debug_matmul": (C.c_int, [C.c_void_p, C.c_char_p, _F32P, C.c_int, _F32P]),
 }
@@ -139,6 +144,28 @@ class Model:
         lib().nb200_get_stats(self._h, C.byref(st))
         return st
 
+    def timer_start(self):
+        if lib().nb200_timer_start(self._h) < 0:
+            raise NB200Error(_err())
+
+    def timer_stop(self) -> float:
+        """Elapsed device time (ms) on the library's stream since timer_start (CUDA events)."""
+        ms = C.c_double()
+        if lib().nb200_timer_stop(self._h, C.byref(ms)) < 0:
+            raise NB200Error(_err())
+        return ms.value
+
+    def profile(self, on: bool):
+        if lib().nb200_profile_enable(self._h, 1 if on else 0) < 0:
+            raise NB200Error(_err())
+
+    def profile_report(self) -> dict:
+        import json
+        buf = C.create_string_buffer(1 << 16)
+        if lib().nb200_profile_report(self._h, buf, len(buf)) < 0:
+            raise NB200Error(_err())
+        return json.loads(buf.value.decode())
+
     def tokens_to_text(self, tokens) -> str:
         t = np.ascontiguousarray(tokens, dtype=np.int32)
         buf = C.create_string_buffer(16 * max(1, t.size) + 16)
@@ -189,6 +216,14 @@ class Stream:
         pcm = np.ascontiguousarray(pcm, dtype=np.int16)
         if lib().nb200_stream_feed(self._h, _ptr(pcm, _I16P), int(pcm.size)) < 0:
             raise NB200Error(_err())
+
+    def feed_ptr(self, address: int, n_samples: int):
+        """Feed from a raw host address (e.g. a pinned torch tensor's data_ptr())."""
+        if lib().nb200_stream_feed(self._h, C.cast(C.c_void_p(address), _I16P), int(n_samples)) < 0:
+            raise NB200Error(_err())
+
+    def ready_chunks(self) -> int:
+        return lib().nb200_stream_ready_chunks(self._h)
 
     def set_taps(self, taps: int):
         lib().nb200_stream_set_taps(self._h, taps)

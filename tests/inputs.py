@@ -40,13 +40,14 @@ STREAM_CASES = (
 )
 
 
-def gguf_path(variant: str, layers: int = TEST_LAYERS) -> str:
+def gguf_path(variant: str, layers: int = TEST_LAYERS, blank_gain: float | None = None) -> str:
     import make_random_gguf as mg
     TMP.mkdir(parents=True, exist_ok=True)
-    p = TMP / f"L{layers}_{variant}_s{SEED}.gguf"
+    tag = "" if blank_gain is None else f"_bg{blank_gain:g}"
+    p = TMP / f"L{layers}_{variant}_s{SEED}{tag}.gguf"
     if not p.exists():
         tmp = p.with_suffix(f".tmp{os.getpid()}")
-        mg.write_gguf(str(tmp), SEED, layers, variant)
+        mg.write_gguf(str(tmp), SEED, layers, variant, blank_gain)
         os.replace(tmp, p)
     return str(p)
 

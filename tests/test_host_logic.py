@@ -1,0 +1,117 @@
+"""CPU-side checks: the C ABI library loads and exports every symbol include/nb200.h declares, fails loudly without a
+GPU, the latency-mode arithmetic, the GGUF writer/reader pair, and the stream->GPU sharding under a 2-rank gloo group."""
+import ctypes
+import os
+import re
+import socket
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import inputs
+import nemo_oracle as no
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def test_header_symbols_exported(lib_built):
+    nb200 = lib_built
+    header = (ROOT / "include" / "nb200.h").read_text()
+    declared = set(re.findall(r"\b(nb200_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 25
+    lib = ctypes.CDLL(str(nb200.LIB_PATH))
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} is declared in include/nb200.h but not exported by libnemob200.so"
+    assert declared == set(nb200.SYMBOLS), "nb200.py must bind exactly the header's entry points"
+    assert nb200.lib().nb200_version() >= 100
+
+
+def test_no_cpu_fallback(lib_built, gguf_q8):
+    """Without a CUDA device the product path must fail loudly (there is no CPU fallback of any kind)."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    nb200 = lib_built
+    with pytest.raises(nb200.NB200Error, match="no CUDA device"):
+        nb200.Model(gguf_q8)
+
+
+def test_product_does_not_import_oracle():
+    for p in (ROOT / "nemotron-asr.cpp_b200").rglob("*"):
+        if p.suffix in (".py", ".cu", ".cuh", ".cpp", ".h") and p.is_file():
+            txt = p.read_text(errors="ignore")
+            assert "nemo_oracle" not in txt and "oracle/" not in txt, f"{p} references the test oracle"
+
+
+def test_latency_modes():
+    """src/nemo-stream.h:65-100 (the table in SURVEY §8): chunk_mel, shift, subsampled lengths, chunk_len."""
+    table = {0: (17, 8, (9, 5, 3), 1), 1: (25, 16, (13, 7, 4), 2), 6: (65, 56, (33, 17, 9), 7), 13: (121, 112, (61, 31, 16), 14)}
+    for rc, (chunk_mel, shift, ts, T) in table.items():
+        s = no.StreamOracle({"nemo.n_layers": 0, "nemo.n_heads": 8, "nemo.d_head": 128, "nemo.d_model": 1024,
+                             "nemo.att_left_context": 70, "nemo.vocab_size": 1025},
+                            {"preprocessor.featurizer.fb": np.zeros((128, 257), np.float32),
+                             "preprocessor.featurizer.window": np.zeros(400, np.float32)}, rc)
+        assert (s.chunk_mel, s.shift, s.valid_out) == (chunk_mel, shift, T)
+        t1 = chunk_mel // 2 + 1
+        t2 = t1 // 2 + 1
+        t3 = t2 // 2 + 1
+        assert (t1, t2, t3) == ts and t3 - 2 == T
+
+
+def test_gguf_roundtrip(oracle_q8, oracle_f32):
+    """Writer (tools/make_random_gguf.py, the converter's format) -> oracle reader: Q8_0 blocks dequantise to exactly the
+    values the F32-of-dequantised file stores."""
+    kv, tq = oracle_q8
+    _, tf = oracle_f32
+    assert kv["nemo.n_layers"] == inputs.TEST_LAYERS and kv["nemo.vocab_size"] == 1025 and len(kv["tokenizer.vocab_list"]) == 1024
+    name = "encoder.layers.1.feed_forward2.linear1.weight"
+    assert isinstance(tq[name], no.Q8Weight) and tq[name].shape == (4096, 1024)
+    assert np.array_equal(tq[name].dequant(), tf[name])
+    assert tq["encoder.layers.0.conv.depthwise_conv.weight"].shape == (9, 1024)
+
+
+def test_shard_partition():
+    import shard
+    for world in (1, 2, 4, 8):
+        parts = [shard.shard_streams(1000, world, r) for r in range(world)]
+        assert sorted(sum(parts, [])) == list(range(1000))
+        assert max(map(len, parts)) - min(map(len, parts)) <= 1
+    with pytest.raises(ValueError):
+        shard.shard_streams(8, 2, 2)
+
+
+_WORKER = r"""
+import os, sys
+sys.path.insert(0, sys.argv[1])
+import torch.distributed as dist
+import shard
+dist.init_process_group("gloo")
+r, w = dist.get_rank(), dist.get_world_size()
+mine = shard.shard_streams(129, w, r)
+gathered = [None] * w
+dist.all_gather_object(gathered, mine)
+assert sorted(sum(gathered, [])) == list(range(129))
+ms, units = shard.reduce_timing(10.0 + 5.0 * r, float(len(mine)))
+assert ms == 10.0 + 5.0 * (w - 1) and units == 129.0, (ms, units)
+dist.barrier()
+dist.destroy_process_group()
+print("rank", r, "ok")
+"""
+
+
+def test_two_rank_gloo(tmp_path):
+    """The N>1 host path (sharding + max-over-ranks timing reduction) under torch.distributed/gloo, world_size 2."""
+    script = tmp_path / "worker.py"
+    script.write_text(_WORKER)
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", str(port), str(script), str(ROOT / "nemotron-asr.cpp_b200")],
+                       env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert r.stdout.count("ok") == 2

@@ -94,7 +94,7 @@ def mel_filterbank() -> np.ndarray:
     return fb.astype(np.float32)
 
 
-def tensor_list(seed: int, n_layers: int):
+def tensor_list(seed: int, n_layers: int, blank_gain: float | None = None):
     """Yields (name, float32 array in PyTorch shape order, quantisable?)."""
     s = seed
     yield "preprocessor.featurizer.fb", mel_filterbank()[None], False
@@ -150,14 +150,18 @@ def tensor_list(seed: int, n_layers: int):
     # largest non-blank logit does, so the per-step blank probability is about the same in every decoder state
     # (a plain blank bias gave either all-blank or runaway 10-symbol loops once the LSTM state left zero).
     wo = normal(s, "joint.joint_net.2.weight", (VOCAB, JOINT), 1.0 / JOINT ** 0.5)
-    wo[VOCAB - 1] = BLANK_GAIN / JOINT
+    wo[VOCAB - 1] = (BLANK_GAIN if blank_gain is None else blank_gain) / JOINT
     yield "joint.joint_net.2.weight", wo, False
     ob = normal(s, "joint.joint_net.2.bias", (VOCAB,), 0.1)
     ob[VOCAB - 1] = 0.0
     yield "joint.joint_net.2.bias", ob, False
 
 
-BLANK_GAIN = 5.9   # tuned against the reference: about 1.2-1.7 emitted tokens per encoder frame
+# The random decoder is bistable in this gain (the LSTM state feeds back into the joint): at 5.9 the reference emits
+# 3-5 tokens per encoder frame (heavy multi-symbol decode: what the parity fixtures use); from about 6.0 (24 layers)
+# it is blank-dominated, ~1.05 symbol steps per frame (real speech: ~1.3). The benchmark passes blank_gain=6.3 so that
+# none of its concurrent streams falls into the runaway regime, and reports the measured steps per frame.
+BLANK_GAIN = 5.9
 PRED_GAIN = 4.0
 LSTM_BIAS = 0.5
 
@@ -167,7 +171,7 @@ def _w_str(f, sbytes: bytes):
     f.write(sbytes)
 
 
-def write_gguf(path: str, seed: int = 1234, n_layers: int = 24, variant: str = "q8_0") -> dict:
+def write_gguf(path: str, seed: int = 1234, n_layers: int = 24, variant: str = "q8_0", blank_gain: float | None = None) -> dict:
     assert variant in ("q8_0", "f32", "f32dq")
     vocab = [("▁" if i % 3 == 0 else "") + f"t{i}" for i in range(VOCAB - 1)]
     hparams = [("nemo.n_mels", N_MELS), ("nemo.d_model", D_MODEL), ("nemo.n_heads", N_HEADS), ("nemo.d_head", D_HEAD),
@@ -176,7 +180,7 @@ def write_gguf(path: str, seed: int = 1234, n_layers: int = 24, variant: str = "
                ("nemo.att_left_context", LEFT), ("nemo.num_prompts", 0)]
     infos, off = [], 0
     blobs = []
-    for name, arr, quantisable in tensor_list(seed, n_layers):
+    for name, arr, quantisable in tensor_list(seed, n_layers, blank_gain):
         arr = np.ascontiguousarray(arr, dtype=np.float32)
         if quantisable and variant == "q8_0":
             data, typ = q8_0_bytes(arr), GGML_Q8_0
@@ -224,8 +228,9 @@ def main(argv=None):
     ap.add_argument("--seed", type=int, default=1234)
     ap.add_argument("--layers", type=int, default=24)
     ap.add_argument("--variant", default="q8_0", choices=("q8_0", "f32", "f32dq"))
+    ap.add_argument("--blank-gain", type=float, default=None)
     a = ap.parse_args(argv)
-    print(write_gguf(a.out, a.seed, a.layers, a.variant))
+    print(write_gguf(a.out, a.seed, a.layers, a.variant, a.blank_gain))
 
 
 if __name__ == "__main__":
