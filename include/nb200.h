@@ -32,6 +32,7 @@ typedef struct nb200_stream nb200_stream; /* replaces struct nemo_stream_context
 #define NB200_FLAG_ACT_QUANT_OFF 1  /* never (weights are still the dequantised Q8_0 values)                       */
 #define NB200_FLAG_ACT_QUANT_ON 2   /* always                                                                      */
 #define NB200_FLAG_GEMM_SIMT 16     /* debug: CUDA-core GEMM instead of the tcgen05 kernel (same operands/epilogues) */
+#define NB200_FLAG_NO_GRAPHS 32     /* debug: launch every kernel eagerly instead of replaying per-shape CUDA graphs */
 
 typedef struct nb200_info {
     int32_t n_mels, d_model, n_heads, d_head, d_ff, n_layers, kernel_size;

@@ -6,6 +6,8 @@
 // output of a step only changes after an emission: it is kept per stream as "pending" state and recomputed after
 // each emission, so a round costs one joint evaluation plus one batched LSTM update. Streams advance through their
 // frames independently (no lock-step over frames).
+#include <algorithm>
+
 #include "kernels.cuh"
 
 namespace nb {
@@ -59,11 +61,69 @@ __global__ void __launch_bounds__(256) sgemm_nt_kernel(const float* __restrict__
     }
 }
 
+// Skinny variant for the decode loop (M <= 64 rows, weights streamed from L2): 64 x 16 tiles so that N/16 CTAs
+// (160 for the LSTM gates, 68 for the joint output) spread over the SMs; each thread owns 4 rows x 1 column.
+// `gate`: when non-null and *gate == 0 the whole launch is a no-op (no stream emitted this round -> LSTM unchanged).
+__global__ void __launch_bounds__(256) sgemm_skinny_kernel(const float* __restrict__ A, const float* __restrict__ W,
+                                                           const float* __restrict__ bias, float* __restrict__ C, int M, int N,
+                                                           int K, int ldc, const int* __restrict__ out_rows,
+                                                           const int* __restrict__ gate) {
+    if (gate != nullptr && *gate == 0) return;
+    __shared__ float As[32][64 + 4];
+    __shared__ float Ws[32][16 + 1];
+    const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+    const int n0 = blockIdx.x * 16;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const int ar = t >> 2, ak = (t & 3) * 8;   // A tile 64 rows x 32 k: thread loads 8 consecutive k of one row
+    const int wr = t >> 4, wk = (t & 15) * 2;  // W tile 16 rows x 32 k: thread loads 2 consecutive k of one row
+    for (int k0 = 0; k0 < K; k0 += 32) {
+        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+        if (ar < M) {
+            const float4* src = reinterpret_cast<const float4*>(A + (size_t)ar * K + k0 + ak);
+            a0 = src[0];
+            a1 = src[1];
+        }
+        const float2 w = *reinterpret_cast<const float2*>(W + (size_t)(n0 + wr) * K + k0 + wk);
+        As[ak + 0][ar] = a0.x; As[ak + 1][ar] = a0.y; As[ak + 2][ar] = a0.z; As[ak + 3][ar] = a0.w;
+        As[ak + 4][ar] = a1.x; As[ak + 5][ar] = a1.y; As[ak + 6][ar] = a1.z; As[ak + 7][ar] = a1.w;
+        Ws[wk + 0][wr] = w.x;
+        Ws[wk + 1][wr] = w.y;
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 32; k++) {
+            const float4 av = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+            const float wv = Ws[k][tx];
+            acc[0] = fmaf(av.x, wv, acc[0]);
+            acc[1] = fmaf(av.y, wv, acc[1]);
+            acc[2] = fmaf(av.z, wv, acc[2]);
+            acc[3] = fmaf(av.w, wv, acc[3]);
+        }
+        __syncthreads();
+    }
+    const int n = n0 + tx;
+    const float bv = bias ? bias[n] : 0.0f;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const int m = ty * 4 + i;
+        if (m >= M) continue;
+        const int orow = out_rows ? out_rows[m] : m;
+        C[(size_t)orow * ldc + n] = acc[i] + bv;
+    }
+}
+
 void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* bias, float* C, int M, int N, int K,
-                  int ldc, const int* out_rows) {
+                  int ldc, const int* out_rows, const int* gate) {
     if (M <= 0) return;
-    if (N % 64 != 0 || K % 16 != 0) throw Error("sgemm: N must be a multiple of 64 and K of 16");
-    ProfScope ps(st, "sgemm_f32", 2.0 * M * (double)N * K, 4.0 * ((double)M * K + (double)N * K + (double)M * N));
+    if (N % 64 != 0 || K % 32 != 0) throw Error("sgemm: N must be a multiple of 64 and K of 32");
+    const double flops = 2.0 * M * (double)N * K, bytes = 4.0 * ((double)M * K + (double)N * K + (double)M * N);
+    if (M <= 64) {
+        ProfScope ps(st, "sgemm_f32_skinny", flops, bytes);
+        sgemm_skinny_kernel<<<N / 16, 256, 0, st>>>(A, W, bias, C, M, N, K, ldc, out_rows, gate);
+        NB_KERNEL_CHECK();
+        return;
+    }
+    if (gate) throw Error("sgemm: gated launches are only supported for M <= 64");
+    ProfScope ps(st, "sgemm_f32", flops, bytes);
     sgemm_nt_kernel<<<dim3(N / 64, cdiv(M, 64)), 256, 0, st>>>(A, W, bias, C, M, N, K, ldc, out_rows);
     NB_KERNEL_CHECK();
 }
@@ -72,6 +132,10 @@ void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* 
 // hid[b] = relu(e[b, fp[b]] + pend_p[slot[b]])   (src/nemo-ggml.cpp:1215-1217); zeros for finished streams
 __global__ void __launch_bounds__(160) hid_kernel(DecodeState s, DecodeBatch d) {
     const int b = blockIdx.x, i = threadIdx.x * 4;
+    if (b == 0 && threadIdx.x == 0) {  // first kernel of a round: reset the round's flags
+        *d.unfinished = 0;
+        *d.any_emit = 0;
+    }
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     const int fp = d.fp[b];
     if (fp < d.nvalid[b]) {
@@ -126,6 +190,7 @@ __global__ void __launch_bounds__(256) argmax_commit_kernel(DecodeWeights w, Dec
                 d.tok_cnt[b]++;
                 s.prev[slot] = besti;
                 s_emit = 1;
+                *d.any_emit = 1;  // benign race: every writer stores 1
                 sy++;
                 if (sy >= MAX_SYMBOLS) { f++; sy = 0; }
             }
@@ -160,7 +225,8 @@ __global__ void __launch_bounds__(256) stage_x0_kernel(DecodeWeights w, DecodeSt
 }
 
 // LSTM cell, gate order i,f,g,o (src/nemo-ggml.cpp:601-618). layer 0 also stages x[b] = [h0' | h1]; layer 1 stages hp.
-__global__ void __launch_bounds__(160) cell_kernel(DecodeState s, DecodeBatch d, int layer) {
+__global__ void __launch_bounds__(160) cell_kernel(DecodeState s, DecodeBatch d, int layer, const int* __restrict__ gate) {
+    if (gate != nullptr && *gate == 0) return;
     const int b = blockIdx.x, slot = d.slot[b];
     const float* g = d.gates + (size_t)b * 4 * DEC;
     const size_t so = (size_t)slot * 2 * DEC + (size_t)layer * DEC;
@@ -179,30 +245,43 @@ __global__ void __launch_bounds__(160) cell_kernel(DecodeState s, DecodeBatch d,
     }
 }
 
-static void lstm_update(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d) {
-    launch_sgemm(st, d.x, w.wcat[0], w.bcat[0], d.gates, d.B, 4 * DEC, 2 * DEC, 4 * DEC, nullptr);
-    cell_kernel<<<d.B, 160, 0, st>>>(s, d, 0);
-    NB_KERNEL_CHECK();
-    launch_sgemm(st, d.x, w.wcat[1], w.bcat[1], d.gates, d.B, 4 * DEC, 2 * DEC, 4 * DEC, nullptr);
-    cell_kernel<<<d.B, 160, 0, st>>>(s, d, 1);
-    NB_KERNEL_CHECK();
-    launch_sgemm(st, d.hp, w.wpred, w.bpred, s.pend_p, d.B, JOINT, DEC, JOINT, d.slot);
+// Recomputes the pending LSTM / joint.pred state of every stream of the batch from its committed state. In the
+// greedy loop it is gated on the round's any_emit flag: a blank leaves (prev, h, c) untouched (src/nemo-stream.cpp:
+// 907-911), so when no stream emitted the pending state is still valid and the five launches are no-ops.
+static void lstm_update(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d, const int* gate) {
+    for (int b0 = 0; b0 < d.B; b0 += 64) {  // the skinny GEMM takes up to 64 rows
+        const int nb = std::min(64, d.B - b0);
+        DecodeBatch e = d;
+        e.slot = d.slot + b0;
+        float* x = d.x + (size_t)b0 * 2 * DEC;
+        float* gates = d.gates + (size_t)b0 * 4 * DEC;
+        float* hp = d.hp + (size_t)b0 * DEC;
+        e.x = x; e.gates = gates; e.hp = hp;
+        launch_sgemm(st, x, w.wcat[0], w.bcat[0], gates, nb, 4 * DEC, 2 * DEC, 4 * DEC, nullptr, gate);
+        cell_kernel<<<nb, 160, 0, st>>>(s, e, 0, gate);
+        NB_KERNEL_CHECK();
+        launch_sgemm(st, x, w.wcat[1], w.bcat[1], gates, nb, 4 * DEC, 2 * DEC, 4 * DEC, nullptr, gate);
+        cell_kernel<<<nb, 160, 0, st>>>(s, e, 1, gate);
+        NB_KERNEL_CHECK();
+        launch_sgemm(st, hp, w.wpred, w.bpred, s.pend_p, nb, JOINT, DEC, JOINT, e.slot, gate);
+    }
 }
 
 void launch_decode_round(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d) {
-    CUDA_CHECK(cudaMemsetAsync(d.unfinished, 0, sizeof(int), st));
     hid_kernel<<<d.B, 160, 0, st>>>(s, d);
     NB_KERNEL_CHECK();
-    launch_sgemm(st, d.hid, w.wout, w.bout, d.logits, d.B, VOCAB_PAD, JOINT, VOCAB_PAD, nullptr);
+    for (int b0 = 0; b0 < d.B; b0 += 64)
+        launch_sgemm(st, d.hid + (size_t)b0 * JOINT, w.wout, w.bout, d.logits + (size_t)b0 * VOCAB_PAD, std::min(64, d.B - b0), VOCAB_PAD,
+                     JOINT, VOCAB_PAD, nullptr, nullptr);
     argmax_commit_kernel<<<d.B, 256, 0, st>>>(w, s, d);
     NB_KERNEL_CHECK();
-    lstm_update(st, w, s, d);
+    lstm_update(st, w, s, d, d.any_emit);
 }
 
 void launch_decode_refresh(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d) {
     stage_x0_kernel<<<d.B, 256, 0, st>>>(w, s, d);
     NB_KERNEL_CHECK();
-    lstm_update(st, w, s, d);
+    lstm_update(st, w, s, d, nullptr);
 }
 
 }  // namespace nb

@@ -87,7 +87,7 @@ namespace nb {
 // C[M,N] = A[M,K] * W[N,K]^T + bias, fp32 on CUDA cores (the reference keeps LSTM/joint weights and math in fp32,
 // src/nemo-ggml.cpp:580-619,1186-1224). N % 64 == 0, K % 16 == 0. Row m of C is stored at row out_rows[m] if given.
 void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* bias, float* C, int M, int N, int K,
-                  int ldc, const int* out_rows);
+                  int ldc, const int* out_rows, const int* gate = nullptr);
 
 struct DecodeState {           // per stream slot, persistent in HBM
     float* h;                  // [slots][2][640] committed LSTM hidden state
@@ -106,6 +106,7 @@ struct DecodeBatch {           // per batched step
     int* tok_out;              // [B][T*MAX_SYMBOLS]
     int* tok_cnt;              // [B]
     int* unfinished;           // [1] streams with fp < nvalid after the last round
+    int* any_emit;             // [1] set when any stream emitted a token in the current round (gates the LSTM update)
     float* min_margin;         // [B] smallest top1-top2 logit gap over this chunk's symbol steps (near-tie tracing)
     float* hid;                // [B][640]
     float* logits;             // [B][1088]
