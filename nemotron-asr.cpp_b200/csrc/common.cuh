@@ -94,6 +94,16 @@ __device__ __forceinline__ float warp_max(float v) {
 }
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + expf(-x)); }
+// GEMM-epilogue versions (ex2.approx + approximate division, ~1e-6 relative): the results are rounded to fp16 (or
+// feed the int8-grid re-quantisation) right after, so the extra ulps are invisible, and the IEEE versions cost
+// ~60 instructions per element on the 4-8 epilogue warps of a tile.
+__device__ __forceinline__ float silu_fast(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+// Scale pair of ggml-CPU's Q8_0 quantiser for a 32-block with the given amax: d = fp16(amax/127), id = 127/amax
+__device__ __forceinline__ void fq_scales(float amax, float& d, float& id) {
+    d = amax == 0.0f ? 0.0f : __half2float(__float2half_rn(__fdiv_rn(amax, 127.0f)));
+    id = amax == 0.0f ? 0.0f : __fdiv_rn(127.0f, amax);
+}
 
 // ggml-CPU's Q8_0 activation quantiser applied to a value given its block's amax, returned dequantised:
 // d = fp16(amax/127), q = rne(x * (127/amax))  (ggml/src/ggml-cpu/arch/x86/quants.c:331-346), value = q*d.

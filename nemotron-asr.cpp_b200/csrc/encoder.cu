@@ -57,24 +57,34 @@ __device__ __forceinline__ float4 ln_1024(float4 v, const float* g, const float*
     return v;
 }
 
-__global__ void __launch_bounds__(256) layernorm_kernel(const float* __restrict__ x, const float* __restrict__ g1,
+__global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, const float* __restrict__ g1,
                                                         const float* __restrict__ b1, float* __restrict__ out_f32,
                                                         const float* __restrict__ g2, const float* __restrict__ b2,
-                                                        __half* __restrict__ out_f16, int act_quant) {
+                                                        __half* __restrict__ out_f16, int act_quant, ResidualIn rin) {
     __shared__ float red[8];
     const size_t off = (size_t)blockIdx.x * D_MODEL + threadIdx.x * 4;
     float4 v = *reinterpret_cast<const float4*>(x + off);
+    if (rin.partials != nullptr) {  // x += alpha * (sum of the preceding GEMM's split-K partials), in split order
+        float4 acc = *reinterpret_cast<const float4*>(rin.partials + off);
+        for (int s = 1; s < rin.nsplit; s++) {
+            const float4 p = *reinterpret_cast<const float4*>(rin.partials + (size_t)s * rin.stride + off);
+            acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+        }
+        v.x += rin.alpha * acc.x; v.y += rin.alpha * acc.y; v.z += rin.alpha * acc.z; v.w += rin.alpha * acc.w;
+        if (out_f32 != x) *reinterpret_cast<float4*>(x + off) = v;  // the residual stream (unless the LN output replaces it)
+    }
     v = ln_1024(v, g1, b1, red);
     if (out_f32) *reinterpret_cast<float4*>(out_f32 + off) = v;
     if (g2) v = ln_1024(v, g2, b2, red);
     if (out_f16) store_f16x4(out_f16 + off, v, act_quant);
 }
 
-void launch_layernorm(cudaStream_t st, const float* x, const float* g1, const float* b1, float* out_f32, const float* g2,
-                      const float* b2, __half* out_f16, int act_quant, int M) {
+void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b1, float* out_f32, const float* g2,
+                      const float* b2, __half* out_f16, int act_quant, int M, const ResidualIn& rin) {
     if (M <= 0) return;
-    ProfScope ps(st, "layernorm", (double)M * D_MODEL * 8, (double)M * D_MODEL * (4 + (out_f32 ? 4 : 0) + (out_f16 ? 2 : 0)));
-    layernorm_kernel<<<M, 256, 0, st>>>(x, g1, b1, out_f32, g2, b2, out_f16, act_quant);
+    ProfScope ps(st, "layernorm", (double)M * D_MODEL * 8,
+                 (double)M * D_MODEL * (4 + (out_f32 ? 4 : 0) + (out_f16 ? 2 : 0) + (rin.partials ? 4.0 * rin.nsplit + (out_f32 != x ? 4 : 0) : 0)));
+    layernorm_kernel<<<M, 256, 0, st>>>(x, g1, b1, out_f32, g2, b2, out_f16, act_quant, rin);
     NB_KERNEL_CHECK();
 }
 

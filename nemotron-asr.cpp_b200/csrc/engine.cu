@@ -130,6 +130,9 @@ struct nb200_model {
     float *ws_mel = nullptr, *ws_a3 = nullptr, *ws_x = nullptr, *ws_q = nullptr, *ws_g = nullptr, *ws_e = nullptr;
     __half *ws_a2h = nullptr, *ws_a5h = nullptr, *ws_a6h = nullptr, *ws_a16 = nullptr, *ws_h16 = nullptr, *ws_pos16 = nullptr;
     float* ws_posf = nullptr;
+    float* ws_part = nullptr;      // split-K partial outputs of the residual GEMMs: [splits][part_rows][1024]
+    size_t part_rows = 0;
+    int part_max_splits = 1;
     Operand op_a2h, op_a5h, op_a6h, op_a16, op_h16, op_pos16;
     int16_t* pcm_ring = nullptr;   // [slots][ring_cap] device-resident audio (nb200_stream_feed uploads into it)
     int ring_cap = 0;              // samples per slot, power of two
@@ -411,6 +414,9 @@ void alloc_state(nb200_model* m) {
     m->ws_a16 = m->alloc<__half>(rows_pad * D_MODEL);
     m->ws_h16 = m->alloc<__half>(rows_pad * D_FF);
     m->ws_posf = m->alloc<float>((size_t)128 * D_MODEL);
+    m->part_rows = rows_pad;
+    m->part_max_splits = rows_pad <= 4096 ? 8 : (rows_pad <= 8192 ? 4 : (rows_pad <= 16384 ? 2 : 1));
+    m->ws_part = m->alloc<float>((size_t)m->part_max_splits * rows_pad * D_MODEL);
     m->ws_pos16 = m->alloc<__half>((size_t)128 * D_MODEL);
     operand_init(m->op_a2h, m->ws_a2h, B * big.t2 * SUB_F2, SUB_CH);
     operand_init(m->op_a5h, m->ws_a5h, (int)rows * SUB_F3, SUB_CH);
@@ -639,14 +645,16 @@ void enqueue_encoder(const StepCtx& c) {
         LayerW& L = m->layers[l];
         EpiParams up;  // linear1 + SiLU (+ re-quantise) -> fp16 [M,4096]
         up.kind = EPI_STORE_F16; up.act = ACT_SILU; up.act_quant = aq; up.out_f16 = m->ws_h16; up.ldo = D_FF;
-        EpiParams half;  // x += 0.5 * linear2(...)
-        half.kind = EPI_RESID; half.alpha = 0.5f; half.out_f32 = m->ws_x; half.ldo = D_MODEL;
-        EpiParams res = half;  // x += ...
-        res.alpha = 1.0f;
+        // The four residual GEMMs (N = 1024) write split-K partials; the LayerNorm that follows adds them to x.
+        EpiParams part;
+        part.kind = EPI_PARTIAL; part.out_f32 = m->ws_part; part.ldo = D_MODEL; part.split_stride = m->part_rows * D_MODEL;
+        ResidualIn rin;
+        rin.partials = m->ws_part; rin.stride = part.split_stride;
         gemm(st, m->op_a16, L.ff1_w1.op, M, up, simt);
-        gemm(st, m->op_h16, L.ff1_w2.op, M, half, simt);
+        rin.nsplit = gemm(st, m->op_h16, L.ff1_w2.op, M, part, simt, m->part_max_splits);
+        rin.alpha = 0.5f;  // x += 0.5 * FFN1
         // self-attention
-        launch_layernorm(st, m->ws_x, L.ln_att_g, L.ln_att_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M);
+        launch_layernorm(st, m->ws_x, L.ln_att_g, L.ln_att_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin);
         float* kr = m->k_ring + (size_t)l * S * RING * D_MODEL;
         float* vr = m->v_ring + (size_t)l * S * RING * D_MODEL;
         EpiParams qkv;
@@ -657,9 +665,10 @@ void enqueue_encoder(const StepCtx& c) {
         at.bias_u = L.pos_u; at.bias_v = L.pos_v; at.slot = d_slot; at.wpos = d_wpos; at.valid = d_valid;
         at.out = m->ws_a16; at.B = B; at.T = T; at.act_quant = aq;
         launch_attention(st, at);
-        gemm(st, m->op_a16, L.wout.op, M, res, simt);
+        rin.nsplit = gemm(st, m->op_a16, L.wout.op, M, part, simt, m->part_max_splits);
+        rin.alpha = 1.0f;  // x += attention
         // convolution module
-        launch_layernorm(st, m->ws_x, L.ln_conv_g, L.ln_conv_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M);
+        launch_layernorm(st, m->ws_x, L.ln_conv_g, L.ln_conv_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin);
         EpiParams glu;
         glu.kind = EPI_GLU; glu.out_f32 = m->ws_g; glu.ldo = D_MODEL;
         gemm(st, m->op_a16, L.pw1.op, M, glu, simt);
@@ -668,15 +677,16 @@ void enqueue_encoder(const StepCtx& c) {
         cv.ln_g = L.bn_g; cv.ln_b = L.bn_b; cv.slot = d_slot; cv.out = m->ws_a16; cv.B = B; cv.T = T; cv.act_quant = aq;
         launch_dwconv(st, cv);
         launch_conv_cache_update(st, cv);
-        gemm(st, m->op_a16, L.pw2.op, M, res, simt);
+        rin.nsplit = gemm(st, m->op_a16, L.pw2.op, M, part, simt, m->part_max_splits);
         // FFN2 and the layer's output norm (fused with the next layer's first norm)
-        launch_layernorm(st, m->ws_x, L.ln_ff2_g, L.ln_ff2_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M);
+        launch_layernorm(st, m->ws_x, L.ln_ff2_g, L.ln_ff2_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin);  // x += conv module
         gemm(st, m->op_a16, L.ff2_w1.op, M, up, simt);
-        gemm(st, m->op_h16, L.ff2_w2.op, M, half, simt);
+        rin.nsplit = gemm(st, m->op_h16, L.ff2_w2.op, M, part, simt, m->part_max_splits);
+        rin.alpha = 0.5f;  // x += 0.5 * FFN2, then x = LN_out(x)
         if (l + 1 < m->n_layers)
-            launch_layernorm(st, m->ws_x, L.ln_out_g, L.ln_out_b, m->ws_x, m->layers[l + 1].ln_ff1_g, m->layers[l + 1].ln_ff1_b, m->ws_a16, aq, M);
+            launch_layernorm(st, m->ws_x, L.ln_out_g, L.ln_out_b, m->ws_x, m->layers[l + 1].ln_ff1_g, m->layers[l + 1].ln_ff1_b, m->ws_a16, aq, M, rin);
         else
-            launch_layernorm(st, m->ws_x, L.ln_out_g, L.ln_out_b, m->ws_x, nullptr, nullptr, nullptr, 0, M);
+            launch_layernorm(st, m->ws_x, L.ln_out_g, L.ln_out_b, m->ws_x, nullptr, nullptr, nullptr, 0, M, rin);
     }
     if (c.taps) {
         for (int b = 0; b < B; b++) {
@@ -1179,6 +1189,55 @@ int nb200_profile_report(nb200_model* m, char* json_out, int cap) {
     if ((int)r.size() + 1 > cap) throw Error("profile report buffer too small");
     memcpy(json_out, r.c_str(), r.size() + 1);
     return (int)r.size();
+    NB_CATCH(NB200_ERR)
+}
+
+int nb200_bench_gemm(nb200_model* m, int M, int N, int K, int epi_kind, int bn, int splits, int iters, double* us_per_launch,
+                     int* bn_used, int* splits_used) {
+    NB_TRY
+    if (!m || M <= 0 || N % 64 || K % 64 || iters <= 0 || !us_per_launch) throw Error("bad argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    const int Mp = (M + 127) / 128 * 128;
+    const int n_w = std::max(2, (int)(((size_t)300 << 20) / ((size_t)N * K * 2)));  // cycle > 2x L2 worth of weights
+    __half* a = dalloc<__half>((size_t)Mp * K);
+    __half* w = dalloc<__half>((size_t)n_w * N * K);
+    float* o32 = dalloc<float>((size_t)8 * Mp * N);
+    __half* o16 = dalloc<__half>((size_t)Mp * N);
+    {
+        std::vector<__half> h((size_t)Mp * K);
+        for (size_t i = 0; i < h.size(); i++) h[i] = __float2half_rn((float)((int)((i * 2654435761u) >> 20 & 255) - 128) / 64.0f);
+        CUDA_CHECK(cudaMemcpy(a, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
+        std::vector<__half> hw((size_t)N * K);
+        for (size_t i = 0; i < hw.size(); i++) hw[i] = __float2half_rn((float)((int)((i * 40503u) >> 9 & 255) - 128) / 2048.0f);
+        for (int j = 0; j < n_w; j++) CUDA_CHECK(cudaMemcpy(w + (size_t)j * N * K, hw.data(), hw.size() * 2, cudaMemcpyHostToDevice));
+    }
+    Operand A;
+    operand_init(A, a, Mp, K);
+    std::vector<Operand> W(n_w);
+    for (int j = 0; j < n_w; j++) operand_init(W[j], w + (size_t)j * N * K, N, K);
+    EpiParams ep;
+    ep.kind = epi_kind;
+    ep.ldo = N;
+    ep.out_f32 = o32;
+    ep.out_f16 = o16;
+    ep.split_stride = (size_t)Mp * N;
+    if (epi_kind == EPI_STORE_F16) { ep.act = ACT_SILU; ep.act_quant = 1; }
+    if (epi_kind == EPI_GLU) ep.ldo = N / 2;
+    gemm_force_config(bn, splits);
+    const GemmConfig c = gemm_pick_config(M, N, K, epi_kind == EPI_PARTIAL ? 8 : 1);
+    if (bn_used) *bn_used = c.bn;
+    if (splits_used) *splits_used = c.splits;
+    for (int i = 0; i < 3; i++) gemm(m->st, A, W[i % n_w], M, ep, false, 8);
+    CUDA_CHECK(cudaEventRecord(m->tev[0], m->st));
+    for (int i = 0; i < iters; i++) gemm(m->st, A, W[i % n_w], M, ep, false, 8);
+    CUDA_CHECK(cudaEventRecord(m->tev[1], m->st));
+    CUDA_CHECK(cudaEventSynchronize(m->tev[1]));
+    gemm_force_config(0, 1);
+    float ms = 0;
+    CUDA_CHECK(cudaEventElapsedTime(&ms, m->tev[0], m->tev[1]));
+    *us_per_launch = ms * 1e3 / iters;
+    cudaFree(a); cudaFree(w); cudaFree(o32); cudaFree(o16);
+    return NB200_OK;
     NB_CATCH(NB200_ERR)
 }
 

@@ -3,6 +3,8 @@
 
 #include <cudaTypedefs.h>
 
+#include <algorithm>
+
 namespace nb {
 
 long long g_launches = 0;
@@ -93,7 +95,7 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
 // ------------------------------------------------------------------------------------------------
 // tcgen05 kernel: one 128 x BN output tile per CTA
 // ------------------------------------------------------------------------------------------------
-constexpr int TC_BM = 128, TC_BK = 64, TC_THREADS = 192;
+constexpr int TC_BM = 128, TC_BK = 64, TC_THREADS = 320;  // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
 
 template <int BN, int STAGES>
 struct TcSmem {
@@ -105,7 +107,7 @@ struct TcSmem {
 
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
-                                                            const __grid_constant__ CUtensorMap map_w, int M, int K,
+                                                            const __grid_constant__ CUtensorMap map_w, int M, int num_k,
                                                             EpiParams epi) {
     using S = TcSmem<BN, STAGES>;
     extern __shared__ uint8_t smem_raw[];
@@ -121,7 +123,8 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_tile = blockIdx.x, m_tile = blockIdx.y;
-    const int num_k = K / TC_BK;
+    const int kb0 = blockIdx.z * num_k;  // split-K: this CTA sums k-blocks [kb0, kb0 + num_k)
+    if (epi.kind == EPI_PARTIAL) epi.out_f32 += (size_t)blockIdx.z * epi.split_stride;
     constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
 
     if (warp == 0 && lane == 0) {
@@ -148,8 +151,8 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
                 mbar_wait(empty_bar(s), ph ^ 1);
                 mbar_expect_tx(full_bar(s), S::STAGE_BYTES);
                 const uint32_t a_dst = base + s * S::STAGE_BYTES;
-                tma_load_2d(a_dst, &map_a, full_bar(s), kb * TC_BK, m_tile * TC_BM);
-                tma_load_2d(a_dst + S::A_BYTES, &map_w, full_bar(s), kb * TC_BK, n_tile * BN);
+                tma_load_2d(a_dst, &map_a, full_bar(s), (kb0 + kb) * TC_BK, m_tile * TC_BM);
+                tma_load_2d(a_dst + S::A_BYTES, &map_w, full_bar(s), (kb0 + kb) * TC_BK, n_tile * BN);
             }
         }
     } else if (warp == 1) {
@@ -172,16 +175,56 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
             }
             umma_commit(accum_bar);  // accumulator complete
         }
-    } else {  // ===== epilogue warps 2..5: TMEM lanes 32*(warp%4) .. +31 =====
-        const int lane_base = (warp & 3) * 32;
+    } else {
+        // ===== epilogue warps 2..9: warp w reads TMEM lanes 32*(w%4) .. +31 (the hardware's lane-quadrant rule) and
+        // the 32-column chunks with index = (w-2)/4 (mod 2). Each chunk: tcgen05.ld (thread = row) -> transform in
+        // registers -> staged through shared memory -> written out row-contiguously (128 or 64 B per row per store
+        // instruction instead of 32 rows x 16 B). The staging area is the operand ring: once accum_bar has fired
+        // every stage has been consumed and the producer is done, so the memory is free.
+        const int ew = warp - 2, quad = warp & 3, half = ew >> 2;
+        const int lane_base = quad * 32;
+        uint32_t* stg = reinterpret_cast<uint32_t*>(smem) + ew * (32 * 36);
         mbar_wait(accum_bar, 0);
         tc_fence_after();
         const int m = m_tile * TC_BM + lane_base + lane;
+        const bool row_ok = m < M;
 #pragma unroll 1
-        for (int c = 0; c < BN; c += 32) {
+        for (int c = half * 32; c < BN; c += 64) {
             float acc[32];
             tmem_ld32(tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)c, acc);  // warp-collective
-            if (m < M) epilogue_apply(epi, m, n_tile * BN + c, acc);
+            uint32_t w[32];
+            char* dst = nullptr;
+            const int nw = (epi.kind == EPI_STORE_F16 || epi.kind == EPI_GLU) ? 16 : 32;  // output words per row and chunk
+            if (row_ok) epilogue_transform(epi, m, n_tile * BN + c, acc, w, dst);
+            const int ld = nw == 32 ? 36 : 20;  // staging row stride in words (16-byte aligned, conflict-free float4 columns)
+            __syncwarp();
+            if (row_ok) {
+#pragma unroll
+                for (int j = 0; j < 8; j++)
+                    if (4 * j < nw) *reinterpret_cast<uint4*>(stg + lane * ld + 4 * j) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+            }
+            __syncwarp();
+            const int lpr = nw >> 2;        // lanes per row (16 B each): 8 or 4
+            const int rpp = 32 / lpr;       // rows per pass: 4 or 8
+            const unsigned long long dst_bits = reinterpret_cast<unsigned long long>(dst);
+            const unsigned ok_mask = __ballot_sync(0xffffffffu, row_ok);
+#pragma unroll 1
+            for (int r0 = 0; r0 < 32; r0 += rpp) {
+                const int rr = r0 + lane / lpr, col = (lane % lpr) * 4;
+                const unsigned long long rb = __shfl_sync(0xffffffffu, dst_bits, rr);
+                if ((ok_mask >> rr) & 1u) {
+                    uint4 v = *reinterpret_cast<const uint4*>(stg + rr * ld + col);
+                    uint4* gp = reinterpret_cast<uint4*>(reinterpret_cast<char*>(rb) + col * 4);
+                    if (epi.kind == EPI_RESID) {
+                        const float4 x = *reinterpret_cast<const float4*>(gp);
+                        v.x = __float_as_uint(x.x + epi.alpha * __uint_as_float(v.x));
+                        v.y = __float_as_uint(x.y + epi.alpha * __uint_as_float(v.y));
+                        v.z = __float_as_uint(x.z + epi.alpha * __uint_as_float(v.z));
+                        v.w = __float_as_uint(x.w + epi.alpha * __uint_as_float(v.w));
+                    }
+                    *gp = v;
+                }
+            }
         }
     }
     tc_fence_before();
@@ -283,47 +326,94 @@ void operand_init(Operand& op, const __half* ptr, int rows, int K) {
     op.ptr = ptr;
     op.rows = rows;
     op.K = K;
+    make_map(&op.map256, ptr, rows, K, 256);
     make_map(&op.map128, ptr, rows, K, 128);
     make_map(&op.map64, ptr, rows, K, 64);
+    make_map(&op.map32, ptr, rows, K, 32);
 }
 
 template <int BN, int STAGES>
-static void launch_tc(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiParams& epi) {
+static void launch_tc(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiParams& epi, int splits) {
     using S = TcSmem<BN, STAGES>;
     static bool configured = false;
     if (!configured) {
         CUDA_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
         configured = true;
     }
-    dim3 grid(W.rows / BN, cdiv(M, TC_BM));
-    gemm_tc_kernel<BN, STAGES><<<grid, TC_THREADS, S::TOTAL, st>>>(A.map128, BN == 128 ? W.map128 : W.map64, M, A.K, epi);
+    dim3 grid(W.rows / BN, cdiv(M, TC_BM), splits);
+    const CUtensorMap& wmap = BN == 256 ? W.map256 : (BN == 128 ? W.map128 : (BN == 64 ? W.map64 : W.map32));
+    gemm_tc_kernel<BN, STAGES><<<grid, TC_THREADS, S::TOTAL, st>>>(A.map128, wmap, M, A.K / TC_BK / splits, epi);
     NB_KERNEL_CHECK();
 }
 
-void gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiParams& epi, bool use_simt) {
-    if (M <= 0) return;
+// ---- tile / split selection ------------------------------------------------------------------------------
+// One 128 x BN tile (x K/splits) per CTA, one wave wherever possible. Cost model in SM clocks per CTA:
+//   k-block time = max(MMA issue 2*BN clk, operand load (128+BN)*128 B at the L2->SM bandwidth shared by the active CTAs)
+//   + a fixed prologue/epilogue cost, times the number of waves; split-K pays for writing and re-reading its partials.
+static int g_force_bn = 0, g_force_splits = 1;
+void gemm_force_config(int bn, int splits) {
+    g_force_bn = bn;
+    g_force_splits = splits < 1 ? 1 : splits;
+}
+
+GemmConfig gemm_pick_config(int M, int N, int K, int max_splits) {
+    const int m_tiles = cdiv(M, TC_BM), kb = K / TC_BK, SMS = 148;
+    if (g_force_bn) {
+        int sp = std::min(g_force_splits, max_splits);
+        while (sp > 1 && kb % sp) sp--;
+        return {g_force_bn, sp, (N / g_force_bn) * m_tiles * sp};
+    }
+    GemmConfig best{64, 1, (N / 64) * m_tiles};
+    double best_cost = 1e30;
+    const int bns[4] = {256, 128, 64, 32};
+    for (int bn : bns) {
+        if (N % bn) continue;
+        for (int sp = 1; sp <= max_splits; sp *= 2) {
+            if (kb % sp) break;
+            const int ctas = (N / bn) * m_tiles * sp;
+            const int waves = cdiv(ctas, SMS);
+            const double active = std::min(ctas, SMS);
+            const double bw = std::min(96.0, 7000.0 / active);               // bytes / clk / SM from L2
+            const double kblock = std::max(2.0 * bn, (128.0 + bn) * 128.0 / bw);
+            const double epilogue = 1500.0 + 12.0 * bn;                        // TMEM drain + global stores of 128 x bn
+            double cost = waves * ((double)(kb / sp) * kblock + 2500.0 + epilogue);
+            if (sp > 1) cost += (double)sp * M * N * 8.0 / 5000.0;           // partials written, then re-read by the LayerNorm
+            if (cost < best_cost) {
+                best_cost = cost;
+                best = {bn, sp, ctas};
+            }
+        }
+    }
+    return best;
+}
+
+int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiParams& epi, bool use_simt, int max_splits) {
+    if (M <= 0) return 1;
     if (A.K != W.K) throw Error("GEMM: K mismatch");
     if (M > A.rows) throw Error("GEMM: M exceeds the activation buffer");
     const int N = W.rows;
     if (N % 64 != 0) throw Error("GEMM: N must be a multiple of 64");
+    if (epi.kind != EPI_PARTIAL) max_splits = 1;
     const double flops = 2.0 * M * (double)N * A.K;
     const double out_b = epi.kind == EPI_RESID ? 8.0 : (epi.kind == EPI_STORE_F16 ? 2.0 : (epi.kind == EPI_GLU ? 2.0 : 4.0));
     const double bytes = 2.0 * ((double)M * A.K + (double)N * A.K) + out_b * M * (double)N;
-    const int m_tiles = cdiv(M, TC_BM);
-    const bool wide = N % 128 == 0 && (N / 128) * m_tiles >= 148;
-    ProfScope ps(st, use_simt ? "gemm_simt" : (wide ? "gemm_tc_128x128" : "gemm_tc_128x64"), flops, bytes);
     if (use_simt) {
+        ProfScope ps(st, "gemm_simt", flops, bytes);
         dim3 grid(N / 64, cdiv(M, 64));
         gemm_simt_kernel<<<grid, 128, 0, st>>>(A.ptr, W.ptr, M, N, A.K, epi);
         NB_KERNEL_CHECK();
-        return;
+        return 1;
     }
-    // Tile width: 128 when that already gives >= 1 wave of CTAs (or N is not a multiple of 128), else 64.
-    if (wide) {
-        launch_tc<128, 3>(st, A, W, M, epi);
-    } else {
-        launch_tc<64, 4>(st, A, W, M, epi);
+    const GemmConfig c = gemm_pick_config(M, N, A.K, max_splits);
+    static const char* names[4] = {"gemm_tc_128x256", "gemm_tc_128x128", "gemm_tc_128x64", "gemm_tc_128x32"};
+    ProfScope ps(st, names[c.bn == 256 ? 0 : (c.bn == 128 ? 1 : (c.bn == 64 ? 2 : 3))], flops, bytes + (c.splits > 1 ? 4.0 * (c.splits - 1) * M * (double)N : 0.0));
+    switch (c.bn) {
+        case 256: launch_tc<256, 4>(st, A, W, M, epi, c.splits); break;
+        case 128: launch_tc<128, 6>(st, A, W, M, epi, c.splits); break;
+        case 64: launch_tc<64, 8>(st, A, W, M, epi, c.splits); break;
+        default: launch_tc<32, 8>(st, A, W, M, epi, c.splits); break;
     }
+    return c.splits;
 }
 
 }  // namespace nb

@@ -12,6 +12,10 @@
 //   EPI_RESID      x += alpha * acc                               (FFN linear2 *0.5, attention out, pointwise_conv2)
 //   EPI_QKV        q -> fp32 buffer, k/v -> the streams' K/V ring caches
 //   EPI_GLU        out_f32[j] = a_j * sigmoid(b_j) with (a_j,b_j) interleaved as columns (2j,2j+1) at load
+//   EPI_PARTIAL    split-K: CTA z of gridDim.z sums its K range and stores the raw partial tile to
+//                  out_f32 + z*split_stride; the LayerNorm that follows every residual GEMM adds alpha * sum_z partial_z
+//                  to x in a fixed order (deterministic, unlike atomics). Used for the N=1024 GEMMs, which would
+//                  otherwise run on 28-112 CTAs with tiles too small for the L2 -> SM bandwidth.
 // fq = ggml-CPU's Q8_0 activation re-quantisation emulated per 32 consecutive features (common.cuh fake_quant).
 #pragma once
 #include <cuda.h>
@@ -20,7 +24,7 @@
 
 namespace nb {
 
-enum EpiKind : int { EPI_STORE = 0, EPI_STORE_F16 = 1, EPI_RESID = 2, EPI_QKV = 3, EPI_GLU = 4 };
+enum EpiKind : int { EPI_STORE = 0, EPI_STORE_F16 = 1, EPI_RESID = 2, EPI_QKV = 3, EPI_GLU = 4, EPI_PARTIAL = 5 };
 enum ActKind : int { ACT_NONE = 0, ACT_RELU = 1, ACT_SILU = 2 };
 
 struct EpiParams {
@@ -38,98 +42,109 @@ struct EpiParams {
     const int* slot = nullptr;  // [B]
     const int* wpos = nullptr;  // [B] ring index where frame 0 of this chunk goes
     int T = 1;
+    size_t split_stride = 0;    // EPI_PARTIAL: elements between the partial outputs of consecutive K splits
 };
 
-// Applies the epilogue to 32 consecutive accumulator columns [n0, n0+32) of row m.
-__device__ __forceinline__ void epilogue_apply(const EpiParams& p, int m, int n0, float (&acc)[32]) {
-    if (p.kind == EPI_RESID) {
-        float4* dst = reinterpret_cast<float4*>(p.out_f32 + (size_t)m * p.ldo + n0);
+// ---- epilogue, stage 1 (registers): bias / activation / re-quantisation / GLU on 32 consecutive accumulator columns
+// [n0, n0+32) of row m. Leaves the row's output words in w[] and returns how many there are: 32 (fp32 outputs) or 16
+// (32 fp16 values, or 16 GLU outputs). `dst` receives the address of the row's first output byte of this chunk.
+__device__ __forceinline__ int epilogue_transform(const EpiParams& p, int m, int n0, float (&acc)[32], uint32_t (&w)[32], char*& dst) {
+    if (p.kind != EPI_RESID && p.kind != EPI_PARTIAL) {
+        if (p.bias != nullptr) {
 #pragma unroll
-        for (int j = 0; j < 8; j++) {
-            float4 v = dst[j];
-            v.x += p.alpha * acc[4 * j + 0];
-            v.y += p.alpha * acc[4 * j + 1];
-            v.z += p.alpha * acc[4 * j + 2];
-            v.w += p.alpha * acc[4 * j + 3];
-            dst[j] = v;
+            for (int j = 0; j < 32; j++) acc[j] += __ldg(p.bias + n0 + j);
         }
-        return;
+        if (p.act == ACT_RELU) {
+#pragma unroll
+            for (int j = 0; j < 32; j++) acc[j] = fmaxf(acc[j], 0.0f);
+        } else if (p.act == ACT_SILU) {
+#pragma unroll
+            for (int j = 0; j < 32; j++) acc[j] = silu_fast(acc[j]);
+        }
     }
-    if (p.bias != nullptr) {
-#pragma unroll
-        for (int j = 0; j < 32; j++) acc[j] += __ldg(p.bias + n0 + j);
-    }
-    if (p.act == ACT_RELU) {
-#pragma unroll
-        for (int j = 0; j < 32; j++) acc[j] = fmaxf(acc[j], 0.0f);
-    } else if (p.act == ACT_SILU) {
-#pragma unroll
-        for (int j = 0; j < 32; j++) acc[j] = silu_f(acc[j]);
-    }
-    if (p.kind == EPI_STORE) {
-        float4* dst = reinterpret_cast<float4*>(p.out_f32 + (size_t)m * p.ldo + n0);
-#pragma unroll
-        for (int j = 0; j < 8; j++) dst[j] = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
-    } else if (p.kind == EPI_STORE_F16) {
+    if (p.kind == EPI_STORE_F16) {
         if (p.act_quant) {
             float amax = 0.0f;
 #pragma unroll
             for (int j = 0; j < 32; j++) amax = fmaxf(amax, fabsf(acc[j]));
+            float d, id;
+            fq_scales(amax, d, id);
 #pragma unroll
-            for (int j = 0; j < 32; j++) acc[j] = fake_quant(acc[j], amax);
+            for (int j = 0; j < 32; j++) acc[j] = rintf(__fmul_rn(acc[j], id)) * d;
         }
-        uint4* dst = reinterpret_cast<uint4*>(p.out_f16 + (size_t)m * p.ldo + n0);
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            __half2 h0 = __floats2half2_rn(acc[8 * j + 0], acc[8 * j + 1]);
-            __half2 h1 = __floats2half2_rn(acc[8 * j + 2], acc[8 * j + 3]);
-            __half2 h2 = __floats2half2_rn(acc[8 * j + 4], acc[8 * j + 5]);
-            __half2 h3 = __floats2half2_rn(acc[8 * j + 6], acc[8 * j + 7]);
-            uint4 u;
-            u.x = *reinterpret_cast<uint32_t*>(&h0);
-            u.y = *reinterpret_cast<uint32_t*>(&h1);
-            u.z = *reinterpret_cast<uint32_t*>(&h2);
-            u.w = *reinterpret_cast<uint32_t*>(&h3);
-            dst[j] = u;
+        for (int j = 0; j < 16; j++) {
+            __half2 h = __floats2half2_rn(acc[2 * j], acc[2 * j + 1]);
+            w[j] = *reinterpret_cast<uint32_t*>(&h);
         }
-    } else if (p.kind == EPI_QKV) {
-        float* base;
-        if (n0 < D_MODEL) {
-            base = p.out_f32 + (size_t)m * D_MODEL + n0;
-        } else {
-            int b = m / p.T, i = m - b * p.T;
-            int pos = p.wpos[b] + i;
-            if (pos >= RING) pos -= RING;
-            float* ring = (n0 < 2 * D_MODEL) ? p.k_ring : p.v_ring;
-            base = ring + ((size_t)p.slot[b] * RING + pos) * D_MODEL + (n0 & (D_MODEL - 1));
-        }
-        float4* dst = reinterpret_cast<float4*>(base);
-#pragma unroll
-        for (int j = 0; j < 8; j++) dst[j] = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
-    } else if (p.kind == EPI_GLU) {
-        float4* dst = reinterpret_cast<float4*>(p.out_f32 + (size_t)m * p.ldo + (n0 >> 1));
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            float4 v;
-            v.x = acc[8 * j + 0] * sigmoid_f(acc[8 * j + 1]);
-            v.y = acc[8 * j + 2] * sigmoid_f(acc[8 * j + 3]);
-            v.z = acc[8 * j + 4] * sigmoid_f(acc[8 * j + 5]);
-            v.w = acc[8 * j + 6] * sigmoid_f(acc[8 * j + 7]);
-            dst[j] = v;
-        }
+        dst = reinterpret_cast<char*>(p.out_f16 + (size_t)m * p.ldo + n0);
+        return 16;
     }
+    if (p.kind == EPI_GLU) {
+#pragma unroll
+        for (int j = 0; j < 16; j++) w[j] = __float_as_uint(acc[2 * j] * sigmoid_fast(acc[2 * j + 1]));
+        dst = reinterpret_cast<char*>(p.out_f32 + (size_t)m * p.ldo + (n0 >> 1));
+        return 16;
+    }
+#pragma unroll
+    for (int j = 0; j < 32; j++) w[j] = __float_as_uint(acc[j]);
+    if (p.kind == EPI_QKV && n0 >= D_MODEL) {
+        const int b = m / p.T, i = m - b * p.T;
+        int pos = p.wpos[b] + i;
+        if (pos >= RING) pos -= RING;
+        float* ring = (n0 < 2 * D_MODEL) ? p.k_ring : p.v_ring;
+        dst = reinterpret_cast<char*>(ring + ((size_t)p.slot[b] * RING + pos) * D_MODEL + (n0 & (D_MODEL - 1)));
+    } else if (p.kind == EPI_QKV) {
+        dst = reinterpret_cast<char*>(p.out_f32 + (size_t)m * D_MODEL + n0);
+    } else {
+        dst = reinterpret_cast<char*>(p.out_f32 + (size_t)m * p.ldo + n0);
+    }
+    return 32;
+}
+
+// Direct (one thread = one row) version used by the CUDA-core checker kernel: same transform, per-thread stores.
+__device__ __forceinline__ void epilogue_apply(const EpiParams& p, int m, int n0, float (&acc)[32]) {
+    uint32_t w[32];
+    char* dst;
+    const int nw = epilogue_transform(p, m, n0, acc, w, dst);
+    uint4* d4 = reinterpret_cast<uint4*>(dst);
+    if (p.kind == EPI_RESID) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            float4 v = reinterpret_cast<float4*>(dst)[j];
+            v.x += p.alpha * __uint_as_float(w[4 * j + 0]);
+            v.y += p.alpha * __uint_as_float(w[4 * j + 1]);
+            v.z += p.alpha * __uint_as_float(w[4 * j + 2]);
+            v.w += p.alpha * __uint_as_float(w[4 * j + 3]);
+            reinterpret_cast<float4*>(dst)[j] = v;
+        }
+        return;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; j++)
+        if (4 * j < nw) d4[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
 }
 
 // One fp16 operand matrix [rows, K] (K contiguous) in HBM, with the TMA descriptors of its two tile heights.
 struct Operand {
     const __half* ptr = nullptr;
     int rows = 0, K = 0;
-    CUtensorMap map128;  // box 64(K) x 128 rows, 128B swizzle
+    CUtensorMap map256;  // box 64(K) x 256 rows, 128B swizzle
+    CUtensorMap map128;  // box 64(K) x 128 rows
     CUtensorMap map64;   // box 64(K) x 64 rows
+    CUtensorMap map32;   // box 64(K) x 32 rows
 };
 void operand_init(Operand& op, const __half* ptr, int rows, int K);  // builds the tensor maps
 
 // C = A * W^T (+ epilogue). M valid rows of A; N = W.rows; K = A.K = W.K. use_simt selects the checker kernel.
-void gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiParams& epi, bool use_simt);
+// Returns the number of K splits used (1 unless epi.kind == EPI_PARTIAL; never more than max_splits).
+int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiParams& epi, bool use_simt, int max_splits = 1);
+// Tile / split configuration the tcgen05 path would pick (exposed for the benchmarks and DESIGN.md)
+struct GemmConfig {
+    int bn, splits, ctas;
+};
+GemmConfig gemm_pick_config(int M, int N, int K, int max_splits);
+// Forces a configuration (bn in {32,64,128,256}, splits >= 1) for tuning runs; bn = 0 restores the heuristic.
+void gemm_force_config(int bn, int splits);
 
 }  // namespace nb

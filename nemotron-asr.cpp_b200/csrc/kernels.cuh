@@ -42,9 +42,17 @@ void launch_sub_stage1(cudaStream_t st, const SubWeights& w, const float* mel, _
 void launch_sub_stage2(cudaStream_t st, const SubWeights& w, const float* a3, __half* out, int B, int t2, int t3);
 
 // ---- encoder.cu ----------------------------------------------------------------------------------
+// Optional residual input: x += alpha * sum_{s<nsplit} partials[s*stride + ...] first (the split-K partial outputs of the
+// GEMM that precedes this norm; src/nemo-stream.cpp:631-634,654,677,682-685 are the adds this replaces), written back to x.
+struct ResidualIn {
+    const float* partials = nullptr;
+    int nsplit = 0;
+    size_t stride = 0;
+    float alpha = 1.0f;
+};
 // y = LN(x; g1,b1); if out_f32: out_f32 = y; z = g2 ? LN(y; g2,b2) : y; out_f16 = fp16(fq ? fake_quant(z) : z)
-void launch_layernorm(cudaStream_t st, const float* x, const float* g1, const float* b1, float* out_f32, const float* g2,
-                      const float* b2, __half* out_f16, int act_quant, int M);
+void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b1, float* out_f32, const float* g2,
+                      const float* b2, __half* out_f16, int act_quant, int M, const ResidualIn& rin = ResidualIn());
 
 struct AttnArgs {
     const float* q;        // [M][1024] fp32 (row m = b*T + i)

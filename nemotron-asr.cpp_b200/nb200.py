@@ -67,6 +67,8 @@ SYMBOLS = {
     "nb200_profile_report": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
     "nb200_mel_batch": (C.c_int, [C.c_void_p, _I16P, C.c_int, C.c_int, _F32P]),
     "nb200_debug_matmul": (C.c_int, [C.c_void_p, C.c_char_p, _F32P, C.c_int, _F32P]),
+    "nb200_bench_gemm": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double),
+                                   C.POINTER(C.c_int), C.POINTER(C.c_int)]),
 }
 
 _lib = None
@@ -184,6 +186,13 @@ class Model:
         if r < 0:
             raise NB200Error(_err())
         return out
+
+    def bench_gemm(self, M: int, N: int, K: int, epi_kind: int = 0, bn: int = 0, splits: int = 1, iters: int = 50) -> dict:
+        """Device time of the tcgen05 GEMM alone (weights streamed from HBM); see include/nb200.h."""
+        us, bn_used, sp_used = C.c_double(), C.c_int(), C.c_int()
+        if lib().nb200_bench_gemm(self._h, M, N, K, epi_kind, bn, splits, iters, C.byref(us), C.byref(bn_used), C.byref(sp_used)) < 0:
+            raise NB200Error(_err())
+        return {"us": us.value, "bn": bn_used.value, "splits": sp_used.value, "tflops": 2.0 * M * N * K / us.value * 1e-6}
 
     def debug_matmul(self, tensor_name: str, x: np.ndarray, n_out: int) -> np.ndarray:
         x = np.ascontiguousarray(x, dtype=np.float32)
