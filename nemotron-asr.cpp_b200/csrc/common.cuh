@@ -53,6 +53,37 @@ struct ProfScope {
     }
 };
 
+// ---- programmatic dependent launch (PDL) -----------------------------------------------------------------------
+// Every kernel of the library starts with pdl_prologue(): "launch_dependents" lets the NEXT kernel in the stream be
+// scheduled as soon as all CTAs of this one have started (its CTAs then sit in their own prologue / at their wait),
+// and "wait" blocks until the PREVIOUS kernel has completed and its writes are visible. All global-memory reads of
+// produced data and all global writes come after the wait, so the only thing that overlaps is launch latency and
+// per-CTA setup (barrier init, TMEM allocation, descriptor prefetch). Kernels are launched through launch_k(), which
+// sets the programmatic-stream-serialization attribute (also inside CUDA-graph capture). NB200_NO_PDL=1 disables it.
+extern bool g_pdl;
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_prologue() {
+    pdl_launch();
+    pdl_wait();
+}
+template <typename... KArgs, typename... Args>
+void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = g_pdl ? 1 : 0;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    CUDA_CHECK(cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...));
+}
+#endif
+
 template <typename T>
 T* dalloc(size_t n) {
     T* p = nullptr;

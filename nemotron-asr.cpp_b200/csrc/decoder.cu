@@ -18,6 +18,7 @@ constexpr int VOCAB_PAD = 1088;
 __global__ void __launch_bounds__(256) sgemm_nt_kernel(const float* __restrict__ A, const float* __restrict__ W,
                                                        const float* __restrict__ bias, float* __restrict__ C, int M, int N,
                                                        int K, int ldc, const int* __restrict__ out_rows) {
+    pdl_prologue();
     __shared__ float As[16][64 + 4];
     __shared__ float Ws[16][64 + 4];
     const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
@@ -68,6 +69,7 @@ __global__ void __launch_bounds__(256) sgemm_skinny_kernel(const float* __restri
                                                            const float* __restrict__ bias, float* __restrict__ C, int M, int N,
                                                            int K, int ldc, const int* __restrict__ out_rows,
                                                            const int* __restrict__ gate) {
+    pdl_prologue();
     if (gate != nullptr && *gate == 0) return;
     __shared__ float As[32][64 + 4];
     __shared__ float Ws[32][16 + 1];
@@ -118,19 +120,20 @@ void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* 
     const double flops = 2.0 * M * (double)N * K, bytes = 4.0 * ((double)M * K + (double)N * K + (double)M * N);
     if (M <= 64) {
         ProfScope ps(st, "sgemm_f32_skinny", flops, bytes);
-        sgemm_skinny_kernel<<<N / 16, 256, 0, st>>>(A, W, bias, C, M, N, K, ldc, out_rows, gate);
+        launch_k(sgemm_skinny_kernel, dim3(N / 16), dim3(256), 0, st, A, W, bias, C, M, N, K, ldc, out_rows, gate);
         NB_KERNEL_CHECK();
         return;
     }
     if (gate) throw Error("sgemm: gated launches are only supported for M <= 64");
     ProfScope ps(st, "sgemm_f32", flops, bytes);
-    sgemm_nt_kernel<<<dim3(N / 64, cdiv(M, 64)), 256, 0, st>>>(A, W, bias, C, M, N, K, ldc, out_rows);
+    launch_k(sgemm_nt_kernel, dim3(dim3(N / 64, cdiv(M, 64))), dim3(256), 0, st, A, W, bias, C, M, N, K, ldc, out_rows);
     NB_KERNEL_CHECK();
 }
 
 // ---- round kernels -------------------------------------------------------------------------------------
 // hid[b] = relu(e[b, fp[b]] + pend_p[slot[b]])   (src/nemo-ggml.cpp:1215-1217); zeros for finished streams
 __global__ void __launch_bounds__(160) hid_kernel(DecodeState s, DecodeBatch d) {
+    pdl_prologue();
     const int b = blockIdx.x, i = threadIdx.x * 4;
     if (b == 0 && threadIdx.x == 0) {  // first kernel of a round: reset the round's flags
         *d.unfinished = 0;
@@ -149,6 +152,7 @@ __global__ void __launch_bounds__(160) hid_kernel(DecodeState s, DecodeBatch d) 
 // first-max argmax over the 1025 logits, then the reference's state machine (src/nemo-stream.cpp:899-926);
 // also stages the LSTM layer-0 input row x[b] = [embed[prev] | h0].
 __global__ void __launch_bounds__(256) argmax_commit_kernel(DecodeWeights w, DecodeState s, DecodeBatch d) {
+    pdl_prologue();
     const int b = blockIdx.x, t = threadIdx.x, slot = d.slot[b];
     __shared__ float bv[8], bs[8];
     __shared__ int bi[8];
@@ -216,6 +220,7 @@ __global__ void __launch_bounds__(256) argmax_commit_kernel(DecodeWeights w, Dec
 
 // stage the layer-0 input without touching the state machine (used by refresh)
 __global__ void __launch_bounds__(256) stage_x0_kernel(DecodeWeights w, DecodeState s, DecodeBatch d) {
+    pdl_prologue();
     const int b = blockIdx.x, t = threadIdx.x, slot = d.slot[b];
     const int prev = s.prev[slot];
     for (int i = t; i < DEC; i += 256) {
@@ -226,6 +231,7 @@ __global__ void __launch_bounds__(256) stage_x0_kernel(DecodeWeights w, DecodeSt
 
 // LSTM cell, gate order i,f,g,o (src/nemo-ggml.cpp:601-618). layer 0 also stages x[b] = [h0' | h1]; layer 1 stages hp.
 __global__ void __launch_bounds__(160) cell_kernel(DecodeState s, DecodeBatch d, int layer, const int* __restrict__ gate) {
+    pdl_prologue();
     if (gate != nullptr && *gate == 0) return;
     const int b = blockIdx.x, slot = d.slot[b];
     const float* g = d.gates + (size_t)b * 4 * DEC;
@@ -258,28 +264,28 @@ static void lstm_update(cudaStream_t st, const DecodeWeights& w, const DecodeSta
         float* hp = d.hp + (size_t)b0 * DEC;
         e.x = x; e.gates = gates; e.hp = hp;
         launch_sgemm(st, x, w.wcat[0], w.bcat[0], gates, nb, 4 * DEC, 2 * DEC, 4 * DEC, nullptr, gate);
-        cell_kernel<<<nb, 160, 0, st>>>(s, e, 0, gate);
+        launch_k(cell_kernel, dim3(nb), dim3(160), 0, st, s, e, 0, gate);
         NB_KERNEL_CHECK();
         launch_sgemm(st, x, w.wcat[1], w.bcat[1], gates, nb, 4 * DEC, 2 * DEC, 4 * DEC, nullptr, gate);
-        cell_kernel<<<nb, 160, 0, st>>>(s, e, 1, gate);
+        launch_k(cell_kernel, dim3(nb), dim3(160), 0, st, s, e, 1, gate);
         NB_KERNEL_CHECK();
         launch_sgemm(st, hp, w.wpred, w.bpred, s.pend_p, nb, JOINT, DEC, JOINT, e.slot, gate);
     }
 }
 
 void launch_decode_round(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d) {
-    hid_kernel<<<d.B, 160, 0, st>>>(s, d);
+    launch_k(hid_kernel, dim3(d.B), dim3(160), 0, st, s, d);
     NB_KERNEL_CHECK();
     for (int b0 = 0; b0 < d.B; b0 += 64)
         launch_sgemm(st, d.hid + (size_t)b0 * JOINT, w.wout, w.bout, d.logits + (size_t)b0 * VOCAB_PAD, std::min(64, d.B - b0), VOCAB_PAD,
                      JOINT, VOCAB_PAD, nullptr, nullptr);
-    argmax_commit_kernel<<<d.B, 256, 0, st>>>(w, s, d);
+    launch_k(argmax_commit_kernel, dim3(d.B), dim3(256), 0, st, w, s, d);
     NB_KERNEL_CHECK();
     lstm_update(st, w, s, d, d.any_emit);
 }
 
 void launch_decode_refresh(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d) {
-    stage_x0_kernel<<<d.B, 256, 0, st>>>(w, s, d);
+    launch_k(stage_x0_kernel, dim3(d.B), dim3(256), 0, st, w, s, d);
     NB_KERNEL_CHECK();
     lstm_update(st, w, s, d, nullptr);
 }

@@ -6,10 +6,11 @@
 namespace nb {
 
 // ---- block reductions over 256 threads ------------------------------------------------------------
+// `red` must be a different 8-float array for consecutive reductions of one kernel: that removes the barrier that
+// would otherwise protect the scratch from the next reduction's writes (one __syncthreads per reduction, not two).
 __device__ __forceinline__ float block_sum_256(float v, float* red) {
     v = warp_sum(v);
     const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-    __syncthreads();
     if (l == 0) red[w] = v;
     __syncthreads();
     float s = 0.0f;
@@ -47,7 +48,7 @@ __device__ __forceinline__ float4 ln_1024(float4 v, const float* g, const float*
     const int c = threadIdx.x * 4;
     const float mean = block_sum_256(v.x + v.y + v.z + v.w, red) * (1.0f / D_MODEL);
     v.x -= mean; v.y -= mean; v.z -= mean; v.w -= mean;
-    const float var = block_sum_256(v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w, red) * (1.0f / D_MODEL);
+    const float var = block_sum_256(v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w, red + 8) * (1.0f / D_MODEL);
     const float sc = 1.0f / sqrtf(var + 1e-5f);
     const float4 gg = *reinterpret_cast<const float4*>(g + c), bb = *reinterpret_cast<const float4*>(b + c);
     v.x = v.x * sc * gg.x + bb.x;
@@ -61,7 +62,8 @@ __global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, c
                                                         const float* __restrict__ b1, float* __restrict__ out_f32,
                                                         const float* __restrict__ g2, const float* __restrict__ b2,
                                                         __half* __restrict__ out_f16, int act_quant, ResidualIn rin) {
-    __shared__ float red[8];
+    pdl_prologue();
+    __shared__ float red[32];
     const size_t off = (size_t)blockIdx.x * D_MODEL + threadIdx.x * 4;
     float4 v = *reinterpret_cast<const float4*>(x + off);
     if (rin.partials != nullptr) {  // x += alpha * (sum of the preceding GEMM's split-K partials), in split order
@@ -75,7 +77,7 @@ __global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, c
     }
     v = ln_1024(v, g1, b1, red);
     if (out_f32) *reinterpret_cast<float4*>(out_f32 + off) = v;
-    if (g2) v = ln_1024(v, g2, b2, red);
+    if (g2) v = ln_1024(v, g2, b2, red + 16);
     if (out_f16) store_f16x4(out_f16 + off, v, act_quant);
 }
 
@@ -84,7 +86,7 @@ void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b
     if (M <= 0) return;
     ProfScope ps(st, "layernorm", (double)M * D_MODEL * 8,
                  (double)M * D_MODEL * (4 + (out_f32 ? 4 : 0) + (out_f16 ? 2 : 0) + (rin.partials ? 4.0 * rin.nsplit + (out_f32 != x ? 4 : 0) : 0)));
-    layernorm_kernel<<<M, 256, 0, st>>>(x, g1, b1, out_f32, g2, b2, out_f16, act_quant, rin);
+    launch_k(layernorm_kernel, dim3(M), dim3(256), 0, st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, rin);
     NB_KERNEL_CHECK();
 }
 
@@ -96,6 +98,7 @@ void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b
 constexpr int ATT_LD = D_HEAD + 1;  // padded row: conflict-free when a warp reads one column of 32 rows
 
 __global__ void __launch_bounds__(256) attention_kernel(AttnArgs a) {
+    pdl_prologue();
     extern __shared__ float sm[];
     const int h = blockIdx.x, b = blockIdx.y, T = a.T;
     const int kv = LEFT + T, npos = LEFT + 2 * T - 1;
@@ -237,6 +240,7 @@ __device__ __forceinline__ void mma_3xtf32(float (&c)[4], const float (&a)[4], c
 }
 
 __global__ void __launch_bounds__(256) attention_tc_kernel(AttnArgs a) {
+    pdl_prologue();
     __shared__ __align__(16) float Qu[16 * QS];
     __shared__ __align__(16) float Qv[16 * QS];
     __shared__ __align__(16) float S1[16 * S1S];
@@ -391,13 +395,13 @@ void launch_attention(cudaStream_t st, const AttnArgs& a) {
             configured = true;
         }
         ProfScope ps(st, "attention_simt", flops, bytes);
-        attention_kernel<<<dim3(N_HEADS, a.B), 256, attn_smem_bytes(a.T), st>>>(a);
+        launch_k(attention_kernel, dim3(dim3(N_HEADS, a.B)), dim3(256), attn_smem_bytes(a.T), st, a);
         NB_KERNEL_CHECK();
         return;
     }
     if (a.T > 14) throw Error("attention: more than 14 frames per chunk");
     ProfScope ps(st, "attention_tc", flops, bytes);
-    attention_tc_kernel<<<dim3(N_HEADS, a.B), 256, 0, st>>>(a);
+    launch_k(attention_tc_kernel, dim3(dim3(N_HEADS, a.B)), dim3(256), 0, st, a);
     NB_KERNEL_CHECK();
 }
 
@@ -405,7 +409,8 @@ void launch_attention(cudaStream_t st, const AttnArgs& a) {
 // One CTA per (frame t, stream): d[t][ch] = sum_k G[t+k][ch] * w[k][ch], G = [cache(8) ; g(T)] (src/nemo-stream.cpp:336-412),
 // products accumulated in tap order like the reference's mul/add chain (:370-388); then LN (conv.batch_norm), SiLU (:671-674).
 __global__ void __launch_bounds__(256) dwconv_kernel(ConvArgs a) {
-    __shared__ float red[8];
+    pdl_prologue();
+    __shared__ float red[16];
     const int t = blockIdx.x, b = blockIdx.y, c = threadIdx.x * 4;
     const float* cache = a.conv_cache + (size_t)a.slot[b] * CONV_CACHE * D_MODEL;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -429,12 +434,13 @@ __global__ void __launch_bounds__(256) dwconv_kernel(ConvArgs a) {
 
 void launch_dwconv(cudaStream_t st, const ConvArgs& a) {
     ProfScope ps(st, "dwconv_ln_silu", (double)a.B * a.T * D_MODEL * 30, (double)a.B * ((a.T + 8.0) * D_MODEL * 4 + (double)a.T * D_MODEL * 2));
-    dwconv_kernel<<<dim3(a.T, a.B), 256, 0, st>>>(a);
+    launch_k(dwconv_kernel, dim3(dim3(a.T, a.B)), dim3(256), 0, st, a);
     NB_KERNEL_CHECK();
 }
 
 // new cache = last 8 rows of [cache ; g]; one CTA per stream, thread = 4 channels, rows staged in registers
 __global__ void __launch_bounds__(256) conv_cache_update_kernel(ConvArgs a) {
+    pdl_prologue();
     const int b = blockIdx.x, c = threadIdx.x * 4, T = a.T;
     float* cache = a.conv_cache + (size_t)a.slot[b] * CONV_CACHE * D_MODEL;
     float4 rows[CONV_CACHE];
@@ -450,12 +456,13 @@ __global__ void __launch_bounds__(256) conv_cache_update_kernel(ConvArgs a) {
 
 void launch_conv_cache_update(cudaStream_t st, const ConvArgs& a) {
     ProfScope ps(st, "conv_cache_update", 0.0, (double)a.B * 16.0 * D_MODEL * 4);
-    conv_cache_update_kernel<<<a.B, 256, 0, st>>>(a);
+    launch_k(conv_cache_update_kernel, dim3(a.B), dim3(256), 0, st, a);
     NB_KERNEL_CHECK();
 }
 
 // ---- helpers for the positional table ---------------------------------------------------------------
 __global__ void __launch_bounds__(256) cast_f16_kernel(const float* __restrict__ x, __half* __restrict__ out, int act_quant, int cols) {
+    pdl_prologue();
     const size_t row = blockIdx.x;
     for (int c = threadIdx.x * 4; c < cols; c += 1024) {
         float4 v = *reinterpret_cast<const float4*>(x + row * cols + c);
@@ -464,12 +471,13 @@ __global__ void __launch_bounds__(256) cast_f16_kernel(const float* __restrict__
 }
 void launch_cast_f16(cudaStream_t st, const float* x, __half* out, int act_quant, int rows, int cols) {
     if (cols % 1024 != 0) throw Error("cast_f16: cols must be a multiple of 1024");
-    cast_f16_kernel<<<rows, 256, 0, st>>>(x, out, act_quant, cols);
+    launch_k(cast_f16_kernel, dim3(rows), dim3(256), 0, st, x, out, act_quant, cols);
     NB_KERNEL_CHECK();
 }
 
 // PE(p)[2i] = sin(p * w_i), PE(p)[2i+1] = cos(p * w_i), w_i = exp(-(2i) * ln(10000) / 1024)  (src/nemo-ggml.cpp:17-32)
 __global__ void pos_emb_kernel(float* out, int p0) {
+    pdl_prologue();
     const int r = blockIdx.x, i2 = threadIdx.x * 2;  // 512 threads
     const float p = (float)(p0 + r);
     const float div = expf(-(float)i2 * logf(10000.0f) / (float)D_MODEL);
@@ -477,7 +485,7 @@ __global__ void pos_emb_kernel(float* out, int p0) {
     out[(size_t)r * D_MODEL + i2 + 1] = cosf(p * div);
 }
 void launch_pos_emb(cudaStream_t st, float* out, int p0, int n) {
-    pos_emb_kernel<<<n, 512, 0, st>>>(out, p0);
+    launch_k(pos_emb_kernel, dim3(n), dim3(512), 0, st, out, p0);
     NB_KERNEL_CHECK();
 }
 

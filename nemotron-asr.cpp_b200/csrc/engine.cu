@@ -517,6 +517,7 @@ void reset_slot(nb200_model* m, int slot) {
 // ---- small copy kernels of the step ---------------------------------------------------------------------
 // chunk[b][0:9] = overlap[slot[b]]; chunk[b][9+n_frames[b] : chunk_mel] = 0 (tail chunk of a finalize)
 __global__ void mel_assemble_kernel(float* chunk, const float* overlap, const int* slot, const int* n_frames, int chunk_mel) {
+    pdl_prologue();
     const int b = blockIdx.y, f = blockIdx.x, t = threadIdx.x;  // 128 threads
     float* dst = chunk + ((size_t)b * chunk_mel + f) * N_MELS + t;
     if (f < MEL_OVERLAP) *dst = overlap[((size_t)slot[b] * MEL_OVERLAP + f) * N_MELS + t];
@@ -524,6 +525,7 @@ __global__ void mel_assemble_kernel(float* chunk, const float* overlap, const in
 }
 // overlap[slot[b]] = chunk[b][shift : shift+9]
 __global__ void mel_save_overlap_kernel(const float* chunk, float* overlap, const int* slot, int chunk_mel, int shift) {
+    pdl_prologue();
     const int b = blockIdx.y, f = blockIdx.x, t = threadIdx.x;
     overlap[((size_t)slot[b] * MEL_OVERLAP + f) * N_MELS + t] = chunk[((size_t)b * chunk_mel + shift + f) * N_MELS + t];
 }
@@ -603,7 +605,7 @@ void enqueue_encoder(const StepCtx& c) {
     const int* d_nframes = m->ws_meta + 4 * capB;
 
     // frontend: log-mel of the new samples, then dw-striding subsampling (src/nemo-ggml.cpp:954-1029)
-    mel_assemble_kernel<<<dim3(md.chunk_mel, B), N_MELS, 0, st>>>(m->ws_mel, m->mel_overlap, d_slot, d_nframes, md.chunk_mel);
+    launch_k(mel_assemble_kernel, dim3(dim3(md.chunk_mel, B)), dim3(N_MELS), 0, st, m->ws_mel, m->mel_overlap, d_slot, d_nframes, md.chunk_mel);
     NB_KERNEL_CHECK();
     {
         MelBatch mb{m->pcm_ring, m->ring_cap, d_slot, d_nframes, m->ws_meta64 + 1 * capB, m->ws_meta64 + 2 * capB, m->ws_meta64 + 0 * capB};
@@ -623,7 +625,7 @@ void enqueue_encoder(const StepCtx& c) {
         }
     }
     launch_sub_stage1(st, m->sub, m->ws_mel, m->ws_a2h, B, md.chunk_mel, md.t1, md.t2);
-    mel_save_overlap_kernel<<<dim3(MEL_OVERLAP, B), N_MELS, 0, st>>>(m->ws_mel, m->mel_overlap, d_slot, md.chunk_mel, md.shift);
+    launch_k(mel_save_overlap_kernel, dim3(dim3(MEL_OVERLAP, B)), dim3(N_MELS), 0, st, m->ws_mel, m->mel_overlap, d_slot, md.chunk_mel, md.shift);
     NB_KERNEL_CHECK();
     {
         EpiParams ep;  // pw3 + bias + ReLU -> fp32 (input of the fp32 depthwise conv5)

@@ -11,6 +11,7 @@
 namespace nb {
 
 __global__ void __launch_bounds__(256) mel_kernel(MelTables tb, MelBatch mb, float* __restrict__ mel_out) {
+    pdl_prologue();
     const int f = blockIdx.x, b = blockIdx.y;
     if (f >= mb.n_frames[b]) return;
     __shared__ float xs[N_FFT + 1];
@@ -69,7 +70,7 @@ __global__ void __launch_bounds__(256) mel_kernel(MelTables tb, MelBatch mb, flo
 void launch_mel(cudaStream_t st, const MelTables& tb, const MelBatch& mb, float* mel_out, int B, int max_frames) {
     if (B <= 0 || max_frames <= 0) return;
     ProfScope ps(st, "mel", (double)B * max_frames * 2.0e5, (double)B * max_frames * (HOP * 2 + N_MELS * 4));
-    mel_kernel<<<dim3(max_frames, B), 256, 0, st>>>(tb, mb, mel_out);
+    launch_k(mel_kernel, dim3(dim3(max_frames, B)), dim3(256), 0, st, tb, mb, mel_out);
     NB_KERNEL_CHECK();
 }
 
@@ -78,6 +79,7 @@ void launch_mel(cudaStream_t st, const MelTables& tb, const MelBatch& mb, float*
 // (h2, stream): thread = channel; the 7 mel rows feeding this output row sit in shared memory, fp16-rounded.
 __global__ void __launch_bounds__(256) sub_stage1_kernel(SubWeights w, const float* __restrict__ mel, __half* __restrict__ out,
                                                          int chunk_mel, int t1, int t2) {
+    pdl_prologue();
     const int h2 = blockIdx.x, b = blockIdx.y, c = threadIdx.x;
     __shared__ float ms[7][N_MELS + 4];  // column index = mel bin + 2 (two zero columns on the left, two on the right)
     const float* msrc = mel + (size_t)b * chunk_mel * N_MELS;
@@ -124,13 +126,14 @@ __global__ void __launch_bounds__(256) sub_stage1_kernel(SubWeights w, const flo
 void launch_sub_stage1(cudaStream_t st, const SubWeights& w, const float* mel, __half* out, int B, int chunk_mel, int t1, int t2) {
     ProfScope ps(st, "sub_conv0_dw2", (double)B * t2 * SUB_F2 * SUB_CH * 2.0 * 9 * 10,
                  (double)B * (chunk_mel * N_MELS * 4.0 + (double)t2 * SUB_F2 * SUB_CH * 2));
-    sub_stage1_kernel<<<dim3(t2, B), 256, 0, st>>>(w, mel, out, chunk_mel, t1, t2);
+    launch_k(sub_stage1_kernel, dim3(dim3(t2, B)), dim3(256), 0, st, w, mel, out, chunk_mel, t1, t2);
     NB_KERNEL_CHECK();
 }
 
 // ---- subsampling stage 2: depthwise conv5 over relu(pw3), only the rows that survive the drop of 2 frames ----------
 __global__ void __launch_bounds__(256) sub_stage2_kernel(SubWeights w, const float* __restrict__ a3, __half* __restrict__ out,
                                                          int t2, int t3) {
+    pdl_prologue();
     const int w3 = blockIdx.x, hh = blockIdx.y, b = blockIdx.z, c = threadIdx.x;
     const int h3 = hh + 2;
     float acc = w.b5[c];
@@ -151,7 +154,7 @@ __global__ void __launch_bounds__(256) sub_stage2_kernel(SubWeights w, const flo
 void launch_sub_stage2(cudaStream_t st, const SubWeights& w, const float* a3, __half* out, int B, int t2, int t3) {
     ProfScope ps(st, "sub_dw5", (double)B * (t3 - 2) * SUB_F3 * SUB_CH * 18.0,
                  (double)B * ((double)t2 * SUB_F2 * SUB_CH * 4 + (double)(t3 - 2) * SUB_F3 * SUB_CH * 2));
-    sub_stage2_kernel<<<dim3(SUB_F3, t3 - 2, B), 256, 0, st>>>(w, a3, out, t2, t3);
+    launch_k(sub_stage2_kernel, dim3(dim3(SUB_F3, t3 - 2, B)), dim3(256), 0, st, w, a3, out, t2, t3);
     NB_KERNEL_CHECK();
 }
 

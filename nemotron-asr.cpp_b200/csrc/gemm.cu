@@ -109,6 +109,7 @@ template <int BN, int STAGES>
 __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                             const __grid_constant__ CUtensorMap map_w, int M, int num_k,
                                                             EpiParams epi) {
+    pdl_launch();
     using S = TcSmem<BN, STAGES>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
@@ -142,6 +143,7 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();  // everything above overlapped the previous kernel's tail; its outputs are visible from here on
 
     if (warp == 0) {
         if (lane == 0) {  // ===== TMA producer =====
@@ -240,6 +242,7 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) gemm_simt_kernel(const __half* __restrict__ A, const __half* __restrict__ W, int M,
                                                        int N, int K, EpiParams epi) {
+    pdl_prologue();
     __shared__ float As[32][64 + 1];
     __shared__ float Ws[32][64 + 4];
     const int t = threadIdx.x;
@@ -342,7 +345,7 @@ static void launch_tc(cudaStream_t st, const Operand& A, const Operand& W, int M
     }
     dim3 grid(W.rows / BN, cdiv(M, TC_BM), splits);
     const CUtensorMap& wmap = BN == 256 ? W.map256 : (BN == 128 ? W.map128 : (BN == 64 ? W.map64 : W.map32));
-    gemm_tc_kernel<BN, STAGES><<<grid, TC_THREADS, S::TOTAL, st>>>(A.map128, wmap, M, A.K / TC_BK / splits, epi);
+    launch_k(gemm_tc_kernel<BN, STAGES>, grid, dim3(TC_THREADS), (size_t)S::TOTAL, st, A.map128, wmap, M, A.K / TC_BK / splits, epi);
     NB_KERNEL_CHECK();
 }
 
@@ -400,7 +403,7 @@ int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiPa
     if (use_simt) {
         ProfScope ps(st, "gemm_simt", flops, bytes);
         dim3 grid(N / 64, cdiv(M, 64));
-        gemm_simt_kernel<<<grid, 128, 0, st>>>(A.ptr, W.ptr, M, N, A.K, epi);
+        launch_k(gemm_simt_kernel, dim3(grid), dim3(128), 0, st, A.ptr, W.ptr, M, N, A.K, epi);
         NB_KERNEL_CHECK();
         return 1;
     }

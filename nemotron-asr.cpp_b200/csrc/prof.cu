@@ -1,5 +1,6 @@
 // prof.cu — per-kernel-family device timing behind nb200_profile_{enable,report}. Events are recorded on the stream
 // the kernel is launched on; durations are resolved when the report is requested (after a stream synchronise).
+#include <cstdlib>
 #include <map>
 #include <string>
 #include <vector>
@@ -9,6 +10,7 @@
 namespace nb {
 
 bool g_prof_on = false;
+bool g_pdl = getenv("NB200_NO_PDL") == nullptr;
 
 namespace {
 struct Rec {
