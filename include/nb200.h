@@ -143,6 +143,12 @@ int nb200_debug_matmul(nb200_model* m, const char* tensor_name, const float* x, 
 int nb200_bench_gemm(nb200_model* m, int M, int N, int K, int epi_kind, int bn, int splits, int iters, double* us_per_launch,
                      int* bn_used, int* splits_used);
 
+/* Phase trace of `launches` back-to-back launches of that GEMM: 8 uint64 per CTA and launch (globaltimer ns):
+ * [0] kernel entry, [1] prologue done, [2] previous kernel's results visible (griddepcontrol.wait returned), [3] first operand
+ * stage landed, [4] accumulator complete, [5] epilogue stored. Returns the CTA count per launch or <0. */
+int nb200_trace_gemm(nb200_model* m, int M, int N, int K, int epi_kind, int bn, int splits, int launches, uint64_t* out,
+                     int cap_words);
+
 #ifdef __cplusplus
 }
 #endif

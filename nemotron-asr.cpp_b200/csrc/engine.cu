@@ -1194,52 +1194,88 @@ int nb200_profile_report(nb200_model* m, char* json_out, int cap) {
     NB_CATCH(NB200_ERR)
 }
 
-int nb200_bench_gemm(nb200_model* m, int M, int N, int K, int epi_kind, int bn, int splits, int iters, double* us_per_launch,
-                     int* bn_used, int* splits_used) {
-    NB_TRY
-    if (!m || M <= 0 || N % 64 || K % 64 || iters <= 0 || !us_per_launch) throw Error("bad argument");
-    CUDA_CHECK(cudaSetDevice(m->device));
-    const int Mp = (M + 127) / 128 * 128;
-    const int n_w = std::max(2, (int)(((size_t)300 << 20) / ((size_t)N * K * 2)));  // cycle > 2x L2 worth of weights
-    __half* a = dalloc<__half>((size_t)Mp * K);
-    __half* w = dalloc<__half>((size_t)n_w * N * K);
-    float* o32 = dalloc<float>((size_t)8 * Mp * N);
-    __half* o16 = dalloc<__half>((size_t)Mp * N);
-    {
+namespace {
+// Synthetic operands for the GEMM microbenchmarks: one activation matrix and enough weight matrices to exceed 2x L2.
+struct GemmBench {
+    int M, N, K, Mp, n_w;
+    __half *a = nullptr, *w = nullptr, *o16 = nullptr;
+    float* o32 = nullptr;
+    Operand A;
+    std::vector<Operand> W;
+    EpiParams ep;
+    GemmBench(int M_, int N_, int K_, int epi_kind) : M(M_), N(N_), K(K_) {
+        Mp = (M + 127) / 128 * 128;
+        n_w = std::max(2, (int)(((size_t)300 << 20) / ((size_t)N * K * 2)));
+        a = dalloc<__half>((size_t)Mp * K);
+        w = dalloc<__half>((size_t)n_w * N * K);
+        o32 = dalloc<float>((size_t)8 * Mp * N);
+        o16 = dalloc<__half>((size_t)Mp * N);
         std::vector<__half> h((size_t)Mp * K);
         for (size_t i = 0; i < h.size(); i++) h[i] = __float2half_rn((float)((int)((i * 2654435761u) >> 20 & 255) - 128) / 64.0f);
         CUDA_CHECK(cudaMemcpy(a, h.data(), h.size() * 2, cudaMemcpyHostToDevice));
         std::vector<__half> hw((size_t)N * K);
         for (size_t i = 0; i < hw.size(); i++) hw[i] = __float2half_rn((float)((int)((i * 40503u) >> 9 & 255) - 128) / 2048.0f);
         for (int j = 0; j < n_w; j++) CUDA_CHECK(cudaMemcpy(w + (size_t)j * N * K, hw.data(), hw.size() * 2, cudaMemcpyHostToDevice));
+        operand_init(A, a, Mp, K);
+        W.resize(n_w);
+        for (int j = 0; j < n_w; j++) operand_init(W[j], w + (size_t)j * N * K, N, K);
+        ep.kind = epi_kind;
+        ep.ldo = N;
+        ep.out_f32 = o32;
+        ep.out_f16 = o16;
+        ep.split_stride = (size_t)Mp * N;
+        if (epi_kind == EPI_STORE_F16) { ep.act = ACT_SILU; ep.act_quant = 1; }
+        if (epi_kind == EPI_GLU) ep.ldo = N / 2;
     }
-    Operand A;
-    operand_init(A, a, Mp, K);
-    std::vector<Operand> W(n_w);
-    for (int j = 0; j < n_w; j++) operand_init(W[j], w + (size_t)j * N * K, N, K);
-    EpiParams ep;
-    ep.kind = epi_kind;
-    ep.ldo = N;
-    ep.out_f32 = o32;
-    ep.out_f16 = o16;
-    ep.split_stride = (size_t)Mp * N;
-    if (epi_kind == EPI_STORE_F16) { ep.act = ACT_SILU; ep.act_quant = 1; }
-    if (epi_kind == EPI_GLU) ep.ldo = N / 2;
+    ~GemmBench() { cudaFree(a); cudaFree(w); cudaFree(o32); cudaFree(o16); }
+};
+}  // namespace
+
+int nb200_bench_gemm(nb200_model* m, int M, int N, int K, int epi_kind, int bn, int splits, int iters, double* us_per_launch,
+                     int* bn_used, int* splits_used) {
+    NB_TRY
+    if (!m || M <= 0 || N % 64 || K % 64 || iters <= 0 || !us_per_launch) throw Error("bad argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    GemmBench gb(M, N, K, epi_kind);
     gemm_force_config(bn, splits);
     const GemmConfig c = gemm_pick_config(M, N, K, epi_kind == EPI_PARTIAL ? 8 : 1);
     if (bn_used) *bn_used = c.bn;
     if (splits_used) *splits_used = c.splits;
-    for (int i = 0; i < 3; i++) gemm(m->st, A, W[i % n_w], M, ep, false, 8);
+    for (int i = 0; i < 3; i++) gemm(m->st, gb.A, gb.W[i % gb.n_w], M, gb.ep, false, 8);
     CUDA_CHECK(cudaEventRecord(m->tev[0], m->st));
-    for (int i = 0; i < iters; i++) gemm(m->st, A, W[i % n_w], M, ep, false, 8);
+    for (int i = 0; i < iters; i++) gemm(m->st, gb.A, gb.W[i % gb.n_w], M, gb.ep, false, 8);
     CUDA_CHECK(cudaEventRecord(m->tev[1], m->st));
     CUDA_CHECK(cudaEventSynchronize(m->tev[1]));
     gemm_force_config(0, 1);
     float ms = 0;
     CUDA_CHECK(cudaEventElapsedTime(&ms, m->tev[0], m->tev[1]));
     *us_per_launch = ms * 1e3 / iters;
-    cudaFree(a); cudaFree(w); cudaFree(o32); cudaFree(o16);
     return NB200_OK;
+    NB_CATCH(NB200_ERR)
+}
+
+int nb200_trace_gemm(nb200_model* m, int M, int N, int K, int epi_kind, int bn, int splits, int launches, uint64_t* out, int cap_words) {
+    NB_TRY
+    if (!m || M <= 0 || N % 64 || K % 64 || launches <= 0 || !out) throw Error("bad argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    GemmBench gb(M, N, K, epi_kind);
+    gemm_force_config(bn, splits);
+    const GemmConfig c = gemm_pick_config(M, N, K, epi_kind == EPI_PARTIAL ? 8 : 1);
+    const size_t words = (size_t)launches * c.ctas * 8;
+    if ((size_t)cap_words < words) { gemm_force_config(0, 1); throw Error("trace buffer too small"); }
+    unsigned long long* d = dalloc<unsigned long long>(words);
+    CUDA_CHECK(cudaMemset(d, 0, words * 8));
+    for (int i = 0; i < 3; i++) gemm(m->st, gb.A, gb.W[i % gb.n_w], M, gb.ep, false, 8);
+    for (int i = 0; i < launches; i++) {
+        EpiParams ep = gb.ep;
+        ep.trace = d + (size_t)i * c.ctas * 8;
+        gemm(m->st, gb.A, gb.W[i % gb.n_w], M, ep, false, 8);
+    }
+    CUDA_CHECK(cudaStreamSynchronize(m->st));
+    gemm_force_config(0, 1);
+    CUDA_CHECK(cudaMemcpy(out, d, words * 8, cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    return c.ctas;
     NB_CATCH(NB200_ERR)
 }
 

@@ -12,6 +12,11 @@ long long g_launches = 0;
 // ------------------------------------------------------------------------------------------------
 // PTX wrappers (sm_100a)
 // ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)::"memory");
+    return t;
+}
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -110,6 +115,8 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
                                                             const __grid_constant__ CUtensorMap map_w, int M, int num_k,
                                                             EpiParams epi) {
     pdl_launch();
+    unsigned long long* trace = epi.trace ? epi.trace + 8 * (size_t)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) : nullptr;
+    if (trace && threadIdx.x == 0) trace[0] = gtimer();
     using S = TcSmem<BN, STAGES>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
@@ -143,7 +150,9 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (trace && threadIdx.x == 0) trace[1] = gtimer();
     pdl_wait();  // everything above overlapped the previous kernel's tail; its outputs are visible from here on
+    if (trace && threadIdx.x == 0) trace[2] = gtimer();
 
     if (warp == 0) {
         if (lane == 0) {  // ===== TMA producer =====
@@ -165,6 +174,7 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
                 const uint32_t ph = (kb / STAGES) & 1;
                 mbar_wait(full_bar(s), ph);
                 tc_fence_after();
+                if (trace && kb == 0) trace[3] = gtimer();
                 const uint32_t a_addr = base + s * S::STAGE_BYTES;
                 const uint64_t adesc = make_smem_desc(a_addr);
                 const uint64_t bdesc = make_smem_desc(a_addr + S::A_BYTES);
@@ -188,6 +198,7 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
         uint32_t* stg = reinterpret_cast<uint32_t*>(smem) + ew * (32 * 36);
         mbar_wait(accum_bar, 0);
         tc_fence_after();
+        if (trace && threadIdx.x == 64) trace[4] = gtimer();
         const int m = m_tile * TC_BM + lane_base + lane;
         const bool row_ok = m < M;
 #pragma unroll 1
@@ -228,9 +239,11 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
                 }
             }
         }
+        if (trace && threadIdx.x == 64) trace[6] = gtimer();
     }
     tc_fence_before();
     __syncthreads();
+    if (trace && threadIdx.x == 0) trace[5] = gtimer();
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, TMEM_COLS);

@@ -43,6 +43,7 @@ struct EpiParams {
     const int* wpos = nullptr;  // [B] ring index where frame 0 of this chunk goes
     int T = 1;
     size_t split_stride = 0;    // EPI_PARTIAL: elements between the partial outputs of consecutive K splits
+    unsigned long long* trace = nullptr;  // debug: per-CTA phase timestamps (globaltimer ns), 8 words per CTA
 };
 
 // ---- epilogue, stage 1 (registers): bias / activation / re-quantisation / GLU on 32 consecutive accumulator columns

@@ -69,6 +69,8 @@ SYMBOLS = {
     "nb200_debug_matmul": (C.c_int, [C.c_void_p, C.c_char_p, _F32P, C.c_int, _F32P]),
     "nb200_bench_gemm": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double),
                                    C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "nb200_trace_gemm": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                   C.POINTER(C.c_uint64), C.c_int]),
 }
 
 _lib = None
@@ -193,6 +195,14 @@ class Model:
         if lib().nb200_bench_gemm(self._h, M, N, K, epi_kind, bn, splits, iters, C.byref(us), C.byref(bn_used), C.byref(sp_used)) < 0:
             raise NB200Error(_err())
         return {"us": us.value, "bn": bn_used.value, "splits": sp_used.value, "tflops": 2.0 * M * N * K / us.value * 1e-6}
+
+    def trace_gemm(self, M: int, N: int, K: int, epi_kind: int = 0, bn: int = 0, splits: int = 1, launches: int = 6) -> np.ndarray:
+        """Per-CTA phase timestamps [launches, ctas, 8] (ns) of back-to-back launches; see include/nb200.h."""
+        buf = np.zeros(launches * 4096 * 8, np.uint64)
+        n = lib().nb200_trace_gemm(self._h, M, N, K, epi_kind, bn, splits, launches, _ptr(buf, C.POINTER(C.c_uint64)), buf.size)
+        if n < 0:
+            raise NB200Error(_err())
+        return buf[: launches * n * 8].reshape(launches, n, 8)
 
     def debug_matmul(self, tensor_name: str, x: np.ndarray, n_out: int) -> np.ndarray:
         x = np.ascontiguousarray(x, dtype=np.float32)
