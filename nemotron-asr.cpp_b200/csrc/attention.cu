@@ -1,0 +1,398 @@
+// attention.cu — cached relative-position multi-head attention (reference: src/nemo-stream.cpp:463-573, rel-shift
+// :419-461, mask fill :1035-1045, cache write-back :251-266).
+//
+// One CTA per (head, stream). For the chunk's T query frames i and kv = 70 + T keys j:
+//   S[i][j] = ((q_i + u_h) . K_j + (q_i + v_h) . P[70 + i - j]) / sqrt(128) + mask_j,  mask_j = -1e9 for j < 70 - valid
+//   ctx_i   = sum_j softmax_j(S[i][.]) V_j
+// (the reference's pad/reshape/drop "rel-shift" is exactly the index 70 + i - j into the projected position table).
+// Keys 0..69 are the stream's cached rows (fp16 ring in HBM, oldest first), keys 70.. are this chunk's rows, which the
+// QKV GEMM has just written densely to qkv[M][3072]; this kernel also appends them to the ring (the reference copies
+// the last 70 rows of [cache ; new] back into the cache tensors after every layer of every chunk).
+//
+// Data movement is the cost (2 x 84 rows x 256 B per CTA from HBM, the rest from L2), so every operand row is brought
+// into shared memory with 16-byte cp.async issued up front (V in a second group that lands while the scores are
+// computed), and the three small products run on mma.sync.m16n8k16 (fp16 in, fp32 accumulate) fed by ldmatrix from
+// conflict-free padded rows. Softmax is fp32.
+#include <cstdlib>
+
+#include "kernels.cuh"
+
+namespace nb {
+
+namespace {
+
+constexpr int AT_THREADS = 256;
+constexpr int ROWB = 272;      // bytes per staged operand row: 128 halves + 16 B pad (ldmatrix rows hit 8 distinct 16-B bank groups)
+constexpr int K_ROWS = 88, V_ROWS = 96, P_ROWS = 104;  // padded to MMA tiles (kv <= 84 -> 11 n-tiles / 6 k-steps; npos <= 97 -> 13 n-tiles)
+constexpr int S1_LD = 92, S2_LD = 108, PR_LD = 104 /* halves: 208 B rows -> conflict-free ldmatrix */, CX_LD = 132;
+
+struct AttSmem {
+    static constexpr int K_OFF = 0;
+    static constexpr int V_OFF = K_OFF + K_ROWS * ROWB;
+    static constexpr int P_OFF = V_OFF + V_ROWS * ROWB;
+    static constexpr int QU_OFF = P_OFF + P_ROWS * ROWB;
+    static constexpr int QV_OFF = QU_OFF + 16 * ROWB;
+    static constexpr int S1_OFF = QV_OFF + 16 * ROWB;
+    static constexpr int S2_OFF = S1_OFF + 16 * S1_LD * 4;
+    static constexpr int PR_OFF = S2_OFF + 16 * S2_LD * 4;
+    static constexpr int TOTAL = PR_OFF + 16 * PR_LD * 2;
+    // the fp32 context [16][CX_LD] is staged over the K rows (dead after the scores)
+    static_assert(16 * CX_LD * 4 <= K_ROWS * ROWB, "context staging must fit the K area");
+};
+
+__device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_f16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ float group8_max(float v) {
+    v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 1));
+    v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 2));
+    v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 4));
+    return v;
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(AT_THREADS, 2) attention_f16_kernel(AttnArgs a) {
+    // PDL: the cached ring rows and the position table were written by earlier steps / at load, so they are fetched
+    // before griddepcontrol.wait (overlapping the tail of the QKV GEMM); everything that reads qkv comes after it.
+    pdl_launch();
+    extern __shared__ __align__(16) uint8_t smem[];
+    using L = AttSmem;
+    const int h = blockIdx.x, b = blockIdx.y, T = a.T;
+    const int kv = LEFT + T, npos = LEFT + 2 * T - 1;
+    const int kvt = (kv + 7) >> 3, npt = (npos + 7) >> 3, kvs = (kv + 15) >> 4;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const int slot = a.slot[b], wpos = a.wpos[b];
+    int start = wpos - LEFT;  // ring index of cached key 0
+    if (start < 0) start += RING;
+    __half* kring = a.k_ring + (size_t)slot * RING * D_MODEL + h * D_HEAD;
+    __half* vring = a.v_ring + (size_t)slot * RING * D_MODEL + h * D_HEAD;
+    const __half* qkv = a.qkv + (size_t)b * T * (3 * D_MODEL) + h * D_HEAD;  // row i: q at +0, k at +1024, v at +2048
+    const __half* pbase = a.pos + h * D_HEAD;
+    const uint32_t sb = s_u32(smem);
+
+    // ---- stage K (cached, then new), P, then V; 16 B per cp.async ----
+    for (int idx = tid; idx < LEFT * 16; idx += AT_THREADS) {
+        const int j = idx >> 4, c = idx & 15;
+        int pos = start + j;
+        if (pos >= RING) pos -= RING;
+        cp_async16(sb + L::K_OFF + j * ROWB + c * 16, kring + (size_t)pos * D_MODEL + c * 8);
+    }
+    for (int idx = tid; idx < npos * 16; idx += AT_THREADS) {
+        const int j = idx >> 4, c = idx & 15;
+        cp_async16(sb + L::P_OFF + j * ROWB + c * 16, pbase + (size_t)j * D_MODEL + c * 8);
+    }
+    pdl_wait();
+    for (int idx = tid; idx < T * 16; idx += AT_THREADS) {
+        const int i = idx >> 4, c = idx & 15;
+        cp_async16(sb + L::K_OFF + (LEFT + i) * ROWB + c * 16, qkv + (size_t)i * (3 * D_MODEL) + D_MODEL + c * 8);
+    }
+    cp_commit();
+    for (int idx = tid; idx < kv * 16; idx += AT_THREADS) {
+        const int j = idx >> 4, c = idx & 15;
+        const __half* src;
+        if (j < LEFT) {
+            int pos = start + j;
+            if (pos >= RING) pos -= RING;
+            src = vring + (size_t)pos * D_MODEL + c * 8;
+        } else {
+            src = qkv + (size_t)(j - LEFT) * (3 * D_MODEL) + 2 * D_MODEL + c * 8;
+        }
+        cp_async16(sb + L::V_OFF + j * ROWB + c * 16, src);
+    }
+    cp_commit();
+    // zero the tile padding rows (their scores are never read, but 0 * garbage must stay finite in P.V)
+    {
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        for (int idx = tid; idx < (K_ROWS - kv) * 16; idx += AT_THREADS)
+            *reinterpret_cast<uint4*>(smem + L::K_OFF + (kv + (idx >> 4)) * ROWB + (idx & 15) * 16) = z;
+        for (int idx = tid; idx < (V_ROWS - kv) * 16; idx += AT_THREADS)
+            *reinterpret_cast<uint4*>(smem + L::V_OFF + (kv + (idx >> 4)) * ROWB + (idx & 15) * 16) = z;
+        for (int idx = tid; idx < (P_ROWS - npos) * 16; idx += AT_THREADS)
+            *reinterpret_cast<uint4*>(smem + L::P_OFF + (npos + (idx >> 4)) * ROWB + (idx & 15) * 16) = z;
+    }
+    // Q + u, Q + v (fp32 add, one rounding to fp16); rows >= T are zero
+    for (int idx = tid; idx < 16 * 16; idx += AT_THREADS) {
+        const int r = idx >> 4, c = idx & 15;
+        uint4 ou = make_uint4(0, 0, 0, 0), ov = ou;
+        if (r < T) {
+            const uint4 q8 = *reinterpret_cast<const uint4*>(qkv + (size_t)r * (3 * D_MODEL) + c * 8);
+            const __half2* qh = reinterpret_cast<const __half2*>(&q8);
+            const float4 u0 = *reinterpret_cast<const float4*>(a.bias_u + h * D_HEAD + c * 8), u1 = *reinterpret_cast<const float4*>(a.bias_u + h * D_HEAD + c * 8 + 4);
+            const float4 v0 = *reinterpret_cast<const float4*>(a.bias_v + h * D_HEAD + c * 8), v1 = *reinterpret_cast<const float4*>(a.bias_v + h * D_HEAD + c * 8 + 4);
+            const float uu[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+            const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+            __half2 hu[4], hv[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const float2 q2 = __half22float2(qh[e]);
+                hu[e] = __floats2half2_rn(q2.x + uu[2 * e], q2.y + uu[2 * e + 1]);
+                hv[e] = __floats2half2_rn(q2.x + vv[2 * e], q2.y + vv[2 * e + 1]);
+            }
+            ou = *reinterpret_cast<uint4*>(hu);
+            ov = *reinterpret_cast<uint4*>(hv);
+        }
+        *reinterpret_cast<uint4*>(smem + L::QU_OFF + r * ROWB + c * 16) = ou;
+        *reinterpret_cast<uint4*>(smem + L::QV_OFF + r * ROWB + c * 16) = ov;
+    }
+    cp_wait<1>();  // K and P have landed (this thread's copies); the barrier makes everyone's visible
+    __syncthreads();
+
+    // ---- append this chunk's K rows to the ring (V follows after its group lands) ----
+    for (int idx = tid; idx < T * 16; idx += AT_THREADS) {
+        const int i = idx >> 4, c = idx & 15;
+        int pos = wpos + i;
+        if (pos >= RING) pos -= RING;
+        *reinterpret_cast<uint4*>(kring + (size_t)pos * D_MODEL + c * 8) = *reinterpret_cast<const uint4*>(smem + L::K_OFF + (LEFT + i) * ROWB + c * 16);
+    }
+
+    // ---- scores: 8-key tiles of (Q+u) K^T, then 8-position tiles of (Q+v) P^T, round-robin over the warps ----
+    float* S1 = reinterpret_cast<float*>(smem + L::S1_OFF);
+    float* S2 = reinterpret_cast<float*>(smem + L::S2_OFF);
+    {
+        const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_col = (lane >> 4) * 16;  // ldmatrix address roles (A operand)
+        const int b_row = lane & 7, b_col = (lane >> 3) * 16;                              // B operand: 4 k-chunks of one 8-row tile
+        for (int tile = warp; tile < kvt + npt; tile += 8) {
+            const bool is_key = tile < kvt;
+            const int n0 = 8 * (is_key ? tile : tile - kvt);
+            const uint32_t qa = sb + (is_key ? L::QU_OFF : L::QV_OFF) + a_row * ROWB + a_col;
+            const uint32_t kb = sb + (is_key ? L::K_OFF : L::P_OFF) + (n0 + b_row) * ROWB + b_col;
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) {  // 32 features per iteration
+                uint32_t bf[4], a0[4], a1[4];
+                ldsm_x4(bf, kb + ks * 64);
+                ldsm_x4(a0, qa + ks * 64);
+                ldsm_x4(a1, qa + ks * 64 + 32);
+                mma_f16(acc, a0, bf[0], bf[1]);
+                mma_f16(acc, a1, bf[2], bf[3]);
+            }
+            float* S = is_key ? S1 : S2;
+            const int ld = is_key ? S1_LD : S2_LD;
+            *reinterpret_cast<float2*>(S + g * ld + n0 + 2 * t) = make_float2(acc[0], acc[1]);
+            *reinterpret_cast<float2*>(S + (g + 8) * ld + n0 + 2 * t) = make_float2(acc[2], acc[3]);
+        }
+    }
+    __syncthreads();
+
+    // ---- rel-shift by indexing, scale, mask, softmax (fp32): one warp per query row -> fp16 probabilities ----
+    {
+        __half* Pr = reinterpret_cast<__half*>(smem + L::PR_OFF);
+        const int masked = LEFT - a.valid[b];
+        const float scale = 1.0f / sqrtf((float)D_HEAD);
+        for (int i = warp; i < 16; i += 8) {
+            __half* prow_out = Pr + i * PR_LD;
+            if (i >= T) {
+                for (int j = lane; j < PR_LD; j += 32) prow_out[j] = __float2half_rn(0.0f);
+                continue;
+            }
+            const float* row = S1 + i * S1_LD;
+            const float* prow = S2 + i * S2_LD + (LEFT + i + T - 1);
+            float sc[3];
+            float mx = -INFINITY;
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+                const int j = lane + 32 * q;
+                float s = -INFINITY;
+                if (j < kv) {
+                    s = (row[j] + prow[-j]) * scale;
+                    if (j < masked) s += -1e9f;
+                }
+                sc[q] = s;
+                mx = fmaxf(mx, s);
+            }
+            mx = warp_max(mx);
+            float sum = 0.0f;
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+                const int j = lane + 32 * q;
+                sc[q] = (j < kv) ? expf(sc[q] - mx) : 0.0f;
+                sum += sc[q];
+            }
+            sum = warp_sum(sum);
+            const float inv = 1.0f / sum;
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+                const int j = lane + 32 * q;
+                prow_out[j] = __float2half_rn(sc[q] * inv);
+            }
+            if (lane < PR_LD - 96) prow_out[96 + lane] = __float2half_rn(0.0f);
+        }
+    }
+    cp_wait<0>();  // V has landed
+    __syncthreads();
+
+    for (int idx = tid; idx < T * 16; idx += AT_THREADS) {
+        const int i = idx >> 4, c = idx & 15;
+        int pos = wpos + i;
+        if (pos >= RING) pos -= RING;
+        *reinterpret_cast<uint4*>(vring + (size_t)pos * D_MODEL + c * 8) = *reinterpret_cast<const uint4*>(smem + L::V_OFF + (LEFT + i) * ROWB + c * 16);
+    }
+
+    // ---- context: warp w owns features [16w, 16w+16); k runs over the keys in steps of 16 ----
+    float* Cx = reinterpret_cast<float*>(smem + L::K_OFF);
+    {
+        float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+        const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_col = (lane >> 4) * 16;
+        const uint32_t pa = sb + L::PR_OFF + a_row * (PR_LD * 2) + a_col;
+        // V^T fragments via ldmatrix.trans: matrices (keys k0..+7 | k0+8..+15) x (features n0..+7 | n0+8..+15)
+        const uint32_t vb = sb + L::V_OFF + ((lane & 7) + ((lane >> 3) & 1) * 8) * ROWB + (16 * warp + (lane >> 4) * 8) * 2;
+        for (int ks = 0; ks < kvs; ks++) {
+            uint32_t af[4], bf[4];
+            ldsm_x4(af, pa + ks * 32);
+            ldsm_x4_t(bf, vb + ks * 16 * ROWB);
+            mma_f16(acc0, af, bf[0], bf[1]);
+            mma_f16(acc1, af, bf[2], bf[3]);
+        }
+        // K rows are dead (every warp passed the barrier after the scores); stage the fp32 context over them
+        *reinterpret_cast<float2*>(Cx + g * CX_LD + 16 * warp + 2 * t) = make_float2(acc0[0], acc0[1]);
+        *reinterpret_cast<float2*>(Cx + (g + 8) * CX_LD + 16 * warp + 2 * t) = make_float2(acc0[2], acc0[3]);
+        *reinterpret_cast<float2*>(Cx + g * CX_LD + 16 * warp + 8 + 2 * t) = make_float2(acc1[0], acc1[1]);
+        *reinterpret_cast<float2*>(Cx + (g + 8) * CX_LD + 16 * warp + 8 + 2 * t) = make_float2(acc1[2], acc1[3]);
+    }
+    __syncthreads();
+    // ---- fp16 store (+ per-32-feature re-quantisation): a warp covers one row, 8 lanes = one 32-feature block ----
+    for (int idx = tid; idx < T * (D_HEAD / 4); idx += AT_THREADS) {
+        const int i = idx >> 5, d = (idx & 31) * 4;
+        float4 v = *reinterpret_cast<const float4*>(Cx + i * CX_LD + d);
+        if (a.act_quant) {
+            const float amax = group8_max(fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+            v.x = fake_quant(v.x, amax);
+            v.y = fake_quant(v.y, amax);
+            v.z = fake_quant(v.z, amax);
+            v.w = fake_quant(v.w, amax);
+        }
+        const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
+        uint2 u;
+        u.x = *reinterpret_cast<const uint32_t*>(&lo);
+        u.y = *reinterpret_cast<const uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(a.out + ((size_t)(b * T + i)) * D_MODEL + h * D_HEAD + d) = u;
+    }
+}
+
+// ---- fp32 CUDA-core checker (NB200_ATTN_SIMT=1): same inputs and outputs, no tensor cores, no staging tricks ----
+__global__ void __launch_bounds__(256) attention_simt_kernel(AttnArgs a) {
+    pdl_prologue();
+    __shared__ float Sc[MAX_T * (LEFT + MAX_T)];
+    const int h = blockIdx.x, b = blockIdx.y, T = a.T, kv = LEFT + T, tid = threadIdx.x;
+    const int slot = a.slot[b], wpos = a.wpos[b];
+    int start = wpos - LEFT;
+    if (start < 0) start += RING;
+    __half* kring = a.k_ring + (size_t)slot * RING * D_MODEL + h * D_HEAD;
+    __half* vring = a.v_ring + (size_t)slot * RING * D_MODEL + h * D_HEAD;
+    const __half* qkv = a.qkv + (size_t)b * T * (3 * D_MODEL) + h * D_HEAD;
+    for (int idx = tid; idx < T * D_HEAD; idx += 256) {  // append first: keys >= 70 are then read from the ring as well
+        const int i = idx >> 7, d = idx & 127;
+        int pos = wpos + i;
+        if (pos >= RING) pos -= RING;
+        kring[(size_t)pos * D_MODEL + d] = qkv[(size_t)i * 3 * D_MODEL + D_MODEL + d];
+        vring[(size_t)pos * D_MODEL + d] = qkv[(size_t)i * 3 * D_MODEL + 2 * D_MODEL + d];
+    }
+    __syncthreads();
+    const int masked = LEFT - a.valid[b];
+    const float scale = 1.0f / sqrtf((float)D_HEAD);
+    for (int idx = tid; idx < T * kv; idx += 256) {
+        const int i = idx / kv, j = idx - i * kv;
+        int pos = start + j;
+        if (pos >= RING) pos -= RING;
+        const __half* kr = kring + (size_t)pos * D_MODEL;
+        const __half* pr = a.pos + (size_t)(LEFT + i - j + T - 1) * D_MODEL + h * D_HEAD;
+        const __half* q = qkv + (size_t)i * 3 * D_MODEL;
+        float s1 = 0.0f, s2 = 0.0f;
+        for (int d = 0; d < D_HEAD; d++) {
+            const float qf = __half2float(q[d]);
+            const float qu = __half2float(__float2half_rn(qf + a.bias_u[h * D_HEAD + d]));
+            const float qv = __half2float(__float2half_rn(qf + a.bias_v[h * D_HEAD + d]));
+            s1 = fmaf(qu, __half2float(kr[d]), s1);
+            s2 = fmaf(qv, __half2float(pr[d]), s2);
+        }
+        float s = (s1 + s2) * scale;
+        if (j < masked) s += -1e9f;
+        Sc[idx] = s;
+    }
+    __syncthreads();
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int i = warp; i < T; i += 8) {
+        float* row = Sc + i * kv;
+        float mx = -INFINITY;
+        for (int j = lane; j < kv; j += 32) mx = fmaxf(mx, row[j]);
+        mx = warp_max(mx);
+        float sum = 0.0f;
+        for (int j = lane; j < kv; j += 32) {
+            const float e = expf(row[j] - mx);
+            row[j] = e;
+            sum += e;
+        }
+        sum = warp_sum(sum);
+        const float inv = 1.0f / sum;
+        for (int j = lane; j < kv; j += 32) row[j] = __half2float(__float2half_rn(row[j] * inv));
+    }
+    __syncthreads();
+    for (int idx = tid; idx < T * (D_HEAD / 4); idx += 256) {
+        const int i = idx >> 5, d = (idx & 31) * 4;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < kv; j++) {
+            int pos = start + j;
+            if (pos >= RING) pos -= RING;
+            const __half* vr = vring + (size_t)pos * D_MODEL + d;
+            const float p = Sc[i * kv + j];
+            acc.x = fmaf(p, __half2float(vr[0]), acc.x);
+            acc.y = fmaf(p, __half2float(vr[1]), acc.y);
+            acc.z = fmaf(p, __half2float(vr[2]), acc.z);
+            acc.w = fmaf(p, __half2float(vr[3]), acc.w);
+        }
+        if (a.act_quant) {
+            const float amax = group8_max(fmaxf(fmaxf(fabsf(acc.x), fabsf(acc.y)), fmaxf(fabsf(acc.z), fabsf(acc.w))));
+            acc.x = fake_quant(acc.x, amax);
+            acc.y = fake_quant(acc.y, amax);
+            acc.z = fake_quant(acc.z, amax);
+            acc.w = fake_quant(acc.w, amax);
+        }
+        const __half2 lo = __floats2half2_rn(acc.x, acc.y), hi = __floats2half2_rn(acc.z, acc.w);
+        uint2 u;
+        u.x = *reinterpret_cast<const uint32_t*>(&lo);
+        u.y = *reinterpret_cast<const uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(a.out + ((size_t)(b * T + i)) * D_MODEL + h * D_HEAD + d) = u;
+    }
+}
+
+void launch_attention(cudaStream_t st, const AttnArgs& a) {
+    static const bool use_simt = getenv("NB200_ATTN_SIMT") != nullptr;
+    if (a.T > MAX_T) throw Error("attention: more than 14 frames per chunk");
+    const double kv = LEFT + a.T;
+    const double flops = 6.0 * a.B * a.T * kv * D_MODEL;
+    // algorithmic bytes: cached K+V rows read, this chunk's q/k/v read, K/V rows appended, context written, positions once
+    const double bytes = (double)a.B * (2.0 * LEFT * D_MODEL * 2 + (double)a.T * D_MODEL * (6 + 4 + 2)) + (LEFT + 2.0 * a.T - 1) * D_MODEL * 2;
+    if (use_simt) {
+        ProfScope ps(st, "attention_simt", flops, bytes);
+        launch_k(attention_simt_kernel, dim3(dim3(N_HEADS, a.B)), dim3(256), 0, st, a);
+        NB_KERNEL_CHECK();
+        return;
+    }
+    static bool configured = false;
+    if (!configured) {
+        CUDA_CHECK(cudaFuncSetAttribute(attention_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttSmem::TOTAL));
+        configured = true;
+    }
+    ProfScope ps(st, "attention_f16", flops, bytes);
+    launch_k(attention_f16_kernel, dim3(dim3(N_HEADS, a.B)), dim3(AT_THREADS), (size_t)AttSmem::TOTAL, st, a);
+    NB_KERNEL_CHECK();
+}
+
+}  // namespace nb

@@ -90,321 +90,6 @@ void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b
     NB_KERNEL_CHECK();
 }
 
-// ---- cached relative-position attention -----------------------------------------------------------
-// One CTA per (head, stream). S[i][j] = ((q_i+u).K_j + (q_i+v).P[70+i-j]) / sqrt(128) + mask_j, softmax over j,
-// ctx_i = sum_j A[i][j] V_j  (src/nemo-stream.cpp:463-573; the pad/reshape rel-shift :419-461 is the index 70+i-j).
-// K_j/V_j for j < 70 are the ring-cache rows before this chunk, j >= 70 this chunk's rows (already written by the
-// QKV GEMM epilogue). mask_j = -1e9 for j < 70 - valid (:1035-1045).
-constexpr int ATT_LD = D_HEAD + 1;  // padded row: conflict-free when a warp reads one column of 32 rows
-
-__global__ void __launch_bounds__(256) attention_kernel(AttnArgs a) {
-    pdl_prologue();
-    extern __shared__ float sm[];
-    const int h = blockIdx.x, b = blockIdx.y, T = a.T;
-    const int kv = LEFT + T, npos = LEFT + 2 * T - 1;
-    float* Ks = sm;                       // [kv][ATT_LD]   (re-used for V)
-    float* Ps = Ks + kv * ATT_LD;         // [npos][ATT_LD]
-    float* Qu = Ps + npos * ATT_LD;       // [T][128]
-    float* Qv = Qu + T * D_HEAD;          // [T][128]
-    float* Sc = Qv + T * D_HEAD;          // [T][kv]
-    const int t = threadIdx.x;
-    const int slot = a.slot[b];
-    int start = a.wpos[b] - LEFT;         // ring index of logical key 0
-    if (start < 0) start += RING;
-    const float* kbase = a.k_ring + (size_t)slot * RING * D_MODEL + h * D_HEAD;
-    const float* vbase = a.v_ring + (size_t)slot * RING * D_MODEL + h * D_HEAD;
-    // load K rows, P rows, q (+u, +v)
-    for (int i = t; i < kv * (D_HEAD / 4); i += 256) {
-        int j = i >> 5, d = (i & 31) * 4;
-        int pos = start + j;
-        if (pos >= RING) pos -= RING;
-        float4 v = *reinterpret_cast<const float4*>(kbase + (size_t)pos * D_MODEL + d);
-        float* dst = Ks + j * ATT_LD + d;
-        dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
-    }
-    for (int i = t; i < npos * (D_HEAD / 4); i += 256) {
-        int j = i >> 5, d = (i & 31) * 4;
-        float4 v = *reinterpret_cast<const float4*>(a.pos + (size_t)j * D_MODEL + h * D_HEAD + d);
-        float* dst = Ps + j * ATT_LD + d;
-        dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
-    }
-    for (int i = t; i < T * D_HEAD; i += 256) {
-        int r = i >> 7, d = i & 127;
-        float qv = a.q[((size_t)(b * T + r)) * D_MODEL + h * D_HEAD + d];
-        Qu[i] = qv + a.bias_u[h * D_HEAD + d];
-        Qv[i] = qv + a.bias_v[h * D_HEAD + d];
-    }
-    __syncthreads();
-    const int masked = LEFT - a.valid[b];
-    const float scale = 1.0f / sqrtf((float)D_HEAD);
-    for (int idx = t; idx < T * kv; idx += 256) {
-        const int i = idx / kv, j = idx - i * kv;
-        const float* kr = Ks + j * ATT_LD;
-        const float* pr = Ps + (LEFT + i - j + T - 1) * ATT_LD;
-        const float* qu = Qu + i * D_HEAD;
-        const float* qv = Qv + i * D_HEAD;
-        float s1 = 0.0f, s2 = 0.0f;
-#pragma unroll 8
-        for (int d = 0; d < D_HEAD; d++) {
-            s1 = fmaf(qu[d], kr[d], s1);
-            s2 = fmaf(qv[d], pr[d], s2);
-        }
-        float s = (s1 + s2) * scale;
-        if (j < masked) s += -1e9f;
-        Sc[idx] = s;
-    }
-    __syncthreads();
-    // V over K's storage
-    for (int i = t; i < kv * (D_HEAD / 4); i += 256) {
-        int j = i >> 5, d = (i & 31) * 4;
-        int pos = start + j;
-        if (pos >= RING) pos -= RING;
-        float4 v = *reinterpret_cast<const float4*>(vbase + (size_t)pos * D_MODEL + d);
-        float* dst = Ks + j * ATT_LD + d;
-        dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
-    }
-    // softmax per query row: one warp per row
-    const int warp = t >> 5, lane = t & 31;
-    for (int i = warp; i < T; i += 8) {
-        float* row = Sc + i * kv;
-        float mx = -INFINITY;
-        for (int j = lane; j < kv; j += 32) mx = fmaxf(mx, row[j]);
-        mx = warp_max(mx);
-        float sum = 0.0f;
-        for (int j = lane; j < kv; j += 32) {
-            float e = expf(row[j] - mx);
-            row[j] = e;
-            sum += e;
-        }
-        sum = warp_sum(sum);
-        const float inv = 1.0f / sum;
-        for (int j = lane; j < kv; j += 32) row[j] *= inv;
-    }
-    __syncthreads();
-    // ctx[i][d]: each thread 4 consecutive d of one row i
-    for (int idx = t; idx < T * (D_HEAD / 4); idx += 256) {
-        const int i = idx >> 5, d = (idx & 31) * 4;
-        const float* row = Sc + i * kv;
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int j = 0; j < kv; j++) {
-            const float p = row[j];
-            const float* vr = Ks + j * ATT_LD + d;
-            acc.x = fmaf(p, vr[0], acc.x);
-            acc.y = fmaf(p, vr[1], acc.y);
-            acc.z = fmaf(p, vr[2], acc.z);
-            acc.w = fmaf(p, vr[3], acc.w);
-        }
-        // 8 consecutive lanes hold 32 consecutive features of the same row -> fake-quant group
-        store_f16x4(a.out + ((size_t)(b * T + i)) * D_MODEL + h * D_HEAD + d, acc, a.act_quant);
-    }
-}
-
-static size_t attn_smem_bytes(int T) {
-    const int kv = LEFT + T, npos = LEFT + 2 * T - 1;
-    return sizeof(float) * ((size_t)kv * ATT_LD + (size_t)npos * ATT_LD + 2 * T * D_HEAD + (size_t)T * kv);
-}
-
-// ---- tensor-core version (the one the step uses) ------------------------------------------------------------
-// Same math, restructured as three small matrix products per (stream, head) on mma.sync.m16n8k8 with 3xTF32 operand
-// splitting (hi + lo, three MMAs: fp32-level accuracy):  C1 = (Q+u) K^T  [16 x kv],  C2 = (Q+v) P^T  [16 x npos],
-// ctx = softmax(...) V  [16 x 128].  T <= 14 query rows fit one 16-row MMA tile. K, V and P rows are read straight
-// from global memory as MMA B-fragments (each element is used once per CTA, so staging them in shared memory buys
-// nothing): the k-slot <-> feature mapping is permuted so that every lane loads 16 contiguous bytes (K, P) or 8
-// (V) and every 32-byte sector fetched is fully used. Shared memory holds only Q(+u,+v), the scores and the context
-// (39 KB -> 5 CTAs per SM instead of 1), so the K/V streams of different CTAs overlap.
-constexpr int QS = 144;   // Q row stride (floats): 128-bit A-fragment loads are conflict-free per quarter-warp
-constexpr int S1S = 92;   // scores/probabilities row stride (>= 88)
-constexpr int S2S = 108;  // positional scores row stride (>= 104)
-constexpr int CXS = 132;
-
-__device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
-    const float r = x - __uint_as_float(hi);
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(lo) : "f"(r));
-}
-__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t (&a)[4], const uint32_t (&b)[2]) {
-    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
-}
-// c += A(16x8) * B(8x8) with fp32 inputs split into tf32 hi/lo: a_hi*b_hi + a_lo*b_hi + a_hi*b_lo
-__device__ __forceinline__ void mma_3xtf32(float (&c)[4], const float (&a)[4], const float (&b)[2]) {
-    uint32_t ah[4], al[4], bh[2], bl[2];
-#pragma unroll
-    for (int i = 0; i < 4; i++) tf32_split(a[i], ah[i], al[i]);
-#pragma unroll
-    for (int i = 0; i < 2; i++) tf32_split(b[i], bh[i], bl[i]);
-    mma_tf32(c, al, bh);
-    mma_tf32(c, ah, bl);
-    mma_tf32(c, ah, bh);
-}
-
-__global__ void __launch_bounds__(256) attention_tc_kernel(AttnArgs a) {
-    pdl_prologue();
-    __shared__ __align__(16) float Qu[16 * QS];
-    __shared__ __align__(16) float Qv[16 * QS];
-    __shared__ __align__(16) float S1[16 * S1S];
-    __shared__ __align__(16) float S2[16 * S2S];
-    __shared__ __align__(16) float Cx[16 * CXS];
-    const int h = blockIdx.x, b = blockIdx.y, T = a.T;
-    const int kv = LEFT + T, npos = LEFT + 2 * T - 1;
-    const int kvt = (kv + 7) >> 3, npt = (npos + 7) >> 3;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
-    const int slot = a.slot[b];
-    int start = a.wpos[b] - LEFT;  // ring index of logical key 0
-    if (start < 0) start += RING;
-    const float* kbase = a.k_ring + (size_t)slot * RING * D_MODEL + h * D_HEAD;
-    const float* vbase = a.v_ring + (size_t)slot * RING * D_MODEL + h * D_HEAD;
-    const float* pbase = a.pos + h * D_HEAD;
-
-    for (int idx = tid; idx < 16 * (D_HEAD / 4); idx += 256) {
-        const int r = idx >> 5, d = (idx & 31) * 4;
-        float4 qu = make_float4(0.f, 0.f, 0.f, 0.f), qv = qu;
-        if (r < T) {
-            const float4 q = *reinterpret_cast<const float4*>(a.q + ((size_t)(b * T + r)) * D_MODEL + h * D_HEAD + d);
-            const float4 u = *reinterpret_cast<const float4*>(a.bias_u + h * D_HEAD + d);
-            const float4 v = *reinterpret_cast<const float4*>(a.bias_v + h * D_HEAD + d);
-            qu = make_float4(q.x + u.x, q.y + u.y, q.z + u.z, q.w + u.w);
-            qv = make_float4(q.x + v.x, q.y + v.y, q.z + v.z, q.w + v.w);
-        }
-        *reinterpret_cast<float4*>(Qu + r * QS + d) = qu;
-        *reinterpret_cast<float4*>(Qv + r * QS + d) = qv;
-    }
-    __syncthreads();
-
-    // ---- scores: 8-column tiles of C1 (keys) then C2 (relative positions), round-robin over the warps ----
-    for (int tile = warp; tile < kvt + npt; tile += 8) {
-        const bool is_key = tile < kvt;
-        const int n0 = 8 * (is_key ? tile : tile - kvt);
-        const int lim = is_key ? kv : npos;
-        const int r = min(n0 + g, lim - 1);  // padding columns re-read the last valid row; their scores are never used
-        const float* src;
-        if (is_key) {
-            int pos = start + r;
-            if (pos >= RING) pos -= RING;
-            src = kbase + (size_t)pos * D_MODEL;
-        } else {
-            src = pbase + (size_t)r * D_MODEL;
-        }
-        const float* Qs = is_key ? Qu : Qv;
-        float acc[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 4
-        for (int kk = 0; kk < 8; kk++) {
-            const float4 bv = __ldg(reinterpret_cast<const float4*>(src + 16 * kk + 4 * t));
-            const float4 qa = *reinterpret_cast<const float4*>(Qs + g * QS + 16 * kk + 4 * t);
-            const float4 qb = *reinterpret_cast<const float4*>(Qs + (g + 8) * QS + 16 * kk + 4 * t);
-            {   // k-slot t <-> feature 16kk+4t, k-slot t+4 <-> feature 16kk+4t+1
-                const float af[4] = {qa.x, qb.x, qa.y, qb.y};
-                const float bf[2] = {bv.x, bv.y};
-                mma_3xtf32(acc, af, bf);
-            }
-            {   // features 16kk+4t+2 and +3
-                const float af[4] = {qa.z, qb.z, qa.w, qb.w};
-                const float bf[2] = {bv.z, bv.w};
-                mma_3xtf32(acc, af, bf);
-            }
-        }
-        float* S = is_key ? S1 : S2;
-        const int ld = is_key ? S1S : S2S;
-        *reinterpret_cast<float2*>(S + g * ld + n0 + 2 * t) = make_float2(acc[0], acc[1]);
-        *reinterpret_cast<float2*>(S + (g + 8) * ld + n0 + 2 * t) = make_float2(acc[2], acc[3]);
-    }
-    __syncthreads();
-
-    // ---- rel-shift by indexing, scale, mask, softmax: one warp per query row; probabilities overwrite S1 ----
-    {
-        const int masked = LEFT - a.valid[b];
-        const float scale = 1.0f / sqrtf((float)D_HEAD);
-        for (int i = warp; i < 16; i += 8) {
-            float* row = S1 + i * S1S;
-            if (i >= T) {
-                for (int j = lane; j < kvt * 8; j += 32) row[j] = 0.0f;
-                continue;
-            }
-            const float* prow = S2 + i * S2S + (LEFT + i + T - 1);
-            float sc[3];
-            float mx = -INFINITY;
-#pragma unroll
-            for (int q = 0; q < 3; q++) {
-                const int j = lane + 32 * q;
-                float s = -INFINITY;
-                if (j < kv) {
-                    s = (row[j] + prow[-j]) * scale;
-                    if (j < masked) s += -1e9f;
-                }
-                sc[q] = s;
-                mx = fmaxf(mx, s);
-            }
-            mx = warp_max(mx);
-            float sum = 0.0f;
-#pragma unroll
-            for (int q = 0; q < 3; q++) {
-                const int j = lane + 32 * q;
-                sc[q] = (j < kv) ? expf(sc[q] - mx) : 0.0f;
-                sum += sc[q];
-            }
-            sum = warp_sum(sum);
-            const float inv = 1.0f / sum;
-#pragma unroll
-            for (int q = 0; q < 3; q++) {
-                const int j = lane + 32 * q;
-                if (j < kvt * 8) row[j] = sc[q] * inv;
-            }
-        }
-    }
-    __syncthreads();
-
-    // ---- context: warp w owns features [16w, 16w+16) as two 8-column tiles (feature = 16w + 2n + q) ----
-    {
-        float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
-        const float* vcol = vbase + 16 * warp + 2 * g;
-        for (int ks = 0; ks < kvt; ks++) {
-            const int j0 = 8 * ks + t, j1 = j0 + 4;
-            int p0 = start + min(j0, kv - 1), p1 = start + min(j1, kv - 1);  // padded keys have probability 0
-            if (p0 >= RING) p0 -= RING;
-            if (p1 >= RING) p1 -= RING;
-            const float2 v0 = __ldg(reinterpret_cast<const float2*>(vcol + (size_t)p0 * D_MODEL));
-            const float2 v1 = __ldg(reinterpret_cast<const float2*>(vcol + (size_t)p1 * D_MODEL));
-            const float af[4] = {S1[g * S1S + j0], S1[(g + 8) * S1S + j0], S1[g * S1S + j1], S1[(g + 8) * S1S + j1]};
-            const float b0[2] = {v0.x, v1.x};
-            const float b1[2] = {v0.y, v1.y};
-            mma_3xtf32(acc0, af, b0);
-            mma_3xtf32(acc1, af, b1);
-        }
-        *reinterpret_cast<float4*>(Cx + g * CXS + 16 * warp + 4 * t) = make_float4(acc0[0], acc1[0], acc0[1], acc1[1]);
-        *reinterpret_cast<float4*>(Cx + (g + 8) * CXS + 16 * warp + 4 * t) = make_float4(acc0[2], acc1[2], acc0[3], acc1[3]);
-    }
-    __syncthreads();
-    // ---- fp16 store (+ per-32-feature re-quantisation): a warp covers one row, 8 lanes = one 32-feature block ----
-    for (int idx = tid; idx < T * (D_HEAD / 4); idx += 256) {
-        const int i = idx >> 5, d = (idx & 31) * 4;
-        const float4 v = *reinterpret_cast<const float4*>(Cx + i * CXS + d);
-        store_f16x4(a.out + ((size_t)(b * T + i)) * D_MODEL + h * D_HEAD + d, v, a.act_quant);
-    }
-}
-
-void launch_attention(cudaStream_t st, const AttnArgs& a) {
-    static const bool use_simt = getenv("NB200_ATTN_SIMT") != nullptr;
-    const double kv = LEFT + a.T;
-    const double flops = 6.0 * a.B * a.T * kv * D_MODEL;
-    const double bytes = (double)a.B * (2.0 * kv * D_MODEL * 4 + (double)a.T * D_MODEL * 6) + (LEFT + 2.0 * a.T - 1) * D_MODEL * 4;
-    if (use_simt) {
-        static bool configured = false;
-        if (!configured) {
-            CUDA_CHECK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_smem_bytes(MAX_T)));
-            configured = true;
-        }
-        ProfScope ps(st, "attention_simt", flops, bytes);
-        launch_k(attention_kernel, dim3(dim3(N_HEADS, a.B)), dim3(256), attn_smem_bytes(a.T), st, a);
-        NB_KERNEL_CHECK();
-        return;
-    }
-    if (a.T > 14) throw Error("attention: more than 14 frames per chunk");
-    ProfScope ps(st, "attention_tc", flops, bytes);
-    launch_k(attention_tc_kernel, dim3(dim3(N_HEADS, a.B)), dim3(256), 0, st, a);
-    NB_KERNEL_CHECK();
-}
-
 // ---- cached causal depthwise conv (9 taps) + LayerNorm + SiLU --------------------------------------
 // One CTA per (frame t, stream): d[t][ch] = sum_k G[t+k][ch] * w[k][ch], G = [cache(8) ; g(T)] (src/nemo-stream.cpp:336-412),
 // products accumulated in tap order like the reference's mul/add chain (:370-388); then LN (conv.batch_norm), SiLU (:671-674).

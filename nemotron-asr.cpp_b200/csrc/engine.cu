@@ -41,7 +41,7 @@ struct LayerW {
 
 struct ModeCtx {
     Mode mode;
-    float* pos_tab = nullptr;  // [L][npos][1024] linear_pos(PE(p)), p = -(T-1) .. 70+T-1
+    __half* pos_tab = nullptr;  // [L][npos][1024] fp16 linear_pos(PE(p)), p = -(T-1) .. 70+T-1
     explicit ModeCtx(int rc) : mode(rc) {}
 };
 
@@ -117,7 +117,8 @@ struct nb200_model {
     };
     std::map<std::string, NamedMatrix> by_name;
     // per-slot state
-    float *k_ring = nullptr, *v_ring = nullptr, *conv_cache = nullptr;  // [L][slots][...]
+    __half *k_ring = nullptr, *v_ring = nullptr;  // [L][slots][RING][1024] fp16
+    float* conv_cache = nullptr;                  // [L][slots][8][1024]
     float* mel_overlap = nullptr;                                      // [slots][9][128]
     DecodeState dstate{};
     std::vector<int> free_slots;
@@ -127,8 +128,8 @@ struct nb200_model {
     std::map<long long, GraphExec> enc_graphs, dec_graphs;
     // workspace (capacity: cap_B streams x MAX_T frames)
     int cap_B = 0;
-    float *ws_mel = nullptr, *ws_a3 = nullptr, *ws_x = nullptr, *ws_q = nullptr, *ws_g = nullptr, *ws_e = nullptr;
-    __half *ws_a2h = nullptr, *ws_a5h = nullptr, *ws_a6h = nullptr, *ws_a16 = nullptr, *ws_h16 = nullptr, *ws_pos16 = nullptr;
+    float *ws_mel = nullptr, *ws_a3 = nullptr, *ws_x = nullptr, *ws_g = nullptr, *ws_e = nullptr;
+    __half *ws_a2h = nullptr, *ws_a5h = nullptr, *ws_a6h = nullptr, *ws_a16 = nullptr, *ws_h16 = nullptr, *ws_pos16 = nullptr, *ws_qkv16 = nullptr;
     float* ws_posf = nullptr;
     float* ws_part = nullptr;      // split-K partial outputs of the residual GEMMs: [splits][part_rows][1024]
     size_t part_rows = 0;
@@ -387,8 +388,8 @@ constexpr int META_ROWS = 8;  // int arrays per batch: slot, wpos, valid, nvalid
 
 void alloc_state(nb200_model* m) {
     const size_t S = (size_t)m->max_streams, L = (size_t)m->n_layers;
-    m->k_ring = m->alloc<float>(L * S * RING * D_MODEL);
-    m->v_ring = m->alloc<float>(L * S * RING * D_MODEL);
+    m->k_ring = m->alloc<__half>(L * S * RING * D_MODEL);
+    m->v_ring = m->alloc<__half>(L * S * RING * D_MODEL);
     m->conv_cache = m->alloc<float>(L * S * CONV_CACHE * D_MODEL);
     m->mel_overlap = m->alloc<float>(S * MEL_OVERLAP * N_MELS);
     m->dstate.h = m->alloc<float>(S * 2 * DEC);
@@ -408,7 +409,7 @@ void alloc_state(nb200_model* m) {
     m->ws_a3 = m->alloc<float>((size_t)B * big.t2 * SUB_F2 * SUB_CH);
     m->ws_a5h = m->alloc<__half>((rows_pad + 128) * SUB_F3 * SUB_CH);
     m->ws_x = m->alloc<float>(rows_pad * D_MODEL);
-    m->ws_q = m->alloc<float>(rows_pad * D_MODEL);
+    m->ws_qkv16 = m->alloc<__half>(rows_pad * 3 * D_MODEL);
     m->ws_g = m->alloc<float>(rows_pad * D_MODEL);
     m->ws_e = m->alloc<float>(rows_pad * JOINT);
     m->ws_a16 = m->alloc<__half>(rows_pad * D_MODEL);
@@ -458,13 +459,13 @@ ModeCtx* get_mode(nb200_model* m, int rc) {
     if (it != m->modes.end()) return it->second.get();
     auto ctx = std::make_unique<ModeCtx>(rc);
     const Mode& md = ctx->mode;
-    ctx->pos_tab = m->alloc<float>((size_t)m->n_layers * md.npos * D_MODEL);
+    ctx->pos_tab = m->alloc<__half>((size_t)m->n_layers * md.npos * D_MODEL);
     launch_pos_emb(m->st, m->ws_posf, -(md.T - 1), md.npos);
     launch_cast_f16(m->st, m->ws_posf, m->ws_pos16, m->act_quant ? 1 : 0, md.npos, D_MODEL);
     for (int l = 0; l < m->n_layers; l++) {
         EpiParams ep;
-        ep.kind = EPI_STORE;
-        ep.out_f32 = ctx->pos_tab + (size_t)l * md.npos * D_MODEL;
+        ep.kind = EPI_STORE_F16;
+        ep.out_f16 = ctx->pos_tab + (size_t)l * md.npos * D_MODEL;
         ep.ldo = D_MODEL;
         gemm(m->st, m->op_pos16, m->layers[l].wpos.op, md.npos, ep, m->simt);
     }
@@ -500,8 +501,8 @@ DecodeBatch decode_batch(nb200_model* m, int B, int T) {
 void reset_slot(nb200_model* m, int slot) {
     const size_t S = (size_t)m->max_streams;
     for (int l = 0; l < m->n_layers; l++) {
-        CUDA_CHECK(cudaMemsetAsync(m->k_ring + ((size_t)l * S + slot) * RING * D_MODEL, 0, sizeof(float) * RING * D_MODEL, m->st));
-        CUDA_CHECK(cudaMemsetAsync(m->v_ring + ((size_t)l * S + slot) * RING * D_MODEL, 0, sizeof(float) * RING * D_MODEL, m->st));
+        CUDA_CHECK(cudaMemsetAsync(m->k_ring + ((size_t)l * S + slot) * RING * D_MODEL, 0, sizeof(__half) * RING * D_MODEL, m->st));
+        CUDA_CHECK(cudaMemsetAsync(m->v_ring + ((size_t)l * S + slot) * RING * D_MODEL, 0, sizeof(__half) * RING * D_MODEL, m->st));
         CUDA_CHECK(cudaMemsetAsync(m->conv_cache + ((size_t)l * S + slot) * CONV_CACHE * D_MODEL, 0, sizeof(float) * CONV_CACHE * D_MODEL, m->st));
     }
     CUDA_CHECK(cudaMemsetAsync(m->mel_overlap + (size_t)slot * MEL_OVERLAP * N_MELS, 0, sizeof(float) * MEL_OVERLAP * N_MELS, m->st));
@@ -657,13 +658,13 @@ void enqueue_encoder(const StepCtx& c) {
         rin.alpha = 0.5f;  // x += 0.5 * FFN1
         // self-attention
         launch_layernorm(st, m->ws_x, L.ln_att_g, L.ln_att_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin);
-        float* kr = m->k_ring + (size_t)l * S * RING * D_MODEL;
-        float* vr = m->v_ring + (size_t)l * S * RING * D_MODEL;
-        EpiParams qkv;
-        qkv.kind = EPI_QKV; qkv.out_f32 = m->ws_q; qkv.k_ring = kr; qkv.v_ring = vr; qkv.slot = d_slot; qkv.wpos = d_wpos; qkv.T = T;
+        __half* kr = m->k_ring + (size_t)l * S * RING * D_MODEL;
+        __half* vr = m->v_ring + (size_t)l * S * RING * D_MODEL;
+        EpiParams qkv;  // q | k | v of the chunk's frames, dense fp16; the attention kernel appends k, v to the stream rings
+        qkv.kind = EPI_STORE_F16; qkv.out_f16 = m->ws_qkv16; qkv.ldo = 3 * D_MODEL;
         gemm(st, m->op_a16, L.wqkv.op, M, qkv, simt);
         AttnArgs at{};
-        at.q = m->ws_q; at.k_ring = kr; at.v_ring = vr; at.pos = mc->pos_tab + (size_t)l * md.npos * D_MODEL;
+        at.qkv = m->ws_qkv16; at.k_ring = kr; at.v_ring = vr; at.pos = mc->pos_tab + (size_t)l * md.npos * D_MODEL;
         at.bias_u = L.pos_u; at.bias_v = L.pos_v; at.slot = d_slot; at.wpos = d_wpos; at.valid = d_valid;
         at.out = m->ws_a16; at.B = B; at.T = T; at.act_quant = aq;
         launch_attention(st, at);

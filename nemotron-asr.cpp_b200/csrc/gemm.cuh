@@ -8,9 +8,8 @@
 //
 // Epilogues (what the reference does as separate ggml nodes, src/nemo-stream.cpp:593-690):
 //   EPI_STORE      out_f32 = act(acc + bias)                      (pre_encode pw3, pre_encode.out, joint.enc)
-//   EPI_STORE_F16  out_f16 = fq(act(acc + bias))                  (FFN linear1 + SiLU, pre_encode pw6 + ReLU)
+//   EPI_STORE_F16  out_f16 = fq(act(acc + bias))                  (FFN linear1 + SiLU, pre_encode pw6 + ReLU, q|k|v, linear_pos)
 //   EPI_RESID      x += alpha * acc                               (FFN linear2 *0.5, attention out, pointwise_conv2)
-//   EPI_QKV        q -> fp32 buffer, k/v -> the streams' K/V ring caches
 //   EPI_GLU        out_f32[j] = a_j * sigmoid(b_j) with (a_j,b_j) interleaved as columns (2j,2j+1) at load
 //   EPI_PARTIAL    split-K: CTA z of gridDim.z sums its K range and stores the raw partial tile to
 //                  out_f32 + z*split_stride; the LayerNorm that follows every residual GEMM adds alpha * sum_z partial_z
@@ -24,7 +23,7 @@
 
 namespace nb {
 
-enum EpiKind : int { EPI_STORE = 0, EPI_STORE_F16 = 1, EPI_RESID = 2, EPI_QKV = 3, EPI_GLU = 4, EPI_PARTIAL = 5 };
+enum EpiKind : int { EPI_STORE = 0, EPI_STORE_F16 = 1, EPI_RESID = 2, EPI_GLU = 4, EPI_PARTIAL = 5 };
 enum ActKind : int { ACT_NONE = 0, ACT_RELU = 1, ACT_SILU = 2 };
 
 struct EpiParams {
@@ -36,12 +35,6 @@ struct EpiParams {
     float* out_f32 = nullptr;   // EPI_STORE / EPI_RESID / EPI_GLU / EPI_QKV(q)
     __half* out_f16 = nullptr;  // EPI_STORE_F16
     int ldo = 0;                // leading dimension of the output (elements)
-    // EPI_QKV: row m = b*T + i belongs to batch item b; its stream slot and ring write position
-    float* k_ring = nullptr;    // this layer's [slots][RING][1024]
-    float* v_ring = nullptr;
-    const int* slot = nullptr;  // [B]
-    const int* wpos = nullptr;  // [B] ring index where frame 0 of this chunk goes
-    int T = 1;
     size_t split_stride = 0;    // EPI_PARTIAL: elements between the partial outputs of consecutive K splits
     unsigned long long* trace = nullptr;  // debug: per-CTA phase timestamps (globaltimer ns), 8 words per CTA
 };
@@ -89,17 +82,7 @@ __device__ __forceinline__ int epilogue_transform(const EpiParams& p, int m, int
     }
 #pragma unroll
     for (int j = 0; j < 32; j++) w[j] = __float_as_uint(acc[j]);
-    if (p.kind == EPI_QKV && n0 >= D_MODEL) {
-        const int b = m / p.T, i = m - b * p.T;
-        int pos = p.wpos[b] + i;
-        if (pos >= RING) pos -= RING;
-        float* ring = (n0 < 2 * D_MODEL) ? p.k_ring : p.v_ring;
-        dst = reinterpret_cast<char*>(ring + ((size_t)p.slot[b] * RING + pos) * D_MODEL + (n0 & (D_MODEL - 1)));
-    } else if (p.kind == EPI_QKV) {
-        dst = reinterpret_cast<char*>(p.out_f32 + (size_t)m * D_MODEL + n0);
-    } else {
-        dst = reinterpret_cast<char*>(p.out_f32 + (size_t)m * p.ldo + n0);
-    }
+    dst = reinterpret_cast<char*>(p.out_f32 + (size_t)m * p.ldo + n0);
     return 32;
 }
 

@@ -55,10 +55,10 @@ void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b
                       const float* b2, __half* out_f16, int act_quant, int M, const ResidualIn& rin = ResidualIn());
 
 struct AttnArgs {
-    const float* q;        // [M][1024] fp32 (row m = b*T + i)
-    const float* k_ring;   // this layer's [slots][RING][1024]
-    const float* v_ring;
-    const float* pos;      // this layer's projected positions [npos][1024], row p + (T-1), p in [-(T-1), 70+T-1]
+    const __half* qkv;     // [M][3072] fp16: q | k | v of this chunk's frames (row m = b*T + i), written by the QKV GEMM
+    __half* k_ring;        // this layer's [slots][RING][1024] fp16: the last 70 key rows of every stream; this chunk's rows are appended
+    __half* v_ring;
+    const __half* pos;     // this layer's projected positions [npos][1024] fp16, row p + (T-1), p in [-(T-1), 70+T-1]
     const float* bias_u;   // [8][128]
     const float* bias_v;
     const int* slot;       // [B]
