@@ -138,7 +138,7 @@ int nb200_mel_batch(nb200_model* m, const int16_t* pcm, int n_streams, int n_sam
 int nb200_debug_matmul(nb200_model* m, const char* tensor_name, const float* x, int M, float* y);
 /* Times the tcgen05 GEMM alone: C[M,N] = A[M,K] * W[N,K]^T on synthetic fp16 operands, cycling through > 2x L2 worth of
  * weight matrices so that W streams from HBM as it does inside a step. epi_kind: 0 store f32, 1 SiLU + re-quantise ->
- * f16, 4 GLU, 5 split-K partials. bn / splits force a tile configuration (bn = 0: the library's heuristic). Device time
+ * f16, 4 GLU, 5 split-K partials, 6 plain f16 store. bn / splits force a tile configuration (bn = 0: the library's heuristic). Device time
  * per launch (CUDA events on the library's stream) in microseconds. */
 int nb200_bench_gemm(nb200_model* m, int M, int N, int K, int epi_kind, int bn, int splits, int iters, double* us_per_launch,
                      int* bn_used, int* splits_used);

@@ -125,11 +125,22 @@ __device__ __forceinline__ float warp_max(float v) {
 }
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + expf(-x)); }
-// GEMM-epilogue versions (ex2.approx + approximate division, ~1e-6 relative): the results are rounded to fp16 (or
-// feed the int8-grid re-quantisation) right after, so the extra ulps are invisible, and the IEEE versions cost
-// ~60 instructions per element on the 4-8 epilogue warps of a tile.
-__device__ __forceinline__ float silu_fast(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
-__device__ __forceinline__ float sigmoid_fast(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+// GEMM-epilogue versions. The epilogue of a 128 x 256 tile evaluates 32768 sigmoids; it is bound by instruction issue
+// (ncu: ~20 instructions per element with the IEEE-safe __expf / division sequences, IPC ~0.5), so these are the
+// shortest forms: ex2.approx.ftz and rcp.approx.ftz (1 ulp each) -> FMUL, MUFU.EX2, FADD, MUFU.RCP, FMUL.
+// x -> -inf gives e = +inf, 1/inf = 0, x*0 = -0: no NaN for finite x.
+__device__ __forceinline__ float ex2_ftz(float t) {
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+    return e;
+}
+__device__ __forceinline__ float rcp_ftz(float y) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(y));
+    return r;
+}
+__device__ __forceinline__ float sigmoid_fast(float x) { return rcp_ftz(1.0f + ex2_ftz(x * -1.4426950408889634f)); }
+__device__ __forceinline__ float silu_fast(float x) { return x * sigmoid_fast(x); }
 // Scale pair of ggml-CPU's Q8_0 quantiser for a 32-block with the given amax: d = fp16(amax/127), id = 127/amax
 __device__ __forceinline__ void fq_scales(float amax, float& d, float& id) {
     d = amax == 0.0f ? 0.0f : __half2float(__float2half_rn(__fdiv_rn(amax, 127.0f)));

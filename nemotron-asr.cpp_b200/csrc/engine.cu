@@ -1220,7 +1220,7 @@ struct GemmBench {
         operand_init(A, a, Mp, K);
         W.resize(n_w);
         for (int j = 0; j < n_w; j++) operand_init(W[j], w + (size_t)j * N * K, N, K);
-        ep.kind = epi_kind;
+        ep.kind = epi_kind == 6 ? (int)EPI_STORE_F16 : epi_kind;  // 6 = fp16 store without activation (q|k|v)
         ep.ldo = N;
         ep.out_f32 = o32;
         ep.out_f16 = o16;

@@ -43,6 +43,16 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(src), "r"(c0), "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -100,7 +110,7 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
 // ------------------------------------------------------------------------------------------------
 // tcgen05 kernel: one 128 x BN output tile per CTA
 // ------------------------------------------------------------------------------------------------
-constexpr int TC_BM = 128, TC_BK = 64, TC_THREADS = 320;  // warp 0 TMA, warp 1 MMA, warps 2-9 epilogue
+constexpr int TC_BM = 128, TC_BK = 64, TC_EPI_WARPS = 16, TC_THREADS = 64 + 32 * TC_EPI_WARPS;  // warp 0 TMA, warp 1 MMA, warps 2-17 epilogue
 
 template <int BN, int STAGES>
 struct TcSmem {
@@ -112,7 +122,8 @@ struct TcSmem {
 
 template <int BN, int STAGES>
 __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
-                                                            const __grid_constant__ CUtensorMap map_w, int M, int num_k,
+                                                            const __grid_constant__ CUtensorMap map_w,
+                                                            const __grid_constant__ CUtensorMap map_out, int M, int num_k,
                                                             EpiParams epi) {
     pdl_launch();
     unsigned long long* trace = epi.trace ? epi.trace + 8 * (size_t)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) : nullptr;
@@ -132,12 +143,12 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_tile = blockIdx.x, m_tile = blockIdx.y;
     const int kb0 = blockIdx.z * num_k;  // split-K: this CTA sums k-blocks [kb0, kb0 + num_k)
-    if (epi.kind == EPI_PARTIAL) epi.out_f32 += (size_t)blockIdx.z * epi.split_stride;
     constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_out) : "memory");
         for (int s = 0; s < STAGES; s++) {
             mbar_init(full_bar(s), 1);
             mbar_init(empty_bar(s), 1);
@@ -151,12 +162,23 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     if (trace && threadIdx.x == 0) trace[1] = gtimer();
-    pdl_wait();  // everything above overlapped the previous kernel's tail; its outputs are visible from here on
+    // The weights do not depend on the previous kernel: their first STAGES k-blocks are requested before
+    // griddepcontrol.wait, so their HBM latency overlaps the tail of whatever runs before this GEMM.
+    const int n_pre = num_k < STAGES ? num_k : STAGES;
+    if (warp == 0 && lane == 0) {
+        for (int kb = 0; kb < n_pre; kb++) {
+            mbar_expect_tx(full_bar(kb), S::STAGE_BYTES);
+            tma_load_2d(base + kb * S::STAGE_BYTES + S::A_BYTES, &map_w, full_bar(kb), (kb0 + kb) * TC_BK, n_tile * BN);
+        }
+    }
+    pdl_wait();  // the previous kernel's outputs (our A operand, and buffers we overwrite) are settled from here on
     if (trace && threadIdx.x == 0) trace[2] = gtimer();
 
     if (warp == 0) {
         if (lane == 0) {  // ===== TMA producer =====
-            for (int kb = 0; kb < num_k; kb++) {
+            for (int kb = 0; kb < n_pre; kb++)
+                tma_load_2d(base + kb * S::STAGE_BYTES, &map_a, full_bar(kb), (kb0 + kb) * TC_BK, m_tile * TC_BM);
+            for (int kb = n_pre; kb < num_k; kb++) {
                 const int s = kb % STAGES;
                 const uint32_t ph = (kb / STAGES) & 1;
                 mbar_wait(empty_bar(s), ph ^ 1);
@@ -188,57 +210,63 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
             umma_commit(accum_bar);  // accumulator complete
         }
     } else {
-        // ===== epilogue warps 2..9: warp w reads TMEM lanes 32*(w%4) .. +31 (the hardware's lane-quadrant rule) and
-        // the 32-column chunks with index = (w-2)/4 (mod 2). Each chunk: tcgen05.ld (thread = row) -> transform in
-        // registers -> staged through shared memory -> written out row-contiguously (128 or 64 B per row per store
-        // instruction instead of 32 rows x 16 B). The staging area is the operand ring: once accum_bar has fired
-        // every stage has been consumed and the producer is done, so the memory is free.
-        const int ew = warp - 2, quad = warp & 3, half = ew >> 2;
+        // ===== epilogue warps 2..17: warp w reads TMEM lanes 32*(w%4) .. +31 (the hardware's lane-quadrant rule); the four
+        // warps of a quadrant alternate over the tile's column groups. Per group: tcgen05.ld (thread = row, 32 columns) ->
+        // bias / activation / re-quantisation in registers -> a 32-row x 128-byte staging tile in shared memory (128B-swizzled,
+        // so the 16-byte row pieces of 8 lanes land in 8 different bank groups) -> one TMA tensor store. Rows >= M are
+        // clipped by the tensor map. The staging tiles reuse the operand ring: once accum_bar has fired every stage has
+        // been consumed. Two tiles per warp, so the store of one group overlaps the math of the next.
+        const int ew = warp - 2, quad = warp & 3, half = ew >> 2;  // half = which of the quadrant's 4 warps
         const int lane_base = quad * 32;
-        uint32_t* stg = reinterpret_cast<uint32_t*>(smem) + ew * (32 * 36);
+        uint8_t* stg = smem + ew * 8192;
         mbar_wait(accum_bar, 0);
         tc_fence_after();
         if (trace && threadIdx.x == 64) trace[4] = gtimer();
         const int m = m_tile * TC_BM + lane_base + lane;
-        const bool row_ok = m < M;
+        const bool packed = (epi.kind == EPI_STORE_F16 || epi.kind == EPI_GLU);  // 64 accumulator columns per 128-byte row
+        const int acc_cols = packed ? 64 : 32;
+        const int out_row = m_tile * TC_BM + lane_base + (epi.kind == EPI_PARTIAL ? (int)blockIdx.z * epi.split_rows : 0);
+        const int sw = lane & 7;
+        int buf = 0;
 #pragma unroll 1
-        for (int c = half * 32; c < BN; c += 64) {
-            float acc[32];
-            tmem_ld32(tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)c, acc);  // warp-collective
-            uint32_t w[32];
-            char* dst = nullptr;
-            const int nw = (epi.kind == EPI_STORE_F16 || epi.kind == EPI_GLU) ? 16 : 32;  // output words per row and chunk
-            if (row_ok) epilogue_transform(epi, m, n_tile * BN + c, acc, w, dst);
-            const int ld = nw == 32 ? 36 : 20;  // staging row stride in words (16-byte aligned, conflict-free float4 columns)
+        for (int c = half * acc_cols; c < BN; c += (TC_EPI_WARPS / 4) * acc_cols, buf ^= 1) {
+            if (lane == 0) bulk_wait_read<1>();  // the store that last read this staging tile has drained it
             __syncwarp();
-            if (row_ok) {
+            uint8_t* row_ptr = stg + buf * 4096 + lane * 128;
+            unsigned long long ck0 = 0, ck1 = 0, ck2 = 0, ck3 = 0, ck4 = 0;
+#pragma unroll 1
+            for (int sub = 0; sub * 32 < acc_cols; sub++) {
+                float acc[32];
+                if (trace && sub == 0) ck0 = gtimer();
+                tmem_ld32(tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(c + 32 * sub), acc);  // warp-collective
+                if (trace && sub == 0) ck1 = gtimer();
+                uint32_t w[32];
+                char* unused = nullptr;
+                const int nw = epilogue_transform(epi, m, n_tile * BN + c + 32 * sub, acc, w, unused);
+                if (trace && sub == 0) ck2 = gtimer();
 #pragma unroll
-                for (int j = 0; j < 8; j++)
-                    if (4 * j < nw) *reinterpret_cast<uint4*>(stg + lane * ld + 4 * j) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
-            }
-            __syncwarp();
-            const int lpr = nw >> 2;        // lanes per row (16 B each): 8 or 4
-            const int rpp = 32 / lpr;       // rows per pass: 4 or 8
-            const unsigned long long dst_bits = reinterpret_cast<unsigned long long>(dst);
-            const unsigned ok_mask = __ballot_sync(0xffffffffu, row_ok);
-#pragma unroll 1
-            for (int r0 = 0; r0 < 32; r0 += rpp) {
-                const int rr = r0 + lane / lpr, col = (lane % lpr) * 4;
-                const unsigned long long rb = __shfl_sync(0xffffffffu, dst_bits, rr);
-                if ((ok_mask >> rr) & 1u) {
-                    uint4 v = *reinterpret_cast<const uint4*>(stg + rr * ld + col);
-                    uint4* gp = reinterpret_cast<uint4*>(reinterpret_cast<char*>(rb) + col * 4);
-                    if (epi.kind == EPI_RESID) {
-                        const float4 x = *reinterpret_cast<const float4*>(gp);
-                        v.x = __float_as_uint(x.x + epi.alpha * __uint_as_float(v.x));
-                        v.y = __float_as_uint(x.y + epi.alpha * __uint_as_float(v.y));
-                        v.z = __float_as_uint(x.z + epi.alpha * __uint_as_float(v.z));
-                        v.w = __float_as_uint(x.w + epi.alpha * __uint_as_float(v.w));
+                for (int j = 0; j < 8; j++) {
+                    if (4 * j < nw) {
+                        const int piece = (nw == 32 ? j : sub * 4 + j) ^ sw;
+                        *reinterpret_cast<uint4*>(row_ptr + piece * 16) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
                     }
-                    *gp = v;
                 }
             }
+            fence_async_smem();
+            __syncwarp();
+            if (trace) ck3 = gtimer();
+            if (lane == 0) {
+                const int col = epi.kind == EPI_GLU ? (n_tile * BN + c) >> 1 : n_tile * BN + c;
+                tma_store_2d(&map_out, smem_u32(stg + buf * 4096), col, out_row);
+                bulk_commit();
+            }
+            if (trace) {
+                ck4 = gtimer();
+                if (threadIdx.x == 64 && c == half * acc_cols)
+                    trace[7] = (ck1 - ck0) | ((ck2 - ck1) << 12) | ((ck3 - ck2) << 24) | ((ck4 - ck3) << 36);
+            }
         }
+        if (lane == 0) bulk_wait_read<0>();  // smem must outlive the reads; global visibility comes with grid completion
         if (trace && threadIdx.x == 64) trace[6] = gtimer();
     }
     tc_fence_before();
@@ -336,6 +364,20 @@ static void make_map(CUtensorMap* map, const __half* ptr, int rows, int K, int b
     if (r != CUDA_SUCCESS) throw Error("cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
 }
 
+// Output tensor map for the epilogue's TMA stores: [rows][cols] elements with leading dimension ld, boxes of 32 rows x 128 bytes.
+static void make_out_map(CUtensorMap* map, void* ptr, bool f16, int rows, int cols, int ld) {
+    const int esz = f16 ? 2 : 4;
+    if (((uintptr_t)ptr & 15) != 0 || ((size_t)ld * esz) % 16 != 0) throw Error("GEMM output must be 16-byte aligned with a 16-byte multiple row pitch");
+    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+    cuuint64_t gstride[1] = {(cuuint64_t)ld * esz};
+    cuuint32_t box[2] = {(cuuint32_t)(128 / esz), 32};
+    cuuint32_t estride[2] = {1, 1};
+    CUresult r = get_encode_fn()(map, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, ptr, gdim, gstride, box, estride,
+                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) throw Error("cuTensorMapEncodeTiled (output) failed with code " + std::to_string((int)r));
+}
+
 void operand_init(Operand& op, const __half* ptr, int rows, int K) {
     if (K % TC_BK != 0) throw Error("GEMM operand K must be a multiple of 64");
     if (((uintptr_t)ptr & 15) != 0) throw Error("GEMM operand must be 16-byte aligned");
@@ -349,7 +391,7 @@ void operand_init(Operand& op, const __half* ptr, int rows, int K) {
 }
 
 template <int BN, int STAGES>
-static void launch_tc(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiParams& epi, int splits) {
+static void launch_tc(cudaStream_t st, const Operand& A, const Operand& W, const CUtensorMap& omap, int M, const EpiParams& epi, int splits) {
     using S = TcSmem<BN, STAGES>;
     static bool configured = false;
     if (!configured) {
@@ -358,7 +400,7 @@ static void launch_tc(cudaStream_t st, const Operand& A, const Operand& W, int M
     }
     dim3 grid(W.rows / BN, cdiv(M, TC_BM), splits);
     const CUtensorMap& wmap = BN == 256 ? W.map256 : (BN == 128 ? W.map128 : (BN == 64 ? W.map64 : W.map32));
-    launch_k(gemm_tc_kernel<BN, STAGES>, grid, dim3(TC_THREADS), (size_t)S::TOTAL, st, A.map128, wmap, M, A.K / TC_BK / splits, epi);
+    launch_k(gemm_tc_kernel<BN, STAGES>, grid, dim3(TC_THREADS), (size_t)S::TOTAL, st, A.map128, wmap, omap, M, A.K / TC_BK / splits, epi);
     NB_KERNEL_CHECK();
 }
 
@@ -372,7 +414,7 @@ void gemm_force_config(int bn, int splits) {
     g_force_splits = splits < 1 ? 1 : splits;
 }
 
-GemmConfig gemm_pick_config(int M, int N, int K, int max_splits) {
+GemmConfig gemm_pick_config(int M, int N, int K, int max_splits, int min_bn) {
     const int m_tiles = cdiv(M, TC_BM), kb = K / TC_BK, SMS = 148;
     if (g_force_bn) {
         int sp = std::min(g_force_splits, max_splits);
@@ -383,7 +425,7 @@ GemmConfig gemm_pick_config(int M, int N, int K, int max_splits) {
     double best_cost = 1e30;
     const int bns[4] = {256, 128, 64, 32};
     for (int bn : bns) {
-        if (N % bn) continue;
+        if (N % bn || bn < min_bn) continue;
         for (int sp = 1; sp <= max_splits; sp *= 2) {
             if (kb % sp) break;
             const int ctas = (N / bn) * m_tiles * sp;
@@ -403,7 +445,8 @@ GemmConfig gemm_pick_config(int M, int N, int K, int max_splits) {
     return best;
 }
 
-int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiParams& epi, bool use_simt, int max_splits) {
+int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiParams& epi_in, bool use_simt, int max_splits) {
+    EpiParams epi = epi_in;
     if (M <= 0) return 1;
     if (A.K != W.K) throw Error("GEMM: K mismatch");
     if (M > A.rows) throw Error("GEMM: M exceeds the activation buffer");
@@ -420,14 +463,31 @@ int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiPa
         NB_KERNEL_CHECK();
         return 1;
     }
-    const GemmConfig c = gemm_pick_config(M, N, A.K, max_splits);
+    const bool packed = epi.kind == EPI_STORE_F16 || epi.kind == EPI_GLU;
+    const GemmConfig c = gemm_pick_config(M, N, A.K, max_splits, packed ? 64 : 32);
+    if (packed && c.bn < 64) throw Error("GEMM: fp16 / GLU outputs need 64-column tiles");
+    CUtensorMap omap;
+    if (epi.kind == EPI_PARTIAL) {
+        if (epi.ldo <= 0 || epi.split_stride % (size_t)epi.ldo) throw Error("GEMM: split stride must be a multiple of the output pitch");
+        epi.split_rows = (int)(epi.split_stride / (size_t)epi.ldo);
+        if (c.splits > 1 && epi.split_rows < cdiv(M, TC_BM) * TC_BM) throw Error("GEMM: split-K workspace rows must cover the padded M");
+        make_out_map(&omap, epi.out_f32, false, c.splits > 1 ? c.splits * epi.split_rows : M, N, epi.ldo);
+    } else if (epi.kind == EPI_STORE_F16) {
+        make_out_map(&omap, epi.out_f16, true, M, N, epi.ldo);
+    } else if (epi.kind == EPI_GLU) {
+        make_out_map(&omap, epi.out_f32, false, M, N / 2, epi.ldo);
+    } else if (epi.kind == EPI_STORE) {
+        make_out_map(&omap, epi.out_f32, false, M, N, epi.ldo);
+    } else {
+        throw Error("GEMM: this epilogue kind is only available on the CUDA-core checker path");
+    }
     static const char* names[4] = {"gemm_tc_128x256", "gemm_tc_128x128", "gemm_tc_128x64", "gemm_tc_128x32"};
     ProfScope ps(st, names[c.bn == 256 ? 0 : (c.bn == 128 ? 1 : (c.bn == 64 ? 2 : 3))], flops, bytes + (c.splits > 1 ? 4.0 * (c.splits - 1) * M * (double)N : 0.0));
     switch (c.bn) {
-        case 256: launch_tc<256, 4>(st, A, W, M, epi, c.splits); break;
-        case 128: launch_tc<128, 6>(st, A, W, M, epi, c.splits); break;
-        case 64: launch_tc<64, 8>(st, A, W, M, epi, c.splits); break;
-        default: launch_tc<32, 8>(st, A, W, M, epi, c.splits); break;
+        case 256: launch_tc<256, 4>(st, A, W, omap, M, epi, c.splits); break;
+        case 128: launch_tc<128, 6>(st, A, W, omap, M, epi, c.splits); break;
+        case 64: launch_tc<64, 8>(st, A, W, omap, M, epi, c.splits); break;
+        default: launch_tc<32, 8>(st, A, W, omap, M, epi, c.splits); break;
     }
     return c.splits;
 }

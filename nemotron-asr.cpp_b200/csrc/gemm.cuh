@@ -35,7 +35,8 @@ struct EpiParams {
     float* out_f32 = nullptr;   // EPI_STORE / EPI_RESID / EPI_GLU / EPI_QKV(q)
     __half* out_f16 = nullptr;  // EPI_STORE_F16
     int ldo = 0;                // leading dimension of the output (elements)
-    size_t split_stride = 0;    // EPI_PARTIAL: elements between the partial outputs of consecutive K splits
+    size_t split_stride = 0;    // EPI_PARTIAL: elements between the partial outputs of consecutive K splits (a multiple of ldo)
+    int split_rows = 0;         // = split_stride / ldo (filled in by gemm())
     unsigned long long* trace = nullptr;  // debug: per-CTA phase timestamps (globaltimer ns), 8 words per CTA
 };
 
@@ -64,7 +65,9 @@ __device__ __forceinline__ int epilogue_transform(const EpiParams& p, int m, int
             float d, id;
             fq_scales(amax, d, id);
 #pragma unroll
-            for (int j = 0; j < 32; j++) acc[j] = rintf(__fmul_rn(acc[j], id)) * d;
+            // round-to-nearest-even of |v| <= 127 by the 1.5 * 2^23 trick (two FADDs on the FMA pipe; rintf is an FRND on the
+            // quarter-rate conversion pipe, which this epilogue already saturates with ex2/rcp)
+            for (int j = 0; j < 32; j++) acc[j] = __fsub_rn(__fadd_rn(__fmul_rn(acc[j], id), 12582912.0f), 12582912.0f) * d;
         }
 #pragma unroll
         for (int j = 0; j < 16; j++) {
@@ -127,7 +130,7 @@ int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiPa
 struct GemmConfig {
     int bn, splits, ctas;
 };
-GemmConfig gemm_pick_config(int M, int N, int K, int max_splits);
+GemmConfig gemm_pick_config(int M, int N, int K, int max_splits, int min_bn = 32);
 // Forces a configuration (bn in {32,64,128,256}, splits >= 1) for tuning runs; bn = 0 restores the heuristic.
 void gemm_force_config(int bn, int splits);
 

@@ -11,7 +11,7 @@ for p in (ROOT / "nemotron-asr.cpp_b200", ROOT / "tools", ROOT / "tests", ROOT):
 import inputs  # noqa: E402
 import nb200  # noqa: E402
 
-SHAPES = [("ffn_w1", 4096, 1024, 1), ("ffn_w2", 1024, 4096, 5), ("qkv", 3072, 1024, 0), ("out_pw2", 1024, 1024, 5), ("pw1", 2048, 1024, 4)]
+SHAPES = [("ffn_w1", 4096, 1024, 1), ("ffn_w2", 1024, 4096, 5), ("qkv", 3072, 1024, 6), ("out_pw2", 1024, 1024, 5), ("pw1", 2048, 1024, 4)]
 
 
 def main():
@@ -28,7 +28,7 @@ def main():
             ph = [(x[:, i] - t0) / 1e3 for i in range(7)]
             print(f"  launch {l}: entry-after-prev-end {(t0 - prev_end) / 1e3:6.2f} us | entry max {ph[0].max():5.2f} | prologue {np.median(ph[1]):5.2f} | "
                   f"dep-wait {np.median(ph[2]):5.2f} (max {ph[2].max():5.2f}) | first-stage {np.median(ph[3]):5.2f} | accum {np.median(ph[4]):5.2f} (max {ph[4].max():5.2f}) | "
-                  f"epi-warp2 {np.median(ph[6]):5.2f} | end {np.median(ph[5]):5.2f} (max {ph[5].max():5.2f}) | launch-to-launch {(t0 - t[l - 1][:, 0].min()) / 1e3:6.2f}")
+                  f"epi-warp2 {np.median(ph[6]):5.2f} | ldtm/xform/sts/tma ns {int(np.median(x[:, 7] & 0xfff))}/{int(np.median((x[:, 7] >> 12) & 0xfff))}/{int(np.median((x[:, 7] >> 24) & 0xfff))}/{int(np.median((x[:, 7] >> 36) & 0xfff))} | end {np.median(ph[5]):5.2f} (max {ph[5].max():5.2f}) | launch-to-launch {(t0 - t[l - 1][:, 0].min()) / 1e3:6.2f}")
     m.close()
 
 
