@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <stdexcept>
 #include <string>
+#include <utility>
 
 namespace nb {
 
@@ -68,19 +69,31 @@ __device__ __forceinline__ void pdl_prologue() {
     pdl_launch();
     pdl_wait();
 }
+// cluster_x > 1 launches thread-block clusters of (cluster_x, 1, 1); grid.x must be a multiple of it.
 template <typename... KArgs, typename... Args>
-void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+void launch_kc(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, int cluster_x, Args&&... args) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid;
     cfg.blockDim = block;
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute at[1];
+    cudaLaunchAttribute at[2];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = g_pdl ? 1 : 0;
-    cfg.attrs = at;
     cfg.numAttrs = 1;
+    if (cluster_x > 1) {
+        at[1].id = cudaLaunchAttributeClusterDimension;
+        at[1].val.clusterDim.x = (unsigned)cluster_x;
+        at[1].val.clusterDim.y = 1;
+        at[1].val.clusterDim.z = 1;
+        cfg.numAttrs = 2;
+    }
+    cfg.attrs = at;
     CUDA_CHECK(cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...));
+}
+template <typename... KArgs, typename... Args>
+void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    launch_kc(kernel, grid, block, smem, st, 1, std::forward<Args>(args)...);
 }
 #endif
 

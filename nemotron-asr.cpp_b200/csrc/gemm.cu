@@ -43,8 +43,8 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
-__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
-    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(src), "r"(c0), "r"(c1)
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2)
                  : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
@@ -108,27 +108,85 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// tcgen05 kernel: one 128 x BN output tile per CTA
+// tcgen05 kernel: one 128 x BN output tile per CTA; with CG = 2 two CTAs of a cluster (one TPC) form a pair that
+// computes a 256 x BN tile with cta_group::2 MMAs: each CTA stages its own 128 rows of A and HALF of the weight tile
+// (BN/2 rows), so the L2 -> SM operand traffic per output element drops by a third to a half — the main loop of the
+// single-CTA kernel is bound by exactly that traffic (measured ~70 B/clk/SM, ~8.3 KB/clk chip-wide).
 // ------------------------------------------------------------------------------------------------
 constexpr int TC_BM = 128, TC_BK = 64, TC_EPI_WARPS = 16, TC_THREADS = 64 + 32 * TC_EPI_WARPS;  // warp 0 TMA, warp 1 MMA, warps 2-17 epilogue
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int CG>
 struct TcSmem {
     static constexpr int A_BYTES = TC_BM * TC_BK * 2;
-    static constexpr int B_BYTES = BN * TC_BK * 2;
+    static constexpr int B_ROWS = BN / CG;              // weight rows this CTA stages per k-block
+    static constexpr int B_BYTES = B_ROWS * TC_BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+    static_assert(STAGES * STAGE_BYTES >= TC_EPI_WARPS * 8192, "the epilogue staging tiles reuse the operand ring");
+    static_assert(B_BYTES % 1024 == 0, "stage sub-buffers must keep the 1024-byte swizzle alignment");
 };
 
-template <int BN, int STAGES>
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t addr, uint32_t rank) {  // shared::cta address -> shared::cluster address in CTA `rank`
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA load issued by either CTA of a pair; the transaction bytes are credited to the barrier at cluster address `bar`
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void umma_f16_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {  // arrives on the barrier at this offset in BOTH CTAs
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"((uint16_t)3)
+                 : "memory");
+}
+template <int CG>
+__device__ __forceinline__ void tmem_alloc_cg(uint32_t dst_smem, uint32_t ncols) {
+    if constexpr (CG == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    } else {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+}
+template <int CG>
+__device__ __forceinline__ void tmem_dealloc_cg(uint32_t taddr, uint32_t ncols) {
+    if constexpr (CG == 1)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+    else
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+
+template <int BN, int STAGES, int CG>
 __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                             const __grid_constant__ CUtensorMap map_w,
-                                                            const __grid_constant__ CUtensorMap map_out, int M, int num_k,
+                                                            const __grid_constant__ CUtensorMap map_out, int M, int kb_total,
                                                             EpiParams epi) {
     pdl_launch();
     unsigned long long* trace = epi.trace ? epi.trace + 8 * (size_t)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) : nullptr;
     if (trace && threadIdx.x == 0) trace[0] = gtimer();
-    using S = TcSmem<BN, STAGES>;
+    using S = TcSmem<BN, STAGES, CG>;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t base = (raw + 1023u) & ~1023u;  // 128B swizzle atoms need 1024-byte alignment
@@ -141,9 +199,14 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + STAGES * S::STAGE_BYTES + 8 * (2 * STAGES + 1));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_tile = blockIdx.x, m_tile = blockIdx.y;
-    const int kb0 = blockIdx.z * num_k;  // split-K: this CTA sums k-blocks [kb0, kb0 + num_k)
-    constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+    // CG = 2: blockIdx.x = 2 * n_tile + rank (cluster dims (2,1,1)); the pair covers rows [256 y, 256 y + 256)
+    const uint32_t rank = CG == 2 ? cluster_rank() : 0u;
+    const int n_tile = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int m_tile = CG == 2 ? (int)(blockIdx.y * 2 + rank) : (int)blockIdx.y;
+    // split-K: CTA z of gridDim.z sums k-blocks [kb0, kb0 + num_k); the ranges differ by at most one block when kb_total % splits != 0
+    const int kb0 = (int)blockIdx.z * kb_total / (int)gridDim.z;
+    const int num_k = ((int)blockIdx.z + 1) * kb_total / (int)gridDim.z - kb0;
+    constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
@@ -156,41 +219,55 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
         mbar_init(accum_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
+    if (warp == 1) tmem_alloc_cg<CG>(smem_u32(tmem_slot), TMEM_COLS);
     tc_fence_before();
-    __syncthreads();
+    if constexpr (CG == 2) cluster_sync_all();  // the peer's TMA loads signal the leader's barriers: they must be initialised first
+    else __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     if (trace && threadIdx.x == 0) trace[1] = gtimer();
+
+    // Full barriers: with CG = 2 only the leader's are used. Its producer arms them with the bytes of BOTH CTAs' loads; the
+    // peer's loads credit them remotely (a complete_tx that lands before the arming only drives the count negative).
+    auto full_bar_addr = [&](int s) { return CG == 2 ? mapa_rank(full_bar(s), 0) : full_bar(s); };
+    auto load_w = [&](int s, int kb) {
+        const uint32_t dst = base + s * S::STAGE_BYTES + S::A_BYTES;
+        const int row = n_tile * BN + (int)rank * S::B_ROWS;
+        if constexpr (CG == 2) tma_load_2d_pair(dst, &map_w, full_bar_addr(s), (kb0 + kb) * TC_BK, row);
+        else tma_load_2d(dst, &map_w, full_bar(s), (kb0 + kb) * TC_BK, row);
+    };
+    auto load_a = [&](int s, int kb) {
+        const uint32_t dst = base + s * S::STAGE_BYTES;
+        if constexpr (CG == 2) tma_load_2d_pair(dst, &map_a, full_bar_addr(s), (kb0 + kb) * TC_BK, m_tile * TC_BM);
+        else tma_load_2d(dst, &map_a, full_bar(s), (kb0 + kb) * TC_BK, m_tile * TC_BM);
+    };
     // The weights do not depend on the previous kernel: their first STAGES k-blocks are requested before
     // griddepcontrol.wait, so their HBM latency overlaps the tail of whatever runs before this GEMM.
     const int n_pre = num_k < STAGES ? num_k : STAGES;
     if (warp == 0 && lane == 0) {
         for (int kb = 0; kb < n_pre; kb++) {
-            mbar_expect_tx(full_bar(kb), S::STAGE_BYTES);
-            tma_load_2d(base + kb * S::STAGE_BYTES + S::A_BYTES, &map_w, full_bar(kb), (kb0 + kb) * TC_BK, n_tile * BN);
+            if (rank == 0) mbar_expect_tx(full_bar(kb), CG * S::STAGE_BYTES);
+            load_w(kb, kb);
         }
     }
     pdl_wait();  // the previous kernel's outputs (our A operand, and buffers we overwrite) are settled from here on
     if (trace && threadIdx.x == 0) trace[2] = gtimer();
 
     if (warp == 0) {
-        if (lane == 0) {  // ===== TMA producer =====
-            for (int kb = 0; kb < n_pre; kb++)
-                tma_load_2d(base + kb * S::STAGE_BYTES, &map_a, full_bar(kb), (kb0 + kb) * TC_BK, m_tile * TC_BM);
+        if (lane == 0) {  // ===== TMA producer (both CTAs of a pair) =====
+            for (int kb = 0; kb < n_pre; kb++) load_a(kb, kb);
             for (int kb = n_pre; kb < num_k; kb++) {
                 const int s = kb % STAGES;
                 const uint32_t ph = (kb / STAGES) & 1;
-                mbar_wait(empty_bar(s), ph ^ 1);
-                mbar_expect_tx(full_bar(s), S::STAGE_BYTES);
-                const uint32_t a_dst = base + s * S::STAGE_BYTES;
-                tma_load_2d(a_dst, &map_a, full_bar(s), (kb0 + kb) * TC_BK, m_tile * TC_BM);
-                tma_load_2d(a_dst + S::A_BYTES, &map_w, full_bar(s), (kb0 + kb) * TC_BK, n_tile * BN);
+                mbar_wait(empty_bar(s), ph ^ 1);  // local: the leader's commit arrives on both CTAs' empty barriers
+                if (rank == 0) mbar_expect_tx(full_bar(s), CG * S::STAGE_BYTES);
+                load_a(s, kb);
+                load_w(s, kb);
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {  // ===== MMA issuer =====
-            constexpr uint32_t idesc = make_idesc_f16(TC_BM, BN);
+        if (lane == 0 && rank == 0) {  // ===== MMA issuer (the leader CTA issues for the pair) =====
+            constexpr uint32_t idesc = make_idesc_f16(TC_BM * CG, BN);
             for (int kb = 0; kb < num_k; kb++) {
                 const int s = kb % STAGES;
                 const uint32_t ph = (kb / STAGES) & 1;
@@ -203,11 +280,15 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
 #pragma unroll
                 for (int k = 0; k < TC_BK / 16; k++) {
                     // advance 16 halves = 32 bytes along K inside the swizzle atom: +2 in the (addr>>4) field
-                    umma_f16(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                    if constexpr (CG == 2) umma_f16_pair(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
+                    else umma_f16(tmem_base, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) ? 1u : 0u);
                 }
-                umma_commit(empty_bar(s));  // frees the smem slot when these MMAs retire
+                // frees the smem slot (in both CTAs) when these MMAs retire
+                if constexpr (CG == 2) umma_commit_pair(empty_bar(s));
+                else umma_commit(empty_bar(s));
             }
-            umma_commit(accum_bar);  // accumulator complete
+            if constexpr (CG == 2) umma_commit_pair(accum_bar);  // accumulator complete, both CTAs
+            else umma_commit(accum_bar);
         }
     } else {
         // ===== epilogue warps 2..17: warp w reads TMEM lanes 32*(w%4) .. +31 (the hardware's lane-quadrant rule); the four
@@ -225,7 +306,7 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
         const int m = m_tile * TC_BM + lane_base + lane;
         const bool packed = (epi.kind == EPI_STORE_F16 || epi.kind == EPI_GLU);  // 64 accumulator columns per 128-byte row
         const int acc_cols = packed ? 64 : 32;
-        const int out_row = m_tile * TC_BM + lane_base + (epi.kind == EPI_PARTIAL ? (int)blockIdx.z * epi.split_rows : 0);
+        const int out_row = m_tile * TC_BM + lane_base;
         const int sw = lane & 7;
         int buf = 0;
 #pragma unroll 1
@@ -257,7 +338,7 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
             if (trace) ck3 = gtimer();
             if (lane == 0) {
                 const int col = epi.kind == EPI_GLU ? (n_tile * BN + c) >> 1 : n_tile * BN + c;
-                tma_store_2d(&map_out, smem_u32(stg + buf * 4096), col, out_row);
+                tma_store_3d(&map_out, smem_u32(stg + buf * 4096), col, out_row, (int)blockIdx.z);  // rows >= M are clipped
                 bulk_commit();
             }
             if (trace) {
@@ -270,11 +351,12 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
         if (trace && threadIdx.x == 64) trace[6] = gtimer();
     }
     tc_fence_before();
-    __syncthreads();
+    if constexpr (CG == 2) cluster_sync_all();  // neither CTA may free TMEM / exit while the pair's MMAs or loads touch it
+    else __syncthreads();
     if (trace && threadIdx.x == 0) trace[5] = gtimer();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, TMEM_COLS);
+        tmem_dealloc_cg<CG>(tmem_base, TMEM_COLS);
     }
 }
 
@@ -364,15 +446,17 @@ static void make_map(CUtensorMap* map, const __half* ptr, int rows, int K, int b
     if (r != CUDA_SUCCESS) throw Error("cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
 }
 
-// Output tensor map for the epilogue's TMA stores: [rows][cols] elements with leading dimension ld, boxes of 32 rows x 128 bytes.
-static void make_out_map(CUtensorMap* map, void* ptr, bool f16, int rows, int cols, int ld) {
+// Output tensor map for the epilogue's TMA stores: [planes][rows][cols] elements (row pitch ld, plane pitch plane_stride elements),
+// boxes of 32 rows x 128 bytes. Split-K partial tiles go to plane blockIdx.z; rows >= `rows` are clipped in every plane.
+static void make_out_map(CUtensorMap* map, void* ptr, bool f16, int rows, int cols, int ld, int planes, size_t plane_stride) {
     const int esz = f16 ? 2 : 4;
-    if (((uintptr_t)ptr & 15) != 0 || ((size_t)ld * esz) % 16 != 0) throw Error("GEMM output must be 16-byte aligned with a 16-byte multiple row pitch");
-    cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-    cuuint64_t gstride[1] = {(cuuint64_t)ld * esz};
-    cuuint32_t box[2] = {(cuuint32_t)(128 / esz), 32};
-    cuuint32_t estride[2] = {1, 1};
-    CUresult r = get_encode_fn()(map, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, ptr, gdim, gstride, box, estride,
+    if (((uintptr_t)ptr & 15) != 0 || ((size_t)ld * esz) % 16 != 0 || (plane_stride * esz) % 16 != 0)
+        throw Error("GEMM output must be 16-byte aligned with 16-byte multiple pitches");
+    cuuint64_t gdim[3] = {(cuuint64_t)cols, (cuuint64_t)rows, (cuuint64_t)planes};
+    cuuint64_t gstride[2] = {(cuuint64_t)ld * esz, (cuuint64_t)(planes > 1 ? plane_stride : (size_t)ld * rows) * esz};
+    cuuint32_t box[3] = {(cuuint32_t)(128 / esz), 32, 1};
+    cuuint32_t estride[3] = {1, 1, 1};
+    CUresult r = get_encode_fn()(map, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, ptr, gdim, gstride, box, estride,
                                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) throw Error("cuTensorMapEncodeTiled (output) failed with code " + std::to_string((int)r));
@@ -384,29 +468,27 @@ void operand_init(Operand& op, const __half* ptr, int rows, int K) {
     op.ptr = ptr;
     op.rows = rows;
     op.K = K;
-    make_map(&op.map256, ptr, rows, K, 256);
-    make_map(&op.map128, ptr, rows, K, 128);
-    make_map(&op.map64, ptr, rows, K, 64);
-    make_map(&op.map32, ptr, rows, K, 32);
+    const int boxes[5] = {32, 64, 96, 128, 256};
+    for (int i = 0; i < 5; i++) make_map(&op.maps[i], ptr, rows, K, boxes[i]);
 }
 
-template <int BN, int STAGES>
+template <int BN, int STAGES, int CG>
 static void launch_tc(cudaStream_t st, const Operand& A, const Operand& W, const CUtensorMap& omap, int M, const EpiParams& epi, int splits) {
-    using S = TcSmem<BN, STAGES>;
+    using S = TcSmem<BN, STAGES, CG>;
     static bool configured = false;
     if (!configured) {
-        CUDA_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+        CUDA_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
         configured = true;
     }
-    dim3 grid(W.rows / BN, cdiv(M, TC_BM), splits);
-    const CUtensorMap& wmap = BN == 256 ? W.map256 : (BN == 128 ? W.map128 : (BN == 64 ? W.map64 : W.map32));
-    launch_k(gemm_tc_kernel<BN, STAGES>, grid, dim3(TC_THREADS), (size_t)S::TOTAL, st, A.map128, wmap, omap, M, A.K / TC_BK / splits, epi);
+    dim3 grid(CG * (W.rows / BN), cdiv(M, TC_BM * CG), splits);
+    launch_kc(gemm_tc_kernel<BN, STAGES, CG>, grid, dim3(TC_THREADS), (size_t)S::TOTAL, st, CG, A.box(128), W.box(S::B_ROWS), omap, M,
+              A.K / TC_BK, epi);
     NB_KERNEL_CHECK();
 }
 
 // ---- tile / split selection ------------------------------------------------------------------------------
-// One 128 x BN tile (x K/splits) per CTA, one wave wherever possible. Cost model in SM clocks per CTA:
-//   k-block time = max(MMA issue 2*BN clk, operand load (128+BN)*128 B at the L2->SM bandwidth shared by the active CTAs)
+// One tile (x K/splits) per CTA or CTA pair, one wave wherever possible. Cost model in SM clocks per CTA:
+//   k-block time = max(MMA issue 2*BN clk, operand bytes (128 + BN/cg rows of 128 B) at the L2->SM bandwidth shared by the active CTAs)
 //   + a fixed prologue/epilogue cost, times the number of waves; split-K pays for writing and re-reading its partials.
 static int g_force_bn = 0, g_force_splits = 1;
 void gemm_force_config(int bn, int splits) {
@@ -415,30 +497,36 @@ void gemm_force_config(int bn, int splits) {
 }
 
 GemmConfig gemm_pick_config(int M, int N, int K, int max_splits, int min_bn) {
-    const int m_tiles = cdiv(M, TC_BM), kb = K / TC_BK, SMS = 148;
+    const int kb = K / TC_BK, SMS = 148;
     if (g_force_bn) {
-        int sp = std::min(g_force_splits, max_splits);
-        while (sp > 1 && kb % sp) sp--;
-        return {g_force_bn, sp, (N / g_force_bn) * m_tiles * sp};
+        const int cg = g_force_bn >= 1000 ? 2 : 1, bn = g_force_bn % 1000;
+        const int sp = std::max(1, std::min(std::min(g_force_splits, max_splits), kb));
+        return {bn, sp, cg * (N / bn) * cdiv(M, TC_BM * cg) * sp, cg};
     }
-    GemmConfig best{64, 1, (N / 64) * m_tiles};
+    // Fitted to B200 measurements (tools/tune_gemm.py, profiles/r01_tune_gemm_v3.json): the main loop is bound by the tensor
+    // pipe, ~600 clk per 64-deep k-block of a 128 x 256 tile (85 % of the nominal 8192 FLOP/clk/SM), for single CTAs and
+    // pairs alike (the L2 -> SM operand stream is not the limiter), so pairs only pay off where they give a better CTA
+    // count (N = 3072: 16 x 4 pairs of 256 x 192); everything else per launch is a ~5 us fixed cost.
+    GemmConfig best{64, 1, (N / 64) * cdiv(M, TC_BM), 1};
     double best_cost = 1e30;
-    const int bns[4] = {256, 128, 64, 32};
-    for (int bn : bns) {
+    struct Cand { int cg, bn; };
+    const Cand cands[6] = {{1, 256}, {2, 192}, {1, 128}, {2, 256}, {1, 64}, {1, 32}};
+    for (const Cand& cd : cands) {
+        const int bn = cd.bn, cg = cd.cg;
         if (N % bn || bn < min_bn) continue;
-        for (int sp = 1; sp <= max_splits; sp *= 2) {
-            if (kb % sp) break;
-            const int ctas = (N / bn) * m_tiles * sp;
+        if (cg == 2 && M <= TC_BM) continue;  // a pair would leave its second CTA without rows
+        for (int sp = 1; sp <= std::min(max_splits, kb); sp++) {
+            const int ctas = cg * (N / bn) * cdiv(M, TC_BM * cg) * sp;
             const int waves = cdiv(ctas, SMS);
             const double active = std::min(ctas, SMS);
-            const double bw = std::min(96.0, 7000.0 / active);               // bytes / clk / SM from L2
-            const double kblock = std::max(2.0 * bn, (128.0 + bn) * 128.0 / bw);
-            const double epilogue = 1500.0 + 12.0 * bn;                        // TMEM drain + global stores of 128 x bn
-            double cost = waves * ((double)(kb / sp) * kblock + 2500.0 + epilogue);
-            if (sp > 1) cost += (double)sp * M * N * 8.0 / 5000.0;           // partials written, then re-read by the LayerNorm
+            const double bw = std::min(96.0, 8300.0 / active);               // bytes / clk / SM from L2
+            const double kblock = std::max(200.0 + 1.56 * bn, (128.0 + bn / cg) * 128.0 / bw);  // fitted: 600 / 400 / 300 clk at bn 256 / 128 / 64
+            const double fixed = 9000.0 + 10.0 * bn + (cg == 2 ? 1000.0 : 0.0);  // launch + fill + TMEM drain + staged TMA stores (fitted)
+            double cost = waves * ((double)cdiv(kb, sp) * kblock + fixed);
+            if (sp > 1) cost += (double)(sp - 1) * M * N * 4.0 / 5000.0;     // extra partial planes re-read by the LayerNorm
             if (cost < best_cost) {
                 best_cost = cost;
-                best = {bn, sp, ctas};
+                best = {bn, sp, ctas, cg};
             }
         }
     }
@@ -468,26 +556,36 @@ int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiPa
     if (packed && c.bn < 64) throw Error("GEMM: fp16 / GLU outputs need 64-column tiles");
     CUtensorMap omap;
     if (epi.kind == EPI_PARTIAL) {
-        if (epi.ldo <= 0 || epi.split_stride % (size_t)epi.ldo) throw Error("GEMM: split stride must be a multiple of the output pitch");
-        epi.split_rows = (int)(epi.split_stride / (size_t)epi.ldo);
-        if (c.splits > 1 && epi.split_rows < cdiv(M, TC_BM) * TC_BM) throw Error("GEMM: split-K workspace rows must cover the padded M");
-        make_out_map(&omap, epi.out_f32, false, c.splits > 1 ? c.splits * epi.split_rows : M, N, epi.ldo);
+        if (c.splits > 1 && epi.split_stride < (size_t)M * epi.ldo) throw Error("GEMM: split-K planes overlap");
+        make_out_map(&omap, epi.out_f32, false, M, N, epi.ldo, c.splits, epi.split_stride);
     } else if (epi.kind == EPI_STORE_F16) {
-        make_out_map(&omap, epi.out_f16, true, M, N, epi.ldo);
+        make_out_map(&omap, epi.out_f16, true, M, N, epi.ldo, 1, 0);
     } else if (epi.kind == EPI_GLU) {
-        make_out_map(&omap, epi.out_f32, false, M, N / 2, epi.ldo);
+        make_out_map(&omap, epi.out_f32, false, M, N / 2, epi.ldo, 1, 0);
     } else if (epi.kind == EPI_STORE) {
-        make_out_map(&omap, epi.out_f32, false, M, N, epi.ldo);
+        make_out_map(&omap, epi.out_f32, false, M, N, epi.ldo, 1, 0);
     } else {
         throw Error("GEMM: this epilogue kind is only available on the CUDA-core checker path");
     }
-    static const char* names[4] = {"gemm_tc_128x256", "gemm_tc_128x128", "gemm_tc_128x64", "gemm_tc_128x32"};
-    ProfScope ps(st, names[c.bn == 256 ? 0 : (c.bn == 128 ? 1 : (c.bn == 64 ? 2 : 3))], flops, bytes + (c.splits > 1 ? 4.0 * (c.splits - 1) * M * (double)N : 0.0));
-    switch (c.bn) {
-        case 256: launch_tc<256, 4>(st, A, W, omap, M, epi, c.splits); break;
-        case 128: launch_tc<128, 6>(st, A, W, omap, M, epi, c.splits); break;
-        case 64: launch_tc<64, 8>(st, A, W, omap, M, epi, c.splits); break;
-        default: launch_tc<32, 8>(st, A, W, omap, M, epi, c.splits); break;
+    static const char* names1[4] = {"gemm_tc_128x256", "gemm_tc_128x128", "gemm_tc_128x64", "gemm_tc_128x32"};
+    static const char* names2[3] = {"gemm_tc2_256x256", "gemm_tc2_256x192", "gemm_tc2_256x128"};
+    const char* name = c.cg == 2 ? names2[c.bn == 256 ? 0 : (c.bn == 192 ? 1 : 2)] : names1[c.bn == 256 ? 0 : (c.bn == 128 ? 1 : (c.bn == 64 ? 2 : 3))];
+    ProfScope ps(st, name, flops, bytes + (c.splits > 1 ? 4.0 * (c.splits - 1) * M * (double)N : 0.0));
+    if (c.cg == 2) {
+        switch (c.bn) {
+            case 256: launch_tc<256, 6, 2>(st, A, W, omap, M, epi, c.splits); break;
+            case 192: launch_tc<192, 7, 2>(st, A, W, omap, M, epi, c.splits); break;
+            case 128: launch_tc<128, 8, 2>(st, A, W, omap, M, epi, c.splits); break;
+            default: throw Error("GEMM: unsupported pair tile width");
+        }
+    } else {
+        switch (c.bn) {
+            case 256: launch_tc<256, 4, 1>(st, A, W, omap, M, epi, c.splits); break;
+            case 128: launch_tc<128, 6, 1>(st, A, W, omap, M, epi, c.splits); break;
+            case 64: launch_tc<64, 8, 1>(st, A, W, omap, M, epi, c.splits); break;
+            case 32: launch_tc<32, 8, 1>(st, A, W, omap, M, epi, c.splits); break;
+            default: throw Error("GEMM: unsupported tile width");
+        }
     }
     return c.splits;
 }

@@ -36,7 +36,6 @@ struct EpiParams {
     __half* out_f16 = nullptr;  // EPI_STORE_F16
     int ldo = 0;                // leading dimension of the output (elements)
     size_t split_stride = 0;    // EPI_PARTIAL: elements between the partial outputs of consecutive K splits (a multiple of ldo)
-    int split_rows = 0;         // = split_stride / ldo (filled in by gemm())
     unsigned long long* trace = nullptr;  // debug: per-CTA phase timestamps (globaltimer ns), 8 words per CTA
 };
 
@@ -116,10 +115,8 @@ __device__ __forceinline__ void epilogue_apply(const EpiParams& p, int m, int n0
 struct Operand {
     const __half* ptr = nullptr;
     int rows = 0, K = 0;
-    CUtensorMap map256;  // box 64(K) x 256 rows, 128B swizzle
-    CUtensorMap map128;  // box 64(K) x 128 rows
-    CUtensorMap map64;   // box 64(K) x 64 rows
-    CUtensorMap map32;   // box 64(K) x 32 rows
+    CUtensorMap maps[5];  // boxes of 64 (K) x {32, 64, 96, 128, 256} rows, 128B swizzle
+    const CUtensorMap& box(int rows) const { return maps[rows == 32 ? 0 : (rows == 64 ? 1 : (rows == 96 ? 2 : (rows == 128 ? 3 : 4)))]; }
 };
 void operand_init(Operand& op, const __half* ptr, int rows, int K);  // builds the tensor maps
 
@@ -129,9 +126,11 @@ int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiPa
 // Tile / split configuration the tcgen05 path would pick (exposed for the benchmarks and DESIGN.md)
 struct GemmConfig {
     int bn, splits, ctas;
+    int cg = 1;  // 1: one CTA per 128 x bn tile; 2: a CTA pair (cta_group::2) per 256 x bn tile
 };
 GemmConfig gemm_pick_config(int M, int N, int K, int max_splits, int min_bn = 32);
-// Forces a configuration (bn in {32,64,128,256}, splits >= 1) for tuning runs; bn = 0 restores the heuristic.
+// Forces a configuration for tuning runs: bn in {32,64,128,256} (single CTA) or 1000 + {128,192,256} (CTA pair), splits >= 1;
+// bn = 0 restores the heuristic.
 void gemm_force_config(int bn, int splits);
 
 }  // namespace nb

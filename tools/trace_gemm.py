@@ -16,9 +16,10 @@ SHAPES = [("ffn_w1", 4096, 1024, 1), ("ffn_w2", 1024, 4096, 5), ("qkv", 3072, 10
 
 def main():
     M = int(sys.argv[1]) if len(sys.argv) > 1 else 896
+    force = [int(x) for x in sys.argv[2:4]] if len(sys.argv) > 3 else None  # bn (1000+ = CTA pair), splits
     m = nb200.Model(inputs.gguf_path("q8_0"), 0, 2)
     for name, N, K, kind in SHAPES:
-        t = m.trace_gemm(M, N, K, kind, 0, 8 if kind == 5 else 1, 8).astype(np.int64)
+        t = (m.trace_gemm(M, N, K, kind, force[0], force[1] if kind == 5 else 1, 8) if force else m.trace_gemm(M, N, K, kind, 0, 8 if kind == 5 else 1, 8)).astype(np.int64)
         L, C, _ = t.shape
         print(f"{name} M={M} N={N} K={K}: {C} CTAs")
         for l in range(2, L):

@@ -21,12 +21,10 @@ def main():
         for name, N, K, kind in SHAPES:
             auto = m.bench_gemm(M, N, K, kind, 0, 1)
             row = {"M": M, "shape": name, "N": N, "K": K, "auto": auto, "sweep": []}
-            for bn in (256, 128, 64, 32):
-                for sp in ((1, 2, 4, 8) if kind == 5 else (1,)):
-                    if (K // 64) % sp:
+            for bn in (1256, 1192, 1128, 256, 128, 64):
+                for sp in ((1, 2, 3, 4, 5, 6, 8) if kind == 5 else (1,)):
+                    if N % (bn % 1000):
                         continue
-                    if bn < 64 and kind in (1, 4, 6):
-                        continue  # fp16 / GLU outputs need 64-column tiles
                     r = m.bench_gemm(M, N, K, kind, bn, sp)
                     row["sweep"].append({"bn": bn, "splits": sp, "us": round(r["us"], 2), "tflops": round(r["tflops"], 1)})
             best = min(row["sweep"], key=lambda x: x["us"])
