@@ -12,13 +12,16 @@
 
 namespace nb {
 
-constexpr int VOCAB_PAD = 1088;
 
-// ---- fp32 SGEMM (NT), 64x64x16 tiles, 4x4 per thread -------------------------------------------------
+
+// ---- fp32 SGEMM (NT), 64x64x16 tiles, 4x4 per thread; the next k-chunk is fetched into registers while the current one
+// is multiplied (the K loop is otherwise a chain of exposed L2 round trips) --------------------------------------------
+// `zero3`: when non-null, thread 0 of block (0,0) clears three ints there (the decode round's counters, see below).
 __global__ void __launch_bounds__(256) sgemm_nt_kernel(const float* __restrict__ A, const float* __restrict__ W,
                                                        const float* __restrict__ bias, float* __restrict__ C, int M, int N,
-                                                       int K, int ldc, const int* __restrict__ out_rows) {
+                                                       int K, int ldc, const int* __restrict__ out_rows, int* zero3) {
     pdl_prologue();
+    if (zero3 != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) zero3[0] = zero3[1] = zero3[2] = 0;
     __shared__ float As[16][64 + 4];
     __shared__ float Ws[16][64 + 4];
     const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
@@ -29,13 +32,19 @@ __global__ void __launch_bounds__(256) sgemm_nt_kernel(const float* __restrict__
     for (int i = 0; i < 4; i++)
 #pragma unroll
         for (int j = 0; j < 4; j++) acc[i][j] = 0.0f;
+    const bool a_ok = m0 + lr < M;
+    const float* ap = A + (size_t)(m0 + lr) * K + lk;
+    const float* wp = W + (size_t)(n0 + lr) * K + lk;
+    float4 a = a_ok ? *reinterpret_cast<const float4*>(ap) : make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 w = *reinterpret_cast<const float4*>(wp);
     for (int k0 = 0; k0 < K; k0 += 16) {
-        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (m0 + lr < M) a = *reinterpret_cast<const float4*>(A + (size_t)(m0 + lr) * K + k0 + lk);
-        const float4 w = *reinterpret_cast<const float4*>(W + (size_t)(n0 + lr) * K + k0 + lk);
         As[lk + 0][lr] = a.x; As[lk + 1][lr] = a.y; As[lk + 2][lr] = a.z; As[lk + 3][lr] = a.w;
         Ws[lk + 0][lr] = w.x; Ws[lk + 1][lr] = w.y; Ws[lk + 2][lr] = w.z; Ws[lk + 3][lr] = w.w;
         __syncthreads();
+        if (k0 + 16 < K) {
+            if (a_ok) a = *reinterpret_cast<const float4*>(ap + k0 + 16);
+            w = *reinterpret_cast<const float4*>(wp + k0 + 16);
+        }
 #pragma unroll
         for (int k = 0; k < 16; k++) {
             const float4 av = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
@@ -63,14 +72,12 @@ __global__ void __launch_bounds__(256) sgemm_nt_kernel(const float* __restrict__
 }
 
 // Skinny variant for the decode loop (M <= 64 rows, weights streamed from L2): 64 x 16 tiles so that N/16 CTAs
-// (160 for the LSTM gates, 68 for the joint output) spread over the SMs; each thread owns 4 rows x 1 column.
-// `gate`: when non-null and *gate == 0 the whole launch is a no-op (no stream emitted this round -> LSTM unchanged).
+// (68 for the joint output) spread over the SMs; each thread owns 4 rows x 1 column. Same register prefetch.
 __global__ void __launch_bounds__(256) sgemm_skinny_kernel(const float* __restrict__ A, const float* __restrict__ W,
                                                            const float* __restrict__ bias, float* __restrict__ C, int M, int N,
-                                                           int K, int ldc, const int* __restrict__ out_rows,
-                                                           const int* __restrict__ gate) {
+                                                           int K, int ldc, const int* __restrict__ out_rows, int* zero3) {
     pdl_prologue();
-    if (gate != nullptr && *gate == 0) return;
+    if (zero3 != nullptr && blockIdx.x == 0 && threadIdx.x == 0) zero3[0] = zero3[1] = zero3[2] = 0;
     __shared__ float As[32][64 + 4];
     __shared__ float Ws[32][16 + 1];
     const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
@@ -78,19 +85,28 @@ __global__ void __launch_bounds__(256) sgemm_skinny_kernel(const float* __restri
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
     const int ar = t >> 2, ak = (t & 3) * 8;   // A tile 64 rows x 32 k: thread loads 8 consecutive k of one row
     const int wr = t >> 4, wk = (t & 15) * 2;  // W tile 16 rows x 32 k: thread loads 2 consecutive k of one row
+    const bool a_ok = ar < M;
+    const float* ap = A + (size_t)ar * K + ak;
+    const float* wp = W + (size_t)(n0 + wr) * K + wk;
+    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+    if (a_ok) {
+        a0 = *reinterpret_cast<const float4*>(ap);
+        a1 = *reinterpret_cast<const float4*>(ap + 4);
+    }
+    float2 w = *reinterpret_cast<const float2*>(wp);
     for (int k0 = 0; k0 < K; k0 += 32) {
-        float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
-        if (ar < M) {
-            const float4* src = reinterpret_cast<const float4*>(A + (size_t)ar * K + k0 + ak);
-            a0 = src[0];
-            a1 = src[1];
-        }
-        const float2 w = *reinterpret_cast<const float2*>(W + (size_t)(n0 + wr) * K + k0 + wk);
         As[ak + 0][ar] = a0.x; As[ak + 1][ar] = a0.y; As[ak + 2][ar] = a0.z; As[ak + 3][ar] = a0.w;
         As[ak + 4][ar] = a1.x; As[ak + 5][ar] = a1.y; As[ak + 6][ar] = a1.z; As[ak + 7][ar] = a1.w;
         Ws[wk + 0][wr] = w.x;
         Ws[wk + 1][wr] = w.y;
         __syncthreads();
+        if (k0 + 32 < K) {
+            if (a_ok) {
+                a0 = *reinterpret_cast<const float4*>(ap + k0 + 32);
+                a1 = *reinterpret_cast<const float4*>(ap + k0 + 36);
+            }
+            w = *reinterpret_cast<const float2*>(wp + k0 + 32);
+        }
 #pragma unroll
         for (int k = 0; k < 32; k++) {
             const float4 av = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
@@ -114,180 +130,429 @@ __global__ void __launch_bounds__(256) sgemm_skinny_kernel(const float* __restri
 }
 
 void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* bias, float* C, int M, int N, int K,
-                  int ldc, const int* out_rows, const int* gate) {
+                  int ldc, const int* out_rows, int* zero3) {
     if (M <= 0) return;
     if (N % 64 != 0 || K % 32 != 0) throw Error("sgemm: N must be a multiple of 64 and K of 32");
     const double flops = 2.0 * M * (double)N * K, bytes = 4.0 * ((double)M * K + (double)N * K + (double)M * N);
     if (M <= 64) {
         ProfScope ps(st, "sgemm_f32_skinny", flops, bytes);
-        launch_k(sgemm_skinny_kernel, dim3(N / 16), dim3(256), 0, st, A, W, bias, C, M, N, K, ldc, out_rows, gate);
+        launch_k(sgemm_skinny_kernel, dim3(N / 16), dim3(256), 0, st, A, W, bias, C, M, N, K, ldc, out_rows, zero3);
         NB_KERNEL_CHECK();
         return;
     }
-    if (gate) throw Error("sgemm: gated launches are only supported for M <= 64");
     ProfScope ps(st, "sgemm_f32", flops, bytes);
-    launch_k(sgemm_nt_kernel, dim3(dim3(N / 64, cdiv(M, 64))), dim3(256), 0, st, A, W, bias, C, M, N, K, ldc, out_rows);
+    launch_k(sgemm_nt_kernel, dim3(dim3(N / 64, cdiv(M, 64))), dim3(256), 0, st, A, W, bias, C, M, N, K, ldc, out_rows, zero3);
     NB_KERNEL_CHECK();
 }
 
-// ---- round kernels -------------------------------------------------------------------------------------
-// hid[b] = relu(e[b, fp[b]] + pend_p[slot[b]])   (src/nemo-ggml.cpp:1215-1217); zeros for finished streams
-__global__ void __launch_bounds__(160) hid_kernel(DecodeState s, DecodeBatch d) {
-    pdl_prologue();
-    const int b = blockIdx.x, i = threadIdx.x * 4;
-    if (b == 0 && threadIdx.x == 0) {  // first kernel of a round: reset the round's flags
-        *d.unfinished = 0;
-        *d.any_emit = 0;
-    }
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    const int fp = d.fp[b];
-    if (fp < d.nvalid[b]) {
-        const float4 e = *reinterpret_cast<const float4*>(d.e + ((size_t)(b * d.T + fp)) * JOINT + i);
-        const float4 p = *reinterpret_cast<const float4*>(s.pend_p + (size_t)d.slot[b] * JOINT + i);
-        v = make_float4(fmaxf(e.x + p.x, 0.f), fmaxf(e.y + p.y, 0.f), fmaxf(e.z + p.z, 0.f), fmaxf(e.w + p.w, 0.f));
-    }
-    *reinterpret_cast<float4*>(d.hid + (size_t)b * JOINT + i) = v;
-}
+// ---- the greedy loop: one persistent launch per batched chunk -------------------------------------------------------
+// G CTAs (one per SM) stay resident for all symbol rounds of the chunk and meet at grid-wide barriers. A round:
+//   L  logits: CTA j owns vocabulary rows [j*R, j*R+R) of joint.out (kept in shared memory for the whole launch). For
+//      every tile of 8 streams it stages hid = relu(joint.enc(frame fp) + pending pred) (src/nemo-ggml.cpp:1215-1217),
+//      one warp per row forms the 8 dot products, and the slice's (first max, runner-up, index) goes to partial[b][j].
+//   -- barrier --
+//   A  argmax: one warp per stream merges the G partials (ties -> lowest index = the reference's strict '>' scan,
+//      src/nemo-stream.cpp:899-906) and runs its state machine (:907-926): blank -> next frame, state untouched;
+//      token -> emit, prev = token, commit the pending LSTM state, join emit_list.
+//   -- barrier --
+//   E  only if some stream emitted (a blank leaves (prev, h, c) untouched, so the pending state stays valid): the
+//      pending LSTM / joint.pred state of the streams in emit_list is recomputed: layer 0, layer 1, joint.pred, each
+//      followed by a barrier (every hidden unit of the previous one is needed); CTA j owns 4-5 hidden units (= the i,f,
+//      g,o gate rows of those units, src/nemo-ggml.cpp:601-618) and loops over the emitting streams in tiles of 8.
+// The loop ends when no stream has frames left. Counters rotate over three slots so that clearing the next round's slot
+// cannot race with a CTA still reading the previous one.
+constexpr int DK_TS = 8, DK_MAXU = 8, DK_MAXR = 8, DK_GROUP = 64;
+struct DkSmem {
+    float xs[DK_GROUP * JOINT];        // L: hid of up to 64 streams [q][640]; E: input vectors of 8 streams [q][1280]
+    float wrow[DK_MAXR][JOINT];        // this CTA's joint.out rows
+    float gs[DK_TS][4 * DK_MAXU];      // gate pre-activations / logits of the tile
+    int sl[DK_TS], bq[DK_TS], rows[4 * DK_MAXU];
+    float bias[DK_MAXR];               // joint.out bias of my rows
+    int act[DK_GROUP];                 // L: batch indices of the group's unfinished streams
+    int n_act;
+};
+static_assert(DK_GROUP * JOINT >= DK_TS * 2 * DEC, "the LSTM tile reuses the hid buffer");
 
-// first-max argmax over the 1025 logits, then the reference's state machine (src/nemo-stream.cpp:899-926);
-// also stages the LSTM layer-0 input row x[b] = [embed[prev] | h0].
-__global__ void __launch_bounds__(256) argmax_commit_kernel(DecodeWeights w, DecodeState s, DecodeBatch d) {
-    pdl_prologue();
-    const int b = blockIdx.x, t = threadIdx.x, slot = d.slot[b];
-    __shared__ float bv[8], bs[8];
-    __shared__ int bi[8];
-    __shared__ int s_emit;
-    const int fp = d.fp[b];
-    const bool active = fp < d.nvalid[b];
-    if (t == 0) s_emit = 0;
-    if (active) {
-        const float* lg = d.logits + (size_t)b * VOCAB_PAD;
-        float best = -INFINITY, second = -INFINITY;
-        int besti = 0x7fffffff;
-        for (int v = t; v < VOCAB; v += 256) {
-            const float x = lg[v];
-            if (x > best) { second = best; best = x; besti = v; }  // increasing v per thread: strict '>' keeps the first maximum
-            else if (x > second) second = x;
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
-            const float os = __shfl_xor_sync(0xffffffffu, second, o);
-            const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
-            if (ob > best || (ob == best && oi < besti)) { second = fmaxf(best, os); best = ob; besti = oi; }
-            else second = fmaxf(second, ob);
-        }
-        if ((t & 31) == 0) { bv[t >> 5] = best; bi[t >> 5] = besti; bs[t >> 5] = second; }
-        __syncthreads();
-        if (t == 0) {
-            for (int i = 1; i < 8; i++) {
-                if (bv[i] > best || (bv[i] == best && bi[i] < besti)) { second = fmaxf(best, bs[i]); best = bv[i]; besti = bi[i]; }
-                else second = fmaxf(second, bv[i]);
-            }
-            d.min_margin[b] = fminf(d.min_margin[b], best - second);
-            int f = fp, sy = d.sym[b];
-            if (besti == BLANK || besti >= VOCAB) {
-                f++;
-                sy = 0;
-            } else {
-                d.tok_out[(size_t)b * d.T * MAX_SYMBOLS + d.tok_cnt[b]] = besti;
-                d.tok_cnt[b]++;
-                s.prev[slot] = besti;
-                s_emit = 1;
-                *d.any_emit = 1;  // benign race: every writer stores 1
-                sy++;
-                if (sy >= MAX_SYMBOLS) { f++; sy = 0; }
-            }
-            d.fp[b] = f;
-            d.sym[b] = sy;
-            if (f < d.nvalid[b]) atomicAdd(d.unfinished, 1);
-        }
-        __syncthreads();
-        if (s_emit) {  // commit the pending LSTM state
-            for (int i = t; i < 2 * DEC; i += 256) {
-                s.h[(size_t)slot * 2 * DEC + i] = s.pend_h[(size_t)slot * 2 * DEC + i];
-                s.c[(size_t)slot * 2 * DEC + i] = s.pend_c[(size_t)slot * 2 * DEC + i];
-            }
-        }
+__device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& phase) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        phase++;
+        __threadfence();
+        atomicAdd(bar, 1u);
+        const unsigned target = phase * gridDim.x;
+        unsigned v;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
+        } while (v < target);
+        __threadfence();
     }
     __syncthreads();
-    const int prev = s.prev[slot];
-    for (int i = t; i < DEC; i += 256) {
-        d.x[(size_t)b * 2 * DEC + i] = w.embed[(size_t)prev * DEC + i];
-        d.x[(size_t)b * 2 * DEC + DEC + i] = s.h[(size_t)slot * 2 * DEC + i];
-    }
 }
 
-// stage the layer-0 input without touching the state machine (used by refresh)
-__global__ void __launch_bounds__(256) stage_x0_kernel(DecodeWeights w, DecodeState s, DecodeBatch d) {
-    pdl_prologue();
-    const int b = blockIdx.x, t = threadIdx.x, slot = d.slot[b];
-    const int prev = s.prev[slot];
-    for (int i = t; i < DEC; i += 256) {
-        d.x[(size_t)b * 2 * DEC + i] = w.embed[(size_t)prev * DEC + i];
-        d.x[(size_t)b * 2 * DEC + DEC + i] = s.h[(size_t)slot * 2 * DEC + i];
+// One warp: n <= R weight rows (wr[i] -> K floats, global or shared memory) times the 8 staged vectors xs[q * LD + k].
+// Lane = (kg = lane & 7: interleaved K slice, sg = lane >> 3: stream pair). Every vector element a warp touches is read
+// once per call, whatever the number of rows (one row per warp would re-read the whole stream tile from shared memory for
+// every row: measured, that made shared-memory bandwidth the limit of the round). On return the lanes with kg == 0 hold
+// v[i][j] = wr[i] . xs[2 sg + j].
+template <int K, int LD, int R>
+__device__ __forceinline__ void dk_block(const float* const (&wr)[R], int n, const float* xs, float (&v)[R][2]) {
+    const int lane = threadIdx.x & 31, kg = lane & 7, sg = lane >> 3;
+    const float* x0 = xs + (size_t)(2 * sg) * LD + 4 * kg;
+    const float* x1 = x0 + LD;
+#pragma unroll
+    for (int i = 0; i < R; i++) v[i][0] = v[i][1] = 0.0f;
+#pragma unroll 4
+    for (int k = 0; k < K; k += 32) {
+        const float4 a = *reinterpret_cast<const float4*>(x0 + k), c = *reinterpret_cast<const float4*>(x1 + k);
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+            if (i < n) {
+                const float4 wv = *reinterpret_cast<const float4*>(wr[i] + 4 * kg + k);
+                v[i][0] = fmaf(wv.x, a.x, v[i][0]);
+                v[i][0] = fmaf(wv.y, a.y, v[i][0]);
+                v[i][0] = fmaf(wv.z, a.z, v[i][0]);
+                v[i][0] = fmaf(wv.w, a.w, v[i][0]);
+                v[i][1] = fmaf(wv.x, c.x, v[i][1]);
+                v[i][1] = fmaf(wv.y, c.y, v[i][1]);
+                v[i][1] = fmaf(wv.z, c.z, v[i][1]);
+                v[i][1] = fmaf(wv.w, c.w, v[i][1]);
+            }
+        }
     }
-}
-
-// LSTM cell, gate order i,f,g,o (src/nemo-ggml.cpp:601-618). layer 0 also stages x[b] = [h0' | h1]; layer 1 stages hp.
-__global__ void __launch_bounds__(160) cell_kernel(DecodeState s, DecodeBatch d, int layer, const int* __restrict__ gate) {
-    pdl_prologue();
-    if (gate != nullptr && *gate == 0) return;
-    const int b = blockIdx.x, slot = d.slot[b];
-    const float* g = d.gates + (size_t)b * 4 * DEC;
-    const size_t so = (size_t)slot * 2 * DEC + (size_t)layer * DEC;
-    for (int i = threadIdx.x; i < DEC; i += 160) {
-        const float ig = sigmoid_f(g[i]), fg = sigmoid_f(g[DEC + i]), gg = tanhf(g[2 * DEC + i]), og = sigmoid_f(g[3 * DEC + i]);
-        const float c2 = fg * s.c[so + i] + ig * gg;
-        const float h2 = og * tanhf(c2);
-        s.pend_c[so + i] = c2;
-        s.pend_h[so + i] = h2;
-        if (layer == 0) {
-            d.x[(size_t)b * 2 * DEC + i] = h2;
-            d.x[(size_t)b * 2 * DEC + DEC + i] = s.h[(size_t)slot * 2 * DEC + DEC + i];
-        } else {
-            d.hp[(size_t)b * DEC + i] = h2;
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            float x = v[i][j];
+            x += __shfl_xor_sync(0xffffffffu, x, 1);
+            x += __shfl_xor_sync(0xffffffffu, x, 2);
+            x += __shfl_xor_sync(0xffffffffu, x, 4);
+            v[i][j] = x;
         }
     }
 }
 
-// Recomputes the pending LSTM / joint.pred state of every stream of the batch from its committed state. In the
-// greedy loop it is gated on the round's any_emit flag: a blank leaves (prev, h, c) untouched (src/nemo-stream.cpp:
-// 907-911), so when no stream emitted the pending state is still valid and the five launches are no-ops.
-static void lstm_update(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d, const int* gate) {
-    for (int b0 = 0; b0 < d.B; b0 += 64) {  // the skinny GEMM takes up to 64 rows
-        const int nb = std::min(64, d.B - b0);
-        DecodeBatch e = d;
-        e.slot = d.slot + b0;
-        float* x = d.x + (size_t)b0 * 2 * DEC;
-        float* gates = d.gates + (size_t)b0 * 4 * DEC;
-        float* hp = d.hp + (size_t)b0 * DEC;
-        e.x = x; e.gates = gates; e.hp = hp;
-        launch_sgemm(st, x, w.wcat[0], w.bcat[0], gates, nb, 4 * DEC, 2 * DEC, 4 * DEC, nullptr, gate);
-        launch_k(cell_kernel, dim3(nb), dim3(160), 0, st, s, e, 0, gate);
-        NB_KERNEL_CHECK();
-        launch_sgemm(st, x, w.wcat[1], w.bcat[1], gates, nb, 4 * DEC, 2 * DEC, 4 * DEC, nullptr, gate);
-        launch_k(cell_kernel, dim3(nb), dim3(160), 0, st, s, e, 1, gate);
-        NB_KERNEL_CHECK();
-        launch_sgemm(st, hp, w.wpred, w.bpred, s.pend_p, nb, JOINT, DEC, JOINT, e.slot, gate);
+// rows[0..nr) of W (K floats each, row-major) times the DK_TS staged vectors xs[q][0..K): warp w takes rows w, w+8, w+16;
+// out(q, r, value + bias[row]).
+template <int K, int LD, typename Out>
+__device__ __forceinline__ void dk_rows(const float* __restrict__ W, const float* __restrict__ bias, const float* xs, int nr,
+                                        const int* rows, Out&& out) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, sg = lane >> 3;
+    const float* wr[3];
+    int n = 0;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        const int r = warp + 8 * i;
+        wr[i] = W + (size_t)rows[r < nr ? r : 0] * K;
+        if (r < nr) n = i + 1;
+    }
+    if (n == 0) return;
+    float v[3][2];
+    dk_block<K, LD, 3>(wr, n, xs, v);
+    if ((lane & 7) == 0) {
+#pragma unroll
+        for (int i = 0; i < 3; i++) {
+            if (i < n) {
+                const int r = warp + 8 * i;
+                const float bv = bias[rows[r]];
+                out(2 * sg, r, v[i][0] + bv);
+                out(2 * sg + 1, r, v[i][1] + bv);
+            }
+        }
     }
 }
 
-void launch_decode_round(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d) {
-    launch_k(hid_kernel, dim3(d.B), dim3(160), 0, st, s, d);
-    NB_KERNEL_CHECK();
-    for (int b0 = 0; b0 < d.B; b0 += 64)
-        launch_sgemm(st, d.hid + (size_t)b0 * JOINT, w.wout, w.bout, d.logits + (size_t)b0 * VOCAB_PAD, std::min(64, d.B - b0), VOCAB_PAD,
-                     JOINT, VOCAB_PAD, nullptr, nullptr);
-    launch_k(argmax_commit_kernel, dim3(d.B), dim3(256), 0, st, w, s, d);
-    NB_KERNEL_CHECK();
-    lstm_update(st, w, s, d, d.any_emit);
+// Recomputes pend_h / pend_c / pend_p of the E streams listed in `list` (batch indices; nullptr = 0..E-1).
+__device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d, DkSmem& sm, const int* list, int E,
+                               unsigned& phase) {
+    const int cta = blockIdx.x, G = gridDim.x, t = threadIdx.x;
+    const int base = DEC / G, rem = DEC % G;
+    const int nu = base + (cta < rem ? 1 : 0), u0 = cta * base + min(cta, rem);  // my hidden units [u0, u0 + nu)
+    for (int layer = 0; layer < 2; layer++) {
+        __syncthreads();
+        if (t < 4 * nu) sm.rows[t] = (t / nu) * DEC + u0 + (t % nu);
+        for (int e0 = 0; e0 < E; e0 += DK_TS) {
+            __syncthreads();
+            if (t < DK_TS) {
+                const int b = (e0 + t < E) ? (list ? __ldcg(list + e0 + t) : e0 + t) : -1;
+                sm.bq[t] = b;
+                sm.sl[t] = b >= 0 ? d.slot[b] : -1;
+            }
+            __syncthreads();
+            // x = [embed[prev] | h0] for layer 0, [h0' | h1] for layer 1 (h0' = this round's new layer-0 output)
+            for (int i = t; i < DK_TS * (2 * DEC / 4); i += 256) {
+                const int q = i / (2 * DEC / 4), k = (i - q * (2 * DEC / 4)) * 4, slot = sm.sl[q];
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (slot >= 0) {
+                    const float* src;
+                    if (k < DEC) src = layer == 0 ? w.embed + (size_t)__ldcg(s.prev + slot) * DEC + k : s.pend_h + (size_t)slot * 2 * DEC + k;
+                    else src = s.h + (size_t)slot * 2 * DEC + (size_t)layer * DEC + (k - DEC);
+                    v = __ldcg(reinterpret_cast<const float4*>(src));  // state written by other CTAs of this launch
+                }
+                *reinterpret_cast<float4*>(&sm.xs[q * 2 * DEC + k]) = v;
+            }
+            __syncthreads();
+            dk_rows<2 * DEC, 2 * DEC>(w.wcat[layer], w.bcat[layer], sm.xs, 4 * nu, sm.rows, [&](int q, int r, float v) { sm.gs[q][r] = v; });
+            __syncthreads();
+            if (t < DK_TS * nu) {
+                const int q = t / nu, ui = t % nu, slot = sm.sl[q];
+                if (slot >= 0) {
+                    const size_t so = (size_t)slot * 2 * DEC + (size_t)layer * DEC + u0 + ui;
+                    const float ig = sigmoid_f(sm.gs[q][ui]), fg = sigmoid_f(sm.gs[q][nu + ui]);
+                    const float gg = tanhf(sm.gs[q][2 * nu + ui]), og = sigmoid_f(sm.gs[q][3 * nu + ui]);
+                    const float c2 = fg * __ldcg(s.c + so) + ig * gg;
+                    s.pend_c[so] = c2;
+                    s.pend_h[so] = og * tanhf(c2);
+                }
+            }
+        }
+        grid_barrier(d.bar, phase);
+    }
+    // joint.pred (src/nemo-ggml.cpp:1207-1211): pend_p = W_pred h1' + b_pred, rows u0 .. u0+nu-1
+    if (t < nu) sm.rows[t] = u0 + t;
+    for (int e0 = 0; e0 < E; e0 += DK_TS) {
+        __syncthreads();
+        if (t < DK_TS) {
+            const int b = (e0 + t < E) ? (list ? __ldcg(list + e0 + t) : e0 + t) : -1;
+            sm.bq[t] = b;
+            sm.sl[t] = b >= 0 ? d.slot[b] : -1;
+        }
+        __syncthreads();
+        for (int i = t; i < DK_TS * (DEC / 4); i += 256) {
+            const int q = i / (DEC / 4), k = (i - q * (DEC / 4)) * 4, slot = sm.sl[q];
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (slot >= 0) v = __ldcg(reinterpret_cast<const float4*>(s.pend_h + (size_t)slot * 2 * DEC + DEC + k));
+            *reinterpret_cast<float4*>(&sm.xs[q * 2 * DEC + k]) = v;
+        }
+        __syncthreads();
+        dk_rows<DEC, 2 * DEC>(w.wpred, w.bpred, sm.xs, nu, sm.rows, [&](int q, int r, float v) {
+            if (sm.sl[q] < 0) return;
+            s.pend_p[(size_t)sm.sl[q] * JOINT + u0 + r] = v;
+            if (list) {  // the stream's next symbol step: hid = relu(joint.enc(frame fp) + new pending pred), my rows
+                const int b = sm.bq[q], fp = __ldcg(d.fp + b);
+                if (fp < d.nvalid[b]) d.hid[(size_t)b * JOINT + u0 + r] = fmaxf(d.e[((size_t)(b * d.T + fp)) * JOINT + u0 + r] + v, 0.0f);
+            }
+        });
+    }
+    grid_barrier(d.bar, phase);
 }
 
-void launch_decode_refresh(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d) {
-    launch_k(stage_x0_kernel, dim3(d.B), dim3(256), 0, st, w, s, d);
+// hid[b] = relu(joint.enc(frame fp) + pend_p[slot]) for one stream, by one warp (src/nemo-ggml.cpp:1215-1217)
+__device__ __forceinline__ void dk_stage_hid(const DecodeState& s, const DecodeBatch& d, int b, int fp, int slot, int lane) {
+    for (int k = 4 * lane; k < JOINT; k += 128) {
+        const float4 e = *reinterpret_cast<const float4*>(d.e + ((size_t)(b * d.T + fp)) * JOINT + k);
+        const float4 p = __ldcg(reinterpret_cast<const float4*>(s.pend_p + (size_t)slot * JOINT + k));
+        *reinterpret_cast<float4*>(d.hid + (size_t)b * JOINT + k) =
+            make_float4(fmaxf(e.x + p.x, 0.f), fmaxf(e.y + p.y, 0.f), fmaxf(e.z + p.z, 0.f), fmaxf(e.w + p.w, 0.f));
+    }
+}
+
+__global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w, DecodeState s, DecodeBatch d, int refresh) {
+    pdl_prologue();
+    extern __shared__ __align__(16) uint8_t dk_raw[];
+    DkSmem& sm = *reinterpret_cast<DkSmem*>(dk_raw);
+    const int cta = blockIdx.x, G = gridDim.x, t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    unsigned phase = 0;
+    unsigned long long* stamps = reinterpret_cast<unsigned long long*>(d.counters + 10);  // [10..11] start, [12..13] end (globaltimer ns)
+    if (cta == 0 && t == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(stamps[0])::"memory");
+    if (refresh) {  // stream create / reset: pending state of every batch item from its committed state
+        dk_lstm_update(w, s, d, sm, nullptr, d.B, phase);
+        return;
+    }
+    // my vocabulary rows, resident in shared memory for the whole launch
+    const int R = (VOCAB + G - 1) / G, v0 = cta * R, nr = max(0, min(R, VOCAB - v0));
+    const int n_part = (VOCAB + R - 1) / R;  // CTAs that own rows
+    for (int i = t; i < nr * (JOINT / 4); i += 256) {
+        const int r = i / (JOINT / 4), k = (i - r * (JOINT / 4)) * 4;
+        *reinterpret_cast<float4*>(&sm.wrow[r][k]) = *reinterpret_cast<const float4*>(w.wout + (size_t)(v0 + r) * JOINT + k);
+    }
+    if (t < nr) sm.bias[t] = w.bout[v0 + t];
+    // hid of every stream's first symbol step (fp = 0, pending pred from the previous chunk); the owner warp of stream b
+    for (int b = cta * 8 + warp; b < d.B; b += G * 8)
+        if (d.nvalid[b] > 0) dk_stage_hid(s, d, b, 0, d.slot[b], lane);
+    grid_barrier(d.bar, phase);
+
+    float4* partial = reinterpret_cast<float4*>(d.partial);
+    int* unfinished = d.counters;      // [3]
+    int* emit_count = d.counters + 3;  // [3]
+    int round = 0;
+    unsigned long long* acc = reinterpret_cast<unsigned long long*>(d.counters + 16);
+    auto now = [] { unsigned long long x; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(x)::"memory"); return x; };
+    const bool tr = cta == 0 && t == 0;
+    for (;; round++) {
+        const int cs = round % 3;
+        unsigned long long t0 = tr ? now() : 0;
+        if (cta == 0 && t == 0) {  // clear the next round's counter slot (last read two barriers ago)
+            unfinished[(round + 1) % 3] = 0;
+            emit_count[(round + 1) % 3] = 0;
+        }
+        // ---- L: logits of my rows; the hid vectors of up to 64 unfinished streams are staged at once ----
+        if (nr > 0) {
+            for (int g0 = 0; g0 < d.B; g0 += DK_GROUP) {
+                __syncthreads();
+                if (warp == 0) {  // compact the group's unfinished streams (ballot scan)
+                    int n = 0;
+                    for (int c = 0; c < DK_GROUP; c += 32) {
+                        const int b = g0 + c + lane;
+                        const bool on = b < d.B && __ldcg(d.fp + b) < d.nvalid[b];
+                        const unsigned m = __ballot_sync(0xffffffffu, on);
+                        if (on) sm.act[n + __popc(m & ((1u << lane) - 1u))] = b;
+                        n += __popc(m);
+                    }
+                    if (lane == 0) sm.n_act = n;
+                }
+                __syncthreads();
+                const int n_act = sm.n_act;
+                unsigned long long u0 = tr ? now() : 0;
+                if (n_act == 0) continue;  // uniform
+                const int n_pad = (n_act + DK_TS - 1) / DK_TS * DK_TS;
+                for (int i0 = 0; i0 < n_pad * (JOINT / 4); i0 += 256 * 8) {  // 8 independent 16-byte loads in flight per thread
+                    float4 v[8];
+#pragma unroll
+                    for (int u = 0; u < 8; u++) {
+                        const int i = i0 + u * 256 + t, q = i / (JOINT / 4), k = (i - q * (JOINT / 4)) * 4;
+                        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (q < n_act) v[u] = __ldcg(reinterpret_cast<const float4*>(d.hid + (size_t)sm.act[q] * JOINT + k));
+                    }
+#pragma unroll
+                    for (int u = 0; u < 8; u++) {
+                        const int i = i0 + u * 256 + t;
+                        if (i < n_pad * (JOINT / 4)) *reinterpret_cast<float4*>(&sm.xs[(size_t)i * 4]) = v[u];
+                    }
+                }
+                __syncthreads();
+                unsigned long long u1 = tr ? now() : 0;
+                if (8 * warp < n_act) {  // warp w: streams 8w .. 8w+7 of the group, all of my rows
+                    const float* wr[DK_MAXR];
+#pragma unroll
+                    for (int i = 0; i < DK_MAXR; i++) wr[i] = &sm.wrow[i < nr ? i : 0][0];
+                    float v[DK_MAXR][2];
+                    dk_block<JOINT, JOINT, DK_MAXR>(wr, nr, sm.xs + (size_t)(8 * warp) * JOINT, v);
+                    if ((lane & 7) == 0) {
+#pragma unroll
+                        for (int j = 0; j < 2; j++) {
+                            const int q = 8 * warp + 2 * (lane >> 3) + j;
+                            if (q < n_act) {
+                                float best = -INFINITY, second = -INFINITY;
+                                int besti = 0;
+#pragma unroll
+                                for (int i = 0; i < DK_MAXR; i++) {
+                                    if (i < nr) {
+                                        const float x = v[i][j] + sm.bias[i];
+                                        if (x > best) { second = best; best = x; besti = v0 + i; }
+                                        else if (x > second) second = x;
+                                    }
+                                }
+                                partial[(size_t)sm.act[q] * G + cta] = make_float4(best, second, __int_as_float(besti), 0.0f);
+                            }
+                        }
+                    }
+                }
+                if (tr) { acc[4] += u0 - t0; acc[5] += u1 - u0; acc[6] += now() - u1; }
+            }
+        }
+        unsigned long long t1 = tr ? now() : 0;
+        grid_barrier(d.bar, phase);
+        unsigned long long t2 = tr ? now() : 0;
+        // ---- A: merge the partial maxima, state machine, next hid; one warp per stream ----
+        for (int b = cta * 8 + warp; b < d.B; b += G * 8) {
+            const int nvalid = d.nvalid[b], slot = d.slot[b];
+            const int fp = __ldcg(d.fp + b);
+            if (fp >= nvalid) continue;
+            float best = -INFINITY, second = -INFINITY;
+            int besti = 0x7fffffff;
+            for (int c = lane; c < n_part; c += 32) {
+                const float4 p = __ldcg(partial + (size_t)b * G + c);
+                const int pi = __float_as_int(p.z);
+                if (p.x > best || (p.x == best && pi < besti)) { second = fmaxf(best, p.y); best = p.x; besti = pi; }
+                else second = fmaxf(second, p.x);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+                const float os = __shfl_xor_sync(0xffffffffu, second, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+                if (ob > best || (ob == best && oi < besti)) { second = fmaxf(best, os); best = ob; besti = oi; }
+                else second = fmaxf(second, ob);
+            }
+            int f = fp, emit = 0;
+            if (lane == 0) {
+                d.min_margin[b] = fminf(d.min_margin[b], best - second);
+                int sy = d.sym[b];
+                if (besti == BLANK) {
+                    f++;
+                    sy = 0;
+                } else {
+                    const int n = d.tok_cnt[b];
+                    d.tok_out[(size_t)b * d.T * MAX_SYMBOLS + n] = besti;
+                    d.tok_cnt[b] = n + 1;
+                    s.prev[slot] = besti;
+                    emit = 1;
+                    d.emit_list[atomicAdd(emit_count + cs, 1)] = b;  // order is irrelevant: the streams are independent
+                    sy++;
+                    if (sy >= MAX_SYMBOLS) { f++; sy = 0; }
+                }
+                d.fp[b] = f;
+                d.sym[b] = sy;
+                if (f < nvalid) atomicAdd(unfinished + cs, 1);
+            }
+            emit = __shfl_sync(0xffffffffu, emit, 0);
+            f = __shfl_sync(0xffffffffu, f, 0);
+            if (emit) {  // commit the pending LSTM state; the new pending state and hid follow in phase E
+                for (int i = lane; i < 2 * DEC; i += 32) {
+                    s.h[(size_t)slot * 2 * DEC + i] = __ldcg(s.pend_h + (size_t)slot * 2 * DEC + i);
+                    s.c[(size_t)slot * 2 * DEC + i] = __ldcg(s.pend_c + (size_t)slot * 2 * DEC + i);
+                }
+            } else if (f < nvalid) {
+                dk_stage_hid(s, d, b, f, slot, lane);  // blank: same pending pred, next frame
+            }
+        }
+        unsigned long long t3 = tr ? now() : 0;
+        grid_barrier(d.bar, phase);
+        if (tr) { const unsigned long long t4 = now(); acc[0] += t1 - t0; acc[1] += t2 - t1; acc[2] += t3 - t2; acc[3] += t4 - t3; }
+        const int E = __ldcg(emit_count + cs), U = __ldcg(unfinished + cs);
+        if (E > 0) dk_lstm_update(w, s, d, sm, d.emit_list, E, phase);
+        if (U == 0 || round + 1 >= d.max_rounds) {
+            if (cta == 0 && t == 0) {
+                d.counters[6] = U;          // streams left unfinished (non-zero only if the round cap was hit)
+                d.counters[7] = round + 1;  // rounds run
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(stamps[1])::"memory");
+            }
+            break;
+        }
+    }
+}
+
+static int decode_grid() {
+    static int g = 0;
+    if (!g) {
+        int dev = 0, sms = 0;
+        CUDA_CHECK(cudaGetDevice(&dev));
+        CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        g = std::min(sms, 148);
+        if ((VOCAB + g - 1) / g > DK_MAXR || (DEC + g - 1) / g > DK_MAXU) throw Error("decode kernel: too few SMs for its row split");
+        CUDA_CHECK(cudaFuncSetAttribute(decode_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DkSmem)));
+    }
+    return g;
+}
+
+int decode_partial_floats(int B) { return 4 * B * 148; }
+
+// All greedy rounds of the batch's chunk in one launch (src/nemo-stream.cpp:1106-1118, 840-930).
+void launch_decode_chunk(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d) {
+    const int g = decode_grid();
+    CUDA_CHECK(cudaMemsetAsync(d.counters, 0, 32 * sizeof(int), st));  // counters, the barrier word, time stamps
+    ProfScope ps(st, "decode_chunk", 2.0 * d.B * d.T * (double)VOCAB * JOINT, 0.0);
+    launch_k(decode_persistent_kernel, dim3(g), dim3(256), sizeof(DkSmem), st, w, s, d, 0);
     NB_KERNEL_CHECK();
-    lstm_update(st, w, s, d, nullptr);
+}
+
+// Recomputes the pending LSTM / joint.pred state of every stream of the batch from its committed state (create / reset).
+void launch_decode_refresh(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d) {
+    const int g = decode_grid();
+    CUDA_CHECK(cudaMemsetAsync(d.counters, 0, 9 * sizeof(int), st));
+    launch_k(decode_persistent_kernel, dim3(g), dim3(256), sizeof(DkSmem), st, w, s, d, 1);
+    NB_KERNEL_CHECK();
 }
 
 }  // namespace nb

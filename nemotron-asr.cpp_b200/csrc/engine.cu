@@ -140,7 +140,8 @@ struct nb200_model {
     int* ws_meta = nullptr;        // int arrays [8][cap_B]
     long long* ws_meta64 = nullptr;  // long long arrays [3][cap_B]: out_off, a0, n_avail
     int *ws_fp = nullptr, *ws_sym = nullptr, *ws_tok = nullptr, *ws_tokcnt = nullptr, *ws_unfinished = nullptr;
-    float *ws_hid = nullptr, *ws_logits = nullptr, *ws_lx = nullptr, *ws_gates = nullptr, *ws_hp = nullptr;
+    float *ws_partial = nullptr, *ws_hid = nullptr;
+    int* ws_emit = nullptr;
     PinnedBuf<int16_t> h_stage;   // pinned staging of fed audio; offsets reset whenever the stream has been synchronised
     size_t stage_off = 0;
     PinnedBuf<int> h_meta;
@@ -438,16 +439,14 @@ void alloc_state(nb200_model* m) {
     m->ws_sym = m->alloc<int>(B);
     m->ws_tok = m->alloc<int>((size_t)B * MAX_T * MAX_SYMBOLS);
     m->ws_tokcnt = m->alloc<int>((size_t)2 * B);  // [B] counts + [B] margins (as float bits)
-    m->ws_unfinished = m->alloc<int>(2);  // [0] unfinished streams, [1] any-emit flag of the current round
+    m->ws_unfinished = m->alloc<int>(64);  // decode kernel counters (kernels.cuh DecodeBatch::counters)
+    m->ws_partial = m->alloc<float>((size_t)decode_partial_floats(B));
     m->ws_hid = m->alloc<float>((size_t)B * JOINT);
-    m->ws_logits = m->alloc<float>((size_t)B * 1088);
-    m->ws_lx = m->alloc<float>((size_t)B * 2 * DEC);
-    m->ws_gates = m->alloc<float>((size_t)B * 4 * DEC);
-    m->ws_hp = m->alloc<float>((size_t)B * DEC);
+    m->ws_emit = m->alloc<int>(B);
     m->h_stage.reserve(std::max<size_t>((size_t)1 << 22, (size_t)B * (HOP * big.shift + 1024)));  // >= one rc=13 chunk per slot
     m->h_meta.reserve((size_t)META_ROWS * B);
     m->h_meta64.reserve((size_t)3 * B);
-    m->h_tok.reserve((size_t)B * (MAX_T * MAX_SYMBOLS + 2) + 1);
+    m->h_tok.reserve((size_t)B * (MAX_T * MAX_SYMBOLS + 2) + 8);
     for (auto& e : m->ev) CUDA_CHECK(cudaEventCreate(&e));
     for (auto& e : m->tev) CUDA_CHECK(cudaEventCreate(&e));
 }
@@ -485,13 +484,12 @@ DecodeBatch decode_batch(nb200_model* m, int B, int T) {
     d.tok_out = m->ws_tok;
     d.tok_cnt = m->ws_tokcnt;
     d.min_margin = reinterpret_cast<float*>(m->ws_tokcnt + m->cap_B);
-    d.unfinished = m->ws_unfinished;
-    d.any_emit = m->ws_unfinished + 1;
+    d.counters = m->ws_unfinished;
+    d.bar = reinterpret_cast<unsigned*>(m->ws_unfinished + 8);
+    d.emit_list = m->ws_emit;
+    d.partial = m->ws_partial;
     d.hid = m->ws_hid;
-    d.logits = m->ws_logits;
-    d.x = m->ws_lx;
-    d.gates = m->ws_gates;
-    d.hp = m->ws_hp;
+    d.max_rounds = T * (MAX_SYMBOLS + 1) + 2;
     d.B = B;
     d.T = T;
     return d;
@@ -708,6 +706,7 @@ void enqueue_encoder(const StepCtx& c) {
     CUDA_CHECK(cudaMemsetAsync(m->ws_sym, 0, sizeof(int) * B, st));
     CUDA_CHECK(cudaMemsetAsync(m->ws_tokcnt, 0, sizeof(int) * B, st));
     CUDA_CHECK(cudaMemsetAsync(m->ws_tokcnt + capB, 0x7f, sizeof(int) * B, st));  // margins = 3.39e38
+    launch_decode_chunk(st, m->dec, m->dstate, decode_batch(m, B, T));  // every greedy round of the chunk, one persistent launch
 }
 
 // Runs `fn` through a CUDA graph keyed by `key`: eagerly on the first request, captured on the second, replayed after.
@@ -744,7 +743,6 @@ void run_graphed(nb200_model* m, std::map<long long, GraphExec>& cache, long lon
     g_launches += g.launches;
 }
 
-constexpr int ROUNDS_PER_GRAPH = 4;
 
 void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
     const Mode& md = mc->mode;
@@ -779,40 +777,28 @@ void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
     run_graphed(m, m->enc_graphs, (long long)md.rc * 1000003 + B, allow_graph, [&] { enqueue_encoder(ctx); });
     CUDA_CHECK(cudaEventRecord(m->ev[2], st));
 
-    // ---- greedy rounds (src/nemo-stream.cpp:1106-1118, 840-930): every stream needs at least nvalid rounds ----
-    DecodeBatch db = decode_batch(m, B, T);
-    int max_valid = 0;
-    for (auto& it : items) max_valid = std::max(max_valid, it.nvalid);
-    long long rounds = 0;
-    int* h_unf = m->h_tok.p;  // word 0 of the pinned token buffer
-    int pending = max_valid;
-    long long syncs = 0;
-    while (pending > 0) {
-        int left = pending;
-        while (left >= ROUNDS_PER_GRAPH) {
-            run_graphed(m, m->dec_graphs, (long long)T * 1000003 + B, allow_graph, [&] {
-                for (int r = 0; r < ROUNDS_PER_GRAPH; r++) launch_decode_round(st, m->dec, m->dstate, db);
-            });
-            left -= ROUNDS_PER_GRAPH;
-        }
-        for (int r = 0; r < left; r++) launch_decode_round(st, m->dec, m->dstate, db);
-        rounds += pending;
-        CUDA_CHECK(cudaMemcpyAsync(h_unf, m->ws_unfinished, sizeof(int), cudaMemcpyDeviceToHost, st));
-        CUDA_CHECK(cudaStreamSynchronize(st));
-        syncs++;
-        pending = (*h_unf > 0) ? ROUNDS_PER_GRAPH : 0;
-        if (rounds > (long long)T * (MAX_SYMBOLS + 1) + 2 * ROUNDS_PER_GRAPH) throw Error("decode loop did not terminate");
-    }
-    int* h_cnt = m->h_tok.p + 1;
+    // The greedy rounds (src/nemo-stream.cpp:1106-1118, 840-930) ran inside the same graph as one persistent launch.
+    int* h_unf = m->h_tok.p;  // word 0, 1 of the pinned token buffer: streams left unfinished, rounds run
+    int* h_cnt = m->h_tok.p + 6;
     int* h_margin = h_cnt + B;
     int* h_toks = h_margin + B;
+    CUDA_CHECK(cudaMemcpyAsync(h_unf, m->ws_unfinished + 6, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaMemcpyAsync(h_unf + 2, m->ws_unfinished + 10, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));  // decode kernel's own start/end stamps
     CUDA_CHECK(cudaMemcpyAsync(h_cnt, m->ws_tokcnt, sizeof(int) * B, cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaMemcpyAsync(h_margin, m->ws_tokcnt + capB, sizeof(int) * B, cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaMemcpyAsync(h_toks, m->ws_tok, sizeof(int) * (size_t)B * T * MAX_SYMBOLS, cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaEventRecord(m->ev[3], st));
     CUDA_CHECK(cudaStreamSynchronize(st));
     m->stage_off = 0;  // every queued audio upload has completed
-    m->stats.d2h_bytes += (long long)sizeof(int) * ((size_t)2 * B + (size_t)B * T * MAX_SYMBOLS) + syncs * (long long)sizeof(int);
+    m->stats.d2h_bytes += (long long)sizeof(int) * ((size_t)2 * B + (size_t)B * T * MAX_SYMBOLS + 6);
+    if (h_unf[0] != 0) throw Error("decode loop did not terminate");
+    if (getenv("NB200_DK_TRACE")) {
+        unsigned long long a[7];
+        CUDA_CHECK(cudaMemcpy(a, m->ws_unfinished + 16, 56, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "decode phases (us): L %.1f (compact %.1f stage %.1f rows %.1f) bar1 %.1f A %.1f bar2 %.1f rounds %d\n", a[0] * 1e-3, a[4] * 1e-3,
+                a[5] * 1e-3, a[6] * 1e-3, a[1] * 1e-3, a[2] * 1e-3, a[3] * 1e-3, h_unf[1]);
+    }
+    const long long rounds = h_unf[1];
 
     // ---- host bookkeeping ----
     long long frames = 0, toks = 0;
@@ -840,8 +826,13 @@ void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
     m->stats.tokens += toks;
     m->stats.decode_rounds += rounds;
     m->stats.last_frontend_ms = 0.0;  // the frontend is part of the encoder graph
-    m->stats.last_encoder_ms = ms02;
-    m->stats.last_decoder_ms = ms23;
+    // the decode kernel stamps its own start / end (globaltimer ns) into counters[10..13]
+    unsigned long long dk0, dk1;
+    memcpy(&dk0, h_unf + 2, 8);
+    memcpy(&dk1, h_unf + 4, 8);
+    const double dec_ms = dk1 > dk0 ? (double)(dk1 - dk0) * 1e-6 : 0.0;
+    m->stats.last_encoder_ms = ms02 + ms23 - dec_ms;
+    m->stats.last_decoder_ms = dec_ms;
     m->stats.last_step_gpu_ms = ms02 + ms23;
     m->stats.gpu_seconds += (ms02 + ms23) * 1e-3;
     m->stats.kernel_launches = g_launches;

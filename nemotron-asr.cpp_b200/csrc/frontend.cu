@@ -77,15 +77,22 @@ void launch_mel(cudaStream_t st, const MelTables& tb, const MelBatch& mb, float*
 // ---- subsampling stage 1: conv0 (1->256, 3x3 s2, fp16-rounded operands) + ReLU + depthwise conv2 (3x3 s2) ----------
 // Causal zero padding (2 before, 1 after) on both axes at every stage (src/nemo-ggml.cpp:905-913). One CTA per
 // (h2, stream): thread = channel; the 7 mel rows feeding this output row sit in shared memory, fp16-rounded.
+// The thread walks along the frequency axis: per output column w2 it reads 4 new mel bins of each row (one 128-bit
+// broadcast load per row), evaluates the two new conv0 columns (w1 = 2 w2 - 1, 2 w2) of the three conv0 rows and
+// reuses column 2 w2 - 2 from the previous step, so every conv0 value is computed once per CTA instead of 9/4 times.
+// Summation orders (conv0: taps row-major; conv2: kh outer, kw inner) are those of the plain triple loop.
+constexpr int S1_PAD = 7;                 // smem column of mel bin 0: the 4 new bins of step w2 start at column 4 w2 + 4
+constexpr int S1_COLS = N_MELS + 1 + S1_PAD;  // bins -7 .. 128
+
 __global__ void __launch_bounds__(256) sub_stage1_kernel(SubWeights w, const float* __restrict__ mel, __half* __restrict__ out,
                                                          int chunk_mel, int t1, int t2) {
     pdl_prologue();
     const int h2 = blockIdx.x, b = blockIdx.y, c = threadIdx.x;
-    __shared__ float ms[7][N_MELS + 4];  // column index = mel bin + 2 (two zero columns on the left, two on the right)
+    __shared__ __align__(16) float ms[7][S1_COLS];
     const float* msrc = mel + (size_t)b * chunk_mel * N_MELS;
-    for (int i = c; i < 7 * (N_MELS + 4); i += 256) {
-        int r = i / (N_MELS + 4), col = i % (N_MELS + 4);
-        int tt = 4 * h2 - 6 + r, ff = col - 2;
+    for (int i = c; i < 7 * S1_COLS; i += 256) {
+        const int r = i / S1_COLS, col = i - r * S1_COLS;
+        const int tt = 4 * h2 - 6 + r, ff = col - S1_PAD;
         float v = 0.0f;
         if (tt >= 0 && tt < chunk_mel && ff >= 0 && ff < N_MELS) v = __half2float(__float2half_rn(msrc[(size_t)tt * N_MELS + ff]));
         ms[r][col] = v;
@@ -97,28 +104,48 @@ __global__ void __launch_bounds__(256) sub_stage1_kernel(SubWeights w, const flo
         k2[i] = w.w2[c * 9 + i];
     }
     const float bias0 = w.b0[c], bias2 = w.b2[c];
+    bool row_ok[3];
+#pragma unroll
+    for (int kh = 0; kh < 3; kh++) {
+        const int h1 = 2 * h2 + kh - 2;
+        row_ok[kh] = h1 >= 0 && h1 < t1;  // otherwise a zero padding row of the conv0 output
+    }
     __syncthreads();
     __half* orow = out + ((size_t)(b * t2 + h2) * SUB_F2) * SUB_CH + c;
+    float carry[7], prev_e[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+    for (int r = 0; r < 7; r++) carry[r] = 0.0f;  // bin -4: only feeds the (invalid) column w1 = -1
+#pragma unroll 1
     for (int w2 = 0; w2 < SUB_F2; w2++) {
+        float4 v[7];
+#pragma unroll
+        for (int r = 0; r < 7; r++) v[r] = *reinterpret_cast<const float4*>(&ms[r][4 * w2 + 4]);  // bins 4 w2 - 3 .. 4 w2
         float acc = bias2;
 #pragma unroll
         for (int kh = 0; kh < 3; kh++) {
-            const int h1 = 2 * h2 + kh - 2;
-            if (h1 < 0 || h1 >= t1) continue;  // zero padding row of the conv0 output
+            if (!row_ok[kh]) continue;
+            float ao = 0.0f, ae = 0.0f;
 #pragma unroll
-            for (int kw = 0; kw < 3; kw++) {
-                const int w1 = 2 * w2 + kw - 2;
-                if (w1 < 0 || w1 >= SUB_F1) continue;
-                // conv0 output at (h1, w1): mel rows 2*h1-2 .. 2*h1 -> smem rows 2*kh .. 2*kh+2; columns 2*w1-2 .. 2*w1
-                float a = 0.0f;
-#pragma unroll
-                for (int i = 0; i < 3; i++)
-#pragma unroll
-                    for (int j = 0; j < 3; j++) a = fmaf(k0[i * 3 + j], ms[2 * kh + i][2 * w1 + j], a);
-                a = fmaxf(a + bias0, 0.0f);
-                acc = fmaf(k2[kh * 3 + kw], a, acc);
+            for (int i = 0; i < 3; i++) {
+                const int r = 2 * kh + i;
+                ao = fmaf(k0[i * 3 + 0], carry[r], ao);
+                ao = fmaf(k0[i * 3 + 1], v[r].x, ao);
+                ao = fmaf(k0[i * 3 + 2], v[r].y, ao);
+                ae = fmaf(k0[i * 3 + 0], v[r].y, ae);
+                ae = fmaf(k0[i * 3 + 1], v[r].z, ae);
+                ae = fmaf(k0[i * 3 + 2], v[r].w, ae);
             }
+            ao = fmaxf(ao + bias0, 0.0f);
+            ae = fmaxf(ae + bias0, 0.0f);
+            if (w2 > 0) {  // columns w1 = 2 w2 - 2 and 2 w2 - 1 exist
+                acc = fmaf(k2[kh * 3 + 0], prev_e[kh], acc);
+                acc = fmaf(k2[kh * 3 + 1], ao, acc);
+            }
+            acc = fmaf(k2[kh * 3 + 2], ae, acc);
+            prev_e[kh] = ae;
         }
+#pragma unroll
+        for (int r = 0; r < 7; r++) carry[r] = v[r].w;
         orow[(size_t)w2 * SUB_CH] = __float2half_rn(acc);
     }
 }

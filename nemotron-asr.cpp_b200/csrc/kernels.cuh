@@ -95,7 +95,7 @@ namespace nb {
 // C[M,N] = A[M,K] * W[N,K]^T + bias, fp32 on CUDA cores (the reference keeps LSTM/joint weights and math in fp32,
 // src/nemo-ggml.cpp:580-619,1186-1224). N % 64 == 0, K % 16 == 0. Row m of C is stored at row out_rows[m] if given.
 void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* bias, float* C, int M, int N, int K,
-                  int ldc, const int* out_rows, const int* gate = nullptr);
+                  int ldc, const int* out_rows, int* zero3 = nullptr);
 
 struct DecodeState {           // per stream slot, persistent in HBM
     float* h;                  // [slots][2][640] committed LSTM hidden state
@@ -113,15 +113,14 @@ struct DecodeBatch {           // per batched step
     int* sym;                  // [B] symbols emitted at the current frame
     int* tok_out;              // [B][T*MAX_SYMBOLS]
     int* tok_cnt;              // [B]
-    int* unfinished;           // [1] streams with fp < nvalid after the last round
-    int* any_emit;             // [1] set when any stream emitted a token in the current round (gates the LSTM update)
     float* min_margin;         // [B] smallest top1-top2 logit gap over this chunk's symbol steps (near-tie tracing)
-    float* hid;                // [B][640]
-    float* logits;             // [B][1088]
-    float* x;                  // [B][1280] LSTM input rows
-    float* gates;              // [B][2560]
-    float* hp;                 // [B][640]
-    int B, T;
+    int* counters;             // [16]: unfinished[3], emit_count[3] (rotating per round), [6] streams left, [7] rounds run, [8] = bar,
+                               //       [10..13] the kernel's start / end globaltimer stamps
+    unsigned* bar;             // = counters + 8: arrival counter of the grid-wide barriers
+    int* emit_list;            // [B] batch indices of the streams that emitted in the current round
+    float* partial;            // [B][G][4] per-CTA (max, runner-up, index) of the current round's logits
+    float* hid;                // [B][640] joint hidden vector of every stream's next symbol step
+    int B, T, max_rounds;
 };
 struct DecodeWeights {
     const float* embed;        // [1025][640]
@@ -132,8 +131,9 @@ struct DecodeWeights {
     const float* wout;         // [1088][640], rows >= 1025 are zero
     const float* bout;         // [1088], entries >= 1025 are -inf
 };
-// one greedy round for every unfinished stream of the batch (src/nemo-stream.cpp:865-927)
-void launch_decode_round(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& b);
+// all greedy rounds of one batched chunk (src/nemo-stream.cpp:840-930, 1106-1118) as one persistent launch
+void launch_decode_chunk(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& b);
+int decode_partial_floats(int B);  // size of DecodeBatch::partial
 // recompute the pending LSTM/pred state of the given slots from their committed state (after create/reset)
 void launch_decode_refresh(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& b);
 
