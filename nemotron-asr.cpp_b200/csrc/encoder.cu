@@ -44,6 +44,7 @@ __device__ __forceinline__ void store_f16x4(__half* dst, float4 v, int act_quant
 
 // LayerNorm over 1024 features the way ggml_norm does it (ggml/src/ggml-cpu/ops.cpp:3698-3741): mean, then the
 // variance of the centred values, eps 1e-5; affine as separate mul/add (src/nemo-stream.cpp:580-591).
+// Block-wide version (256 threads = one row), used by the depthwise-conv kernel.
 __device__ __forceinline__ float4 ln_1024(float4 v, const float* g, const float* b, float* red) {
     const int c = threadIdx.x * 4;
     const float mean = block_sum_256(v.x + v.y + v.z + v.w, red) * (1.0f / D_MODEL);
@@ -90,58 +91,49 @@ void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b
     NB_KERNEL_CHECK();
 }
 
-// ---- cached causal depthwise conv (9 taps) + LayerNorm + SiLU --------------------------------------
-// One CTA per (frame t, stream): d[t][ch] = sum_k G[t+k][ch] * w[k][ch], G = [cache(8) ; g(T)] (src/nemo-stream.cpp:336-412),
+// ---- cached causal depthwise conv (9 taps) + LayerNorm + SiLU + cache roll-forward --------------------------------
+// One CTA per (frame t, stream), thread = 4 channels: d[t][ch] = sum_k G[t+k][ch] * w[k][ch], G = [cache(8) ; g(T)] (src/nemo-stream.cpp:336-412),
 // products accumulated in tap order like the reference's mul/add chain (:370-388); then LN (conv.batch_norm), SiLU (:671-674).
+// The new cache (last 8 rows of G, :399-409) goes to the stream's OTHER cache buffer (two buffers per stream and layer,
+// flipped every chunk), so the CTAs of a stream can write it while others still read the old one: row t of g is new cache
+// row t + 8 - T, written by the CTA that owns frame t; when T < 8 the CTA of frame 0 also moves old rows T.. up.
 __global__ void __launch_bounds__(256) dwconv_kernel(ConvArgs a) {
     pdl_prologue();
     __shared__ float red[16];
-    const int t = blockIdx.x, b = blockIdx.y, c = threadIdx.x * 4;
-    const float* cache = a.conv_cache + (size_t)a.slot[b] * CONV_CACHE * D_MODEL;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const int t = blockIdx.x, b = blockIdx.y, c = threadIdx.x * 4, T = a.T;
+    const int par = a.parity[b] & 1;
+    const float* rd = a.conv_cache + ((size_t)a.slot[b] * 2 + par) * CONV_CACHE * D_MODEL;
+    float* wr = a.conv_cache + ((size_t)a.slot[b] * 2 + (par ^ 1)) * CONV_CACHE * D_MODEL;
+    const float* g = a.g + (size_t)b * T * D_MODEL;
+    float4 x[KERNEL];
 #pragma unroll
     for (int k = 0; k < KERNEL; k++) {
         const int r = t + k;  // row of G
-        const float* src = (r < CONV_CACHE) ? cache + (size_t)r * D_MODEL + c
-                                            : a.g + ((size_t)(b * a.T + (r - CONV_CACHE))) * D_MODEL + c;
-        const float4 x = *reinterpret_cast<const float4*>(src);
+        x[k] = *reinterpret_cast<const float4*>(r < CONV_CACHE ? rd + (size_t)r * D_MODEL + c : g + (size_t)(r - CONV_CACHE) * D_MODEL + c);
+    }
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k < KERNEL; k++) {
         const float4 w = *reinterpret_cast<const float4*>(a.w_dw + k * D_MODEL + c);
         if (k == 0) {
-            acc.x = x.x * w.x; acc.y = x.y * w.y; acc.z = x.z * w.z; acc.w = x.w * w.w;
+            acc.x = x[k].x * w.x; acc.y = x[k].y * w.y; acc.z = x[k].z * w.z; acc.w = x[k].w * w.w;
         } else {
-            acc.x += x.x * w.x; acc.y += x.y * w.y; acc.z += x.z * w.z; acc.w += x.w * w.w;
+            acc.x += x[k].x * w.x; acc.y += x[k].y * w.y; acc.z += x[k].z * w.z; acc.w += x[k].w * w.w;
         }
+    }
+    if (t + CONV_CACHE - T >= 0) *reinterpret_cast<float4*>(wr + (size_t)(t + CONV_CACHE - T) * D_MODEL + c) = x[KERNEL - 1];  // g row t
+    if (t == 0) {
+        for (int r = 0; r < CONV_CACHE - T; r++)
+            *reinterpret_cast<float4*>(wr + (size_t)r * D_MODEL + c) = *reinterpret_cast<const float4*>(rd + (size_t)(T + r) * D_MODEL + c);
     }
     float4 v = ln_1024(acc, a.ln_g, a.ln_b, red);
     v.x = silu_f(v.x); v.y = silu_f(v.y); v.z = silu_f(v.z); v.w = silu_f(v.w);
-    store_f16x4(a.out + ((size_t)(b * a.T + t)) * D_MODEL + c, v, a.act_quant);
+    store_f16x4(a.out + ((size_t)(b * T + t)) * D_MODEL + c, v, a.act_quant);
 }
 
 void launch_dwconv(cudaStream_t st, const ConvArgs& a) {
-    ProfScope ps(st, "dwconv_ln_silu", (double)a.B * a.T * D_MODEL * 30, (double)a.B * ((a.T + 8.0) * D_MODEL * 4 + (double)a.T * D_MODEL * 2));
+    ProfScope ps(st, "dwconv_ln_silu", (double)a.B * a.T * D_MODEL * 30, (double)a.B * ((a.T + 16.0) * D_MODEL * 4 + (double)a.T * D_MODEL * 2));
     launch_k(dwconv_kernel, dim3(dim3(a.T, a.B)), dim3(256), 0, st, a);
-    NB_KERNEL_CHECK();
-}
-
-// new cache = last 8 rows of [cache ; g]; one CTA per stream, thread = 4 channels, rows staged in registers
-__global__ void __launch_bounds__(256) conv_cache_update_kernel(ConvArgs a) {
-    pdl_prologue();
-    const int b = blockIdx.x, c = threadIdx.x * 4, T = a.T;
-    float* cache = a.conv_cache + (size_t)a.slot[b] * CONV_CACHE * D_MODEL;
-    float4 rows[CONV_CACHE];
-#pragma unroll
-    for (int r = 0; r < CONV_CACHE; r++) {
-        const int src = T + r;  // row of G = [cache ; g]
-        rows[r] = (src < CONV_CACHE) ? *reinterpret_cast<const float4*>(cache + (size_t)src * D_MODEL + c)
-                                     : *reinterpret_cast<const float4*>(a.g + ((size_t)(b * T + (src - CONV_CACHE))) * D_MODEL + c);
-    }
-#pragma unroll
-    for (int r = 0; r < CONV_CACHE; r++) *reinterpret_cast<float4*>(cache + (size_t)r * D_MODEL + c) = rows[r];
-}
-
-void launch_conv_cache_update(cudaStream_t st, const ConvArgs& a) {
-    ProfScope ps(st, "conv_cache_update", 0.0, (double)a.B * 16.0 * D_MODEL * 4);
-    launch_k(conv_cache_update_kernel, dim3(a.B), dim3(256), 0, st, a);
     NB_KERNEL_CHECK();
 }
 

@@ -118,7 +118,7 @@ struct nb200_model {
     std::map<std::string, NamedMatrix> by_name;
     // per-slot state
     __half *k_ring = nullptr, *v_ring = nullptr;  // [L][slots][RING][1024] fp16
-    float* conv_cache = nullptr;                  // [L][slots][8][1024]
+    float* conv_cache = nullptr;                  // [L][slots][2][8][1024] (two buffers, flipped every chunk)
     float* mel_overlap = nullptr;                                      // [slots][9][128]
     DecodeState dstate{};
     std::vector<int> free_slots;
@@ -385,13 +385,13 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
 
 namespace {
 
-constexpr int META_ROWS = 8;  // int arrays per batch: slot, wpos, valid, nvalid, n_frames, (3 spare)
+constexpr int META_ROWS = 8;  // int arrays per batch: slot, wpos, valid, nvalid, n_frames, conv-cache parity, (2 spare)
 
 void alloc_state(nb200_model* m) {
     const size_t S = (size_t)m->max_streams, L = (size_t)m->n_layers;
     m->k_ring = m->alloc<__half>(L * S * RING * D_MODEL);
     m->v_ring = m->alloc<__half>(L * S * RING * D_MODEL);
-    m->conv_cache = m->alloc<float>(L * S * CONV_CACHE * D_MODEL);
+    m->conv_cache = m->alloc<float>(L * S * 2 * CONV_CACHE * D_MODEL);
     m->mel_overlap = m->alloc<float>(S * MEL_OVERLAP * N_MELS);
     m->dstate.h = m->alloc<float>(S * 2 * DEC);
     m->dstate.c = m->alloc<float>(S * 2 * DEC);
@@ -501,7 +501,7 @@ void reset_slot(nb200_model* m, int slot) {
     for (int l = 0; l < m->n_layers; l++) {
         CUDA_CHECK(cudaMemsetAsync(m->k_ring + ((size_t)l * S + slot) * RING * D_MODEL, 0, sizeof(__half) * RING * D_MODEL, m->st));
         CUDA_CHECK(cudaMemsetAsync(m->v_ring + ((size_t)l * S + slot) * RING * D_MODEL, 0, sizeof(__half) * RING * D_MODEL, m->st));
-        CUDA_CHECK(cudaMemsetAsync(m->conv_cache + ((size_t)l * S + slot) * CONV_CACHE * D_MODEL, 0, sizeof(float) * CONV_CACHE * D_MODEL, m->st));
+        CUDA_CHECK(cudaMemsetAsync(m->conv_cache + ((size_t)l * S + slot) * 2 * CONV_CACHE * D_MODEL, 0, sizeof(float) * 2 * CONV_CACHE * D_MODEL, m->st));
     }
     CUDA_CHECK(cudaMemsetAsync(m->mel_overlap + (size_t)slot * MEL_OVERLAP * N_MELS, 0, sizeof(float) * MEL_OVERLAP * N_MELS, m->st));
     CUDA_CHECK(cudaMemsetAsync(m->dstate.h + (size_t)slot * 2 * DEC, 0, sizeof(float) * 2 * DEC, m->st));
@@ -602,6 +602,7 @@ void enqueue_encoder(const StepCtx& c) {
     const int* d_wpos = m->ws_meta + 1 * capB;
     const int* d_valid = m->ws_meta + 2 * capB;
     const int* d_nframes = m->ws_meta + 4 * capB;
+    const int* d_parity = m->ws_meta + 5 * capB;
 
     // frontend: log-mel of the new samples, then dw-striding subsampling (src/nemo-ggml.cpp:954-1029)
     launch_k(mel_assemble_kernel, dim3(dim3(md.chunk_mel, B)), dim3(N_MELS), 0, st, m->ws_mel, m->mel_overlap, d_slot, d_nframes, md.chunk_mel);
@@ -674,10 +675,9 @@ void enqueue_encoder(const StepCtx& c) {
         glu.kind = EPI_GLU; glu.out_f32 = m->ws_g; glu.ldo = D_MODEL;
         gemm(st, m->op_a16, L.pw1.op, M, glu, simt);
         ConvArgs cv{};
-        cv.g = m->ws_g; cv.conv_cache = m->conv_cache + (size_t)l * S * CONV_CACHE * D_MODEL; cv.w_dw = L.w_dw;
+        cv.g = m->ws_g; cv.conv_cache = m->conv_cache + (size_t)l * S * 2 * CONV_CACHE * D_MODEL; cv.parity = d_parity; cv.w_dw = L.w_dw;
         cv.ln_g = L.bn_g; cv.ln_b = L.bn_b; cv.slot = d_slot; cv.out = m->ws_a16; cv.B = B; cv.T = T; cv.act_quant = aq;
         launch_dwconv(st, cv);
-        launch_conv_cache_update(st, cv);
         rin.nsplit = gemm(st, m->op_a16, L.pw2.op, M, part, simt, m->part_max_splits);
         // FFN2 and the layer's output norm (fused with the next layer's first norm)
         launch_layernorm(st, m->ws_x, L.ln_ff2_g, L.ln_ff2_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin);  // x += conv module
@@ -761,6 +761,7 @@ void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
         meta[2 * capB + b] = s->valid;
         meta[3 * capB + b] = items[b].nvalid;
         meta[4 * capB + b] = items[b].n_frames;
+        meta[5 * capB + b] = (int)(s->chunks_done & 1);
         meta64[0 * capB + b] = ((long long)b * md.chunk_mel + MEL_OVERLAP) * N_MELS;
         // frame f of this chunk covers absolute samples a0 + 160 f + [0, 513): a0 = first new frame's first sample - 1
         meta64[1 * capB + b] = (long long)HOP * md.shift * s->chunks_done - 257;

@@ -519,7 +519,7 @@ GemmConfig gemm_pick_config(int M, int N, int K, int max_splits, int min_bn) {
             const int ctas = cg * (N / bn) * cdiv(M, TC_BM * cg) * sp;
             const int waves = cdiv(ctas, SMS);
             const double active = std::min(ctas, SMS);
-            const double bw = std::min(96.0, 8300.0 / active);               // bytes / clk / SM from L2
+            const double bw = std::min(96.0, 11000.0 / active);              // bytes / clk / SM from L2 (not the limiter at one wave)
             const double kblock = std::max(200.0 + 1.56 * bn, (128.0 + bn / cg) * 128.0 / bw);  // fitted: 600 / 400 / 300 clk at bn 256 / 128 / 64
             const double fixed = 9000.0 + 10.0 * bn + (cg == 2 ? 1000.0 : 0.0);  // launch + fill + TMEM drain + staged TMA stores (fitted)
             double cost = waves * ((double)cdiv(kb, sp) * kblock + fixed);

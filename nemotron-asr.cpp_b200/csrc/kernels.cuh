@@ -71,7 +71,8 @@ void launch_attention(cudaStream_t st, const AttnArgs& a);
 
 struct ConvArgs {
     const float* g;        // GLU output [M][1024]
-    float* conv_cache;     // this layer's [slots][8][1024]
+    float* conv_cache;     // this layer's [slots][2][8][1024]: two buffers per stream, read parity[b], write the other
+    const int* parity;     // [B] chunks processed so far (its low bit selects the buffer to read)
     const float* w_dw;     // [9][1024]
     const float* ln_g;     // conv.batch_norm (a LayerNorm)
     const float* ln_b;
@@ -79,8 +80,7 @@ struct ConvArgs {
     __half* out;           // [M][1024] fp16 = fq(silu(LN(dwconv)))
     int B, T, act_quant;
 };
-void launch_dwconv(cudaStream_t st, const ConvArgs& a);        // reads cache, writes out
-void launch_conv_cache_update(cudaStream_t st, const ConvArgs& a);  // cache = last 8 of [cache ; g]
+void launch_dwconv(cudaStream_t st, const ConvArgs& a);  // out = fq(silu(LN(dwconv([cache ; g])))), other cache buffer = last 8 of [cache ; g]
 
 // fp32 [rows][1024] -> fp16 with optional fake-quant per 32 (used to prepare the positional table GEMM input)
 void launch_cast_f16(cudaStream_t st, const float* x, __half* out, int act_quant, int rows, int cols);
