@@ -62,6 +62,9 @@ struct ProfScope {
 // per-CTA setup (barrier init, TMEM allocation, descriptor prefetch). Kernels are launched through launch_k(), which
 // sets the programmatic-stream-serialization attribute (also inside CUDA-graph capture). NB200_NO_PDL=1 disables it.
 extern bool g_pdl;
+// Timing experiment: NB200_DUP=<family> makes the launcher of that kernel family launch it twice, so its marginal in-graph cost is
+// (step time with - without) / launches. Results are garbage in that mode.
+bool dup_family(const char* family);
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }

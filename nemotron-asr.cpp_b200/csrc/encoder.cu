@@ -87,7 +87,8 @@ void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b
     if (M <= 0) return;
     ProfScope ps(st, "layernorm", (double)M * D_MODEL * 8,
                  (double)M * D_MODEL * (4 + (out_f32 ? 4 : 0) + (out_f16 ? 2 : 0) + (rin.partials ? 4.0 * rin.nsplit + (out_f32 != x ? 4 : 0) : 0)));
-    launch_k(layernorm_kernel, dim3(M), dim3(256), 0, st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, rin);
+    for (int rep = dup_family("layernorm") ? 2 : 1; rep > 0; rep--)
+        launch_k(layernorm_kernel, dim3(M), dim3(256), 0, st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, rin);
     NB_KERNEL_CHECK();
 }
 
@@ -133,7 +134,7 @@ __global__ void __launch_bounds__(256) dwconv_kernel(ConvArgs a) {
 
 void launch_dwconv(cudaStream_t st, const ConvArgs& a) {
     ProfScope ps(st, "dwconv_ln_silu", (double)a.B * a.T * D_MODEL * 30, (double)a.B * ((a.T + 16.0) * D_MODEL * 4 + (double)a.T * D_MODEL * 2));
-    launch_k(dwconv_kernel, dim3(dim3(a.T, a.B)), dim3(256), 0, st, a);
+    for (int rep = dup_family("dwconv") ? 2 : 1; rep > 0; rep--) launch_k(dwconv_kernel, dim3(dim3(a.T, a.B)), dim3(256), 0, st, a);
     NB_KERNEL_CHECK();
 }
 

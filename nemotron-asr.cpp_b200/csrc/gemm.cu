@@ -571,6 +571,7 @@ int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiPa
     static const char* names2[3] = {"gemm_tc2_256x256", "gemm_tc2_256x192", "gemm_tc2_256x128"};
     const char* name = c.cg == 2 ? names2[c.bn == 256 ? 0 : (c.bn == 192 ? 1 : 2)] : names1[c.bn == 256 ? 0 : (c.bn == 128 ? 1 : (c.bn == 64 ? 2 : 3))];
     ProfScope ps(st, name, flops, bytes + (c.splits > 1 ? 4.0 * (c.splits - 1) * M * (double)N : 0.0));
+    for (int rep = dup_family("gemm") ? 2 : 1; rep > 0; rep--)
     if (c.cg == 2) {
         switch (c.bn) {
             case 256: launch_tc<256, 6, 2>(st, A, W, omap, M, epi, c.splits); break;

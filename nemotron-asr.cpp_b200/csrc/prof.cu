@@ -12,6 +12,11 @@ namespace nb {
 bool g_prof_on = false;
 bool g_pdl = getenv("NB200_NO_PDL") == nullptr;
 
+bool dup_family(const char* family) {
+    static const char* want = getenv("NB200_DUP");
+    return want != nullptr && std::string(want) == family;
+}
+
 namespace {
 struct Rec {
     const char* family;
