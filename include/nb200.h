@@ -80,8 +80,9 @@ void nb200_stream_free(nb200_stream* s);
 int nb200_stream_reset(nb200_stream* s);
 
 /* First half of nemo_stream_process_incremental (src/nemo-stream.cpp:1145-1162): buffer PCM. The samples are
- * uploaded (pinned staging + async copy on the library's stream) into the stream's device-resident PCM ring, so a
- * later nb200_step starts with its inputs already in HBM. Enqueue only: no kernel runs here. */
+ * copied into a pinned staging arena; the next nb200_step moves everything fed since the last one with ONE
+ * host->device copy and one scatter kernel into the streams' device-resident PCM rings (a cudaMemcpyAsync per stream
+ * cost 64 x 5 us of host time per step). Enqueue only: no kernel runs here unless the arena fills up. */
 int nb200_stream_feed(nb200_stream* s, const int16_t* pcm, int n_samples);
 /* nemo_stream_finalize (src/nemo-stream.cpp:1217-1293): mark the stream so the next nb200_step flushes its
  * zero-padded tail chunk (keeps floor(new_mel/8) frames). */
@@ -95,6 +96,20 @@ int nb200_stream_ready_chunks(const nb200_stream* s);
  * cross-stream batching; the reference runs one stream at a time (src/nemo-server.cpp:192-271).
  * Returns the number of stream-chunks processed (0 = nothing ready) or <0 on error. */
 int nb200_step(nb200_model* m);
+/* nb200_step in two halves, for a server loop that keeps receiving audio while the GPU works: _begin collects the
+ * ready chunks and launches the batched step without waiting; _end waits for it and appends the tokens. Between the
+ * two, nb200_stream_feed / nb200_feed_batch / polls are allowed (host-side staging only); create / free / reset
+ * complete the running step first. nb200_step == _begin followed by _end. The reference has no counterpart: its worker
+ * is one thread doing one stream at a time (src/nemo-server.cpp:192-271). Both return the stream-chunk count or <0. */
+int nb200_step_begin(nb200_model* m);
+int nb200_step_end(nb200_model* m);
+/* nb200_stream_feed for `count` streams of one model in one call (the server's reader threads hand the worker a list
+ * of (stream, bytes) events, src/nemo-server.cpp:201-262). */
+int nb200_feed_batch(nb200_model* m, nb200_stream* const* streams, const int16_t* const* pcm, const int* n_samples, int count);
+/* nb200_stream_poll_tokens for `count` streams: new tokens concatenated into tokens_out (capacity cap), per-stream
+ * counts into counts_out[count]. Returns the total number of tokens written; when cap is too small nothing is
+ * consumed, counts_out holds the waiting counts and the call returns <0. */
+int nb200_poll_batch(nb200_model* m, nb200_stream* const* streams, int count, int32_t* tokens_out, int cap, int32_t* counts_out);
 /* Convenience: nb200_step until no stream has a ready chunk. Returns total stream-chunks processed. */
 int nb200_drain(nb200_model* m);
 

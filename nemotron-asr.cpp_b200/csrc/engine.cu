@@ -70,6 +70,27 @@ struct GraphExec {
     int seen = 0;  // times this shape was requested; the first request runs eagerly (lazy cudaFuncSetAttribute calls)
 };
 
+// One contiguous run of fed samples: arena offset -> position in a slot's device PCM ring
+struct UploadSeg {
+    long long dst;  // sample index into pcm_ring
+    int src;        // sample offset in the staging arena
+    int n;
+};
+constexpr int MAX_UPLOAD_SEGS = 8192;
+struct UploadArena {
+    PinnedBuf<int16_t> pcm;
+    PinnedBuf<UploadSeg> segs;
+    size_t off = 0;
+    int nseg = 0, max_n = 0;
+    cudaEvent_t done = nullptr;
+    bool busy = false;
+};
+struct BatchItem {
+    nb200_stream* s;
+    int n_frames;  // new mel frames this chunk really has (shift for a full chunk, fewer for a finalize tail)
+    int nvalid;    // encoder frames to decode
+};
+
 }  // namespace
 
 struct nb200_stream {
@@ -142,8 +163,19 @@ struct nb200_model {
     int *ws_fp = nullptr, *ws_sym = nullptr, *ws_tok = nullptr, *ws_tokcnt = nullptr, *ws_unfinished = nullptr;
     float *ws_partial = nullptr, *ws_hid = nullptr;
     int* ws_emit = nullptr;
-    PinnedBuf<int16_t> h_stage;   // pinned staging of fed audio; offsets reset whenever the stream has been synchronised
-    size_t stage_off = 0;
+    // Fed audio is gathered on the host (pinned arenas) and moved at the next step by ONE copy + one scatter kernel
+    // instead of a cudaMemcpyAsync per stream; two arenas so feeding can go on while a flushed one is still in flight.
+    UploadArena arena[2];
+    int cur_arena = 0;
+    int16_t* d_stage = nullptr;    // device copy of the arena being flushed
+    UploadSeg* d_segs = nullptr;
+    // a step launched by nb200_step_begin and not yet completed by nb200_step_end
+    struct Inflight {
+        bool active = false;
+        int total = 0;
+        ModeCtx* mc = nullptr;
+        std::vector<BatchItem> items;
+    } inflight;
     PinnedBuf<int> h_meta;
     PinnedBuf<long long> h_meta64;
     PinnedBuf<int> h_tok;
@@ -172,6 +204,8 @@ struct nb200_model {
             if (e) cudaEventDestroy(e);
         for (auto& e : tev)
             if (e) cudaEventDestroy(e);
+        for (auto& A : arena)
+            if (A.done) cudaEventDestroy(A.done);
         for (auto* gm : {&enc_graphs, &dec_graphs})
             for (auto& kv : *gm)
                 if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
@@ -443,7 +477,16 @@ void alloc_state(nb200_model* m) {
     m->ws_partial = m->alloc<float>((size_t)decode_partial_floats(B));
     m->ws_hid = m->alloc<float>((size_t)B * JOINT);
     m->ws_emit = m->alloc<int>(B);
-    m->h_stage.reserve(std::max<size_t>((size_t)1 << 22, (size_t)B * (HOP * big.shift + 1024)));  // >= one rc=13 chunk per slot
+    {   // upload arenas: >= two rc=13 chunks per slot each
+        const size_t cap = std::max<size_t>((size_t)1 << 22, (size_t)B * 2 * (HOP * big.shift + 1024));
+        for (auto& A : m->arena) {
+            A.pcm.reserve(cap);
+            A.segs.reserve(MAX_UPLOAD_SEGS);
+            CUDA_CHECK(cudaEventCreateWithFlags(&A.done, cudaEventDisableTiming));
+        }
+        m->d_stage = m->alloc<int16_t>(cap, false);
+        m->d_segs = m->alloc<UploadSeg>(MAX_UPLOAD_SEGS, false);
+    }
     m->h_meta.reserve((size_t)META_ROWS * B);
     m->h_meta64.reserve((size_t)3 * B);
     m->h_tok.reserve((size_t)B * (MAX_T * MAX_SYMBOLS + 2) + 8);
@@ -539,26 +582,60 @@ long long keep_from(const nb200_stream* s) {
     return std::max<long long>(0, (long long)HOP * md.shift * s->chunks_done - 257);
 }
 
-// Upload up to n samples into the slot's device ring (pinned staging -> cudaMemcpyAsync on the library's stream, at
-// most two segments when the ring wraps). Returns the number of samples taken (less than n when the ring is full).
+// Scatter of one flushed arena into the slots' PCM rings: block (x = segment, y = 4096-sample piece).
+__global__ void __launch_bounds__(256) pcm_scatter_kernel(const int16_t* __restrict__ stage, const UploadSeg* __restrict__ segs, int16_t* __restrict__ ring) {
+    pdl_prologue();
+    const UploadSeg sg = segs[blockIdx.x];
+    const int16_t* src = stage + sg.src;
+    int16_t* dst = ring + sg.dst;
+    const int end = min(sg.n, (int)(blockIdx.y + 1) * 4096);
+    for (int i = blockIdx.y * 4096 + threadIdx.x; i < end; i += 256) dst[i] = src[i];
+}
+
+// Sends the current arena to the device (one H2D copy of the samples, one of the segment table, one scatter kernel on
+// the library's stream) and switches to the other arena. No host synchronisation unless that one is still in flight.
+void flush_uploads(nb200_model* m) {
+    UploadArena& A = m->arena[m->cur_arena];
+    if (A.nseg == 0) return;
+    cudaStream_t st = m->st;
+    CUDA_CHECK(cudaMemcpyAsync(m->d_stage, A.pcm.p, A.off * sizeof(int16_t), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(m->d_segs, A.segs.p, (size_t)A.nseg * sizeof(UploadSeg), cudaMemcpyHostToDevice, st));
+    launch_k(pcm_scatter_kernel, dim3(A.nseg, cdiv(A.max_n, 4096)), dim3(256), 0, st, (const int16_t*)m->d_stage, (const UploadSeg*)m->d_segs, m->pcm_ring);
+    NB_KERNEL_CHECK();
+    CUDA_CHECK(cudaEventRecord(A.done, st));
+    A.busy = true;
+    m->stats.h2d_bytes += (long long)(A.off * sizeof(int16_t) + (size_t)A.nseg * sizeof(UploadSeg));
+    m->cur_arena ^= 1;
+    UploadArena& N = m->arena[m->cur_arena];
+    if (N.busy) {
+        CUDA_CHECK(cudaEventSynchronize(N.done));
+        N.busy = false;
+    }
+    N.off = 0;
+    N.nseg = 0;
+    N.max_n = 0;
+}
+
+// Stage up to n samples for the slot's device ring (at most two segments when the ring wraps). Returns the number of
+// samples taken (less than n when the ring is full). The data reaches the device at the next flush_uploads().
 size_t upload_pcm(nb200_model* m, nb200_stream* s, const int16_t* pcm, size_t n) {
     const long long space = (long long)m->ring_cap - (s->fed - keep_from(s));
     n = (size_t)std::max<long long>(0, std::min<long long>((long long)n, space));
     size_t done = 0;
     while (done < n) {
-        if (m->stage_off >= m->h_stage.n) {  // staging exhausted: wait for the queued copies, then reuse it
-            CUDA_CHECK(cudaStreamSynchronize(m->st));
-            m->stage_off = 0;
+        UploadArena* A = &m->arena[m->cur_arena];
+        if (A->off >= A->pcm.n || A->nseg >= MAX_UPLOAD_SEGS) {  // arena full: send it and continue in the other one
+            flush_uploads(m);
+            A = &m->arena[m->cur_arena];
         }
         const size_t pos = (size_t)(s->fed & (long long)(m->ring_cap - 1));
-        const size_t k = std::min({n - done, m->h_stage.n - m->stage_off, (size_t)m->ring_cap - pos});
-        int16_t* stg = m->h_stage.p + m->stage_off;
-        memcpy(stg, pcm + done, k * sizeof(int16_t));
-        CUDA_CHECK(cudaMemcpyAsync(m->pcm_ring + (size_t)s->slot * m->ring_cap + pos, stg, k * sizeof(int16_t), cudaMemcpyHostToDevice, m->st));
-        m->stage_off += k;
+        const size_t k = std::min({n - done, A->pcm.n - A->off, (size_t)m->ring_cap - pos});
+        memcpy(A->pcm.p + A->off, pcm + done, k * sizeof(int16_t));
+        A->segs.p[A->nseg++] = UploadSeg{(long long)s->slot * m->ring_cap + (long long)pos, (int)A->off, (int)k};
+        A->max_n = std::max(A->max_n, (int)k);
+        A->off += k;
         s->fed += (long long)k;
         done += k;
-        m->stats.h2d_bytes += (long long)(k * sizeof(int16_t));
     }
     return n;
 }
@@ -569,13 +646,8 @@ void flush_pending(nb200_model* m, nb200_stream* s) {
     s->pending.erase(s->pending.begin(), s->pending.begin() + k);
 }
 
-struct BatchItem {
-    nb200_stream* s;
-    int n_frames;  // new mel frames computed for this chunk (shift, or fewer for a finalize tail)
-    int nvalid;    // encoder frames to decode
-};
-
-void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items);
+void run_batch_launch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items);
+void run_batch_finish(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items);
 
 }  // namespace
 
@@ -744,7 +816,8 @@ void run_graphed(nb200_model* m, std::map<long long, GraphExec>& cache, long lon
 }
 
 
-void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
+// Enqueues one batched chunk (metadata upload, encoder + decode graph, token copies) without waiting for it.
+void run_batch_launch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
     const Mode& md = mc->mode;
     const int B = (int)items.size(), T = md.T, capB = m->cap_B;
     cudaStream_t st = m->st;
@@ -789,8 +862,18 @@ void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
     CUDA_CHECK(cudaMemcpyAsync(h_margin, m->ws_tokcnt + capB, sizeof(int) * B, cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaMemcpyAsync(h_toks, m->ws_tok, sizeof(int) * (size_t)B * T * MAX_SYMBOLS, cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaEventRecord(m->ev[3], st));
-    CUDA_CHECK(cudaStreamSynchronize(st));
-    m->stage_off = 0;  // every queued audio upload has completed
+}
+
+// Waits for the batch launched by run_batch_launch and does the host bookkeeping (tokens, cache positions, statistics).
+void run_batch_finish(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
+    const Mode& md = mc->mode;
+    const int B = (int)items.size(), T = md.T, capB = m->cap_B;
+    int* h_unf = m->h_tok.p;
+    int* h_cnt = m->h_tok.p + 6;
+    int* h_margin = h_cnt + B;
+    int* h_toks = h_margin + B;
+    (void)capB;
+    CUDA_CHECK(cudaEventSynchronize(m->ev[3]));
     m->stats.d2h_bytes += (long long)sizeof(int) * ((size_t)2 * B + (size_t)B * T * MAX_SYMBOLS + 6);
     if (h_unf[0] != 0) throw Error("decode loop did not terminate");
     if (getenv("NB200_DK_TRACE")) {
@@ -853,6 +936,8 @@ void run_batch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
     }
 
 extern "C" {
+
+static int finish_inflight(nb200_model* m);
 
 const char* nb200_last_error(void) { return g_error.c_str(); }
 int nb200_version(void) { return 100; }
@@ -948,6 +1033,13 @@ nb200_stream* nb200_stream_create(nb200_model* m, int right_context) {
 void nb200_stream_free(nb200_stream* s) {
     if (!s) return;
     nb200_model* m = s->model;
+    try {  // the step in flight may reference this stream; audio staged for its slot must land before the slot is reused
+        cudaSetDevice(m->device);
+        finish_inflight(m);
+        flush_uploads(m);
+    } catch (const std::exception& e) {
+        set_error(e.what());
+    }
     m->free_slots.push_back(s->slot);
     m->streams.erase(std::remove(m->streams.begin(), m->streams.end(), s), m->streams.end());
     delete s;
@@ -957,6 +1049,8 @@ int nb200_stream_reset(nb200_stream* s) {
     NB_TRY
     if (!s) throw Error("null stream");
     CUDA_CHECK(cudaSetDevice(s->model->device));
+    finish_inflight(s->model);
+    flush_uploads(s->model);  // audio staged before the reset lands (stream-ordered) before anything fed after it
     reset_slot(s->model, s->slot);
     s->pending.clear();
     s->fed = s->samples_total = s->chunks_done = 0;
@@ -1017,9 +1111,18 @@ int nb200_stream_ready_chunks(const nb200_stream* s) {
     return n;
 }
 
-int nb200_step(nb200_model* m) {
+// Completes the step nb200_step_begin left running (no-op when there is none). Returns its stream-chunk count.
+static int finish_inflight(nb200_model* m) {
+    if (!m->inflight.active) return 0;
+    m->inflight.active = false;  // cleared first: a failure below must not leave a half-finished step behind
+    run_batch_finish(m, m->inflight.mc, m->inflight.items);
+    return m->inflight.total;
+}
+
+int nb200_step_begin(nb200_model* m) {
     NB_TRY
     if (!m) throw Error("null model");
+    if (m->inflight.active) throw Error("nb200_step_begin: the previous step has not been completed by nb200_step_end");
     CUDA_CHECK(cudaSetDevice(m->device));
     std::map<int, std::vector<BatchItem>> groups;
     for (nb200_stream* s : m->streams) {
@@ -1036,13 +1139,70 @@ int nb200_step(nb200_model* m) {
             s->finalize_requested = false;
         }
     }
+    flush_uploads(m);  // all fed audio: one copy + one scatter kernel ahead of the step's kernels
     int total = 0;
+    size_t left = groups.size();
     for (auto& kv : groups) {
-        run_batch(m, get_mode(m, kv.first), kv.second);
+        ModeCtx* mc = get_mode(m, kv.first);
         total += (int)kv.second.size();
+        run_batch_launch(m, mc, kv.second);
+        if (--left > 0) {  // the latency modes share one workspace: all but the last group complete here
+            run_batch_finish(m, mc, kv.second);
+        } else {
+            m->inflight.active = true;
+            m->inflight.mc = mc;
+            m->inflight.items = std::move(kv.second);
+        }
     }
+    m->inflight.total = total;
     return total;
     NB_CATCH(NB200_ERR)
+}
+
+int nb200_step_end(nb200_model* m) {
+    NB_TRY
+    if (!m) throw Error("null model");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    return finish_inflight(m);
+    NB_CATCH(NB200_ERR)
+}
+
+int nb200_step(nb200_model* m) {
+    const int n = nb200_step_begin(m);
+    if (n <= 0) return n;
+    return nb200_step_end(m);
+}
+
+int nb200_feed_batch(nb200_model* m, nb200_stream* const* streams, const int16_t* const* pcm, const int* n_samples, int count) {
+    if (!m || !streams || !pcm || !n_samples) return NB200_ERR;
+    for (int i = 0; i < count; i++) {
+        if (!streams[i] || streams[i]->model != m) {
+            set_error("nb200_feed_batch: stream " + std::to_string(i) + " does not belong to this model");
+            return NB200_ERR;
+        }
+        const int r = nb200_stream_feed(streams[i], pcm[i], n_samples[i]);
+        if (r < 0) return r;
+    }
+    return NB200_OK;
+}
+
+int nb200_poll_batch(nb200_model* m, nb200_stream* const* streams, int count, int32_t* tokens_out, int cap, int32_t* counts_out) {
+    if (!m || !streams || !counts_out || (!tokens_out && cap > 0)) return NB200_ERR;
+    long long need = 0;
+    for (int i = 0; i < count; i++) {
+        counts_out[i] = streams[i] ? (int)(streams[i]->tokens.size() - streams[i]->poll_cursor) : 0;
+        need += counts_out[i];
+    }
+    if (need > cap) {  // nothing is consumed: counts_out holds what is waiting, the caller retries with a larger buffer
+        set_error("nb200_poll_batch: " + std::to_string(need) + " tokens waiting, buffer holds " + std::to_string(cap));
+        return NB200_ERR;
+    }
+    int total = 0;
+    for (int i = 0; i < count; i++) {
+        if (counts_out[i] == 0) continue;
+        total += nb200_stream_poll_tokens(streams[i], tokens_out + total, counts_out[i]);
+    }
+    return total;
 }
 
 int nb200_drain(nb200_model* m) {

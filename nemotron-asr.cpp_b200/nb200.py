@@ -53,6 +53,10 @@ SYMBOLS = {
     "nb200_stream_finalize": (C.c_int, [C.c_void_p]),
     "nb200_stream_ready_chunks": (C.c_int, [C.c_void_p]),
     "nb200_step": (C.c_int, [C.c_void_p]),
+    "nb200_step_begin": (C.c_int, [C.c_void_p]),
+    "nb200_step_end": (C.c_int, [C.c_void_p]),
+    "nb200_feed_batch": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), _I32P, C.c_int]),
+    "nb200_poll_batch": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int, _I32P, C.c_int, _I32P]),
     "nb200_drain": (C.c_int, [C.c_void_p]),
     "nb200_stream_poll_tokens": (C.c_int, [C.c_void_p, _I32P, C.c_int]),
     "nb200_stream_get_tokens": (C.c_int, [C.c_void_p, _I32P, C.c_int]),
@@ -137,6 +141,22 @@ class Model:
             raise NB200Error(_err())
         return n
 
+    def step_begin(self) -> int:
+        """Launch one batched step without waiting (nb200_step_begin); feed() may go on until step_end()."""
+        n = lib().nb200_step_begin(self._h)
+        if n < 0:
+            raise NB200Error(_err())
+        return n
+
+    def step_end(self) -> int:
+        n = lib().nb200_step_end(self._h)
+        if n < 0:
+            raise NB200Error(_err())
+        return n
+
+    def batch_io(self, streams: "list[Stream]") -> "BatchIO":
+        return BatchIO(self, streams)
+
     def drain(self) -> int:
         n = lib().nb200_drain(self._h)
         if n < 0:
@@ -210,6 +230,38 @@ class Model:
         if lib().nb200_debug_matmul(self._h, tensor_name.encode(), _ptr(x, _F32P), x.shape[0], _ptr(y, _F32P)) < 0:
             raise NB200Error(_err())
         return y
+
+
+class BatchIO:
+    """Feeds / polls a fixed list of streams with one library call each (nb200_feed_batch / nb200_poll_batch)."""
+
+    def __init__(self, model: Model, streams: "list[Stream]"):
+        self.model, self.n = model, len(streams)
+        self._handles = (C.c_void_p * self.n)(*[s._h for s in streams])
+        self._ptrs = (C.c_void_p * self.n)()
+        self._ptr_view = np.frombuffer(self._ptrs, dtype=np.uint64)
+        self._lens = np.zeros(self.n, np.int32)
+        self._counts = np.zeros(self.n, np.int32)
+        self._toks = np.zeros(max(4096, 256 * self.n), np.int32)
+
+    def feed_ptrs(self, addresses: np.ndarray, n_samples):
+        """addresses: uint64 host addresses of int16 PCM, one per stream; n_samples: scalar or per-stream array."""
+        self._ptr_view[:] = addresses
+        self._lens[:] = n_samples
+        if lib().nb200_feed_batch(self.model._h, self._handles, self._ptrs, _ptr(self._lens, _I32P), self.n) < 0:
+            raise NB200Error(_err())
+
+    def poll(self):
+        """-> (tokens int32 [total], counts int32 [n_streams]) of everything emitted since the last poll."""
+        for _ in range(2):
+            n = lib().nb200_poll_batch(self.model._h, self._handles, self.n, _ptr(self._toks, _I32P), self._toks.size, _ptr(self._counts, _I32P))
+            if n >= 0:
+                return self._toks[:n].copy(), self._counts.copy()
+            need = int(self._counts.sum())
+            if need <= self._toks.size:
+                break
+            self._toks = np.zeros(need, np.int32)  # counts hold what is waiting: retry once with room for all of it
+        raise NB200Error(_err())
 
 
 class Stream:

@@ -196,6 +196,52 @@ def test_batched_equals_single(nb, model_f32):
         s.free()
 
 
+def test_pipelined_step_and_batch_io(nb, model_f32):
+    """nb200_step_begin / nb200_feed_batch (while the step runs) / nb200_step_end / nb200_poll_batch give exactly the
+    tokens of the strictly sequential per-stream calls; mixed latency modes; errors of the two-phase protocol."""
+    specs = [(13, 11, 4.6), (13, 12, 4.6), (0, 13, 1.0), (13, 14, 3.5)]
+    pcms = [inputs.pcm(seed, secs) for _, seed, secs in specs]
+    alone = [run_stream(nb, model_f32, p, rc) for (rc, _, _), p in zip(specs, pcms)]
+    streams = [model_f32.stream(rc) for rc, _, _ in specs]
+    io = model_f32.batch_io(streams)
+    piece = 17920
+    n_pieces = max(-(-len(p) // piece) for p in pcms)
+    got = [[] for _ in specs]
+
+    def feed(k):
+        bufs = [np.ascontiguousarray(p[k * piece:(k + 1) * piece]) for p in pcms]
+        io.feed_ptrs(np.array([b.ctypes.data for b in bufs], np.uint64), np.array([b.size for b in bufs], np.int32))
+
+    def collect():
+        toks, counts = io.poll()
+        off = 0
+        for i, c in enumerate(counts):
+            got[i] += toks[off:off + c].tolist()
+            off += c
+
+    feed(0)
+    for k in range(n_pieces):
+        n = model_f32.step_begin()
+        if n > 0:
+            with pytest.raises(nb.NB200Error, match="not been completed"):
+                model_f32.step_begin()
+        if k + 1 < n_pieces:
+            feed(k + 1)  # staged on the host while the step is in flight
+        assert model_f32.step_end() == n
+        collect()
+    while model_f32.step() > 0:
+        collect()
+    for s in streams:
+        nb.lib().nb200_stream_finalize(s._h)
+    while model_f32.step() > 0:
+        pass
+    collect()
+    for s, g, ref in zip(streams, got, alone):
+        assert g == ref["tokens"] and s.tokens == ref["tokens"] and s.chunk_token_counts == ref["chunk_tokens"]
+    for s in streams:
+        s.free()
+
+
 def test_feed_granularity_and_ring_overflow(nb, model_f32):
     """Slice size must not matter (src/preprocessor.cpp:389-393 keeps the tail; tests/test_preprocessor.cpp:100-105
     feeds 180-sample slices), including one 12 s feed that exceeds the 8.2 s device PCM ring (host overflow queue)."""
