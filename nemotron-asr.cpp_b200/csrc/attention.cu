@@ -286,6 +286,223 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attention_f16_kernel(AttnArgs a
     }
 }
 
+// ---- streaming kernel for the low-latency modes (T <= 2: right_context 0 and 1) -----------------------------------
+// With one or two query frames there is nothing for a tensor core to do (the MMA kernel pads to 16 query rows and
+// stages 100 KB per CTA, two CTAs per SM): the work is reading 70 K rows, 70 V rows and ~71 position rows per (stream,
+// head) exactly once. Here one WARP owns a (stream, head): every load is a fully coalesced 512-byte warp access (two
+// 256-byte rows, 16 lanes each, 16 B per lane) straight from global memory into registers, no shared-memory staging
+// of operands, ~24 warps resident per SM for latency hiding. Lane c of a half-warp holds features [8c, 8c+8) of q+u /
+// q+v in fp32; a row's dot product is 8 FMAs + a 4-step shuffle reduction over the half-warp. Probabilities stay fp32.
+template <int NQ>
+__global__ void __launch_bounds__(128) attention_stream_kernel(AttnArgs a) {
+    pdl_launch();
+    constexpr int WARPS = 4, SLD = 96;
+    __shared__ float S[WARPS][NQ][SLD];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, hw = lane >> 4, c = lane & 15;
+    const int item = blockIdx.x * WARPS + warp;
+    const int h = item & (N_HEADS - 1), b = item >> 3;  // the 4 warps of a CTA read 4 adjacent heads of the same rows
+    if (b >= a.B) return;
+    const int T = a.T, kv = LEFT + T, npos = LEFT + 2 * T - 1;
+    const int slot = a.slot[b], wpos = a.wpos[b];
+    int start = wpos - LEFT;
+    if (start < 0) start += RING;
+    __half* kring = a.k_ring + (size_t)slot * RING * D_MODEL + h * D_HEAD + c * 8;
+    __half* vring = a.v_ring + (size_t)slot * RING * D_MODEL + h * D_HEAD + c * 8;
+    const __half* pbase = a.pos + h * D_HEAD + c * 8;
+    float (*Sw)[SLD] = S[warp];
+
+    // position scores first: the table was written at load time, so this part overlaps the QKV GEMM's tail (PDL) --
+    // but it needs q. So only the addresses are prepared here; everything that depends on qkv follows the wait.
+    pdl_wait();
+    const __half* qkv = a.qkv + (size_t)b * T * (3 * D_MODEL) + h * D_HEAD + c * 8;
+    float qu[NQ][8], qv[NQ][8];
+    {
+        const float4 u0 = *reinterpret_cast<const float4*>(a.bias_u + h * D_HEAD + c * 8), u1 = *reinterpret_cast<const float4*>(a.bias_u + h * D_HEAD + c * 8 + 4);
+        const float4 v0 = *reinterpret_cast<const float4*>(a.bias_v + h * D_HEAD + c * 8), v1 = *reinterpret_cast<const float4*>(a.bias_v + h * D_HEAD + c * 8 + 4);
+        const float uu[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+        const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+        for (int i = 0; i < NQ; i++) {
+            uint4 q8 = make_uint4(0, 0, 0, 0);
+            if (i < T) q8 = *reinterpret_cast<const uint4*>(qkv + (size_t)i * (3 * D_MODEL));
+            const __half2* qh = reinterpret_cast<const __half2*>(&q8);
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const float2 f = __half22float2(qh[e]);
+                qu[i][2 * e] = f.x + uu[2 * e]; qu[i][2 * e + 1] = f.y + uu[2 * e + 1];
+                qv[i][2 * e] = f.x + vv[2 * e]; qv[i][2 * e + 1] = f.y + vv[2 * e + 1];
+            }
+        }
+    }
+    auto dot8 = [](const uint4& r, const float (&q)[8]) {
+        const __half2* rh = reinterpret_cast<const __half2*>(&r);
+        float s = 0.0f;
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const float2 f = __half22float2(rh[e]);
+            s = fmaf(f.x, q[2 * e], s);
+            s = fmaf(f.y, q[2 * e + 1], s);
+        }
+        return s;
+    };
+    auto half_sum = [](float s) {  // sum over the 16 lanes of a half-warp
+        s += __shfl_xor_sync(0xffffffffu, s, 8);
+        s += __shfl_xor_sync(0xffffffffu, s, 4);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        return s;
+    };
+    constexpr int UN = 6;  // rows in flight per half-warp: 6 x 512 B per warp
+    const uint4 z4 = make_uint4(0, 0, 0, 0);
+
+    // ---- key scores (Q+u).K_j; this chunk's key rows come from qkv and are appended to the ring on the way ----
+    for (int j0 = 0; j0 < kv; j0 += 2 * UN) {
+        uint4 r[UN];
+#pragma unroll
+        for (int u = 0; u < UN; u++) {
+            const int j = j0 + 2 * u + hw;
+            r[u] = z4;
+            if (j < LEFT) {
+                int pos = start + j;
+                if (pos >= RING) pos -= RING;
+                r[u] = *reinterpret_cast<const uint4*>(kring + (size_t)pos * D_MODEL);
+            } else if (j < kv) {
+                r[u] = *reinterpret_cast<const uint4*>(qkv + (size_t)(j - LEFT) * (3 * D_MODEL) + D_MODEL);
+                int pos = wpos + (j - LEFT);
+                if (pos >= RING) pos -= RING;
+                *reinterpret_cast<uint4*>(kring + (size_t)pos * D_MODEL) = r[u];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < UN; u++) {
+            const int j = j0 + 2 * u + hw;
+#pragma unroll
+            for (int i = 0; i < NQ; i++) {
+                const float d = half_sum(dot8(r[u], qu[i]));
+                if (c == 0 && j < kv) Sw[i][j] = d;
+            }
+        }
+    }
+    __syncwarp();
+    // ---- position scores (Q+v).P_r, added at key j = LEFT + i + T - 1 - r (the reference's rel-shift) ----
+    for (int r0 = 0; r0 < npos; r0 += 2 * UN) {
+        uint4 r[UN];
+#pragma unroll
+        for (int u = 0; u < UN; u++) {
+            const int rr = r0 + 2 * u + hw;
+            r[u] = rr < npos ? *reinterpret_cast<const uint4*>(pbase + (size_t)rr * D_MODEL) : z4;
+        }
+#pragma unroll
+        for (int u = 0; u < UN; u++) {
+            const int rr = r0 + 2 * u + hw;
+#pragma unroll
+            for (int i = 0; i < NQ; i++) {
+                const float d = half_sum(dot8(r[u], qv[i]));
+                const int j = LEFT + i + T - 1 - rr;
+                if (c == 0 && i < T && rr < npos && j >= 0 && j < kv) Sw[i][j] += d;
+            }
+        }
+    }
+    __syncwarp();
+    // ---- scale, mask, softmax (fp32) ----
+    {
+        const int masked = LEFT - a.valid[b];
+        const float scale = 1.0f / sqrtf((float)D_HEAD);
+#pragma unroll
+        for (int i = 0; i < NQ; i++) {
+            if (i >= T) break;
+            float sc[3];
+            float mx = -INFINITY;
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+                const int j = lane + 32 * q;
+                float s = -INFINITY;
+                if (j < kv) {
+                    s = Sw[i][j] * scale;
+                    if (j < masked) s += -1e9f;
+                }
+                sc[q] = s;
+                mx = fmaxf(mx, s);
+            }
+            mx = warp_max(mx);
+            float sum = 0.0f;
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+                const int j = lane + 32 * q;
+                sc[q] = (j < kv) ? expf(sc[q] - mx) : 0.0f;
+                sum += sc[q];
+            }
+            sum = warp_sum(sum);
+            const float inv = 1.0f / sum;
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+                const int j = lane + 32 * q;
+                if (j < SLD) Sw[i][j] = sc[q] * inv;
+            }
+        }
+    }
+    __syncwarp();
+    // ---- context: each half-warp accumulates every other key row, lane c owns features [8c, 8c+8) ----
+    float acc[NQ][8];
+#pragma unroll
+    for (int i = 0; i < NQ; i++)
+#pragma unroll
+        for (int e = 0; e < 8; e++) acc[i][e] = 0.0f;
+    for (int j0 = 0; j0 < kv; j0 += 2 * UN) {
+        uint4 r[UN];
+#pragma unroll
+        for (int u = 0; u < UN; u++) {
+            const int j = j0 + 2 * u + hw;
+            r[u] = z4;
+            if (j < LEFT) {
+                int pos = start + j;
+                if (pos >= RING) pos -= RING;
+                r[u] = *reinterpret_cast<const uint4*>(vring + (size_t)pos * D_MODEL);
+            } else if (j < kv) {
+                r[u] = *reinterpret_cast<const uint4*>(qkv + (size_t)(j - LEFT) * (3 * D_MODEL) + 2 * D_MODEL);
+                int pos = wpos + (j - LEFT);
+                if (pos >= RING) pos -= RING;
+                *reinterpret_cast<uint4*>(vring + (size_t)pos * D_MODEL) = r[u];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < UN; u++) {
+            const int j = j0 + 2 * u + hw;
+            const __half2* rh = reinterpret_cast<const __half2*>(&r[u]);
+#pragma unroll
+            for (int i = 0; i < NQ; i++) {
+                const float p = (j < kv) ? Sw[i][j] : 0.0f;
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const float2 f = __half22float2(rh[e]);
+                    acc[i][2 * e] = fmaf(p, f.x, acc[i][2 * e]);
+                    acc[i][2 * e + 1] = fmaf(p, f.y, acc[i][2 * e + 1]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < NQ; i++) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) acc[i][e] += __shfl_xor_sync(0xffffffffu, acc[i][e], 16);
+        if (a.act_quant) {  // 32 consecutive features = 4 adjacent lanes
+            float amax = 0.0f;
+#pragma unroll
+            for (int e = 0; e < 8; e++) amax = fmaxf(amax, fabsf(acc[i][e]));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+#pragma unroll
+            for (int e = 0; e < 8; e++) acc[i][e] = fake_quant(acc[i][e], amax);
+        }
+        if (hw == 0 && i < T) {
+            __half2 o[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) o[e] = __floats2half2_rn(acc[i][2 * e], acc[i][2 * e + 1]);
+            *reinterpret_cast<uint4*>(a.out + ((size_t)(b * T + i)) * D_MODEL + h * D_HEAD + c * 8) = *reinterpret_cast<const uint4*>(o);
+        }
+    }
+}
+
 // ---- fp32 CUDA-core checker (NB200_ATTN_SIMT=1): same inputs and outputs, no tensor cores, no staging tricks ----
 __global__ void __launch_bounds__(256) attention_simt_kernel(AttnArgs a) {
     pdl_prologue();
@@ -382,6 +599,19 @@ void launch_attention(cudaStream_t st, const AttnArgs& a) {
     if (use_simt) {
         ProfScope ps(st, "attention_simt", flops, bytes);
         launch_k(attention_simt_kernel, dim3(dim3(N_HEADS, a.B)), dim3(256), 0, st, a);
+        NB_KERNEL_CHECK();
+        return;
+    }
+    static const bool no_stream_kernel = getenv("NB200_ATTN_MMA_ONLY") != nullptr;
+    if (a.T <= 2 && !no_stream_kernel) {
+        ProfScope ps(st, "attention_stream", flops, bytes);
+        const dim3 grid(cdiv(a.B * N_HEADS, 4));
+        for (int rep = dup_family("attention") ? 2 : 1; rep > 0; rep--) {
+            if (a.T == 1)
+                launch_k(attention_stream_kernel<1>, grid, dim3(128), 0, st, a);
+            else
+                launch_k(attention_stream_kernel<2>, grid, dim3(128), 0, st, a);
+        }
         NB_KERNEL_CHECK();
         return;
     }

@@ -198,48 +198,69 @@ def test_batched_equals_single(nb, model_f32):
 
 def test_pipelined_step_and_batch_io(nb, model_f32):
     """nb200_step_begin / nb200_feed_batch (while the step runs) / nb200_step_end / nb200_poll_batch give exactly the
-    tokens of the strictly sequential per-stream calls; mixed latency modes; errors of the two-phase protocol."""
+    tokens of the strictly sequential per-stream calls on the same schedule (same batches, same kernels: bit-identical);
+    mixed latency modes; the error of the two-phase protocol."""
     specs = [(13, 11, 4.6), (13, 12, 4.6), (0, 13, 1.0), (13, 14, 3.5)]
     pcms = [inputs.pcm(seed, secs) for _, seed, secs in specs]
-    alone = [run_stream(nb, model_f32, p, rc) for (rc, _, _), p in zip(specs, pcms)]
-    streams = [model_f32.stream(rc) for rc, _, _ in specs]
-    io = model_f32.batch_io(streams)
     piece = 17920
     n_pieces = max(-(-len(p) // piece) for p in pcms)
-    got = [[] for _ in specs]
 
-    def feed(k):
-        bufs = [np.ascontiguousarray(p[k * piece:(k + 1) * piece]) for p in pcms]
-        io.feed_ptrs(np.array([b.ctypes.data for b in bufs], np.uint64), np.array([b.size for b in bufs], np.int32))
+    def run(pipelined: bool):
+        streams = [model_f32.stream(rc) for rc, _, _ in specs]
+        io = model_f32.batch_io(streams)
+        got = [[] for _ in specs]
 
-    def collect():
-        toks, counts = io.poll()
-        off = 0
-        for i, c in enumerate(counts):
-            got[i] += toks[off:off + c].tolist()
-            off += c
+        def feed(k):
+            bufs = [np.ascontiguousarray(p[k * piece:(k + 1) * piece]) for p in pcms]
+            if pipelined:
+                io.feed_ptrs(np.array([b.ctypes.data for b in bufs], np.uint64), np.array([b.size for b in bufs], np.int32))
+            else:
+                for s, b in zip(streams, bufs):
+                    s.feed(b)
 
-    feed(0)
-    for k in range(n_pieces):
-        n = model_f32.step_begin()
-        if n > 0:
-            with pytest.raises(nb.NB200Error, match="not been completed"):
-                model_f32.step_begin()
-        if k + 1 < n_pieces:
-            feed(k + 1)  # staged on the host while the step is in flight
-        assert model_f32.step_end() == n
+        def collect():
+            if pipelined:
+                toks, counts = io.poll()
+                off = 0
+                for i, c in enumerate(counts):
+                    got[i] += toks[off:off + c].tolist()
+                    off += c
+            else:
+                for i, s in enumerate(streams):
+                    got[i] += s.poll_tokens()
+
+        feed(0)
+        for k in range(n_pieces):
+            if pipelined:
+                n = model_f32.step_begin()
+                if n > 0:
+                    with pytest.raises(nb.NB200Error, match="not been completed"):
+                        model_f32.step_begin()
+                if k + 1 < n_pieces:
+                    feed(k + 1)  # staged on the host while the step is in flight
+                assert model_f32.step_end() == n
+            else:
+                model_f32.step()
+                if k + 1 < n_pieces:
+                    feed(k + 1)
+            collect()
+        while model_f32.step() > 0:
+            collect()
+        for s in streams:
+            nb.lib().nb200_stream_finalize(s._h)
+        while model_f32.step() > 0:
+            pass
         collect()
-    while model_f32.step() > 0:
-        collect()
-    for s in streams:
-        nb.lib().nb200_stream_finalize(s._h)
-    while model_f32.step() > 0:
-        pass
-    collect()
-    for s, g, ref in zip(streams, got, alone):
-        assert g == ref["tokens"] and s.tokens == ref["tokens"] and s.chunk_token_counts == ref["chunk_tokens"]
-    for s in streams:
-        s.free()
+        res = [(g, s.tokens, s.chunk_token_counts) for g, s in zip(got, streams)]
+        for s in streams:
+            s.free()
+        return res
+
+    seq, pipe = run(False), run(True)
+    for (rc, _, secs), a, b in zip(specs, seq, pipe):
+        assert a[0] == a[1] and b[0] == b[1]  # polled tokens == nemo_stream_get_tokens
+        assert a == b
+        assert len(a[2]) > 0
 
 
 def test_feed_granularity_and_ring_overflow(nb, model_f32):
