@@ -305,6 +305,61 @@ def test_reset_reuse_and_errors(nb, model_f32):
     empty.free()
 
 
+def test_mel_batch_sweep_is_batch_invariant(nb, model_q8):
+    """BASELINE.json config 4 (frontend only, batch sweep): the log-mel of a signal must not depend on how many streams
+    share the launch, nor on its position in the batch: bit-identical for B = 1 .. 1024."""
+    pcm = inputs.pcm(11, 4.0)
+    ref = np.load(GOLD / "mel_s11.npz")["mel"]
+    one = model_q8.mel_batch(pcm[None])[0]
+    assert np.abs(one - ref).max() <= 4e-6
+    rng = np.random.default_rng(5)
+    for B in (4, 64, 1024):
+        sig = rng.integers(-20000, 20000, (B, pcm.size), dtype=np.int16)
+        where = sorted({0, B // 2, B - 1})
+        for w in where:
+            sig[w] = pcm
+        got = model_q8.mel_batch(sig)
+        for w in where:
+            assert np.array_equal(got[w], one), (B, w)
+
+
+def test_longform_cache_rollforward(nb, model_f32, oracle_f32):
+    """BASELINE.json config 5 in miniature (cache roll-forward stress): 30 s at right_context 13 and 8 s at 0 against the
+    numpy oracle. The K/V ring (84 rows) wraps 5 and 1.2 times, the device PCM ring (8.2 s) 3.7 times, cache_valid_len
+    saturates; the per-chunk error must not grow with time, and device memory must not grow while stepping."""
+    import torch
+    kv, t = oracle_f32
+    for rc, seed, secs in ((13, 31, 30.0), (0, 32, 8.0)):
+        pcm = inputs.pcm(seed, secs)
+        o = no.StreamOracle(kv, t, rc)
+        o.feed(pcm)
+        o.finalize()
+        s = model_f32.stream(rc)
+        s.set_taps(nb.TAP_ENC)
+        cs = 8 * (1 + rc) * 160
+        free0 = None
+        for k, i in enumerate(range(0, len(pcm), cs)):
+            s.process_incremental(pcm[i:i + cs])
+            if k == 2:
+                free0 = torch.cuda.mem_get_info(0)[0]
+        s.finalize()
+        assert torch.cuda.mem_get_info(0)[0] >= free0 - (8 << 20), "device memory grew while stepping"
+        enc = s.fetch_tap(nb.TAP_ENC).reshape(-1, 1 + rc, 1024)
+        ref = np.stack(o.enc_chunks)
+        assert enc.shape == ref.shape
+        rels = np.array([rel(a, b) for a, b in zip(enc, ref)])
+        n = len(rels)
+        assert rels.max() < 3e-3, rels
+        assert rels[n // 2:].mean() < 2.0 * rels[: n // 2].mean() + 1e-4, "error grows along the stream"
+        got = {"tokens": s.tokens, "chunk_tokens": s.chunk_token_counts, "margins": s.chunk_margins}
+        same, comparable, margin = compare_tokens(got, o.tokens, o.chunk_tokens)
+        print(f"long-form rc={rc}: {n} chunks, enc rel first/second half {rels[: n // 2].mean():.2e}/{rels[n // 2:].mean():.2e}, "
+              f"token chunks identical {same}/{comparable}, mismatch margin {margin}")
+        if margin is not None:
+            assert margin < TIE_GAP
+        s.free()
+
+
 def test_smoke_entry(nb):
     import __graft_entry__ as ge
     ge.smoke()
