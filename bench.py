@@ -308,7 +308,15 @@ def main():
     else:
         ach = d["bytes"] / (d["ms"] * 1e-3) / 1e9
         roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"]}
-    roofline.update({"traffic": None, "peak_source": pk["source"], "share_of_step": d["ms"] / tot_ms, "avg_launch_us": per_launch_ms * 1e3,
+    traffic = None
+    try:  # DRAM bytes per launch of this kernel family from this round's ncu --set full capture (profiles/ncu_traffic.json)
+        if a.streams == 64 or dom == "attention_stream":
+            traffic = json.loads((ROOT / "profiles" / "ncu_traffic.json").read_text()).get(dom, {}).get("traffic")
+    except Exception:
+        traffic = None
+    roofline.update({"traffic": traffic, "algorithmic": (d["flops"] if dom.startswith("gemm") else d["bytes"]) / d["launches"],
+                     "timing": "CUDA events around every launch of an eager (non-graph) pass; in the graph the same launches cost less "
+                               "(DESIGN.md section 4: GEMMs 587 TFLOP/s in-graph)", "peak_source": pk["source"], "share_of_step": d["ms"] / tot_ms, "avg_launch_us": per_launch_ms * 1e3,
                      "launches_per_step": d["launches"] // 2})
     kernels = {k: {"share": round(v["ms"] / tot_ms, 4), "launches_per_step": v["launches"] // 2, "avg_us": round(v["ms"] / v["launches"] * 1e3, 2),
                    "tflops": round(v["flops"] / (v["ms"] * 1e-3) / 1e12, 2), "gbs": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 1)}

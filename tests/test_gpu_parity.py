@@ -360,6 +360,26 @@ def test_longform_cache_rollforward(nb, model_f32, oracle_f32):
         s.free()
 
 
+def test_server_loop_batches(nb, gguf_f32, tmp_path):
+    """the cross-stream batching worker (nemotron-asr.cpp_b200/server_loop.h, C++ over the C ABI).
+    10 sessions in all four latency modes, fed in 100 ms packets by two reader threads, must produce the texts of the
+    reference's serial order (one stream at a time), close every session once, and really batch (max_batch > 1)."""
+    import json
+    import subprocess
+    root = GOLD.parents[1]
+    exe = tmp_path / "server_loop_test"
+    pkg = root / "nemotron-asr.cpp_b200"
+    subprocess.run(["g++", "-std=c++17", "-O2", "-I", str(root / "include"), "-I", str(pkg), str(root / "tests" / "server_loop_test.cpp"),
+                    "-o", str(exe), "-L", str(pkg), "-lnemob200", f"-Wl,-rpath,{pkg}", "-lpthread"], check=True)
+    pcms = [inputs.pcm_path(41, 5.0), inputs.pcm_path(42, 3.7), inputs.pcm_path(43, 4.4)]
+    r = subprocess.run([str(exe), gguf_f32, "10", *pcms], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
+    print(r.stdout, r.stderr[-2000:])
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    assert d["mismatches"] == 0 and d["not_closed"] == 0 and d["errors"] == 0
+    assert d["max_batch"] > 1 and d["stream_chunks"] > d["steps"]
+
+
 def test_smoke_entry(nb):
     import __graft_entry__ as ge
     ge.smoke()
