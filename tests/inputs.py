@@ -40,6 +40,14 @@ STREAM_CASES = (
 )
 
 
+# the converter's other on-disk formats: checked against the compiled reference on the GPU path only
+FORMAT_CASES = (
+    ("f16", 13, 11, 3.0),
+    ("q4_0", 13, 11, 3.0),
+    ("q4_0", 0, 12, 1.5),
+)
+
+
 def gguf_path(variant: str, layers: int = TEST_LAYERS, blank_gain: float | None = None) -> str:
     import make_random_gguf as mg
     TMP.mkdir(parents=True, exist_ok=True)

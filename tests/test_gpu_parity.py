@@ -171,6 +171,42 @@ def test_stream_q8_within_reference_self_noise(nb, model_q8, rc):
     assert same >= min(ref_self, n) // 2
 
 
+def test_format_f16_matches_reference(nb, lib_built):
+    """an F16 GGUF (convert_to_gguf.py --quantize f16). ggml-CPU multiplies F16 weights by activations
+    rounded to fp16 with fp32 accumulation, which is what the tcgen05 path does natively: same tolerance as the F32 file."""
+    variant, rc, seed, secs = inputs.FORMAT_CASES[0]
+    gold = np.load(GOLD / f"stream_{variant}_rc{rc}.npz")
+    model = nb.Model(inputs.gguf_path(variant), device=0, max_streams=4)
+    assert model.info.weights_quantized == 0 and model.info.act_quant == 0
+    got = run_stream(nb, model, inputs.pcm(seed, secs), rc)
+    model.close()
+    assert got["enc"].shape == gold["enc"].shape
+    rels = [rel(a, b) for a, b in zip(got["enc"], gold["enc"])]
+    print(f"f16 rc={rc}: enc rel {rels}")
+    assert max(rels) < 3e-3, rels
+    same, comparable, margin = compare_tokens(got, gold["tokens"], gold["chunk_tokens"])
+    if margin is not None:
+        assert margin < TIE_GAP, f"token mismatch in chunk {same} is not a near-tie (gap {margin})"
+
+
+@pytest.mark.parametrize("variant,rc,seed,secs", [c for c in inputs.FORMAT_CASES if c[0] == "q4_0"])
+def test_format_q4_0_within_reference_self_noise(nb, lib_built, variant, rc, seed, secs):
+    """a Q4_0 GGUF. ggml-CPU re-quantises the activations to Q8_0 blocks for Q4_0 weights too
+    (vec_dot_type of Q4_0 is Q8_0), so this is the chaotic path again: inside the reference's own ISA-to-ISA envelope."""
+    gold = np.load(GOLD / f"stream_{variant}_rc{rc}.npz")
+    model = nb.Model(inputs.gguf_path(variant), device=0, max_streams=4)
+    assert model.info.weights_quantized == 1 and model.info.act_quant == 1
+    got = run_stream(nb, model, inputs.pcm(seed, secs), rc)
+    model.close()
+    assert got["enc"].shape == gold["enc"].shape
+    n = got["enc"].shape[0]
+    self_noise = np.array([rel(gold["enc_alt"][c], gold["enc"][c]) for c in range(n)])
+    ours = np.array([min(rel(got["enc"][c], gold["enc"][c]), rel(got["enc"][c], gold["enc_alt"][c])) for c in range(n)])
+    print(f"q4_0 rc={rc}: ours median {np.median(ours):.2e} max {ours.max():.2e}; reference self-noise median {np.median(self_noise):.2e} max {self_noise.max():.2e}")
+    assert np.median(ours) < 1e-2
+    assert ours.max() <= 1.6 * self_noise.max(), (ours, self_noise)
+
+
 def test_batched_equals_single(nb, model_f32):
     """Cross-stream batching must not change any stream's result: 5 streams in mixed latency modes, stepped together,
     equal the same streams run alone (same kernels, same per-row arithmetic)."""

@@ -11,7 +11,7 @@ The on-disk format follows the reference's converter, which defines it:
 
 Everything is a pure function of (seed, tensor name), so the GPU box regenerates byte-identical files.
 variants: q8_0 (11 matrices/layer as Q8_0), f32 (same weights unquantised), f32dq (F32 file holding the
-dequantised Q8_0 weights).
+dequantised Q8_0 weights), f16 and q4_0 (the converter's other two --quantize modes, convert_to_gguf.py:157-204,322-336).
 """
 from __future__ import annotations
 
@@ -22,7 +22,7 @@ import zlib
 
 import numpy as np
 
-GGML_F32, GGML_F16, GGML_Q8_0 = 0, 1, 8
+GGML_F32, GGML_F16, GGML_Q4_0, GGML_Q8_0 = 0, 1, 2, 8
 ALIGN = 32
 
 N_MELS, D_MODEL, N_HEADS, D_HEAD, D_FF, KERNEL = 128, 1024, 8, 128, 4096, 9
@@ -59,6 +59,24 @@ def q8_0_bytes(a: np.ndarray) -> bytes:
     out = np.empty(scales.shape[0], dtype=np.dtype([("d", np.float16), ("q", np.int8, 32)]))
     out["d"] = scales
     out["q"] = q
+    return out.tobytes()
+
+
+def q4_0_bytes(a: np.ndarray) -> bytes:
+    """Q4_0 blocks the way the converter writes them (convert_to_gguf.py:157-204): fp16 d = amax/7, q = clip(rne(x/d), -8, 7),
+    byte j = (q[j] + 8) | (q[j + 16] + 8) << 4."""
+    blocks = a.astype(np.float32).reshape(-1, 32)
+    amax = np.max(np.abs(blocks), axis=1)
+    scales = np.where(amax != 0, amax / 7.0, 0.0).astype(np.float16)
+    s32 = scales.astype(np.float32)[:, None]
+    safe = np.where(s32 != 0, s32, 1.0)
+    q = np.clip(np.round(blocks / safe).astype(np.int8), -8, 7)
+    q = np.where(s32 != 0, q, 0)
+    u = (q + 8).astype(np.uint8)
+    packed = ((u[:, :16] & 0x0F) | ((u[:, 16:] & 0x0F) << 4)).astype(np.uint8)
+    out = np.empty(scales.shape[0], dtype=np.dtype([("d", np.float16), ("q", np.uint8, 16)]))
+    out["d"] = scales
+    out["q"] = packed
     return out.tobytes()
 
 
@@ -172,7 +190,7 @@ def _w_str(f, sbytes: bytes):
 
 
 def write_gguf(path: str, seed: int = 1234, n_layers: int = 24, variant: str = "q8_0", blank_gain: float | None = None) -> dict:
-    assert variant in ("q8_0", "f32", "f32dq")
+    assert variant in ("q8_0", "f32", "f32dq", "f16", "q4_0")
     vocab = [("▁" if i % 3 == 0 else "") + f"t{i}" for i in range(VOCAB - 1)]
     hparams = [("nemo.n_mels", N_MELS), ("nemo.d_model", D_MODEL), ("nemo.n_heads", N_HEADS), ("nemo.d_head", D_HEAD),
                ("nemo.d_ff", D_FF), ("nemo.n_layers", n_layers), ("nemo.kernel_size", KERNEL), ("nemo.vocab_size", VOCAB),
@@ -184,6 +202,10 @@ def write_gguf(path: str, seed: int = 1234, n_layers: int = 24, variant: str = "
         arr = np.ascontiguousarray(arr, dtype=np.float32)
         if quantisable and variant == "q8_0":
             data, typ = q8_0_bytes(arr), GGML_Q8_0
+        elif quantisable and variant == "q4_0":
+            data, typ = q4_0_bytes(arr), GGML_Q4_0
+        elif quantisable and variant == "f16":
+            data, typ = arr.astype(np.float16).tobytes(), GGML_F16
         elif quantisable and variant == "f32dq":
             data, typ = dequantize_q8_0(arr).astype(np.float32).tobytes(), GGML_F32
         else:
@@ -227,7 +249,7 @@ def main(argv=None):
     ap.add_argument("out")
     ap.add_argument("--seed", type=int, default=1234)
     ap.add_argument("--layers", type=int, default=24)
-    ap.add_argument("--variant", default="q8_0", choices=("q8_0", "f32", "f32dq"))
+    ap.add_argument("--variant", default="q8_0", choices=("q8_0", "f32", "f32dq", "f16", "q4_0"))
     ap.add_argument("--blank-gain", type=float, default=None)
     a = ap.parse_args(argv)
     print(write_gguf(a.out, a.seed, a.layers, a.variant, a.blank_gain))
