@@ -74,6 +74,13 @@ int nb200_tokens_to_text(const nb200_model* m, const int32_t* tokens, int n, cha
 
 /* nemo_stream_init(ctx, cfg) with cfg.att_right_context in {0,1,6,13} — src/nemo-stream.h:271, .cpp:696-733 */
 nb200_stream* nb200_stream_create(nb200_model* m, int right_context);
+/* nemo_stream_set_language — src/nemo-stream.h:279, src/nemo-stream.cpp:735-749 (multilingual checkpoints: the language
+ * code is looked up in the GGUF's nemo.prompt_langs / nemo.prompt_ids; it may change between chunks). Fails like the
+ * reference (which returns false) when the model has no prompts or the code is unknown. New streams start with the
+ * loader's default prompt 101 = "auto" (src/nemo-ggml.cpp:459-462). _set_prompt_index sets the field the server writes
+ * directly (sctx->prompt_index, src/nemo-server.cpp:244). */
+int nb200_stream_set_language(nb200_stream* s, const char* lang);
+int nb200_stream_set_prompt_index(nb200_stream* s, int prompt_index);
 /* nemo_stream_free — src/nemo-stream.h:324 */
 void nb200_stream_free(nb200_stream* s);
 /* nemo_stream_reset — src/nemo-stream.h:319 (this backend also re-zeroes the conv cache; the reference does not) */

@@ -17,6 +17,7 @@ constexpr int VOCAB = 1025, BLANK = 1024, DEC = 640, JOINT = 640, LEFT = 70, CON
 constexpr int SUB_CH = 256, SUB_F1 = 65, SUB_F2 = 33, SUB_F3 = 17, SUB_FEAT = SUB_CH * SUB_F3;  // 4352
 constexpr int N_FFT = 512, HOP = 160, N_BINS = 257, MEL_OVERLAP = 9;
 constexpr int RING = 84;          // K/V ring capacity: 70 cached + up to 14 new frames
+constexpr int PROMPT_HIDDEN = 2048;  // prompt_kernel hidden width (multilingual checkpoints)
 constexpr int MAX_T = 14;         // encoder frames per chunk at right_context 13
 constexpr int MAX_SYMBOLS = 10;   // src/nemo-stream.cpp:849
 

@@ -139,6 +139,27 @@ void launch_dwconv(cudaStream_t st, const ConvArgs& a) {
 }
 
 // ---- helpers for the positional table ---------------------------------------------------------------
+// ---- prompt fusion, one-hot half of fc1 + ReLU: concat([enc ; onehot(lang)]) . W1^T = enc . W1[:, :1024]^T + W1[:, 1024 + lang] ----
+__global__ void __launch_bounds__(256) prompt_add_relu_kernel(float* __restrict__ h, const float* __restrict__ w_lang, const int* __restrict__ lang, int T) {
+    pdl_prologue();
+    const int m = blockIdx.x;
+    const float* wl = w_lang + (size_t)lang[m / T] * PROMPT_HIDDEN;
+    float* row = h + (size_t)m * PROMPT_HIDDEN;
+    for (int c = threadIdx.x * 4; c < PROMPT_HIDDEN; c += 1024) {
+        float4 v = *reinterpret_cast<float4*>(row + c);
+        const float4 w = *reinterpret_cast<const float4*>(wl + c);
+        v.x = fmaxf(v.x + w.x, 0.0f); v.y = fmaxf(v.y + w.y, 0.0f); v.z = fmaxf(v.z + w.z, 0.0f); v.w = fmaxf(v.w + w.w, 0.0f);
+        *reinterpret_cast<float4*>(row + c) = v;
+    }
+}
+
+void launch_prompt_add_relu(cudaStream_t st, float* h, const float* w_lang, const int* lang, int T, int M) {
+    if (M <= 0) return;
+    ProfScope ps(st, "prompt_add_relu", (double)M * PROMPT_HIDDEN * 2, (double)M * PROMPT_HIDDEN * 8);
+    launch_k(prompt_add_relu_kernel, dim3(M), dim3(256), 0, st, h, w_lang, lang, T);
+    NB_KERNEL_CHECK();
+}
+
 __global__ void __launch_bounds__(256) cast_f16_kernel(const float* __restrict__ x, __half* __restrict__ out, int act_quant, int cols) {
     pdl_prologue();
     const size_t row = blockIdx.x;

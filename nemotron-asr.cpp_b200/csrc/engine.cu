@@ -110,6 +110,7 @@ struct nb200_stream {
     size_t poll_cursor = 0;
     std::vector<int32_t> chunk_tokens;
     std::vector<float> chunk_margins;  // per chunk: smallest top1-top2 logit gap of its symbol steps
+    int prompt_index = -1;  // multilingual checkpoints: language prompt id (src/nemo-stream.h prompt_index); -1 = model has none
     int taps = 0;
     std::vector<float> tap_mel, tap_enc;
 };
@@ -129,6 +130,11 @@ struct nb200_model {
     float *sub_b3 = nullptr, *sub_b6 = nullptr, *sub_bout = nullptr;
     F16Matrix sub_w3, sub_w6, sub_wout;
     float *joint_enc_w = nullptr, *joint_enc_b = nullptr;  // fp32: the decoder side stays in fp32 like the reference
+    // multilingual prompt fusion (src/nemo-ggml.cpp:1087-1105), fp32 like the file: fc1 split into its encoder part
+    // [2048][1024] and its one-hot part stored per language [num_prompts][2048]; fc2 [1024][2048]
+    int num_prompts = 0, default_prompt = -1;
+    float *pk_w1 = nullptr, *pk_w1_lang = nullptr, *pk_b1 = nullptr, *pk_w2 = nullptr, *pk_b2 = nullptr;
+    std::map<std::string, int> prompt_dict;
     std::vector<LayerW> layers;
     DecodeWeights dec{};
     struct NamedMatrix {   // GGUF tensor name -> where its rows live in our (possibly fused / interleaved) fp16 storage
@@ -152,6 +158,7 @@ struct nb200_model {
     float *ws_mel = nullptr, *ws_a3 = nullptr, *ws_x = nullptr, *ws_g = nullptr, *ws_e = nullptr;
     __half *ws_a2h = nullptr, *ws_a5h = nullptr, *ws_a6h = nullptr, *ws_a16 = nullptr, *ws_h16 = nullptr, *ws_pos16 = nullptr, *ws_qkv16 = nullptr;
     float* ws_posf = nullptr;
+    float* ws_pk = nullptr;        // prompt fusion hidden layer [rows][2048] fp32 (multilingual checkpoints only)
     float* ws_part = nullptr;      // split-K partial outputs of the residual GEMMs: [splits][part_rows][1024]
     size_t part_rows = 0;
     int part_max_splits = 1;
@@ -264,7 +271,7 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
         hp.vocab_size != VOCAB || hp.decoder_dim != DEC || hp.joint_dim != JOINT || hp.subsampling_factor != 8 ||
         hp.att_left_context != LEFT)
         throw Error("this backend is built for the nemotron-speech-streaming 0.6B architecture; the GGUF header differs");
-    if (hp.num_prompts != 0) throw Error("multilingual prompt fusion (num_prompts > 0) is not supported by this backend yet");
+    if (hp.num_prompts < 0 || hp.num_prompts > 4096) throw Error("nemo.num_prompts out of range");
     m->n_layers = hp.n_layers;
     // vocabulary (src/nemo-ggml.cpp:149-169)
     if (g.str_arr.count("tokenizer.vocab_list")) {
@@ -413,6 +420,28 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
         m->joint_enc_w = m->upload(load_f32(g, "joint.enc.weight", (int64_t)JOINT * D_MODEL));
         m->joint_enc_b = m->upload(load_f32(g, "joint.enc.bias", JOINT));
     }
+    m->num_prompts = hp.num_prompts;
+    if (hp.num_prompts > 0) {  // the prompt kernel must be present exactly when the header advertises prompts (src/nemo-ggml.cpp:424-434)
+        const int P = hp.num_prompts, H = PROMPT_HIDDEN;
+        std::vector<float> w1 = load_f32(g, "prompt_kernel.0.weight", (int64_t)H * (D_MODEL + P));
+        std::vector<float> a((size_t)H * D_MODEL), l((size_t)P * H);
+        for (int n = 0; n < H; n++) {
+            memcpy(&a[(size_t)n * D_MODEL], &w1[(size_t)n * (D_MODEL + P)], D_MODEL * sizeof(float));
+            for (int q = 0; q < P; q++) l[(size_t)q * H + n] = w1[(size_t)n * (D_MODEL + P) + D_MODEL + q];
+        }
+        m->pk_w1 = m->upload(a);
+        m->pk_w1_lang = m->upload(l);
+        m->pk_b1 = m->upload(load_f32(g, "prompt_kernel.0.bias", H));
+        m->pk_w2 = m->upload(load_f32(g, "prompt_kernel.2.weight", (int64_t)D_MODEL * H));
+        m->pk_b2 = m->upload(load_f32(g, "prompt_kernel.2.bias", D_MODEL));
+        m->default_prompt = 101 < P ? 101 : 0;  // 101 = "auto" (src/nemo-ggml.cpp:459-462)
+        auto lk = g.str_arr.find("nemo.prompt_langs");
+        auto vk = g.i32_arr.find("nemo.prompt_ids");
+        if (lk != g.str_arr.end() && vk != g.i32_arr.end())
+            for (size_t i = 0; i < lk->second.size() && i < vk->second.size(); i++) m->prompt_dict[lk->second[i]] = vk->second[i];
+    } else if (g.has("prompt_kernel.0.weight")) {
+        throw Error("prompt_kernel weights present but nemo.num_prompts is 0");
+    }
 }
 
 }  // namespace
@@ -453,6 +482,7 @@ void alloc_state(nb200_model* m) {
     m->part_rows = rows_pad;
     m->part_max_splits = rows_pad <= 4096 ? 8 : (rows_pad <= 8192 ? 4 : (rows_pad <= 16384 ? 2 : 1));
     m->ws_part = m->alloc<float>((size_t)m->part_max_splits * rows_pad * D_MODEL);
+    if (m->num_prompts > 0) m->ws_pk = m->alloc<float>((size_t)rows_pad * PROMPT_HIDDEN);
     m->ws_pos16 = m->alloc<__half>((size_t)128 * D_MODEL);
     operand_init(m->op_a2h, m->ws_a2h, B * big.t2 * SUB_F2, SUB_CH);
     operand_init(m->op_a5h, m->ws_a5h, (int)rows * SUB_F3, SUB_CH);
@@ -761,19 +791,28 @@ void enqueue_encoder(const StepCtx& c) {
         else
             launch_layernorm(st, m->ws_x, L.ln_out_g, L.ln_out_b, m->ws_x, nullptr, nullptr, nullptr, 0, M, rin);
     }
+    // multilingual checkpoints: language-prompt fusion on the encoder output (src/nemo-ggml.cpp:1087-1105, src/nemo-stream.cpp:236-242),
+    // fp32 like the file: relu(fc1 . [enc ; onehot]) = relu(enc . W1a^T + b1 + W1[:, 1024 + lang]), then fc2
+    const float* enc_out = m->ws_x;
+    if (m->num_prompts > 0) {
+        launch_sgemm(st, m->ws_x, m->pk_w1, m->pk_b1, m->ws_pk, M, PROMPT_HIDDEN, D_MODEL, PROMPT_HIDDEN, nullptr);
+        launch_prompt_add_relu(st, m->ws_pk, m->pk_w1_lang, m->ws_meta + 6 * capB, T, M);
+        launch_sgemm(st, m->ws_pk, m->pk_w2, m->pk_b2, m->ws_g, M, D_MODEL, PROMPT_HIDDEN, D_MODEL, nullptr);
+        enc_out = m->ws_g;
+    }
     if (c.taps) {
         for (int b = 0; b < B; b++) {
             nb200_stream* s = (*c.items)[b].s;
             if (s->taps & NB200_TAP_ENC) {
                 const size_t n = (size_t)T * D_MODEL, old = s->tap_enc.size();
                 s->tap_enc.resize(old + n);
-                CUDA_CHECK(cudaMemcpyAsync(s->tap_enc.data() + old, m->ws_x + (size_t)b * T * D_MODEL, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+                CUDA_CHECK(cudaMemcpyAsync(s->tap_enc.data() + old, enc_out + (size_t)b * T * D_MODEL, n * sizeof(float), cudaMemcpyDeviceToHost, st));
                 CUDA_CHECK(cudaStreamSynchronize(st));
             }
         }
     }
     // joint.enc over all frames of the batch, and the decode loop's per-step state
-    launch_sgemm(st, m->ws_x, m->joint_enc_w, m->joint_enc_b, m->ws_e, M, JOINT, D_MODEL, JOINT, nullptr);
+    launch_sgemm(st, enc_out, m->joint_enc_w, m->joint_enc_b, m->ws_e, M, JOINT, D_MODEL, JOINT, nullptr);
     CUDA_CHECK(cudaMemsetAsync(m->ws_fp, 0, sizeof(int) * B, st));
     CUDA_CHECK(cudaMemsetAsync(m->ws_sym, 0, sizeof(int) * B, st));
     CUDA_CHECK(cudaMemsetAsync(m->ws_tokcnt, 0, sizeof(int) * B, st));
@@ -835,6 +874,7 @@ void run_batch_launch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
         meta[3 * capB + b] = items[b].nvalid;
         meta[4 * capB + b] = items[b].n_frames;
         meta[5 * capB + b] = (int)(s->chunks_done & 1);
+        meta[6 * capB + b] = (s->prompt_index >= 0 && s->prompt_index < m->num_prompts) ? s->prompt_index : 0;  // src/nemo-stream.cpp:1052-1053
         meta64[0 * capB + b] = ((long long)b * md.chunk_mel + MEL_OVERLAP) * N_MELS;
         // frame f of this chunk covers absolute samples a0 + 160 f + [0, 513): a0 = first new frame's first sample - 1
         meta64[1 * capB + b] = (long long)HOP * md.shift * s->chunks_done - 257;
@@ -1022,6 +1062,7 @@ nb200_stream* nb200_stream_create(nb200_model* m, int right_context) {
     nb200_stream* s = new nb200_stream();
     s->model = m;
     s->rc = right_context;
+    s->prompt_index = m->default_prompt;
     s->slot = m->free_slots.back();
     m->free_slots.pop_back();
     reset_slot(m, s->slot);
@@ -1242,6 +1283,27 @@ int nb200_stream_chunk_margins(const nb200_stream* s, float* out, int cap) {
     const int n = std::min<int>(cap, (int)s->chunk_margins.size());
     for (int i = 0; i < n; i++) out[i] = s->chunk_margins[i];
     return (int)s->chunk_margins.size();
+}
+
+int nb200_stream_set_language(nb200_stream* s, const char* lang) {
+    NB_TRY
+    if (!s || !lang) throw Error("null argument");
+    nb200_model* m = s->model;
+    if (m->num_prompts <= 0) throw Error("model is not multilingual (num_prompts=0)");
+    auto it = m->prompt_dict.find(lang);
+    if (it == m->prompt_dict.end()) throw Error(std::string("unknown language code '") + lang + "'");
+    s->prompt_index = it->second;
+    return NB200_OK;
+    NB_CATCH(NB200_ERR)
+}
+
+int nb200_stream_set_prompt_index(nb200_stream* s, int prompt_index) {
+    NB_TRY
+    if (!s) throw Error("null stream");
+    if (s->model->num_prompts <= 0) throw Error("model is not multilingual (num_prompts=0)");
+    s->prompt_index = prompt_index;  // out-of-range ids fall back to 0 when the chunk runs, like src/nemo-stream.cpp:1052-1053
+    return NB200_OK;
+    NB_CATCH(NB200_ERR)
 }
 
 int nb200_stream_set_taps(nb200_stream* s, int taps) {

@@ -51,6 +51,8 @@ struct ResidualIn {
     float alpha = 1.0f;
 };
 // y = LN(x; g1,b1); if out_f32: out_f32 = y; z = g2 ? LN(y; g2,b2) : y; out_f16 = fp16(fq ? fake_quant(z) : z)
+// h[m][n] = relu(h[m][n] + w_lang[lang[m / T]][n]) over [M][2048]: the one-hot half of prompt_kernel.0 (src/nemo-ggml.cpp:1097-1101)
+void launch_prompt_add_relu(cudaStream_t st, float* h, const float* w_lang, const int* lang, int T, int M);
 void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b1, float* out_f32, const float* g2,
                       const float* b2, __half* out_f16, int act_quant, int M, const ResidualIn& rin = ResidualIn());
 

@@ -49,6 +49,8 @@ SYMBOLS = {
     "nb200_stream_create": (C.c_void_p, [C.c_void_p, C.c_int]),
     "nb200_stream_free": (None, [C.c_void_p]),
     "nb200_stream_reset": (C.c_int, [C.c_void_p]),
+    "nb200_stream_set_language": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "nb200_stream_set_prompt_index": (C.c_int, [C.c_void_p, C.c_int]),
     "nb200_stream_feed": (C.c_int, [C.c_void_p, _I16P, C.c_int]),
     "nb200_stream_finalize": (C.c_int, [C.c_void_p]),
     "nb200_stream_ready_chunks": (C.c_int, [C.c_void_p]),
@@ -281,6 +283,11 @@ class Stream:
 
     def reset(self):
         if lib().nb200_stream_reset(self._h) < 0:
+            raise NB200Error(_err())
+
+    def set_language(self, lang: str):
+        """nemo_stream_set_language (src/nemo-stream.cpp:735-749); raises where the reference returns false."""
+        if lib().nb200_stream_set_language(self._h, lang.encode()) < 0:
             raise NB200Error(_err())
 
     def feed(self, pcm: np.ndarray):

@@ -310,6 +310,10 @@ class StreamOracle:
         self.vocab = int(kv["nemo.vocab_size"])
         self.blank = self.vocab - 1
         self.rc = right_context
+        # multilingual checkpoints: language prompt (src/nemo-ggml.cpp:459-462 default 101 = "auto"; set_language :735-749)
+        self.num_prompts = int(kv.get("nemo.num_prompts", 0))
+        self.prompt_index = 101 if self.num_prompts > 0 else -1
+        self.prompt_dict = dict(zip(kv.get("nemo.prompt_langs", []), kv.get("nemo.prompt_ids", [])))
         self.chunk_mel = 9 + 8 * (1 + right_context)  # src/nemo-stream.h:65-72
         self.shift = 8 * (1 + right_context)  # :76-81
         self.valid_out = 1 + right_context  # :98-100
@@ -399,7 +403,21 @@ class StreamOracle:
         for l in range(self.L):
             x = self._layer(l, x)
         self.valid = min(self.valid + x.shape[0], self.left)  # :1085
+        if self.num_prompts > 0:  # build_prompt_fusion, src/nemo-ggml.cpp:1087-1105; one-hot fill src/nemo-stream.cpp:1047-1059
+            idx = self.prompt_index if 0 <= self.prompt_index < self.num_prompts else 0
+            onehot = np.zeros((x.shape[0], self.num_prompts), F32)
+            onehot[:, idx] = 1.0
+            cat = np.concatenate([x, onehot], axis=1)
+            h = np.maximum(mm(cat, self.t["prompt_kernel.0.weight"]) + self.t["prompt_kernel.0.bias"], 0.0).astype(F32)
+            x = (mm(h, self.t["prompt_kernel.2.weight"]) + self.t["prompt_kernel.2.bias"]).astype(F32)
         return x
+
+    def set_language(self, lang: str) -> bool:
+        """nemo_stream_set_language, src/nemo-stream.cpp:735-749."""
+        if self.num_prompts <= 0 or lang not in self.prompt_dict:
+            return False
+        self.prompt_index = int(self.prompt_dict[lang])
+        return True
 
     # -- decoder -------------------------------------------------------------------------------
     def _lstm(self, l: int, x, h, c):  # src/nemo-ggml.cpp:580-619, gate order i,f,g,o

@@ -8,7 +8,7 @@
 // and reads the public struct fields sctx->encoder_graph.encoder_out, sctx->tokens,
 // sctx->{encoder,decoder,transfer}_seconds to dump what the parity tests compare against.
 //
-//   ref_harness stream <gguf> <pcm.s16le> <right_context> <threads> <out_prefix|-> [max_seconds]
+//   ref_harness stream <gguf> <pcm.s16le> <right_context> <threads> <out_prefix|-> [max_seconds] [language|-]
 //       feeds shift*160 samples per call (=> at most one encoder chunk per call), then finalize.
 //       writes <prefix>.mel.f32 [frames,128], <prefix>.enc.f32 [chunks,T,d_model] (all T frames of
 //       every chunk, before the valid_out truncation), <prefix>.tokens.i32, <prefix>.chunk_tokens.i32
@@ -96,6 +96,9 @@ static int run_stream(int argc, char** argv) {
     cfg.att_right_context = rc;
     nemo_stream_context* s = nemo_stream_init(ctx, &cfg);
     if (!s) return 1;
+    // multilingual checkpoints: optional language code (nemo_stream_set_language, src/nemo-stream.cpp:735-749); "-" keeps
+    // the loader's default prompt ("auto", src/nemo-ggml.cpp:459-462)
+    if (argc > 8 && strcmp(argv[8], "-") != 0 && !nemo_stream_set_language(s, argv[8])) return 3;
 
     const size_t feed = s->config.get_shift_mel_frames() * s->config.hop_length;
     const int d_model = s->config.d_model;

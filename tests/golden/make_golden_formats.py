@@ -4,6 +4,7 @@ reference), produced like make_golden.py by the UNMODIFIED reference (oracle/_re
 
     make -C oracle -j8 && python tests/golden/make_golden_formats.py
 
+  stream_ml_<lang>_rc<rc>.npz  multilingual GGUF (num_prompts = 128, prompt_kernel.*): nemo_stream_set_language + prompt fusion
   stream_<variant>_rc<rc>.npz  per-chunk encoder_out, tokens, tokens per chunk; both ISA builds for q4_0 (its activations
                                are re-quantised to Q8_0 like the Q8_0 path, so it has the same self-noise), avx2 only for f16.
 """
@@ -46,6 +47,21 @@ def main():
             e["self_noise_rel_l2"] = [round(float(np.linalg.norm(a - b) / np.linalg.norm(a)), 5) for a, b in zip(d["enc"], d["enc_alt"])]
         manifest["fixtures"][name] = e
         print(name, e)
+    # ---- multilingual checkpoint: prompt fusion with the default prompt and with explicit languages ----
+    path = inputs.gguf_path("f32dq", multilingual=True)
+    manifest["inputs"]["f32dq_ml"] = {"sha256": sha(path), "bytes": Path(path).stat().st_size}
+    for lang, rc, seed, secs in inputs.PROMPT_CASES:
+        T = 1 + rc
+        pref = TMP / f"gold_ml_{lang}_rc{rc}"
+        info = run([harness("avx2"), "stream", path, inputs.pcm_path(seed, secs), str(rc), "4", str(pref), "0", lang or "-"])
+        d = {"enc": np.fromfile(str(pref) + ".enc.f32", dtype=np.float32).reshape(-1, T, 1024),
+             "tokens": np.fromfile(str(pref) + ".tokens.i32", dtype=np.int32),
+             "chunk_tokens": np.fromfile(str(pref) + ".chunk_tokens.i32", dtype=np.int32)}
+        assert d["enc"].shape[0] == info["chunks"]
+        name = f"stream_ml_{lang or 'default'}_rc{rc}.npz"
+        np.savez_compressed(GOLD / name, **d)
+        manifest["fixtures"][name] = {"pcm": f"seed {seed}, {secs} s", "language": lang, "chunks": int(d["enc"].shape[0]), "tokens": int(d["tokens"].size)}
+        print(name, manifest["fixtures"][name])
     (GOLD / "manifest_formats.json").write_text(json.dumps(manifest, indent=1) + "\n")
 
 

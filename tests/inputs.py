@@ -48,14 +48,22 @@ FORMAT_CASES = (
 )
 
 
-def gguf_path(variant: str, layers: int = TEST_LAYERS, blank_gain: float | None = None) -> str:
+# multilingual checkpoint (prompt fusion): (language code or None = the loader's default "auto", rc, seed, secs)
+PROMPT_CASES = (
+    (None, 13, 11, 3.0),
+    ("de", 13, 11, 3.0),
+    ("ja", 0, 12, 1.0),
+)
+
+
+def gguf_path(variant: str, layers: int = TEST_LAYERS, blank_gain: float | None = None, multilingual: bool = False) -> str:
     import make_random_gguf as mg
     TMP.mkdir(parents=True, exist_ok=True)
-    tag = "" if blank_gain is None else f"_bg{blank_gain:g}"
+    tag = ("" if blank_gain is None else f"_bg{blank_gain:g}") + ("_ml" if multilingual else "")
     p = TMP / f"L{layers}_{variant}_s{SEED}{tag}.gguf"
     if not p.exists():
         tmp = p.with_suffix(f".tmp{os.getpid()}")
-        mg.write_gguf(str(tmp), SEED, layers, variant, blank_gain)
+        mg.write_gguf(str(tmp), SEED, layers, variant, blank_gain, multilingual)
         os.replace(tmp, p)
     return str(p)
 

@@ -207,6 +207,46 @@ def test_format_q4_0_within_reference_self_noise(nb, lib_built, variant, rc, see
     assert ours.max() <= 1.6 * self_noise.max(), (ours, self_noise)
 
 
+def test_prompt_fusion_matches_reference(nb, lib_built, model_f32):
+    """multilingual checkpoint. Three sessions with different language prompts (default "auto", "de",
+    "ja") run in the same batched steps and must each match the reference run with that language; errors like the
+    reference's nemo_stream_set_language (unknown code, monolingual model)."""
+    model = nb.Model(inputs.gguf_path("f32dq", multilingual=True), device=0, max_streams=4)
+    assert model.info.num_prompts == 128
+    streams = []
+    for lang, rc, seed, secs in inputs.PROMPT_CASES:
+        s = model.stream(rc)
+        with pytest.raises(nb.NB200Error, match="unknown language"):
+            s.set_language("xx")
+        if lang:
+            s.set_language(lang)
+        s.set_taps(nb.TAP_ENC)
+        s.feed(inputs.pcm(seed, secs))
+        streams.append(s)
+    while model.step() > 0:
+        pass
+    for s in streams:
+        nb.lib().nb200_stream_finalize(s._h)
+    while model.step() > 0:
+        pass
+    for (lang, rc, seed, secs), s in zip(inputs.PROMPT_CASES, streams):
+        gold = np.load(GOLD / f"stream_ml_{lang or 'default'}_rc{rc}.npz")
+        enc = s.fetch_tap(nb.TAP_ENC).reshape(-1, 1 + rc, 1024)
+        assert enc.shape == gold["enc"].shape
+        rels = [rel(a, b) for a, b in zip(enc, gold["enc"])]
+        got = {"tokens": s.tokens, "chunk_tokens": s.chunk_token_counts, "margins": s.chunk_margins}
+        same, comparable, margin = compare_tokens(got, gold["tokens"], gold["chunk_tokens"])
+        print(f"prompt {lang}: enc rel max {max(rels):.2e}; token chunks identical {same}/{comparable}, mismatch margin {margin}")
+        assert max(rels) < 3e-3, rels
+        if margin is not None:
+            assert margin < TIE_GAP
+    model.close()
+    mono = model_f32.stream(0)
+    with pytest.raises(nb.NB200Error, match="not multilingual"):
+        mono.set_language("de")
+    mono.free()
+
+
 def test_batched_equals_single(nb, model_f32):
     """Cross-stream batching must not change any stream's result: 5 streams in mixed latency modes, stepped together,
     equal the same streams run alone (same kernels, same per-row arithmetic)."""

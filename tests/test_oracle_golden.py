@@ -99,6 +99,29 @@ def test_stream_q8_within_reference_self_noise(rc, oracle_q8):
     assert (ours <= np.maximum(1.5 * self_noise, 2e-3)).all(), (ours, self_noise)
 
 
+@pytest.mark.parametrize("lang,rc,seed,secs", inputs.PROMPT_CASES)
+def test_prompt_fusion_matches_reference(lang, rc, seed, secs):
+    """multilingual GGUF (num_prompts = 128). nemo_stream_set_language + build_prompt_fusion
+    (src/nemo-ggml.cpp:1087-1105) of the oracle against the compiled reference: default prompt ("auto", 101) and two languages."""
+    kv, t = no.load_gguf(inputs.gguf_path("f32dq", multilingual=True))
+    gold = np.load(GOLD / f"stream_ml_{lang or 'default'}_rc{rc}.npz")
+    s = no.StreamOracle(kv, t, rc)
+    assert s.num_prompts == 128 and s.prompt_index == 101
+    assert not s.set_language("xx")
+    if lang:
+        assert s.set_language(lang)
+    pcm = inputs.pcm(seed, secs)
+    feed = 8 * (1 + rc) * 160
+    for i in range(0, len(pcm), feed):
+        s.feed(pcm[i:i + feed])
+    s.finalize()
+    enc = np.stack(s.enc_chunks)
+    assert enc.shape == gold["enc"].shape
+    rels = [rel(a, b) for a, b in zip(enc, gold["enc"])]
+    assert max(rels) < 2e-4, rels
+    assert s.chunk_tokens == gold["chunk_tokens"].tolist() and s.tokens == gold["tokens"].tolist()
+
+
 def test_tokens_to_text():
     vocab = ["▁he", "llo", "▁wor", "ld"]
     assert no.tokens_to_text([0, 1, 2, 3, 99], vocab) == " hello world"

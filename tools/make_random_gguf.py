@@ -112,6 +112,24 @@ def mel_filterbank() -> np.ndarray:
     return fb.astype(np.float32)
 
 
+NUM_PROMPTS, PROMPT_HIDDEN = 128, 2048
+# language code -> prompt id, like the multilingual checkpoints' dictionary (src/nemo-ggml.cpp:171-181; 101 = "auto" is the
+# default of nemo_init_with_backend, :459-462)
+PROMPT_DICT = (("en", 0), ("de", 3), ("fr", 7), ("es", 12), ("ja", 64), ("auto", 101))
+
+
+def prompt_tensors(seed: int):
+    """prompt_kernel.{0,2}: Linear(1024 + 128 -> 2048) + ReLU + Linear(2048 -> 1024), F32 (src/nemo-ggml.cpp:390-394,1087-1105).
+    The one-hot columns are large enough that the language visibly changes the encoder output."""
+    s = seed
+    w0 = normal(s, "prompt_kernel.0.weight", (PROMPT_HIDDEN, D_MODEL + NUM_PROMPTS), (2.0 / D_MODEL) ** 0.5)
+    w0[:, D_MODEL:] = normal(s, "prompt_kernel.0.weight.onehot", (PROMPT_HIDDEN, NUM_PROMPTS), 0.7)
+    yield "prompt_kernel.0.weight", w0, False
+    yield "prompt_kernel.0.bias", normal(s, "prompt_kernel.0.bias", (PROMPT_HIDDEN,), 0.1), False
+    yield "prompt_kernel.2.weight", normal(s, "prompt_kernel.2.weight", (D_MODEL, PROMPT_HIDDEN), (2.0 / PROMPT_HIDDEN) ** 0.5), False
+    yield "prompt_kernel.2.bias", normal(s, "prompt_kernel.2.bias", (D_MODEL,), 0.1), False
+
+
 def tensor_list(seed: int, n_layers: int, blank_gain: float | None = None):
     """Yields (name, float32 array in PyTorch shape order, quantisable?)."""
     s = seed
@@ -189,16 +207,18 @@ def _w_str(f, sbytes: bytes):
     f.write(sbytes)
 
 
-def write_gguf(path: str, seed: int = 1234, n_layers: int = 24, variant: str = "q8_0", blank_gain: float | None = None) -> dict:
+def write_gguf(path: str, seed: int = 1234, n_layers: int = 24, variant: str = "q8_0", blank_gain: float | None = None,
+               multilingual: bool = False) -> dict:
     assert variant in ("q8_0", "f32", "f32dq", "f16", "q4_0")
     vocab = [("▁" if i % 3 == 0 else "") + f"t{i}" for i in range(VOCAB - 1)]
     hparams = [("nemo.n_mels", N_MELS), ("nemo.d_model", D_MODEL), ("nemo.n_heads", N_HEADS), ("nemo.d_head", D_HEAD),
                ("nemo.d_ff", D_FF), ("nemo.n_layers", n_layers), ("nemo.kernel_size", KERNEL), ("nemo.vocab_size", VOCAB),
                ("nemo.decoder_dim", DEC), ("nemo.joint_dim", JOINT), ("nemo.subsampling_factor", SUBS),
-               ("nemo.att_left_context", LEFT), ("nemo.num_prompts", 0)]
+               ("nemo.att_left_context", LEFT), ("nemo.num_prompts", NUM_PROMPTS if multilingual else 0)]
     infos, off = [], 0
     blobs = []
-    for name, arr, quantisable in tensor_list(seed, n_layers, blank_gain):
+    import itertools
+    for name, arr, quantisable in itertools.chain(tensor_list(seed, n_layers, blank_gain), prompt_tensors(seed) if multilingual else ()):
         arr = np.ascontiguousarray(arr, dtype=np.float32)
         if quantisable and variant == "q8_0":
             data, typ = q8_0_bytes(arr), GGML_Q8_0
@@ -218,7 +238,7 @@ def write_gguf(path: str, seed: int = 1234, n_layers: int = 24, variant: str = "
         f.write(b"GGUF")
         f.write(struct.pack("<I", 3))
         f.write(struct.pack("<q", len(infos)))
-        f.write(struct.pack("<q", len(hparams) + 3))
+        f.write(struct.pack("<q", len(hparams) + 3 + (2 if multilingual else 0)))
         for k, v in (("general.architecture", "nemo"), ("general.name", f"random-init-{variant}-L{n_layers}-s{seed}")):
             _w_str(f, k.encode()); f.write(struct.pack("<I", 8)); _w_str(f, v.encode())
         _w_str(f, b"tokenizer.vocab_list"); f.write(struct.pack("<I", 9)); f.write(struct.pack("<I", 8))
@@ -227,6 +247,15 @@ def write_gguf(path: str, seed: int = 1234, n_layers: int = 24, variant: str = "
             _w_str(f, t.encode("utf-8"))
         for k, v in hparams:
             _w_str(f, k.encode()); f.write(struct.pack("<I", 4)); f.write(struct.pack("<I", v))
+        if multilingual:  # parallel arrays: string[] codes, i32[] ids
+            _w_str(f, b"nemo.prompt_langs"); f.write(struct.pack("<I", 9)); f.write(struct.pack("<I", 8))
+            f.write(struct.pack("<Q", len(PROMPT_DICT)))
+            for code, _ in PROMPT_DICT:
+                _w_str(f, code.encode())
+            _w_str(f, b"nemo.prompt_ids"); f.write(struct.pack("<I", 9)); f.write(struct.pack("<I", 5))
+            f.write(struct.pack("<Q", len(PROMPT_DICT)))
+            for _, pid in PROMPT_DICT:
+                f.write(struct.pack("<i", pid))
         for name, shape, typ, o, _ in infos:
             _w_str(f, name.encode()); f.write(struct.pack("<I", len(shape)))
             for dim in shape:
