@@ -6,6 +6,8 @@
 // mel sum over FFT bins (:374-383). Every multiply/add is an explicit round-to-nearest intrinsic so nvcc cannot
 // contract them into FMAs (the reference binary is built without FMA, Makefile:7). Zero filterbank weights are skipped:
 // adding +0 never changes an fp32 sum, so the result is bit-identical to the dense 257-term loop.
+#include <cstdlib>
+
 #include "kernels.cuh"
 
 namespace nb {
@@ -67,10 +69,140 @@ __global__ void __launch_bounds__(256) mel_kernel(MelTables tb, MelBatch mb, flo
     }
 }
 
+// ---- radix-8 register version -------------------------------------------------------------------------------------
+// Same butterflies, same twiddle table entries, same operation order inside every butterfly as mel_kernel above (hence
+// bit-identical: a radix-2 DIT stage only orders independent butterflies), but three consecutive stages are done on 8
+// complex values held in registers: 3 shared-memory round trips and 5 barriers per frame instead of 9 and 13. 64
+// threads per frame, 4 frames per CTA. Shared-memory index i lives at i + 8 * (i >> 6): the pad makes the stride-8
+// (stages 4-6) and stride-64 (stages 7-9) accesses conflict-free.
+constexpr int MEL_FPB = 4;  // frames per CTA
+__device__ __forceinline__ int mel_pos(int i) { return i + ((i >> 6) << 3); }
+
+// One radix-2 butterfly exactly as in the reference's fft_frame (src/preprocessor.cpp:140-156)
+__device__ __forceinline__ void mel_bfly(float& r1, float& q1, float& r2, float& q2, float wr, float wi) {
+    const float tr = __fsub_rn(__fmul_rn(wr, r2), __fmul_rn(wi, q2));
+    const float ti = __fadd_rn(__fmul_rn(wr, q2), __fmul_rn(wi, r2));
+    const float a = r1, c = q1;
+    r2 = __fsub_rn(a, tr);
+    q2 = __fsub_rn(c, ti);
+    r1 = __fadd_rn(a, tr);
+    q1 = __fadd_rn(c, ti);
+}
+
+// Stages 3*PASS+1 .. 3*PASS+3 on the thread's 8 values. Element k of thread g is global index
+//   PASS 0: 8 g + k      PASS 1: 64 (g >> 3) + (g & 7) + 8 k      PASS 2: g + 64 k
+// j0 = the part of the butterfly's twiddle index j = i1 & (m2 - 1) that does not depend on k.
+template <int PASS>
+__device__ __forceinline__ void mel_fft_pass(float (&r)[8], float (&q)[8], int g, const float* __restrict__ cs, const float* __restrict__ sn) {
+    const int j0 = PASS == 0 ? 0 : (PASS == 1 ? (g & 7) : g);
+    constexpr int unit = PASS == 0 ? 1 : (PASS == 1 ? 8 : 64);  // index distance between consecutive k
+#pragma unroll
+    for (int sp = 1; sp <= 3; sp++) {
+        const int lg = 3 * PASS + sp, half = 1 << (sp - 1);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            if (k & half) continue;
+            const int j = j0 + unit * (k & (half - 1));
+            const int idx = j << (9 - lg);
+            mel_bfly(r[k], q[k], r[k + half], q[k + half], cs[idx], -sn[idx]);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(64 * MEL_FPB) mel_r8_kernel(MelTables tb, MelBatch mb, float* __restrict__ mel_out) {
+    pdl_prologue();
+    constexpr int PADN = N_FFT + 8 * (N_FFT / 64);  // 576
+    __shared__ float xs[MEL_FPB][N_FFT + 1];
+    __shared__ float re[MEL_FPB][PADN], im[MEL_FPB][PADN];
+    __shared__ float pw[MEL_FPB][N_BINS + 3];
+    __shared__ float cs[N_FFT / 2], sn[N_FFT / 2];
+    const int t = threadIdx.x, fs = t >> 6, g = t & 63, b = blockIdx.y;
+    const int f = blockIdx.x * MEL_FPB + fs;
+    const bool active = f < mb.n_frames[b];
+    for (int i = t; i < N_FFT / 2; i += 64 * MEL_FPB) {
+        cs[i] = tb.cos_tbl[i];
+        sn[i] = tb.sin_tbl[i];
+    }
+    if (active) {
+        const int16_t* ring = mb.ring + (size_t)mb.slot[b] * mb.ring_cap;
+        const long long a_first = mb.a0[b] + (long long)f * HOP, n_avail = mb.n_avail[b];
+        for (int i = g; i < N_FFT + 1; i += 64) {
+            const long long a = a_first + i;
+            const int16_t s = (a >= 0 && a < n_avail) ? ring[a & (long long)(mb.ring_cap - 1)] : (int16_t)0;
+            xs[fs][i] = __fmul_rn((float)s, 1.0f / 32768.0f);
+        }
+    }
+    __syncthreads();
+    float r[8], q[8];
+    if (active) {
+        // pass 0 reads its inputs straight from the windowed signal: element k of thread g is bit-reversed index 8 g + k,
+        // i.e. time sample brev9(8 g + k) (src/preprocessor.cpp:120-131)
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const int i = __brev((unsigned)(8 * g + k)) >> 23;
+            float y = __fsub_rn(xs[fs][i + 1], __fmul_rn(0.97f, xs[fs][i]));
+            r[k] = __fmul_rn(y, tb.win512[i]);
+            q[k] = 0.0f;
+        }
+        mel_fft_pass<0>(r, q, g, cs, sn);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            re[fs][mel_pos(8 * g + k)] = r[k];
+            im[fs][mel_pos(8 * g + k)] = q[k];
+        }
+    }
+    __syncthreads();
+    if (active) {
+        const int base = 64 * (g >> 3) + (g & 7);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            r[k] = re[fs][mel_pos(base + 8 * k)];
+            q[k] = im[fs][mel_pos(base + 8 * k)];
+        }
+        mel_fft_pass<1>(r, q, g, cs, sn);
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            re[fs][mel_pos(base + 8 * k)] = r[k];
+            im[fs][mel_pos(base + 8 * k)] = q[k];
+        }
+    }
+    __syncthreads();
+    if (active) {
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            r[k] = re[fs][mel_pos(g + 64 * k)];
+            q[k] = im[fs][mel_pos(g + 64 * k)];
+        }
+        mel_fft_pass<2>(r, q, g, cs, sn);
+        // bins 0..256: elements k = 0..3 of every thread, plus element 4 of thread 0
+#pragma unroll
+        for (int k = 0; k < 5; k++) {
+            if (k == 4 && g != 0) break;
+            const float mag = __fsqrt_rn(__fadd_rn(__fmul_rn(r[k], r[k]), __fmul_rn(q[k], q[k])));
+            pw[fs][g + 64 * k] = __fmul_rn(mag, mag);
+        }
+    }
+    __syncthreads();
+    if (active) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            const int mbin = g + 64 * h;
+            const int2 rg = tb.fb_range[mbin];
+            float sum = 0.0f;
+            for (int k = rg.x; k < rg.y; k++) sum = __fadd_rn(sum, __fmul_rn(tb.fbT[k * N_MELS + mbin], pw[fs][k]));
+            mel_out[mb.out_off[b] + (long long)f * N_MELS + mbin] = logf(__fadd_rn(sum, 5.960464477539063e-8f));
+        }
+    }
+}
+
 void launch_mel(cudaStream_t st, const MelTables& tb, const MelBatch& mb, float* mel_out, int B, int max_frames) {
     if (B <= 0 || max_frames <= 0) return;
+    static const bool radix2 = getenv("NB200_MEL_RADIX2") != nullptr;  // the one-stage-per-barrier kernel, kept as the checker
     ProfScope ps(st, "mel", (double)B * max_frames * 2.0e5, (double)B * max_frames * (HOP * 2 + N_MELS * 4));
-    launch_k(mel_kernel, dim3(dim3(max_frames, B)), dim3(256), 0, st, tb, mb, mel_out);
+    if (radix2)
+        launch_k(mel_kernel, dim3(dim3(max_frames, B)), dim3(256), 0, st, tb, mb, mel_out);
+    else
+        launch_k(mel_r8_kernel, dim3(dim3(cdiv(max_frames, MEL_FPB), B)), dim3(64 * MEL_FPB), 0, st, tb, mb, mel_out);
     NB_KERNEL_CHECK();
 }
 
