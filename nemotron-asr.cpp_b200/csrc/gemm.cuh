@@ -53,7 +53,7 @@ __device__ __forceinline__ int epilogue_transform(const EpiParams& p, int m, int
             for (int j = 0; j < 32; j++) acc[j] = fmaxf(acc[j], 0.0f);
         } else if (p.act == ACT_SILU) {
 #pragma unroll
-            for (int j = 0; j < 32; j++) acc[j] = silu_fast(acc[j]);
+            for (int j = 0; j < 32; j += 4) silu_fast4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
         }
     }
     if (p.kind == EPI_STORE_F16) {
@@ -78,7 +78,12 @@ __device__ __forceinline__ int epilogue_transform(const EpiParams& p, int m, int
     }
     if (p.kind == EPI_GLU) {
 #pragma unroll
-        for (int j = 0; j < 16; j++) w[j] = __float_as_uint(acc[2 * j] * sigmoid_fast(acc[2 * j + 1]));
+        for (int j = 0; j < 16; j += 4) {
+            float o[4];
+            glu_fast4(o, acc[2 * j], acc[2 * j + 1], acc[2 * j + 2], acc[2 * j + 3], acc[2 * j + 4], acc[2 * j + 5], acc[2 * j + 6], acc[2 * j + 7]);
+#pragma unroll
+            for (int e = 0; e < 4; e++) w[j + e] = __float_as_uint(o[e]);
+        }
         dst = reinterpret_cast<char*>(p.out_f32 + (size_t)m * p.ldo + (n0 >> 1));
         return 16;
     }
