@@ -59,6 +59,9 @@ __device__ __forceinline__ float4 ln_1024(float4 v, const float* g, const float*
     return v;
 }
 
+// NS = number of split-K partials to add (0: plain LayerNorm of x). A compile-time count lets all NS + 1 loads of a thread
+// be in flight together (with a run-time loop they were issued one round trip after the other); the sums keep split order.
+template <int NS>
 __global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, const float* __restrict__ g1,
                                                         const float* __restrict__ b1, float* __restrict__ out_f32,
                                                         const float* __restrict__ g2, const float* __restrict__ b2,
@@ -67,11 +70,14 @@ __global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, c
     __shared__ float red[32];
     const size_t off = (size_t)blockIdx.x * D_MODEL + threadIdx.x * 4;
     float4 v = *reinterpret_cast<const float4*>(x + off);
-    if (rin.partials != nullptr) {  // x += alpha * (sum of the preceding GEMM's split-K partials), in split order
-        float4 acc = *reinterpret_cast<const float4*>(rin.partials + off);
-        for (int s = 1; s < rin.nsplit; s++) {
-            const float4 p = *reinterpret_cast<const float4*>(rin.partials + (size_t)s * rin.stride + off);
-            acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+    if constexpr (NS > 0) {  // x += alpha * (sum of the preceding GEMM's split-K partials), in split order
+        float4 p[NS];
+#pragma unroll
+        for (int s = 0; s < NS; s++) p[s] = *reinterpret_cast<const float4*>(rin.partials + (size_t)s * rin.stride + off);
+        float4 acc = p[0];
+#pragma unroll
+        for (int s = 1; s < NS; s++) {
+            acc.x += p[s].x; acc.y += p[s].y; acc.z += p[s].z; acc.w += p[s].w;
         }
         v.x += rin.alpha * acc.x; v.y += rin.alpha * acc.y; v.z += rin.alpha * acc.z; v.w += rin.alpha * acc.w;
         if (out_f32 != x) *reinterpret_cast<float4*>(x + off) = v;  // the residual stream (unless the LN output replaces it)
@@ -82,13 +88,32 @@ __global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, c
     if (out_f16) store_f16x4(out_f16 + off, v, act_quant);
 }
 
+template <int NS>
+static void launch_ln_ns(cudaStream_t st, float* x, const float* g1, const float* b1, float* out_f32, const float* g2, const float* b2,
+                         __half* out_f16, int act_quant, int M, const ResidualIn& rin) {
+    launch_k(layernorm_kernel<NS>, dim3(M), dim3(256), 0, st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, rin);
+}
+
 void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b1, float* out_f32, const float* g2,
                       const float* b2, __half* out_f16, int act_quant, int M, const ResidualIn& rin) {
     if (M <= 0) return;
     ProfScope ps(st, "layernorm", (double)M * D_MODEL * 8,
                  (double)M * D_MODEL * (4 + (out_f32 ? 4 : 0) + (out_f16 ? 2 : 0) + (rin.partials ? 4.0 * rin.nsplit + (out_f32 != x ? 4 : 0) : 0)));
-    for (int rep = dup_family("layernorm") ? 2 : 1; rep > 0; rep--)
-        launch_k(layernorm_kernel, dim3(M), dim3(256), 0, st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, rin);
+    const int ns = rin.partials ? rin.nsplit : 0;
+    if (ns < 0 || ns > 8) throw Error("layernorm: at most 8 split-K partials");
+    for (int rep = dup_family("layernorm") ? 2 : 1; rep > 0; rep--) {
+        switch (ns) {
+            case 0: launch_ln_ns<0>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
+            case 1: launch_ln_ns<1>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
+            case 2: launch_ln_ns<2>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
+            case 3: launch_ln_ns<3>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
+            case 4: launch_ln_ns<4>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
+            case 5: launch_ln_ns<5>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
+            case 6: launch_ln_ns<6>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
+            case 7: launch_ln_ns<7>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
+            default: launch_ln_ns<8>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
+        }
+    }
     NB_KERNEL_CHECK();
 }
 
