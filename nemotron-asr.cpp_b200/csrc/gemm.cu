@@ -178,12 +178,13 @@ __device__ __forceinline__ void tmem_dealloc_cg(uint32_t taddr, uint32_t ncols) 
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
 
-template <int BN, int STAGES, int CG>
+template <int BN, int STAGES, int CG, int EC>
 __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                             const __grid_constant__ CUtensorMap map_w,
                                                             const __grid_constant__ CUtensorMap map_out, int M, int kb_total,
-                                                            EpiParams epi) {
+                                                            EpiParams epi_in) {
     pdl_launch();
+    const EpiParams epi = epi_specialize<EC>(epi_in);
     unsigned long long* trace = epi.trace ? epi.trace + 8 * (size_t)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)) : nullptr;
     if (trace && threadIdx.x == 0) trace[0] = gtimer();
     using S = TcSmem<BN, STAGES, CG>;
@@ -472,18 +473,34 @@ void operand_init(Operand& op, const __half* ptr, int rows, int K) {
     for (int i = 0; i < 5; i++) make_map(&op.maps[i], ptr, rows, K, boxes[i]);
 }
 
-template <int BN, int STAGES, int CG>
-static void launch_tc(cudaStream_t st, const Operand& A, const Operand& W, const CUtensorMap& omap, int M, const EpiParams& epi, int splits) {
+template <int BN, int STAGES, int CG, int EC>
+static void launch_tc_ec(cudaStream_t st, const Operand& A, const Operand& W, const CUtensorMap& omap, int M, const EpiParams& epi, int splits) {
     using S = TcSmem<BN, STAGES, CG>;
     static bool configured = false;
     if (!configured) {
-        CUDA_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+        CUDA_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, CG, EC>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
         configured = true;
     }
     dim3 grid(CG * (W.rows / BN), cdiv(M, TC_BM * CG), splits);
-    launch_kc(gemm_tc_kernel<BN, STAGES, CG>, grid, dim3(TC_THREADS), (size_t)S::TOTAL, st, CG, A.box(128), W.box(S::B_ROWS), omap, M,
+    launch_kc(gemm_tc_kernel<BN, STAGES, CG, EC>, grid, dim3(TC_THREADS), (size_t)S::TOTAL, st, CG, A.box(128), W.box(S::B_ROWS), omap, M,
               A.K / TC_BK, epi);
     NB_KERNEL_CHECK();
+}
+
+template <int BN, int STAGES, int CG>
+static void launch_tc(cudaStream_t st, const Operand& A, const Operand& W, const CUtensorMap& omap, int M, const EpiParams& epi, int splits) {
+    static const bool generic_only = getenv("NB200_GEMM_GENERIC_EPILOGUE") != nullptr;  // checker: the run-time-switched epilogue for everything
+    const int ec = (generic_only || epi.trace != nullptr) ? (int)EC_GENERIC : epi_class_of(epi);
+    if constexpr (BN >= 64) {  // fp16 / GLU outputs need 64-column tiles
+        switch (ec) {
+            case EC_SILU_F16: return launch_tc_ec<BN, STAGES, CG, EC_SILU_F16>(st, A, W, omap, M, epi, splits);
+            case EC_GLU: return launch_tc_ec<BN, STAGES, CG, EC_GLU>(st, A, W, omap, M, epi, splits);
+            case EC_PLAIN_F16: return launch_tc_ec<BN, STAGES, CG, EC_PLAIN_F16>(st, A, W, omap, M, epi, splits);
+            default: break;
+        }
+    }
+    if (ec == EC_PARTIAL) return launch_tc_ec<BN, STAGES, CG, EC_PARTIAL>(st, A, W, omap, M, epi, splits);
+    launch_tc_ec<BN, STAGES, CG, EC_GENERIC>(st, A, W, omap, M, epi, splits);
 }
 
 // ---- tile / split selection ------------------------------------------------------------------------------

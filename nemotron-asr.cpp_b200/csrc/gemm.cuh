@@ -93,6 +93,28 @@ __device__ __forceinline__ int epilogue_transform(const EpiParams& p, int m, int
     return 32;
 }
 
+// Epilogue classes the tcgen05 kernel is compiled for: with the kind / activation / bias fixed at compile time the other
+// branches of epilogue_transform (predicated-off instructions that still take issue slots) disappear. EC_GENERIC keeps
+// everything a run-time switch (subsampling GEMMs with bias / ReLU, anything else).
+enum EpiClass : int { EC_GENERIC = 0, EC_SILU_F16 = 1, EC_PARTIAL = 2, EC_GLU = 3, EC_PLAIN_F16 = 4 };
+__host__ __device__ inline int epi_class_of(const EpiParams& p) {
+    if (p.kind == EPI_PARTIAL) return EC_PARTIAL;
+    if (p.bias != nullptr) return EC_GENERIC;
+    if (p.kind == EPI_STORE_F16 && p.act == ACT_SILU) return EC_SILU_F16;
+    if (p.kind == EPI_STORE_F16 && p.act == ACT_NONE) return EC_PLAIN_F16;
+    if (p.kind == EPI_GLU && p.act == ACT_NONE) return EC_GLU;
+    return EC_GENERIC;
+}
+template <int EC>
+__device__ __forceinline__ EpiParams epi_specialize(const EpiParams& in) {
+    EpiParams p = in;
+    if constexpr (EC == EC_SILU_F16) { p.kind = EPI_STORE_F16; p.act = ACT_SILU; p.bias = nullptr; }
+    if constexpr (EC == EC_PARTIAL) { p.kind = EPI_PARTIAL; p.act = ACT_NONE; p.bias = nullptr; p.act_quant = 0; }
+    if constexpr (EC == EC_GLU) { p.kind = EPI_GLU; p.act = ACT_NONE; p.bias = nullptr; p.act_quant = 0; }
+    if constexpr (EC == EC_PLAIN_F16) { p.kind = EPI_STORE_F16; p.act = ACT_NONE; p.bias = nullptr; }
+    return p;
+}
+
 // Direct (one thread = one row) version used by the CUDA-core checker kernel: same transform, per-thread stores.
 __device__ __forceinline__ void epilogue_apply(const EpiParams& p, int m, int n0, float (&acc)[32]) {
     uint32_t w[32];
