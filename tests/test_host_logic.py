@@ -115,3 +115,16 @@ def test_two_rank_gloo(tmp_path):
                        env=env, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert r.stdout.count("ok") == 2
+
+
+def test_server_loop_header_compiles(lib_built, tmp_path):
+    """nemotron-asr.cpp_b200/server_loop.h and its GPU test driver build against include/nb200.h and link with the library
+    (no GPU needed to compile and link; the driver itself runs in the gpu suite)."""
+    import subprocess
+    root = Path(__file__).resolve().parents[1]
+    pkg = root / "nemotron-asr.cpp_b200"
+    exe = tmp_path / "server_loop_test"
+    subprocess.run(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-I", str(root / "include"), "-I", str(pkg),
+                    str(root / "tests" / "server_loop_test.cpp"), "-o", str(exe), "-L", str(pkg), "-lnemob200", f"-Wl,-rpath,{pkg}", "-lpthread"],
+                   check=True)
+    assert exe.exists()
