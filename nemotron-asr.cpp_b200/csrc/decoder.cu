@@ -367,6 +367,14 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
         *reinterpret_cast<float4*>(&sm.wrow[r][k]) = *reinterpret_cast<const float4*>(w.wout + (size_t)(v0 + r) * JOINT + k);
     }
     if (t < nr) sm.bias[t] = w.bout[v0 + t];
+    // per-chunk decode state (was four memset nodes in front of this kernel): frame pointers, symbol counters, token counts,
+    // margins = 3.39e38. Nothing reads them before the grid barrier below.
+    for (int b = cta * 256 + t; b < d.B; b += G * 256) {
+        d.fp[b] = 0;
+        d.sym[b] = 0;
+        d.tok_cnt[b] = 0;
+        d.min_margin[b] = __int_as_float(0x7f7f7f7f);
+    }
     // hid of every stream's first symbol step (fp = 0, pending pred from the previous chunk); the owner warp of stream b
     for (int b = cta * 8 + warp; b < d.B; b += G * 8)
         if (d.nvalid[b] > 0) dk_stage_hid(s, d, b, 0, d.slot[b], lane);

@@ -813,10 +813,6 @@ void enqueue_encoder(const StepCtx& c) {
     }
     // joint.enc over all frames of the batch, and the decode loop's per-step state
     launch_sgemm(st, enc_out, m->joint_enc_w, m->joint_enc_b, m->ws_e, M, JOINT, D_MODEL, JOINT, nullptr);
-    CUDA_CHECK(cudaMemsetAsync(m->ws_fp, 0, sizeof(int) * B, st));
-    CUDA_CHECK(cudaMemsetAsync(m->ws_sym, 0, sizeof(int) * B, st));
-    CUDA_CHECK(cudaMemsetAsync(m->ws_tokcnt, 0, sizeof(int) * B, st));
-    CUDA_CHECK(cudaMemsetAsync(m->ws_tokcnt + capB, 0x7f, sizeof(int) * B, st));  // margins = 3.39e38
     launch_decode_chunk(st, m->dec, m->dstate, decode_batch(m, B, T));  // every greedy round of the chunk, one persistent launch
 }
 
@@ -892,14 +888,13 @@ void run_batch_launch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
     CUDA_CHECK(cudaEventRecord(m->ev[2], st));
 
     // The greedy rounds (src/nemo-stream.cpp:1106-1118, 840-930) ran inside the same graph as one persistent launch.
-    int* h_unf = m->h_tok.p;  // word 0, 1 of the pinned token buffer: streams left unfinished, rounds run
-    int* h_cnt = m->h_tok.p + 6;
-    int* h_margin = h_cnt + B;
-    int* h_toks = h_margin + B;
-    CUDA_CHECK(cudaMemcpyAsync(h_unf, m->ws_unfinished + 6, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CUDA_CHECK(cudaMemcpyAsync(h_unf + 2, m->ws_unfinished + 10, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));  // decode kernel's own start/end stamps
-    CUDA_CHECK(cudaMemcpyAsync(h_cnt, m->ws_tokcnt, sizeof(int) * B, cudaMemcpyDeviceToHost, st));
-    CUDA_CHECK(cudaMemcpyAsync(h_margin, m->ws_tokcnt + capB, sizeof(int) * B, cudaMemcpyDeviceToHost, st));
+    // pinned result buffer: [0..7] = decode counters 6..13 (streams left unfinished, rounds run, barrier word, -, the kernel's
+    // start / end globaltimer stamps), then token counts [capB], margins [capB], tokens [B][T*MAX_SYMBOLS]: three copies
+    int* h_unf = m->h_tok.p;
+    int* h_cnt = m->h_tok.p + 8;
+    int* h_toks = h_cnt + 2 * capB;
+    CUDA_CHECK(cudaMemcpyAsync(h_unf, m->ws_unfinished + 6, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaMemcpyAsync(h_cnt, m->ws_tokcnt, sizeof(int) * 2 * capB, cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaMemcpyAsync(h_toks, m->ws_tok, sizeof(int) * (size_t)B * T * MAX_SYMBOLS, cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaEventRecord(m->ev[3], st));
 }
@@ -909,12 +904,11 @@ void run_batch_finish(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
     const Mode& md = mc->mode;
     const int B = (int)items.size(), T = md.T, capB = m->cap_B;
     int* h_unf = m->h_tok.p;
-    int* h_cnt = m->h_tok.p + 6;
-    int* h_margin = h_cnt + B;
-    int* h_toks = h_margin + B;
-    (void)capB;
+    int* h_cnt = m->h_tok.p + 8;
+    int* h_margin = h_cnt + capB;
+    int* h_toks = h_cnt + 2 * capB;
     CUDA_CHECK(cudaEventSynchronize(m->ev[3]));
-    m->stats.d2h_bytes += (long long)sizeof(int) * ((size_t)2 * B + (size_t)B * T * MAX_SYMBOLS + 6);
+    m->stats.d2h_bytes += (long long)sizeof(int) * ((size_t)2 * capB + (size_t)B * T * MAX_SYMBOLS + 8);
     if (h_unf[0] != 0) throw Error("decode loop did not terminate");
     if (getenv("NB200_DK_TRACE")) {
         unsigned long long a[7];
@@ -952,8 +946,8 @@ void run_batch_finish(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
     m->stats.last_frontend_ms = 0.0;  // the frontend is part of the encoder graph
     // the decode kernel stamps its own start / end (globaltimer ns) into counters[10..13]
     unsigned long long dk0, dk1;
-    memcpy(&dk0, h_unf + 2, 8);
-    memcpy(&dk1, h_unf + 4, 8);
+    memcpy(&dk0, h_unf + 4, 8);
+    memcpy(&dk1, h_unf + 6, 8);
     const double dec_ms = dk1 > dk0 ? (double)(dk1 - dk0) * 1e-6 : 0.0;
     m->stats.last_encoder_ms = ms02 + ms23 - dec_ms;
     m->stats.last_decoder_ms = dec_ms;
