@@ -130,6 +130,9 @@ struct nb200_model {
     float *sub_b3 = nullptr, *sub_b6 = nullptr, *sub_bout = nullptr;
     F16Matrix sub_w3, sub_w6, sub_wout;
     float *joint_enc_w = nullptr, *joint_enc_b = nullptr;  // fp32: the decoder side stays in fp32 like the reference
+    F16Matrix joint_enc_w3;    // joint.enc as [Wh | Wh | Wl] fp16 [640][3072] (split-precision tensor-core GEMM, see split_f16x3_kernel)
+    Operand op_x3;             // [rows][3072] view of ws_h16: (hi, lo, hi) of the encoder output
+    bool joint_enc_tc = true;  // NB200_JOINT_SGEMM=1: fp32 CUDA-core SGEMM instead
     // multilingual prompt fusion (src/nemo-ggml.cpp:1087-1105), fp32 like the file: fc1 split into its encoder part
     // [2048][1024] and its one-hot part stored per language [num_prompts][2048]; fc2 [1024][2048]
     int num_prompts = 0, default_prompt = -1;
@@ -419,6 +422,20 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
         m->dec.bout = m->upload(bo);
         m->joint_enc_w = m->upload(load_f32(g, "joint.enc.weight", (int64_t)JOINT * D_MODEL));
         m->joint_enc_b = m->upload(load_f32(g, "joint.enc.bias", JOINT));
+        {
+            const std::vector<float> w = load_f32(g, "joint.enc.weight", (int64_t)JOINT * D_MODEL);
+            std::vector<float> w3((size_t)JOINT * 3 * D_MODEL);
+            for (int n = 0; n < JOINT; n++)
+                for (int k = 0; k < D_MODEL; k++) {
+                    const float v = w[(size_t)n * D_MODEL + k];
+                    const float hi = __half2float(__float2half_rn(v));
+                    w3[(size_t)n * 3 * D_MODEL + k] = hi;
+                    w3[(size_t)n * 3 * D_MODEL + D_MODEL + k] = hi;
+                    w3[(size_t)n * 3 * D_MODEL + 2 * D_MODEL + k] = v - hi;  // rounded to fp16 by make_f16
+                }
+            make_f16(m, m->joint_enc_w3, w3, JOINT, 3 * D_MODEL);
+            m->joint_enc_tc = getenv("NB200_JOINT_SGEMM") == nullptr;
+        }
     }
     m->num_prompts = hp.num_prompts;
     if (hp.num_prompts > 0) {  // the prompt kernel must be present exactly when the header advertises prompts (src/nemo-ggml.cpp:424-434)
@@ -490,6 +507,7 @@ void alloc_state(nb200_model* m) {
     operand_init(m->op_a6h, m->ws_a6h, (int)rows_pad, SUB_FEAT);
     operand_init(m->op_a16, m->ws_a16, (int)rows_pad, D_MODEL);
     operand_init(m->op_h16, m->ws_h16, (int)rows_pad, D_FF);
+    operand_init(m->op_x3, m->ws_h16, (int)rows_pad, 3 * D_MODEL);  // same memory, free once the last layer has run
     operand_init(m->op_pos16, m->ws_pos16, 128, D_MODEL);
     {   // device PCM ring per slot: default 2^17 samples (8.2 s); NB200_PCM_RING_LOG2 overrides (15..24)
         int lg = 17;
@@ -812,7 +830,14 @@ void enqueue_encoder(const StepCtx& c) {
         }
     }
     // joint.enc over all frames of the batch, and the decode loop's per-step state
-    launch_sgemm(st, enc_out, m->joint_enc_w, m->joint_enc_b, m->ws_e, M, JOINT, D_MODEL, JOINT, nullptr);
+    if (m->joint_enc_tc && !simt) {
+        launch_split_f16x3(st, enc_out, m->ws_h16, M);
+        EpiParams ej;
+        ej.kind = EPI_STORE; ej.bias = m->joint_enc_b; ej.out_f32 = m->ws_e; ej.ldo = JOINT;
+        gemm(st, m->op_x3, m->joint_enc_w3.op, M, ej, false);
+    } else {
+        launch_sgemm(st, enc_out, m->joint_enc_w, m->joint_enc_b, m->ws_e, M, JOINT, D_MODEL, JOINT, nullptr);
+    }
     launch_decode_chunk(st, m->dec, m->dstate, decode_batch(m, B, T));  // every greedy round of the chunk, one persistent launch
 }
 
