@@ -189,11 +189,11 @@ void launch_prompt_add_relu(cudaStream_t st, float* h, const float* w_lang, cons
 // x = hi + lo + O(2^-24 |x|) with hi = fp16(x), lo = fp16(x - hi). With weights split the same way and laid out as
 // [Wh | Wh | Wl] along K, one fp16 GEMM over K' = 3 * 1024 gives hi.Wh + lo.Wh + hi.Wl = x.W up to ~1e-6 relative (the lo.Wl
 // term, 2^-24, is dropped; fp32 accumulation in TMEM). Used for joint.enc, whose weights the reference keeps in F32.
-__global__ void __launch_bounds__(256) split_f16x3_kernel(const float* __restrict__ x, __half* __restrict__ out) {
+__global__ void __launch_bounds__(256) split_f16x3_kernel(const float* __restrict__ x, __half* __restrict__ out, int cols) {
     pdl_prologue();
     const size_t m = blockIdx.x;
-    const int c = threadIdx.x * 4;
-    const float4 v = *reinterpret_cast<const float4*>(x + m * D_MODEL + c);
+    const int c = blockIdx.y * 1024 + threadIdx.x * 4;
+    const float4 v = *reinterpret_cast<const float4*>(x + m * cols + c);
     const float f[4] = {v.x, v.y, v.z, v.w};
     __half hi[4], lo[4];
 #pragma unroll
@@ -201,16 +201,17 @@ __global__ void __launch_bounds__(256) split_f16x3_kernel(const float* __restric
         hi[i] = __float2half_rn(f[i]);
         lo[i] = __float2half_rn(f[i] - __half2float(hi[i]));
     }
-    __half* row = out + m * (3 * D_MODEL) + c;
+    __half* row = out + m * (3 * (size_t)cols) + c;
     *reinterpret_cast<uint2*>(row) = *reinterpret_cast<const uint2*>(hi);
-    *reinterpret_cast<uint2*>(row + D_MODEL) = *reinterpret_cast<const uint2*>(lo);
-    *reinterpret_cast<uint2*>(row + 2 * D_MODEL) = *reinterpret_cast<const uint2*>(hi);
+    *reinterpret_cast<uint2*>(row + cols) = *reinterpret_cast<const uint2*>(lo);
+    *reinterpret_cast<uint2*>(row + 2 * cols) = *reinterpret_cast<const uint2*>(hi);
 }
 
-void launch_split_f16x3(cudaStream_t st, const float* x, __half* out, int M) {
+void launch_split_f16x3(cudaStream_t st, const float* x, __half* out, int M, int cols) {
     if (M <= 0) return;
-    ProfScope ps(st, "split_f16x3", (double)M * D_MODEL * 3, (double)M * D_MODEL * 10);
-    launch_k(split_f16x3_kernel, dim3(M), dim3(256), 0, st, x, out);
+    if (cols % 1024 != 0) throw Error("split_f16x3: the row length must be a multiple of 1024");
+    ProfScope ps(st, "split_f16x3", (double)M * cols * 3, (double)M * cols * 10);
+    launch_k(split_f16x3_kernel, dim3(dim3(M, cols / 1024)), dim3(256), 0, st, x, out, cols);
     NB_KERNEL_CHECK();
 }
 

@@ -130,6 +130,9 @@ struct nb200_model {
     float *sub_b3 = nullptr, *sub_b6 = nullptr, *sub_bout = nullptr;
     F16Matrix sub_w3, sub_w6, sub_wout;
     float *joint_enc_w = nullptr, *joint_enc_b = nullptr;  // fp32: the decoder side stays in fp32 like the reference
+    F16Matrix pk_w1_3, pk_w2_3;  // prompt kernel fc1 (encoder part) / fc2 as fp16 triples
+    __half* ws_pk16 = nullptr;   // (hi, lo, hi) of the prompt kernel's hidden layer [rows][3 * 2048]
+    Operand op_pk3;
     F16Matrix joint_enc_w3;    // joint.enc as [Wh | Wh | Wl] fp16 [640][3072] (split-precision tensor-core GEMM, see split_f16x3_kernel)
     Operand op_x3;             // [rows][3072] view of ws_h16: (hi, lo, hi) of the encoder output
     bool joint_enc_tc = true;  // NB200_JOINT_SGEMM=1: fp32 CUDA-core SGEMM instead
@@ -240,6 +243,20 @@ void make_f16(nb200_model* m, F16Matrix& dst, const std::vector<float>& w, int r
     dst.ptr = m->upload(h);
     operand_init(dst.op, dst.ptr, rows, K);
     if (!name.empty()) m->by_name[name] = {dst.ptr, rows, K, false};
+}
+
+// fp32 weights [rows][K] as the fp16 triple [Wh | Wh | Wl] along K (see split_f16x3_kernel): the B operand of a GEMM of fp32 quality
+void make_split3(nb200_model* m, F16Matrix& dst, const std::vector<float>& w, int rows, int K) {
+    std::vector<float> w3((size_t)rows * 3 * K);
+    for (int n = 0; n < rows; n++)
+        for (int k = 0; k < K; k++) {
+            const float v = w[(size_t)n * K + k];
+            const float hi = __half2float(__float2half_rn(v));
+            w3[(size_t)n * 3 * K + k] = hi;
+            w3[(size_t)n * 3 * K + K + k] = hi;
+            w3[(size_t)n * 3 * K + 2 * K + k] = v - hi;  // rounded to fp16 by make_f16
+        }
+    make_f16(m, dst, w3, rows, 3 * K);
 }
 
 void load_matrix(nb200_model* m, const GgufFile& g, F16Matrix& dst, const std::string& name, int rows, int K) {
@@ -423,17 +440,7 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
         m->joint_enc_w = m->upload(load_f32(g, "joint.enc.weight", (int64_t)JOINT * D_MODEL));
         m->joint_enc_b = m->upload(load_f32(g, "joint.enc.bias", JOINT));
         {
-            const std::vector<float> w = load_f32(g, "joint.enc.weight", (int64_t)JOINT * D_MODEL);
-            std::vector<float> w3((size_t)JOINT * 3 * D_MODEL);
-            for (int n = 0; n < JOINT; n++)
-                for (int k = 0; k < D_MODEL; k++) {
-                    const float v = w[(size_t)n * D_MODEL + k];
-                    const float hi = __half2float(__float2half_rn(v));
-                    w3[(size_t)n * 3 * D_MODEL + k] = hi;
-                    w3[(size_t)n * 3 * D_MODEL + D_MODEL + k] = hi;
-                    w3[(size_t)n * 3 * D_MODEL + 2 * D_MODEL + k] = v - hi;  // rounded to fp16 by make_f16
-                }
-            make_f16(m, m->joint_enc_w3, w3, JOINT, 3 * D_MODEL);
+            make_split3(m, m->joint_enc_w3, load_f32(g, "joint.enc.weight", (int64_t)JOINT * D_MODEL), JOINT, D_MODEL);
             m->joint_enc_tc = getenv("NB200_JOINT_SGEMM") == nullptr;
         }
     }
@@ -447,9 +454,14 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
             for (int q = 0; q < P; q++) l[(size_t)q * H + n] = w1[(size_t)n * (D_MODEL + P) + D_MODEL + q];
         }
         m->pk_w1 = m->upload(a);
+        make_split3(m, m->pk_w1_3, a, H, D_MODEL);
         m->pk_w1_lang = m->upload(l);
         m->pk_b1 = m->upload(load_f32(g, "prompt_kernel.0.bias", H));
-        m->pk_w2 = m->upload(load_f32(g, "prompt_kernel.2.weight", (int64_t)D_MODEL * H));
+        {
+            const std::vector<float> w2 = load_f32(g, "prompt_kernel.2.weight", (int64_t)D_MODEL * H);
+            m->pk_w2 = m->upload(w2);
+            make_split3(m, m->pk_w2_3, w2, D_MODEL, H);
+        }
         m->pk_b2 = m->upload(load_f32(g, "prompt_kernel.2.bias", D_MODEL));
         m->default_prompt = 101 < P ? 101 : 0;  // 101 = "auto" (src/nemo-ggml.cpp:459-462)
         auto lk = g.str_arr.find("nemo.prompt_langs");
@@ -499,7 +511,11 @@ void alloc_state(nb200_model* m) {
     m->part_rows = rows_pad;
     m->part_max_splits = rows_pad <= 4096 ? 8 : (rows_pad <= 8192 ? 4 : (rows_pad <= 16384 ? 2 : 1));
     m->ws_part = m->alloc<float>((size_t)m->part_max_splits * rows_pad * D_MODEL);
-    if (m->num_prompts > 0) m->ws_pk = m->alloc<float>((size_t)rows_pad * PROMPT_HIDDEN);
+    if (m->num_prompts > 0) {
+        m->ws_pk = m->alloc<float>((size_t)rows_pad * PROMPT_HIDDEN);
+        m->ws_pk16 = m->alloc<__half>((size_t)rows_pad * 3 * PROMPT_HIDDEN);
+        operand_init(m->op_pk3, m->ws_pk16, (int)rows_pad, 3 * PROMPT_HIDDEN);
+    }
     m->ws_pos16 = m->alloc<__half>((size_t)128 * D_MODEL);
     operand_init(m->op_a2h, m->ws_a2h, B * big.t2 * SUB_F2, SUB_CH);
     operand_init(m->op_a5h, m->ws_a5h, (int)rows * SUB_F3, SUB_CH);
@@ -813,9 +829,21 @@ void enqueue_encoder(const StepCtx& c) {
     // fp32 like the file: relu(fc1 . [enc ; onehot]) = relu(enc . W1a^T + b1 + W1[:, 1024 + lang]), then fc2
     const float* enc_out = m->ws_x;
     if (m->num_prompts > 0) {
-        launch_sgemm(st, m->ws_x, m->pk_w1, m->pk_b1, m->ws_pk, M, PROMPT_HIDDEN, D_MODEL, PROMPT_HIDDEN, nullptr);
-        launch_prompt_add_relu(st, m->ws_pk, m->pk_w1_lang, m->ws_meta + 6 * capB, T, M);
-        launch_sgemm(st, m->ws_pk, m->pk_w2, m->pk_b2, m->ws_g, M, D_MODEL, PROMPT_HIDDEN, D_MODEL, nullptr);
+        if (m->joint_enc_tc && !simt) {  // split-precision tensor-core GEMMs (fp32 quality), like joint.enc below
+            launch_split_f16x3(st, m->ws_x, m->ws_h16, M);
+            EpiParams e1;
+            e1.kind = EPI_STORE; e1.bias = m->pk_b1; e1.out_f32 = m->ws_pk; e1.ldo = PROMPT_HIDDEN;
+            gemm(st, m->op_x3, m->pk_w1_3.op, M, e1, false);
+            launch_prompt_add_relu(st, m->ws_pk, m->pk_w1_lang, m->ws_meta + 6 * capB, T, M);
+            launch_split_f16x3(st, m->ws_pk, m->ws_pk16, M, PROMPT_HIDDEN);
+            EpiParams e2;
+            e2.kind = EPI_STORE; e2.bias = m->pk_b2; e2.out_f32 = m->ws_g; e2.ldo = D_MODEL;
+            gemm(st, m->op_pk3, m->pk_w2_3.op, M, e2, false);
+        } else {
+            launch_sgemm(st, m->ws_x, m->pk_w1, m->pk_b1, m->ws_pk, M, PROMPT_HIDDEN, D_MODEL, PROMPT_HIDDEN, nullptr);
+            launch_prompt_add_relu(st, m->ws_pk, m->pk_w1_lang, m->ws_meta + 6 * capB, T, M);
+            launch_sgemm(st, m->ws_pk, m->pk_w2, m->pk_b2, m->ws_g, M, D_MODEL, PROMPT_HIDDEN, D_MODEL, nullptr);
+        }
         enc_out = m->ws_g;
     }
     if (c.taps) {

@@ -85,8 +85,8 @@ struct ConvArgs {
 void launch_dwconv(cudaStream_t st, const ConvArgs& a);  // out = fq(silu(LN(dwconv([cache ; g])))), other cache buffer = last 8 of [cache ; g]
 
 // fp32 [rows][1024] -> fp16 with optional fake-quant per 32 (used to prepare the positional table GEMM input)
-// out[m] = (fp16(x), fp16(x - fp16(x)), fp16(x)) over [M][3 * 1024]: A operand of the split-precision joint.enc GEMM
-void launch_split_f16x3(cudaStream_t st, const float* x, __half* out, int M);
+// out[m] = (fp16(x), fp16(x - fp16(x)), fp16(x)) over [M][3 * cols]: A operand of the split-precision GEMMs (joint.enc, prompt kernel)
+void launch_split_f16x3(cudaStream_t st, const float* x, __half* out, int M, int cols = D_MODEL);
 void launch_cast_f16(cudaStream_t st, const float* x, __half* out, int act_quant, int rows, int cols);
 // sinusoid rows for relative positions p0 .. p0+n-1 (src/nemo-ggml.cpp:17-32) -> fp32 [n][1024]
 void launch_pos_emb(cudaStream_t st, float* out, int p0, int n);
