@@ -202,7 +202,7 @@ void launch_mel(cudaStream_t st, const MelTables& tb, const MelBatch& mb, float*
     if (radix2)
         launch_k(mel_kernel, dim3(dim3(max_frames, B)), dim3(256), 0, st, tb, mb, mel_out);
     else
-        launch_k(mel_r8_kernel, dim3(dim3(cdiv(max_frames, MEL_FPB), B)), dim3(64 * MEL_FPB), 0, st, tb, mb, mel_out);
+        for (int rep = dup_family("mel") ? 2 : 1; rep > 0; rep--) launch_k(mel_r8_kernel, dim3(dim3(cdiv(max_frames, MEL_FPB), B)), dim3(64 * MEL_FPB), 0, st, tb, mb, mel_out);
     NB_KERNEL_CHECK();
 }
 
@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(256) sub_stage1_kernel(SubWeights w, const flo
 void launch_sub_stage1(cudaStream_t st, const SubWeights& w, const float* mel, __half* out, int B, int chunk_mel, int t1, int t2) {
     ProfScope ps(st, "sub_conv0_dw2", (double)B * t2 * SUB_F2 * SUB_CH * 2.0 * 9 * 10,
                  (double)B * (chunk_mel * N_MELS * 4.0 + (double)t2 * SUB_F2 * SUB_CH * 2));
-    launch_k(sub_stage1_kernel, dim3(dim3(t2, B)), dim3(256), 0, st, w, mel, out, chunk_mel, t1, t2);
+    for (int rep = dup_family("sub1") ? 2 : 1; rep > 0; rep--) launch_k(sub_stage1_kernel, dim3(dim3(t2, B)), dim3(256), 0, st, w, mel, out, chunk_mel, t1, t2);
     NB_KERNEL_CHECK();
 }
 
@@ -313,7 +313,7 @@ __global__ void __launch_bounds__(256) sub_stage2_kernel(SubWeights w, const flo
 void launch_sub_stage2(cudaStream_t st, const SubWeights& w, const float* a3, __half* out, int B, int t2, int t3) {
     ProfScope ps(st, "sub_dw5", (double)B * (t3 - 2) * SUB_F3 * SUB_CH * 18.0,
                  (double)B * ((double)t2 * SUB_F2 * SUB_CH * 4 + (double)(t3 - 2) * SUB_F3 * SUB_CH * 2));
-    launch_k(sub_stage2_kernel, dim3(dim3(SUB_F3, t3 - 2, B)), dim3(256), 0, st, w, a3, out, t2, t3);
+    for (int rep = dup_family("sub2") ? 2 : 1; rep > 0; rep--) launch_k(sub_stage2_kernel, dim3(dim3(SUB_F3, t3 - 2, B)), dim3(256), 0, st, w, a3, out, t2, t3);
     NB_KERNEL_CHECK();
 }
 
