@@ -286,6 +286,255 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attention_f16_kernel(AttnArgs a
     }
 }
 
+// ---- single-wave variant (default for T > 2) --------------------------------------------------------------------------
+// Same math as attention_f16_kernel with 51 KB of shared memory instead of 103 KB, so that four CTAs fit on an SM and the
+// 512 (head, stream) items of the 64-stream step are ONE wave instead of 1.7:
+//   * the projected positions are not staged: their MMA B fragments come straight from global memory (the table is shared
+//     by all streams and stays in L2). Lane (g, t) loads the 16 contiguous bytes P[n0 + g][32 ks + 8 t .. + 8): a dot product
+//     does not care in which order k is summed, so the 16 k-slots of an MMA are mapped to features 8 t + {0..3} (first MMA
+//     of a 32-feature block) and 8 t + {4..7} (second), and the A fragments of Q + v are read with the same map;
+//   * K and V share one buffer: V is fetched (after an L2 prefetch issued at the start) once every warp is done with K,
+//     under the softmax.
+struct AttSmemS {
+    static constexpr int KV_ROWS = 96;
+    static constexpr int KV_OFF = 0;
+    static constexpr int QU_OFF = KV_OFF + KV_ROWS * ROWB;
+    static constexpr int QV_OFF = QU_OFF + 16 * ROWB;
+    static constexpr int S1_OFF = QV_OFF + 16 * ROWB;
+    static constexpr int S2_OFF = S1_OFF + 16 * S1_LD * 4;
+    static constexpr int PR_OFF = S2_OFF + 16 * S2_LD * 4;
+    static constexpr int TOTAL = PR_OFF + 16 * PR_LD * 2;
+    static_assert(16 * CX_LD * 4 <= 16 * S1_LD * 4 + 16 * S2_LD * 4, "context staging must fit the score area");
+    static_assert(TOTAL <= 52 * 1024, "four CTAs per SM");
+};
+
+__global__ void __launch_bounds__(AT_THREADS, 4) attention_f16s_kernel(AttnArgs a) {
+    pdl_launch();
+    extern __shared__ __align__(16) uint8_t smem[];
+    using L = AttSmemS;
+    const int h = blockIdx.x, b = blockIdx.y, T = a.T;
+    const int kv = LEFT + T, npos = LEFT + 2 * T - 1;
+    const int kvt = (kv + 7) >> 3, npt = (npos + 7) >> 3, kvs = (kv + 15) >> 4;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const int slot = a.slot[b], wpos = a.wpos[b];
+    int start = wpos - LEFT;
+    if (start < 0) start += RING;
+    __half* kring = a.k_ring + (size_t)slot * RING * D_MODEL + h * D_HEAD;
+    __half* vring = a.v_ring + (size_t)slot * RING * D_MODEL + h * D_HEAD;
+    const __half* qkv = a.qkv + (size_t)b * T * (3 * D_MODEL) + h * D_HEAD;
+    const __half* pbase = a.pos + h * D_HEAD;
+    const uint32_t sb = s_u32(smem);
+
+    // cached K rows (written by earlier steps): requested before griddepcontrol.wait; cached V rows: pulled into L2 now
+    for (int idx = tid; idx < LEFT * 16; idx += AT_THREADS) {
+        const int j = idx >> 4, c = idx & 15;
+        int pos = start + j;
+        if (pos >= RING) pos -= RING;
+        cp_async16(sb + L::KV_OFF + j * ROWB + c * 16, kring + (size_t)pos * D_MODEL + c * 8);
+    }
+    for (int idx = tid; idx < LEFT * 2; idx += AT_THREADS) {
+        int pos = start + (idx >> 1);
+        if (pos >= RING) pos -= RING;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(vring + (size_t)pos * D_MODEL + (idx & 1) * 64));
+    }
+    {   // rows kv .. 95 stay zero for both operands (0 * garbage must stay finite in P.V)
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        for (int idx = tid; idx < (L::KV_ROWS - kv) * 16; idx += AT_THREADS)
+            *reinterpret_cast<uint4*>(smem + L::KV_OFF + (kv + (idx >> 4)) * ROWB + (idx & 15) * 16) = z;
+    }
+    pdl_wait();
+    for (int idx = tid; idx < T * 16; idx += AT_THREADS) {
+        const int i = idx >> 4, c = idx & 15;
+        cp_async16(sb + L::KV_OFF + (LEFT + i) * ROWB + c * 16, qkv + (size_t)i * (3 * D_MODEL) + D_MODEL + c * 8);
+    }
+    cp_commit();
+    // Q + u, Q + v (fp32 add, one rounding to fp16); rows >= T are zero
+    for (int idx = tid; idx < 16 * 16; idx += AT_THREADS) {
+        const int r = idx >> 4, c = idx & 15;
+        uint4 ou = make_uint4(0, 0, 0, 0), ov = ou;
+        if (r < T) {
+            const uint4 q8 = *reinterpret_cast<const uint4*>(qkv + (size_t)r * (3 * D_MODEL) + c * 8);
+            const __half2* qh = reinterpret_cast<const __half2*>(&q8);
+            const float4 u0 = *reinterpret_cast<const float4*>(a.bias_u + h * D_HEAD + c * 8), u1 = *reinterpret_cast<const float4*>(a.bias_u + h * D_HEAD + c * 8 + 4);
+            const float4 v0 = *reinterpret_cast<const float4*>(a.bias_v + h * D_HEAD + c * 8), v1 = *reinterpret_cast<const float4*>(a.bias_v + h * D_HEAD + c * 8 + 4);
+            const float uu[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+            const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+            __half2 hu[4], hv[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const float2 q2 = __half22float2(qh[e]);
+                hu[e] = __floats2half2_rn(q2.x + uu[2 * e], q2.y + uu[2 * e + 1]);
+                hv[e] = __floats2half2_rn(q2.x + vv[2 * e], q2.y + vv[2 * e + 1]);
+            }
+            ou = *reinterpret_cast<uint4*>(hu);
+            ov = *reinterpret_cast<uint4*>(hv);
+        }
+        *reinterpret_cast<uint4*>(smem + L::QU_OFF + r * ROWB + c * 16) = ou;
+        *reinterpret_cast<uint4*>(smem + L::QV_OFF + r * ROWB + c * 16) = ov;
+    }
+    __syncthreads();  // Q + u, Q + v visible
+
+    float* S1 = reinterpret_cast<float*>(smem + L::S1_OFF);
+    float* S2 = reinterpret_cast<float*>(smem + L::S2_OFF);
+    // ---- position scores (Q + v) P^T, 8 positions per tile, B fragments from global with the permuted k map ----
+    for (int tile = warp; tile < npt; tile += 8) {
+        const int n0 = 8 * tile;
+        const int prow = min(n0 + g, npos - 1);  // rows beyond the table are never read back: any finite row will do
+        const __half* pp = pbase + (size_t)prow * D_MODEL + 8 * t;
+        uint4 pf[4];
+#pragma unroll
+        for (int ks = 0; ks < 4; ks++) pf[ks] = __ldg(reinterpret_cast<const uint4*>(pp + 32 * ks));
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int ks = 0; ks < 4; ks++) {
+            const uint4 q0 = *reinterpret_cast<const uint4*>(smem + L::QV_OFF + g * ROWB + (32 * ks + 8 * t) * 2);
+            const uint4 q1 = *reinterpret_cast<const uint4*>(smem + L::QV_OFF + (g + 8) * ROWB + (32 * ks + 8 * t) * 2);
+            const uint32_t a0[4] = {q0.x, q1.x, q0.y, q1.y}, a1[4] = {q0.z, q1.z, q0.w, q1.w};
+            mma_f16(acc, a0, pf[ks].x, pf[ks].y);
+            mma_f16(acc, a1, pf[ks].z, pf[ks].w);
+        }
+        *reinterpret_cast<float2*>(S2 + g * S2_LD + n0 + 2 * t) = make_float2(acc[0], acc[1]);
+        *reinterpret_cast<float2*>(S2 + (g + 8) * S2_LD + n0 + 2 * t) = make_float2(acc[2], acc[3]);
+    }
+    cp_wait<0>();  // K has landed (this thread's copies); the barrier makes everyone's visible
+    __syncthreads();
+
+    // ---- append this chunk's K rows to the ring ----
+    for (int idx = tid; idx < T * 16; idx += AT_THREADS) {
+        const int i = idx >> 4, c = idx & 15;
+        int pos = wpos + i;
+        if (pos >= RING) pos -= RING;
+        *reinterpret_cast<uint4*>(kring + (size_t)pos * D_MODEL + c * 8) = *reinterpret_cast<const uint4*>(smem + L::KV_OFF + (LEFT + i) * ROWB + c * 16);
+    }
+    // ---- key scores (Q + u) K^T ----
+    {
+        const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_col = (lane >> 4) * 16;
+        const int b_row = lane & 7, b_col = (lane >> 3) * 16;
+        for (int tile = warp; tile < kvt; tile += 8) {
+            const int n0 = 8 * tile;
+            const uint32_t qa = sb + L::QU_OFF + a_row * ROWB + a_col;
+            const uint32_t kb = sb + L::KV_OFF + (n0 + b_row) * ROWB + b_col;
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) {
+                uint32_t bf[4], a0[4], a1[4];
+                ldsm_x4(bf, kb + ks * 64);
+                ldsm_x4(a0, qa + ks * 64);
+                ldsm_x4(a1, qa + ks * 64 + 32);
+                mma_f16(acc, a0, bf[0], bf[1]);
+                mma_f16(acc, a1, bf[2], bf[3]);
+            }
+            *reinterpret_cast<float2*>(S1 + g * S1_LD + n0 + 2 * t) = make_float2(acc[0], acc[1]);
+            *reinterpret_cast<float2*>(S1 + (g + 8) * S1_LD + n0 + 2 * t) = make_float2(acc[2], acc[3]);
+        }
+    }
+    __syncthreads();  // every warp is done with K: the buffer now receives V
+
+    for (int idx = tid; idx < kv * 16; idx += AT_THREADS) {
+        const int j = idx >> 4, c = idx & 15;
+        const __half* src;
+        if (j < LEFT) {
+            int pos = start + j;
+            if (pos >= RING) pos -= RING;
+            src = vring + (size_t)pos * D_MODEL + c * 8;
+        } else {
+            src = qkv + (size_t)(j - LEFT) * (3 * D_MODEL) + 2 * D_MODEL + c * 8;
+        }
+        cp_async16(sb + L::KV_OFF + j * ROWB + c * 16, src);
+    }
+    cp_commit();
+
+    // ---- rel-shift by indexing, scale, mask, softmax (fp32): one warp per query row -> fp16 probabilities ----
+    {
+        __half* Pr = reinterpret_cast<__half*>(smem + L::PR_OFF);
+        const int masked = LEFT - a.valid[b];
+        const float scale = 1.0f / sqrtf((float)D_HEAD);
+        for (int i = warp; i < 16; i += 8) {
+            __half* prow_out = Pr + i * PR_LD;
+            if (i >= T) {
+                for (int j = lane; j < PR_LD; j += 32) prow_out[j] = __float2half_rn(0.0f);
+                continue;
+            }
+            const float* row = S1 + i * S1_LD;
+            const float* prow = S2 + i * S2_LD + (LEFT + i + T - 1);
+            float sc[3];
+            float mx = -INFINITY;
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+                const int j = lane + 32 * q;
+                float s = -INFINITY;
+                if (j < kv) {
+                    s = (row[j] + prow[-j]) * scale;
+                    if (j < masked) s += -1e9f;
+                }
+                sc[q] = s;
+                mx = fmaxf(mx, s);
+            }
+            mx = warp_max(mx);
+            float sum = 0.0f;
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+                const int j = lane + 32 * q;
+                sc[q] = (j < kv) ? expf(sc[q] - mx) : 0.0f;
+                sum += sc[q];
+            }
+            sum = warp_sum(sum);
+            const float inv = 1.0f / sum;
+#pragma unroll
+            for (int q = 0; q < 3; q++) {
+                const int j = lane + 32 * q;
+                prow_out[j] = __float2half_rn(sc[q] * inv);
+            }
+            if (lane < PR_LD - 96) prow_out[96 + lane] = __float2half_rn(0.0f);
+        }
+    }
+    cp_wait<0>();  // V has landed
+    __syncthreads();  // ... and the probabilities are complete; S1 / S2 are dead from here on
+
+    for (int idx = tid; idx < T * 16; idx += AT_THREADS) {
+        const int i = idx >> 4, c = idx & 15;
+        int pos = wpos + i;
+        if (pos >= RING) pos -= RING;
+        *reinterpret_cast<uint4*>(vring + (size_t)pos * D_MODEL + c * 8) = *reinterpret_cast<const uint4*>(smem + L::KV_OFF + (LEFT + i) * ROWB + c * 16);
+    }
+    // ---- context: warp w owns features [16w, 16w+16); k runs over the keys in steps of 16 ----
+    float* Cx = reinterpret_cast<float*>(smem + L::S1_OFF);
+    {
+        float acc0[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+        const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_col = (lane >> 4) * 16;
+        const uint32_t pa = sb + L::PR_OFF + a_row * (PR_LD * 2) + a_col;
+        const uint32_t vb = sb + L::KV_OFF + ((lane & 7) + ((lane >> 3) & 1) * 8) * ROWB + (16 * warp + (lane >> 4) * 8) * 2;
+        for (int ks = 0; ks < kvs; ks++) {
+            uint32_t af[4], bf[4];
+            ldsm_x4(af, pa + ks * 32);
+            ldsm_x4_t(bf, vb + ks * 16 * ROWB);
+            mma_f16(acc0, af, bf[0], bf[1]);
+            mma_f16(acc1, af, bf[2], bf[3]);
+        }
+        *reinterpret_cast<float2*>(Cx + g * CX_LD + 16 * warp + 2 * t) = make_float2(acc0[0], acc0[1]);
+        *reinterpret_cast<float2*>(Cx + (g + 8) * CX_LD + 16 * warp + 2 * t) = make_float2(acc0[2], acc0[3]);
+        *reinterpret_cast<float2*>(Cx + g * CX_LD + 16 * warp + 8 + 2 * t) = make_float2(acc1[0], acc1[1]);
+        *reinterpret_cast<float2*>(Cx + (g + 8) * CX_LD + 16 * warp + 8 + 2 * t) = make_float2(acc1[2], acc1[3]);
+    }
+    __syncthreads();
+    for (int idx = tid; idx < T * (D_HEAD / 4); idx += AT_THREADS) {
+        const int i = idx >> 5, d = (idx & 31) * 4;
+        float4 v = *reinterpret_cast<const float4*>(Cx + i * CX_LD + d);
+        if (a.act_quant) {
+            const float amax = group8_max(fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+            v.x = fake_quant(v.x, amax);
+            v.y = fake_quant(v.y, amax);
+            v.z = fake_quant(v.z, amax);
+            v.w = fake_quant(v.w, amax);
+        }
+        const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
+        uint2 u;
+        u.x = *reinterpret_cast<const uint32_t*>(&lo);
+        u.y = *reinterpret_cast<const uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(a.out + ((size_t)(b * T + i)) * D_MODEL + h * D_HEAD + d) = u;
+    }
+}
+
 // ---- streaming kernel for the low-latency modes (T <= 2: right_context 0 and 1) -----------------------------------
 // With one or two query frames there is nothing for a tensor core to do (the MMA kernel pads to 16 query rows and
 // stages 100 KB per CTA, two CTAs per SM): the work is reading 70 K rows, 70 V rows and ~71 position rows per (stream,
@@ -615,14 +864,20 @@ void launch_attention(cudaStream_t st, const AttnArgs& a) {
         NB_KERNEL_CHECK();
         return;
     }
+    static const bool two_wave = getenv("NB200_ATTN_STAGED") != nullptr;  // the 103 KB version that stages K, V and P at once
     static bool configured = false;
     if (!configured) {
         CUDA_CHECK(cudaFuncSetAttribute(attention_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttSmem::TOTAL));
+        CUDA_CHECK(cudaFuncSetAttribute(attention_f16s_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttSmemS::TOTAL));
         configured = true;
     }
     ProfScope ps(st, "attention_f16", flops, bytes);
-    for (int rep = dup_family("attention") ? 2 : 1; rep > 0; rep--)
-        launch_k(attention_f16_kernel, dim3(dim3(N_HEADS, a.B)), dim3(AT_THREADS), (size_t)AttSmem::TOTAL, st, a);
+    for (int rep = dup_family("attention") ? 2 : 1; rep > 0; rep--) {
+        if (two_wave)
+            launch_k(attention_f16_kernel, dim3(dim3(N_HEADS, a.B)), dim3(AT_THREADS), (size_t)AttSmem::TOTAL, st, a);
+        else
+            launch_k(attention_f16s_kernel, dim3(dim3(N_HEADS, a.B)), dim3(AT_THREADS), (size_t)AttSmemS::TOTAL, st, a);
+    }
     NB_KERNEL_CHECK();
 }
 
