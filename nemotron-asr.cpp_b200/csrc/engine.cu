@@ -180,6 +180,9 @@ struct nb200_model {
     // instead of a cudaMemcpyAsync per stream; two arenas so feeding can go on while a flushed one is still in flight.
     UploadArena arena[2];
     int cur_arena = 0;
+    cudaStream_t st_copy = nullptr;  // audio uploads (H2D + scatter) run here, beside the step's stream
+    cudaEvent_t upload_ev = nullptr; // recorded after every flush; the next step's stream waits for it
+    bool upload_wait = false;
     int16_t* d_stage = nullptr;    // device copy of the arena being flushed
     UploadSeg* d_segs = nullptr;
     // a step launched by nb200_step_begin and not yet completed by nb200_step_end
@@ -222,6 +225,8 @@ struct nb200_model {
         for (auto* gm : {&enc_graphs, &dec_graphs})
             for (auto& kv : *gm)
                 if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+        if (upload_ev) cudaEventDestroy(upload_ev);
+        if (st_copy) cudaStreamDestroy(st_copy);
         if (st) cudaStreamDestroy(st);
     }
 };
@@ -656,18 +661,23 @@ __global__ void __launch_bounds__(256) pcm_scatter_kernel(const int16_t* __restr
     for (int i = blockIdx.y * 4096 + threadIdx.x; i < end; i += 256) dst[i] = src[i];
 }
 
-// Sends the current arena to the device (one H2D copy of the samples, one of the segment table, one scatter kernel on
-// the library's stream) and switches to the other arena. No host synchronisation unless that one is still in flight.
+// Sends the current arena to the device (one H2D copy of the samples, one of the segment table, one scatter kernel) and
+// switches to the other arena. No host synchronisation unless that one is still in flight. The work goes to the COPY
+// stream, so audio fed while a step is running (nb200_feed_batch between nb200_step_begin and _end) is already in the
+// rings when the next step starts; that step's stream waits for `upload_ev`. Ring positions written here are never ones
+// a launched-but-unfinished chunk still reads (upload_pcm only takes what fits before keep_from()).
 void flush_uploads(nb200_model* m) {
     UploadArena& A = m->arena[m->cur_arena];
     if (A.nseg == 0) return;
-    cudaStream_t st = m->st;
+    cudaStream_t st = m->st_copy;
     CUDA_CHECK(cudaMemcpyAsync(m->d_stage, A.pcm.p, A.off * sizeof(int16_t), cudaMemcpyHostToDevice, st));
     CUDA_CHECK(cudaMemcpyAsync(m->d_segs, A.segs.p, (size_t)A.nseg * sizeof(UploadSeg), cudaMemcpyHostToDevice, st));
     launch_k(pcm_scatter_kernel, dim3(A.nseg, cdiv(A.max_n, 4096)), dim3(256), 0, st, (const int16_t*)m->d_stage, (const UploadSeg*)m->d_segs, m->pcm_ring);
     NB_KERNEL_CHECK();
     CUDA_CHECK(cudaEventRecord(A.done, st));
     A.busy = true;
+    CUDA_CHECK(cudaEventRecord(m->upload_ev, st));
+    m->upload_wait = true;
     m->stats.h2d_bytes += (long long)(A.off * sizeof(int16_t) + (size_t)A.nseg * sizeof(UploadSeg));
     m->cur_arena ^= 1;
     UploadArena& N = m->arena[m->cur_arena];
@@ -1047,6 +1057,8 @@ nb200_model* nb200_model_load(const char* gguf_path, int device, int max_streams
         m->device = device;
         m->max_streams = max_streams;
         CUDA_CHECK(cudaStreamCreateWithFlags(&m->st, cudaStreamNonBlocking));
+        CUDA_CHECK(cudaStreamCreateWithFlags(&m->st_copy, cudaStreamNonBlocking));
+        CUDA_CHECK(cudaEventCreateWithFlags(&m->upload_ev, cudaEventDisableTiming));
         build_model(m, gguf_path, flags);
         alloc_state(m);
         CUDA_CHECK(cudaStreamSynchronize(m->st));
@@ -1227,7 +1239,11 @@ int nb200_step_begin(nb200_model* m) {
             s->finalize_requested = false;
         }
     }
-    flush_uploads(m);  // all fed audio: one copy + one scatter kernel ahead of the step's kernels
+    flush_uploads(m);  // whatever was fed since the last flush: one copy + one scatter kernel on the copy stream
+    if (m->upload_wait) {
+        CUDA_CHECK(cudaStreamWaitEvent(m->st, m->upload_ev, 0));
+        m->upload_wait = false;
+    }
     int total = 0;
     size_t left = groups.size();
     for (auto& kv : groups) {
@@ -1270,6 +1286,13 @@ int nb200_feed_batch(nb200_model* m, nb200_stream* const* streams, const int16_t
         }
         const int r = nb200_stream_feed(streams[i], pcm[i], n_samples[i]);
         if (r < 0) return r;
+    }
+    try {  // start the transfer now: it overlaps the step that may be running
+        CUDA_CHECK(cudaSetDevice(m->device));
+        flush_uploads(m);
+    } catch (const std::exception& e) {
+        set_error(e.what());
+        return NB200_ERR;
     }
     return NB200_OK;
 }
