@@ -865,11 +865,10 @@ void launch_attention(cudaStream_t st, const AttnArgs& a) {
         return;
     }
     static const bool two_wave = getenv("NB200_ATTN_STAGED") != nullptr;  // the 103 KB version that stages K, V and P at once
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceOnce once;
+    if (once.first()) {
         CUDA_CHECK(cudaFuncSetAttribute(attention_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttSmem::TOTAL));
         CUDA_CHECK(cudaFuncSetAttribute(attention_f16s_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AttSmemS::TOTAL));
-        configured = true;
     }
     ProfScope ps(st, "attention_f16", flops, bytes);
     for (int rep = dup_family("attention") ? 2 : 1; rep > 0; rep--) {

@@ -101,6 +101,20 @@ void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cuda
 }
 #endif
 
+// cudaFuncSetAttribute is per device: "done once" flags must be kept per device, or a second model on another GPU of
+// the same process (server_loop.h ShardedWorkers) would launch with the default 48 KB dynamic shared-memory limit.
+struct PerDeviceOnce {
+    bool done[64] = {};
+    bool first() {  // true the first time it is called for the current device
+        int dev = 0;
+        cudaGetDevice(&dev);
+        dev &= 63;
+        if (done[dev]) return false;
+        done[dev] = true;
+        return true;
+    }
+};
+
 template <typename T>
 T* dalloc(size_t n) {
     T* p = nullptr;

@@ -533,14 +533,15 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
 
 static int decode_grid() {
     static int g = 0;
+    static PerDeviceOnce once;
     if (!g) {
         int dev = 0, sms = 0;
         CUDA_CHECK(cudaGetDevice(&dev));
         CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
         g = std::min(sms, 148);
         if ((VOCAB + g - 1) / g > DK_MAXR || (DEC + g - 1) / g > DK_MAXU) throw Error("decode kernel: too few SMs for its row split");
-        CUDA_CHECK(cudaFuncSetAttribute(decode_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DkSmem)));
     }
+    if (once.first()) CUDA_CHECK(cudaFuncSetAttribute(decode_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DkSmem)));
     return g;
 }
 

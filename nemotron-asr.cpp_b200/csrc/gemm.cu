@@ -476,11 +476,8 @@ void operand_init(Operand& op, const __half* ptr, int rows, int K) {
 template <int BN, int STAGES, int CG, int EC>
 static void launch_tc_ec(cudaStream_t st, const Operand& A, const Operand& W, const CUtensorMap& omap, int M, const EpiParams& epi, int splits) {
     using S = TcSmem<BN, STAGES, CG>;
-    static bool configured = false;
-    if (!configured) {
-        CUDA_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, CG, EC>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
-        configured = true;
-    }
+    static PerDeviceOnce once;
+    if (once.first()) CUDA_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, CG, EC>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
     dim3 grid(CG * (W.rows / BN), cdiv(M, TC_BM * CG), splits);
     launch_kc(gemm_tc_kernel<BN, STAGES, CG, EC>, grid, dim3(TC_THREADS), (size_t)S::TOTAL, st, CG, A.box(128), W.box(S::B_ROWS), omap, M,
               A.K / TC_BK, epi);

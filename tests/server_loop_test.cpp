@@ -54,18 +54,25 @@ int main(int argc, char** argv) {
     const int n_streams = atoi(argv[2]);
     std::vector<std::vector<int16_t>> pcms;
     for (int i = 3; i < argc; i++) pcms.push_back(read_pcm(argv[i]));
-    nb200_model* m = nb200_model_load(argv[1], 0, n_streams + 1, 0);
-    if (!m) {
-        fprintf(stderr, "load failed: %s\n", nb200_last_error());
-        return 1;
+    // NB200_TEST_DEVICES=n: one model replica per GPU in this process, sessions pinned by stream_id % n (ShardedWorkers)
+    const int n_dev = getenv("NB200_TEST_DEVICES") ? atoi(getenv("NB200_TEST_DEVICES")) : 1;
+    std::vector<nb200_model*> models;
+    for (int d = 0; d < n_dev; d++) {
+        nb200_model* md = nb200_model_load(argv[1], d, n_streams + 1, 0);
+        if (!md) {
+            fprintf(stderr, "load failed on device %d: %s\n", d, nb200_last_error());
+            return 1;
+        }
+        models.push_back(md);
     }
+    nb200_model* m = models[0];
     const int modes[4] = {13, 0, 6, 13};
     std::mutex mu;
     std::map<uint64_t, std::string> texts;
     std::map<uint64_t, int> finals;
     nb200::WorkerStats st;
     {
-        nb200::BatchWorker w(m, [&](uint64_t id, const std::string& t, bool fin) {
+        nb200::ShardedWorkers w(models, [&](uint64_t id, const std::string& t, bool fin) {
             std::lock_guard<std::mutex> g(mu);
             texts[id] += t;
             finals[id] += fin ? 1 : 0;
@@ -89,7 +96,11 @@ int main(int argc, char** argv) {
         r0.join();
         r1.join();
         w.stop();
-        st = w.stats();
+        for (size_t d = 0; d < w.size(); d++) {
+            const nb200::WorkerStats sd = w.stats(d);
+            st.steps += sd.steps; st.stream_chunks += sd.stream_chunks; st.events += sd.events; st.errors += sd.errors;
+            st.max_batch = std::max(st.max_batch, sd.max_batch);
+        }
     }
     int mismatches = 0, not_closed = 0;
     for (int i = 0; i < n_streams; i++) {
@@ -102,9 +113,9 @@ int main(int argc, char** argv) {
     }
     nb200_stats gs;
     nb200_get_stats(m, &gs);
-    printf("{\"streams\": %d, \"mismatches\": %d, \"not_closed\": %d, \"steps\": %llu, \"stream_chunks\": %llu, \"max_batch\": %d, \"events\": %llu, \"errors\": %llu}\n",
-           n_streams, mismatches, not_closed, (unsigned long long)st.steps, (unsigned long long)st.stream_chunks, st.max_batch,
+    printf("{\"devices\": %d, \"streams\": %d, \"mismatches\": %d, \"not_closed\": %d, \"steps\": %llu, \"stream_chunks\": %llu, \"max_batch\": %d, \"events\": %llu, \"errors\": %llu}\n",
+           n_dev, n_streams, mismatches, not_closed, (unsigned long long)st.steps, (unsigned long long)st.stream_chunks, st.max_batch,
            (unsigned long long)st.events, (unsigned long long)st.errors);
-    nb200_model_free(m);
+    for (nb200_model* md : models) nb200_model_free(md);
     return mismatches || not_closed || st.errors ? 1 : 0;
 }

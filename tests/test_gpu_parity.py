@@ -4,6 +4,8 @@
 Tolerances (BASELINE.json north_star): log-mel <= 1e-4 absolute; encoder_out per chunk <= 1e-2 relative L2; greedy
 tokens identical per chunk with every mismatch traced to a near-tie logit (top1-top2 gap recorded by the library).
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -448,12 +450,15 @@ def test_server_loop_batches(nb, gguf_f32, tmp_path):
     subprocess.run(["g++", "-std=c++17", "-O2", "-I", str(root / "include"), "-I", str(pkg), str(root / "tests" / "server_loop_test.cpp"),
                     "-o", str(exe), "-L", str(pkg), "-lnemob200", f"-Wl,-rpath,{pkg}", "-lpthread"], check=True)
     pcms = [inputs.pcm_path(41, 5.0), inputs.pcm_path(42, 3.7), inputs.pcm_path(43, 4.4)]
-    r = subprocess.run([str(exe), gguf_f32, "10", *pcms], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300)
-    print(r.stdout, r.stderr[-2000:])
-    assert r.returncode == 0, r.stderr[-2000:]
-    d = json.loads(r.stdout.strip().splitlines()[-1])
-    assert d["mismatches"] == 0 and d["not_closed"] == 0 and d["errors"] == 0
-    assert d["max_batch"] > 1 and d["stream_chunks"] > d["steps"]
+    import torch
+    for n_dev in ((1, 2) if torch.cuda.device_count() >= 2 else (1,)):  # 2: one model replica per GPU in one process (ShardedWorkers)
+        r = subprocess.run([str(exe), gguf_f32, "10", *pcms], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=300,
+                           env=dict(os.environ, NB200_TEST_DEVICES=str(n_dev)))
+        print(r.stdout, r.stderr[-2000:])
+        assert r.returncode == 0, r.stderr[-2000:]
+        d = json.loads(r.stdout.strip().splitlines()[-1])
+        assert d["devices"] == n_dev and d["mismatches"] == 0 and d["not_closed"] == 0 and d["errors"] == 0
+        assert d["max_batch"] > 1 and d["stream_chunks"] > d["steps"]
 
 
 def test_smoke_entry(nb):
