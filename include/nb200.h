@@ -71,6 +71,10 @@ int nb200_model_info(const nb200_model* m, nb200_info* out);
 const char* nb200_model_token(const nb200_model* m, int32_t id);
 /* tokens_to_text — src/nemo-ggml.cpp:1556-1583 (U+2581 -> ' '); returns bytes written (excluding NUL) or <0 */
 int nb200_tokens_to_text(const nb200_model* m, const int32_t* tokens, int n, char* out, int cap);
+/* tokens_to_text(timed tokens, vocab, timestamp_words = true) — src/nemo-ggml.cpp:1556-1583: a piece that starts with
+ * U+2581 becomes " {%.2f}" + rest, the time being timed_token::to_seconds (src/nemo-ggml.h:383-395): frame * 1280 /
+ * 16000 in fp32. frames[i] is the encoder frame token i was emitted at (nb200_stream_poll_timed). */
+int nb200_tokens_to_text_timed(const nb200_model* m, const int32_t* tokens, const int64_t* frames, int n, char* out, int cap);
 
 /* nemo_stream_init(ctx, cfg) with cfg.att_right_context in {0,1,6,13} — src/nemo-stream.h:271, .cpp:696-733 */
 nb200_stream* nb200_stream_create(nb200_model* m, int right_context);
@@ -122,6 +126,13 @@ int nb200_drain(nb200_model* m);
 
 /* Tokens emitted since the last poll (sctx->tokens, src/nemo-stream.h:231). Returns count copied. */
 int nb200_stream_poll_tokens(nb200_stream* s, int32_t* out, int cap);
+/* Same, with the encoder frame (80 ms units, counted over the frames the stream has decoded so far) at which each
+ * token was emitted: the timed_token{token_id, frame_idx} pairs of the reference's offline decoder
+ * (greedy_decode, src/nemo-ggml.cpp:1233-1380; struct at src/nemo-ggml.h:383-395), which its streaming path drops
+ * (tokens_to_text_simple fills frame 0, src/nemo-stream.cpp:755-762). frames_out may be NULL. */
+int nb200_stream_poll_timed(nb200_stream* s, int32_t* tokens_out, int64_t* frames_out, int cap);
+/* frame index of every token so far; returns total count, copies min(total, cap) */
+int nb200_stream_get_token_frames(const nb200_stream* s, int64_t* out, int cap);
 /* nemo_stream_get_tokens — all tokens so far; returns total count, copies min(total, cap) */
 int nb200_stream_get_tokens(const nb200_stream* s, int32_t* out, int cap);
 /* per-chunk token counts (for parity tests); returns number of chunks processed */

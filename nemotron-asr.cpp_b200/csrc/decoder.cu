@@ -492,7 +492,7 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                     sy = 0;
                 } else {
                     const int n = d.tok_cnt[b];
-                    d.tok_out[(size_t)b * d.T * MAX_SYMBOLS + n] = besti;
+                    d.tok_out[(size_t)b * d.T * MAX_SYMBOLS + n] = besti | (fp << 16);  // token id | chunk-local frame it was emitted at
                     d.tok_cnt[b] = n + 1;
                     s.prev[slot] = besti;
                     emit = 1;

@@ -107,6 +107,8 @@ struct nb200_stream {
     int wpos = 0;   // K/V ring write index
     int valid = 0;  // cache_valid_len
     std::vector<int32_t> tokens;
+    std::vector<int64_t> token_frames;  // encoder frame each token was emitted at (timed_token::frame_idx, src/nemo-ggml.h:383-395)
+    long long frames_done = 0;          // encoder frames decoded so far
     size_t poll_cursor = 0;
     std::vector<int32_t> chunk_tokens;
     std::vector<float> chunk_margins;  // per chunk: smallest top1-top2 logit gap of its symbol steps
@@ -986,7 +988,12 @@ void run_batch_finish(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
     for (int b = 0; b < B; b++) {
         nb200_stream* s = items[b].s;
         const int n = h_cnt[b];
-        for (int i = 0; i < n; i++) s->tokens.push_back(h_toks[(size_t)b * T * MAX_SYMBOLS + i]);
+        for (int i = 0; i < n; i++) {  // word = token id | chunk-local frame << 16 (decoder.cu, phase A)
+            const int w = h_toks[(size_t)b * T * MAX_SYMBOLS + i];
+            s->tokens.push_back(w & 0xffff);
+            s->token_frames.push_back(s->frames_done + (w >> 16));
+        }
+        s->frames_done += items[b].nvalid;
         s->chunk_tokens.push_back(n);
         float mg;
         memcpy(&mg, &h_margin[b], sizeof(float));
@@ -1110,6 +1117,29 @@ int nb200_tokens_to_text(const nb200_model* m, const int32_t* tokens, int n, cha
     return w;
 }
 
+int nb200_tokens_to_text_timed(const nb200_model* m, const int32_t* tokens, const int64_t* frames, int n, char* out, int cap) {
+    if (!m || ((!tokens || !frames) && n > 0) || !out || cap <= 0) return NB200_ERR;
+    std::string res;
+    for (int i = 0; i < n; i++) {
+        if (tokens[i] < 0 || tokens[i] >= (int)m->vocab.size()) continue;
+        const std::string& piece = m->vocab[tokens[i]];
+        if (piece.compare(0, 3, "\xe2\x96\x81") == 0) {  // word start: " {seconds}" + the rest of the piece
+            const float sec = (float)frames[i] * 1280 / 16000;  // timed_token::to_seconds, src/nemo-ggml.h:393-395
+            char buf[32];
+            snprintf(buf, sizeof(buf), "{%.2f}", sec);
+            res += ' ';
+            res += buf;
+            res.append(piece, 3, std::string::npos);
+        } else {
+            res += piece;
+        }
+    }
+    const int w = std::min((int)res.size(), cap - 1);
+    memcpy(out, res.data(), w);
+    out[w] = 0;
+    return w;
+}
+
 nb200_stream* nb200_stream_create(nb200_model* m, int right_context) {
     NB_TRY
     if (!m) throw Error("null model");
@@ -1157,6 +1187,8 @@ int nb200_stream_reset(nb200_stream* s) {
     s->finalize_requested = s->finalized = false;
     s->wpos = s->valid = 0;
     s->tokens.clear();
+    s->token_frames.clear();
+    s->frames_done = 0;
     s->poll_cursor = 0;
     s->chunk_tokens.clear();
     s->chunk_margins.clear();
@@ -1332,6 +1364,24 @@ int nb200_stream_poll_tokens(nb200_stream* s, int32_t* out, int cap) {
     for (int i = 0; i < n; i++) out[i] = s->tokens[s->poll_cursor + i];
     s->poll_cursor += n;
     return n;
+}
+
+int nb200_stream_poll_timed(nb200_stream* s, int32_t* tokens_out, int64_t* frames_out, int cap) {
+    if (!s || (!tokens_out && cap > 0)) return NB200_ERR;
+    const int n = std::min<int>(cap, (int)(s->tokens.size() - s->poll_cursor));
+    for (int i = 0; i < n; i++) {
+        tokens_out[i] = s->tokens[s->poll_cursor + i];
+        if (frames_out) frames_out[i] = s->token_frames[s->poll_cursor + i];
+    }
+    s->poll_cursor += n;
+    return n;
+}
+
+int nb200_stream_get_token_frames(const nb200_stream* s, int64_t* out, int cap) {
+    if (!s || (!out && cap > 0)) return NB200_ERR;
+    const int n = std::min<int>(cap, (int)s->token_frames.size());
+    for (int i = 0; i < n; i++) out[i] = s->token_frames[i];
+    return (int)s->token_frames.size();
 }
 
 int nb200_stream_get_tokens(const nb200_stream* s, int32_t* out, int cap) {

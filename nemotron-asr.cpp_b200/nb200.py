@@ -38,6 +38,7 @@ class Stats(C.Structure):
 
 # every symbol include/nb200.h declares: (restype, argtypes)
 _I16P, _I32P, _F32P = C.POINTER(C.c_int16), C.POINTER(C.c_int32), C.POINTER(C.c_float)
+_I64P = C.POINTER(C.c_int64)
 SYMBOLS = {
     "nb200_last_error": (C.c_char_p, []),
     "nb200_version": (C.c_int, []),
@@ -46,6 +47,7 @@ SYMBOLS = {
     "nb200_model_info": (C.c_int, [C.c_void_p, C.POINTER(Info)]),
     "nb200_model_token": (C.c_char_p, [C.c_void_p, C.c_int32]),
     "nb200_tokens_to_text": (C.c_int, [C.c_void_p, _I32P, C.c_int, C.c_char_p, C.c_int]),
+    "nb200_tokens_to_text_timed": (C.c_int, [C.c_void_p, _I32P, _I64P, C.c_int, C.c_char_p, C.c_int]),
     "nb200_stream_create": (C.c_void_p, [C.c_void_p, C.c_int]),
     "nb200_stream_free": (None, [C.c_void_p]),
     "nb200_stream_reset": (C.c_int, [C.c_void_p]),
@@ -62,6 +64,8 @@ SYMBOLS = {
     "nb200_drain": (C.c_int, [C.c_void_p]),
     "nb200_stream_poll_tokens": (C.c_int, [C.c_void_p, _I32P, C.c_int]),
     "nb200_stream_get_tokens": (C.c_int, [C.c_void_p, _I32P, C.c_int]),
+    "nb200_stream_poll_timed": (C.c_int, [C.c_void_p, _I32P, _I64P, C.c_int]),
+    "nb200_stream_get_token_frames": (C.c_int, [C.c_void_p, _I64P, C.c_int]),
     "nb200_stream_chunk_token_counts": (C.c_int, [C.c_void_p, _I32P, C.c_int]),
     "nb200_stream_chunk_margins": (C.c_int, [C.c_void_p, _F32P, C.c_int]),
     "nb200_stream_set_taps": (C.c_int, [C.c_void_p, C.c_int]),
@@ -200,6 +204,18 @@ class Model:
             raise NB200Error(_err())
         return buf.raw[:n].decode("utf-8", errors="replace")
 
+    def tokens_to_text_timed(self, tokens, frames) -> str:
+        """tokens_to_text(timed tokens, vocab, timestamp_words=true), src/nemo-ggml.cpp:1556-1583"""
+        t = np.ascontiguousarray(tokens, dtype=np.int32)
+        f = np.ascontiguousarray(frames, dtype=np.int64)
+        if t.size != f.size:
+            raise ValueError("tokens and frames differ in length")
+        buf = C.create_string_buffer(48 * max(1, t.size) + 16)
+        n = lib().nb200_tokens_to_text_timed(self._h, _ptr(t, _I32P), _ptr(f, _I64P), int(t.size), buf, len(buf))
+        if n < 0:
+            raise NB200Error(_err())
+        return buf.raw[:n].decode("utf-8", errors="replace")
+
     def mel_batch(self, pcm: np.ndarray) -> np.ndarray:
         """nemo_preprocessor_process for [n_streams, n_samples] int16 signals, each from a fresh preprocessor."""
         pcm = np.ascontiguousarray(pcm, dtype=np.int16)
@@ -321,6 +337,25 @@ class Stream:
             if n <= 0:
                 return out
             out.extend(buf[:n].tolist())
+
+    def poll_timed(self) -> tuple[list[int], list[int]]:
+        """new (tokens, encoder frames they were emitted at): the reference's timed_token pairs (src/nemo-ggml.h:383-395)"""
+        buf, fr = np.zeros(4096, np.int32), np.zeros(4096, np.int64)
+        toks: list[int] = []
+        frames: list[int] = []
+        while True:
+            n = lib().nb200_stream_poll_timed(self._h, _ptr(buf, _I32P), _ptr(fr, _I64P), buf.size)
+            if n <= 0:
+                return toks, frames
+            toks.extend(buf[:n].tolist())
+            frames.extend(fr[:n].tolist())
+
+    @property
+    def token_frames(self) -> list[int]:
+        n = lib().nb200_stream_get_token_frames(self._h, None, 0)
+        buf = np.zeros(max(n, 1), np.int64)
+        lib().nb200_stream_get_token_frames(self._h, _ptr(buf, _I64P), n)
+        return buf[:n].tolist()
 
     @property
     def tokens(self) -> list[int]:

@@ -327,6 +327,8 @@ class StreamOracle:
         self.c = np.zeros((2, 640), F32)
         self.prev = self.blank
         self.tokens: list[int] = []
+        self.token_frames: list[int] = []  # encoder frame (80 ms) each token was emitted at, counted over the decoded frames of the stream
+        self.frames_done = 0
         self.enc_chunks: list[np.ndarray] = []  # all T frames of every chunk (before valid_out truncation)
         self.chunk_tokens: list[int] = []
         self.decode_iters = 0
@@ -455,8 +457,12 @@ class StreamOracle:
         enc = self.encode_chunk(mel)
         self.enc_chunks.append(enc)
         n0 = len(self.tokens)
-        for f in range(min(enc.shape[0], valid_out)):
-            self.tokens.extend(self.decode_frame(enc[f]))
+        nf = min(enc.shape[0], valid_out)
+        for f in range(nf):
+            new = self.decode_frame(enc[f])
+            self.tokens.extend(new)
+            self.token_frames.extend([self.frames_done + f] * len(new))
+        self.frames_done += nf
         self.chunk_tokens.append(len(self.tokens) - n0)
 
     def feed(self, pcm: np.ndarray):
@@ -481,3 +487,20 @@ class StreamOracle:
 def tokens_to_text(tokens, vocab):
     """src/nemo-ggml.cpp:1556-1583 (no timestamps): concatenate pieces, U+2581 -> space."""
     return "".join(vocab[t] for t in tokens if 0 <= t < len(vocab)).replace("▁", " ")
+
+
+def tokens_to_text_timed(tokens, frames, vocab):
+    """src/nemo-ggml.cpp:1556-1583 with timestamp_words: a piece that STARTS with U+2581 becomes ' {%.2f}' + rest, the
+    time being timed_token::to_seconds (src/nemo-ggml.h:393-395): float(frame) * 1280 / 16000 in fp32. Only the leading
+    U+2581 is replaced (the untimed helper above replaces all of them, which is the same for SentencePiece vocabularies)."""
+    out = []
+    for t, f in zip(tokens, frames):
+        if not 0 <= t < len(vocab):
+            continue
+        piece = vocab[t]
+        if piece.startswith("▁"):
+            sec = F32(F32(F32(f) * F32(1280)) / F32(16000))
+            out.append(" {%.2f}" % float(sec) + piece[1:])
+        else:
+            out.append(piece)
+    return "".join(out)

@@ -18,6 +18,8 @@
 //   ref_harness matmul <gguf> <tensor_name> <x.f32> <M> <out.f32> [threads]
 //       y[M,N] = ggml_mul_mat(W, x) on the reference's CPU backend for one weight tensor of the file (Q8_0 or F32),
 //       i.e. exactly the kernel the encoder graph runs for that tensor (src/nemo-stream.cpp:593-603).
+//   ref_harness text <gguf> <tokens.i32> <frames.i64> <timestamp_words 0|1> <out.txt>
+//       tokens_to_text (src/nemo-ggml.cpp:1556-1583) over timed_token{token, frame} pairs with the file's vocabulary.
 #include "nemo-ggml.h"
 #include "nemo-stream.h"
 #include "preprocessor.h"
@@ -200,11 +202,42 @@ static int run_matmul(int argc, char** argv) {
     return 0;
 }
 
+// declared in the reference's translation units only (src/nemo-stream.cpp:752), defined at src/nemo-ggml.cpp:1556
+std::string tokens_to_text(const std::vector<timed_token>& tokens, const std::vector<std::string>& vocab, bool timestamp_words);
+
+static int run_text(int argc, char** argv) {
+    if (argc < 7) { fprintf(stderr, "usage: text <gguf> <tokens.i32> <frames.i64> <timestamp_words> <out.txt>\n"); return 2; }
+    nemo_context* ctx = nemo_init_with_backend(argv[2], NEMO_BACKEND_CPU);
+    if (!ctx) return 1;
+    std::vector<int32_t> tok;
+    std::vector<int64_t> frames;
+    {
+        FILE* f = fopen(argv[3], "rb");
+        if (!f) return 2;
+        int32_t v;
+        while (fread(&v, 4, 1, f) == 1) tok.push_back(v);
+        fclose(f);
+        f = fopen(argv[4], "rb");
+        if (!f) return 2;
+        int64_t w;
+        while (fread(&w, 8, 1, f) == 1) frames.push_back(w);
+        fclose(f);
+    }
+    if (tok.size() != frames.size()) { fprintf(stderr, "tokens / frames length mismatch\n"); return 2; }
+    std::vector<timed_token> tt;
+    for (size_t i = 0; i < tok.size(); i++) tt.push_back(timed_token(tok[i], frames[i]));
+    const std::string text = tokens_to_text(tt, ctx->model.vocab, atoi(argv[5]) != 0);
+    write_file(argv[6], text.data(), text.size());
+    nemo_free(ctx);
+    return 0;
+}
+
 int main(int argc, char** argv) {
-    if (argc < 2) { fprintf(stderr, "usage: ref_harness stream|mel|matmul ...\n"); return 2; }
+    if (argc < 2) { fprintf(stderr, "usage: ref_harness stream|mel|matmul|text ...\n"); return 2; }
     if (!strcmp(argv[1], "mel")) return run_mel(argc, argv);
     if (!strcmp(argv[1], "stream")) return run_stream(argc, argv);
     if (!strcmp(argv[1], "matmul")) return run_matmul(argc, argv);
+    if (!strcmp(argv[1], "text")) return run_text(argc, argv);
     fprintf(stderr, "unknown mode %s\n", argv[1]);
     return 2;
 }

@@ -249,6 +249,51 @@ def test_prompt_fusion_matches_reference(nb, lib_built, model_f32):
     mono.free()
 
 
+def test_timed_tokens(nb, model_f32, oracle_f32):
+    """Frame stamps of the emitted tokens (timed_token::frame_idx, src/nemo-ggml.h:383-395) against the numpy oracle on
+    the same stream, for as long as the token sequences agree; timed text against the compiled reference's
+    tokens_to_text(..., timestamp_words = true) (tests/golden/text_timed.json)."""
+    import json
+    kv, t = oracle_f32
+    for rc, seed, secs in ((13, 21, 5.0), (1, 22, 3.0), (0, 23, 2.5)):
+        pcm = inputs.pcm(seed, secs)
+        o = no.StreamOracle(kv, t, rc)
+        o.feed(pcm)
+        o.finalize()
+        s = model_f32.stream(rc)
+        cs = 8 * (1 + rc) * 160
+        polled_t, polled_f = [], []
+        for i in range(0, len(pcm), cs):
+            s.feed(pcm[i:i + cs])
+            model_f32.drain()
+            a, b = s.poll_timed()
+            polled_t += a
+            polled_f += b
+        assert nb.lib().nb200_stream_finalize(s._h) == 0  # the raw call: Stream.finalize() would poll the tail's tokens itself
+        model_f32.drain()
+        a, b = s.poll_timed()
+        polled_t += a
+        polled_f += b
+        assert polled_t == s.tokens and polled_f == s.token_frames
+        got = {"tokens": s.tokens, "chunk_tokens": s.chunk_token_counts, "margins": s.chunk_margins}
+        same, comparable, margin = compare_tokens(got, o.tokens, o.chunk_tokens)
+        if margin is not None:
+            assert margin < TIE_GAP
+        n_same = int(np.sum(o.chunk_tokens[:same]))
+        assert n_same > 0 or len(o.tokens) == 0
+        assert s.token_frames[:n_same] == o.token_frames[:n_same], (rc, s.token_frames[:n_same], o.token_frames[:n_same])
+        assert np.all(np.diff(s.token_frames) >= 0)
+        text = model_f32.tokens_to_text_timed(s.tokens[:n_same], s.token_frames[:n_same])
+        assert text == no.tokens_to_text_timed(o.tokens[:n_same], o.token_frames[:n_same], kv["tokenizer.vocab_list"])
+        print(f"timed tokens rc={rc}: {len(s.tokens)} tokens, {n_same} compared, last frame {s.token_frames[-1] if s.tokens else None}")
+        s.reset()
+        assert s.token_frames == [] and s.tokens == []
+        s.free()
+    gold = json.loads((GOLD / "text_timed.json").read_text())
+    assert model_f32.tokens_to_text(gold["tokens"]) == gold["text_plain"]
+    assert model_f32.tokens_to_text_timed(gold["tokens"], gold["frames"]) == gold["text_timed"]
+
+
 def test_batched_equals_single(nb, model_f32):
     """Cross-stream batching must not change any stream's result: 5 streams in mixed latency modes, stepped together,
     equal the same streams run alone (same kernels, same per-row arithmetic)."""

@@ -76,6 +76,15 @@ def test_stream_f32_matches_reference(variant, rc, seed, secs, oracle_f32):
     ct = gold["chunk_tokens"][:n]
     assert s.chunk_tokens == ct.tolist()
     assert s.tokens == gold["tokens"][: int(ct.sum())].tolist()
+    # frame stamps (timed_token::frame_idx): the reference's streaming path only reveals tokens per chunk, so they are
+    # pinned at that granularity: the tokens stamped inside chunk c's frame range are exactly the chunk's tokens
+    fr = np.asarray(s.token_frames)
+    assert len(fr) == len(s.tokens) and np.all(np.diff(fr) >= 0)
+    if len(fr):
+        assert np.bincount(fr).max() <= no.StreamOracle.MAX_SYMBOLS
+    n_full = n - 1 if full else n
+    for c in range(n_full):
+        assert int(((fr >= c * s.valid_out) & (fr < (c + 1) * s.valid_out)).sum()) == int(ct[c])
 
 
 @pytest.mark.parametrize("rc", [0, 13])
@@ -125,3 +134,13 @@ def test_prompt_fusion_matches_reference(lang, rc, seed, secs):
 def test_tokens_to_text():
     vocab = ["▁he", "llo", "▁wor", "ld"]
     assert no.tokens_to_text([0, 1, 2, 3, 99], vocab) == " hello world"
+    assert no.tokens_to_text_timed([0, 1, 2, 3, 99], [0, 0, 7, 8, 9], vocab) == " {0.00}hello {0.56}world"
+
+
+def test_timed_text_matches_reference(oracle_f32):
+    """tokens_to_text with and without timestamp_words against the compiled reference (tests/golden/make_golden_text.py)"""
+    kv, _ = oracle_f32
+    gold = json.loads((GOLD / "text_timed.json").read_text())
+    vocab = kv["tokenizer.vocab_list"]
+    assert no.tokens_to_text(gold["tokens"], vocab) == gold["text_plain"]
+    assert no.tokens_to_text_timed(gold["tokens"], gold["frames"], vocab) == gold["text_timed"]
