@@ -358,7 +358,8 @@ class StreamOracle:
         v = mm(y, t[p + "self_attn.linear_v.weight"])
         K = np.concatenate([self.kc[l], k], axis=0)  # [70+T,1024]
         V = np.concatenate([self.vc[l], v], axis=0)
-        self.kc[l], self.vc[l] = K[-self.left:], V[-self.left:]  # :504-512
+        if self.left > 0:
+            self.kc[l], self.vc[l] = K[-self.left:], V[-self.left:]  # :504-512
         P = self._pos_proj(l, T)  # index p + T - 1
         kv_len = self.left + T
         qh = q.reshape(T, self.H, self.DH)
@@ -482,6 +483,49 @@ class StreamOracle:
                 if total < self.chunk_mel:
                     self.mel_buf = np.concatenate([self.mel_buf, np.zeros((self.chunk_mel - total, 128), F32)])
                 self._step(self.mel_buf[:self.chunk_mel], n_valid)
+
+
+class OfflineOracle(StreamOracle):
+    """The reference's offline path (nemo_encode, src/nemo-ggml.cpp:1592-1670): whole-utterance log-mel ->
+    build_conv_subsampling with its causal zero padding, nothing dropped (:954-1029) -> 24 layers with FULL-sequence
+    relative-position attention (build_rel_pos_mha :668-757: no cache, no mask, positions T-1 .. -(T-1); the rel-shift
+    :625-662 picks position i - j for query i, key j) and the causal depthwise conv over zero left padding (:796-823) ->
+    greedy_decode (:1233-1380) from a zero LSTM state, tokens stamped with their frame. That is the streaming layer
+    with an empty left context, so it is restated as StreamOracle with left = 0 and zero conv cache."""
+
+    def __init__(self, kv: dict, tensors: dict):
+        super().__init__(kv, tensors, 0)
+        self.left = 0
+        self.kc = np.zeros((self.L, 0, self.D), F32)
+        self.vc = np.zeros((self.L, 0, self.D), F32)
+
+    def encode(self, mel: np.ndarray) -> np.ndarray:
+        x = conv_subsampling(mel, self.t)
+        for l in range(self.L):
+            self.cc[l] = 0
+            x = self._layer(l, x)
+        if self.num_prompts > 0:
+            idx = self.prompt_index if 0 <= self.prompt_index < self.num_prompts else 0
+            onehot = np.zeros((x.shape[0], self.num_prompts), F32)
+            onehot[:, idx] = 1.0
+            cat = np.concatenate([x, onehot], axis=1)
+            h = np.maximum(mm(cat, self.t["prompt_kernel.0.weight"]) + self.t["prompt_kernel.0.bias"], 0.0).astype(F32)
+            x = (mm(h, self.t["prompt_kernel.2.weight"]) + self.t["prompt_kernel.2.bias"]).astype(F32)
+        return x
+
+    def transcribe(self, pcm: np.ndarray):
+        """-> (encoder_out [T,1024], tokens, frames)"""
+        mel = Preprocessor(self.t["preprocessor.featurizer.fb"], self.t["preprocessor.featurizer.window"]).process(pcm)
+        enc = self.encode(mel)
+        self.h[:] = 0
+        self.c[:] = 0
+        self.prev = self.blank
+        tokens, frames = [], []
+        for f in range(enc.shape[0]):
+            new = self.decode_frame(enc[f])
+            tokens += new
+            frames += [f] * len(new)
+        return enc, tokens, frames
 
 
 def tokens_to_text(tokens, vocab):

@@ -18,6 +18,11 @@
 //   ref_harness matmul <gguf> <tensor_name> <x.f32> <M> <out.f32> [threads]
 //       y[M,N] = ggml_mul_mat(W, x) on the reference's CPU backend for one weight tensor of the file (Q8_0 or F32),
 //       i.e. exactly the kernel the encoder graph runs for that tensor (src/nemo-stream.cpp:593-603).
+//   ref_harness offline <gguf> <pcm.s16le> <threads> <out_prefix> [max_seconds]
+//       the reference's offline path: nemo_encode_audio (src/nemo-ggml.cpp:1690-1715 = nemo_preprocessor_process over the
+//       whole utterance + build_encoder with full-sequence attention + greedy_decode) -> <prefix>.tokens.i32,
+//       <prefix>.frames.i64 (timed_token::frame_idx); and, through the public build_encoder (src/nemo-ggml.h:342) on the
+//       same mel, <prefix>.enc.f32 [T, d_model] and <prefix>.mel.f32.
 //   ref_harness text <gguf> <tokens.i32> <frames.i64> <timestamp_words 0|1> <out.txt>
 //       tokens_to_text (src/nemo-ggml.cpp:1556-1583) over timed_token{token, frame} pairs with the file's vocabulary.
 #include "nemo-ggml.h"
@@ -202,6 +207,59 @@ static int run_matmul(int argc, char** argv) {
     return 0;
 }
 
+static int run_offline(int argc, char** argv) {
+    if (argc < 6) { fprintf(stderr, "usage: offline <gguf> <pcm> <threads> <prefix> [max_seconds]\n"); return 2; }
+    std::vector<int16_t> pcm = read_pcm(argv[3]);
+    const int threads = atoi(argv[4]);
+    const std::string prefix = argv[5];
+    const double max_seconds = argc > 6 ? atof(argv[6]) : 0.0;
+    if (max_seconds > 0 && pcm.size() > (size_t)(max_seconds * 16000)) pcm.resize((size_t)(max_seconds * 16000));
+    nemo_context* ctx = nemo_init_with_backend(argv[2], NEMO_BACKEND_CPU);
+    if (!ctx) return 1;
+    if (threads > 0) ggml_backend_cpu_set_n_threads(ctx->model.backend, threads);
+
+    // nemo_encode_audio's body (src/nemo-ggml.cpp:1690-1715): preprocessor over the whole utterance, then nemo_encode. (The
+    // header declares it with a std::vector& parameter that has no definition, src/nemo-ggml.h:370-373, so the two calls
+    // are made here.)
+    double t0 = now_s();
+    std::vector<float> mel;
+    const size_t n_frames = nemo_preprocessor_process(ctx->preprocessor, pcm.data(), pcm.size(), mel);
+    std::vector<timed_token> tt = nemo_encode(ctx, mel.data(), (int)n_frames);
+    const double t_proc = now_s() - t0;
+    std::vector<int32_t> tok;
+    std::vector<int64_t> frames;
+    for (const timed_token& t : tt) { tok.push_back(t.token_id); frames.push_back(t.frame_idx); }
+    write_file(prefix + ".tokens.i32", tok.data(), tok.size() * sizeof(int32_t));
+    write_file(prefix + ".frames.i64", frames.data(), frames.size() * sizeof(int64_t));
+
+    // encoder output of the same utterance: the graph nemo_encode builds (src/nemo-ggml.cpp:1592-1658), minus the decode
+    write_file(prefix + ".mel.f32", mel.data(), mel.size() * sizeof(float));
+    const int n_mels = ctx->model.hparams.n_mels;
+    size_t buf_size = ggml_tensor_overhead() * 8000 + ggml_graph_overhead_custom(16384, false);
+    std::vector<uint8_t> buf(buf_size);
+    ggml_init_params ip = {buf_size, buf.data(), true};
+    ggml_context* c0 = ggml_init(ip);
+    ggml_tensor* inp = ggml_new_tensor_3d(c0, GGML_TYPE_F32, n_mels, (int64_t)n_frames, 1);
+    ggml_set_input(inp);
+    ggml_tensor* enc = build_encoder(c0, inp, &ctx->model);
+    ggml_set_output(enc);
+    ggml_cgraph* gf = ggml_new_graph_custom(c0, 16384, false);
+    ggml_build_forward_expand(gf, enc);
+    ggml_gallocr_t ga = ggml_gallocr_new(ggml_backend_get_default_buffer_type(ctx->model.backend));
+    if (!ggml_gallocr_alloc_graph(ga, gf)) return 1;
+    ggml_backend_tensor_set(inp, mel.data(), 0, mel.size() * sizeof(float));
+    ggml_backend_graph_compute(ctx->model.backend, gf);
+    std::vector<float> out(ggml_nelements(enc));
+    ggml_backend_tensor_get(enc, out.data(), 0, out.size() * sizeof(float));
+    write_file(prefix + ".enc.f32", out.data(), out.size() * sizeof(float));
+    printf("{\"mode\":\"offline\",\"threads\":%d,\"audio_s\":%.4f,\"proc_s\":%.4f,\"mel_frames\":%zu,\"enc_T\":%lld,\"tokens\":%zu}\n",
+           threads, (double)pcm.size() / 16000.0, t_proc, n_frames, (long long)enc->ne[1], tok.size());
+    ggml_gallocr_free(ga);
+    ggml_free(c0);
+    nemo_free(ctx);
+    return 0;
+}
+
 // declared in the reference's translation units only (src/nemo-stream.cpp:752), defined at src/nemo-ggml.cpp:1556
 std::string tokens_to_text(const std::vector<timed_token>& tokens, const std::vector<std::string>& vocab, bool timestamp_words);
 
@@ -233,11 +291,12 @@ static int run_text(int argc, char** argv) {
 }
 
 int main(int argc, char** argv) {
-    if (argc < 2) { fprintf(stderr, "usage: ref_harness stream|mel|matmul|text ...\n"); return 2; }
+    if (argc < 2) { fprintf(stderr, "usage: ref_harness stream|mel|matmul|text|offline ...\n"); return 2; }
     if (!strcmp(argv[1], "mel")) return run_mel(argc, argv);
     if (!strcmp(argv[1], "stream")) return run_stream(argc, argv);
     if (!strcmp(argv[1], "matmul")) return run_matmul(argc, argv);
     if (!strcmp(argv[1], "text")) return run_text(argc, argv);
+    if (!strcmp(argv[1], "offline")) return run_offline(argc, argv);
     fprintf(stderr, "unknown mode %s\n", argv[1]);
     return 2;
 }

@@ -56,6 +56,14 @@ PROMPT_CASES = (
 )
 
 
+# offline path (nemo_encode, full-sequence attention, timed tokens): (variant, seed, seconds)
+OFFLINE_CASES = (
+    ("f32dq", 41, 6.0),
+    ("f32dq", 42, 0.9),
+    ("q8_0", 41, 4.0),
+)
+
+
 def gguf_path(variant: str, layers: int = TEST_LAYERS, blank_gain: float | None = None, multilingual: bool = False) -> str:
     import make_random_gguf as mg
     TMP.mkdir(parents=True, exist_ok=True)

@@ -144,3 +144,27 @@ def test_timed_text_matches_reference(oracle_f32):
     vocab = kv["tokenizer.vocab_list"]
     assert no.tokens_to_text(gold["tokens"], vocab) == gold["text_plain"]
     assert no.tokens_to_text_timed(gold["tokens"], gold["frames"], vocab) == gold["text_timed"]
+
+
+@pytest.mark.parametrize("variant,seed,secs", inputs.OFFLINE_CASES)
+def test_offline_matches_reference(variant, seed, secs, oracle_q8, oracle_f32):
+    """Offline path (nemo_encode: full-sequence attention, greedy_decode with timed tokens) against the compiled
+    reference (tests/golden/make_golden_offline.py). F32 file: encoder_out <= 2e-4 relative (measured 1e-5), tokens and
+    frame stamps identical. Q8_0 file: inside the reference's own ISA-to-ISA envelope, tokens compared up to the first
+    difference between the two reference builds."""
+    kv, t = oracle_f32 if variant == "f32dq" else oracle_q8
+    gold = np.load(GOLD / f"offline_{variant}_s{seed}.npz")
+    enc, tokens, frames = no.OfflineOracle(kv, t).transcribe(inputs.pcm(seed, secs))
+    assert enc.shape == gold["enc"].shape
+    r = rel(enc, gold["enc"])
+    if variant == "f32dq":
+        assert r < 2e-4, r
+        assert tokens == gold["tokens"].tolist() and frames == gold["frames"].tolist()
+    else:
+        self_noise = rel(gold["enc_avx512"], gold["enc"])
+        assert r < 1e-2 and r < 1.5 * self_noise + 1e-3, (r, self_noise)
+        a, b = gold["tokens"].tolist(), gold["tokens_avx512"].tolist()
+        n_same = next((i for i, (x, y) in enumerate(zip(a, b)) if x != y), min(len(a), len(b)))
+        agree = next((i for i, (x, y) in enumerate(zip(tokens, a)) if x != y), min(len(tokens), len(a)))
+        print(f"offline q8_0: rel {r:.2e}, reference self-noise {self_noise:.2e}, builds agree on {n_same} tokens, oracle on {agree}")
+        assert frames[:agree] == gold["frames"][:agree].tolist()
