@@ -121,6 +121,14 @@ int nb200_feed_batch(nb200_model* m, nb200_stream* const* streams, const int16_t
  * counts into counts_out[count]. Returns the total number of tokens written; when cap is too small nothing is
  * consumed, counts_out holds the waiting counts and the call returns <0. */
 int nb200_poll_batch(nb200_model* m, nb200_stream* const* streams, int count, int32_t* tokens_out, int cap, int32_t* counts_out);
+/* Offline path — nemo_encode_audio(ctx, pcm, n) -> std::vector<timed_token> (src/nemo-ggml.cpp:1690-1715, nemo_encode
+ * :1592-1670): whole-utterance log-mel, subsampling, 24 layers with FULL-sequence relative-position attention, greedy decode
+ * from a fresh decoder state. Writes min(n, cap) (token, encoder frame) pairs and returns the number of tokens n, or <0.
+ * enc_out (may be NULL) receives the encoder output [T][1024] fp32 (parity tests), *n_frames_out = T. Utterances up to
+ * min(512, 14 * max_streams) encoder frames (the reference's positional table ends at 512, :1061); needs one free stream
+ * slot; synchronous; must not be called between nb200_step_begin and nb200_step_end of other streams' steps. */
+int nb200_encode_audio(nb200_model* m, const int16_t* pcm, int n_samples, int32_t* tokens_out, int64_t* frames_out, int cap,
+                       float* enc_out, int64_t enc_cap_floats, int* n_frames_out);
 /* Convenience: nb200_step until no stream has a ready chunk. Returns total stream-chunks processed. */
 int nb200_drain(nb200_model* m);
 

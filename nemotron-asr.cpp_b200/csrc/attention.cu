@@ -838,6 +838,134 @@ __global__ void __launch_bounds__(256) attention_simt_kernel(AttnArgs a) {
     }
 }
 
+// ---- offline path: full-sequence relative-position attention over one utterance -------------------------------------
+// build_rel_pos_mha (src/nemo-ggml.cpp:668-757): scores[i][j] = ((q_i + u) . k_j + (q_i + v) . pos[i - j]) / sqrt(128), softmax over
+// all T keys (no cache, no mask), context = P V. One CTA = 8 query rows of one head (a warp each); keys go through shared
+// memory in tiles of 32 (lane = key) together with the 39 position rows the 8 x 32 (query, key) pairs of the tile need; the
+// score rows (<= 512 keys, fp32) stay in shared memory for the softmax and the P V pass (lane = 4 output features).
+// K, V and the projected positions are fp16 like in the streaming kernels; q + u, q + v, scores and probabilities are fp32.
+constexpr int AF_QB = 8, AF_KT = 32, AF_PITCH = D_HEAD + 8;  // 272-byte rows: 16-byte row pieces of consecutive rows fall in different bank groups
+
+__global__ void __launch_bounds__(256) attention_full_kernel(AttnFullArgs a) {
+    pdl_prologue();
+    __shared__ float S[AF_QB][ATTN_FULL_MAX_T];
+    __shared__ __align__(16) __half Kt[AF_KT][AF_PITCH];
+    __shared__ __align__(16) __half Pt[AF_KT + AF_QB - 1][AF_PITCH];
+    __shared__ __align__(16) float qu[AF_QB][D_HEAD];
+    __shared__ __align__(16) float qv[AF_QB][D_HEAD];
+    const int T = a.T, h = blockIdx.y, i0 = blockIdx.x * AF_QB;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int i = i0 + warp;
+    const __half* qkv = a.qkv + h * D_HEAD;
+    const __half* pbase = a.pos + h * D_HEAD;
+    {   // q + u, q + v of the CTA's 8 query rows (rows >= T: zero)
+        float4 u4 = make_float4(0.f, 0.f, 0.f, 0.f), v4 = u4;
+        if (i < T) {
+            const uint2 raw = *reinterpret_cast<const uint2*>(qkv + (size_t)i * (3 * D_MODEL) + 4 * lane);
+            const float2 q01 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x)), q23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+            const float4 bu = *reinterpret_cast<const float4*>(a.bias_u + h * D_HEAD + 4 * lane);
+            const float4 bv = *reinterpret_cast<const float4*>(a.bias_v + h * D_HEAD + 4 * lane);
+            u4 = make_float4(q01.x + bu.x, q01.y + bu.y, q23.x + bu.z, q23.y + bu.w);
+            v4 = make_float4(q01.x + bv.x, q01.y + bv.y, q23.x + bv.z, q23.y + bv.w);
+        }
+        *reinterpret_cast<float4*>(&qu[warp][4 * lane]) = u4;
+        *reinterpret_cast<float4*>(&qv[warp][4 * lane]) = v4;
+    }
+    const float scale = 1.0f / sqrtf((float)D_HEAD);
+    const uint4 z4 = make_uint4(0, 0, 0, 0);
+    for (int j0 = 0; j0 < T; j0 += AF_KT) {
+        __syncthreads();  // the previous tile has been consumed (first pass: q + u, q + v are visible after the barrier below)
+        for (int idx = tid; idx < AF_KT * 16; idx += 256) {
+            const int r = idx >> 4, c = idx & 15, j = j0 + r;
+            *reinterpret_cast<uint4*>(&Kt[r][c * 8]) = j < T ? *reinterpret_cast<const uint4*>(qkv + (size_t)j * (3 * D_MODEL) + D_MODEL + c * 8) : z4;
+        }
+        // pair (query i0 + w, key j0 + l) uses position p = (i0 + w) - (j0 + l): table row p + T - 1 = rlo + (w - l + 31)
+        const int rlo = i0 - j0 - (AF_KT - 1) + T - 1;
+        for (int idx = tid; idx < (AF_KT + AF_QB - 1) * 16; idx += 256) {
+            const int r = idx >> 4, c = idx & 15, row = rlo + r;
+            *reinterpret_cast<uint4*>(&Pt[r][c * 8]) = (row >= 0 && row < 2 * T - 1) ? *reinterpret_cast<const uint4*>(pbase + (size_t)row * D_MODEL + c * 8) : z4;
+        }
+        __syncthreads();
+        const int j = j0 + lane;
+        if (i < T && j < T) {
+            const __half* kr = &Kt[lane][0];
+            const __half* pr = &Pt[warp - lane + AF_KT - 1][0];
+            float sc = 0.0f, sp = 0.0f;
+#pragma unroll 4
+            for (int d = 0; d < D_HEAD; d += 8) {
+                const uint4 k8 = *reinterpret_cast<const uint4*>(kr + d), p8 = *reinterpret_cast<const uint4*>(pr + d);
+                const float4 u0 = *reinterpret_cast<const float4*>(&qu[warp][d]), u1 = *reinterpret_cast<const float4*>(&qu[warp][d + 4]);
+                const float4 v0 = *reinterpret_cast<const float4*>(&qv[warp][d]), v1 = *reinterpret_cast<const float4*>(&qv[warp][d + 4]);
+                const __half2* kh = reinterpret_cast<const __half2*>(&k8);
+                const __half2* ph = reinterpret_cast<const __half2*>(&p8);
+                const float2 k0 = __half22float2(kh[0]), k1 = __half22float2(kh[1]), k2 = __half22float2(kh[2]), k3 = __half22float2(kh[3]);
+                const float2 p0 = __half22float2(ph[0]), p1 = __half22float2(ph[1]), p2 = __half22float2(ph[2]), p3 = __half22float2(ph[3]);
+                sc = fmaf(u0.x, k0.x, sc); sc = fmaf(u0.y, k0.y, sc); sc = fmaf(u0.z, k1.x, sc); sc = fmaf(u0.w, k1.y, sc);
+                sc = fmaf(u1.x, k2.x, sc); sc = fmaf(u1.y, k2.y, sc); sc = fmaf(u1.z, k3.x, sc); sc = fmaf(u1.w, k3.y, sc);
+                sp = fmaf(v0.x, p0.x, sp); sp = fmaf(v0.y, p0.y, sp); sp = fmaf(v0.z, p1.x, sp); sp = fmaf(v0.w, p1.y, sp);
+                sp = fmaf(v1.x, p2.x, sp); sp = fmaf(v1.y, p2.y, sp); sp = fmaf(v1.z, p3.x, sp); sp = fmaf(v1.w, p3.y, sp);
+            }
+            S[warp][j] = (sc + sp) * scale;
+        }
+    }
+    // softmax over the T keys of the warp's row (ggml_soft_max: max-subtracted exp, normalised), fp32
+    float inv = 0.0f;
+    if (i < T) {
+        float mx = -INFINITY;
+        for (int j = lane; j < T; j += 32) mx = fmaxf(mx, S[warp][j]);
+        mx = warp_max(mx);
+        float sum = 0.0f;
+        for (int j = lane; j < T; j += 32) {
+            const float e = expf(S[warp][j] - mx);
+            S[warp][j] = e;
+            sum += e;
+        }
+        inv = 1.0f / warp_sum(sum);
+    }
+    // context: lane owns features 4 lane .. 4 lane + 3; V goes through the K tile buffer
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int j0 = 0; j0 < T; j0 += AF_KT) {
+        __syncthreads();
+        for (int idx = tid; idx < AF_KT * 16; idx += 256) {
+            const int r = idx >> 4, c = idx & 15, j = j0 + r;
+            *reinterpret_cast<uint4*>(&Kt[r][c * 8]) = j < T ? *reinterpret_cast<const uint4*>(qkv + (size_t)j * (3 * D_MODEL) + 2 * D_MODEL + c * 8) : z4;
+        }
+        __syncthreads();
+        if (i < T) {
+            const int n = min(AF_KT, T - j0);
+            for (int jj = 0; jj < n; jj++) {
+                const float p = S[warp][j0 + jj];
+                const uint2 raw = *reinterpret_cast<const uint2*>(&Kt[jj][4 * lane]);
+                const float2 v01 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x)), v23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+                acc.x = fmaf(p, v01.x, acc.x); acc.y = fmaf(p, v01.y, acc.y); acc.z = fmaf(p, v23.x, acc.z); acc.w = fmaf(p, v23.y, acc.w);
+            }
+        }
+    }
+    if (i < T) {
+        float4 v = make_float4(acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv);
+        if (a.act_quant) {  // the warp is converged here: i < T is warp-uniform
+            const float amax = group8_max(fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+            v.x = fake_quant(v.x, amax);
+            v.y = fake_quant(v.y, amax);
+            v.z = fake_quant(v.z, amax);
+            v.w = fake_quant(v.w, amax);
+        }
+        const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
+        uint2 u;
+        u.x = *reinterpret_cast<const uint32_t*>(&lo);
+        u.y = *reinterpret_cast<const uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(a.out + (size_t)i * D_MODEL + h * D_HEAD + 4 * lane) = u;
+    }
+}
+
+void launch_attention_full(cudaStream_t st, const AttnFullArgs& a) {
+    if (a.T <= 0) return;
+    if (a.T > ATTN_FULL_MAX_T) throw Error("offline attention: more than 512 encoder frames");
+    ProfScope ps(st, "attention_full", 6.0 * N_HEADS * (double)a.T * a.T * D_HEAD, (double)a.T * D_MODEL * 2 * 6);
+    launch_k(attention_full_kernel, dim3(dim3(cdiv(a.T, AF_QB), N_HEADS)), dim3(256), 0, st, a);
+    NB_KERNEL_CHECK();
+}
+
 void launch_attention(cudaStream_t st, const AttnArgs& a) {
     static const bool use_simt = getenv("NB200_ATTN_SIMT") != nullptr;
     if (a.T > MAX_T) throw Error("attention: more than 14 frames per chunk");

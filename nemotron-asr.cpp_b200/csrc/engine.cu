@@ -141,6 +141,11 @@ struct nb200_model {
     // multilingual prompt fusion (src/nemo-ggml.cpp:1087-1105), fp32 like the file: fc1 split into its encoder part
     // [2048][1024] and its one-hot part stored per language [num_prompts][2048]; fc2 [1024][2048]
     int num_prompts = 0, default_prompt = -1;
+    // offline path (nb200_encode_audio): positional table of the last utterance length, allocated on first use
+    float* off_posf = nullptr;
+    __half *off_pos16 = nullptr, *off_pos_tab = nullptr;
+    Operand op_off_pos16;
+    int off_max_T = 0, off_pos_T = 0;
     float *pk_w1 = nullptr, *pk_w1_lang = nullptr, *pk_b1 = nullptr, *pk_w2 = nullptr, *pk_b2 = nullptr;
     std::map<std::string, int> prompt_dict;
     std::vector<LayerW> layers;
@@ -729,65 +734,17 @@ void run_batch_finish(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
 
 namespace {
 
-struct StepCtx {
-    nb200_model* m;
-    ModeCtx* mc;
-    int B;
-    bool taps;
-    std::vector<BatchItem>* items;
-};
-
-// ---- frontend + 24 conformer layers + joint.enc: no host synchronisation inside unless parity taps are on ----
-void enqueue_encoder(const StepCtx& c) {
-    nb200_model* m = c.m;
-    ModeCtx* mc = c.mc;
-    const Mode& md = mc->mode;
-    const int B = c.B, T = md.T, M = B * T, capB = m->cap_B;
+// LayerNorm + 24 conformer layers (+ the multilingual prompt fusion) over the M = B * T rows in ws_x; `attn(l)` turns layer l's
+// q | k | v (ws_qkv16) into the attention context (ws_a16). Shared by the streaming step and the offline path. Returns the
+// encoder output ([M][1024] fp32, ws_x or ws_g).
+template <typename AttnFn>
+const float* enqueue_layers(nb200_model* m, int B, int T, AttnFn&& attn) {
+    const int M = B * T, capB = m->cap_B;
     const int aq = m->act_quant ? 1 : 0;
     const bool simt = m->simt;
     cudaStream_t st = m->st;
     const int* d_slot = m->ws_meta + 0 * capB;
-    const int* d_wpos = m->ws_meta + 1 * capB;
-    const int* d_valid = m->ws_meta + 2 * capB;
-    const int* d_nframes = m->ws_meta + 4 * capB;
     const int* d_parity = m->ws_meta + 5 * capB;
-
-    // frontend: log-mel of the new samples, then dw-striding subsampling (src/nemo-ggml.cpp:954-1029)
-    launch_k(mel_assemble_kernel, dim3(dim3(md.chunk_mel, B)), dim3(N_MELS), 0, st, m->ws_mel, m->mel_overlap, d_slot, d_nframes, md.chunk_mel);
-    NB_KERNEL_CHECK();
-    {
-        MelBatch mb{m->pcm_ring, m->ring_cap, d_slot, d_nframes, m->ws_meta64 + 1 * capB, m->ws_meta64 + 2 * capB, m->ws_meta64 + 0 * capB};
-        launch_mel(st, m->mel_tb, mb, m->ws_mel, B, md.shift);
-    }
-    if (c.taps) {
-        for (int b = 0; b < B; b++) {
-            nb200_stream* s = (*c.items)[b].s;
-            const int nfr = (*c.items)[b].n_frames;
-            if ((s->taps & NB200_TAP_MEL) && nfr > 0) {
-                const size_t n = (size_t)nfr * N_MELS, old = s->tap_mel.size();
-                s->tap_mel.resize(old + n);
-                CUDA_CHECK(cudaMemcpyAsync(s->tap_mel.data() + old, m->ws_mel + ((size_t)b * md.chunk_mel + MEL_OVERLAP) * N_MELS,
-                                           n * sizeof(float), cudaMemcpyDeviceToHost, st));
-                CUDA_CHECK(cudaStreamSynchronize(st));
-            }
-        }
-    }
-    launch_sub_stage1(st, m->sub, m->ws_mel, m->ws_a2h, B, md.chunk_mel, md.t1, md.t2);
-    launch_k(mel_save_overlap_kernel, dim3(dim3(MEL_OVERLAP, B)), dim3(N_MELS), 0, st, m->ws_mel, m->mel_overlap, d_slot, md.chunk_mel, md.shift);
-    NB_KERNEL_CHECK();
-    {
-        EpiParams ep;  // pw3 + bias + ReLU -> fp32 (input of the fp32 depthwise conv5)
-        ep.kind = EPI_STORE; ep.act = ACT_RELU; ep.bias = m->sub_b3; ep.out_f32 = m->ws_a3; ep.ldo = SUB_CH;
-        gemm(st, m->op_a2h, m->sub_w3.op, B * md.t2 * SUB_F2, ep, simt);
-        launch_sub_stage2(st, m->sub, m->ws_a3, m->ws_a5h, B, md.t2, md.t3);
-        EpiParams e6;  // pw6 + bias + ReLU -> fp16 [B*T*17][256], whose rows (b,t) are the K=4352 operand of pre_encode.out
-        e6.kind = EPI_STORE_F16; e6.act = ACT_RELU; e6.bias = m->sub_b6; e6.out_f16 = m->ws_a6h; e6.ldo = SUB_CH; e6.act_quant = 0;
-        gemm(st, m->op_a5h, m->sub_w6.op, M * SUB_F3, e6, simt);
-        EpiParams eo;
-        eo.kind = EPI_STORE; eo.bias = m->sub_bout; eo.out_f32 = m->ws_x; eo.ldo = D_MODEL;
-        gemm(st, m->op_a6h, m->sub_wout.op, M, eo, simt);
-    }
-
     // 24 cache-aware conformer layers (src/nemo-stream.cpp:605-690)
     const size_t S = (size_t)m->max_streams;
     launch_layernorm(st, m->ws_x, m->layers[0].ln_ff1_g, m->layers[0].ln_ff1_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M);
@@ -805,16 +762,10 @@ void enqueue_encoder(const StepCtx& c) {
         rin.alpha = 0.5f;  // x += 0.5 * FFN1
         // self-attention
         launch_layernorm(st, m->ws_x, L.ln_att_g, L.ln_att_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin);
-        __half* kr = m->k_ring + (size_t)l * S * RING * D_MODEL;
-        __half* vr = m->v_ring + (size_t)l * S * RING * D_MODEL;
         EpiParams qkv;  // q | k | v of the chunk's frames, dense fp16; the attention kernel appends k, v to the stream rings
         qkv.kind = EPI_STORE_F16; qkv.out_f16 = m->ws_qkv16; qkv.ldo = 3 * D_MODEL;
         gemm(st, m->op_a16, L.wqkv.op, M, qkv, simt);
-        AttnArgs at{};
-        at.qkv = m->ws_qkv16; at.k_ring = kr; at.v_ring = vr; at.pos = mc->pos_tab + (size_t)l * md.npos * D_MODEL;
-        at.bias_u = L.pos_u; at.bias_v = L.pos_v; at.slot = d_slot; at.wpos = d_wpos; at.valid = d_valid;
-        at.out = m->ws_a16; at.B = B; at.T = T; at.act_quant = aq;
-        launch_attention(st, at);
+        attn(l);  // q | k | v in ws_qkv16 -> context in ws_a16 (cached streaming attention, or full-sequence attention offline)
         rin.nsplit = gemm(st, m->op_a16, L.wout.op, M, part, simt, m->part_max_splits);
         rin.alpha = 1.0f;  // x += attention
         // convolution module
@@ -858,6 +809,91 @@ void enqueue_encoder(const StepCtx& c) {
         }
         enc_out = m->ws_g;
     }
+    return enc_out;
+}
+
+// joint.enc over all frames (fp32 quality: split-precision tensor-core GEMM, or the fp32 CUDA-core checker)
+void enqueue_joint_enc(nb200_model* m, const float* enc_out, int M) {
+    cudaStream_t st = m->st;
+    if (m->joint_enc_tc && !m->simt) {
+        launch_split_f16x3(st, enc_out, m->ws_h16, M);
+        EpiParams ej;
+        ej.kind = EPI_STORE; ej.bias = m->joint_enc_b; ej.out_f32 = m->ws_e; ej.ldo = JOINT;
+        gemm(st, m->op_x3, m->joint_enc_w3.op, M, ej, false);
+    } else {
+        launch_sgemm(st, enc_out, m->joint_enc_w, m->joint_enc_b, m->ws_e, M, JOINT, D_MODEL, JOINT, nullptr);
+    }
+}
+
+struct StepCtx {
+    nb200_model* m;
+    ModeCtx* mc;
+    int B;
+    bool taps;
+    std::vector<BatchItem>* items;
+};
+
+// ---- frontend + 24 conformer layers + joint.enc: no host synchronisation inside unless parity taps are on ----
+void enqueue_encoder(const StepCtx& c) {
+    nb200_model* m = c.m;
+    ModeCtx* mc = c.mc;
+    const Mode& md = mc->mode;
+    const int B = c.B, T = md.T, M = B * T, capB = m->cap_B;
+    const int aq = m->act_quant ? 1 : 0;
+    const bool simt = m->simt;
+    cudaStream_t st = m->st;
+    const int* d_slot = m->ws_meta + 0 * capB;
+    const int* d_wpos = m->ws_meta + 1 * capB;
+    const int* d_valid = m->ws_meta + 2 * capB;
+    const int* d_nframes = m->ws_meta + 4 * capB;
+
+    // frontend: log-mel of the new samples, then dw-striding subsampling (src/nemo-ggml.cpp:954-1029)
+    launch_k(mel_assemble_kernel, dim3(dim3(md.chunk_mel, B)), dim3(N_MELS), 0, st, m->ws_mel, m->mel_overlap, d_slot, d_nframes, md.chunk_mel);
+    NB_KERNEL_CHECK();
+    {
+        MelBatch mb{m->pcm_ring, m->ring_cap, d_slot, d_nframes, m->ws_meta64 + 1 * capB, m->ws_meta64 + 2 * capB, m->ws_meta64 + 0 * capB};
+        launch_mel(st, m->mel_tb, mb, m->ws_mel, B, md.shift);
+    }
+    if (c.taps) {
+        for (int b = 0; b < B; b++) {
+            nb200_stream* s = (*c.items)[b].s;
+            const int nfr = (*c.items)[b].n_frames;
+            if ((s->taps & NB200_TAP_MEL) && nfr > 0) {
+                const size_t n = (size_t)nfr * N_MELS, old = s->tap_mel.size();
+                s->tap_mel.resize(old + n);
+                CUDA_CHECK(cudaMemcpyAsync(s->tap_mel.data() + old, m->ws_mel + ((size_t)b * md.chunk_mel + MEL_OVERLAP) * N_MELS,
+                                           n * sizeof(float), cudaMemcpyDeviceToHost, st));
+                CUDA_CHECK(cudaStreamSynchronize(st));
+            }
+        }
+    }
+    launch_sub_stage1(st, m->sub, m->ws_mel, m->ws_a2h, B, md.chunk_mel, md.t1, md.t2);
+    launch_k(mel_save_overlap_kernel, dim3(dim3(MEL_OVERLAP, B)), dim3(N_MELS), 0, st, m->ws_mel, m->mel_overlap, d_slot, md.chunk_mel, md.shift);
+    NB_KERNEL_CHECK();
+    {
+        EpiParams ep;  // pw3 + bias + ReLU -> fp32 (input of the fp32 depthwise conv5)
+        ep.kind = EPI_STORE; ep.act = ACT_RELU; ep.bias = m->sub_b3; ep.out_f32 = m->ws_a3; ep.ldo = SUB_CH;
+        gemm(st, m->op_a2h, m->sub_w3.op, B * md.t2 * SUB_F2, ep, simt);
+        launch_sub_stage2(st, m->sub, m->ws_a3, m->ws_a5h, B, md.t2, md.t3);
+        EpiParams e6;  // pw6 + bias + ReLU -> fp16 [B*T*17][256], whose rows (b,t) are the K=4352 operand of pre_encode.out
+        e6.kind = EPI_STORE_F16; e6.act = ACT_RELU; e6.bias = m->sub_b6; e6.out_f16 = m->ws_a6h; e6.ldo = SUB_CH; e6.act_quant = 0;
+        gemm(st, m->op_a5h, m->sub_w6.op, M * SUB_F3, e6, simt);
+        EpiParams eo;
+        eo.kind = EPI_STORE; eo.bias = m->sub_bout; eo.out_f32 = m->ws_x; eo.ldo = D_MODEL;
+        gemm(st, m->op_a6h, m->sub_wout.op, M, eo, simt);
+    }
+
+    // 24 cache-aware conformer layers (src/nemo-stream.cpp:605-690)
+    const size_t S = (size_t)m->max_streams;
+    const float* enc_out = enqueue_layers(m, B, T, [&](int l) {
+        LayerW& L = m->layers[l];
+        AttnArgs at{};
+        at.qkv = m->ws_qkv16; at.k_ring = m->k_ring + (size_t)l * S * RING * D_MODEL; at.v_ring = m->v_ring + (size_t)l * S * RING * D_MODEL;
+        at.pos = mc->pos_tab + (size_t)l * md.npos * D_MODEL;
+        at.bias_u = L.pos_u; at.bias_v = L.pos_v; at.slot = d_slot; at.wpos = d_wpos; at.valid = d_valid;
+        at.out = m->ws_a16; at.B = B; at.T = T; at.act_quant = aq;
+        launch_attention(st, at);
+    });
     if (c.taps) {
         for (int b = 0; b < B; b++) {
             nb200_stream* s = (*c.items)[b].s;
@@ -870,14 +906,7 @@ void enqueue_encoder(const StepCtx& c) {
         }
     }
     // joint.enc over all frames of the batch, and the decode loop's per-step state
-    if (m->joint_enc_tc && !simt) {
-        launch_split_f16x3(st, enc_out, m->ws_h16, M);
-        EpiParams ej;
-        ej.kind = EPI_STORE; ej.bias = m->joint_enc_b; ej.out_f32 = m->ws_e; ej.ldo = JOINT;
-        gemm(st, m->op_x3, m->joint_enc_w3.op, M, ej, false);
-    } else {
-        launch_sgemm(st, enc_out, m->joint_enc_w, m->joint_enc_b, m->ws_e, M, JOINT, D_MODEL, JOINT, nullptr);
-    }
+    enqueue_joint_enc(m, enc_out, M);
     launch_decode_chunk(st, m->dec, m->dstate, decode_batch(m, B, T));  // every greedy round of the chunk, one persistent launch
 }
 
@@ -1481,6 +1510,126 @@ int nb200_mel_batch(nb200_model* m, const int16_t* pcm, int n_streams, int n_sam
     cudaFree(d_l);
     cudaFree(d_mel);
     return nf;
+    NB_CATCH(NB200_ERR)
+}
+
+// ---- offline path: nemo_encode_audio (src/nemo-ggml.cpp:1690-1715 -> nemo_encode :1592-1670) ---------------------------
+// Whole-utterance log-mel -> dw-striding subsampling with its causal zero padding, nothing dropped -> 24 layers with
+// full-sequence relative-position attention (no cache, no mask) and the causal depthwise conv over zero left padding ->
+// (prompt fusion) -> greedy decode from a zero LSTM state with timed tokens. Same kernels as the streaming step (one
+// "chunk" of T frames on a scratch slot with zeroed caches) except for the attention. Eager launches, synchronous.
+int nb200_encode_audio(nb200_model* m, const int16_t* pcm, int n_samples, int32_t* tokens_out, int64_t* frames_out, int cap,
+                       float* enc_out, int64_t enc_cap_floats, int* n_frames_out) {
+    NB_TRY
+    if (!m || (!pcm && n_samples > 0) || (!tokens_out && cap > 0)) throw Error("null argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    if (finish_inflight(m) < 0) return NB200_ERR;
+    if (n_frames_out) *n_frames_out = 0;
+    const int nf = (int)frames_available(n_samples);
+    if (nf <= 0) return 0;  // nemo_encode_audio returns no tokens for an utterance without a single frame
+    const int t1 = nf / 2 + 1, t2 = t1 / 2 + 1, T = t2 / 2 + 1;  // causal stride-2 convs: pad 2 before, 1 after (src/nemo-ggml.cpp:897-952)
+    const int capB = m->cap_B;
+    const Mode big(13);
+    if (T > ATTN_FULL_MAX_T) throw Error("offline path: utterance longer than 512 encoder frames (the reference's positional table, src/nemo-ggml.cpp:1061)");
+    if (nf > capB * big.chunk_mel || t2 > capB * big.t2 || T > capB * MAX_T)
+        throw Error("offline path: utterance too long for this model's workspaces (" + std::to_string(T) + " frames; max_streams * 14 = " +
+                    std::to_string(capB * MAX_T) + "): raise max_streams at model load");
+    if (m->free_slots.empty()) throw Error("offline path needs one free stream slot");
+    const int slot = m->free_slots.back();  // scratch: zero conv caches and decoder state, left free afterwards
+    cudaStream_t st = m->st;
+    flush_uploads(m);
+    reset_slot(m, slot);
+    const int aq = m->act_quant ? 1 : 0;
+
+    // positional table for this length: rows p + (T - 1), p = i - j in [-(T-1), T-1] (ascending p; the reference stores the
+    // same rows in descending order and its rel-shift reads row j - i + T - 1, src/nemo-ggml.cpp:17-32,625-662)
+    if (!m->off_pos_tab) {
+        m->off_max_T = std::min(ATTN_FULL_MAX_T, capB * MAX_T);
+        const size_t rows = (size_t)2 * m->off_max_T;
+        m->off_posf = m->alloc<float>(rows * D_MODEL);
+        m->off_pos16 = m->alloc<__half>(rows * D_MODEL);
+        m->off_pos_tab = m->alloc<__half>((size_t)m->n_layers * rows * D_MODEL);
+        operand_init(m->op_off_pos16, m->off_pos16, (int)rows, D_MODEL);
+    }
+    const int npos = 2 * T - 1;
+    if (m->off_pos_T != T) {
+        launch_pos_emb(st, m->off_posf, -(T - 1), npos);
+        launch_cast_f16(st, m->off_posf, m->off_pos16, aq, npos, D_MODEL);
+        for (int l = 0; l < m->n_layers; l++) {
+            EpiParams ep;
+            ep.kind = EPI_STORE_F16;
+            ep.out_f16 = m->off_pos_tab + (size_t)l * npos * D_MODEL;
+            ep.ldo = D_MODEL;
+            gemm(st, m->op_off_pos16, m->layers[l].wpos.op, npos, ep, m->simt);
+        }
+        m->off_pos_T = T;
+    }
+
+    // audio + metadata of the one "stream" (b = 0)
+    const int ring = 1 << 30;  // the mel kernel indexes a ring: make it larger than any utterance
+    int16_t* d_pcm = dalloc<int16_t>((size_t)n_samples + 8);
+    std::vector<int> meta((size_t)META_ROWS * capB, 0);
+    std::vector<long long> meta64((size_t)3 * capB, 0);
+    meta[0 * capB] = slot;      // slot (scratch: zeroed caches)
+    meta[3 * capB] = T;         // frames to decode
+    meta[4 * capB] = nf;
+    meta[6 * capB] = (m->default_prompt >= 0 && m->default_prompt < m->num_prompts) ? m->default_prompt : 0;
+    meta64[0 * capB] = 0;       // mel rows start at ws_mel
+    meta64[1 * capB] = -257;    // 256 zeros of centre padding + the pre-emphasis sample (src/preprocessor.cpp:300-328)
+    meta64[2 * capB] = n_samples;
+    int zero = 0;
+    CUDA_CHECK(cudaMemcpyAsync(d_pcm, pcm, (size_t)n_samples * sizeof(int16_t), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(m->ws_meta, meta.data(), meta.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(m->ws_meta64, meta64.data(), meta64.size() * sizeof(long long), cudaMemcpyHostToDevice, st));
+    int* d_zero_slot = m->ws_meta + 7 * capB;  // spare meta row: the mel kernel's ring slot index (0: d_pcm is the whole "ring")
+    CUDA_CHECK(cudaMemcpyAsync(d_zero_slot, &zero, sizeof(int), cudaMemcpyHostToDevice, st));
+    {
+        MelBatch mb{d_pcm, ring, d_zero_slot, m->ws_meta + 4 * capB, m->ws_meta64 + 1 * capB, m->ws_meta64 + 2 * capB, m->ws_meta64 + 0 * capB};
+        launch_mel(st, m->mel_tb, mb, m->ws_mel, 1, nf);
+    }
+    launch_sub_stage1(st, m->sub, m->ws_mel, m->ws_a2h, 1, nf, t1, t2);
+    {
+        EpiParams ep;
+        ep.kind = EPI_STORE; ep.act = ACT_RELU; ep.bias = m->sub_b3; ep.out_f32 = m->ws_a3; ep.ldo = SUB_CH;
+        gemm(st, m->op_a2h, m->sub_w3.op, t2 * SUB_F2, ep, m->simt);
+        launch_sub_stage2(st, m->sub, m->ws_a3, m->ws_a5h, 1, t2, T, 0);
+        EpiParams e6;
+        e6.kind = EPI_STORE_F16; e6.act = ACT_RELU; e6.bias = m->sub_b6; e6.out_f16 = m->ws_a6h; e6.ldo = SUB_CH; e6.act_quant = 0;
+        gemm(st, m->op_a5h, m->sub_w6.op, T * SUB_F3, e6, m->simt);
+        EpiParams eo;
+        eo.kind = EPI_STORE; eo.bias = m->sub_bout; eo.out_f32 = m->ws_x; eo.ldo = D_MODEL;
+        gemm(st, m->op_a6h, m->sub_wout.op, T, eo, m->simt);
+    }
+    const float* enc = enqueue_layers(m, 1, T, [&](int l) {
+        LayerW& L = m->layers[l];
+        AttnFullArgs at{};
+        at.qkv = m->ws_qkv16; at.pos = m->off_pos_tab + (size_t)l * npos * D_MODEL;
+        at.bias_u = L.pos_u; at.bias_v = L.pos_v; at.out = m->ws_a16; at.T = T; at.act_quant = aq;
+        launch_attention_full(st, at);
+    });
+    if (enc_out) {
+        if (enc_cap_floats < (int64_t)T * D_MODEL) throw Error("encoder output buffer too small");
+        CUDA_CHECK(cudaMemcpyAsync(enc_out, enc, (size_t)T * D_MODEL * sizeof(float), cudaMemcpyDeviceToHost, st));
+    }
+    enqueue_joint_enc(m, enc, T);
+    launch_decode_chunk(st, m->dec, m->dstate, decode_batch(m, 1, T));  // greedy_decode (src/nemo-ggml.cpp:1233-1380): same rounds, fresh state
+    int counters[8], n_tok = 0;
+    CUDA_CHECK(cudaMemcpyAsync(counters, m->ws_unfinished + 6, sizeof(counters), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaMemcpyAsync(&n_tok, m->ws_tokcnt, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    cudaFree(d_pcm);
+    if (counters[0] != 0) throw Error("decode loop did not terminate");
+    std::vector<int> words((size_t)std::max(n_tok, 1));
+    CUDA_CHECK(cudaMemcpy(words.data(), m->ws_tok, (size_t)n_tok * sizeof(int), cudaMemcpyDeviceToHost));
+    for (int i = 0; i < std::min(n_tok, cap); i++) {
+        tokens_out[i] = words[i] & 0xffff;
+        if (frames_out) frames_out[i] = words[i] >> 16;
+    }
+    if (n_frames_out) *n_frames_out = T;
+    m->stats.audio_seconds += (double)n_samples / 16000.0;
+    m->stats.frames += T;
+    m->stats.tokens += n_tok;
+    return n_tok;
     NB_CATCH(NB200_ERR)
 }
 

@@ -289,12 +289,13 @@ void launch_sub_stage1(cudaStream_t st, const SubWeights& w, const float* mel, _
     NB_KERNEL_CHECK();
 }
 
-// ---- subsampling stage 2: depthwise conv5 over relu(pw3), only the rows that survive the drop of 2 frames ----------
+// ---- subsampling stage 2: depthwise conv5 over relu(pw3), only the rows that survive the drop of `drop` frames (2 in the
+// streaming path, src/nemo-stream.cpp:154-162; 0 in the offline path) -------------------------------------------------
 __global__ void __launch_bounds__(256) sub_stage2_kernel(SubWeights w, const float* __restrict__ a3, __half* __restrict__ out,
-                                                         int t2, int t3) {
+                                                         int t2, int t3, int drop) {
     pdl_prologue();
     const int w3 = blockIdx.x, hh = blockIdx.y, b = blockIdx.z, c = threadIdx.x;
-    const int h3 = hh + 2;
+    const int h3 = hh + drop;
     float acc = w.b5[c];
 #pragma unroll
     for (int kh = 0; kh < 3; kh++) {
@@ -307,13 +308,13 @@ __global__ void __launch_bounds__(256) sub_stage2_kernel(SubWeights w, const flo
             acc = fmaf(w.w5[c * 9 + kh * 3 + kw], a3[((size_t)(b * t2 + h2) * SUB_F2 + w2) * SUB_CH + c], acc);
         }
     }
-    out[((size_t)(b * (t3 - 2) + hh) * SUB_F3 + w3) * SUB_CH + c] = __float2half_rn(acc);
+    out[((size_t)(b * (t3 - drop) + hh) * SUB_F3 + w3) * SUB_CH + c] = __float2half_rn(acc);
 }
 
-void launch_sub_stage2(cudaStream_t st, const SubWeights& w, const float* a3, __half* out, int B, int t2, int t3) {
-    ProfScope ps(st, "sub_dw5", (double)B * (t3 - 2) * SUB_F3 * SUB_CH * 18.0,
-                 (double)B * ((double)t2 * SUB_F2 * SUB_CH * 4 + (double)(t3 - 2) * SUB_F3 * SUB_CH * 2));
-    for (int rep = dup_family("sub2") ? 2 : 1; rep > 0; rep--) launch_k(sub_stage2_kernel, dim3(dim3(SUB_F3, t3 - 2, B)), dim3(256), 0, st, w, a3, out, t2, t3);
+void launch_sub_stage2(cudaStream_t st, const SubWeights& w, const float* a3, __half* out, int B, int t2, int t3, int drop) {
+    ProfScope ps(st, "sub_dw5", (double)B * (t3 - drop) * SUB_F3 * SUB_CH * 18.0,
+                 (double)B * ((double)t2 * SUB_F2 * SUB_CH * 4 + (double)(t3 - drop) * SUB_F3 * SUB_CH * 2));
+    for (int rep = dup_family("sub2") ? 2 : 1; rep > 0; rep--) launch_k(sub_stage2_kernel, dim3(dim3(SUB_F3, t3 - drop, B)), dim3(256), 0, st, w, a3, out, t2, t3, drop);
     NB_KERNEL_CHECK();
 }
 

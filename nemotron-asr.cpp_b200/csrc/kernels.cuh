@@ -38,8 +38,8 @@ struct SubWeights {          // encoder.pre_encode.* (src/nemo-ggml.cpp:296-307)
 };
 // mel chunk [B][chunk_mel][128] -> relu(conv0) -> depthwise conv2 (+bias) -> fp16 [B][t2][33][256]
 void launch_sub_stage1(cudaStream_t st, const SubWeights& w, const float* mel, __half* out, int B, int chunk_mel, int t1, int t2);
-// relu(pw3) fp32 [B][t2][33][256] -> depthwise conv5 (+bias), rows h3 >= 2 only -> fp16 [B][t3-2][17][256]
-void launch_sub_stage2(cudaStream_t st, const SubWeights& w, const float* a3, __half* out, int B, int t2, int t3);
+// relu(pw3) fp32 [B][t2][33][256] -> depthwise conv5 (+bias), rows h3 >= drop only -> fp16 [B][t3-drop][17][256]
+void launch_sub_stage2(cudaStream_t st, const SubWeights& w, const float* a3, __half* out, int B, int t2, int t3, int drop = 2);
 
 // ---- encoder.cu ----------------------------------------------------------------------------------
 // Optional residual input: x += alpha * sum_{s<nsplit} partials[s*stride + ...] first (the split-K partial outputs of the
@@ -70,6 +70,19 @@ struct AttnArgs {
     int B, T, act_quant;
 };
 void launch_attention(cudaStream_t st, const AttnArgs& a);
+
+// Offline path: full-sequence relative-position attention over one utterance (build_rel_pos_mha, src/nemo-ggml.cpp:668-757):
+// no cache, no mask; query i, key j use position i - j (the rel-shift, :625-662).
+struct AttnFullArgs {
+    const __half* qkv;     // [T][3072] fp16: q | k | v
+    const __half* pos;     // this layer's projected positions [2T-1][1024] fp16, row p + (T-1), p = i - j in [-(T-1), T-1]
+    const float* bias_u;   // [8][128]
+    const float* bias_v;
+    __half* out;           // [T][1024] fp16 context (fq per 32 features when act_quant)
+    int T, act_quant;
+};
+constexpr int ATTN_FULL_MAX_T = 512;  // the reference's positional table covers 512 frames (src/nemo-ggml.cpp:233,1061)
+void launch_attention_full(cudaStream_t st, const AttnFullArgs& a);
 
 struct ConvArgs {
     const float* g;        // GLU output [M][1024]

@@ -62,6 +62,7 @@ SYMBOLS = {
     "nb200_feed_batch": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), _I32P, C.c_int]),
     "nb200_poll_batch": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int, _I32P, C.c_int, _I32P]),
     "nb200_drain": (C.c_int, [C.c_void_p]),
+    "nb200_encode_audio": (C.c_int, [C.c_void_p, _I16P, C.c_int, _I32P, _I64P, C.c_int, _F32P, C.c_int64, C.POINTER(C.c_int)]),
     "nb200_stream_poll_tokens": (C.c_int, [C.c_void_p, _I32P, C.c_int]),
     "nb200_stream_get_tokens": (C.c_int, [C.c_void_p, _I32P, C.c_int]),
     "nb200_stream_poll_timed": (C.c_int, [C.c_void_p, _I32P, _I64P, C.c_int]),
@@ -203,6 +204,22 @@ class Model:
         if n < 0:
             raise NB200Error(_err())
         return buf.raw[:n].decode("utf-8", errors="replace")
+
+    def encode_audio(self, pcm: np.ndarray, want_enc: bool = False):
+        """nemo_encode_audio (src/nemo-ggml.cpp:1690-1715), the offline path: -> (tokens, frames) or (tokens, frames, enc [T,1024])"""
+        pcm = np.ascontiguousarray(pcm, dtype=np.int16)
+        max_frames = pcm.size // 1280 + 4
+        cap = 10 * max_frames
+        tok, fr = np.zeros(cap, np.int32), np.zeros(cap, np.int64)
+        enc = np.zeros((max_frames, 1024), np.float32) if want_enc else None
+        nfr = C.c_int(0)
+        n = lib().nb200_encode_audio(self._h, _ptr(pcm, _I16P), int(pcm.size), _ptr(tok, _I32P), _ptr(fr, _I64P), cap,
+                                     _ptr(enc, _F32P) if want_enc else None, int(enc.size) if want_enc else 0, C.byref(nfr))
+        if n < 0:
+            raise NB200Error(_err())
+        if want_enc:
+            return tok[:n].tolist(), fr[:n].tolist(), enc[: nfr.value].copy()
+        return tok[:n].tolist(), fr[:n].tolist()
 
     def tokens_to_text_timed(self, tokens, frames) -> str:
         """tokens_to_text(timed tokens, vocab, timestamp_words=true), src/nemo-ggml.cpp:1556-1583"""
