@@ -78,6 +78,10 @@ int nb200_tokens_to_text_timed(const nb200_model* m, const int32_t* tokens, cons
 
 /* nemo_stream_init(ctx, cfg) with cfg.att_right_context in {0,1,6,13} — src/nemo-stream.h:271, .cpp:696-733 */
 nb200_stream* nb200_stream_create(nb200_model* m, int right_context);
+/* nemo_set_language(ctx, lang) — src/nemo-ggml.h:266, .cpp:497-511: the model-wide language prompt (multilingual files):
+ * used by the offline path (nb200_encode_audio) and inherited by streams created afterwards (nemo_stream_init copies
+ * ctx->prompt_index). Unknown code or a monolingual model: error, nothing changes. */
+int nb200_model_set_language(nb200_model* m, const char* lang);
 /* nemo_stream_set_language — src/nemo-stream.h:279, src/nemo-stream.cpp:735-749 (multilingual checkpoints: the language
  * code is looked up in the GGUF's nemo.prompt_langs / nemo.prompt_ids; it may change between chunks). Fails like the
  * reference (which returns false) when the model has no prompts or the code is unknown. New streams start with the

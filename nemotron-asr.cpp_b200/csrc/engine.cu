@@ -1434,6 +1434,17 @@ int nb200_stream_chunk_margins(const nb200_stream* s, float* out, int cap) {
     return (int)s->chunk_margins.size();
 }
 
+int nb200_model_set_language(nb200_model* m, const char* lang) {
+    NB_TRY
+    if (!m || !lang) throw Error("null argument");
+    if (m->num_prompts <= 0) throw Error("model is not multilingual (num_prompts=0)");
+    auto it = m->prompt_dict.find(lang);
+    if (it == m->prompt_dict.end()) throw Error(std::string("unknown language code '") + lang + "'");
+    m->default_prompt = it->second;
+    return NB200_OK;
+    NB_CATCH(NB200_ERR)
+}
+
 int nb200_stream_set_language(nb200_stream* s, const char* lang) {
     NB_TRY
     if (!s || !lang) throw Error("null argument");

@@ -52,6 +52,7 @@ SYMBOLS = {
     "nb200_stream_free": (None, [C.c_void_p]),
     "nb200_stream_reset": (C.c_int, [C.c_void_p]),
     "nb200_stream_set_language": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "nb200_model_set_language": (C.c_int, [C.c_void_p, C.c_char_p]),
     "nb200_stream_set_prompt_index": (C.c_int, [C.c_void_p, C.c_int]),
     "nb200_stream_feed": (C.c_int, [C.c_void_p, _I16P, C.c_int]),
     "nb200_stream_finalize": (C.c_int, [C.c_void_p]),
@@ -204,6 +205,10 @@ class Model:
         if n < 0:
             raise NB200Error(_err())
         return buf.raw[:n].decode("utf-8", errors="replace")
+
+    def set_language(self, lang: str) -> bool:
+        """nemo_set_language (src/nemo-ggml.cpp:497-511): False (and no change) for an unknown code / monolingual model"""
+        return lib().nb200_model_set_language(self._h, lang.encode()) == 0
 
     def encode_audio(self, pcm: np.ndarray, want_enc: bool = False):
         """nemo_encode_audio (src/nemo-ggml.cpp:1690-1715), the offline path: -> (tokens, frames) or (tokens, frames, enc [T,1024])"""

@@ -18,11 +18,12 @@
 //   ref_harness matmul <gguf> <tensor_name> <x.f32> <M> <out.f32> [threads]
 //       y[M,N] = ggml_mul_mat(W, x) on the reference's CPU backend for one weight tensor of the file (Q8_0 or F32),
 //       i.e. exactly the kernel the encoder graph runs for that tensor (src/nemo-stream.cpp:593-603).
-//   ref_harness offline <gguf> <pcm.s16le> <threads> <out_prefix> [max_seconds]
+//   ref_harness offline <gguf> <pcm.s16le> <threads> <out_prefix> [max_seconds] [language|-]
 //       the reference's offline path: nemo_encode_audio (src/nemo-ggml.cpp:1690-1715 = nemo_preprocessor_process over the
 //       whole utterance + build_encoder with full-sequence attention + greedy_decode) -> <prefix>.tokens.i32,
 //       <prefix>.frames.i64 (timed_token::frame_idx); and, through the public build_encoder (src/nemo-ggml.h:342) on the
-//       same mel, <prefix>.enc.f32 [T, d_model] and <prefix>.mel.f32.
+//       same mel (+ build_prompt_fusion :351 for multilingual files, like nemo_encode), <prefix>.enc.f32 [T, d_model] and
+//       <prefix>.mel.f32. language: nemo_set_language (src/nemo-ggml.cpp:497-511).
 //   ref_harness text <gguf> <tokens.i32> <frames.i64> <timestamp_words 0|1> <out.txt>
 //       tokens_to_text (src/nemo-ggml.cpp:1556-1583) over timed_token{token, frame} pairs with the file's vocabulary.
 #include "nemo-ggml.h"
@@ -217,6 +218,7 @@ static int run_offline(int argc, char** argv) {
     nemo_context* ctx = nemo_init_with_backend(argv[2], NEMO_BACKEND_CPU);
     if (!ctx) return 1;
     if (threads > 0) ggml_backend_cpu_set_n_threads(ctx->model.backend, threads);
+    if (argc > 7 && strcmp(argv[7], "-") != 0 && !nemo_set_language(ctx, argv[7])) return 3;
 
     // nemo_encode_audio's body (src/nemo-ggml.cpp:1690-1715): preprocessor over the whole utterance, then nemo_encode. (The
     // header declares it with a std::vector& parameter that has no definition, src/nemo-ggml.h:370-373, so the two calls
@@ -242,12 +244,25 @@ static int run_offline(int argc, char** argv) {
     ggml_tensor* inp = ggml_new_tensor_3d(c0, GGML_TYPE_F32, n_mels, (int64_t)n_frames, 1);
     ggml_set_input(inp);
     ggml_tensor* enc = build_encoder(c0, inp, &ctx->model);
+    ggml_tensor* prompt = nullptr;
+    const int num_prompts = ctx->model.hparams.num_prompts;
+    if (num_prompts > 0) {  // what nemo_encode does at src/nemo-ggml.cpp:1630-1636 (its helpers are file-static)
+        prompt = ggml_new_tensor_3d(c0, GGML_TYPE_F32, num_prompts, enc->ne[1], enc->ne[2]);
+        ggml_set_input(prompt);
+        enc = build_prompt_fusion(c0, enc, prompt, &ctx->model);
+    }
     ggml_set_output(enc);
     ggml_cgraph* gf = ggml_new_graph_custom(c0, 16384, false);
     ggml_build_forward_expand(gf, enc);
     ggml_gallocr_t ga = ggml_gallocr_new(ggml_backend_get_default_buffer_type(ctx->model.backend));
     if (!ggml_gallocr_alloc_graph(ga, gf)) return 1;
     ggml_backend_tensor_set(inp, mel.data(), 0, mel.size() * sizeof(float));
+    if (prompt) {  // one-hot rows, fill_prompt_onehot src/nemo-ggml.cpp:1118-1130
+        std::vector<float> oh((size_t)ggml_nelements(prompt), 0.0f);
+        const int idx = (ctx->prompt_index >= 0 && ctx->prompt_index < num_prompts) ? ctx->prompt_index : 0;
+        for (int64_t r = 0; r < prompt->ne[1] * prompt->ne[2]; r++) oh[(size_t)r * num_prompts + idx] = 1.0f;
+        ggml_backend_tensor_set(prompt, oh.data(), 0, oh.size() * sizeof(float));
+    }
     ggml_backend_graph_compute(ctx->model.backend, gf);
     std::vector<float> out(ggml_nelements(enc));
     ggml_backend_tensor_get(enc, out.data(), 0, out.size() * sizeof(float));

@@ -24,11 +24,11 @@ import inputs  # noqa: E402
 GOLD = Path(__file__).resolve().parent
 
 
-def run(isa, gguf, pcm, prefix, secs):
+def run(isa, gguf, pcm, prefix, secs, lang=None):
     h = ROOT / "oracle" / "_ref" / isa / "ref_harness"
     if not h.exists():
         raise SystemExit(f"{h} missing: run `make -C oracle -j8` first")
-    r = subprocess.run([str(h), "offline", gguf, pcm, "8", str(prefix), str(secs)], check=True, stdout=subprocess.PIPE,
+    r = subprocess.run([str(h), "offline", gguf, pcm, "8", str(prefix), str(secs), lang or "-"], check=True, stdout=subprocess.PIPE,
                        stderr=subprocess.DEVNULL, text=True)
     info = json.loads(r.stdout.strip().splitlines()[-1])
     return info, {"enc": np.fromfile(f"{prefix}.enc.f32", np.float32).reshape(-1, 1024),
@@ -37,15 +37,17 @@ def run(isa, gguf, pcm, prefix, secs):
 
 def main():
     manifest = {}
-    for variant, seed, secs in inputs.OFFLINE_CASES:
-        gguf, pcm = inputs.gguf_path(variant), inputs.pcm_path(seed, secs)
-        info, out = run("avx2", gguf, pcm, inputs.TMP / "off_a", secs)
-        if variant != "f32dq":
-            _, o2 = run("avx512", gguf, pcm, inputs.TMP / "off_b", secs)
+    for variant, seed, secs, lang in inputs.OFFLINE_CASES:
+        gguf, pcm = inputs.offline_gguf(variant), inputs.pcm_path(seed, secs)
+        info, out = run("avx2", gguf, pcm, inputs.TMP / "off_a", secs, lang)
+        if variant == "q8_0":
+            _, o2 = run("avx512", gguf, pcm, inputs.TMP / "off_b", secs, lang)
             out.update({k + "_avx512": v for k, v in o2.items()})
-        name = f"offline_{variant}_s{seed}.npz"
+        if secs > 10.0:
+            out["enc"] = out["enc"][:: inputs.OFFLINE_ENC_STRIDE]
+        name = inputs.offline_name(variant, seed, lang)
         np.savez_compressed(GOLD / name, **out)
-        manifest[name] = {"variant": variant, "seed": seed, "seconds": secs, "mel_frames": info["mel_frames"], "enc_T": info["enc_T"],
+        manifest[name] = {"variant": variant, "seed": seed, "seconds": secs, "language": lang, "mel_frames": info["mel_frames"], "enc_T": info["enc_T"],
                           "tokens": info["tokens"]}
         print(name, manifest[name])
     (GOLD / "manifest_offline.json").write_text(json.dumps(manifest, indent=1) + "\n")

@@ -56,12 +56,26 @@ PROMPT_CASES = (
 )
 
 
-# offline path (nemo_encode, full-sequence attention, timed tokens): (variant, seed, seconds)
+# offline path (nemo_encode, full-sequence attention, timed tokens): (variant, seed, seconds, language);
+# "ml" = the multilingual F32 file (prompt fusion; language None = the loader's default prompt). The 30 s case (376 frames,
+# 751 relative positions) stores every 8th encoder frame.
 OFFLINE_CASES = (
-    ("f32dq", 41, 6.0),
-    ("f32dq", 42, 0.9),
-    ("q8_0", 41, 4.0),
+    ("f32dq", 41, 6.0, None),
+    ("f32dq", 42, 0.9, None),
+    ("q8_0", 41, 4.0, None),
+    ("ml", 41, 3.0, None),
+    ("ml", 41, 3.0, "de"),
+    ("f32dq", 44, 30.0, None),
 )
+OFFLINE_ENC_STRIDE = 8  # for utterances longer than 10 s
+
+
+def offline_gguf(variant: str) -> str:
+    return gguf_path("f32dq", multilingual=True) if variant == "ml" else gguf_path(variant)
+
+
+def offline_name(variant: str, seed: int, lang) -> str:
+    return f"offline_{variant}{'_' + lang if lang else ''}_s{seed}.npz"
 
 
 def gguf_path(variant: str, layers: int = TEST_LAYERS, blank_gain: float | None = None, multilingual: bool = False) -> str:
