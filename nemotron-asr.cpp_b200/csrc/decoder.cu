@@ -159,6 +159,11 @@ void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* 
 //      pending LSTM / joint.pred state of the streams in emit_list is recomputed: layer 0, layer 1, joint.pred, each
 //      followed by a barrier (every hidden unit of the previous one is needed); CTA j owns 4-5 hidden units (= the i,f,
 //      g,o gate rows of those units, src/nemo-ggml.cpp:601-618) and loops over the emitting streams in tiles of 8.
+// Window mode (DecodeBatch::W > 1, used by the offline path where one utterance is the whole batch): a blank leaves the
+// decoder state untouched, so the logits of the next W frames can all be formed with the same pending prediction; a round
+// evaluates W consecutive frames of the stream as W items, the argmax phase walks them in order up to the first non-blank
+// one (everything before it is a blank step, everything after it is discarded), and a round advances up to W frames instead
+// of one. Same steps, same arithmetic per step, same tokens and frame stamps as W = 1.
 // The loop ends when no stream has frames left. Counters rotate over three slots so that clearing the next round's slot
 // cannot race with a CTA still reading the previous one.
 constexpr int DK_TS = 8, DK_MAXU = 8, DK_MAXR = 8, DK_GROUP = 64;
@@ -168,8 +173,10 @@ struct DkSmem {
     float gs[DK_TS][4 * DK_MAXU];      // gate pre-activations / logits of the tile
     int sl[DK_TS], bq[DK_TS], rows[4 * DK_MAXU];
     float bias[DK_MAXR];               // joint.out bias of my rows
-    int act[DK_GROUP];                 // L: batch indices of the group's unfinished streams
+    int act[DK_GROUP];                 // L: item indices (stream * W + window offset) of the group's pending symbol steps
     int n_act;
+    float wbest[DK_GROUP], wsecond[DK_GROUP];  // A, window mode: merged (max, runner-up, index) of a stream's window items
+    int widx[DK_GROUP], wemit, wf;
 };
 static_assert(DK_GROUP * JOINT >= DK_TS * 2 * DEC, "the LSTM tile reuses the hid buffer");
 
@@ -329,8 +336,9 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
             if (sm.sl[q] < 0) return;
             s.pend_p[(size_t)sm.sl[q] * JOINT + u0 + r] = v;
             if (list) {  // the stream's next symbol step: hid = relu(joint.enc(frame fp) + new pending pred), my rows
-                const int b = sm.bq[q], fp = __ldcg(d.fp + b);
-                if (fp < d.nvalid[b]) d.hid[(size_t)b * JOINT + u0 + r] = fmaxf(d.e[((size_t)(b * d.T + fp)) * JOINT + u0 + r] + v, 0.0f);
+                const int b = sm.bq[q], fp = __ldcg(d.fp + b), nv = d.nvalid[b];
+                for (int wi = 0; wi < d.W && fp + wi < nv; wi++)
+                    d.hid[(size_t)(b * d.W + wi) * JOINT + u0 + r] = fmaxf(d.e[((size_t)(b * d.T + fp + wi)) * JOINT + u0 + r] + v, 0.0f);
             }
         });
     }
@@ -338,11 +346,12 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
 }
 
 // hid[b] = relu(joint.enc(frame fp) + pend_p[slot]) for one stream, by one warp (src/nemo-ggml.cpp:1215-1217)
-__device__ __forceinline__ void dk_stage_hid(const DecodeState& s, const DecodeBatch& d, int b, int fp, int slot, int lane) {
+// (item = b * W + window offset; W = 1: item = b)
+__device__ __forceinline__ void dk_stage_hid(const DecodeState& s, const DecodeBatch& d, int item, int b, int fp, int slot, int lane) {
     for (int k = 4 * lane; k < JOINT; k += 128) {
         const float4 e = *reinterpret_cast<const float4*>(d.e + ((size_t)(b * d.T + fp)) * JOINT + k);
         const float4 p = __ldcg(reinterpret_cast<const float4*>(s.pend_p + (size_t)slot * JOINT + k));
-        *reinterpret_cast<float4*>(d.hid + (size_t)b * JOINT + k) =
+        *reinterpret_cast<float4*>(d.hid + (size_t)item * JOINT + k) =
             make_float4(fmaxf(e.x + p.x, 0.f), fmaxf(e.y + p.y, 0.f), fmaxf(e.z + p.z, 0.f), fmaxf(e.w + p.w, 0.f));
     }
 }
@@ -376,8 +385,9 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
         d.min_margin[b] = __int_as_float(0x7f7f7f7f);
     }
     // hid of every stream's first symbol step (fp = 0, pending pred from the previous chunk); the owner warp of stream b
+    const int W = d.W;
     for (int b = cta * 8 + warp; b < d.B; b += G * 8)
-        if (d.nvalid[b] > 0) dk_stage_hid(s, d, b, 0, d.slot[b], lane);
+        for (int wi = 0; wi < W && wi < d.nvalid[b]; wi++) dk_stage_hid(s, d, b * W + wi, b, wi, d.slot[b], lane);
     grid_barrier(d.bar, phase);
 
     float4* partial = reinterpret_cast<float4*>(d.partial);
@@ -396,15 +406,15 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
         }
         // ---- L: logits of my rows; the hid vectors of up to 64 unfinished streams are staged at once ----
         if (nr > 0) {
-            for (int g0 = 0; g0 < d.B; g0 += DK_GROUP) {
+            for (int g0 = 0; g0 < d.B * W; g0 += DK_GROUP) {
                 __syncthreads();
-                if (warp == 0) {  // compact the group's unfinished streams (ballot scan)
+                if (warp == 0) {  // compact the group's pending items (ballot scan)
                     int n = 0;
                     for (int c = 0; c < DK_GROUP; c += 32) {
-                        const int b = g0 + c + lane;
-                        const bool on = b < d.B && __ldcg(d.fp + b) < d.nvalid[b];
+                        const int it = g0 + c + lane, b = it / W, wi = it - b * W;
+                        const bool on = it < d.B * W && __ldcg(d.fp + b) + wi < d.nvalid[b];
                         const unsigned m = __ballot_sync(0xffffffffu, on);
-                        if (on) sm.act[n + __popc(m & ((1u << lane) - 1u))] = b;
+                        if (on) sm.act[n + __popc(m & ((1u << lane) - 1u))] = it;
                         n += __popc(m);
                     }
                     if (lane == 0) sm.n_act = n;
@@ -463,6 +473,74 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
         grid_barrier(d.bar, phase);
         unsigned long long t2 = tr ? now() : 0;
         // ---- A: merge the partial maxima, state machine, next hid; one warp per stream ----
+        if (W > 1) {
+            // window mode: CTA 0 walks the streams; its 8 warps merge the window's items, thread 0 runs the state machine over them in frame order
+            for (int b = 0; cta == 0 && b < d.B; b++) {
+                const int nvalid = d.nvalid[b], slot = d.slot[b];
+                const int fp = __ldcg(d.fp + b);
+                if (fp >= nvalid) continue;  // uniform
+                const int nw = min(W, nvalid - fp);
+                for (int wi = warp; wi < nw; wi += 8) {
+                    float best = -INFINITY, second = -INFINITY;
+                    int besti = 0x7fffffff;
+                    for (int c = lane; c < n_part; c += 32) {
+                        const float4 p = __ldcg(partial + (size_t)(b * W + wi) * G + c);
+                        const int pi = __float_as_int(p.z);
+                        if (p.x > best || (p.x == best && pi < besti)) { second = fmaxf(best, p.y); best = p.x; besti = pi; }
+                        else second = fmaxf(second, p.x);
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {
+                        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+                        const float os = __shfl_xor_sync(0xffffffffu, second, o);
+                        const int oi = __shfl_xor_sync(0xffffffffu, besti, o);
+                        if (ob > best || (ob == best && oi < besti)) { second = fmaxf(best, os); best = ob; besti = oi; }
+                        else second = fmaxf(second, ob);
+                    }
+                    if (lane == 0) { sm.wbest[wi] = best; sm.wsecond[wi] = second; sm.widx[wi] = besti; }
+                }
+                __syncthreads();
+                if (t == 0) {
+                    int f = fp, sy = d.sym[b], emit = 0;
+                    float mg = d.min_margin[b];
+                    for (int wi = 0; wi < nw; wi++) {
+                        mg = fminf(mg, sm.wbest[wi] - sm.wsecond[wi]);
+                        const int besti = sm.widx[wi];
+                        if (besti == BLANK) {
+                            f++;
+                            sy = 0;
+                        } else {
+                            const int n = d.tok_cnt[b];
+                            d.tok_out[(size_t)b * d.T * MAX_SYMBOLS + n] = besti | (f << 16);
+                            d.tok_cnt[b] = n + 1;
+                            s.prev[slot] = besti;
+                            emit = 1;
+                            d.emit_list[atomicAdd(emit_count + cs, 1)] = b;
+                            sy++;
+                            if (sy >= MAX_SYMBOLS) { f++; sy = 0; }
+                            break;  // the later items of the window were formed with the old prediction: discarded
+                        }
+                    }
+                    d.min_margin[b] = mg;
+                    d.fp[b] = f;
+                    d.sym[b] = sy;
+                    if (f < nvalid) atomicAdd(unfinished + cs, 1);
+                    sm.wemit = emit;
+                    sm.wf = f;
+                }
+                __syncthreads();
+                const int emit = sm.wemit, f = sm.wf;
+                if (emit) {  // commit the pending LSTM state; the new pending state and the next window's hid follow in phase E
+                    for (int i = t; i < 2 * DEC; i += 256) {
+                        s.h[(size_t)slot * 2 * DEC + i] = __ldcg(s.pend_h + (size_t)slot * 2 * DEC + i);
+                        s.c[(size_t)slot * 2 * DEC + i] = __ldcg(s.pend_c + (size_t)slot * 2 * DEC + i);
+                    }
+                } else {  // all blank: same pending pred, next window
+                    for (int wi = warp; wi < W && f + wi < nvalid; wi += 8) dk_stage_hid(s, d, b * W + wi, b, f + wi, slot, lane);
+                }
+                __syncthreads();
+            }
+        } else
         for (int b = cta * 8 + warp; b < d.B; b += G * 8) {
             const int nvalid = d.nvalid[b], slot = d.slot[b];
             const int fp = __ldcg(d.fp + b);
@@ -512,7 +590,7 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                     s.c[(size_t)slot * 2 * DEC + i] = __ldcg(s.pend_c + (size_t)slot * 2 * DEC + i);
                 }
             } else if (f < nvalid) {
-                dk_stage_hid(s, d, b, f, slot, lane);  // blank: same pending pred, next frame
+                dk_stage_hid(s, d, b, b, f, slot, lane);  // blank: same pending pred, next frame
             }
         }
         unsigned long long t3 = tr ? now() : 0;

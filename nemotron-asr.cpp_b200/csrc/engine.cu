@@ -593,7 +593,7 @@ ModeCtx* get_mode(nb200_model* m, int rc) {
     return r;
 }
 
-DecodeBatch decode_batch(nb200_model* m, int B, int T) {
+DecodeBatch decode_batch(nb200_model* m, int B, int T, int W = 1) {
     DecodeBatch d{};
     d.e = m->ws_e;
     d.slot = m->ws_meta + 0 * m->cap_B;
@@ -611,6 +611,7 @@ DecodeBatch decode_batch(nb200_model* m, int B, int T) {
     d.max_rounds = T * (MAX_SYMBOLS + 1) + 2;
     d.B = B;
     d.T = T;
+    d.W = W;
     return d;
 }
 
@@ -1623,7 +1624,11 @@ int nb200_encode_audio(nb200_model* m, const int16_t* pcm, int n_samples, int32_
         CUDA_CHECK(cudaMemcpyAsync(enc_out, enc, (size_t)T * D_MODEL * sizeof(float), cudaMemcpyDeviceToHost, st));
     }
     enqueue_joint_enc(m, enc, T);
-    launch_decode_chunk(st, m->dec, m->dstate, decode_batch(m, 1, T));  // greedy_decode (src/nemo-ggml.cpp:1233-1380): same rounds, fresh state
+    // greedy_decode (src/nemo-ggml.cpp:1233-1380) from the fresh state; one utterance is the whole batch, so a round evaluates a
+    // window of consecutive frames (decoder.cu, window mode): blank runs cost one round per window instead of one per frame
+    static const int win_env = getenv("NB200_OFFLINE_WINDOW") ? atoi(getenv("NB200_OFFLINE_WINDOW")) : 0;
+    const int win = std::max(1, std::min(win_env > 0 ? win_env : 32, std::min(capB, 64)));
+    launch_decode_chunk(st, m->dec, m->dstate, decode_batch(m, 1, T, win));
     int counters[8], n_tok = 0;
     CUDA_CHECK(cudaMemcpyAsync(counters, m->ws_unfinished + 6, sizeof(counters), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaMemcpyAsync(&n_tok, m->ws_tokcnt, sizeof(int), cudaMemcpyDeviceToHost, st));

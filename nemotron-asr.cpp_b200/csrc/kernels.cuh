@@ -136,8 +136,9 @@ struct DecodeBatch {           // per batched step
     unsigned* bar;             // = counters + 8: arrival counter of the grid-wide barriers
     int* emit_list;            // [B] batch indices of the streams that emitted in the current round
     float* partial;            // [B][G][4] per-CTA (max, runner-up, index) of the current round's logits
-    float* hid;                // [B][640] joint hidden vector of every stream's next symbol step
+    float* hid;                // [B*W][640] joint hidden vector of every stream's next symbol step(s)
     int B, T, max_rounds;
+    int W;                     // frames evaluated per stream and round (1 = one symbol step per round; > 1: window mode, B * W <= 64 items)
 };
 struct DecodeWeights {
     const float* embed;        // [1025][640]
