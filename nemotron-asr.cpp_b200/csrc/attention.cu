@@ -958,11 +958,233 @@ __global__ void __launch_bounds__(256) attention_full_kernel(AttnFullArgs a) {
     }
 }
 
+// ---- offline path, tensor-core version: 16 query rows of one head per CTA, mma.sync.m16n8k16 for the three products ---------
+// Per tile of 64 keys: K rows and the 79 position rows the 16 x 64 (query, key) pairs need are staged with cp.async; content
+// scores (Q + u) K^T and position scores (Q + v) P^T run on the tensor cores (fp16 operands, fp32 accumulate, the fragments
+// of the streaming kernel above); the rel-shift is the index i - jj + 63 into the tile's position scores. The whole score row
+// (<= 512 keys, fp32) stays in shared memory for the softmax; P (fp16, unnormalised) . V follows tile by tile with the
+// accumulators in registers. The CUDA-core kernel above is kept as the checker (NB200_ATTN_FULL_SIMT=1).
+struct AfSmem {
+    static constexpr int KT = 64, PROWS = 80;
+    static constexpr int S_LD = 516, P2_LD = 84, PR_PITCH = 1040;  // floats, floats, bytes (1040 / 16 odd: conflict-free ldmatrix)
+    static constexpr int QU_OFF = 0;
+    static constexpr int QV_OFF = QU_OFF + 16 * ROWB;
+    static constexpr int KV_OFF = QV_OFF + 16 * ROWB;
+    static constexpr int POS_OFF = KV_OFF + KT * ROWB;
+    static constexpr int S_OFF = POS_OFF + PROWS * ROWB;
+    static constexpr int P2_OFF = S_OFF + 16 * S_LD * 4;
+    static constexpr int INV_OFF = P2_OFF + 16 * P2_LD * 4;
+    static constexpr int TOTAL = INV_OFF + 16 * 4;
+    static constexpr int PR_OFF = POS_OFF;  // probabilities (fp16) over the position rows, dead after the scores
+    static constexpr int CX_OFF = S_OFF;    // fp32 context over the score rows, dead after the softmax
+    static_assert(16 * PR_PITCH <= PROWS * ROWB, "probabilities must fit the position area");
+    static_assert(16 * CX_LD * 4 <= 16 * S_LD * 4, "context staging must fit the score area");
+};
+
+__global__ void __launch_bounds__(128) attention_full_mma_kernel(AttnFullArgs a) {
+    pdl_prologue();
+    extern __shared__ __align__(16) uint8_t smem[];
+    using L = AfSmem;
+    const int T = a.T, h = blockIdx.y, i0 = blockIdx.x * 16;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+    const __half* qkv = a.qkv + h * D_HEAD;
+    const __half* pbase = a.pos + h * D_HEAD;
+    const uint32_t sb = s_u32(smem);
+    const uint4 z4 = make_uint4(0, 0, 0, 0);
+    float* S = reinterpret_cast<float*>(smem + L::S_OFF);
+    float* P2 = reinterpret_cast<float*>(smem + L::P2_OFF);
+    float* inv = reinterpret_cast<float*>(smem + L::INV_OFF);
+
+    // Q + u, Q + v (fp32 add, one rounding to fp16); rows >= T are zero
+    for (int idx = tid; idx < 16 * 16; idx += 128) {
+        const int r = idx >> 4, c = idx & 15;
+        uint4 ou = z4, ov = z4;
+        if (i0 + r < T) {
+            const uint4 q8 = *reinterpret_cast<const uint4*>(qkv + (size_t)(i0 + r) * (3 * D_MODEL) + c * 8);
+            const __half2* qh = reinterpret_cast<const __half2*>(&q8);
+            const float4 u0 = *reinterpret_cast<const float4*>(a.bias_u + h * D_HEAD + c * 8), u1 = *reinterpret_cast<const float4*>(a.bias_u + h * D_HEAD + c * 8 + 4);
+            const float4 v0 = *reinterpret_cast<const float4*>(a.bias_v + h * D_HEAD + c * 8), v1 = *reinterpret_cast<const float4*>(a.bias_v + h * D_HEAD + c * 8 + 4);
+            const float uu[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+            const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+            __half2 hu[4], hv[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const float2 q2 = __half22float2(qh[e]);
+                hu[e] = __floats2half2_rn(q2.x + uu[2 * e], q2.y + uu[2 * e + 1]);
+                hv[e] = __floats2half2_rn(q2.x + vv[2 * e], q2.y + vv[2 * e + 1]);
+            }
+            ou = *reinterpret_cast<uint4*>(hu);
+            ov = *reinterpret_cast<uint4*>(hv);
+        }
+        *reinterpret_cast<uint4*>(smem + L::QU_OFF + r * ROWB + c * 16) = ou;
+        *reinterpret_cast<uint4*>(smem + L::QV_OFF + r * ROWB + c * 16) = ov;
+    }
+    const float scale = 1.0f / sqrtf((float)D_HEAD);
+    const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_col = (lane >> 4) * 16;
+    const int b_row = lane & 7, b_col = (lane >> 3) * 16;
+    const int n_tiles = (T + L::KT - 1) / L::KT;
+
+    // ---- scores ----
+    for (int kt = 0; kt < n_tiles; kt++) {
+        const int j0 = kt * L::KT;
+        __syncthreads();  // the previous tile's K / position rows and P2 have been consumed
+        for (int idx = tid; idx < L::KT * 16; idx += 128) {
+            const int r = idx >> 4, c = idx & 15, j = j0 + r;
+            if (j < T) cp_async16(sb + L::KV_OFF + r * ROWB + c * 16, qkv + (size_t)j * (3 * D_MODEL) + D_MODEL + c * 8);
+            else *reinterpret_cast<uint4*>(smem + L::KV_OFF + r * ROWB + c * 16) = z4;
+        }
+        // pair (query i0 + i, key j0 + jj) uses position (i0 + i) - (j0 + jj): table row rlo + (i - jj + 63)
+        const int rlo = i0 - j0 - (L::KT - 1) + T - 1;
+        for (int idx = tid; idx < L::PROWS * 16; idx += 128) {
+            const int r = idx >> 4, c = idx & 15, row = rlo + r;
+            if (row >= 0 && row < 2 * T - 1) cp_async16(sb + L::POS_OFF + r * ROWB + c * 16, pbase + (size_t)row * D_MODEL + c * 8);
+            else *reinterpret_cast<uint4*>(smem + L::POS_OFF + r * ROWB + c * 16) = z4;
+        }
+        cp_commit();
+        cp_wait<0>();
+        __syncthreads();
+        // content scores: 8 key tiles of 8, two per warp -> S[i][j0 + jj] (raw)
+        for (int tile = warp; tile < L::KT / 8; tile += 4) {
+            const int n0 = 8 * tile;
+            const uint32_t qa = sb + L::QU_OFF + a_row * ROWB + a_col;
+            const uint32_t kb = sb + L::KV_OFF + (n0 + b_row) * ROWB + b_col;
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) {
+                uint32_t bf[4], a0[4], a1[4];
+                ldsm_x4(bf, kb + ks * 64);
+                ldsm_x4(a0, qa + ks * 64);
+                ldsm_x4(a1, qa + ks * 64 + 32);
+                mma_f16(acc, a0, bf[0], bf[1]);
+                mma_f16(acc, a1, bf[2], bf[3]);
+            }
+            *reinterpret_cast<float2*>(S + g * L::S_LD + j0 + n0 + 2 * t) = make_float2(acc[0], acc[1]);
+            *reinterpret_cast<float2*>(S + (g + 8) * L::S_LD + j0 + n0 + 2 * t) = make_float2(acc[2], acc[3]);
+        }
+        // position scores of the tile's 80 rows -> P2[i][r]
+        for (int tile = warp; tile < L::PROWS / 8; tile += 4) {
+            const int n0 = 8 * tile;
+            const uint32_t qa = sb + L::QV_OFF + a_row * ROWB + a_col;
+            const uint32_t kb = sb + L::POS_OFF + (n0 + b_row) * ROWB + b_col;
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) {
+                uint32_t bf[4], a0[4], a1[4];
+                ldsm_x4(bf, kb + ks * 64);
+                ldsm_x4(a0, qa + ks * 64);
+                ldsm_x4(a1, qa + ks * 64 + 32);
+                mma_f16(acc, a0, bf[0], bf[1]);
+                mma_f16(acc, a1, bf[2], bf[3]);
+            }
+            *reinterpret_cast<float2*>(P2 + g * L::P2_LD + n0 + 2 * t) = make_float2(acc[0], acc[1]);
+            *reinterpret_cast<float2*>(P2 + (g + 8) * L::P2_LD + n0 + 2 * t) = make_float2(acc[2], acc[3]);
+        }
+        __syncthreads();
+        // rel-shift by indexing, scale
+        for (int idx = tid; idx < 16 * L::KT; idx += 128) {
+            const int i = idx >> 6, jj = idx & 63;
+            S[i * L::S_LD + j0 + jj] = (S[i * L::S_LD + j0 + jj] + P2[i * L::P2_LD + i - jj + (L::KT - 1)]) * scale;
+        }
+    }
+    __syncthreads();
+    // ---- softmax over the T keys (fp32), one warp per 4 query rows -> fp16 probabilities (unnormalised), 1 / sum kept per row ----
+    const int kpad = n_tiles * L::KT;
+    for (int r = warp * 4; r < warp * 4 + 4; r++) {
+        __half* prow = reinterpret_cast<__half*>(smem + L::PR_OFF + r * L::PR_PITCH);
+        float mx = -INFINITY;
+        for (int j = lane; j < T; j += 32) mx = fmaxf(mx, S[r * L::S_LD + j]);
+        mx = warp_max(mx);
+        float sum = 0.0f;
+        for (int j = lane; j < kpad; j += 32) {
+            float e = 0.0f;
+            if (j < T) {
+                e = expf(S[r * L::S_LD + j] - mx);
+                sum += e;
+            }
+            prow[j] = __float2half_rn(e);
+        }
+        sum = warp_sum(sum);
+        if (lane == 0) inv[r] = 1.0f / sum;
+    }
+    // ---- context: warp w owns features [32 w, 32 w + 32) ----
+    float acc[2][2][4];
+#pragma unroll
+    for (int x = 0; x < 2; x++)
+#pragma unroll
+        for (int y = 0; y < 2; y++)
+#pragma unroll
+            for (int e = 0; e < 4; e++) acc[x][y][e] = 0.0f;
+    for (int kt = 0; kt < n_tiles; kt++) {
+        const int j0 = kt * L::KT;
+        __syncthreads();  // first pass: probabilities complete, K tile consumed; later: previous V tile consumed
+        for (int idx = tid; idx < L::KT * 16; idx += 128) {
+            const int r = idx >> 4, c = idx & 15, j = j0 + r;
+            if (j < T) cp_async16(sb + L::KV_OFF + r * ROWB + c * 16, qkv + (size_t)j * (3 * D_MODEL) + 2 * D_MODEL + c * 8);
+            else *reinterpret_cast<uint4*>(smem + L::KV_OFF + r * ROWB + c * 16) = z4;
+        }
+        cp_commit();
+        cp_wait<0>();
+        __syncthreads();
+        const uint32_t pa = sb + L::PR_OFF + a_row * L::PR_PITCH + a_col + j0 * 2;
+#pragma unroll
+        for (int ks = 0; ks < L::KT / 16; ks++) {
+            uint32_t af[4];
+            ldsm_x4(af, pa + ks * 32);
+#pragma unroll
+            for (int x = 0; x < 2; x++) {
+                const uint32_t vb = sb + L::KV_OFF + ((lane & 7) + ((lane >> 3) & 1) * 8 + ks * 16) * ROWB + (32 * warp + 16 * x + (lane >> 4) * 8) * 2;
+                uint32_t bf[4];
+                ldsm_x4_t(bf, vb);
+                mma_f16(acc[x][0], af, bf[0], bf[1]);
+                mma_f16(acc[x][1], af, bf[2], bf[3]);
+            }
+        }
+    }
+    __syncthreads();  // every warp is done with the score rows' neighbours (probabilities alias the position area, not S): S is free
+    float* Cx = reinterpret_cast<float*>(smem + L::CX_OFF);
+#pragma unroll
+    for (int x = 0; x < 2; x++) {
+        const int f0 = 32 * warp + 16 * x;
+        *reinterpret_cast<float2*>(Cx + g * CX_LD + f0 + 2 * t) = make_float2(acc[x][0][0], acc[x][0][1]);
+        *reinterpret_cast<float2*>(Cx + (g + 8) * CX_LD + f0 + 2 * t) = make_float2(acc[x][0][2], acc[x][0][3]);
+        *reinterpret_cast<float2*>(Cx + g * CX_LD + f0 + 8 + 2 * t) = make_float2(acc[x][1][0], acc[x][1][1]);
+        *reinterpret_cast<float2*>(Cx + (g + 8) * CX_LD + f0 + 8 + 2 * t) = make_float2(acc[x][1][2], acc[x][1][3]);
+    }
+    __syncthreads();
+    for (int idx = tid; idx < 16 * (D_HEAD / 4); idx += 128) {  // a warp = one row: the 8-lane groups of group8_max are 32 features
+        const int i = idx >> 5, d = (idx & 31) * 4;
+        const float s1 = inv[i];
+        float4 v = *reinterpret_cast<const float4*>(Cx + i * CX_LD + d);
+        v = make_float4(v.x * s1, v.y * s1, v.z * s1, v.w * s1);
+        if (a.act_quant) {
+            const float amax = group8_max(fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+            v.x = fake_quant(v.x, amax);
+            v.y = fake_quant(v.y, amax);
+            v.z = fake_quant(v.z, amax);
+            v.w = fake_quant(v.w, amax);
+        }
+        if (i0 + i < T) {
+            const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
+            uint2 u;
+            u.x = *reinterpret_cast<const uint32_t*>(&lo);
+            u.y = *reinterpret_cast<const uint32_t*>(&hi);
+            *reinterpret_cast<uint2*>(a.out + (size_t)(i0 + i) * D_MODEL + h * D_HEAD + d) = u;
+        }
+    }
+}
+
 void launch_attention_full(cudaStream_t st, const AttnFullArgs& a) {
     if (a.T <= 0) return;
     if (a.T > ATTN_FULL_MAX_T) throw Error("offline attention: more than 512 encoder frames");
+    static const bool simt = getenv("NB200_ATTN_FULL_SIMT") != nullptr;
     ProfScope ps(st, "attention_full", 6.0 * N_HEADS * (double)a.T * a.T * D_HEAD, (double)a.T * D_MODEL * 2 * 6);
-    launch_k(attention_full_kernel, dim3(dim3(cdiv(a.T, AF_QB), N_HEADS)), dim3(256), 0, st, a);
+    if (simt) {
+        launch_k(attention_full_kernel, dim3(dim3(cdiv(a.T, AF_QB), N_HEADS)), dim3(256), 0, st, a);
+    } else {
+        static PerDeviceOnce once;
+        if (once.first()) CUDA_CHECK(cudaFuncSetAttribute(attention_full_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AfSmem::TOTAL));
+        launch_k(attention_full_mma_kernel, dim3(dim3(cdiv(a.T, 16), N_HEADS)), dim3(128), (size_t)AfSmem::TOTAL, st, a);
+    }
     NB_KERNEL_CHECK();
 }
 
