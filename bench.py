@@ -249,7 +249,11 @@ def main():
     value = audio_all / (ms_max * 1e-3)
     launches = st1.kernel_launches - st0.kernel_launches
     frames = st1.frames - st0.frames
-    steps_per_frame = (st1.decode_rounds - st0.decode_rounds) / max(a.steps * T, 1)
+    # symbol steps per frame: every decoded frame costs its blank step plus one step per emitted token (MAX_SYMBOLS cap aside);
+    # a decode ROUND evaluates `decode window` consecutive frames of every stream at once, so rounds per chunk can be < T
+    tokens = st1.tokens - st0.tokens
+    steps_per_frame = (frames + tokens) / max(frames, 1)
+    rounds_per_step = (st1.decode_rounds - st0.decode_rounds) / max(a.steps, 1)
 
     # ---- leg 2: end to end through feed / step / poll ------------------------------------------------------
     # The server-loop order: while the GPU runs step k the host stages the audio of step k+1 (nb200_step_begin /
@@ -348,7 +352,8 @@ def main():
             "dtype": "f16 operands, f32 accumulate (Q8_0 weights dequantised; ggml's int8 activation re-quantisation emulated)",
             "data": "synthetic", "config": config, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "latency_ms": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)), "what": "feed+step+poll of one batched chunk, in sequence (wall clock)"},
-            "decode_steps_per_frame": steps_per_frame, "frames_decoded": int(frames), "streams_total": a.streams * world,
+            "decode_steps_per_frame": steps_per_frame, "decode_rounds_per_step": rounds_per_step, "tokens_emitted": int(tokens),
+            "frames_decoded": int(frames), "streams_total": a.streams * world,
             "realtime_streams_supported": value, "roofline": roofline, "kernels": kernels}
 
     if world == 1 and not a.no_cpu_baseline:

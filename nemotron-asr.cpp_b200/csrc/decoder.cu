@@ -201,14 +201,17 @@ __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& phase) {
 // once per call, whatever the number of rows (one row per warp would re-read the whole stream tile from shared memory for
 // every row: measured, that made shared-memory bandwidth the limit of the round). On return the lanes with kg == 0 hold
 // v[i][j] = wr[i] . xs[2 sg + j].
-template <int K, int LD, int R>
+// UNROLL k-steps are in flight at once: with the weights in L2 (the LSTM / joint.pred rows of phase E) the loop is bound by
+// that latency, not by bandwidth, so E asks for 10 (30 independent 16-byte loads per lane); the logits phase reads its rows
+// from shared memory and keeps 4.
+template <int K, int LD, int R, int UNROLL = 4>
 __device__ __forceinline__ void dk_block(const float* const (&wr)[R], int n, const float* xs, float (&v)[R][2]) {
     const int lane = threadIdx.x & 31, kg = lane & 7, sg = lane >> 3;
     const float* x0 = xs + (size_t)(2 * sg) * LD + 4 * kg;
     const float* x1 = x0 + LD;
 #pragma unroll
     for (int i = 0; i < R; i++) v[i][0] = v[i][1] = 0.0f;
-#pragma unroll 4
+#pragma unroll UNROLL
     for (int k = 0; k < K; k += 32) {
         const float4 a = *reinterpret_cast<const float4*>(x0 + k), c = *reinterpret_cast<const float4*>(x1 + k);
 #pragma unroll
@@ -255,7 +258,7 @@ __device__ __forceinline__ void dk_rows(const float* __restrict__ W, const float
     }
     if (n == 0) return;
     float v[3][2];
-    dk_block<K, LD, 3>(wr, n, xs, v);
+    dk_block<K, LD, 3, 10>(wr, n, xs, v);
     if ((lane & 7) == 0) {
 #pragma unroll
         for (int i = 0; i < 3; i++) {
@@ -474,8 +477,8 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
         unsigned long long t2 = tr ? now() : 0;
         // ---- A: merge the partial maxima, state machine, next hid; one warp per stream ----
         if (W > 1) {
-            // window mode: CTA 0 walks the streams; its 8 warps merge the window's items, thread 0 runs the state machine over them in frame order
-            for (int b = 0; cta == 0 && b < d.B; b++) {
+            // window mode: a CTA per stream; its 8 warps merge the window's items, thread 0 runs the state machine over them in frame order
+            for (int b = cta; b < d.B; b += G) {
                 const int nvalid = d.nvalid[b], slot = d.slot[b];
                 const int fp = __ldcg(d.fp + b);
                 if (fp >= nvalid) continue;  // uniform

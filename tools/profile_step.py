@@ -38,7 +38,7 @@ def main():
         n = m.step()
         st = m.stats()
         print(f"step {k}: items={n} gpu_ms={st.last_step_gpu_ms:.3f} frontend={st.last_frontend_ms:.3f} encoder={st.last_encoder_ms:.3f} "
-              f"decoder={st.last_decoder_ms:.3f} launches={st.kernel_launches} rounds={st.decode_rounds}")
+              f"decoder={st.last_decoder_ms:.3f} launches={st.kernel_launches} rounds={st.decode_rounds} frames={st.frames} tokens={st.tokens}")
     m.close()
 
 
