@@ -243,17 +243,17 @@ __device__ __forceinline__ void dk_block(const float* const (&wr)[R], int n, con
 }
 
 // rows[0..nr) of W (K floats each, row-major) times the DK_TS staged vectors xs[q][0..K): warp w takes rows w, w+8, w+16;
-// out(q, r, value + bias[row]).
+// out(q, r, value + bias[row]). wsm (optional): the same rows already staged in shared memory, row r at wsm + r * K.
 template <int K, int LD, typename Out>
 __device__ __forceinline__ void dk_rows(const float* __restrict__ W, const float* __restrict__ bias, const float* xs, int nr,
-                                        const int* rows, Out&& out) {
+                                        const int* rows, Out&& out, const float* wsm = nullptr) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, sg = lane >> 3;
     const float* wr[3];
     int n = 0;
 #pragma unroll
     for (int i = 0; i < 3; i++) {
         const int r = warp + 8 * i;
-        wr[i] = W + (size_t)rows[r < nr ? r : 0] * K;
+        wr[i] = wsm ? wsm + (size_t)(r < nr ? r : 0) * K : W + (size_t)rows[r < nr ? r : 0] * K;
         if (r < nr) n = i + 1;
     }
     if (n == 0) return;
@@ -272,15 +272,34 @@ __device__ __forceinline__ void dk_rows(const float* __restrict__ W, const float
     }
 }
 
+// cp.async copy of rows[0..nrows) of W (K floats each) to dst[r * K ..] by the whole CTA, one commit group
+__device__ __forceinline__ void dk_stage_rows(float* dst, const float* __restrict__ W, int K, const int* rows, int nrows) {
+    const int per_row = K / 4;
+    for (int i = threadIdx.x; i < nrows * per_row; i += 256) {
+        const int r = i / per_row, c = i - r * per_row;
+        const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst + (size_t)r * K + 4 * c);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(W + (size_t)rows[r] * K + 4 * c) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void dk_stage_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
 // Recomputes pend_h / pend_c / pend_p of the E streams listed in `list` (batch indices; nullptr = 0..E-1).
+// The CTA's weight rows of a phase (16-20 gate rows x 1280 floats = 100 KB per LSTM layer, 4-5 x 640 for joint.pred) are brought
+// into the idle part of the hid buffer with cp.async by all 256 threads (bandwidth- instead of latency-bound), the next
+// phase's rows while this phase finishes its gate math and waits at the grid barrier.
 __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d, DkSmem& sm, const int* list, int E,
                                unsigned& phase) {
     const int cta = blockIdx.x, G = gridDim.x, t = threadIdx.x;
     const int base = DEC / G, rem = DEC % G;
     const int nu = base + (cta < rem ? 1 : 0), u0 = cta * base + min(cta, rem);  // my hidden units [u0, u0 + nu)
+    // behind the input tile: room for 24 rows x 1280 floats (nu <= 5 on 148 SMs needs 20); otherwise the rows are read from L2
+    float* wsm = 4 * nu * 2 * DEC <= DK_GROUP * JOINT - DK_TS * 2 * DEC ? sm.xs + DK_TS * 2 * DEC : nullptr;
+    __syncthreads();
+    if (t < 4 * nu) sm.rows[t] = (t / nu) * DEC + u0 + (t % nu);  // the same gate rows in both layers; rows[0..nu) = u0.. are also joint.pred's
+    __syncthreads();
+    if (wsm) dk_stage_rows(wsm, w.wcat[0], 2 * DEC, sm.rows, 4 * nu);
     for (int layer = 0; layer < 2; layer++) {
-        __syncthreads();
-        if (t < 4 * nu) sm.rows[t] = (t / nu) * DEC + u0 + (t % nu);
         for (int e0 = 0; e0 < E; e0 += DK_TS) {
             __syncthreads();
             if (t < DK_TS) {
@@ -301,9 +320,14 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
                 }
                 *reinterpret_cast<float4*>(&sm.xs[q * 2 * DEC + k]) = v;
             }
+            dk_stage_wait();  // this layer's rows (requested before the previous barrier), my copies ...
+            __syncthreads();  // ... and everyone's, and the input tile
+            dk_rows<2 * DEC, 2 * DEC>(w.wcat[layer], w.bcat[layer], sm.xs, 4 * nu, sm.rows, [&](int q, int r, float v) { sm.gs[q][r] = v; }, wsm);
             __syncthreads();
-            dk_rows<2 * DEC, 2 * DEC>(w.wcat[layer], w.bcat[layer], sm.xs, 4 * nu, sm.rows, [&](int q, int r, float v) { sm.gs[q][r] = v; });
-            __syncthreads();
+            if (wsm && e0 + DK_TS >= E) {  // last tile: the rows are dead, fetch the next phase's while the gates and the barrier run
+                if (layer == 0) dk_stage_rows(wsm, w.wcat[1], 2 * DEC, sm.rows, 4 * nu);
+                else dk_stage_rows(wsm, w.wpred, DEC, sm.rows, nu);
+            }
             if (t < DK_TS * nu) {
                 const int q = t / nu, ui = t % nu, slot = sm.sl[q];
                 if (slot >= 0) {
@@ -334,6 +358,7 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
             if (slot >= 0) v = __ldcg(reinterpret_cast<const float4*>(s.pend_h + (size_t)slot * 2 * DEC + DEC + k));
             *reinterpret_cast<float4*>(&sm.xs[q * 2 * DEC + k]) = v;
         }
+        dk_stage_wait();
         __syncthreads();
         dk_rows<DEC, 2 * DEC>(w.wpred, w.bpred, sm.xs, nu, sm.rows, [&](int q, int r, float v) {
             if (sm.sl[q] < 0) return;
@@ -343,7 +368,7 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
                 for (int wi = 0; wi < d.W && fp + wi < nv; wi++)
                     d.hid[(size_t)(b * d.W + wi) * JOINT + u0 + r] = fmaxf(d.e[((size_t)(b * d.T + fp + wi)) * JOINT + u0 + r] + v, 0.0f);
             }
-        });
+        }, wsm);
     }
     grid_barrier(d.bar, phase);
 }
