@@ -468,7 +468,30 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                 }
                 __syncthreads();
                 unsigned long long u1 = tr ? now() : 0;
-                if (8 * warp < n_act) {  // warp w: streams 8w .. 8w+7 of the group, all of my rows
+                if (n_act <= DK_TS) {
+                    // few pending items (the tail of a chunk, or a batch of a few streams): a warp per row instead of one warp for
+                    // all rows; same per-row arithmetic, rows merged in index order like below
+                    if (warp < nr) {
+                        const float* w1[1] = {&sm.wrow[warp][0]};
+                        float v1[1][2];
+                        dk_block<JOINT, JOINT, 1>(w1, 1, sm.xs, v1);
+                        if ((lane & 7) == 0) {
+                            sm.gs[2 * (lane >> 3)][warp] = v1[0][0] + sm.bias[warp];
+                            sm.gs[2 * (lane >> 3) + 1][warp] = v1[0][1] + sm.bias[warp];
+                        }
+                    }
+                    __syncthreads();
+                    if (t < n_act) {
+                        float best = -INFINITY, second = -INFINITY;
+                        int besti = 0;
+                        for (int i = 0; i < nr; i++) {
+                            const float x = sm.gs[t][i];
+                            if (x > best) { second = best; best = x; besti = v0 + i; }
+                            else if (x > second) second = x;
+                        }
+                        partial[(size_t)sm.act[t] * G + cta] = make_float4(best, second, __int_as_float(besti), 0.0f);
+                    }
+                } else if (8 * warp < n_act) {  // warp w: streams 8w .. 8w+7 of the group, all of my rows
                     const float* wr[DK_MAXR];
 #pragma unroll
                     for (int i = 0; i < DK_MAXR; i++) wr[i] = &sm.wrow[i < nr ? i : 0][0];
