@@ -367,6 +367,44 @@ def test_offline_edge_cases(nb, model_f32):
         model_f32.encode_audio(pcm)  # 20 s = 251 frames > 8 streams * 14
 
 
+def test_decode_window_invariance(nb, model_f32, gguf_f32):
+    """The decode kernel's window mode (W frames of a stream per round) must not change a single token or frame stamp: the
+    same two streams (one per latency mode, token-heavy random decoder) run in fresh processes at NB200_DECODE_WINDOW = 1
+    (one symbol step per round) and 4, and here at the default (2)."""
+    import json
+    import subprocess
+    import sys
+    code = (
+        "import sys, json\n"
+        "sys.path[:0] = %r\n"
+        "import inputs, nb200\n"
+        "m = nb200.Model(%r, 0, 4)\n"
+        "out = []\n"
+        "for rc, seed, secs in ((13, 61, 5.0), (6, 62, 3.0)):\n"
+        "    s = m.stream(rc)\n"
+        "    s.process_incremental(inputs.pcm(seed, secs))\n"
+        "    s.finalize()\n"
+        "    out.append([s.tokens, s.token_frames])\n"
+        "print(json.dumps(out))\n"
+    ) % ([p for p in sys.path if p], gguf_f32)
+
+    def run(window):
+        env = dict(os.environ, NB200_DECODE_WINDOW=str(window))
+        r = subprocess.run([sys.executable, "-c", code], env=env, check=True, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=300)
+        return json.loads(r.stdout.strip().splitlines()[-1])
+
+    here = []
+    for rc, seed, secs in ((13, 61, 5.0), (6, 62, 3.0)):
+        s = model_f32.stream(rc)
+        s.process_incremental(inputs.pcm(seed, secs))
+        s.finalize()
+        here.append([s.tokens, s.token_frames])
+        s.free()
+    assert sum(len(t) for t, _ in here) > 20, "the case should emit tokens"
+    assert run(1) == here
+    assert run(4) == here
+
+
 def test_batched_equals_single(nb, model_f32):
     """Cross-stream batching must not change any stream's result: 5 streams in mixed latency modes, stepped together,
     equal the same streams run alone (same kernels, same per-row arithmetic)."""
