@@ -130,6 +130,49 @@ def build_pcm(n_streams: int, n_samples: int, first_id: int):
     return out
 
 
+def offline_main(a) -> None:
+    """`bench.py --offline`: the offline path (nb200_encode_audio) on single utterances of several lengths, one after the other
+    on one GPU (it is not batched across utterances), with the unmodified reference's offline path (nemo_encode through
+    `oracle/_ref/<isa>/ref_harness offline`) on the host cores as the CPU baseline. Not the headline metric: one JSON line of
+    its own."""
+    import inputs
+    lib_path = ROOT / "nemotron-asr.cpp_b200" / "libnemob200.so"
+    if not lib_path.exists():
+        import __graft_entry__ as ge
+        ge.build_library()
+    import nb200
+    gguf = inputs.gguf_path(a.variant, a.layers, BENCH_BLANK_GAIN)
+    m = nb200.Model(gguf, 0, 40)
+    rows = []
+    for secs in a.offline_secs:
+        pcm = inputs.pcm(51, secs)
+        m.encode_audio(pcm)  # warm-up: positional table of this length, lazy kernel attributes
+        times = []
+        for _ in range(a.offline_reps):
+            t0 = time.perf_counter()
+            tok, _fr = m.encode_audio(pcm)
+            times.append(time.perf_counter() - t0)
+        dt = float(np.median(times))
+        row = {"seconds": secs, "frames": int(len(pcm) // 1280), "ms": dt * 1e3, "ms_min": min(times) * 1e3, "ms_max": max(times) * 1e3,
+               "audio_s_per_s": secs / dt, "tokens": len(tok)}
+        if not a.no_cpu_baseline:
+            exe, isa = ref_harness_bin()
+            if exe is not None:
+                r = subprocess.run([exe, "offline", gguf, inputs.pcm_path(51, secs), "0", str(Path(inputs.TMP) / "boff"), str(secs)],
+                                   stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                if r.returncode == 0:
+                    info = json.loads(r.stdout.strip().splitlines()[-1])
+                    row["cpu_reference_ms"] = info["proc_s"] * 1e3
+                    row["cpu_reference_audio_s_per_s"] = secs / info["proc_s"]
+                    row["cpu_reference_isa"] = isa
+        rows.append(row)
+        print(json.dumps(row), file=sys.stderr)
+    m.close()
+    print(json.dumps({"metric": "offline_rtfx_single_utterance", "unit": "audio-s/s", "higher_is_better": True,
+                      "model": f"0.6B architecture, {a.layers} layers, {a.variant}, random init", "data": "synthetic",
+                      "timing": "wall clock around nb200_encode_audio (host PCM in, host tokens out), median of reps", "results": rows}))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -142,7 +185,12 @@ def main():
     ap.add_argument("--variant", default="q8_0", choices=("q8_0", "f32dq"))
     ap.add_argument("--no-token-heavy", action="store_true", help="skip the token-heavy decode side measurement")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--offline", action="store_true", help="side benchmark of the offline path (nb200_encode_audio), its own JSON line")
+    ap.add_argument("--offline-secs", type=float, nargs="+", default=[5.0, 10.0, 20.0, 40.0])
+    ap.add_argument("--offline-reps", type=int, default=10)
     a = ap.parse_args()
+    if a.offline:
+        return offline_main(a)
     if a.warmup < 3:
         a.warmup = 3
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
