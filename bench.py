@@ -10,10 +10,16 @@ Workload at N=1 = BASELINE.json configs[1]: nemotron-speech-streaming 0.6B archi
 GGUF, seed 1234), 64 concurrent streams, 1.12 s chunks (right_context 13). One "step" = one batched chunk of every
 stream (64 x 1.12 s of audio). Weak scaling: 64 streams per GPU.
 
+The model is random-init (no checkpoint offline) with a decoder calibrated to emit ~0.25 tokens per encoder frame like real
+speech (tools/make_random_gguf.py), so the greedy loop's LSTM updates run inside every timed step.
+
 Legs (all timed with CUDA events on the library's stream, max over ranks):
   value  K steps with the audio already resident in HBM (fed into the device PCM rings before the timed region)
   e2e    K steps through the public call sequence feed (pinned host PCM -> H2D) / step / poll tokens (D2H)
-  roofline  per-kernel-family device time from a profiled pass of the same steps (events around every launch)
+  roofline  the tcgen05 GEMMs' in-graph cost (K more steps with every GEMM launched twice, minus the K timed steps) against the
+            sustained bf16 peak; the back-to-back microbenchmark against the burst peak and the eager per-launch events beside it
+  latency_path  BASELINE config 3: 128 streams per GPU x 80 ms chunks (1024 streams at N = 8): ms per step, p50/p99 chunk latency,
+            achieved fraction of the HBM roofline (weights + K/V caches streamed once per step)
   cpu_baseline  the unmodified reference (oracle/_ref ref_harness) on the host cores, bounded sample
 """
 from __future__ import annotations
@@ -36,8 +42,22 @@ for _p in (ROOT / "nemotron-asr.cpp_b200", ROOT / "tools", ROOT / "tests"):
 METRIC = "audio-sec/sec (RTFx) over concurrent streams"
 UNIT = "audio-s/s"
 HOP, SR = 160, 16000
-TOKEN_HEAVY_GAIN = 6.2  # the random decoder's token-heavy regime: ~0.3 tokens per frame on average, a few streams at the 10-symbol cap
-BENCH_BLANK_GAIN = 6.3  # see tools/make_random_gguf.py: blank-dominated decode, ~1.05 symbol steps per encoder frame
+# The benchmark model: random-init weights of the 0.6B architecture with the depth-scaled residual initialisation (the encoder
+# output then follows the audio frame by frame) and the "stationary" decoder, calibrated to the profile of real speech: ~0.25
+# tokens per encoder frame, hardly ever more than 3 symbols on a frame (tools/make_random_gguf.py DECODERS,
+# tests/golden/calibrate_bench_decoder.py). Both arms load the same file.
+BENCH_BLANK_GAIN = 6.0
+BENCH_DECODER = "stationary"
+BENCH_RES_SCALE = 0.1
+LATENCY_STREAMS = 128  # BASELINE config 3: 1024 concurrent 80 ms-chunk streams sharded by stream over 8 GPUs = 128 per GPU
+# fp16 operand bytes a step reads per conformer layer: two FFNs (2 x 2 x 4096 x 1024), q|k|v (3 x 1024^2), linear_out, pointwise_conv1
+# (2 x 1024^2), pointwise_conv2 (linear_pos is folded into a per-mode table at stream creation)
+WEIGHT_BYTES_PER_LAYER = 2 * (4 * 4096 * 1024 + 3 * 1024 * 1024 + 1024 * 1024 + 2 * 1024 * 1024 + 1024 * 1024)
+
+
+def bench_gguf(variant: str, layers: int) -> str:
+    import inputs
+    return inputs.gguf_path(variant, layers, BENCH_BLANK_GAIN, decoder=BENCH_DECODER, res_scale=BENCH_RES_SCALE)
 
 
 def chunk_samples(rc: int) -> int:
@@ -141,7 +161,7 @@ def offline_main(a) -> None:
         import __graft_entry__ as ge
         ge.build_library()
     import nb200
-    gguf = inputs.gguf_path(a.variant, a.layers, BENCH_BLANK_GAIN)
+    gguf = bench_gguf(a.variant, a.layers)
     m = nb200.Model(gguf, 0, 40)
     rows = []
     for secs in a.offline_secs:
@@ -183,7 +203,8 @@ def main():
     ap.add_argument("--rc", type=int, default=13, choices=(0, 1, 6, 13))
     ap.add_argument("--layers", type=int, default=24)
     ap.add_argument("--variant", default="q8_0", choices=("q8_0", "f32dq"))
-    ap.add_argument("--no-token-heavy", action="store_true", help="skip the token-heavy decode side measurement")
+    ap.add_argument("--no-latency-path", action="store_true", help="skip the config-3 leg (80 ms chunks, 128 streams per GPU)")
+    ap.add_argument("--latency-steps", type=int, default=200)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--offline", action="store_true", help="side benchmark of the offline path (nb200_encode_audio), its own JSON line")
     ap.add_argument("--offline-secs", type=float, nargs="+", default=[5.0, 10.0, 20.0, 40.0])
@@ -198,17 +219,18 @@ def main():
     workload = f"nemotron-speech-streaming-0.6B ({a.layers} layers, random-init {a.variant}), {a.streams} concurrent streams per GPU, " \
                f"{cs / SR:.2f} s chunks (right_context {a.rc})"
     config = {"workload": workload, "streams_per_gpu": a.streams, "right_context": a.rc, "chunk_seconds": cs / SR, "layers": a.layers,
-              "weights": a.variant, "l2_policy": "inputs larger than L2: weights 1.2 GB + 0.9 GB of K/V caches are re-read every step"}
+              "weights": a.variant, "decoder": f"random-init '{BENCH_DECODER}' decoder, blank gain {BENCH_BLANK_GAIN:g}, residual scale {BENCH_RES_SCALE:g}: "
+                                               "~0.25 tokens per encoder frame (tools/make_random_gguf.py)", "l2_policy": "inputs larger than L2: weights 1.2 GB + 0.9 GB of K/V caches are re-read every step"}
 
     import inputs
-    gguf_done = Path(inputs.TMP) / f".gguf_ready_{a.layers}_{a.variant}"
+    gguf_done = Path(inputs.TMP) / f".gguf_ready_{a.layers}_{a.variant}_{BENCH_DECODER}_{BENCH_BLANK_GAIN:g}_{BENCH_RES_SCALE:g}"
     if local == 0:
-        gguf = inputs.gguf_path(a.variant, a.layers, BENCH_BLANK_GAIN)
+        gguf = bench_gguf(a.variant, a.layers)
         gguf_done.touch()
     else:
         while not gguf_done.exists():
             time.sleep(0.5)
-        gguf = inputs.gguf_path(a.variant, a.layers, BENCH_BLANK_GAIN)
+        gguf = bench_gguf(a.variant, a.layers)
 
     # ------------------------------------------------------------------------------------------------------
     if a.impl == "reference":
@@ -255,12 +277,12 @@ def main():
             dist.barrier(device_ids=[local])
         torch.cuda.synchronize()
 
-    n_total_steps = 2 * a.warmup + 3 * a.steps + 6
+    n_total_steps = 3 * a.warmup + 4 * a.steps + 8
     need = (a.warmup + a.steps + 2) * cs + 1024
     os.environ["NB200_PCM_RING_LOG2"] = str(max(17, int(np.ceil(np.log2(need)))))
     my_ids = shard.shard_streams(a.streams * world, world, rank)
     assert len(my_ids) == a.streams
-    model = nb200.Model(gguf, device=local, max_streams=a.streams)
+    model = nb200.Model(gguf, device=local, max_streams=max(a.streams, 0 if a.no_latency_path else LATENCY_STREAMS))
     streams = [model.stream(a.rc) for _ in my_ids]
     pcm = build_pcm(a.streams, n_total_steps * cs, my_ids[0])
     base_ptr, row_bytes = pcm.data_ptr(), pcm.stride(0) * 2
@@ -342,7 +364,6 @@ def main():
         assert n == a.streams, n
         io.poll()
         lat.append((time.perf_counter() - t1) * 1e3)
-    clocks = sampler.stop() if rank == 0 else None
 
     # ---- leg 3: per-kernel device time (profiled pass, outside the timed regions) ---------------------------
     model.profile(True)
@@ -352,44 +373,129 @@ def main():
     prof = model.profile_report()
     model.profile(False)
     tot_ms = sum(v["ms"] for v in prof.values()) or 1.0
-    dom = max(prof, key=lambda k: prof[k]["ms"])
     pk = peaks()
-    d = prof[dom]
-    per_launch_ms = d["ms"] / d["launches"]
-    if dom.startswith("gemm"):
-        ach_eager = d["flops"] / (d["ms"] * 1e-3) / 1e12
-        # The encoder's GEMMs as they run in the step: back-to-back programmatic-dependent launches (no event between them),
-        # each launch streaming a different layer's weights from HBM (300 MB pool > L2). Shapes of the FFN pair, which is
-        # the dominant tile family (W1: SiLU + re-quantise epilogue; W2: split-K partial epilogue), M = streams x frames.
-        M = a.streams * T
-        runs = [model.bench_gemm(M, 4096, 1024, 1, 0, 1, 96), model.bench_gemm(M, 1024, 4096, 5, 0, 1, 96)]
-        fl = [2.0 * M * 4096 * 1024, 2.0 * M * 1024 * 4096]
-        ach = sum(fl) / (sum(r["us"] for r in runs) * 1e-6) / 1e12
-        per_launch_ms = sum(r["us"] for r in runs) / len(runs) * 1e-3
-        roofline = {"kernel": dom, "bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"],
-                    "achieved_eager_events": ach_eager, "frac_eager_events": ach_eager / pk["tflops"],
-                    "shapes": [{"N": 4096, "K": 1024, "us": runs[0]["us"], "bn": runs[0]["bn"], "splits": runs[0]["splits"]},
-                               {"N": 1024, "K": 4096, "us": runs[1]["us"], "bn": runs[1]["bn"], "splits": runs[1]["splits"]}]}
-    else:
-        ach = d["bytes"] / (d["ms"] * 1e-3) / 1e9
-        roofline = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"]}
+    gemm_fams = [k for k in prof if k.startswith("gemm_tc")]
+    gemm_flops_step = sum(prof[k]["flops"] for k in gemm_fams) / 2
+    gemm_launches_step = sum(prof[k]["launches"] for k in gemm_fams) // 2
+    gemm_ms_eager = sum(prof[k]["ms"] for k in gemm_fams) / 2
+    dom = max(prof, key=lambda k: prof[k]["ms"])
+    M = a.streams * T
+
+    # ---- leg 4: what the GEMMs cost INSIDE the step (the roofline figure) ------------------------------------------------------
+    # Every tcgen05 GEMM of the step is launched twice inside the graph (nb200_set_dup_family("gemm"); their epilogues are pure
+    # stores, so the results do not change); the step-time difference over the same K device-resident steps is the in-graph cost
+    # of all GEMM launches: producer -> consumer dependencies, PDL overlap and graph replay included, weights streaming from HBM.
+    model.set_dup_family("gemm")
+    feed_chunks(a.warmup + a.steps)
+    for _ in range(a.warmup):
+        assert model.step() == a.streams
+    barrier()
+    model.timer_start()
+    for _ in range(a.steps):
+        assert model.step() == a.streams
+    ms_dup = model.timer_stop()
+    barrier()
+    model.set_dup_family(None)
+    gemm_ms_step = max((ms_dup - ms_dev) / a.steps, 1e-6)
+    ach = gemm_flops_step / (gemm_ms_step * 1e-3) / 1e12
+    # beside it: the FFN pair back to back on synthetic operands (a burst of 96 PDL launches per shape, weights cycling through
+    # a 300 MB pool): held against the BURST peak
+    runs = [model.bench_gemm(M, 4096, 1024, 1, 0, 1, 96), model.bench_gemm(M, 1024, 4096, 5, 0, 1, 96)]
+    fl = [2.0 * M * 4096 * 1024, 2.0 * M * 1024 * 4096]
+    ach_burst = sum(fl) / (sum(r["us"] for r in runs) * 1e-6) / 1e12
+    burst_peak = pk["tflops"]
+    try:
+        burst_peak = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())["bf16_tflops"]
+    except Exception:
+        pass
     traffic = None
-    try:  # DRAM bytes per launch of this kernel family from this round's ncu --set full capture (profiles/ncu_traffic.json)
-        if a.streams == 64 or dom == "attention_stream":
-            traffic = json.loads((ROOT / "profiles" / "ncu_traffic.json").read_text()).get(dom, {}).get("traffic")
+    try:  # DRAM bytes per launch of the dominant GEMM from this round's ncu --set full capture (profiles/ncu_traffic.json)
+        if a.streams == 64 and a.rc == 13:
+            traffic = json.loads((ROOT / "profiles" / "ncu_traffic.json").read_text()).get("gemm_tc_128x256", {}).get("traffic")
     except Exception:
         traffic = None
-    roofline.update({"traffic": traffic, "algorithmic": (d["flops"] if dom.startswith("gemm") else d["bytes"]) / d["launches"],
-                     "timing": ("CUDA events around 96 back-to-back PDL launches per shape, weights cycling through a 300 MB pool (HBM-resident); "
-                                "achieved_eager_events = the same family timed launch by launch with an event pair around each (per-kernel table)")
-                     if dom.startswith("gemm") else "CUDA events around every launch of an eager (non-graph) pass", "peak_source": pk["source"], "share_of_step": d["ms"] / tot_ms, "avg_launch_us": per_launch_ms * 1e3,
-                     "launches_per_step": d["launches"] // 2})
+    roofline = {"kernel": "gemm_tc_kernel (all tcgen05 GEMM launches of the step)", "bound": "tensor", "achieved": ach, "peak": pk["tflops"],
+                "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": traffic, "algorithmic": gemm_flops_step / max(gemm_launches_step, 1),
+                "launches_per_step": gemm_launches_step, "avg_launch_us": gemm_ms_step / max(gemm_launches_step, 1) * 1e3,
+                "gemm_ms_per_step": gemm_ms_step, "share_of_step": gemm_ms_step / (ms_dev / a.steps), "peak_source": pk["source"],
+                "timing": "in-graph marginal cost: K steps with every GEMM launched twice minus the K timed steps (CUDA events on the library's "
+                          "stream), divided by the GEMM FLOPs of a step; peak = sustained bf16",
+                "burst_microbench": {"achieved": ach_burst, "peak_burst": burst_peak, "frac_of_burst_peak": ach_burst / burst_peak,
+                                     "what": "FFN pair (W1 SiLU + re-quantise, W2 split-K), 96 back-to-back launches per shape on synthetic operands",
+                                     "shapes": [{"N": 4096, "K": 1024, "us": runs[0]["us"], "bn": runs[0]["bn"], "splits": runs[0]["splits"]},
+                                                {"N": 1024, "K": 4096, "us": runs[1]["us"], "bn": runs[1]["bn"], "splits": runs[1]["splits"]}]},
+                "eager_events": {"achieved": gemm_flops_step / (gemm_ms_eager * 1e-3) / 1e12, "what": "event pair around every launch of a non-graph pass"},
+                "step_tflops": gemm_flops_step / (ms_dev / a.steps * 1e-3) / 1e12}
     kernels = {k: {"share": round(v["ms"] / tot_ms, 4), "launches_per_step": v["launches"] // 2, "avg_us": round(v["ms"] / v["launches"] * 1e3, 2),
                    "tflops": round(v["flops"] / (v["ms"] * 1e-3) / 1e12, 2), "gbs": round(v["bytes"] / (v["ms"] * 1e-3) / 1e9, 1)}
                for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms"])}
-
     for s in streams:
         s.free()
+
+    # ---- leg 5: the latency path (BASELINE config 3): 80 ms chunks, right_context 0, 128 streams per GPU -------------------------
+    latency_path = None
+    if not a.no_latency_path:
+        L_S, cs0 = LATENCY_STREAMS, chunk_samples(0)
+        warm0, k0 = 20, a.latency_steps
+        ls = [model.stream(0) for _ in range(L_S)]
+        pcm0 = build_pcm(L_S, (warm0 + 2 * k0 + 8) * cs0, my_ids[0] * 2)
+        io0 = model.batch_io(ls)
+        addr0 = np.uint64(pcm0.data_ptr()) + np.arange(L_S, dtype=np.uint64) * np.uint64(pcm0.stride(0) * 2)
+        cur0 = 0
+
+        def feed0(n):
+            nonlocal cur0
+            io0.feed_ptrs(addr0 + np.uint64(cur0 * 2), n * cs0)
+            cur0 += n * cs0
+
+        feed0(2)  # one chunk of look-ahead: a centred STFT frame needs 256 samples beyond its hop
+        for _ in range(warm0):
+            assert model.step() == L_S
+            io0.poll()
+            feed0(1)
+        q0 = model.stats()
+        barrier()
+        # (a) chunk latency: feed -> step -> poll strictly in sequence, wall clock per 80 ms chunk of all 128 streams
+        lat0 = []
+        model.timer_start()
+        for _ in range(k0):
+            t1 = time.perf_counter()
+            feed0(1)
+            n = model.step()
+            assert n == L_S, n
+            io0.poll()
+            lat0.append((time.perf_counter() - t1) * 1e3)
+        ms_seq = model.timer_stop()
+        barrier()
+        q1 = model.stats()
+        # (b) throughput: device-resident audio, K steps back to back
+        feed0(k0)
+        barrier()
+        model.timer_start()
+        for _ in range(k0):
+            assert model.step() == L_S
+        ms_res = model.timer_stop()
+        barrier()
+        q2 = model.stats()
+        ms0_max, audio0 = shard.reduce_timing(ms_res, k0 * L_S * cs0 / SR, dev)
+        seq_max, _ = shard.reduce_timing(ms_seq, 0.0, dev)
+        kv_bytes = L_S * a.layers * 2 * 70 * 1024 * 2
+        w_bytes = a.layers * WEIGHT_BYTES_PER_LAYER
+        step_ms = ms0_max / k0
+        latency_path = {"workload": f"{L_S} concurrent streams per GPU x 80 ms chunks (right_context 0), {L_S * world} streams on {world} GPU(s)",
+                        "ms_per_step": step_ms, "value": audio0 / (ms0_max * 1e-3), "unit": UNIT, "steps": k0,
+                        "realtime_duty": step_ms / 80.0, "streams_total": L_S * world,
+                        "chunk_latency_ms": {"p50": float(np.percentile(lat0, 50)), "p99": float(np.percentile(lat0, 99)), "max": float(max(lat0)),
+                                             "what": "feed (host PCM -> H2D) + step + poll (tokens D2H) of one 80 ms chunk of every stream, in sequence, wall clock, this rank"},
+                        "ms_per_step_sequential": seq_max / k0,
+                        "gpu_launches_per_step": int((q2.kernel_launches - q1.kernel_launches) // k0),
+                        "tokens_per_frame": (q2.tokens - q0.tokens) / max(q2.frames - q0.frames, 1),
+                        "hbm": {"bytes_per_step": w_bytes + kv_bytes, "weights": w_bytes, "kv_cache_read": kv_bytes, "achieved_gbs": (w_bytes + kv_bytes) / (step_ms * 1e-3) / 1e9,
+                                "peak_gbs": pk["hbm_gbs"], "frac": (w_bytes + kv_bytes) / (step_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                                "what": "every step streams all fp16 weights and the 70 cached K and V rows of every stream and layer once: the floor of this path"}}
+        for s in ls:
+            s.free()
+    clocks = sampler.stop() if rank == 0 else None
     model.close()
     if world > 1:
         dist.barrier(device_ids=[local])
@@ -404,35 +510,8 @@ def main():
             "latency_ms": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)), "what": "feed+step+poll of one batched chunk, in sequence (wall clock)"},
             "decode_steps_per_frame": steps_per_frame, "decode_rounds_per_step": rounds_per_step, "tokens_emitted": int(tokens),
             "frames_decoded": int(frames), "streams_total": a.streams * world,
-            "realtime_streams_supported": value, "roofline": roofline, "kernels": kernels}
-
-    # ---- side measurement (not the headline): the same step with a decoder that emits tokens ------------------------------
-    # The headline workload decodes all-blank (tokens_emitted above), the floor of the decode cost. This leg repeats the
-    # device-resident measurement with the random decoder pushed into its token-heavy regime, where the rounds with an emission
-    # add the LSTM update and the streams at the 10-symbols-per-frame cap make the chunk's round count 10 x its frames.
-    if world == 1 and not a.no_token_heavy:
-        try:
-            m2 = nb200.Model(inputs.gguf_path(a.variant, a.layers, TOKEN_HEAVY_GAIN), device=local, max_streams=a.streams)
-            s2 = [m2.stream(a.rc) for _ in range(a.streams)]
-            k2, w2 = min(a.steps, 10), 2
-            m2.batch_io(s2).feed_ptrs(row_addr, (w2 + k2 + 1) * cs)
-            for _ in range(w2):
-                m2.step()
-            q0 = m2.stats()
-            torch.cuda.synchronize()
-            m2.timer_start()
-            for _ in range(k2):
-                m2.step()
-            ms2 = m2.timer_stop()
-            q1 = m2.stats()
-            fr2, tk2 = q1.frames - q0.frames, q1.tokens - q0.tokens
-            line["token_heavy_decode"] = {"blank_gain": TOKEN_HEAVY_GAIN, "steps": k2, "ms_per_step": ms2 / k2, "value": k2 * a.streams * cs / SR / (ms2 * 1e-3),
-                                          "unit": UNIT, "tokens_per_frame": tk2 / max(fr2, 1), "decode_rounds_per_step": (q1.decode_rounds - q0.decode_rounds) / k2,
-                                          "what": "same step, device-resident audio, random decoder in its token-heavy regime (bistable: a few streams run at "
-                                                  "the 10-symbols-per-frame cap, so a chunk takes up to 10 x T dependent rounds); not the headline"}
-            m2.close()
-        except Exception as e:
-            line["token_heavy_decode"] = {"unavailable": str(e)}
+            "tokens_per_frame": tokens / max(frames, 1), "realtime_streams_supported": value, "roofline": roofline, "kernels": kernels,
+            "dominant_family_eager": dom, "latency_path": latency_path}
 
     if world == 1 and not a.no_cpu_baseline:
         try:

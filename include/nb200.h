@@ -64,6 +64,11 @@ int nb200_version(void);
 /* nemo_init_with_backend(path, backend) — src/nemo-ggml.h:259, src/nemo-ggml.cpp:448-495 (GGUF load :83-442).
  * device: CUDA ordinal. max_streams: stream slots to reserve (K/V/conv caches live in HBM per slot). */
 nb200_model* nb200_model_load(const char* gguf_path, int device, int max_streams, int flags);
+/* Host-only check of a GGUF file (no GPU needed): parses the container exactly like nb200_model_load — header, KVs, tensor
+ * table with the bounds of every tensor inside the file, the vocabulary (tokenizer.vocab_list, or the legacy 8-byte-piece blob
+ * tokenizer.vocab, src/nemo-ggml.cpp:149-169) — and writes a JSON summary {"tensors", "tensor_bytes", "vocab_source",
+ * "vocab_pieces", "n_layers", "first_pieces"} into json_out. Returns its length, or <0 with nb200_last_error() on a malformed file. */
+int nb200_gguf_check(const char* gguf_path, char* json_out, int cap);
 /* nemo_free — src/nemo-ggml.h:261 */
 void nb200_model_free(nb200_model* m);
 int nb200_model_info(const nb200_model* m, nb200_info* out);
@@ -171,6 +176,12 @@ int nb200_timer_stop(nb200_model* m, double* ms_out);
  * report() writes a JSON object {"family": {"launches","ms","flops","bytes"}} (algorithmic FLOPs / bytes of the
  * launches) into json_out, clears the records and returns the string length, or <0 if cap is too small. */
 int nb200_profile_enable(nb200_model* m, int on);
+/* In-graph marginal cost of a kernel family: while set, every launch of that family ("gemm", "layernorm", "attention",
+ * "dwconv") is issued TWICE inside the step's graph, so (step time with - step time without) / launches is what one launch of
+ * the family costs where it actually runs (between its producer and consumer, PDL and graph replay included). The GEMM
+ * epilogues are pure stores, so "gemm" leaves the results intact; the other families' results are garbage while set.
+ * NULL or "" switches it off. Drops the model's captured graphs (they are re-captured on the next steps). */
+int nb200_set_dup_family(nb200_model* m, const char* family);
 int nb200_profile_report(nb200_model* m, char* json_out, int cap);
 
 /* ---- kernel-level entry points (used by the parity tests and bench; same kernels the step uses) -------- */
@@ -181,6 +192,14 @@ int nb200_mel_batch(nb200_model* m, const int16_t* pcm, int n_streams, int n_sam
 /* Y[M,N] = X[M,K] * W^T with W one of the model's encoder matrices (by GGUF tensor name), using exactly the
  * operand preparation (activation re-quantisation, fp16 operands) and GEMM kernel of the step. Host buffers. */
 int nb200_debug_matmul(nb200_model* m, const char* tensor_name, const float* x, int M, float* y);
+/* The same, through the FUSED EPILOGUE the step uses for that matrix class and with the tile configuration the step would pick
+ * for this M (what src/nemo-stream.cpp:593-603,631-690 does as separate ggml nodes): epi_kind 0 = fp32 store, 1 = SiLU (+ the
+ * Q8_0 re-quantisation when the model emulates it) -> fp16 (linear1), 4 = GLU on pointwise_conv1 -> [M][N/2], 5 = split-K partial
+ * planes added to a zero residual stream by the step's LayerNorm kernel (N = 1024 matrices: linear2, linear_out, pointwise_conv2):
+ * y = the sum, y_ln (may be NULL) = the LayerNorm output (unit gain) as the next GEMM's fp16 operand, 6 = plain fp16 store
+ * ("encoder.layers.<l>.self_attn.qkv" names the stacked q|k|v matrix). fp16 results are returned widened to fp32.
+ * cfg_out (may be NULL) receives {tile width BN, K splits, CTAs per tile (2 = cta_group::2 pair), CTAs launched}. */
+int nb200_debug_gemm(nb200_model* m, const char* tensor_name, const float* x, int M, int epi_kind, float* y, float* y_ln, int* cfg_out);
 /* Times the tcgen05 GEMM alone: C[M,N] = A[M,K] * W[N,K]^T on synthetic fp16 operands, cycling through > 2x L2 worth of
  * weight matrices so that W streams from HBM as it does inside a step. epi_kind: 0 store f32, 1 SiLU + re-quantise ->
  * f16, 4 GLU, 5 split-K partials, 6 plain f16 store. bn / splits force a tile configuration (bn = 0: the library's heuristic). Device time

@@ -34,13 +34,15 @@ inline void cuda_check(cudaError_t e, const char* what, const char* file, int li
 }
 #define CUDA_CHECK(x) ::nb::cuda_check((x), #x, __FILE__, __LINE__)
 
-extern long long g_launches;  // kernels launched by this library (reported as gpu_launches)
+// Kernels launched by this library on the calling thread (one thread owns a model, include/nb200.h: the engine adds the
+// per-entry-point difference to the model's own total, which is what nb200_get_stats reports as kernel_launches).
+extern thread_local long long g_launches;
 #define NB_LAUNCHED() (++::nb::g_launches)
 #define NB_KERNEL_CHECK() do { NB_LAUNCHED(); CUDA_CHECK(cudaGetLastError()); } while (0)
 
 // Per-kernel-family device timing (nb200_profile_*): when enabled, every launcher brackets its launch with CUDA events
 // on the launching stream and reports the algorithmic FLOPs / bytes of that launch; prof.cu aggregates per family.
-extern bool g_prof_on;
+extern thread_local bool g_prof_on;  // per thread, like the records it fills
 void prof_begin(cudaStream_t st, const char* family, double flops, double bytes);
 void prof_end(cudaStream_t st);
 std::string prof_report();  // JSON of per-family totals since the last report; clears the records
@@ -66,6 +68,7 @@ extern bool g_pdl;
 // Timing experiment: NB200_DUP=<family> makes the launcher of that kernel family launch it twice, so its marginal in-graph cost is
 // (step time with - without) / launches. Results are garbage in that mode.
 bool dup_family(const char* family);
+void set_dup_family(const char* family);  // nullptr / "" = off (nb200_set_dup_family; initialised from NB200_DUP)
 #ifdef __CUDACC__
 __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
@@ -93,6 +96,23 @@ void launch_kc(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cud
         cfg.numAttrs = 2;
     }
     cfg.attrs = at;
+    CUDA_CHECK(cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...));
+}
+// Cooperative launch (no programmatic overlap): for kernels whose CTAs wait for each other at hand-rolled grid barriers. The
+// driver then places the whole grid at once or fails the launch (cudaErrorCooperativeLaunchTooLarge) instead of letting a
+// partially resident grid spin forever when another kernel holds some of the SMs. Capturable into CUDA graphs.
+template <typename... KArgs, typename... Args>
+void launch_coop(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeCooperative;
+    at[0].val.cooperative = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
     CUDA_CHECK(cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...));
 }
 template <typename... KArgs, typename... Args>

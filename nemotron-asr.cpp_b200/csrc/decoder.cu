@@ -7,6 +7,7 @@
 // each emission, so a round costs one joint evaluation plus one batched LSTM update. Streams advance through their
 // frames independently (no lock-step over frames).
 #include <algorithm>
+#include <cstdlib>
 
 #include "kernels.cuh"
 
@@ -660,6 +661,10 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
     }
 }
 
+// The persistent kernel's CTAs meet at hand-rolled grid barriers, so all of them must be resident at once: it is launched
+// cooperatively (the driver refuses a grid it cannot place whole, e.g. while a second model's decode kernel holds SMs of the
+// same device, instead of letting it hang), and the grid is checked against the occupancy once per device.
+// NB200_DECODE_NO_COOP=1 falls back to a plain programmatic-dependent launch (debugging only).
 static int decode_grid() {
     static int g = 0;
     static PerDeviceOnce once;
@@ -670,8 +675,22 @@ static int decode_grid() {
         g = std::min(sms, 148);
         if ((VOCAB + g - 1) / g > DK_MAXR || (DEC + g - 1) / g > DK_MAXU) throw Error("decode kernel: too few SMs for its row split");
     }
-    if (once.first()) CUDA_CHECK(cudaFuncSetAttribute(decode_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DkSmem)));
+    if (once.first()) {
+        CUDA_CHECK(cudaFuncSetAttribute(decode_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DkSmem)));
+        int dev = 0, sms = 0, per_sm = 0, coop = 0;
+        CUDA_CHECK(cudaGetDevice(&dev));
+        CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        CUDA_CHECK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+        CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, decode_persistent_kernel, 256, sizeof(DkSmem)));
+        if (!coop) throw Error("decode kernel: the device does not support cooperative launches");
+        if (per_sm * sms < g) throw Error("decode kernel: its grid cannot be co-resident on this device");
+    }
     return g;
+}
+static void launch_decode(cudaStream_t st, int g, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d, int refresh) {
+    static const bool no_coop = getenv("NB200_DECODE_NO_COOP") != nullptr;
+    if (no_coop) launch_k(decode_persistent_kernel, dim3(g), dim3(256), sizeof(DkSmem), st, w, s, d, refresh);
+    else launch_coop(decode_persistent_kernel, dim3(g), dim3(256), sizeof(DkSmem), st, w, s, d, refresh);
 }
 
 int decode_partial_floats(int B) { return 4 * B * 148; }
@@ -681,7 +700,7 @@ void launch_decode_chunk(cudaStream_t st, const DecodeWeights& w, const DecodeSt
     const int g = decode_grid();
     CUDA_CHECK(cudaMemsetAsync(d.counters, 0, 32 * sizeof(int), st));  // counters, the barrier word, time stamps
     ProfScope ps(st, "decode_chunk", 2.0 * d.B * d.T * (double)VOCAB * JOINT, 0.0);
-    launch_k(decode_persistent_kernel, dim3(g), dim3(256), sizeof(DkSmem), st, w, s, d, 0);
+    launch_decode(st, g, w, s, d, 0);
     NB_KERNEL_CHECK();
 }
 
@@ -689,7 +708,7 @@ void launch_decode_chunk(cudaStream_t st, const DecodeWeights& w, const DecodeSt
 void launch_decode_refresh(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d) {
     const int g = decode_grid();
     CUDA_CHECK(cudaMemsetAsync(d.counters, 0, 9 * sizeof(int), st));
-    launch_k(decode_persistent_kernel, dim3(g), dim3(256), sizeof(DkSmem), st, w, s, d, 1);
+    launch_decode(st, g, w, s, d, 1);
     NB_KERNEL_CHECK();
 }
 

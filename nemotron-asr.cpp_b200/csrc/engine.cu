@@ -200,6 +200,13 @@ struct nb200_model {
         ModeCtx* mc = nullptr;
         std::vector<BatchItem> items;
     } inflight;
+    // slots waiting for their state reset (apply_resets), the pinned / device copies of that list
+    std::vector<int> reset_queue;
+    PinnedBuf<int> h_reset;
+    int* d_reset = nullptr;
+    cudaEvent_t reset_ev = nullptr;
+    bool reset_busy = false;
+    long long launches = 0;  // kernels this model has launched (the per-thread counter g_launches, accumulated per entry point)
     PinnedBuf<int> h_meta;
     PinnedBuf<long long> h_meta64;
     PinnedBuf<int> h_tok;
@@ -234,6 +241,7 @@ struct nb200_model {
             for (auto& kv : *gm)
                 if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
         if (upload_ev) cudaEventDestroy(upload_ev);
+        if (reset_ev) cudaEventDestroy(reset_ev);
         if (st_copy) cudaStreamDestroy(st_copy);
         if (st) cudaStreamDestroy(st);
     }
@@ -281,6 +289,23 @@ uint32_t kv_u32(const GgufFile& g, const char* key, uint32_t dflt) {
     return it == g.u32.end() ? dflt : it->second;
 }
 
+// Vocabulary (src/nemo-ggml.cpp:149-169): the string array `tokenizer.vocab_list`, else the legacy `tokenizer.vocab` blob of
+// fixed 8-byte, NUL-padded pieces (vocab_size - 1 of them: the blank has no piece). Returns which of the two was read.
+const char* load_vocab(GgufFile& g, int vocab_size, std::vector<std::string>& vocab) {
+    vocab.clear();
+    if (g.str_arr.count("tokenizer.vocab_list")) {
+        vocab = g.str_arr["tokenizer.vocab_list"];
+        return "tokenizer.vocab_list";
+    }
+    if (g.str.count("tokenizer.vocab")) {
+        const std::string& blob = g.str["tokenizer.vocab"];
+        for (size_t i = 0; i + 8 <= blob.size() && (int)(i / 8) < vocab_size - 1; i += 8)
+            vocab.emplace_back(blob.data() + i, strnlen(blob.data() + i, 8));
+        return "tokenizer.vocab";
+    }
+    throw Error("no vocabulary in GGUF (need tokenizer.vocab_list or tokenizer.vocab)");
+}
+
 void build_model(nb200_model* m, const std::string& path, int flags) {
     GgufFile g;
     g.open(path);
@@ -306,16 +331,7 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
         throw Error("this backend is built for the nemotron-speech-streaming 0.6B architecture; the GGUF header differs");
     if (hp.num_prompts < 0 || hp.num_prompts > 4096) throw Error("nemo.num_prompts out of range");
     m->n_layers = hp.n_layers;
-    // vocabulary (src/nemo-ggml.cpp:149-169)
-    if (g.str_arr.count("tokenizer.vocab_list")) {
-        m->vocab = g.str_arr["tokenizer.vocab_list"];
-    } else if (g.str.count("tokenizer.vocab")) {
-        const std::string& blob = g.str["tokenizer.vocab"];
-        for (size_t i = 0; i + 8 <= blob.size() && (int)i / 8 < hp.vocab_size - 1; i += 8)
-            m->vocab.emplace_back(blob.data() + i, strnlen(blob.data() + i, 8));
-    } else {
-        throw Error("no vocabulary in GGUF (need tokenizer.vocab_list or tokenizer.vocab)");
-    }
+    load_vocab(g, hp.vocab_size, m->vocab);
     const std::string l0 = "encoder.layers.0.";
     const GgufTensor& dw0 = g.tensor(l0 + "conv.depthwise_conv.weight");
     hp.kernel_size = dw0.dims.size() > 1 ? (int)dw0.dims[1] : 0;  // inferred like src/nemo-ggml.cpp:357-360
@@ -412,6 +428,7 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
             }
             make_f16(m, L.wqkv, w, 3 * D_MODEL, D_MODEL);
             for (int i = 0; i < 3; i++) m->by_name[p + nm[i]] = {L.wqkv.ptr + (size_t)i * D_MODEL * D_MODEL, D_MODEL, D_MODEL, false};
+            m->by_name[p + "self_attn.qkv"] = {L.wqkv.ptr, 3 * D_MODEL, D_MODEL, false};  // the stacked matrix the step multiplies by (debug entry points)
         }
         {   // pointwise_conv1: rows 0..1023 = GLU value, 1024..2047 = gate -> interleave (value_j, gate_j)
             std::vector<float> w = load_f32(g, p + "conv.pointwise_conv1.weight", (int64_t)2 * D_MODEL * D_MODEL), wi(w.size());
@@ -559,6 +576,8 @@ void alloc_state(nb200_model* m) {
     m->ws_partial = m->alloc<float>((size_t)decode_partial_floats(B) * m->dec_window);
     m->ws_hid = m->alloc<float>((size_t)B * JOINT * m->dec_window);
     m->ws_emit = m->alloc<int>(B);
+    m->d_reset = m->alloc<int>(B);
+    CUDA_CHECK(cudaEventCreateWithFlags(&m->reset_ev, cudaEventDisableTiming));
     {   // upload arenas: >= two rc=13 chunks per slot each
         const size_t cap = std::max<size_t>((size_t)1 << 22, (size_t)B * 2 * (HOP * big.shift + 1024));
         for (auto& A : m->arena) {
@@ -621,22 +640,60 @@ DecodeBatch decode_batch(nb200_model* m, int B, int T, int W = 1) {
     return d;
 }
 
-// zero a slot's state and recompute its pending decoder state (prev = blank, h = c = 0)
-void reset_slot(nb200_model* m, int slot) {
-    const size_t S = (size_t)m->max_streams;
-    for (int l = 0; l < m->n_layers; l++) {
-        CUDA_CHECK(cudaMemsetAsync(m->k_ring + ((size_t)l * S + slot) * RING * D_MODEL, 0, sizeof(__half) * RING * D_MODEL, m->st));
-        CUDA_CHECK(cudaMemsetAsync(m->v_ring + ((size_t)l * S + slot) * RING * D_MODEL, 0, sizeof(__half) * RING * D_MODEL, m->st));
-        CUDA_CHECK(cudaMemsetAsync(m->conv_cache + ((size_t)l * S + slot) * 2 * CONV_CACHE * D_MODEL, 0, sizeof(float) * 2 * CONV_CACHE * D_MODEL, m->st));
+// ---- stream create / reset: zero the slots' state slabs and recompute their pending decoder state --------------------------
+// One kernel over all queued slots instead of 75 memsets + a host synchronisation per stream (1024 creates = 77 k calls):
+// block (x = slot index in the list, y = layer, z = part). Parts 0 / 1 / 2 = the layer's K ring, V ring, conv cache of the slot;
+// the blocks of layer 0 / part 0 also clear the slot's mel overlap and committed LSTM state and set prev = blank.
+struct ResetArgs {
+    const int* slots;
+    __half *k_ring, *v_ring;
+    float *conv_cache, *mel_overlap, *h, *c;
+    int* prev;
+    size_t S;  // slots per layer
+};
+__device__ __forceinline__ void zero_bytes(void* p, size_t bytes) {  // bytes % 16 == 0, p 16-byte aligned
+    uint4* q = reinterpret_cast<uint4*>(p);
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    for (size_t i = threadIdx.x; i < bytes / 16; i += blockDim.x) q[i] = z;
+}
+__global__ void __launch_bounds__(256) reset_slots_kernel(ResetArgs a) {
+    pdl_prologue();
+    const size_t slot = (size_t)a.slots[blockIdx.x], l = blockIdx.y;
+    if (blockIdx.z == 0) zero_bytes(a.k_ring + (l * a.S + slot) * RING * D_MODEL, sizeof(__half) * RING * D_MODEL);
+    else if (blockIdx.z == 1) zero_bytes(a.v_ring + (l * a.S + slot) * RING * D_MODEL, sizeof(__half) * RING * D_MODEL);
+    else zero_bytes(a.conv_cache + (l * a.S + slot) * 2 * CONV_CACHE * D_MODEL, sizeof(float) * 2 * CONV_CACHE * D_MODEL);
+    if (l == 0 && blockIdx.z == 0) {
+        zero_bytes(a.mel_overlap + slot * MEL_OVERLAP * N_MELS, sizeof(float) * MEL_OVERLAP * N_MELS);
+        zero_bytes(a.h + slot * 2 * DEC, sizeof(float) * 2 * DEC);
+        zero_bytes(a.c + slot * 2 * DEC, sizeof(float) * 2 * DEC);
+        if (threadIdx.x == 0) a.prev[slot] = BLANK;
     }
-    CUDA_CHECK(cudaMemsetAsync(m->mel_overlap + (size_t)slot * MEL_OVERLAP * N_MELS, 0, sizeof(float) * MEL_OVERLAP * N_MELS, m->st));
-    CUDA_CHECK(cudaMemsetAsync(m->dstate.h + (size_t)slot * 2 * DEC, 0, sizeof(float) * 2 * DEC, m->st));
-    CUDA_CHECK(cudaMemsetAsync(m->dstate.c + (size_t)slot * 2 * DEC, 0, sizeof(float) * 2 * DEC, m->st));
-    const int blank = BLANK;
-    CUDA_CHECK(cudaMemcpyAsync(m->dstate.prev + slot, &blank, sizeof(int), cudaMemcpyHostToDevice, m->st));
-    CUDA_CHECK(cudaMemcpyAsync(m->ws_meta, &slot, sizeof(int), cudaMemcpyHostToDevice, m->st));
-    launch_decode_refresh(m->st, m->dec, m->dstate, decode_batch(m, 1, 1));
-    CUDA_CHECK(cudaStreamSynchronize(m->st));
+}
+
+// Resets are queued (nb200_stream_create / _reset) and applied here, stream-ordered on the step's stream, by everything that
+// touches slot state next (the next step, the offline path): no host synchronisation, and a create between nb200_step_begin and
+// nb200_step_end neither waits for nor disturbs the step in flight (its kernels precede these in stream order).
+void apply_resets(nb200_model* m) {
+    if (m->reset_queue.empty()) return;
+    const int n = (int)m->reset_queue.size();
+    if (m->reset_busy) CUDA_CHECK(cudaEventSynchronize(m->reset_ev));  // the pinned list of the previous batch of resets is still being read
+    m->h_reset.reserve((size_t)m->cap_B);
+    std::copy(m->reset_queue.begin(), m->reset_queue.end(), m->h_reset.p);
+    m->reset_queue.clear();
+    cudaStream_t st = m->st;
+    CUDA_CHECK(cudaMemcpyAsync(m->d_reset, m->h_reset.p, (size_t)n * sizeof(int), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaEventRecord(m->reset_ev, st));
+    m->reset_busy = true;
+    ResetArgs ra{m->d_reset, m->k_ring, m->v_ring, m->conv_cache, m->mel_overlap, m->dstate.h, m->dstate.c, m->dstate.prev, (size_t)m->max_streams};
+    launch_k(reset_slots_kernel, dim3(n, m->n_layers, 3), dim3(256), 0, st, ra);
+    NB_KERNEL_CHECK();
+    DecodeBatch d = decode_batch(m, n, 1);
+    d.slot = m->d_reset;
+    launch_decode_refresh(st, m->dec, m->dstate, d);
+}
+
+void reset_slot(nb200_model* m, int slot) {
+    if (std::find(m->reset_queue.begin(), m->reset_queue.end(), slot) == m->reset_queue.end()) m->reset_queue.push_back(slot);
 }
 
 // ---- small copy kernels of the step ---------------------------------------------------------------------
@@ -832,6 +889,24 @@ void enqueue_joint_enc(nb200_model* m, const float* enc_out, int M) {
     }
 }
 
+// Adds the kernels launched inside a scope (this thread's counter) to the model's own total: g_launches is per thread, so
+// several models stepping on their own threads (server_loop.h ShardedWorkers) do not race on it.
+// Temporary device buffers of the synchronous entry points, freed on every path (including a throw)
+struct DevBufs {
+    std::vector<void*> v;
+    DevBufs() = default;
+    DevBufs(const DevBufs&) = delete;
+    ~DevBufs() { for (void* p : v) cudaFree(p); }
+    template <typename T> T* get(size_t n) { T* p = dalloc<T>(n); v.push_back(p); return p; }
+};
+
+struct LaunchCount {
+    nb200_model* m;
+    long long t0;
+    explicit LaunchCount(nb200_model* mm) : m(mm), t0(g_launches) {}
+    ~LaunchCount() { m->launches += g_launches - t0; }
+};
+
 struct StepCtx {
     nb200_model* m;
     ModeCtx* mc;
@@ -957,6 +1032,7 @@ void run_batch_launch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
     const Mode& md = mc->mode;
     const int B = (int)items.size(), T = md.T, capB = m->cap_B;
     cudaStream_t st = m->st;
+    LaunchCount lc(m);
 
     // ---- per-item metadata (the audio itself is already resident in the slots' device PCM rings) ----
     int* meta = m->h_meta.p;
@@ -1059,7 +1135,7 @@ void run_batch_finish(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
     m->stats.last_decoder_ms = dec_ms;
     m->stats.last_step_gpu_ms = ms02 + ms23;
     m->stats.gpu_seconds += (ms02 + ms23) * 1e-3;
-    m->stats.kernel_launches = g_launches;
+    m->stats.kernel_launches = m->launches;
 }
 
 }  // namespace
@@ -1081,6 +1157,38 @@ static int finish_inflight(nb200_model* m);
 
 const char* nb200_last_error(void) { return g_error.c_str(); }
 int nb200_version(void) { return 100; }
+
+// Host-only: parses the GGUF container (header, KVs, tensor table, bounds of every tensor) and the vocabulary the way
+// nb200_model_load does, without touching a GPU.
+int nb200_gguf_check(const char* gguf_path, char* json_out, int cap) {
+    NB_TRY
+    if (!gguf_path || !json_out || cap <= 0) throw Error("bad argument");
+    GgufFile g;
+    g.open(gguf_path);
+    std::vector<std::string> vocab;
+    const int vocab_size = (int)kv_u32(g, "nemo.vocab_size", VOCAB);
+    const char* src = load_vocab(g, vocab_size, vocab);
+    size_t bytes = 0;
+    for (auto& kv : g.tensors) bytes += kv.second.nbytes;
+    auto esc = [](const std::string& t) {
+        std::string o;
+        for (unsigned char ch : t) {
+            if (ch == '"' || ch == '\\') { o += '\\'; o += (char)ch; }
+            else if (ch < 0x20) { char b[8]; snprintf(b, sizeof b, "\\u%04x", ch); o += b; }
+            else o += (char)ch;
+        }
+        return o;
+    };
+    std::string r = "{\"tensors\": " + std::to_string(g.tensors.size()) + ", \"tensor_bytes\": " + std::to_string(bytes) +
+                    ", \"vocab_source\": \"" + src + "\", \"vocab_pieces\": " + std::to_string(vocab.size()) + ", \"n_layers\": " +
+                    std::to_string(kv_u32(g, "nemo.n_layers", 24)) + ", \"first_pieces\": [";
+    for (size_t i = 0; i < vocab.size() && i < 4; i++) r += std::string(i ? ", " : "") + "\"" + esc(vocab[i]) + "\"";
+    r += "]}";
+    if ((int)r.size() + 1 > cap) throw Error("gguf_check: buffer too small");
+    memcpy(json_out, r.c_str(), r.size() + 1);
+    return (int)r.size();
+    NB_CATCH(NB200_ERR)
+}
 
 nb200_model* nb200_model_load(const char* gguf_path, int device, int max_streams, int flags) {
     nb200_model* m = nullptr;
@@ -1308,6 +1416,7 @@ int nb200_step_begin(nb200_model* m) {
         }
     }
     flush_uploads(m);  // whatever was fed since the last flush: one copy + one scatter kernel on the copy stream
+    apply_resets(m);   // state of the streams created / reset since the last step (one kernel + one decode refresh, no host sync)
     if (m->upload_wait) {
         CUDA_CHECK(cudaStreamWaitEvent(m->st, m->upload_ev, 0));
         m->upload_wait = false;
@@ -1490,7 +1599,7 @@ int64_t nb200_stream_fetch_tap(const nb200_stream* s, int tap, float* out, int64
 int nb200_get_stats(const nb200_model* m, nb200_stats* out) {
     if (!m || !out) return NB200_ERR;
     *out = m->stats;
-    out->kernel_launches = g_launches;
+    out->kernel_launches = m->launches;
     return NB200_OK;
 }
 
@@ -1510,10 +1619,12 @@ int nb200_mel_batch(nb200_model* m, const int16_t* pcm, int n_streams, int n_sam
         m64[1 * n_streams + b] = -257;                        // a0: 256 zeros of centre padding + the pre-emphasis sample
         m64[2 * n_streams + b] = n_samples;                   // n_avail
     }
-    int16_t* d_pcm = dalloc<int16_t>((size_t)n_streams * cap);
-    int* d_i = dalloc<int>((size_t)2 * n_streams);
-    long long* d_l = dalloc<long long>(m64.size());
-    float* d_mel = dalloc<float>((size_t)n_streams * nf * N_MELS);
+    DevBufs bufs;
+    LaunchCount lc(m);
+    int16_t* d_pcm = bufs.get<int16_t>((size_t)n_streams * cap);
+    int* d_i = bufs.get<int>((size_t)2 * n_streams);
+    long long* d_l = bufs.get<long long>(m64.size());
+    float* d_mel = bufs.get<float>((size_t)n_streams * nf * N_MELS);
     CUDA_CHECK(cudaMemcpy2DAsync(d_pcm, (size_t)cap * sizeof(int16_t), pcm, (size_t)n_samples * sizeof(int16_t),
                                  (size_t)n_samples * sizeof(int16_t), n_streams, cudaMemcpyHostToDevice, m->st));
     CUDA_CHECK(cudaMemcpyAsync(d_i, slot.data(), n_streams * sizeof(int), cudaMemcpyHostToDevice, m->st));
@@ -1523,10 +1634,6 @@ int nb200_mel_batch(nb200_model* m, const int16_t* pcm, int n_streams, int n_sam
     launch_mel(m->st, m->mel_tb, mb, d_mel, n_streams, nf);
     CUDA_CHECK(cudaMemcpyAsync(mel_out, d_mel, (size_t)n_streams * nf * N_MELS * sizeof(float), cudaMemcpyDeviceToHost, m->st));
     CUDA_CHECK(cudaStreamSynchronize(m->st));
-    cudaFree(d_pcm);
-    cudaFree(d_i);
-    cudaFree(d_l);
-    cudaFree(d_mel);
     return nf;
     NB_CATCH(NB200_ERR)
 }
@@ -1555,8 +1662,10 @@ int nb200_encode_audio(nb200_model* m, const int16_t* pcm, int n_samples, int32_
     if (m->free_slots.empty()) throw Error("offline path needs one free stream slot");
     const int slot = m->free_slots.back();  // scratch: zero conv caches and decoder state, left free afterwards
     cudaStream_t st = m->st;
+    LaunchCount lc(m);
     flush_uploads(m);
     reset_slot(m, slot);
+    apply_resets(m);
     const int aq = m->act_quant ? 1 : 0;
 
     // positional table for this length: rows p + (T - 1), p = i - j in [-(T-1), T-1] (ascending p; the reference stores the
@@ -1585,7 +1694,8 @@ int nb200_encode_audio(nb200_model* m, const int16_t* pcm, int n_samples, int32_
 
     // audio + metadata of the one "stream" (b = 0)
     const int ring = 1 << 30;  // the mel kernel indexes a ring: make it larger than any utterance
-    int16_t* d_pcm = dalloc<int16_t>((size_t)n_samples + 8);
+    DevBufs bufs;
+    int16_t* d_pcm = bufs.get<int16_t>((size_t)n_samples + 8);
     std::vector<int> meta((size_t)META_ROWS * capB, 0);
     std::vector<long long> meta64((size_t)3 * capB, 0);
     meta[0 * capB] = slot;      // slot (scratch: zeroed caches)
@@ -1639,7 +1749,6 @@ int nb200_encode_audio(nb200_model* m, const int16_t* pcm, int n_samples, int32_
     CUDA_CHECK(cudaMemcpyAsync(counters, m->ws_unfinished + 6, sizeof(counters), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaMemcpyAsync(&n_tok, m->ws_tokcnt, sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
-    cudaFree(d_pcm);
     if (counters[0] != 0) throw Error("decode loop did not terminate");
     std::vector<int> words((size_t)std::max(n_tok, 1));
     CUDA_CHECK(cudaMemcpy(words.data(), m->ws_tok, (size_t)n_tok * sizeof(int), cudaMemcpyDeviceToHost));
@@ -1684,6 +1793,22 @@ int nb200_profile_enable(nb200_model* m, int on) {
     CUDA_CHECK(cudaStreamSynchronize(m->st));
     if (on) prof_report();  // drop stale records
     g_prof_on = on != 0;
+    return NB200_OK;
+    NB_CATCH(NB200_ERR)
+}
+
+int nb200_set_dup_family(nb200_model* m, const char* family) {
+    NB_TRY
+    if (!m) throw Error("null model");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    if (finish_inflight(m) < 0) return NB200_ERR;
+    CUDA_CHECK(cudaStreamSynchronize(m->st));
+    set_dup_family(family);
+    for (auto* gm : {&m->enc_graphs, &m->dec_graphs}) {  // the captured graphs hold the old launch sequence
+        for (auto& kv : *gm)
+            if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+        gm->clear();
+    }
     return NB200_OK;
     NB_CATCH(NB200_ERR)
 }
@@ -1796,9 +1921,10 @@ int nb200_debug_matmul(nb200_model* m, const char* tensor_name, const float* x, 
     const int K = W.K, N = W.rows;
     if (K % 1024 != 0) throw Error("debug_matmul supports K multiple of 1024");
     const int Mp = (M + 127) / 128 * 128;
-    float* dx = dalloc<float>((size_t)M * K);
-    __half* dx16 = dalloc<__half>((size_t)Mp * K);
-    float* dy = dalloc<float>((size_t)M * N);
+    DevBufs bufs;
+    float* dx = bufs.get<float>((size_t)M * K);
+    __half* dx16 = bufs.get<__half>((size_t)Mp * K);
+    float* dy = bufs.get<float>((size_t)M * N);
     CUDA_CHECK(cudaMemsetAsync(dx16, 0, (size_t)Mp * K * sizeof(__half), m->st));
     CUDA_CHECK(cudaMemcpyAsync(dx, x, (size_t)M * K * sizeof(float), cudaMemcpyHostToDevice, m->st));
     launch_cast_f16(m->st, dx, dx16, m->act_quant ? 1 : 0, M, K);
@@ -1822,9 +1948,85 @@ int nb200_debug_matmul(nb200_model* m, const char* tensor_name, const float* x, 
         CUDA_CHECK(cudaMemcpyAsync(y, dy, (size_t)M * N * sizeof(float), cudaMemcpyDeviceToHost, m->st));
     }
     CUDA_CHECK(cudaStreamSynchronize(m->st));
-    cudaFree(dx);
-    cudaFree(dx16);
-    cudaFree(dy);
+    return NB200_OK;
+    NB_CATCH(NB200_ERR)
+}
+
+// The step's GEMM + fused epilogue on one of the model's matrices, exactly as enqueue_layers launches it (same operand preparation,
+// same tile selection for this M, same epilogue class), for the parity tests of the shapes the benchmark runs.
+int nb200_debug_gemm(nb200_model* m, const char* tensor_name, const float* x, int M, int epi_kind, float* y, float* y_ln, int* cfg_out) {
+    NB_TRY
+    if (!m || !tensor_name || !x || !y || M <= 0) throw Error("bad argument");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    if (finish_inflight(m) < 0) return NB200_ERR;
+    auto it = m->by_name.find(tensor_name);
+    if (it == m->by_name.end()) throw Error(std::string("no such encoder matrix: ") + tensor_name);
+    Operand W;
+    operand_init(W, it->second.ptr, it->second.rows, it->second.K);
+    const int K = W.K, N = W.rows, aq = m->act_quant ? 1 : 0;
+    if (K % 1024 != 0) throw Error("debug_gemm supports K multiple of 1024");
+    if (epi_kind == EPI_GLU && !it->second.glu_interleaved) throw Error("debug_gemm: the GLU epilogue needs pointwise_conv1 (value / gate rows interleaved)");
+    if (epi_kind == EPI_PARTIAL && N != D_MODEL) throw Error("debug_gemm: the split-K + LayerNorm class needs N = 1024");
+    const int Mp = (M + 127) / 128 * 128;
+    const int n_out = epi_kind == EPI_GLU ? N / 2 : N;
+    DevBufs bufs;
+    float* dx = bufs.get<float>((size_t)M * K);
+    __half* dx16 = bufs.get<__half>((size_t)Mp * K);
+    cudaStream_t st = m->st;
+    CUDA_CHECK(cudaMemsetAsync(dx16, 0, (size_t)Mp * K * sizeof(__half), st));
+    CUDA_CHECK(cudaMemcpyAsync(dx, x, (size_t)M * K * sizeof(float), cudaMemcpyHostToDevice, st));
+    launch_cast_f16(st, dx, dx16, aq, M, K);
+    Operand A;
+    operand_init(A, dx16, Mp, K);
+    EpiParams ep;
+    ep.ldo = n_out;
+    const int max_splits = epi_kind == EPI_PARTIAL ? m->part_max_splits : 1;
+    const bool packed = epi_kind == EPI_STORE_F16 || epi_kind == 6 || epi_kind == EPI_GLU;
+    const GemmConfig c = gemm_pick_config(M, N, K, max_splits, packed ? 64 : 32);
+    if (cfg_out) { cfg_out[0] = c.bn; cfg_out[1] = c.splits; cfg_out[2] = c.cg; cfg_out[3] = c.ctas; }
+    std::vector<float> host((size_t)M * n_out);
+    if (epi_kind == EPI_STORE_F16 || epi_kind == 6) {  // linear1 + SiLU (+ re-quantise) -> fp16, or a plain fp16 store (q | k | v)
+        __half* d16 = bufs.get<__half>((size_t)Mp * N);
+        ep.kind = EPI_STORE_F16; ep.out_f16 = d16;
+        if (epi_kind == EPI_STORE_F16) { ep.act = ACT_SILU; ep.act_quant = aq; }
+        gemm(st, A, W, M, ep, m->simt);
+        std::vector<__half> h16((size_t)M * N);
+        CUDA_CHECK(cudaMemcpyAsync(h16.data(), d16, h16.size() * sizeof(__half), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        for (size_t i = 0; i < h16.size(); i++) y[i] = __half2float(h16[i]);
+        return NB200_OK;
+    }
+    if (epi_kind == EPI_PARTIAL) {  // split-K partial planes, then the step's LayerNorm adds them to a zero residual stream: y = sum, y_ln = fp16(fq(LN(sum)))
+        const size_t plane = (size_t)Mp * N;
+        float* dpart = bufs.get<float>((size_t)max_splits * plane);
+        float* dres = bufs.get<float>(plane);
+        __half* dln = bufs.get<__half>(plane);
+        std::vector<float> ones(N, 1.0f), zeros(N, 0.0f);
+        float* dg = bufs.get<float>(N);
+        float* db = bufs.get<float>(N);
+        CUDA_CHECK(cudaMemcpyAsync(dg, ones.data(), N * sizeof(float), cudaMemcpyHostToDevice, st));
+        CUDA_CHECK(cudaMemcpyAsync(db, zeros.data(), N * sizeof(float), cudaMemcpyHostToDevice, st));
+        CUDA_CHECK(cudaMemsetAsync(dres, 0, plane * sizeof(float), st));
+        ep.kind = EPI_PARTIAL; ep.out_f32 = dpart; ep.split_stride = plane;
+        ResidualIn rin;
+        rin.partials = dpart; rin.stride = plane; rin.alpha = 1.0f;
+        rin.nsplit = gemm(st, A, W, M, ep, m->simt, max_splits);
+        launch_layernorm(st, dres, dg, db, nullptr, nullptr, nullptr, dln, aq, M, rin);
+        CUDA_CHECK(cudaMemcpyAsync(y, dres, (size_t)M * N * sizeof(float), cudaMemcpyDeviceToHost, st));
+        std::vector<__half> h16((size_t)M * N);
+        CUDA_CHECK(cudaMemcpyAsync(h16.data(), dln, h16.size() * sizeof(__half), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        if (y_ln) for (size_t i = 0; i < h16.size(); i++) y_ln[i] = __half2float(h16[i]);
+        return NB200_OK;
+    }
+    float* dy = bufs.get<float>((size_t)Mp * n_out);
+    ep.out_f32 = dy;
+    if (epi_kind == EPI_GLU) ep.kind = EPI_GLU;
+    else if (epi_kind == EPI_STORE) ep.kind = EPI_STORE;
+    else throw Error("debug_gemm: epilogue kind must be 0 (f32), 1 (SiLU -> f16), 4 (GLU), 5 (split-K + LayerNorm) or 6 (f16)");
+    gemm(st, A, W, M, ep, m->simt);
+    CUDA_CHECK(cudaMemcpyAsync(y, dy, (size_t)M * n_out * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
     return NB200_OK;
     NB_CATCH(NB200_ERR)
 }

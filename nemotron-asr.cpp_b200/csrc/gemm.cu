@@ -7,7 +7,7 @@
 
 namespace nb {
 
-long long g_launches = 0;
+thread_local long long g_launches = 0;
 
 // ------------------------------------------------------------------------------------------------
 // PTX wrappers (sm_100a)
@@ -504,7 +504,7 @@ static void launch_tc(cudaStream_t st, const Operand& A, const Operand& W, const
 // One tile (x K/splits) per CTA or CTA pair, one wave wherever possible. Cost model in SM clocks per CTA:
 //   k-block time = max(MMA issue 2*BN clk, operand bytes (128 + BN/cg rows of 128 B) at the L2->SM bandwidth shared by the active CTAs)
 //   + a fixed prologue/epilogue cost, times the number of waves; split-K pays for writing and re-reading its partials.
-static int g_force_bn = 0, g_force_splits = 1;
+static thread_local int g_force_bn = 0, g_force_splits = 1;  // tuning runs force a configuration on their own thread only
 void gemm_force_config(int bn, int splits) {
     g_force_bn = bn;
     g_force_splits = splits < 1 ? 1 : splits;

@@ -9,13 +9,14 @@
 
 namespace nb {
 
-bool g_prof_on = false;
+thread_local bool g_prof_on = false;
 bool g_pdl = getenv("NB200_NO_PDL") == nullptr;
 
-bool dup_family(const char* family) {
-    static const char* want = getenv("NB200_DUP");
-    return want != nullptr && std::string(want) == family;
+namespace {
+thread_local std::string g_dup = getenv("NB200_DUP") ? getenv("NB200_DUP") : "";
 }
+bool dup_family(const char* family) { return !g_dup.empty() && g_dup == family; }
+void set_dup_family(const char* family) { g_dup = family ? family : ""; }
 
 namespace {
 struct Rec {
@@ -23,8 +24,8 @@ struct Rec {
     double flops, bytes;
     cudaEvent_t a, b;
 };
-std::vector<Rec> g_recs;
-std::vector<cudaEvent_t> g_pool;
+thread_local std::vector<Rec> g_recs;
+thread_local std::vector<cudaEvent_t> g_pool;
 
 cudaEvent_t get_event() {
     if (!g_pool.empty()) {

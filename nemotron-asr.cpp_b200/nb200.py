@@ -43,6 +43,7 @@ SYMBOLS = {
     "nb200_last_error": (C.c_char_p, []),
     "nb200_version": (C.c_int, []),
     "nb200_model_load": (C.c_void_p, [C.c_char_p, C.c_int, C.c_int, C.c_int]),
+    "nb200_gguf_check": (C.c_int, [C.c_char_p, C.c_char_p, C.c_int]),
     "nb200_model_free": (None, [C.c_void_p]),
     "nb200_model_info": (C.c_int, [C.c_void_p, C.POINTER(Info)]),
     "nb200_model_token": (C.c_char_p, [C.c_void_p, C.c_int32]),
@@ -76,9 +77,11 @@ SYMBOLS = {
     "nb200_timer_start": (C.c_int, [C.c_void_p]),
     "nb200_timer_stop": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "nb200_profile_enable": (C.c_int, [C.c_void_p, C.c_int]),
+    "nb200_set_dup_family": (C.c_int, [C.c_void_p, C.c_char_p]),
     "nb200_profile_report": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int]),
     "nb200_mel_batch": (C.c_int, [C.c_void_p, _I16P, C.c_int, C.c_int, _F32P]),
     "nb200_debug_matmul": (C.c_int, [C.c_void_p, C.c_char_p, _F32P, C.c_int, _F32P]),
+    "nb200_debug_gemm": (C.c_int, [C.c_void_p, C.c_char_p, _F32P, C.c_int, C.c_int, _F32P, _F32P, _I32P]),
     "nb200_bench_gemm": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double),
                                    C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "nb200_trace_gemm": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
@@ -111,6 +114,15 @@ def _err() -> str:
 
 def _ptr(a: np.ndarray, typ):
     return a.ctypes.data_as(typ)
+
+
+def gguf_check(path: str) -> dict:
+    """Host-only parse of a GGUF file the way nb200_model_load reads it (nb200_gguf_check); raises NB200Error on a malformed file."""
+    import json
+    buf = C.create_string_buffer(1 << 14)
+    if lib().nb200_gguf_check(os.fsencode(path), buf, len(buf)) < 0:
+        raise NB200Error(_err())
+    return json.loads(buf.value.decode())
 
 
 class Model:
@@ -170,6 +182,11 @@ class Model:
         if n < 0:
             raise NB200Error(_err())
         return n
+
+    def set_dup_family(self, family: "str | None"):
+        """nb200_set_dup_family: launch every kernel of `family` twice inside the step (marginal in-graph cost); None = off."""
+        if lib().nb200_set_dup_family(self._h, family.encode() if family else None) < 0:
+            raise NB200Error(_err())
 
     def stats(self) -> Stats:
         st = Stats()
@@ -270,6 +287,20 @@ class Model:
         if lib().nb200_debug_matmul(self._h, tensor_name.encode(), _ptr(x, _F32P), x.shape[0], _ptr(y, _F32P)) < 0:
             raise NB200Error(_err())
         return y
+
+
+    EPI_F32, EPI_SILU_F16, EPI_GLU, EPI_SPLITK_LN, EPI_F16 = 0, 1, 4, 5, 6
+
+    def debug_gemm(self, tensor_name: str, x: np.ndarray, n_out: int, epi_kind: int):
+        """The step's GEMM + fused epilogue on one matrix (nb200_debug_gemm). -> (y [M, n_out], y_ln or None, cfg dict)."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        y = np.zeros((x.shape[0], n_out), np.float32)
+        y_ln = np.zeros_like(y) if epi_kind == self.EPI_SPLITK_LN else None
+        cfg = np.zeros(4, np.int32)
+        if lib().nb200_debug_gemm(self._h, tensor_name.encode(), _ptr(x, _F32P), x.shape[0], epi_kind, _ptr(y, _F32P),
+                                  _ptr(y_ln, _F32P) if y_ln is not None else None, _ptr(cfg, _I32P)) < 0:
+            raise NB200Error(_err())
+        return y, y_ln, {"bn": int(cfg[0]), "splits": int(cfg[1]), "cta_group": int(cfg[2]), "ctas": int(cfg[3])}
 
 
 class BatchIO:

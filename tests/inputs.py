@@ -40,6 +40,16 @@ STREAM_CASES = (
 )
 
 
+# The full-depth model (24 layers, what the benchmark runs): (variant, rc, pcm seed, seconds). The F32 file pins the 24-layer
+# stack against the reference (fp16-operand error through 24 layers); the Q8_0 file is stored from both ISA builds so the
+# reference's own self-noise at full depth is known (tests/golden/make_golden_deep.py).
+DEEP_LAYERS = 24
+DEEP_CASES = (
+    ("f32dq", 13, 71, 3.6),
+    ("q8_0", 13, 71, 3.6),
+)
+
+
 # the converter's other on-disk formats: checked against the compiled reference on the GPU path only
 FORMAT_CASES = (
     ("f16", 13, 11, 3.0),
@@ -78,14 +88,17 @@ def offline_name(variant: str, seed: int, lang) -> str:
     return f"offline_{variant}{'_' + lang if lang else ''}_s{seed}.npz"
 
 
-def gguf_path(variant: str, layers: int = TEST_LAYERS, blank_gain: float | None = None, multilingual: bool = False) -> str:
+def gguf_path(variant: str, layers: int = TEST_LAYERS, blank_gain: float | None = None, multilingual: bool = False,
+              decoder: str = "bistable", legacy_vocab: bool = False, res_scale: float = 1.0) -> str:
     import make_random_gguf as mg
     TMP.mkdir(parents=True, exist_ok=True)
-    tag = ("" if blank_gain is None else f"_bg{blank_gain:g}") + ("_ml" if multilingual else "")
+    tag = ("" if blank_gain is None else f"_bg{blank_gain:g}") + ("_ml" if multilingual else "") + \
+          ("" if decoder == "bistable" else f"_{decoder}") + ("_legacyvocab" if legacy_vocab else "") + \
+          ("" if res_scale == 1.0 else f"_rs{res_scale:g}")
     p = TMP / f"L{layers}_{variant}_s{SEED}{tag}.gguf"
     if not p.exists():
         tmp = p.with_suffix(f".tmp{os.getpid()}")
-        mg.write_gguf(str(tmp), SEED, layers, variant, blank_gain, multilingual)
+        mg.write_gguf(str(tmp), SEED, layers, variant, blank_gain, multilingual, decoder=decoder, legacy_vocab=legacy_vocab, res_scale=res_scale)
         os.replace(tmp, p)
     return str(p)
 

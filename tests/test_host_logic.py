@@ -132,3 +132,105 @@ def test_server_loop_header_compiles(lib_built, tmp_path):
                     str(root / "tests" / "server_loop_test.cpp"), "-o", str(exe), "-L", str(pkg), "-lnemob200", f"-Wl,-rpath,{pkg}", "-lpthread"],
                    check=True)
     assert exe.exists()
+
+
+# ---- GGUF container: the host-only parser nb200_model_load uses (nb200_gguf_check needs no GPU) --------------------------
+def _tiny_gguf(n_tensors=1, n_kv=1, nd=1, dims=(64,), ttype=0, data_bytes=256, str_len=None, vocab_key=b"tokenizer.vocab_list",
+               legacy_blob=None):
+    """A minimal GGUF v3 image: one vocabulary KV and one tensor "x"; every field of the header can be corrupted."""
+    import struct
+
+    def s(b, n=None):
+        return struct.pack("<Q", len(b) if n is None else n) + b
+
+    out = b"GGUF" + struct.pack("<I", 3) + struct.pack("<q", n_tensors) + struct.pack("<q", n_kv)
+    if legacy_blob is not None:
+        out += s(b"tokenizer.vocab") + struct.pack("<I", 8) + s(legacy_blob)
+    else:
+        out += s(vocab_key) + struct.pack("<I", 9) + struct.pack("<I", 8) + struct.pack("<Q", 2) + s(b"a", str_len) + s(b"bc")
+    out += s(b"x") + struct.pack("<I", nd)
+    for d in dims:
+        out += struct.pack("<q", d)
+    out += struct.pack("<i", ttype) + struct.pack("<Q", 0)
+    out += b"\0" * ((len(out) + 31) // 32 * 32 - len(out))
+    return out + b"\0" * data_bytes
+
+
+def test_gguf_check_accepts_and_rejects(lib_built, tmp_path):
+    """Well-formed files parse; truncated or crafted headers (wrapping 64-bit lengths, absurd counts, negative or overflowing
+    dimensions, a quantised tensor that is not a whole number of blocks, more than 4 dimensions, data outside the file) are
+    refused with an error instead of reading outside the mapping."""
+    nb200 = lib_built
+
+    def check(img):
+        p = tmp_path / "t.gguf"
+        p.write_bytes(img)
+        return nb200.gguf_check(str(p))
+
+    ok = check(_tiny_gguf())
+    assert ok["tensors"] == 1 and ok["tensor_bytes"] == 256 and ok["vocab_source"] == "tokenizer.vocab_list" and ok["first_pieces"] == ["a", "bc"]
+    assert check(_tiny_gguf(ttype=8, dims=(64,), data_bytes=68))["tensor_bytes"] == 68  # 2 Q8_0 blocks
+    bad = {
+        "truncated": _tiny_gguf()[:40],
+        "string length wraps": _tiny_gguf(str_len=2 ** 64 - 8),
+        "string past the end": _tiny_gguf(str_len=1 << 40),
+        "absurd kv count": _tiny_gguf(n_kv=2 ** 62),
+        "negative tensor count": _tiny_gguf(n_tensors=-5),
+        "negative dimension": _tiny_gguf(dims=(-64,)),
+        "dimension product overflows": _tiny_gguf(nd=3, dims=(2 ** 31, 2 ** 31, 2 ** 31)),
+        "five dimensions": _tiny_gguf(nd=5, dims=(2, 2, 2, 2, 2)),
+        "q8_0 with a partial block": _tiny_gguf(ttype=8, dims=(40,)),
+        "data outside the file": _tiny_gguf(dims=(1 << 20,)),
+        "unknown tensor type": _tiny_gguf(ttype=77),
+        "no vocabulary": _tiny_gguf(vocab_key=b"tokenizer.something"),
+        "bad magic": b"GGUX" + _tiny_gguf()[4:],
+    }
+    for what, img in bad.items():
+        with pytest.raises(nb200.NB200Error):
+            check(img)
+            pytest.fail(f"accepted a malformed file: {what}")
+    with pytest.raises(nb200.NB200Error, match="cannot open"):
+        nb200.gguf_check(str(tmp_path / "missing.gguf"))
+
+
+def test_legacy_vocab_blob(lib_built, tmp_path):
+    """The loader's fallback vocabulary (src/nemo-ggml.cpp:156-165): `tokenizer.vocab` = vocab_size - 1 pieces of 8 bytes,
+    NUL-padded. The generator's --legacy-vocab file must read back the pieces of the string-array file (cut to 8 bytes)."""
+    nb200 = lib_built
+    tiny = tmp_path / "l.gguf"
+    tiny.write_bytes(_tiny_gguf(legacy_blob=b"ab\0\0\0\0\0\0" + "▁t3".encode() + b"\0\0\0" + b"12345678" + b"tail"))
+    d = nb200.gguf_check(str(tiny))
+    assert d["vocab_source"] == "tokenizer.vocab" and d["vocab_pieces"] == 3 and d["first_pieces"] == ["ab", "▁t3", "12345678"]
+    import make_random_gguf as mg
+    a, b = tmp_path / "list.gguf", tmp_path / "blob.gguf"
+    mg.write_gguf(str(a), 7, 0, "f32")
+    mg.write_gguf(str(b), 7, 0, "f32", legacy_vocab=True)
+    da, db = nb200.gguf_check(str(a)), nb200.gguf_check(str(b))
+    assert da["vocab_source"] == "tokenizer.vocab_list" and db["vocab_source"] == "tokenizer.vocab"
+    assert da["vocab_pieces"] == db["vocab_pieces"] == 1024 and da["first_pieces"] == db["first_pieces"] == ["▁t0", "t1", "t2", "▁t3"]
+    assert da["tensors"] == db["tensors"] and da["tensor_bytes"] == db["tensor_bytes"] and da["n_layers"] == 0
+
+
+def test_bench_decoder_profile():
+    """bench.py's random-init decoder (make_random_gguf decoder="stationary" + the committed encoder-mean calibration): greedy
+    decode by the oracle over seeded stand-ins for the varying part of the encoder output must give the profile of real speech
+    (a fraction of a token per frame, hardly ever more than 3 symbols on a frame), not the all-blank / 10-symbol-cap pair."""
+    import make_random_gguf as mg
+    m = mg.encoder_mean(inputs.SEED, 24, 0.1)
+    assert m is not None and m.shape == (1024,), "tools/decoder_calibration.npz lost its entry for the benchmark model"
+    dec = {n: a for n, a, _ in mg.tensor_list(inputs.SEED, 24, 6.0, "stationary", 0.1) if n.startswith(("decoder.", "joint."))}
+    o = no.StreamOracle({"nemo.n_layers": 0, "nemo.n_heads": 8, "nemo.d_head": 128, "nemo.d_model": 1024, "nemo.att_left_context": 70,
+                         "nemo.vocab_size": 1025}, dict({"preprocessor.featurizer.fb": np.zeros((128, 257), np.float32),
+                                                         "preprocessor.featurizer.window": np.zeros(400, np.float32)}, **dec), 13)
+    rng = np.random.default_rng(3)
+    low = rng.standard_normal((16, 1024)).astype(np.float32)  # the varying part lives in a few directions and changes smoothly
+    hist, n, frames = np.zeros(11, int), 0, 600
+    state = np.zeros(16, np.float32)
+    for f in range(frames):
+        state = 0.6 * state + 0.8 * rng.standard_normal(16).astype(np.float32)
+        enc = m + 0.03 * (state @ low) + 0.08 * rng.standard_normal(1024).astype(np.float32)  # ~5 from the mean, like the measured frames
+        k = len(o.decode_frame(enc.astype(np.float32)))
+        hist[k] += 1
+        n += k
+    print(f"stationary decoder on synthetic encoder frames: {n / frames:.3f} tokens/frame, histogram {hist.tolist()}")
+    assert 0.03 < n / frames < 1.0 and hist[4:].sum() <= 0.02 * frames and hist[10] <= 2

@@ -130,9 +130,13 @@ def prompt_tensors(seed: int):
     yield "prompt_kernel.2.bias", normal(s, "prompt_kernel.2.bias", (D_MODEL,), 0.1), False
 
 
-def tensor_list(seed: int, n_layers: int, blank_gain: float | None = None):
-    """Yields (name, float32 array in PyTorch shape order, quantisable?)."""
+def tensor_list(seed: int, n_layers: int, blank_gain: float | None = None, decoder: str = "bistable", res_scale: float = 1.0):
+    """Yields (name, float32 array in PyTorch shape order, quantisable?). decoder: see DECODERS below. res_scale multiplies the
+    output projection of every residual branch (FFN linear2, attention linear_out, pointwise_conv2), the usual depth-scaled
+    initialisation: with 1.0 the output of a 24-layer random stack is an almost constant vector (96 random branch outputs swamp
+    the frontend's features; adjacent frames correlate at 0.997), with ~0.1 it still follows the audio frame by frame."""
     s = seed
+    rs = np.float32(res_scale)
     yield "preprocessor.featurizer.fb", mel_filterbank()[None], False
     n = np.arange(400, dtype=np.float64)
     yield "preprocessor.featurizer.window", (0.5 - 0.5 * np.cos(2 * np.pi * n / 399)).astype(np.float32), False
@@ -157,9 +161,10 @@ def tensor_list(seed: int, n_layers: int, blank_gain: float | None = None):
             yield p + nm + ".bias", normal(s, p + nm + ".bias", (D_MODEL,), 0.02), False
         for ff in ("feed_forward1", "feed_forward2"):
             yield p + ff + ".linear1.weight", normal(s, p + ff + ".linear1.weight", (D_FF, D_MODEL), (1.0 / D_MODEL) ** 0.5), True
-            yield p + ff + ".linear2.weight", normal(s, p + ff + ".linear2.weight", (D_MODEL, D_FF), (1.0 / D_FF) ** 0.5), True
+            yield p + ff + ".linear2.weight", normal(s, p + ff + ".linear2.weight", (D_MODEL, D_FF), (1.0 / D_FF) ** 0.5) * rs, True
         for nm in ("linear_q", "linear_k", "linear_v", "linear_pos", "linear_out"):
-            yield p + f"self_attn.{nm}.weight", normal(s, p + f"self_attn.{nm}.weight", (D_MODEL, D_MODEL), (1.0 / D_MODEL) ** 0.5), True
+            yield p + f"self_attn.{nm}.weight", normal(s, p + f"self_attn.{nm}.weight", (D_MODEL, D_MODEL), (1.0 / D_MODEL) ** 0.5) * \
+                (rs if nm == "linear_out" else np.float32(1.0)), True
         yield p + "self_attn.pos_bias_u", normal(s, p + "self_attn.pos_bias_u", (N_HEADS, D_HEAD), 0.3), False
         yield p + "self_attn.pos_bias_v", normal(s, p + "self_attn.pos_bias_v", (N_HEADS, D_HEAD), 0.3), False
         yield p + "conv.pointwise_conv1.weight", normal(s, p + "conv.pointwise_conv1.weight", (2 * D_MODEL, D_MODEL), (1.0 / D_MODEL) ** 0.5), True
@@ -167,25 +172,50 @@ def tensor_list(seed: int, n_layers: int, blank_gain: float | None = None):
         yield p + "conv.depthwise_conv.weight", normal(s, p + "conv.depthwise_conv.weight", (KERNEL, D_MODEL), (1.0 / KERNEL) ** 0.5), False
         yield p + "conv.batch_norm.weight", 1.0 + normal(s, p + "conv.batch_norm.weight", (D_MODEL,), 0.05), False
         yield p + "conv.batch_norm.bias", normal(s, p + "conv.batch_norm.bias", (D_MODEL,), 0.02), False
-        yield p + "conv.pointwise_conv2.weight", normal(s, p + "conv.pointwise_conv2.weight", (D_MODEL, D_MODEL), (1.0 / D_MODEL) ** 0.5), True
+        yield p + "conv.pointwise_conv2.weight", normal(s, p + "conv.pointwise_conv2.weight", (D_MODEL, D_MODEL), (1.0 / D_MODEL) ** 0.5) * rs, True
 
     d = "decoder.prediction."
+    wo = normal(s, "joint.joint_net.2.weight", (VOCAB, JOINT), 1.0 / JOINT ** 0.5)
     emb = normal(s, d + "embed.weight", (VOCAB, DEC), 1.0)
+    if decoder == "stationary":
+        emb = wo.copy()  # the prediction network carries the previous token's OUTPUT row through to joint.pred (see DECODERS)
     emb[VOCAB - 1] = 0.0  # blank/pad row is zero in a trained model
     yield d + "embed.weight", emb, False
     b = 1.0 / DEC ** 0.5
     for l in (0, 1):
         for nm, shp in (("weight_ih", (4 * DEC, DEC)), ("weight_hh", (4 * DEC, DEC)), ("bias_ih", (4 * DEC,)), ("bias_hh", (4 * DEC,))):
             name = d + f"dec_rnn.lstm.{nm}_l{l}"
-            yield name, uniform(s, name, shp, LSTM_BIAS if nm.startswith("bias") else b), False
-    yield "joint.enc.weight", normal(s, "joint.enc.weight", (JOINT, D_MODEL), (1.0 / D_MODEL) ** 0.5), False
-    yield "joint.enc.bias", normal(s, "joint.enc.bias", (JOINT,), 0.1), False
-    yield "joint.pred.weight", normal(s, "joint.pred.weight", (JOINT, DEC), PRED_GAIN / DEC ** 0.5), False
+            w = uniform(s, name, shp, LSTM_BIAS if nm.startswith("bias") else b)
+            if decoder == "stationary":  # gate order i, f, g, o (src/nemo-ggml.cpp:601-618)
+                w = w * np.float32(STATIONARY_NOISE)
+                if nm == "weight_ih":
+                    w[2 * DEC:3 * DEC] += np.float32(STATIONARY_PASS) * np.eye(DEC, dtype=np.float32)  # g = tanh(pass * x): x passes through
+                if nm == "bias_ih":
+                    w[0:DEC] += 4.0            # input gates open
+                    # layer 0 remembers: c = MEMORY c + tanh(PASS embed[prev]) accumulates the rows of the recently emitted tokens
+                    # (state only moves on an emission); layer 1 passes its input through (forget gates shut)
+                    w[DEC:2 * DEC] += np.float32(np.log(STATIONARY_MEMORY / (1.0 - STATIONARY_MEMORY)) if l == 0 else -4.0)
+                    w[3 * DEC:4 * DEC] += 4.0  # output gates open
+            yield name, w, False
+    we = normal(s, "joint.enc.weight", (JOINT, D_MODEL), (1.0 / D_MODEL) ** 0.5)
+    be = normal(s, "joint.enc.bias", (JOINT,), 0.1)
+    if decoder == "stationary":
+        # fold the encoder output's time-average (a measured constant of this random model, tests/golden/calibrate_bench_decoder.py) into the
+        # bias and amplify what is left: the joint then sees the part of the encoder output that follows the audio
+        m = encoder_mean(seed, n_layers, res_scale)
+        if m is not None:
+            we = we * np.float32(STATIONARY_ENC_GAIN)
+            be = (be - we @ m).astype(np.float32)
+    yield "joint.enc.weight", we, False
+    yield "joint.enc.bias", be, False
+    wp = normal(s, "joint.pred.weight", (JOINT, DEC), PRED_GAIN / DEC ** 0.5)
+    if decoder == "stationary":  # pred = -SUPPRESS * (the previous token's joint_net row) + a small random part
+        wp = wp * np.float32(STATIONARY_NOISE) - np.float32(STATIONARY_SUPPRESS / STATIONARY_PASS ** 2) * np.eye(JOINT, dtype=np.float32)
+    yield "joint.pred.weight", wp, False
     yield "joint.pred.bias", normal(s, "joint.pred.bias", (JOINT,), 0.1), False
     # Scale-free blank: logit_blank = BLANK_GAIN * mean(relu(hidden)) grows with the hidden norm exactly like the
     # largest non-blank logit does, so the per-step blank probability is about the same in every decoder state
     # (a plain blank bias gave either all-blank or runaway 10-symbol loops once the LSTM state left zero).
-    wo = normal(s, "joint.joint_net.2.weight", (VOCAB, JOINT), 1.0 / JOINT ** 0.5)
     wo[VOCAB - 1] = (BLANK_GAIN if blank_gain is None else blank_gain) / JOINT
     yield "joint.joint_net.2.weight", wo, False
     ob = normal(s, "joint.joint_net.2.bias", (VOCAB,), 0.1)
@@ -200,6 +230,36 @@ def tensor_list(seed: int, n_layers: int, blank_gain: float | None = None):
 BLANK_GAIN = 5.9
 PRED_GAIN = 4.0
 LSTM_BIAS = 0.5
+# DECODERS. "bistable": the plain random LSTM above (parity fixtures; token-heavy at gain 5.9, all-blank from ~6.0: once a frame
+# emits, the hidden vector of its next symbol step is nearly the same, so it emits again up to the 10-symbol cap).
+# "stationary" (bench.py): the architecture and every tensor shape are unchanged, but the prediction network is initialised so
+# that it does what a trained RNNT predictor does after an emission - suppress the token just emitted. embed[v] = the
+# joint_net row of v; both LSTM layers pass their input through (input / output gates open, forget gates shut, g = tanh(PASS x),
+# recurrent weights ~0), joint.pred = -(SUPPRESS / PASS^2) I + noise: pred(prev) ~ -SUPPRESS * W_out[prev], which lowers the
+# logit of prev by ~SUPPRESS |W_out[prev]|^2 / 2 and leaves the other tokens alone. Emissions then follow the encoder frame
+# (through joint.enc), a second symbol on the same frame needs the runner-up to beat the blank as well, and the statistics are
+# the same in every decoder state (no drift into all-blank or 10-symbols-per-frame regimes). The blank gain sets the rate:
+# tests/golden/calibrate_bench_decoder.py. All other weights keep a random part (NOISE) so no product is trivially zero.
+STATIONARY_NOISE = 0.1
+STATIONARY_PASS = 0.5
+STATIONARY_SUPPRESS = 1.0
+STATIONARY_MEMORY = 0.8
+STATIONARY_ENC_GAIN = 4.0
+
+
+def calibration_key(seed: int, n_layers: int, res_scale: float) -> str:
+    return f"enc_mean_s{seed}_L{n_layers}_rs{res_scale:g}"
+
+
+def encoder_mean(seed: int, n_layers: int, res_scale: float):
+    """Measured time-average of the encoder output of the model (seed, n_layers, res_scale), or None if it was never measured."""
+    from pathlib import Path
+    p = Path(__file__).resolve().parent / "decoder_calibration.npz"
+    if not p.exists():
+        return None
+    d = np.load(p)
+    k = calibration_key(seed, n_layers, res_scale)
+    return d[k].astype(np.float32) if k in d.files else None
 
 
 def _w_str(f, sbytes: bytes):
@@ -208,8 +268,10 @@ def _w_str(f, sbytes: bytes):
 
 
 def write_gguf(path: str, seed: int = 1234, n_layers: int = 24, variant: str = "q8_0", blank_gain: float | None = None,
-               multilingual: bool = False) -> dict:
-    assert variant in ("q8_0", "f32", "f32dq", "f16", "q4_0")
+               multilingual: bool = False, decoder: str = "bistable", legacy_vocab: bool = False, res_scale: float = 1.0) -> dict:
+    """legacy_vocab: write the vocabulary as the old `tokenizer.vocab` blob of fixed 8-byte NUL-padded pieces instead of the
+    `tokenizer.vocab_list` string array (the loader's fallback branch, /root/reference/src/nemo-ggml.cpp:156-165)."""
+    assert variant in ("q8_0", "f32", "f32dq", "f16", "q4_0") and decoder in ("bistable", "stationary")
     vocab = [("▁" if i % 3 == 0 else "") + f"t{i}" for i in range(VOCAB - 1)]
     hparams = [("nemo.n_mels", N_MELS), ("nemo.d_model", D_MODEL), ("nemo.n_heads", N_HEADS), ("nemo.d_head", D_HEAD),
                ("nemo.d_ff", D_FF), ("nemo.n_layers", n_layers), ("nemo.kernel_size", KERNEL), ("nemo.vocab_size", VOCAB),
@@ -218,7 +280,7 @@ def write_gguf(path: str, seed: int = 1234, n_layers: int = 24, variant: str = "
     infos, off = [], 0
     blobs = []
     import itertools
-    for name, arr, quantisable in itertools.chain(tensor_list(seed, n_layers, blank_gain), prompt_tensors(seed) if multilingual else ()):
+    for name, arr, quantisable in itertools.chain(tensor_list(seed, n_layers, blank_gain, decoder, res_scale), prompt_tensors(seed) if multilingual else ()):
         arr = np.ascontiguousarray(arr, dtype=np.float32)
         if quantisable and variant == "q8_0":
             data, typ = q8_0_bytes(arr), GGML_Q8_0
@@ -241,10 +303,14 @@ def write_gguf(path: str, seed: int = 1234, n_layers: int = 24, variant: str = "
         f.write(struct.pack("<q", len(hparams) + 3 + (2 if multilingual else 0)))
         for k, v in (("general.architecture", "nemo"), ("general.name", f"random-init-{variant}-L{n_layers}-s{seed}")):
             _w_str(f, k.encode()); f.write(struct.pack("<I", 8)); _w_str(f, v.encode())
-        _w_str(f, b"tokenizer.vocab_list"); f.write(struct.pack("<I", 9)); f.write(struct.pack("<I", 8))
-        f.write(struct.pack("<Q", len(vocab)))
-        for t in vocab:
-            _w_str(f, t.encode("utf-8"))
+        if legacy_vocab:  # one string: vocab_size - 1 pieces of 8 bytes, NUL-padded (pieces longer than 8 bytes are cut)
+            _w_str(f, b"tokenizer.vocab"); f.write(struct.pack("<I", 8))
+            _w_str(f, b"".join(t.encode("utf-8")[:8].ljust(8, b"\0") for t in vocab))
+        else:
+            _w_str(f, b"tokenizer.vocab_list"); f.write(struct.pack("<I", 9)); f.write(struct.pack("<I", 8))
+            f.write(struct.pack("<Q", len(vocab)))
+            for t in vocab:
+                _w_str(f, t.encode("utf-8"))
         for k, v in hparams:
             _w_str(f, k.encode()); f.write(struct.pack("<I", 4)); f.write(struct.pack("<I", v))
         if multilingual:  # parallel arrays: string[] codes, i32[] ids
@@ -280,8 +346,11 @@ def main(argv=None):
     ap.add_argument("--layers", type=int, default=24)
     ap.add_argument("--variant", default="q8_0", choices=("q8_0", "f32", "f32dq", "f16", "q4_0"))
     ap.add_argument("--blank-gain", type=float, default=None)
+    ap.add_argument("--decoder", default="bistable", choices=("bistable", "stationary"))
+    ap.add_argument("--legacy-vocab", action="store_true")
+    ap.add_argument("--res-scale", type=float, default=1.0)
     a = ap.parse_args(argv)
-    print(write_gguf(a.out, a.seed, a.layers, a.variant, a.blank_gain))
+    print(write_gguf(a.out, a.seed, a.layers, a.variant, a.blank_gain, decoder=a.decoder, legacy_vocab=a.legacy_vocab, res_scale=a.res_scale))
 
 
 if __name__ == "__main__":
