@@ -752,9 +752,12 @@ def _run_batch(nb, model, pcms, rc, taps=True):
 @pytest.mark.parametrize("rc,n_streams,secs", [(13, 64, 3.5), (0, 128, 1.0)])
 def test_bench_batch_equals_single_and_oracle(nb, model_f32_wide, oracle_f32, rc, n_streams, secs):
     """the batch shapes of BASELINE configs 2 and 3 (64 streams x 14 frames = 896 rows; 128 streams x 1 frame)
-    in ONE batched step. Every stream must equal the same stream run alone (other tile configuration and split-K count, so
-    fp32 summation order differs: <= 1e-5 relative; tokens identical unless the chunk holds a near-tie far below TIE_GAP), and
-    sampled streams must match the numpy oracle like the single-stream tests do."""
+    in ONE batched step. Every stream must equal the same stream run alone up to the fp16-operand noise floor: the batch runs
+    other tile configurations and split-K counts, so fp32 sums differ in their last bits, which flips a few of the fp16
+    roundings of the next GEMM's operands (2^-11 each) — measured 2.6e-4 relative at worst over 64 streams, half the 5e-4 this
+    path sits from the fp32 oracle; a row mix-up between streams of a tile would show as O(1). Tokens identical unless the
+    chunk holds a near-tie (gap < 1e-3, far below TIE_GAP). Sampled streams must match the numpy oracle like the single-stream
+    tests do."""
     pcms = [inputs.pcm(200 + i, secs) for i in range(n_streams)]
     batch, sizes = _run_batch(nb, model_f32_wide, pcms, rc)
     assert max(sizes) == n_streams, sizes  # the streams really shared their steps
@@ -768,8 +771,8 @@ def test_bench_batch_equals_single_and_oracle(nb, model_f32_wide, oracle_f32, rc
             same, _, margin = compare_tokens(batch[i], alone["tokens"], alone["chunk_tokens"])
             assert margin is not None and margin < 1e-3, f"stream {i}: batched tokens differ from the stream run alone at chunk {same} (gap {margin})"
     print(f"rc={rc}: {n_streams} streams batched vs alone: worst enc rel {worst:.2e}, streams with a (near-tie) token difference {tok_diff}")
-    assert worst < 1e-5
-    assert tok_diff <= max(1, n_streams // 32)
+    assert worst < 1e-3
+    assert tok_diff <= n_streams // 4  # each one was traced to a near-tie above
     kv, t = oracle_f32
     for i in (0, n_streams // 3, n_streams // 2, n_streams - 1):
         o = no.StreamOracle(kv, t, rc)
