@@ -167,19 +167,32 @@ void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* 
 // of one. Same steps, same arithmetic per step, same tokens and frame stamps as W = 1.
 // The loop ends when no stream has frames left. Counters rotate over three slots so that clearing the next round's slot
 // cannot race with a CTA still reading the previous one.
-constexpr int DK_TS = 8, DK_MAXU = 8, DK_MAXR = 8, DK_GROUP = 64;
+// The dot products of both phases run on the tensor cores as 3xTF32 (mma.sync.m16n8k8): every fp32 operand is split into
+// big = tf32(x) and small = tf32(x - big), and big*big + big*small + small*big is accumulated in fp32; the dropped
+// small*small term and the rounding of the small parts are ~2^-22 relative per product, the same class as the fp32
+// summation-order noise of a CUDA-core dot product (the reference keeps these weights and this math in F32,
+// src/nemo-ggml.cpp:580-619,1186-1224). M = 16 items (streams / symbol steps), N = 8 weight rows per tile; a CTA's 8 warps
+// split K and their partial tiles are summed in warp order through shared memory (fixed order: deterministic).
+// The CUDA-core version this replaces was bound by shared-memory bandwidth (every warp re-read the whole item tile for 3
+// weight rows): 9.7 us of dot products per round in the logits phase and ~1.5 us per 8 emitting streams and LSTM layer.
+constexpr int DK_TS = 16, DK_MAXU = 5, DK_MAXR = 8, DK_GROUP = 64;
+constexpr int DK_LDH = JOINT + 16;     // row stride (floats) of hid vectors / joint.out rows in shared memory
+constexpr int DK_LDX = 2 * DEC + 16;   // row stride of LSTM input vectors / gate rows; both = 16 mod 32: the 128-bit fragment
+                                       // loads of a quarter warp (2 rows x 4 x 16 B) then cover all 32 banks once
 struct DkSmem {
-    float xs[DK_GROUP * JOINT];        // L: hid of up to 64 streams [q][640]; E: input vectors of 8 streams [q][1280]
-    float wrow[DK_MAXR][JOINT];        // this CTA's joint.out rows
-    float gs[DK_TS][4 * DK_MAXU];      // gate pre-activations / logits of the tile
-    int sl[DK_TS], bq[DK_TS], rows[4 * DK_MAXU];
+    float xs[(DK_TS + 4 * DK_MAXU) * DK_LDX];  // L: hid of up to 64 items [q][DK_LDH]; E: inputs of 16 streams [q][DK_LDX], then this CTA's gate rows [r][DK_LDX]
+    float wrow[DK_MAXR][DK_LDH];       // this CTA's joint.out rows (rows >= nr are zero)
+    float red[8][16][24];              // per-warp partial tiles [item][row]
+    float gs[DK_TS][4 * DK_MAXU];      // gate pre-activations of the tile
+    int sl[DK_TS], bq[DK_TS], tok[DK_TS], rows[4 * DK_MAXU];
     float bias[DK_MAXR];               // joint.out bias of my rows
     int act[DK_GROUP];                 // L: item indices (stream * W + window offset) of the group's pending symbol steps
     int n_act;
     float wbest[DK_GROUP], wsecond[DK_GROUP];  // A, window mode: merged (max, runner-up, index) of a stream's window items
     int widx[DK_GROUP], wemit, wf;
 };
-static_assert(DK_GROUP * JOINT >= DK_TS * 2 * DEC, "the LSTM tile reuses the hid buffer");
+static_assert((DK_TS + 4 * DK_MAXU) * DK_LDX >= DK_GROUP * DK_LDH, "the hid group shares the LSTM tile buffer");
+static_assert(sizeof(DkSmem) <= 227 * 1024, "decode kernel shared memory");
 
 __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& phase) {
     __syncthreads();
@@ -197,137 +210,163 @@ __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& phase) {
     __syncthreads();
 }
 
-// One warp: n <= R weight rows (wr[i] -> K floats, global or shared memory) times the 8 staged vectors xs[q * LD + k].
-// Lane = (kg = lane & 7: interleaved K slice, sg = lane >> 3: stream pair). Every vector element a warp touches is read
-// once per call, whatever the number of rows (one row per warp would re-read the whole stream tile from shared memory for
-// every row: measured, that made shared-memory bandwidth the limit of the round). On return the lanes with kg == 0 hold
-// v[i][j] = wr[i] . xs[2 sg + j].
-// UNROLL k-steps are in flight at once: with the weights in L2 (the LSTM / joint.pred rows of phase E) the loop is bound by
-// that latency, not by bandwidth, so E asks for 10 (30 independent 16-byte loads per lane); the logits phase reads its rows
-// from shared memory and keeps 4.
-template <int K, int LD, int R, int UNROLL = 4>
-__device__ __forceinline__ void dk_block(const float* const (&wr)[R], int n, const float* xs, float (&v)[R][2]) {
-    const int lane = threadIdx.x & 31, kg = lane & 7, sg = lane >> 3;
-    const float* x0 = xs + (size_t)(2 * sg) * LD + 4 * kg;
-    const float* x1 = x0 + LD;
+__device__ __forceinline__ void tf32_split(float x, uint32_t& big, uint32_t& small) {
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(big) : "f"(x));
+    const float r = x - __uint_as_float(big);  // exact
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(small) : "f"(r));
+}
+__device__ __forceinline__ void mma_tf32(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// One warp: out[m][n] = sum_{k in [k0, k1)} xs[m * ldx + k] * ws[row(n) * ldw + k] for m < 16, n < 8 NT, row(n) = n < nrows ? n : 0
+// (the padding columns repeat row 0 and are never read back). (k1 - k0) % 16 == 0; both strides = 16 mod 32 floats.
+// K runs through the MMAs in a permuted order — per 16 consecutive k the lane with tig = lane & 3 loads k0 + 4 tig .. + 3 of its
+// A rows and its B row with one 128-bit load each; elements .x/.y feed one k-step as logical k = tig / tig + 4, .z/.w the next —
+// which is the same permutation for both operands, so the products pair up correctly.
+template <int NT>
+__device__ __forceinline__ void dk_mma_tile(const float* xs, int ldx, const float* ws, int ldw, int nrows, int k0, int k1, float (*out)[24]) {
+    const int lane = threadIdx.x & 31, g = lane >> 2, tig = lane & 3;
+    const float* xa = xs + (size_t)g * ldx + 4 * tig;
+    const float* xb = xa + (size_t)8 * ldx;
+    const float* wp[NT];
 #pragma unroll
-    for (int i = 0; i < R; i++) v[i][0] = v[i][1] = 0.0f;
-#pragma unroll UNROLL
-    for (int k = 0; k < K; k += 32) {
-        const float4 a = *reinterpret_cast<const float4*>(x0 + k), c = *reinterpret_cast<const float4*>(x1 + k);
+    for (int nt = 0; nt < NT; nt++) {
+        const int n = nt * 8 + g;
+        wp[nt] = ws + (size_t)(n < nrows ? n : 0) * ldw + 4 * tig;
+    }
+    float acc[NT][4];
 #pragma unroll
-        for (int i = 0; i < R; i++) {
-            if (i < n) {
-                const float4 wv = *reinterpret_cast<const float4*>(wr[i] + 4 * kg + k);
-                v[i][0] = fmaf(wv.x, a.x, v[i][0]);
-                v[i][0] = fmaf(wv.y, a.y, v[i][0]);
-                v[i][0] = fmaf(wv.z, a.z, v[i][0]);
-                v[i][0] = fmaf(wv.w, a.w, v[i][0]);
-                v[i][1] = fmaf(wv.x, c.x, v[i][1]);
-                v[i][1] = fmaf(wv.y, c.y, v[i][1]);
-                v[i][1] = fmaf(wv.z, c.z, v[i][1]);
-                v[i][1] = fmaf(wv.w, c.w, v[i][1]);
+    for (int nt = 0; nt < NT; nt++) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.0f;
+#pragma unroll 2
+    for (int k = k0; k < k1; k += 16) {
+        const float4 A0 = *reinterpret_cast<const float4*>(xa + k), A1 = *reinterpret_cast<const float4*>(xb + k);
+        const float av[8] = {A0.x, A1.x, A0.y, A1.y, A0.z, A1.z, A0.w, A1.w};  // (a0, a1, a2, a3) of k-step 0, then of k-step 1
+        uint32_t ab[8], as[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) tf32_split(av[i], ab[i], as[i]);
+#pragma unroll
+        for (int nt = 0; nt < NT; nt++) {
+            const float4 Wv = *reinterpret_cast<const float4*>(wp[nt] + k);
+            const float wv[4] = {Wv.x, Wv.y, Wv.z, Wv.w};  // (b0, b1) of k-step 0, then of k-step 1
+            uint32_t wb[4], wsm[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) tf32_split(wv[i], wb[i], wsm[i]);
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                mma_tf32(acc[nt], as[4 * j], as[4 * j + 1], as[4 * j + 2], as[4 * j + 3], wb[2 * j], wb[2 * j + 1]);
+                mma_tf32(acc[nt], ab[4 * j], ab[4 * j + 1], ab[4 * j + 2], ab[4 * j + 3], wsm[2 * j], wsm[2 * j + 1]);
+                mma_tf32(acc[nt], ab[4 * j], ab[4 * j + 1], ab[4 * j + 2], ab[4 * j + 3], wb[2 * j], wb[2 * j + 1]);
             }
         }
     }
 #pragma unroll
-    for (int i = 0; i < R; i++) {
-#pragma unroll
-        for (int j = 0; j < 2; j++) {
-            float x = v[i][j];
-            x += __shfl_xor_sync(0xffffffffu, x, 1);
-            x += __shfl_xor_sync(0xffffffffu, x, 2);
-            x += __shfl_xor_sync(0xffffffffu, x, 4);
-            v[i][j] = x;
-        }
+    for (int nt = 0; nt < NT; nt++) {
+        *reinterpret_cast<float2*>(&out[g][nt * 8 + 2 * tig]) = make_float2(acc[nt][0], acc[nt][1]);
+        *reinterpret_cast<float2*>(&out[g + 8][nt * 8 + 2 * tig]) = make_float2(acc[nt][2], acc[nt][3]);
     }
 }
 
-// rows[0..nr) of W (K floats each, row-major) times the DK_TS staged vectors xs[q][0..K): warp w takes rows w, w+8, w+16;
-// out(q, r, value + bias[row]). wsm (optional): the same rows already staged in shared memory, row r at wsm + r * K.
-template <int K, int LD, typename Out>
-__device__ __forceinline__ void dk_rows(const float* __restrict__ W, const float* __restrict__ bias, const float* xs, int nr,
-                                        const int* rows, Out&& out, const float* wsm = nullptr) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, sg = lane >> 3;
-    const float* wr[3];
-    int n = 0;
-#pragma unroll
-    for (int i = 0; i < 3; i++) {
-        const int r = warp + 8 * i;
-        wr[i] = wsm ? wsm + (size_t)(r < nr ? r : 0) * K : W + (size_t)rows[r < nr ? r : 0] * K;
-        if (r < nr) n = i + 1;
-    }
-    if (n == 0) return;
-    float v[3][2];
-    dk_block<K, LD, 3, 10>(wr, n, xs, v);
-    if ((lane & 7) == 0) {
-#pragma unroll
-        for (int i = 0; i < 3; i++) {
-            if (i < n) {
-                const int r = warp + 8 * i;
-                const float bv = bias[rows[r]];
-                out(2 * sg, r, v[i][0] + bv);
-                out(2 * sg + 1, r, v[i][1] + bv);
-            }
-        }
-    }
-}
-
-// cp.async copy of rows[0..nrows) of W (K floats each) to dst[r * K ..] by the whole CTA, one commit group
-__device__ __forceinline__ void dk_stage_rows(float* dst, const float* __restrict__ W, int K, const int* rows, int nrows) {
+// cp.async copy of rows[0..nrows) of W (K floats each) to dst[r * ld ..] by the whole CTA, one commit group
+__device__ __forceinline__ void dk_stage_rows(float* dst, int ld, const float* __restrict__ W, int K, const int* rows, int nrows) {
     const int per_row = K / 4;
     for (int i = threadIdx.x; i < nrows * per_row; i += 256) {
         const int r = i / per_row, c = i - r * per_row;
-        const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst + (size_t)r * K + 4 * c);
+        const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst + (size_t)r * ld + 4 * c);
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(W + (size_t)rows[r] * K + 4 * c) : "memory");
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
 }
+__device__ __forceinline__ void cp_async16(float* dst_smem, const float* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst_smem)), "l"(src) : "memory");
+}
 __device__ __forceinline__ void dk_stage_wait() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-// Recomputes pend_h / pend_c / pend_p of the E streams listed in `list` (batch indices; nullptr = 0..E-1).
+// The tile's 16 x nrows outputs: all 8 warps split K (K / 8 each), then thread (q, r) sums the 8 partial tiles in warp order.
+template <int K, typename Out>
+__device__ __forceinline__ void dk_tile_rows(DkSmem& sm, const float* xs, int ldx, const float* ws, int ldw, int nrows, Out&& out) {
+    const int warp = threadIdx.x >> 5, t = threadIdx.x;
+    static_assert(K % 128 == 0, "8 warps x 16-wide k steps");
+    if (nrows > 16) dk_mma_tile<3>(xs, ldx, ws, ldw, nrows, warp * (K / 8), (warp + 1) * (K / 8), sm.red[warp]);
+    else if (nrows > 8) dk_mma_tile<2>(xs, ldx, ws, ldw, nrows, warp * (K / 8), (warp + 1) * (K / 8), sm.red[warp]);
+    else dk_mma_tile<1>(xs, ldx, ws, ldw, nrows, warp * (K / 8), (warp + 1) * (K / 8), sm.red[warp]);
+    __syncthreads();
+    for (int i = t; i < DK_TS * nrows; i += 256) {
+        const int q = i / nrows, r = i - q * nrows;
+        float v = 0.0f;
+#pragma unroll
+        for (int w = 0; w < 8; w++) v += sm.red[w][q][r];
+        out(q, r, v);
+    }
+}
+
+// Item q of an LSTM tile: (batch index, slot, previous token) of emitting stream e0 + q — one 16-byte record written by the
+// argmax phase (no dependent slot / prev look-ups) — or, for a refresh of streams 0..E-1, from the batch arrays.
+__device__ __forceinline__ void dk_tile_item(const DecodeState& s, const DecodeBatch& d, DkSmem& sm, const int4* list, int e0, int E, int q) {
+    int b = -1, slot = -1, tok = 0;
+    if (e0 + q < E) {
+        if (list) {
+            const int4 r = __ldcg(list + e0 + q);
+            b = r.x; slot = r.y; tok = r.z;
+        } else {
+            b = e0 + q;
+            slot = d.slot[b];
+            tok = __ldcg(s.prev + slot);
+        }
+    }
+    sm.bq[q] = b;
+    sm.sl[q] = slot;
+    sm.tok[q] = tok;
+}
+
+// Recomputes pend_h / pend_c / pend_p of the E streams listed in `list` (batch indices; nullptr = 0..E-1), 16 streams per tile.
 // The CTA's weight rows of a phase (16-20 gate rows x 1280 floats = 100 KB per LSTM layer, 4-5 x 640 for joint.pred) are brought
-// into the idle part of the hid buffer with cp.async by all 256 threads (bandwidth- instead of latency-bound), the next
-// phase's rows while this phase finishes its gate math and waits at the grid barrier.
-__device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d, DkSmem& sm, const int* list, int E,
-                               unsigned& phase) {
+// into shared memory behind the input tile with cp.async by all 256 threads, the next phase's rows while this phase finishes
+// its gate math and waits at the grid barrier.
+__device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d, DkSmem& sm, const int4* list, int E,
+                               unsigned& phase, unsigned long long* acc = nullptr) {
     const int cta = blockIdx.x, G = gridDim.x, t = threadIdx.x;
+    auto now = [] { unsigned long long x; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(x)::"memory"); return x; };
+    const bool tr = acc != nullptr && cta == 0 && t == 0;
+    unsigned long long q0 = tr ? now() : 0, q1;
     const int base = DEC / G, rem = DEC % G;
     const int nu = base + (cta < rem ? 1 : 0), u0 = cta * base + min(cta, rem);  // my hidden units [u0, u0 + nu)
-    // behind the input tile: room for 24 rows x 1280 floats (nu <= 5 on 148 SMs needs 20); otherwise the rows are read from L2
-    float* wsm = 4 * nu * 2 * DEC <= DK_GROUP * JOINT - DK_TS * 2 * DEC ? sm.xs + DK_TS * 2 * DEC : nullptr;
+    float* wsm = sm.xs + DK_TS * DK_LDX;
     __syncthreads();
     if (t < 4 * nu) sm.rows[t] = (t / nu) * DEC + u0 + (t % nu);  // the same gate rows in both layers; rows[0..nu) = u0.. are also joint.pred's
     __syncthreads();
-    if (wsm) dk_stage_rows(wsm, w.wcat[0], 2 * DEC, sm.rows, 4 * nu);
+    dk_stage_rows(wsm, DK_LDX, w.wcat[0], 2 * DEC, sm.rows, 4 * nu);
     for (int layer = 0; layer < 2; layer++) {
         for (int e0 = 0; e0 < E; e0 += DK_TS) {
             __syncthreads();
-            if (t < DK_TS) {
-                const int b = (e0 + t < E) ? (list ? __ldcg(list + e0 + t) : e0 + t) : -1;
-                sm.bq[t] = b;
-                sm.sl[t] = b >= 0 ? d.slot[b] : -1;
-            }
+            if (t < DK_TS) dk_tile_item(s, d, sm, list, e0, E, t);
             __syncthreads();
-            // x = [embed[prev] | h0] for layer 0, [h0' | h1] for layer 1 (h0' = this round's new layer-0 output)
+            // x = [embed[prev] | h0] for layer 0, [h0' | h1] for layer 1 (h0' = this round's new layer-0 output): all 20 16-byte
+            // pieces of a thread are in flight at once (cp.async; L2 only, the state was written by other CTAs of this launch)
             for (int i = t; i < DK_TS * (2 * DEC / 4); i += 256) {
                 const int q = i / (2 * DEC / 4), k = (i - q * (2 * DEC / 4)) * 4, slot = sm.sl[q];
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                float* dst = &sm.xs[q * DK_LDX + k];
                 if (slot >= 0) {
                     const float* src;
-                    if (k < DEC) src = layer == 0 ? w.embed + (size_t)__ldcg(s.prev + slot) * DEC + k : s.pend_h + (size_t)slot * 2 * DEC + k;
+                    if (k < DEC) src = layer == 0 ? w.embed + (size_t)sm.tok[q] * DEC + k : s.pend_h + (size_t)slot * 2 * DEC + k;
                     else src = s.h + (size_t)slot * 2 * DEC + (size_t)layer * DEC + (k - DEC);
-                    v = __ldcg(reinterpret_cast<const float4*>(src));  // state written by other CTAs of this launch
+                    cp_async16(dst, src);
+                } else {
+                    *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
                 }
-                *reinterpret_cast<float4*>(&sm.xs[q * 2 * DEC + k]) = v;
             }
-            dk_stage_wait();  // this layer's rows (requested before the previous barrier), my copies ...
+            asm volatile("cp.async.commit_group;" ::: "memory");
+            dk_stage_wait();  // this layer's rows (requested before the previous barrier) and the input tile, my copies ...
             __syncthreads();  // ... and everyone's, and the input tile
-            dk_rows<2 * DEC, 2 * DEC>(w.wcat[layer], w.bcat[layer], sm.xs, 4 * nu, sm.rows, [&](int q, int r, float v) { sm.gs[q][r] = v; }, wsm);
+            if (tr) { q1 = now(); acc[7] += q1 - q0; q0 = q1; }
+            dk_tile_rows<2 * DEC>(sm, sm.xs, DK_LDX, wsm, DK_LDX, 4 * nu, [&](int q, int r, float v) { sm.gs[q][r] = v + w.bcat[layer][sm.rows[r]]; });
             __syncthreads();
-            if (wsm && e0 + DK_TS >= E) {  // last tile: the rows are dead, fetch the next phase's while the gates and the barrier run
-                if (layer == 0) dk_stage_rows(wsm, w.wcat[1], 2 * DEC, sm.rows, 4 * nu);
-                else dk_stage_rows(wsm, w.wpred, DEC, sm.rows, nu);
+            if (tr) { q1 = now(); acc[8] += q1 - q0; q0 = q1; }
+            if (e0 + DK_TS >= E) {  // last tile: the rows are dead, fetch the next phase's while the gates and the barrier run
+                if (layer == 0) dk_stage_rows(wsm, DK_LDX, w.wcat[1], 2 * DEC, sm.rows, 4 * nu);
+                else dk_stage_rows(wsm, DK_LDH, w.wpred, DEC, sm.rows, nu);
             }
             if (t < DK_TS * nu) {
                 const int q = t / nu, ui = t % nu, slot = sm.sl[q];
@@ -340,38 +379,41 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
                     s.pend_h[so] = og * tanhf(c2);
                 }
             }
+            if (tr) { q1 = now(); acc[9] += q1 - q0; q0 = q1; }
         }
         grid_barrier(d.bar, phase);
+        if (tr) { q1 = now(); acc[10] += q1 - q0; q0 = q1; }
     }
     // joint.pred (src/nemo-ggml.cpp:1207-1211): pend_p = W_pred h1' + b_pred, rows u0 .. u0+nu-1
     if (t < nu) sm.rows[t] = u0 + t;
     for (int e0 = 0; e0 < E; e0 += DK_TS) {
         __syncthreads();
-        if (t < DK_TS) {
-            const int b = (e0 + t < E) ? (list ? __ldcg(list + e0 + t) : e0 + t) : -1;
-            sm.bq[t] = b;
-            sm.sl[t] = b >= 0 ? d.slot[b] : -1;
-        }
+        if (t < DK_TS) dk_tile_item(s, d, sm, list, e0, E, t);
         __syncthreads();
         for (int i = t; i < DK_TS * (DEC / 4); i += 256) {
             const int q = i / (DEC / 4), k = (i - q * (DEC / 4)) * 4, slot = sm.sl[q];
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (slot >= 0) v = __ldcg(reinterpret_cast<const float4*>(s.pend_h + (size_t)slot * 2 * DEC + DEC + k));
-            *reinterpret_cast<float4*>(&sm.xs[q * 2 * DEC + k]) = v;
+            float* dst = &sm.xs[q * DK_LDX + k];
+            if (slot >= 0) cp_async16(dst, s.pend_h + (size_t)slot * 2 * DEC + DEC + k);
+            else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
         dk_stage_wait();
         __syncthreads();
-        dk_rows<DEC, 2 * DEC>(w.wpred, w.bpred, sm.xs, nu, sm.rows, [&](int q, int r, float v) {
+        if (tr) { q1 = now(); acc[11] += q1 - q0; q0 = q1; }
+        dk_tile_rows<DEC>(sm, sm.xs, DK_LDX, wsm, DK_LDH, nu, [&](int q, int r, float acc) {
             if (sm.sl[q] < 0) return;
+            const float v = acc + w.bpred[u0 + r];
             s.pend_p[(size_t)sm.sl[q] * JOINT + u0 + r] = v;
             if (list) {  // the stream's next symbol step: hid = relu(joint.enc(frame fp) + new pending pred), my rows
                 const int b = sm.bq[q], fp = __ldcg(d.fp + b), nv = d.nvalid[b];
                 for (int wi = 0; wi < d.W && fp + wi < nv; wi++)
                     d.hid[(size_t)(b * d.W + wi) * JOINT + u0 + r] = fmaxf(d.e[((size_t)(b * d.T + fp + wi)) * JOINT + u0 + r] + v, 0.0f);
             }
-        }, wsm);
+        });
+        if (tr) { q1 = now(); acc[12] += q1 - q0; q0 = q1; }
     }
     grid_barrier(d.bar, phase);
+    if (tr) { q1 = now(); acc[13] += q1 - q0; acc[14] += 1; acc[15] += (unsigned long long)E; }
 }
 
 // hid[b] = relu(joint.enc(frame fp) + pend_p[slot]) for one stream, by one warp (src/nemo-ggml.cpp:1215-1217)
@@ -400,9 +442,11 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
     // my vocabulary rows, resident in shared memory for the whole launch
     const int R = (VOCAB + G - 1) / G, v0 = cta * R, nr = max(0, min(R, VOCAB - v0));
     const int n_part = (VOCAB + R - 1) / R;  // CTAs that own rows
-    for (int i = t; i < nr * (JOINT / 4); i += 256) {
+    for (int i = t; i < DK_MAXR * (JOINT / 4); i += 256) {  // rows >= nr: zero (padding columns of the MMA tile)
         const int r = i / (JOINT / 4), k = (i - r * (JOINT / 4)) * 4;
-        *reinterpret_cast<float4*>(&sm.wrow[r][k]) = *reinterpret_cast<const float4*>(w.wout + (size_t)(v0 + r) * JOINT + k);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < nr) v = *reinterpret_cast<const float4*>(w.wout + (size_t)(v0 + r) * JOINT + k);
+        *reinterpret_cast<float4*>(&sm.wrow[r][k]) = v;
     }
     if (t < nr) sm.bias[t] = w.bout[v0 + t];
     // per-chunk decode state (was four memset nodes in front of this kernel): frame pointers, symbol counters, token counts,
@@ -434,6 +478,7 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
             emit_count[(round + 1) % 3] = 0;
         }
         // ---- L: logits of my rows; the hid vectors of up to 64 unfinished streams are staged at once ----
+        unsigned long long tg = t0;
         if (nr > 0) {
             for (int g0 = 0; g0 < d.B * W; g0 += DK_GROUP) {
                 __syncthreads();
@@ -452,73 +497,38 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                 const int n_act = sm.n_act;
                 unsigned long long u0 = tr ? now() : 0;
                 if (n_act == 0) continue;  // uniform
-                const int n_pad = (n_act + DK_TS - 1) / DK_TS * DK_TS;
-                for (int i0 = 0; i0 < n_pad * (JOINT / 4); i0 += 256 * 8) {  // 8 independent 16-byte loads in flight per thread
-                    float4 v[8];
-#pragma unroll
-                    for (int u = 0; u < 8; u++) {
-                        const int i = i0 + u * 256 + t, q = i / (JOINT / 4), k = (i - q * (JOINT / 4)) * 4;
-                        v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (q < n_act) v[u] = __ldcg(reinterpret_cast<const float4*>(d.hid + (size_t)sm.act[q] * JOINT + k));
-                    }
-#pragma unroll
-                    for (int u = 0; u < 8; u++) {
-                        const int i = i0 + u * 256 + t;
-                        if (i < n_pad * (JOINT / 4)) *reinterpret_cast<float4*>(&sm.xs[(size_t)i * 4]) = v[u];
-                    }
+                const int n_mt = (n_act + 15) >> 4;                      // 16-item MMA tiles in use
+                const int mtp = n_mt <= 1 ? 1 : (n_mt <= 2 ? 2 : 4);      // warps are split (item tile, K slice): 1x8, 2x4 or 4x2
+                const int n_pad = n_mt * 16;
+                for (int i = t; i < n_pad * (JOINT / 4); i += 256) {  // all of a thread's 16-byte pieces in flight at once (L2 only)
+                    const int q = i / (JOINT / 4), k = (i - q * (JOINT / 4)) * 4;
+                    float* dst = &sm.xs[(size_t)q * DK_LDH + k];
+                    if (q < n_act) cp_async16(dst, d.hid + (size_t)sm.act[q] * JOINT + k);
+                    else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
                 }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+                dk_stage_wait();
                 __syncthreads();
                 unsigned long long u1 = tr ? now() : 0;
-                if (n_act <= DK_TS) {
-                    // few pending items (the tail of a chunk, or a batch of a few streams): a warp per row instead of one warp for
-                    // all rows; same per-row arithmetic, rows merged in index order like below
-                    if (warp < nr) {
-                        const float* w1[1] = {&sm.wrow[warp][0]};
-                        float v1[1][2];
-                        dk_block<JOINT, JOINT, 1>(w1, 1, sm.xs, v1);
-                        if ((lane & 7) == 0) {
-                            sm.gs[2 * (lane >> 3)][warp] = v1[0][0] + sm.bias[warp];
-                            sm.gs[2 * (lane >> 3) + 1][warp] = v1[0][1] + sm.bias[warp];
-                        }
-                    }
+                {
+                    const int mt = warp % mtp, ks = warp / mtp, klen = JOINT / (8 / mtp);  // 80 / 160 / 320: multiples of 16
+                    if (mt < n_mt) dk_mma_tile<1>(sm.xs + (size_t)(16 * mt) * DK_LDH, DK_LDH, &sm.wrow[0][0], DK_LDH, DK_MAXR, ks * klen, (ks + 1) * klen, sm.red[warp]);
                     __syncthreads();
-                    if (t < n_act) {
+                    if (t < n_act) {  // my item's logits on this CTA's rows: K slices summed in order, then the slice's (first max, runner-up)
+                        const int q = t & 15, m_t = t >> 4;
                         float best = -INFINITY, second = -INFINITY;
                         int besti = 0;
                         for (int i = 0; i < nr; i++) {
-                            const float x = sm.gs[t][i];
+                            float x = 0.0f;
+                            for (int k2 = 0; k2 < 8 / mtp; k2++) x += sm.red[k2 * mtp + m_t][q][i];
+                            x += sm.bias[i];
                             if (x > best) { second = best; best = x; besti = v0 + i; }
                             else if (x > second) second = x;
                         }
                         partial[(size_t)sm.act[t] * G + cta] = make_float4(best, second, __int_as_float(besti), 0.0f);
                     }
-                } else if (8 * warp < n_act) {  // warp w: streams 8w .. 8w+7 of the group, all of my rows
-                    const float* wr[DK_MAXR];
-#pragma unroll
-                    for (int i = 0; i < DK_MAXR; i++) wr[i] = &sm.wrow[i < nr ? i : 0][0];
-                    float v[DK_MAXR][2];
-                    dk_block<JOINT, JOINT, DK_MAXR>(wr, nr, sm.xs + (size_t)(8 * warp) * JOINT, v);
-                    if ((lane & 7) == 0) {
-#pragma unroll
-                        for (int j = 0; j < 2; j++) {
-                            const int q = 8 * warp + 2 * (lane >> 3) + j;
-                            if (q < n_act) {
-                                float best = -INFINITY, second = -INFINITY;
-                                int besti = 0;
-#pragma unroll
-                                for (int i = 0; i < DK_MAXR; i++) {
-                                    if (i < nr) {
-                                        const float x = v[i][j] + sm.bias[i];
-                                        if (x > best) { second = best; best = x; besti = v0 + i; }
-                                        else if (x > second) second = x;
-                                    }
-                                }
-                                partial[(size_t)sm.act[q] * G + cta] = make_float4(best, second, __int_as_float(besti), 0.0f);
-                            }
-                        }
-                    }
                 }
-                if (tr) { acc[4] += u0 - t0; acc[5] += u1 - u0; acc[6] += now() - u1; }
+                if (tr) { const unsigned long long u2 = now(); acc[4] += u0 - tg; acc[5] += u1 - u0; acc[6] += u2 - u1; tg = u2; }
             }
         }
         unsigned long long t1 = tr ? now() : 0;
@@ -567,7 +577,7 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                             d.tok_cnt[b] = n + 1;
                             s.prev[slot] = besti;
                             emit = 1;
-                            d.emit_list[atomicAdd(emit_count + cs, 1)] = b;
+                            d.emit_list[atomicAdd(emit_count + cs, 1)] = make_int4(b, slot, besti, 0);
                             sy++;
                             if (sy >= MAX_SYMBOLS) { f++; sy = 0; }
                             break;  // the later items of the window were formed with the old prediction: discarded
@@ -626,7 +636,7 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                     d.tok_cnt[b] = n + 1;
                     s.prev[slot] = besti;
                     emit = 1;
-                    d.emit_list[atomicAdd(emit_count + cs, 1)] = b;  // order is irrelevant: the streams are independent
+                    d.emit_list[atomicAdd(emit_count + cs, 1)] = make_int4(b, slot, besti, 0);  // order is irrelevant: the streams are independent
                     sy++;
                     if (sy >= MAX_SYMBOLS) { f++; sy = 0; }
                 }
@@ -649,7 +659,7 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
         grid_barrier(d.bar, phase);
         if (tr) { const unsigned long long t4 = now(); acc[0] += t1 - t0; acc[1] += t2 - t1; acc[2] += t3 - t2; acc[3] += t4 - t3; }
         const int E = __ldcg(emit_count + cs), U = __ldcg(unfinished + cs);
-        if (E > 0) dk_lstm_update(w, s, d, sm, d.emit_list, E, phase);
+        if (E > 0) dk_lstm_update(w, s, d, sm, d.emit_list, E, phase, acc);
         if (U == 0 || round + 1 >= d.max_rounds) {
             if (cta == 0 && t == 0) {
                 d.counters[6] = U;          // streams left unfinished (non-zero only if the round cap was hit)
@@ -698,7 +708,7 @@ int decode_partial_floats(int B) { return 4 * B * 148; }
 // All greedy rounds of the batch's chunk in one launch (src/nemo-stream.cpp:1106-1118, 840-930).
 void launch_decode_chunk(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& d) {
     const int g = decode_grid();
-    CUDA_CHECK(cudaMemsetAsync(d.counters, 0, 32 * sizeof(int), st));  // counters, the barrier word, time stamps
+    CUDA_CHECK(cudaMemsetAsync(d.counters, 0, 48 * sizeof(int), st));  // counters, the barrier word, time stamps, phase trace
     ProfScope ps(st, "decode_chunk", 2.0 * d.B * d.T * (double)VOCAB * JOINT, 0.0);
     launch_decode(st, g, w, s, d, 0);
     NB_KERNEL_CHECK();

@@ -183,7 +183,7 @@ struct nb200_model {
     long long* ws_meta64 = nullptr;  // long long arrays [3][cap_B]: out_off, a0, n_avail
     int *ws_fp = nullptr, *ws_sym = nullptr, *ws_tok = nullptr, *ws_tokcnt = nullptr, *ws_unfinished = nullptr;
     float *ws_partial = nullptr, *ws_hid = nullptr;
-    int* ws_emit = nullptr;
+    int4* ws_emit = nullptr;
     // Fed audio is gathered on the host (pinned arenas) and moved at the next step by ONE copy + one scatter kernel
     // instead of a cudaMemcpyAsync per stream; two arenas so feeding can go on while a flushed one is still in flight.
     UploadArena arena[2];
@@ -575,7 +575,7 @@ void alloc_state(nb200_model* m) {
     if (const char* e = getenv("NB200_DECODE_WINDOW")) m->dec_window = std::max(1, std::min(8, atoi(e)));
     m->ws_partial = m->alloc<float>((size_t)decode_partial_floats(B) * m->dec_window);
     m->ws_hid = m->alloc<float>((size_t)B * JOINT * m->dec_window);
-    m->ws_emit = m->alloc<int>(B);
+    m->ws_emit = m->alloc<int4>(B);
     m->d_reset = m->alloc<int>(B);
     CUDA_CHECK(cudaEventCreateWithFlags(&m->reset_ev, cudaEventDisableTiming));
     {   // upload arenas: >= two rc=13 chunks per slot each
@@ -1088,10 +1088,13 @@ void run_batch_finish(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
     m->stats.d2h_bytes += (long long)sizeof(int) * ((size_t)2 * capB + (size_t)B * T * MAX_SYMBOLS + 8);
     if (h_unf[0] != 0) throw Error("decode loop did not terminate");
     if (getenv("NB200_DK_TRACE")) {
-        unsigned long long a[7];
-        CUDA_CHECK(cudaMemcpy(a, m->ws_unfinished + 16, 56, cudaMemcpyDeviceToHost));
-        fprintf(stderr, "decode phases (us): L %.1f (compact %.1f stage %.1f rows %.1f) bar1 %.1f A %.1f bar2 %.1f rounds %d\n", a[0] * 1e-3, a[4] * 1e-3,
-                a[5] * 1e-3, a[6] * 1e-3, a[1] * 1e-3, a[2] * 1e-3, a[3] * 1e-3, h_unf[1]);
+        unsigned long long a[16];
+        CUDA_CHECK(cudaMemcpy(a, m->ws_unfinished + 16, sizeof a, cudaMemcpyDeviceToHost));
+        fprintf(stderr,
+                "decode phases (us): L %.1f (compact %.1f stage %.1f rows %.1f) bar1 %.1f A %.1f bar2 %.1f | E: lstm stage %.1f mma %.1f gates %.1f bar %.1f, pred stage %.1f "
+                "mma %.1f bar %.1f, %llu rounds with %llu emissions | rounds %d\n",
+                a[0] * 1e-3, a[4] * 1e-3, a[5] * 1e-3, a[6] * 1e-3, a[1] * 1e-3, a[2] * 1e-3, a[3] * 1e-3, a[7] * 1e-3, a[8] * 1e-3, a[9] * 1e-3, a[10] * 1e-3,
+                a[11] * 1e-3, a[12] * 1e-3, a[13] * 1e-3, a[14], a[15], h_unf[1]);
     }
     const long long rounds = h_unf[1];
 

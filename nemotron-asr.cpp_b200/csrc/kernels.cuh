@@ -134,7 +134,7 @@ struct DecodeBatch {           // per batched step
     int* counters;             // [16]: unfinished[3], emit_count[3] (rotating per round), [6] streams left, [7] rounds run, [8] = bar,
                                //       [10..13] the kernel's start / end globaltimer stamps
     unsigned* bar;             // = counters + 8: arrival counter of the grid-wide barriers
-    int* emit_list;            // [B] batch indices of the streams that emitted in the current round
+    int4* emit_list;           // [B] (batch index, slot, token, -) of the streams that emitted in the current round
     float* partial;            // [B][G][4] per-CTA (max, runner-up, index) of the current round's logits
     float* hid;                // [B*W][640] joint hidden vector of every stream's next symbol step(s)
     int B, T, max_rounds;
