@@ -167,10 +167,11 @@ void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* 
 // of one. Same steps, same arithmetic per step, same tokens and frame stamps as W = 1.
 // The loop ends when no stream has frames left. Counters rotate over three slots so that clearing the next round's slot
 // cannot race with a CTA still reading the previous one.
-// The dot products of both phases run on the tensor cores as 3xTF32 (mma.sync.m16n8k8): every fp32 operand is split into
-// big = tf32(x) and small = tf32(x - big), and big*big + big*small + small*big is accumulated in fp32; the dropped
-// small*small term and the rounding of the small parts are ~2^-22 relative per product, the same class as the fp32
-// summation-order noise of a CUDA-core dot product (the reference keeps these weights and this math in F32,
+// The dot products of both phases run on the tensor cores in split precision (mma.sync.m16n8k16, fp16 operands, fp32
+// accumulation): every fp32 operand is hi + lo / 2048 with hi = fp16(x), lo = fp16((x - hi) * 2048), and hi*hi + (hi*lo + lo*hi) /
+// 2048 is accumulated in fp32 (weights pre-split at load, activations split in the loop); the dropped lo*lo term and the
+// rounding of the lo parts are ~2^-22 relative per product, the same class as the fp32 summation-order noise of a CUDA-core
+// dot product. (3xTF32 on m16n8k8 gave the same results at twice the MMA count: the legacy tensor path is the limiter.) (the reference keeps these weights and this math in F32,
 // src/nemo-ggml.cpp:580-619,1186-1224). M = 16 items (streams / symbol steps), N = 8 weight rows per tile; a CTA's 8 warps
 // split K and their partial tiles are summed in warp order through shared memory (fixed order: deterministic).
 // The CUDA-core version this replaces was bound by shared-memory bandwidth (every warp re-read the whole item tile for 3
@@ -210,22 +211,31 @@ __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& phase) {
     __syncthreads();
 }
 
-__device__ __forceinline__ void tf32_split(float x, uint32_t& big, uint32_t& small) {
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(big) : "f"(x));
-    const float r = x - __uint_as_float(big);  // exact
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(small) : "f"(r));
+// hi / lo halves of 4 consecutive fp32 values: hi = fp16(x), lo = fp16((x - hi) * 2048). x = hi + lo / 2048 to ~2^-22 relative
+// (the scale keeps lo a normal fp16 number wherever hi is one).
+__device__ __forceinline__ void f16_split4(const float4& v, uint32_t& h01, uint32_t& h23, uint32_t& l01, uint32_t& l23) {
+    const __half2 a = __floats2half2_rn(v.x, v.y), b = __floats2half2_rn(v.z, v.w);
+    const float2 fa = __half22float2(a), fb = __half22float2(b);
+    const __half2 la = __floats2half2_rn((v.x - fa.x) * 2048.0f, (v.y - fa.y) * 2048.0f);
+    const __half2 lb = __floats2half2_rn((v.z - fb.x) * 2048.0f, (v.w - fb.y) * 2048.0f);
+    h01 = *reinterpret_cast<const uint32_t*>(&a);
+    h23 = *reinterpret_cast<const uint32_t*>(&b);
+    l01 = *reinterpret_cast<const uint32_t*>(&la);
+    l23 = *reinterpret_cast<const uint32_t*>(&lb);
 }
-__device__ __forceinline__ void mma_tf32(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+__device__ __forceinline__ void mma_f16(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
                  : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-// One warp: out[m][n] = sum_{k in [k0, k1)} xs[m * ldx + k] * ws[row(n) * ldw + k] for m < 16, n < 8 NT, row(n) = n < nrows ? n : 0
-// (the padding columns repeat row 0 and are never read back). (k1 - k0) % 16 == 0; both strides = 16 mod 32 floats.
-// K runs through the MMAs in a permuted order — per 16 consecutive k the lane with tig = lane & 3 loads k0 + 4 tig .. + 3 of its
-// A rows and its B row with one 128-bit load each; elements .x/.y feed one k-step as logical k = tig / tig + 4, .z/.w the next —
-// which is the same permutation for both operands, so the products pair up correctly.
+// One warp: out[m][n] = sum_{k in [k0, k1)} xs[m * ldx + k] * W[row(n)][k] for m < 16, n < 8 NT, row(n) = n < nrows ? n : 0
+// (the padding columns repeat row 0 and are never read back). xs: fp32; ws: the rows in the pre-split format, row r at
+// ws + r * ldw floats. (k1 - k0) % 16 == 0; both strides = 16 mod 32 floats.
+// K runs through the MMAs in a permuted order: per 16 consecutive k the lane with tig = lane & 3 takes k0 + 4 tig .. + 3 of its
+// two A rows and of its B row (one 128-bit load each) as the fragment's logical k = 2 tig, 2 tig + 1, 2 tig + 8, 2 tig + 9 —
+// the same permutation for both operands, so the products pair up correctly.
+// x . w = hi hi + (hi lo' + lo' hi) / 2048: the main and the correction terms have their own fp32 accumulators.
 template <int NT>
 __device__ __forceinline__ void dk_mma_tile(const float* xs, int ldx, const float* ws, int ldw, int nrows, int k0, int k1, float (*out)[24]) {
     const int lane = threadIdx.x & 31, g = lane >> 2, tig = lane & 3;
@@ -237,35 +247,31 @@ __device__ __forceinline__ void dk_mma_tile(const float* xs, int ldx, const floa
         const int n = nt * 8 + g;
         wp[nt] = ws + (size_t)(n < nrows ? n : 0) * ldw + 4 * tig;
     }
-    float acc[NT][4];
+    float acc[NT][4], cor[NT][4];
 #pragma unroll
-    for (int nt = 0; nt < NT; nt++) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.0f;
+    for (int nt = 0; nt < NT; nt++)
+#pragma unroll
+        for (int i = 0; i < 4; i++) acc[nt][i] = cor[nt][i] = 0.0f;
 #pragma unroll 2
     for (int k = k0; k < k1; k += 16) {
         const float4 A0 = *reinterpret_cast<const float4*>(xa + k), A1 = *reinterpret_cast<const float4*>(xb + k);
-        const float av[8] = {A0.x, A1.x, A0.y, A1.y, A0.z, A1.z, A0.w, A1.w};  // (a0, a1, a2, a3) of k-step 0, then of k-step 1
-        uint32_t ab[8], as[8];
-#pragma unroll
-        for (int i = 0; i < 8; i++) tf32_split(av[i], ab[i], as[i]);
+        uint32_t ah[4], al[4];  // (a0, a1, a2, a3) = (row g k-lo, row g+8 k-lo, row g k-hi, row g+8 k-hi)
+        f16_split4(A0, ah[0], ah[2], al[0], al[2]);
+        f16_split4(A1, ah[1], ah[3], al[1], al[3]);
 #pragma unroll
         for (int nt = 0; nt < NT; nt++) {
-            const float4 Wv = *reinterpret_cast<const float4*>(wp[nt] + k);
-            const float wv[4] = {Wv.x, Wv.y, Wv.z, Wv.w};  // (b0, b1) of k-step 0, then of k-step 1
-            uint32_t wb[4], wsm[4];
-#pragma unroll
-            for (int i = 0; i < 4; i++) tf32_split(wv[i], wb[i], wsm[i]);
-#pragma unroll
-            for (int j = 0; j < 2; j++) {
-                mma_tf32(acc[nt], as[4 * j], as[4 * j + 1], as[4 * j + 2], as[4 * j + 3], wb[2 * j], wb[2 * j + 1]);
-                mma_tf32(acc[nt], ab[4 * j], ab[4 * j + 1], ab[4 * j + 2], ab[4 * j + 3], wsm[2 * j], wsm[2 * j + 1]);
-                mma_tf32(acc[nt], ab[4 * j], ab[4 * j + 1], ab[4 * j + 2], ab[4 * j + 3], wb[2 * j], wb[2 * j + 1]);
-            }
+            const uint4 Wv = *reinterpret_cast<const uint4*>(wp[nt] + k);  // {hi b0, hi b1, lo b0, lo b1}
+            mma_f16(cor[nt], al[0], al[1], al[2], al[3], Wv.x, Wv.y);
+            mma_f16(cor[nt], ah[0], ah[1], ah[2], ah[3], Wv.z, Wv.w);
+            mma_f16(acc[nt], ah[0], ah[1], ah[2], ah[3], Wv.x, Wv.y);
         }
     }
 #pragma unroll
     for (int nt = 0; nt < NT; nt++) {
-        *reinterpret_cast<float2*>(&out[g][nt * 8 + 2 * tig]) = make_float2(acc[nt][0], acc[nt][1]);
-        *reinterpret_cast<float2*>(&out[g + 8][nt * 8 + 2 * tig]) = make_float2(acc[nt][2], acc[nt][3]);
+        *reinterpret_cast<float2*>(&out[g][nt * 8 + 2 * tig]) =
+            make_float2(fmaf(cor[nt][0], 1.0f / 2048.0f, acc[nt][0]), fmaf(cor[nt][1], 1.0f / 2048.0f, acc[nt][1]));
+        *reinterpret_cast<float2*>(&out[g + 8][nt * 8 + 2 * tig]) =
+            make_float2(fmaf(cor[nt][2], 1.0f / 2048.0f, acc[nt][2]), fmaf(cor[nt][3], 1.0f / 2048.0f, acc[nt][3]));
     }
 }
 
@@ -337,7 +343,7 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
     __syncthreads();
     if (t < 4 * nu) sm.rows[t] = (t / nu) * DEC + u0 + (t % nu);  // the same gate rows in both layers; rows[0..nu) = u0.. are also joint.pred's
     __syncthreads();
-    dk_stage_rows(wsm, DK_LDX, w.wcat[0], 2 * DEC, sm.rows, 4 * nu);
+    dk_stage_rows(wsm, DK_LDX, w.wcat_s[0], 2 * DEC, sm.rows, 4 * nu);
     for (int layer = 0; layer < 2; layer++) {
         for (int e0 = 0; e0 < E; e0 += DK_TS) {
             __syncthreads();
@@ -365,8 +371,8 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
             __syncthreads();
             if (tr) { q1 = now(); acc[8] += q1 - q0; q0 = q1; }
             if (e0 + DK_TS >= E) {  // last tile: the rows are dead, fetch the next phase's while the gates and the barrier run
-                if (layer == 0) dk_stage_rows(wsm, DK_LDX, w.wcat[1], 2 * DEC, sm.rows, 4 * nu);
-                else dk_stage_rows(wsm, DK_LDH, w.wpred, DEC, sm.rows, nu);
+                if (layer == 0) dk_stage_rows(wsm, DK_LDX, w.wcat_s[1], 2 * DEC, sm.rows, 4 * nu);
+                else dk_stage_rows(wsm, DK_LDH, w.wpred_s, DEC, sm.rows, nu);
             }
             if (t < DK_TS * nu) {
                 const int q = t / nu, ui = t % nu, slot = sm.sl[q];
@@ -445,7 +451,7 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
     for (int i = t; i < DK_MAXR * (JOINT / 4); i += 256) {  // rows >= nr: zero (padding columns of the MMA tile)
         const int r = i / (JOINT / 4), k = (i - r * (JOINT / 4)) * 4;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < nr) v = *reinterpret_cast<const float4*>(w.wout + (size_t)(v0 + r) * JOINT + k);
+        if (r < nr) v = *reinterpret_cast<const float4*>(w.wout_s + (size_t)(v0 + r) * JOINT + k);  // pre-split halves; zero bits = zero
         *reinterpret_cast<float4*>(&sm.wrow[r][k]) = v;
     }
     if (t < nr) sm.bias[t] = w.bout[v0 + t];

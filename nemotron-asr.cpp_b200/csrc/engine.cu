@@ -267,6 +267,22 @@ void make_f16(nb200_model* m, F16Matrix& dst, const std::vector<float>& w, int r
 }
 
 // fp32 weights [rows][K] as the fp16 triple [Wh | Wh | Wl] along K (see split_f16x3_kernel): the B operand of a GEMM of fp32 quality
+// Decode-kernel operand format (kernels.cuh DecodeWeights::wcat_s): per 4 consecutive floats 16 bytes of halves
+// {hi0..hi3 | lo0..lo3}, hi = fp16(w), lo = fp16((w - hi) * 2048); returned as floats (bit containers) of the same geometry.
+static std::vector<float> split_f16_pairs(const std::vector<float>& w) {
+    std::vector<float> out(w.size());
+    uint16_t* o = reinterpret_cast<uint16_t*>(out.data());
+    for (size_t i = 0; i + 3 < w.size(); i += 4) {
+        for (int j = 0; j < 4; j++) {
+            const __half h = __float2half_rn(w[i + j]);
+            const __half l = __float2half_rn((w[i + j] - __half2float(h)) * 2048.0f);
+            o[2 * i + j] = __half_as_ushort(h);
+            o[2 * i + 4 + j] = __half_as_ushort(l);
+        }
+    }
+    return out;
+}
+
 void make_split3(nb200_model* m, F16Matrix& dst, const std::vector<float>& w, int rows, int K) {
     std::vector<float> w3((size_t)rows * 3 * K);
     for (int n = 0; n < rows; n++)
@@ -458,14 +474,17 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
                 bc[r] = bih[r] + bhh[r];
             }
             m->dec.wcat[l] = m->upload(wc);
+            m->dec.wcat_s[l] = m->upload(split_f16_pairs(wc));
             m->dec.bcat[l] = m->upload(bc);
         }
         m->dec.wpred = m->upload(load_f32(g, "joint.pred.weight", (int64_t)JOINT * DEC));
+        m->dec.wpred_s = m->upload(split_f16_pairs(load_f32(g, "joint.pred.weight", (int64_t)JOINT * DEC)));
         m->dec.bpred = m->upload(load_f32(g, "joint.pred.bias", JOINT));
         std::vector<float> wo = load_f32(g, "joint.joint_net.2.weight", (int64_t)VOCAB * JOINT), bo = load_f32(g, "joint.joint_net.2.bias", VOCAB);
         wo.resize((size_t)1088 * JOINT, 0.0f);
         bo.resize(1088, -INFINITY);
         m->dec.wout = m->upload(wo);
+        m->dec.wout_s = m->upload(split_f16_pairs(wo));
         m->dec.bout = m->upload(bo);
         m->joint_enc_w = m->upload(load_f32(g, "joint.enc.weight", (int64_t)JOINT * D_MODEL));
         m->joint_enc_b = m->upload(load_f32(g, "joint.enc.bias", JOINT));

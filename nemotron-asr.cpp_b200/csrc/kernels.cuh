@@ -148,6 +148,12 @@ struct DecodeWeights {
     const float* bpred;
     const float* wout;         // [1088][640], rows >= 1025 are zero
     const float* bout;         // [1088], entries >= 1025 are -inf
+    // The same matrices pre-split for the decode kernel's fp16 tensor-core dot products: every 4 consecutive floats become 16
+    // bytes {hi0 hi1 hi2 hi3 | lo0 lo1 lo2 lo3} of halves, hi = fp16(w), lo = fp16((w - hi) * 2048) (decoder.cu). Same geometry
+    // as the fp32 matrix (4 bytes per element), so rows are addressed alike.
+    const float* wcat_s[2];
+    const float* wpred_s;
+    const float* wout_s;
 };
 // all greedy rounds of one batched chunk (src/nemo-stream.cpp:840-930, 1106-1118) as one persistent launch
 void launch_decode_chunk(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& b);
