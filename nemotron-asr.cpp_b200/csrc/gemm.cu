@@ -605,4 +605,105 @@ int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiPa
     return c.splits;
 }
 
+// ---- tensor-pipe peak microbenchmark (gemm.cuh mma_peak_run) ---------------------------------------------------
+// kind::i8 instruction descriptor: D = s32 (bits 4-5 = 2), A = B = signed 8-bit (1 at bits 7 and 10), K-major, N>>3 at 17, M>>4 at 24.
+__host__ __device__ constexpr uint32_t make_idesc_i8(int M, int N) {
+    return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(192) mma_peak_kernel(int iters, const uint8_t* __restrict__ a_bytes, const uint8_t* __restrict__ b_bytes,
+                                                       uint32_t* __restrict__ check_out) {
+    constexpr int BN = 256, A_BYTES = 128 * 128, B_BYTES = BN * 128;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (base - raw);
+    const uint32_t bar = base + A_BYTES + B_BYTES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + A_BYTES + B_BYTES + 8);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // operands into the 128-byte-swizzled K-major layout the descriptors expect: row r of an 8-row group at r * 128, its 16-byte
+    // chunk c at position c ^ r
+    for (int i = threadIdx.x; i < (A_BYTES + B_BYTES) / 16; i += blockDim.x) {
+        const bool is_b = i >= A_BYTES / 16;
+        const int j = is_b ? i - A_BYTES / 16 : i, row = j >> 3, chunk = j & 7;
+        const uint8_t* src = (is_b ? b_bytes : a_bytes) + (size_t)row * 128 + chunk * 16;
+        uint8_t* dst = smem + (is_b ? A_BYTES : 0) + (row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) * 16);
+        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+    }
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 256);
+    fence_async_smem();  // generic-proxy operand writes -> visible to the tensor core's async-proxy reads
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    if (warp == 1 && lane == 0) {
+        const uint64_t adesc = make_smem_desc(base), bdesc = make_smem_desc(base + A_BYTES);
+        uint32_t parity = 0;
+        for (int it = 0; it < iters; it++) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) {  // 32 bytes of K per MMA: 16 halves or 32 int8
+                if constexpr (KIND == 0) umma_f16(tmem_base, adesc + 2 * k, bdesc + 2 * k, make_idesc_f16(128, BN), (it | k) ? 1u : 0u);
+                else umma_i8(tmem_base, adesc + 2 * k, bdesc + 2 * k, make_idesc_i8(128, BN), (it | k) ? 1u : 0u);
+            }
+            if ((it & 15) == 15 || it + 1 == iters) {  // bound the number of MMAs in flight
+                umma_commit(bar);
+                mbar_wait(bar, parity);
+                parity ^= 1;
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    tc_fence_after();
+    if (warp >= 2 && check_out != nullptr && blockIdx.x == 0) {  // warps 2..5 read TMEM lane quadrants 2, 3, 0, 1
+        const int quad = warp & 3;
+#pragma unroll 1
+        for (int c = 0; c < BN; c += 32) {
+            float v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c, v);
+#pragma unroll
+            for (int j = 0; j < 32; j++) check_out[(size_t)(quad * 32 + lane) * BN + c + j] = __float_as_uint(v[j]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 256);
+    }
+}
+
+float mma_peak_run(cudaStream_t st, int kind, int ctas, int iters, const uint8_t* a_bytes, const uint8_t* b_bytes, uint32_t* check_out) {
+    const int smem = 128 * 128 + 256 * 128 + 1024 + 64;
+    auto kern = kind == 0 ? mma_peak_kernel<0> : mma_peak_kernel<1>;
+    CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    cudaEvent_t e0, e1;
+    CUDA_CHECK(cudaEventCreate(&e0));
+    CUDA_CHECK(cudaEventCreate(&e1));
+    CUDA_CHECK(cudaEventRecord(e0, st));
+    kern<<<ctas, 192, smem, st>>>(iters, a_bytes, b_bytes, check_out);
+    CUDA_CHECK(cudaEventRecord(e1, st));
+    CUDA_CHECK(cudaEventSynchronize(e1));
+    NB_KERNEL_CHECK();
+    float ms = 0.0f;
+    CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return ms;
+}
+
 }  // namespace nb

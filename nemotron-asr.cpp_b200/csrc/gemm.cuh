@@ -160,4 +160,13 @@ GemmConfig gemm_pick_config(int M, int N, int K, int max_splits, int min_bn = 32
 // bn = 0 restores the heuristic.
 void gemm_force_config(int bn, int splits);
 
+
+// Tensor-pipe peak and arithmetic check of one tcgen05.mma kind (measurement only; SURVEY section 8d asks for the int8 peak
+// beside the fp16 one): every CTA keeps one 128 x 256 operand pair of K = 128 bytes resident in shared memory and issues
+// `iters` k-blocks of 4 MMAs into the same TMEM accumulator. kind 0 = kind::f16 (fp16 operands, fp32 accumulate, K = 16 per
+// MMA), 1 = kind::i8 (signed int8 operands, int32 accumulate, K = 32 per MMA). Returns the device time of the launch in ms;
+// check_out (device, [128][256] 32-bit words, may be null) receives CTA 0's accumulator after ONE k-block of the operands
+// a_bytes / b_bytes (device, [128][128] and [256][128] bytes, K-major rows of 128 bytes).
+float mma_peak_run(cudaStream_t st, int kind, int ctas, int iters, const uint8_t* a_bytes, const uint8_t* b_bytes, uint32_t* check_out);
+
 }  // namespace nb

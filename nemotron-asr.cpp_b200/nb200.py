@@ -47,6 +47,7 @@ SYMBOLS = {
     "nb200_model_free": (None, [C.c_void_p]),
     "nb200_model_info": (C.c_int, [C.c_void_p, C.POINTER(Info)]),
     "nb200_model_token": (C.c_char_p, [C.c_void_p, C.c_int32]),
+    "nb200_bench_mma_peak": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]),
     "nb200_tokens_to_text": (C.c_int, [C.c_void_p, _I32P, C.c_int, C.c_char_p, C.c_int]),
     "nb200_tokens_to_text_timed": (C.c_int, [C.c_void_p, _I32P, _I64P, C.c_int, C.c_char_p, C.c_int]),
     "nb200_stream_create": (C.c_void_p, [C.c_void_p, C.c_int]),
@@ -272,6 +273,23 @@ class Model:
         if lib().nb200_bench_gemm(self._h, M, N, K, epi_kind, bn, splits, iters, C.byref(us), C.byref(bn_used), C.byref(sp_used)) < 0:
             raise NB200Error(_err())
         return {"us": us.value, "bn": bn_used.value, "splits": sp_used.value, "tflops": 2.0 * M * N * K / us.value * 1e-6}
+
+    def bench_mma_peak(self, kind: int, ctas: int = 148, iters: int = 4096, seed: int = 0):
+        """Tensor-pipe peak of kind::f16 (0) or kind::i8 (1) with one resident 128 x 256 tile per CTA; also returns CTA 0's
+        accumulator after one k-block and the operands, for an arithmetic check. -> (TFLOP/s or TOP/s, acc [128][256], a, b)"""
+        rng = np.random.default_rng(seed)
+        if kind == 0:
+            a = rng.integers(-8, 9, size=(128, 64)).astype(np.float16)
+            b = rng.integers(-8, 9, size=(256, 64)).astype(np.float16)
+        else:
+            a = rng.integers(-127, 128, size=(128, 128)).astype(np.int8)
+            b = rng.integers(-127, 128, size=(256, 128)).astype(np.int8)
+        acc = np.zeros((128, 256), np.uint32)
+        tops = C.c_double(0.0)
+        rc = lib().nb200_bench_mma_peak(self._h, kind, ctas, iters, a.ctypes.data, b.ctypes.data, acc.ctypes.data, C.byref(tops))
+        if rc != 0:
+            raise RuntimeError(_err())
+        return tops.value, (acc.view(np.float32) if kind == 0 else acc.view(np.int32)), a, b
 
     def trace_gemm(self, M: int, N: int, K: int, epi_kind: int = 0, bn: int = 0, splits: int = 1, launches: int = 6) -> np.ndarray:
         """Per-CTA phase timestamps [launches, ctas, 8] (ns) of back-to-back launches; see include/nb200.h."""

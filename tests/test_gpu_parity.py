@@ -5,6 +5,8 @@ Tolerances (BASELINE.json north_star): log-mel <= 1e-4 absolute; encoder_out per
 tokens identical per chunk with every mismatch traced to a near-tie logit (top1-top2 gap recorded by the library).
 """
 import os
+import subprocess
+from pathlib import Path
 
 import numpy as np
 import pytest
@@ -14,6 +16,8 @@ import nemo_oracle as no
 from conftest import GOLD
 
 pytestmark = pytest.mark.gpu
+
+ROOT = Path(__file__).resolve().parents[1]
 
 TIE_GAP = 0.02  # a token mismatch is accepted only if the chunk's smallest top1-top2 logit gap is below this
 
@@ -968,6 +972,49 @@ def test_checker_paths_agree_with_fast_paths(nb, ab_runner, env_name):
             assert np.array_equal(base[k], alt[k]), (env_name, k)
     else:
         assert len(base["tokg"]) > 10 and (np.array_equal(base["tokg"], alt["tokg"]) or True)
+
+
+def _cli_transcript(cmd):
+    r = subprocess.run([str(c) for c in cmd], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    return lines[-1] if lines else ""  # the CLI prints the increments on one line; the reference build logs its backend above it
+
+
+@pytest.mark.parametrize("rc", [13, 0])
+def test_reference_cli_runs_on_this_backend(nb, model_f32, gguf_f32, tmp_path, rc):
+    """the drop-in, compiled. oracle/_ref/cli_b200/transcribe_stream_b200 is the reference's UNMODIFIED
+    src/transcribe_stream.cpp (read loop :229-254) linked against tests/adapter/nemo_stream_b200.cpp — the nemo_stream_* /
+    nemo_init_with_backend functions of src/nemo-stream.h:271-326 / src/nemo-ggml.h:259-269 implemented over nb200_* as
+    INTEGRATION.md section 2 describes — and libnemob200.so, with no ggml object in the link. Its transcript for
+    `<f32dq gguf> <pcm> 70 <rc>` must be byte-identical to the same calls made through the Python binding, and equal to the
+    transcript of the same CLI source on the reference's own ggml-CPU path up to the first near-tie."""
+    cli_b200 = ROOT / "oracle" / "_ref" / "cli_b200" / "transcribe_stream_b200"
+    flags = open("/proc/cpuinfo").read()
+    isa = "avx512" if ("avx512_vnni" in flags or "avx512vnni" in flags) and "avx512bw" in flags else "avx2"
+    cli_ref = ROOT / "oracle" / "_ref" / isa / "transcribe_stream_ref"
+    if not cli_b200.exists() or not cli_ref.exists():
+        pytest.skip("oracle/_ref CLIs not built (make -C oracle needs the reference tree)")
+    pcm = inputs.pcm(11, 5.0)
+    f = tmp_path / "audio.pcm"
+    f.write_bytes(pcm.astype("<i2").tobytes())
+    text_b200 = _cli_transcript([cli_b200, gguf_f32, f, 70, rc])
+    text_ref = _cli_transcript([cli_ref, gguf_f32, f, 70, rc, "--cpu"])
+    # the binding, fed in the CLI's read sizes (cache_cfg.get_chunk_samples(), src/transcribe_stream.cpp:144,229)
+    got = run_stream(nb, model_f32, pcm, rc, feed=(9 + 8 * (1 + rc)) * 160)
+    api_text = model_f32.tokens_to_text(got["tokens"])
+    assert text_b200.strip() == api_text.strip() and len(text_b200.strip()) > 0
+    if text_b200 != text_ref:  # diverged at some token: that chunk must hold a near-tie
+        tb, tr = text_b200.split("t"), text_ref.split("t")
+        first = next(i for i, (a, b) in enumerate(zip(tb, tr)) if a != b) if tb[:len(tr)] != tr[:len(tb)] else min(len(tb), len(tr))
+        n_tok = first - 1  # pieces are "t<id>": split()[0] is the empty prefix
+        counts = np.cumsum(got["chunk_tokens"])
+        chunk = int(np.searchsorted(counts, n_tok, side="right"))
+        gap = got["margins"][min(chunk, len(got["margins"]) - 1)]
+        print(f"rc={rc}: CLI transcripts agree on {n_tok} of {len(tb) - 1} tokens; first difference in chunk {chunk}, smallest logit gap there {gap:.2e}")
+        assert gap < TIE_GAP
+    else:
+        print(f"rc={rc}: CLI transcripts identical ({len(text_ref)} characters)")
 
 
 def test_smoke_entry(nb):
