@@ -422,14 +422,42 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
     if (tr) { q1 = now(); acc[13] += q1 - q0; acc[14] += 1; acc[15] += (unsigned long long)E; }
 }
 
+// Commit of an emission: (h, c) = (pend_h, pend_c) of one slot (2 x 1280 floats) by NT threads. All of a thread's loads are
+// issued before its stores: a load / store pair per iteration serialises on the L2 round trip (the pointers may alias as far as
+// the compiler knows) — 40 dependent round trips per warp, which made the streams that emit hold the round's barrier for ~20 us.
+template <int NT>
+__device__ __forceinline__ void dk_commit_state(const DecodeState& s, int slot, int tid) {
+    constexpr int N4 = 2 * DEC / 4, IT = (N4 + NT - 1) / NT;
+    const float4* src[2] = {reinterpret_cast<const float4*>(s.pend_h + (size_t)slot * 2 * DEC), reinterpret_cast<const float4*>(s.pend_c + (size_t)slot * 2 * DEC)};
+    float4* dst[2] = {reinterpret_cast<float4*>(s.h + (size_t)slot * 2 * DEC), reinterpret_cast<float4*>(s.c + (size_t)slot * 2 * DEC)};
+#pragma unroll
+    for (int a = 0; a < 2; a++) {
+        float4 v[IT];
+#pragma unroll
+        for (int i = 0; i < IT; i++)
+            if (tid + i * NT < N4) v[i] = __ldcg(src[a] + tid + i * NT);
+#pragma unroll
+        for (int i = 0; i < IT; i++)
+            if (tid + i * NT < N4) dst[a][tid + i * NT] = v[i];
+    }
+}
+
 // hid[b] = relu(joint.enc(frame fp) + pend_p[slot]) for one stream, by one warp (src/nemo-ggml.cpp:1215-1217)
 // (item = b * W + window offset; W = 1: item = b)
 __device__ __forceinline__ void dk_stage_hid(const DecodeState& s, const DecodeBatch& d, int item, int b, int fp, int slot, int lane) {
-    for (int k = 4 * lane; k < JOINT; k += 128) {
-        const float4 e = *reinterpret_cast<const float4*>(d.e + ((size_t)(b * d.T + fp)) * JOINT + k);
-        const float4 p = __ldcg(reinterpret_cast<const float4*>(s.pend_p + (size_t)slot * JOINT + k));
+    constexpr int IT = JOINT / 128;  // 5 x (32 lanes x 4 floats); all loads are issued before the stores (see dk_commit_state)
+    float4 e[IT], p[IT];
+#pragma unroll
+    for (int i = 0; i < IT; i++) {
+        const int k = 4 * lane + 128 * i;
+        e[i] = *reinterpret_cast<const float4*>(d.e + ((size_t)(b * d.T + fp)) * JOINT + k);
+        p[i] = __ldcg(reinterpret_cast<const float4*>(s.pend_p + (size_t)slot * JOINT + k));
+    }
+#pragma unroll
+    for (int i = 0; i < IT; i++) {
+        const int k = 4 * lane + 128 * i;
         *reinterpret_cast<float4*>(d.hid + (size_t)item * JOINT + k) =
-            make_float4(fmaxf(e.x + p.x, 0.f), fmaxf(e.y + p.y, 0.f), fmaxf(e.z + p.z, 0.f), fmaxf(e.w + p.w, 0.f));
+            make_float4(fmaxf(e[i].x + p[i].x, 0.f), fmaxf(e[i].y + p[i].y, 0.f), fmaxf(e[i].z + p[i].z, 0.f), fmaxf(e[i].w + p[i].w, 0.f));
     }
 }
 
@@ -465,7 +493,7 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
     }
     // hid of every stream's first symbol step (fp = 0, pending pred from the previous chunk); the owner warp of stream b
     const int W = d.W;
-    for (int b = cta * 8 + warp; b < d.B; b += G * 8)
+    for (int b = cta + G * warp; b < d.B; b += G * 8)
         for (int wi = 0; wi < W && wi < d.nvalid[b]; wi++) dk_stage_hid(s, d, b * W + wi, b, wi, d.slot[b], lane);
     grid_barrier(d.bar, phase);
 
@@ -599,17 +627,14 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                 __syncthreads();
                 const int emit = sm.wemit, f = sm.wf;
                 if (emit) {  // commit the pending LSTM state; the new pending state and the next window's hid follow in phase E
-                    for (int i = t; i < 2 * DEC; i += 256) {
-                        s.h[(size_t)slot * 2 * DEC + i] = __ldcg(s.pend_h + (size_t)slot * 2 * DEC + i);
-                        s.c[(size_t)slot * 2 * DEC + i] = __ldcg(s.pend_c + (size_t)slot * 2 * DEC + i);
-                    }
+                    dk_commit_state<256>(s, slot, t);
                 } else {  // all blank: same pending pred, next window
                     for (int wi = warp; wi < W && f + wi < nvalid; wi += 8) dk_stage_hid(s, d, b * W + wi, b, f + wi, slot, lane);
                 }
                 __syncthreads();
             }
         } else
-        for (int b = cta * 8 + warp; b < d.B; b += G * 8) {
+        for (int b = cta + G * warp; b < d.B; b += G * 8) {  // a warp per stream, the streams spread over all CTAs
             const int nvalid = d.nvalid[b], slot = d.slot[b];
             const int fp = __ldcg(d.fp + b);
             if (fp >= nvalid) continue;
@@ -653,10 +678,7 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
             emit = __shfl_sync(0xffffffffu, emit, 0);
             f = __shfl_sync(0xffffffffu, f, 0);
             if (emit) {  // commit the pending LSTM state; the new pending state and hid follow in phase E
-                for (int i = lane; i < 2 * DEC; i += 32) {
-                    s.h[(size_t)slot * 2 * DEC + i] = __ldcg(s.pend_h + (size_t)slot * 2 * DEC + i);
-                    s.c[(size_t)slot * 2 * DEC + i] = __ldcg(s.pend_c + (size_t)slot * 2 * DEC + i);
-                }
+                dk_commit_state<32>(s, slot, lane);
             } else if (f < nvalid) {
                 dk_stage_hid(s, d, b, b, f, slot, lane);  // blank: same pending pred, next frame
             }
