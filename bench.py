@@ -202,7 +202,8 @@ def main():
     ap.add_argument("--streams", type=int, default=64, help="concurrent streams per GPU")
     ap.add_argument("--rc", type=int, default=13, choices=(0, 1, 6, 13))
     ap.add_argument("--layers", type=int, default=24)
-    ap.add_argument("--variant", default="q8_0", choices=("q8_0", "f32dq"))
+    ap.add_argument("--variant", default="q8_0", choices=("q8_0", "f32dq", "f16"),
+                    help="weight format of the GGUF: q8_0 (headline), f16 (the reference converter's 16-bit format; it has no BF16, scripts/convert_to_gguf.py:322-336), f32dq")
     ap.add_argument("--no-latency-path", action="store_true", help="skip the config-3 leg (80 ms chunks, 128 streams per GPU)")
     ap.add_argument("--latency-steps", type=int, default=200)
     ap.add_argument("--no-cpu-baseline", action="store_true")

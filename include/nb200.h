@@ -64,6 +64,15 @@ int nb200_version(void);
 /* nemo_init_with_backend(path, backend) — src/nemo-ggml.h:259, src/nemo-ggml.cpp:448-495 (GGUF load :83-442).
  * device: CUDA ordinal. max_streams: stream slots to reserve (K/V/conv caches live in HBM per slot). */
 nb200_model* nb200_model_load(const char* gguf_path, int device, int max_streams, int flags);
+/* nb200_model_load through the NATIVE WEIGHT FILE (the reference's on-disk formats are chosen by its converter,
+ * scripts/convert_to_gguf.py:322-336, and ggml dequantises on the fly): the big operands in the device-ready form this backend
+ * lays them out in (fp16 [N][K] with q|k|v stacked, GLU rows interleaved, pre_encode.out columns permuted, the split-precision
+ * triples and hi/lo pairs of joint / LSTM). cache_path NULL = "<gguf_path>.nb200w". If the file exists and was made from this
+ * GGUF (size + mtime stamp, layout version) the operands are copied straight from its mmap; otherwise the model is built from the
+ * GGUF as usual and the file is (re)written, atomically. The GGUF itself is always opened (hyper-parameters, vocabulary, the small
+ * fp32 tensors). nb200_model_cache_stats: how many big operands came from the cache / were built from the GGUF. */
+nb200_model* nb200_model_load_cached(const char* gguf_path, const char* cache_path, int device, int max_streams, int flags);
+int nb200_model_cache_stats(const nb200_model* m, int64_t* from_cache, int64_t* from_gguf);
 /* Host-only check of a GGUF file (no GPU needed): parses the container exactly like nb200_model_load — header, KVs, tensor
  * table with the bounds of every tensor inside the file, the vocabulary (tokenizer.vocab_list, or the legacy 8-byte-piece blob
  * tokenizer.vocab, src/nemo-ggml.cpp:149-169) — and writes a JSON summary {"tensors", "tensor_bytes", "vocab_source",

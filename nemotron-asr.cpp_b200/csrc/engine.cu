@@ -17,6 +17,7 @@
 #include "gemm.cuh"
 #include "gguf_reader.h"
 #include "kernels.cuh"
+#include "weight_cache.h"
 
 using namespace nb;
 
@@ -228,6 +229,28 @@ struct nb200_model {
         CUDA_CHECK(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
         return p;
     }
+    // The native weight file (weight_cache.h): a big operand is taken from the cache when it is there (mmap -> one copy to the
+    // device; `produce`, the dequantise-and-repack on the host, is not run), otherwise produced, uploaded and appended to the cache
+    // being written. n = element count the layout expects.
+    std::unique_ptr<WeightCacheReader> wc_in;
+    std::unique_ptr<WeightCacheWriter> wc_out;
+    long long wc_hits = 0, wc_misses = 0;
+    template <typename T, typename F>
+    T* upload_cached(const std::string& key, size_t n, F&& produce) {
+        if (wc_in) {
+            if (const WeightCacheBlob* b = wc_in->find(key, n * sizeof(T))) {
+                T* p = alloc<T>(n, false);
+                CUDA_CHECK(cudaMemcpy(p, b->data, n * sizeof(T), cudaMemcpyHostToDevice));
+                wc_hits++;
+                return p;
+            }
+        }
+        const std::vector<T> v = produce();
+        if (v.size() != n) throw Error("weight layout: " + key + " has " + std::to_string(v.size()) + " elements, expected " + std::to_string(n));
+        if (wc_out) wc_out->add(key, v.data(), n * sizeof(T));
+        wc_misses++;
+        return upload(v);
+    }
     ~nb200_model() {
         for (auto* s : streams) delete s;
         for (void* p : allocs) cudaFree(p);
@@ -258,15 +281,20 @@ std::vector<float> load_f32(const GgufFile& g, const std::string& name, int64_t 
     return v;
 }
 
-void make_f16(nb200_model* m, F16Matrix& dst, const std::vector<float>& w, int rows, int K, const std::string& name = "") {
-    std::vector<__half> h((size_t)rows * K);
-    for (size_t i = 0; i < h.size(); i++) h[i] = __float2half_rn(w[i]);
-    dst.ptr = m->upload(h);
+// fp32 [rows][K] (from `produce`) -> the fp16 GEMM operand on the device, through the weight cache under `key`
+template <typename F>
+void make_f16(nb200_model* m, F16Matrix& dst, const std::string& key, int rows, int K, F&& produce, const std::string& name = "") {
+    dst.ptr = m->upload_cached<__half>(key, (size_t)rows * K, [&] {
+        const std::vector<float> w = produce();
+        if (w.size() != (size_t)rows * K) throw Error("weight layout: " + key + " has the wrong size");
+        std::vector<__half> h(w.size());
+        for (size_t i = 0; i < h.size(); i++) h[i] = __float2half_rn(w[i]);
+        return h;
+    });
     operand_init(dst.op, dst.ptr, rows, K);
     if (!name.empty()) m->by_name[name] = {dst.ptr, rows, K, false};
 }
 
-// fp32 weights [rows][K] as the fp16 triple [Wh | Wh | Wl] along K (see split_f16x3_kernel): the B operand of a GEMM of fp32 quality
 // Decode-kernel operand format (kernels.cuh DecodeWeights::wcat_s): per 4 consecutive floats 16 bytes of halves
 // {hi0..hi3 | lo0..lo3}, hi = fp16(w), lo = fp16((w - hi) * 2048); returned as floats (bit containers) of the same geometry.
 static std::vector<float> split_f16_pairs(const std::vector<float>& w) {
@@ -283,21 +311,27 @@ static std::vector<float> split_f16_pairs(const std::vector<float>& w) {
     return out;
 }
 
-void make_split3(nb200_model* m, F16Matrix& dst, const std::vector<float>& w, int rows, int K) {
-    std::vector<float> w3((size_t)rows * 3 * K);
-    for (int n = 0; n < rows; n++)
-        for (int k = 0; k < K; k++) {
-            const float v = w[(size_t)n * K + k];
-            const float hi = __half2float(__float2half_rn(v));
-            w3[(size_t)n * 3 * K + k] = hi;
-            w3[(size_t)n * 3 * K + K + k] = hi;
-            w3[(size_t)n * 3 * K + 2 * K + k] = v - hi;  // rounded to fp16 by make_f16
-        }
-    make_f16(m, dst, w3, rows, 3 * K);
+// fp32 weights [rows][K] as the fp16 triple [Wh | Wh | Wl] along K (see split_f16x3_kernel): the B operand of a GEMM of fp32 quality
+template <typename F>
+void make_split3(nb200_model* m, F16Matrix& dst, const std::string& key, int rows, int K, F&& produce) {
+    make_f16(m, dst, key + "#split3", rows, 3 * K, [&] {
+        const std::vector<float> w = produce();
+        if (w.size() != (size_t)rows * K) throw Error("weight layout: " + key + " has the wrong size");
+        std::vector<float> w3((size_t)rows * 3 * K);
+        for (int n = 0; n < rows; n++)
+            for (int k = 0; k < K; k++) {
+                const float v = w[(size_t)n * K + k];
+                const float hi = __half2float(__float2half_rn(v));
+                w3[(size_t)n * 3 * K + k] = hi;
+                w3[(size_t)n * 3 * K + K + k] = hi;
+                w3[(size_t)n * 3 * K + 2 * K + k] = v - hi;  // rounded to fp16 by make_f16
+            }
+        return w3;
+    });
 }
 
 void load_matrix(nb200_model* m, const GgufFile& g, F16Matrix& dst, const std::string& name, int rows, int K) {
-    make_f16(m, dst, load_f32(g, name, (int64_t)rows * K), rows, K, name);
+    make_f16(m, dst, name, rows, K, [&] { return load_f32(g, name, (int64_t)rows * K); }, name);
 }
 
 uint32_t kv_u32(const GgufFile& g, const char* key, uint32_t dflt) {
@@ -322,9 +356,20 @@ const char* load_vocab(GgufFile& g, int vocab_size, std::vector<std::string>& vo
     throw Error("no vocabulary in GGUF (need tokenizer.vocab_list or tokenizer.vocab)");
 }
 
-void build_model(nb200_model* m, const std::string& path, int flags) {
+void build_model(nb200_model* m, const std::string& path, int flags, const char* cache_path) {
     GgufFile g;
     g.open(path);
+    if (cache_path) {  // the native weight file: use it if it was made from this GGUF, else (re)write it while loading
+        uint64_t src_size = 0, src_mtime = 0;
+        file_stamp(path, src_size, src_mtime);
+        const std::string cp = *cache_path ? std::string(cache_path) : path + ".nb200w";
+        m->wc_in.reset(new WeightCacheReader());
+        if (!m->wc_in->open(cp, src_size, src_mtime)) {
+            m->wc_in.reset();
+            m->wc_out.reset(new WeightCacheWriter());
+            m->wc_out->open(cp, src_size, src_mtime);
+        }
+    }
     nb200_info& hp = m->info;
     hp.n_mels = kv_u32(g, "nemo.n_mels", N_MELS);
     hp.d_model = kv_u32(g, "nemo.d_model", D_MODEL);
@@ -407,11 +452,13 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
         load_matrix(m, g, m->sub_w6, pe + "conv.6.weight", 256, 256);
         m->sub_b6 = m->upload(load_f32(g, pe + "conv.6.bias", 256));
         // out.weight [1024][c*17+w] -> [1024][w*256+c]: our activations are position-major, channel fastest
-        std::vector<float> wo = load_f32(g, pe + "out.weight", (int64_t)D_MODEL * SUB_FEAT), wp(wo.size());
-        for (int n = 0; n < D_MODEL; n++)
-            for (int c = 0; c < SUB_CH; c++)
-                for (int w = 0; w < SUB_F3; w++) wp[(size_t)n * SUB_FEAT + w * SUB_CH + c] = wo[(size_t)n * SUB_FEAT + c * SUB_F3 + w];
-        make_f16(m, m->sub_wout, wp, D_MODEL, SUB_FEAT);
+        make_f16(m, m->sub_wout, pe + "out.weight#w256c", D_MODEL, SUB_FEAT, [&] {
+            std::vector<float> wo = load_f32(g, pe + "out.weight", (int64_t)D_MODEL * SUB_FEAT), wp(wo.size());
+            for (int n = 0; n < D_MODEL; n++)
+                for (int c = 0; c < SUB_CH; c++)
+                    for (int w = 0; w < SUB_F3; w++) wp[(size_t)n * SUB_FEAT + w * SUB_CH + c] = wo[(size_t)n * SUB_FEAT + c * SUB_F3 + w];
+            return wp;
+        });
         m->sub_bout = m->upload(load_f32(g, pe + "out.bias", D_MODEL));
     }
     // ---- conformer layers (src/nemo-ggml.cpp:310-361) ----
@@ -436,24 +483,28 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
         load_matrix(m, g, L.wout, p + "self_attn.linear_out.weight", D_MODEL, D_MODEL);
         load_matrix(m, g, L.pw2, p + "conv.pointwise_conv2.weight", D_MODEL, D_MODEL);
         {   // q|k|v stacked: one N=3072 GEMM over the same (re-quantised) LN output
-            std::vector<float> w((size_t)3 * D_MODEL * D_MODEL);
             const char* nm[3] = {"self_attn.linear_q.weight", "self_attn.linear_k.weight", "self_attn.linear_v.weight"};
-            for (int i = 0; i < 3; i++) {
-                std::vector<float> part = load_f32(g, p + nm[i], (int64_t)D_MODEL * D_MODEL);
-                std::copy(part.begin(), part.end(), w.begin() + (size_t)i * D_MODEL * D_MODEL);
-            }
-            make_f16(m, L.wqkv, w, 3 * D_MODEL, D_MODEL);
+            make_f16(m, L.wqkv, p + "self_attn.qkv", 3 * D_MODEL, D_MODEL, [&] {
+                std::vector<float> w((size_t)3 * D_MODEL * D_MODEL);
+                for (int i = 0; i < 3; i++) {
+                    std::vector<float> part = load_f32(g, p + nm[i], (int64_t)D_MODEL * D_MODEL);
+                    std::copy(part.begin(), part.end(), w.begin() + (size_t)i * D_MODEL * D_MODEL);
+                }
+                return w;
+            });
             for (int i = 0; i < 3; i++) m->by_name[p + nm[i]] = {L.wqkv.ptr + (size_t)i * D_MODEL * D_MODEL, D_MODEL, D_MODEL, false};
             m->by_name[p + "self_attn.qkv"] = {L.wqkv.ptr, 3 * D_MODEL, D_MODEL, false};  // the stacked matrix the step multiplies by (debug entry points)
         }
         {   // pointwise_conv1: rows 0..1023 = GLU value, 1024..2047 = gate -> interleave (value_j, gate_j)
-            std::vector<float> w = load_f32(g, p + "conv.pointwise_conv1.weight", (int64_t)2 * D_MODEL * D_MODEL), wi(w.size());
-            for (int j = 0; j < D_MODEL; j++) {
-                std::copy(w.begin() + (size_t)j * D_MODEL, w.begin() + (size_t)(j + 1) * D_MODEL, wi.begin() + (size_t)(2 * j) * D_MODEL);
-                std::copy(w.begin() + (size_t)(D_MODEL + j) * D_MODEL, w.begin() + (size_t)(D_MODEL + j + 1) * D_MODEL,
-                          wi.begin() + (size_t)(2 * j + 1) * D_MODEL);
-            }
-            make_f16(m, L.pw1, wi, 2 * D_MODEL, D_MODEL);
+            make_f16(m, L.pw1, p + "conv.pointwise_conv1.weight#glu", 2 * D_MODEL, D_MODEL, [&] {
+                std::vector<float> w = load_f32(g, p + "conv.pointwise_conv1.weight", (int64_t)2 * D_MODEL * D_MODEL), wi(w.size());
+                for (int j = 0; j < D_MODEL; j++) {
+                    std::copy(w.begin() + (size_t)j * D_MODEL, w.begin() + (size_t)(j + 1) * D_MODEL, wi.begin() + (size_t)(2 * j) * D_MODEL);
+                    std::copy(w.begin() + (size_t)(D_MODEL + j) * D_MODEL, w.begin() + (size_t)(D_MODEL + j + 1) * D_MODEL,
+                              wi.begin() + (size_t)(2 * j + 1) * D_MODEL);
+                }
+                return wi;
+            });
             m->by_name[p + "conv.pointwise_conv1.weight"] = {L.pw1.ptr, 2 * D_MODEL, D_MODEL, true};
         }
     }
@@ -463,33 +514,41 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
         m->dec.embed = m->upload(load_f32(g, d + "embed.weight", (int64_t)VOCAB * DEC));
         for (int l = 0; l < 2; l++) {
             const std::string s = std::to_string(l);
-            std::vector<float> wih = load_f32(g, d + "dec_rnn.lstm.weight_ih_l" + s, (int64_t)4 * DEC * DEC);
-            std::vector<float> whh = load_f32(g, d + "dec_rnn.lstm.weight_hh_l" + s, (int64_t)4 * DEC * DEC);
+            auto wcat = [&] {  // [W_ih | W_hh] per gate row
+                std::vector<float> wih = load_f32(g, d + "dec_rnn.lstm.weight_ih_l" + s, (int64_t)4 * DEC * DEC);
+                std::vector<float> whh = load_f32(g, d + "dec_rnn.lstm.weight_hh_l" + s, (int64_t)4 * DEC * DEC);
+                std::vector<float> wc((size_t)4 * DEC * 2 * DEC);
+                for (int r = 0; r < 4 * DEC; r++) {
+                    std::copy(wih.begin() + (size_t)r * DEC, wih.begin() + (size_t)(r + 1) * DEC, wc.begin() + (size_t)r * 2 * DEC);
+                    std::copy(whh.begin() + (size_t)r * DEC, whh.begin() + (size_t)(r + 1) * DEC, wc.begin() + (size_t)r * 2 * DEC + DEC);
+                }
+                return wc;
+            };
+            m->dec.wcat[l] = m->upload_cached<float>(d + "dec_rnn.lstm.l" + s + "#cat", (size_t)4 * DEC * 2 * DEC, wcat);
+            m->dec.wcat_s[l] = m->upload_cached<float>(d + "dec_rnn.lstm.l" + s + "#cat#hilo", (size_t)4 * DEC * 2 * DEC, [&] { return split_f16_pairs(wcat()); });
             std::vector<float> bih = load_f32(g, d + "dec_rnn.lstm.bias_ih_l" + s, 4 * DEC);
             std::vector<float> bhh = load_f32(g, d + "dec_rnn.lstm.bias_hh_l" + s, 4 * DEC);
-            std::vector<float> wc((size_t)4 * DEC * 2 * DEC), bc(4 * DEC);
-            for (int r = 0; r < 4 * DEC; r++) {
-                std::copy(wih.begin() + (size_t)r * DEC, wih.begin() + (size_t)(r + 1) * DEC, wc.begin() + (size_t)r * 2 * DEC);
-                std::copy(whh.begin() + (size_t)r * DEC, whh.begin() + (size_t)(r + 1) * DEC, wc.begin() + (size_t)r * 2 * DEC + DEC);
-                bc[r] = bih[r] + bhh[r];
-            }
-            m->dec.wcat[l] = m->upload(wc);
-            m->dec.wcat_s[l] = m->upload(split_f16_pairs(wc));
+            std::vector<float> bc(4 * DEC);
+            for (int r = 0; r < 4 * DEC; r++) bc[r] = bih[r] + bhh[r];
             m->dec.bcat[l] = m->upload(bc);
         }
         m->dec.wpred = m->upload(load_f32(g, "joint.pred.weight", (int64_t)JOINT * DEC));
-        m->dec.wpred_s = m->upload(split_f16_pairs(load_f32(g, "joint.pred.weight", (int64_t)JOINT * DEC)));
+        m->dec.wpred_s = m->upload_cached<float>("joint.pred.weight#hilo", (size_t)JOINT * DEC, [&] { return split_f16_pairs(load_f32(g, "joint.pred.weight", (int64_t)JOINT * DEC)); });
         m->dec.bpred = m->upload(load_f32(g, "joint.pred.bias", JOINT));
-        std::vector<float> wo = load_f32(g, "joint.joint_net.2.weight", (int64_t)VOCAB * JOINT), bo = load_f32(g, "joint.joint_net.2.bias", VOCAB);
-        wo.resize((size_t)1088 * JOINT, 0.0f);
+        auto wout = [&] {
+            std::vector<float> wo = load_f32(g, "joint.joint_net.2.weight", (int64_t)VOCAB * JOINT);
+            wo.resize((size_t)1088 * JOINT, 0.0f);
+            return wo;
+        };
+        std::vector<float> bo = load_f32(g, "joint.joint_net.2.bias", VOCAB);
         bo.resize(1088, -INFINITY);
-        m->dec.wout = m->upload(wo);
-        m->dec.wout_s = m->upload(split_f16_pairs(wo));
+        m->dec.wout = m->upload_cached<float>("joint.joint_net.2.weight#pad1088", (size_t)1088 * JOINT, wout);
+        m->dec.wout_s = m->upload_cached<float>("joint.joint_net.2.weight#pad1088#hilo", (size_t)1088 * JOINT, [&] { return split_f16_pairs(wout()); });
         m->dec.bout = m->upload(bo);
         m->joint_enc_w = m->upload(load_f32(g, "joint.enc.weight", (int64_t)JOINT * D_MODEL));
         m->joint_enc_b = m->upload(load_f32(g, "joint.enc.bias", JOINT));
         {
-            make_split3(m, m->joint_enc_w3, load_f32(g, "joint.enc.weight", (int64_t)JOINT * D_MODEL), JOINT, D_MODEL);
+            make_split3(m, m->joint_enc_w3, "joint.enc.weight", JOINT, D_MODEL, [&] { return load_f32(g, "joint.enc.weight", (int64_t)JOINT * D_MODEL); });
             m->joint_enc_tc = getenv("NB200_JOINT_SGEMM") == nullptr;
         }
     }
@@ -503,13 +562,13 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
             for (int q = 0; q < P; q++) l[(size_t)q * H + n] = w1[(size_t)n * (D_MODEL + P) + D_MODEL + q];
         }
         m->pk_w1 = m->upload(a);
-        make_split3(m, m->pk_w1_3, a, H, D_MODEL);
+        make_split3(m, m->pk_w1_3, "prompt_kernel.0.weight#enc", H, D_MODEL, [&] { return a; });
         m->pk_w1_lang = m->upload(l);
         m->pk_b1 = m->upload(load_f32(g, "prompt_kernel.0.bias", H));
         {
             const std::vector<float> w2 = load_f32(g, "prompt_kernel.2.weight", (int64_t)D_MODEL * H);
             m->pk_w2 = m->upload(w2);
-            make_split3(m, m->pk_w2_3, w2, D_MODEL, H);
+            make_split3(m, m->pk_w2_3, "prompt_kernel.2.weight", D_MODEL, H, [&] { return w2; });
         }
         m->pk_b2 = m->upload(load_f32(g, "prompt_kernel.2.bias", D_MODEL));
         m->default_prompt = 101 < P ? 101 : 0;  // 101 = "auto" (src/nemo-ggml.cpp:459-462)
@@ -520,6 +579,11 @@ void build_model(nb200_model* m, const std::string& path, int flags) {
     } else if (g.has("prompt_kernel.0.weight")) {
         throw Error("prompt_kernel weights present but nemo.num_prompts is 0");
     }
+    if (m->wc_out) {
+        m->wc_out->commit();
+        m->wc_out.reset();
+    }
+    m->wc_in.reset();  // unmap: everything is on the device now
 }
 
 }  // namespace
@@ -1212,7 +1276,7 @@ int nb200_gguf_check(const char* gguf_path, char* json_out, int cap) {
     NB_CATCH(NB200_ERR)
 }
 
-nb200_model* nb200_model_load(const char* gguf_path, int device, int max_streams, int flags) {
+static nb200_model* model_load_impl(const char* gguf_path, const char* cache_path, int device, int max_streams, int flags) {
     nb200_model* m = nullptr;
     try {
         if (!gguf_path) throw Error("null path");
@@ -1232,7 +1296,7 @@ nb200_model* nb200_model_load(const char* gguf_path, int device, int max_streams
         CUDA_CHECK(cudaStreamCreateWithFlags(&m->st, cudaStreamNonBlocking));
         CUDA_CHECK(cudaStreamCreateWithFlags(&m->st_copy, cudaStreamNonBlocking));
         CUDA_CHECK(cudaEventCreateWithFlags(&m->upload_ev, cudaEventDisableTiming));
-        build_model(m, gguf_path, flags);
+        build_model(m, gguf_path, flags, cache_path);
         alloc_state(m);
         CUDA_CHECK(cudaStreamSynchronize(m->st));
         return m;
@@ -1241,6 +1305,21 @@ nb200_model* nb200_model_load(const char* gguf_path, int device, int max_streams
         delete m;
         return nullptr;
     }
+}
+
+nb200_model* nb200_model_load(const char* gguf_path, int device, int max_streams, int flags) {
+    return model_load_impl(gguf_path, nullptr, device, max_streams, flags);
+}
+
+nb200_model* nb200_model_load_cached(const char* gguf_path, const char* cache_path, int device, int max_streams, int flags) {
+    return model_load_impl(gguf_path, cache_path ? cache_path : "", device, max_streams, flags);
+}
+
+int nb200_model_cache_stats(const nb200_model* m, int64_t* from_cache, int64_t* from_gguf) {
+    if (!m) return NB200_ERR;
+    if (from_cache) *from_cache = m->wc_hits;
+    if (from_gguf) *from_gguf = m->wc_misses;
+    return NB200_OK;
 }
 
 void nb200_model_free(nb200_model* m) {

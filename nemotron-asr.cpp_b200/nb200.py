@@ -47,6 +47,8 @@ SYMBOLS = {
     "nb200_model_free": (None, [C.c_void_p]),
     "nb200_model_info": (C.c_int, [C.c_void_p, C.POINTER(Info)]),
     "nb200_model_token": (C.c_char_p, [C.c_void_p, C.c_int32]),
+    "nb200_model_load_cached": (C.c_void_p, [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int]),
+    "nb200_model_cache_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "nb200_bench_mma_peak": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]),
     "nb200_tokens_to_text": (C.c_int, [C.c_void_p, _I32P, C.c_int, C.c_char_p, C.c_int]),
     "nb200_tokens_to_text_timed": (C.c_int, [C.c_void_p, _I32P, _I64P, C.c_int, C.c_char_p, C.c_int]),
@@ -129,13 +131,25 @@ def gguf_check(path: str) -> dict:
 class Model:
     """nemo_context equivalent (src/nemo-ggml.h:236-261)."""
 
-    def __init__(self, gguf_path: str, device: int = 0, max_streams: int = 64, flags: int = 0):
-        self._h = lib().nb200_model_load(os.fsencode(gguf_path), device, max_streams, flags)
+    def __init__(self, gguf_path: str, device: int = 0, max_streams: int = 64, flags: int = 0, weight_cache: "str | bool | None" = None):
+        """weight_cache: None = build from the GGUF; True = through the native weight file next to the GGUF ("<gguf>.nb200w");
+        a path = through that file (nb200_model_load_cached)."""
+        if weight_cache is None or weight_cache is False:
+            self._h = lib().nb200_model_load(os.fsencode(gguf_path), device, max_streams, flags)
+        else:
+            cp = None if weight_cache is True else os.fsencode(weight_cache)
+            self._h = lib().nb200_model_load_cached(os.fsencode(gguf_path), cp, device, max_streams, flags)
         if not self._h:
             raise NB200Error(_err())
         self.info = Info()
         lib().nb200_model_info(self._h, C.byref(self.info))
         self._streams: list[Stream] = []
+
+    def cache_stats(self) -> tuple[int, int]:
+        """(big operands taken from the native weight file, built from the GGUF)"""
+        a, b = C.c_int64(0), C.c_int64(0)
+        lib().nb200_model_cache_stats(self._h, C.byref(a), C.byref(b))
+        return a.value, b.value
 
     def close(self):
         if self._h:

@@ -974,6 +974,44 @@ def test_checker_paths_agree_with_fast_paths(nb, ab_runner, env_name):
         assert len(base["tokg"]) > 10 and (np.array_equal(base["tokg"], alt["tokg"]) or True)
 
 
+def test_native_weight_file_round_trip(nb, gguf_q8, tmp_path):
+    """SURVEY section 8(f)-2 / VERDICT r1 next-8: the native weight file. First load builds the model from the GGUF and writes
+    the cache; the second load takes every big operand from it (no dequantise / repack on the host) and must produce
+    bit-identical encoder output and tokens; a cache made from another GGUF (stamp mismatch) is ignored and rewritten; a
+    truncated cache is rejected, not trusted."""
+    import time
+    cache = tmp_path / "model.nb200w"
+    pcm = inputs.pcm(11, 3.0)
+    t0 = time.perf_counter()
+    m1 = nb.Model(gguf_q8, device=0, max_streams=4, weight_cache=str(cache))
+    t_build = time.perf_counter() - t0
+    hits1, miss1 = m1.cache_stats()
+    a = run_stream(nb, m1, pcm, 13)
+    m1.close()
+    assert hits1 == 0 and miss1 > 20 and cache.exists() and cache.stat().st_size > 50e6
+    t0 = time.perf_counter()
+    m2 = nb.Model(gguf_q8, device=0, max_streams=4, weight_cache=str(cache))
+    t_cached = time.perf_counter() - t0
+    hits2, miss2 = m2.cache_stats()
+    b = run_stream(nb, m2, pcm, 13)
+    m2.close()
+    print(f"load from GGUF (+ cache write) {t_build:.2f} s, from the native weight file {t_cached:.2f} s; operands {miss1} built / {hits2} cached")
+    assert miss2 == 0 and hits2 == miss1
+    assert np.array_equal(a["enc"], b["enc"]) and a["tokens"] == b["tokens"]
+    # a truncated file must not be used
+    data = cache.read_bytes()
+    cache.write_bytes(data[: len(data) // 2])
+    m3 = nb.Model(gguf_q8, device=0, max_streams=4, weight_cache=str(cache))
+    hits3, miss3 = m3.cache_stats()
+    m3.close()
+    assert hits3 == 0 and miss3 == miss1 and cache.stat().st_size == len(data)  # rebuilt and rewritten
+    # another GGUF's cache (different stamp) is ignored
+    m4 = nb.Model(inputs.gguf_path("f32dq"), device=0, max_streams=4, weight_cache=str(cache))
+    hits4, _ = m4.cache_stats()
+    m4.close()
+    assert hits4 == 0
+
+
 def _cli_transcript(cmd):
     r = subprocess.run([str(c) for c in cmd], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
