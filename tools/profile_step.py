@@ -20,11 +20,11 @@ def main():
     ap.add_argument("--rc", type=int, default=13)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--layers", type=int, default=24)
-    ap.add_argument("--blank-gain", type=float, default=6.3)
     a = ap.parse_args()
+    import bench
     import inputs
     import nb200
-    gguf = inputs.gguf_path("q8_0", a.layers, a.blank_gain)
+    gguf = bench.bench_gguf("q8_0", a.layers)  # the benchmark's model (token-emitting decoder)
     m = nb200.Model(gguf, 0, a.streams)
     cs = 8 * (1 + a.rc) * 160
     base = [inputs.pcm(100 + i, 8.0) for i in range(8)]
