@@ -885,7 +885,7 @@ namespace {
 // q | k | v (ws_qkv16) into the attention context (ws_a16). Shared by the streaming step and the offline path. Returns the
 // encoder output ([M][1024] fp32, ws_x or ws_g).
 template <typename AttnFn>
-const float* enqueue_layers(nb200_model* m, int B, int T, AttnFn&& attn) {
+const float* enqueue_layers(nb200_model* m, int B, int T, AttnFn&& attn, bool kv_prefetch = false) {
     const int M = B * T, capB = m->cap_B;
     const int aq = m->act_quant ? 1 : 0;
     const bool simt = m->simt;
@@ -904,30 +904,55 @@ const float* enqueue_layers(nb200_model* m, int B, int T, AttnFn&& attn) {
         part.kind = EPI_PARTIAL; part.out_f32 = m->ws_part; part.ldo = D_MODEL; part.split_stride = m->part_rows * D_MODEL;
         ResidualIn rin;
         rin.partials = m->ws_part; rin.stride = part.split_stride;
+        // every GEMM asks for the NEXT GEMM's weights to be brought into L2 while its own main loop runs (EpiParams::pf_ptr)
+        auto next_w = [](EpiParams& e, const F16Matrix* w) {
+            e.pf_ptr = w ? w->ptr : nullptr;
+            e.pf_bytes = w ? (size_t)w->op.rows * w->op.K * sizeof(__half) : 0;
+        };
+        // ... and, during FFN1, for this layer's K / V ring slabs of the batch's streams (read by the attention kernel 4 launches later)
+        auto kv_slabs = [&](EpiParams& e, const __half* ring) {
+            e.pf2_base = kv_prefetch ? ring + (size_t)l * S * RING * D_MODEL : nullptr;
+            e.pf2_stride = (size_t)RING * D_MODEL * sizeof(__half);
+            e.pf2_bytes = (unsigned)(RING * D_MODEL * sizeof(__half));
+            e.pf2_slot = d_slot;
+            e.pf2_count = B;
+        };
+        next_w(up, &L.ff1_w2);
+        kv_slabs(up, m->k_ring);
         gemm(st, m->op_a16, L.ff1_w1.op, M, up, simt);
+        up.pf2_base = nullptr;
+        next_w(part, &L.wqkv);
+        kv_slabs(part, m->v_ring);
         rin.nsplit = gemm(st, m->op_h16, L.ff1_w2.op, M, part, simt, m->part_max_splits);
+        part.pf2_base = nullptr;
         rin.alpha = 0.5f;  // x += 0.5 * FFN1
         // self-attention
         launch_layernorm(st, m->ws_x, L.ln_att_g, L.ln_att_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin);
         EpiParams qkv;  // q | k | v of the chunk's frames, dense fp16; the attention kernel appends k, v to the stream rings
         qkv.kind = EPI_STORE_F16; qkv.out_f16 = m->ws_qkv16; qkv.ldo = 3 * D_MODEL;
+        next_w(qkv, &L.wout);
         gemm(st, m->op_a16, L.wqkv.op, M, qkv, simt);
         attn(l);  // q | k | v in ws_qkv16 -> context in ws_a16 (cached streaming attention, or full-sequence attention offline)
+        next_w(part, &L.pw1);
         rin.nsplit = gemm(st, m->op_a16, L.wout.op, M, part, simt, m->part_max_splits);
         rin.alpha = 1.0f;  // x += attention
         // convolution module
         launch_layernorm(st, m->ws_x, L.ln_conv_g, L.ln_conv_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin);
         EpiParams glu;
         glu.kind = EPI_GLU; glu.out_f32 = m->ws_g; glu.ldo = D_MODEL;
+        next_w(glu, &L.pw2);
         gemm(st, m->op_a16, L.pw1.op, M, glu, simt);
         ConvArgs cv{};
         cv.g = m->ws_g; cv.conv_cache = m->conv_cache + (size_t)l * S * 2 * CONV_CACHE * D_MODEL; cv.parity = d_parity; cv.w_dw = L.w_dw;
         cv.ln_g = L.bn_g; cv.ln_b = L.bn_b; cv.slot = d_slot; cv.out = m->ws_a16; cv.B = B; cv.T = T; cv.act_quant = aq;
         launch_dwconv(st, cv);
+        next_w(part, &L.ff2_w1);
         rin.nsplit = gemm(st, m->op_a16, L.pw2.op, M, part, simt, m->part_max_splits);
         // FFN2 and the layer's output norm (fused with the next layer's first norm)
         launch_layernorm(st, m->ws_x, L.ln_ff2_g, L.ln_ff2_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin);  // x += conv module
+        next_w(up, &L.ff2_w2);
         gemm(st, m->op_a16, L.ff2_w1.op, M, up, simt);
+        next_w(part, l + 1 < m->n_layers ? &m->layers[l + 1].ff1_w1 : nullptr);
         rin.nsplit = gemm(st, m->op_h16, L.ff2_w2.op, M, part, simt, m->part_max_splits);
         rin.alpha = 0.5f;  // x += 0.5 * FFN2, then x = LN_out(x)
         if (l + 1 < m->n_layers)
@@ -1058,7 +1083,7 @@ void enqueue_encoder(const StepCtx& c) {
         at.bias_u = L.pos_u; at.bias_v = L.pos_v; at.slot = d_slot; at.wpos = d_wpos; at.valid = d_valid;
         at.out = m->ws_a16; at.B = B; at.T = T; at.act_quant = aq;
         launch_attention(st, at);
-    });
+    }, /*kv_prefetch=*/true);
     if (c.taps) {
         for (int b = 0; b < B; b++) {
             nb200_stream* s = (*c.items)[b].s;

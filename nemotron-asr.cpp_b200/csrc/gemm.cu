@@ -301,6 +301,25 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
         const int ew = warp - 2, quad = warp & 3, half = ew >> 2;  // half = which of the quadrant's 4 warps
         const int lane_base = quad * 32;
         uint8_t* stg = smem + ew * 8192;
+        if (epi.pf_ptr != nullptr && threadIdx.x == 64) {  // my slice of the next GEMM's weights -> L2 (EpiParams::pf_ptr)
+            const size_t cta = blockIdx.x + gridDim.x * (blockIdx.y + (size_t)gridDim.y * blockIdx.z);
+            size_t off = cta * epi.pf_slice;
+            const size_t end = off + epi.pf_slice < epi.pf_bytes ? off + epi.pf_slice : epi.pf_bytes;
+            for (; off < end; off += 16384) {
+                const uint32_t n = (uint32_t)(end - off < 16384 ? end - off : 16384) & ~15u;
+                if (n) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(static_cast<const char*>(epi.pf_ptr) + off), "r"(n) : "memory");
+            }
+        }
+        if (epi.pf2_base != nullptr && threadIdx.x == 96) {  // state slabs of the batch's streams -> L2 (EpiParams::pf2_base)
+            const int cta = (int)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)), nctas = (int)(gridDim.x * gridDim.y * gridDim.z);
+            for (int i = cta; i < epi.pf2_count; i += nctas) {
+                const char* slab = static_cast<const char*>(epi.pf2_base) + (size_t)epi.pf2_slot[i] * epi.pf2_stride;
+                for (unsigned off = 0; off < epi.pf2_bytes; off += 16384) {
+                    const uint32_t n = (epi.pf2_bytes - off < 16384u ? epi.pf2_bytes - off : 16384u) & ~15u;
+                    if (n) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(slab + off), "r"(n) : "memory");
+                }
+            }
+        }
         mbar_wait(accum_bar, 0);
         tc_fence_after();
         if (trace && threadIdx.x == 64) trace[4] = gtimer();
@@ -567,6 +586,10 @@ int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiPa
     }
     const bool packed = epi.kind == EPI_STORE_F16 || epi.kind == EPI_GLU;
     const GemmConfig c = gemm_pick_config(M, N, A.K, max_splits, packed ? 64 : 32);
+    static const bool no_prefetch = getenv("NB200_NO_WEIGHT_PREFETCH") != nullptr;
+    if (no_prefetch || ((uintptr_t)epi.pf_ptr & 15) != 0) epi.pf_ptr = nullptr;
+    if (no_prefetch || ((uintptr_t)epi.pf2_base & 15) != 0 || epi.pf2_stride % 16 != 0) epi.pf2_base = nullptr;
+    epi.pf_slice = epi.pf_ptr ? (unsigned)(((epi.pf_bytes + c.ctas - 1) / c.ctas + 127) / 128 * 128) : 0u;
     if (packed && c.bn < 64) throw Error("GEMM: fp16 / GLU outputs need 64-column tiles");
     CUtensorMap omap;
     if (epi.kind == EPI_PARTIAL) {

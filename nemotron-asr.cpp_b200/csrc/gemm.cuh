@@ -37,6 +37,20 @@ struct EpiParams {
     int ldo = 0;                // leading dimension of the output (elements)
     size_t split_stride = 0;    // EPI_PARTIAL: elements between the partial outputs of consecutive K splits (a multiple of ldo)
     unsigned long long* trace = nullptr;  // debug: per-CTA phase timestamps (globaltimer ns), 8 words per CTA
+    // L2 prefetch of the NEXT GEMM's weights (they do not depend on anything this step computes): every CTA asks for its slice
+    // while its own main loop runs — the tensor pipe is the limiter then and HBM is ~10 % busy — so the next kernel's operand
+    // ring fills from L2 instead of ramping up an HBM stream behind a dependency edge. pf_slice is set by gemm().
+    const void* pf_ptr = nullptr;
+    size_t pf_bytes = 0;
+    unsigned pf_slice = 0;
+    // ... and of per-stream state the kernels behind this GEMM will read from HBM (the K / V ring slabs of the batch's streams for the
+    // attention two kernels later): slab i = pf2_base + pf2_slot[i] * pf2_stride, pf2_bytes each, i < pf2_count; CTA c takes slabs
+    // c, c + #CTAs, ...
+    const void* pf2_base = nullptr;
+    size_t pf2_stride = 0;
+    unsigned pf2_bytes = 0;
+    const int* pf2_slot = nullptr;
+    int pf2_count = 0;
 };
 
 // ---- epilogue, stage 1 (registers): bias / activation / re-quantisation / GLU on 32 consecutive accumulator columns
