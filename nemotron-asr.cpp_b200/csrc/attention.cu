@@ -542,7 +542,11 @@ __global__ void __launch_bounds__(AT_THREADS, 4) attention_f16s_kernel(AttnArgs 
 // 256-byte rows, 16 lanes each, 16 B per lane) straight from global memory into registers, no shared-memory staging
 // of operands, ~24 warps resident per SM for latency hiding. Lane c of a half-warp holds features [8c, 8c+8) of q+u /
 // q+v in fp32; a row's dot product is 8 FMAs + a 4-step shuffle reduction over the half-warp. Probabilities stay fp32.
-template <int NQ>
+// UN = rows in flight per half-warp and phase (UN x 512 B per warp). Each phase is a chain of ceil(71 / 2 UN) dependent memory round
+// trips: 6 at UN = 6. With up to ~256 streams there are only a few warps per SM to hide them (7 at 128 streams), so the small-batch
+// instantiation keeps 12 rows in flight (3 round trips per phase; 48 more registers, irrelevant at that occupancy) and requests
+// the first V rows before the softmax; the large-batch one (1024 streams: 55 warps per SM, 73 % of the HBM peak) keeps 6.
+template <int NQ, int UN>
 __global__ void __launch_bounds__(128) attention_stream_kernel(AttnArgs a) {
     pdl_launch();
     constexpr int WARPS = 4, SLD = 96;
@@ -560,8 +564,14 @@ __global__ void __launch_bounds__(128) attention_stream_kernel(AttnArgs a) {
     const __half* pbase = a.pos + h * D_HEAD + c * 8;
     float (*Sw)[SLD] = S[warp];
 
-    // position scores first: the table was written at load time, so this part overlaps the QKV GEMM's tail (PDL) --
-    // but it needs q. So only the addresses are prepared here; everything that depends on qkv follows the wait.
+    // The position table was written at load time: its first batch of rows is requested before the dependency wait (it lands
+    // while the QKV GEMM finishes); everything that depends on qkv follows the wait.
+    uint4 rp[UN];
+#pragma unroll
+    for (int u = 0; u < UN; u++) {
+        const int rr = 2 * u + hw;
+        rp[u] = rr < npos ? __ldg(reinterpret_cast<const uint4*>(pbase + (size_t)rr * D_MODEL)) : make_uint4(0, 0, 0, 0);
+    }
     pdl_wait();
     const __half* qkv = a.qkv + (size_t)b * T * (3 * D_MODEL) + h * D_HEAD + c * 8;
     float qu[NQ][8], qv[NQ][8];
@@ -601,7 +611,6 @@ __global__ void __launch_bounds__(128) attention_stream_kernel(AttnArgs a) {
         s += __shfl_xor_sync(0xffffffffu, s, 1);
         return s;
     };
-    constexpr int UN = 6;  // rows in flight per half-warp: 6 x 512 B per warp
     const uint4 z4 = make_uint4(0, 0, 0, 0);
 
     // ---- key scores (Q+u).K_j; this chunk's key rows come from qkv and are appended to the ring on the way ----
@@ -635,24 +644,45 @@ __global__ void __launch_bounds__(128) attention_stream_kernel(AttnArgs a) {
     __syncwarp();
     // ---- position scores (Q+v).P_r, added at key j = LEFT + i + T - 1 - r (the reference's rel-shift) ----
     for (int r0 = 0; r0 < npos; r0 += 2 * UN) {
-        uint4 r[UN];
+        if (r0 > 0) {
 #pragma unroll
-        for (int u = 0; u < UN; u++) {
-            const int rr = r0 + 2 * u + hw;
-            r[u] = rr < npos ? *reinterpret_cast<const uint4*>(pbase + (size_t)rr * D_MODEL) : z4;
+            for (int u = 0; u < UN; u++) {
+                const int rr = r0 + 2 * u + hw;
+                rp[u] = rr < npos ? __ldg(reinterpret_cast<const uint4*>(pbase + (size_t)rr * D_MODEL)) : z4;
+            }
         }
 #pragma unroll
         for (int u = 0; u < UN; u++) {
             const int rr = r0 + 2 * u + hw;
 #pragma unroll
             for (int i = 0; i < NQ; i++) {
-                const float d = half_sum(dot8(r[u], qv[i]));
+                const float d = half_sum(dot8(rp[u], qv[i]));
                 const int j = LEFT + i + T - 1 - rr;
                 if (c == 0 && i < T && rr < npos && j >= 0 && j < kv) Sw[i][j] += d;
             }
         }
     }
     __syncwarp();
+    // the first batch of V rows is requested now: it is in flight while the softmax runs
+    auto load_v = [&](int j0, uint4 (&r)[UN]) {
+#pragma unroll
+        for (int u = 0; u < UN; u++) {
+            const int j = j0 + 2 * u + hw;
+            r[u] = z4;
+            if (j < LEFT) {
+                int pos = start + j;
+                if (pos >= RING) pos -= RING;
+                r[u] = *reinterpret_cast<const uint4*>(vring + (size_t)pos * D_MODEL);
+            } else if (j < kv) {
+                r[u] = *reinterpret_cast<const uint4*>(qkv + (size_t)(j - LEFT) * (3 * D_MODEL) + 2 * D_MODEL);
+                int pos = wpos + (j - LEFT);
+                if (pos >= RING) pos -= RING;
+                *reinterpret_cast<uint4*>(vring + (size_t)pos * D_MODEL) = r[u];
+            }
+        }
+    };
+    uint4 rv[UN];
+    load_v(0, rv);
     // ---- scale, mask, softmax (fp32) ----
     {
         const int masked = LEFT - a.valid[b];
@@ -698,26 +728,11 @@ __global__ void __launch_bounds__(128) attention_stream_kernel(AttnArgs a) {
 #pragma unroll
         for (int e = 0; e < 8; e++) acc[i][e] = 0.0f;
     for (int j0 = 0; j0 < kv; j0 += 2 * UN) {
-        uint4 r[UN];
+        if (j0 > 0) load_v(j0, rv);
 #pragma unroll
         for (int u = 0; u < UN; u++) {
             const int j = j0 + 2 * u + hw;
-            r[u] = z4;
-            if (j < LEFT) {
-                int pos = start + j;
-                if (pos >= RING) pos -= RING;
-                r[u] = *reinterpret_cast<const uint4*>(vring + (size_t)pos * D_MODEL);
-            } else if (j < kv) {
-                r[u] = *reinterpret_cast<const uint4*>(qkv + (size_t)(j - LEFT) * (3 * D_MODEL) + 2 * D_MODEL);
-                int pos = wpos + (j - LEFT);
-                if (pos >= RING) pos -= RING;
-                *reinterpret_cast<uint4*>(vring + (size_t)pos * D_MODEL) = r[u];
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < UN; u++) {
-            const int j = j0 + 2 * u + hw;
-            const __half2* rh = reinterpret_cast<const __half2*>(&r[u]);
+            const __half2* rh = reinterpret_cast<const __half2*>(&rv[u]);
 #pragma unroll
             for (int i = 0; i < NQ; i++) {
                 const float p = (j < kv) ? Sw[i][j] : 0.0f;
@@ -1206,10 +1221,14 @@ void launch_attention(cudaStream_t st, const AttnArgs& a) {
         ProfScope ps(st, "attention_stream", flops, bytes);
         const dim3 grid(cdiv(a.B * N_HEADS, 4));
         for (int rep = dup_family("attention") ? 2 : 1; rep > 0; rep--) {
-            if (a.T == 1)
-                launch_k(attention_stream_kernel<1>, grid, dim3(128), 0, st, a);
-            else
-                launch_k(attention_stream_kernel<2>, grid, dim3(128), 0, st, a);
+            const bool small = a.B <= 320;  // <= ~17 warps per SM: latency-bound, keep more rows in flight (see the kernel's comment)
+            if (a.T == 1) {
+                if (small) launch_k(attention_stream_kernel<1, 12>, grid, dim3(128), 0, st, a);
+                else launch_k(attention_stream_kernel<1, 6>, grid, dim3(128), 0, st, a);
+            } else {
+                if (small) launch_k(attention_stream_kernel<2, 12>, grid, dim3(128), 0, st, a);
+                else launch_k(attention_stream_kernel<2, 6>, grid, dim3(128), 0, st, a);
+            }
         }
         NB_KERNEL_CHECK();
         return;
