@@ -176,7 +176,7 @@ void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* 
 // split K and their partial tiles are summed in warp order through shared memory (fixed order: deterministic).
 // The CUDA-core version this replaces was bound by shared-memory bandwidth (every warp re-read the whole item tile for 3
 // weight rows): 9.7 us of dot products per round in the logits phase and ~1.5 us per 8 emitting streams and LSTM layer.
-constexpr int DK_TS = 16, DK_MAXU = 5, DK_MAXR = 8, DK_GROUP = 64;
+constexpr int DK_TS = 16, DK_MAXU = 5, DK_MAXR = 8, DK_GROUP = 64, DK_SCAN = 256;
 constexpr int DK_LDH = JOINT + 16;     // row stride (floats) of hid vectors / joint.out rows in shared memory
 constexpr int DK_LDX = 2 * DEC + 16;   // row stride of LSTM input vectors / gate rows; both = 16 mod 32: the 128-bit fragment
                                        // loads of a quarter warp (2 rows x 4 x 16 B) then cover all 32 banks once
@@ -187,8 +187,8 @@ struct DkSmem {
     float gs[DK_TS][4 * DK_MAXU];      // gate pre-activations of the tile
     int sl[DK_TS], bq[DK_TS], tok[DK_TS], rows[4 * DK_MAXU];
     float bias[DK_MAXR];               // joint.out bias of my rows
-    int act[DK_GROUP];                 // L: item indices (stream * W + window offset) of the group's pending symbol steps
-    int n_act;
+    int act[DK_SCAN];                  // L: item indices (stream * W + window offset) of the pending symbol steps of up to 256 item slots
+    unsigned cmask[8];                 // L: per-warp ballot of the scan
     float wbest[DK_GROUP], wsecond[DK_GROUP];  // A, window mode: merged (max, runner-up, index) of a stream's window items
     int widx[DK_GROUP], wemit, wf;
 };
@@ -367,6 +367,8 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
             dk_stage_wait();  // this layer's rows (requested before the previous barrier) and the input tile, my copies ...
             __syncthreads();  // ... and everyone's, and the input tile
             if (tr) { q1 = now(); acc[7] += q1 - q0; q0 = q1; }
+            float c_old = 0.0f;  // the gate threads' cell state, requested now so that it is there when the MMAs are done
+            if (t < DK_TS * nu && sm.sl[t / nu] >= 0) c_old = __ldcg(s.c + (size_t)sm.sl[t / nu] * 2 * DEC + (size_t)layer * DEC + u0 + t % nu);
             dk_tile_rows<2 * DEC>(sm, sm.xs, DK_LDX, wsm, DK_LDX, 4 * nu, [&](int q, int r, float v) { sm.gs[q][r] = v + w.bcat[layer][sm.rows[r]]; });
             __syncthreads();
             if (tr) { q1 = now(); acc[8] += q1 - q0; q0 = q1; }
@@ -380,7 +382,7 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
                     const size_t so = (size_t)slot * 2 * DEC + (size_t)layer * DEC + u0 + ui;
                     const float ig = sigmoid_f(sm.gs[q][ui]), fg = sigmoid_f(sm.gs[q][nu + ui]);
                     const float gg = tanhf(sm.gs[q][2 * nu + ui]), og = sigmoid_f(sm.gs[q][3 * nu + ui]);
-                    const float c2 = fg * __ldcg(s.c + so) + ig * gg;
+                    const float c2 = fg * c_old + ig * gg;
                     s.pend_c[so] = c2;
                     s.pend_h[so] = og * tanhf(c2);
                 }
@@ -514,30 +516,37 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
         // ---- L: logits of my rows; the hid vectors of up to 64 unfinished streams are staged at once ----
         unsigned long long tg = t0;
         if (nr > 0) {
-            for (int g0 = 0; g0 < d.B * W; g0 += DK_GROUP) {
+            // The pending items (stream, window offset) of up to 256 consecutive item slots are compacted at once — warp w scans 32 of
+            // them, one L2 round trip for the whole round — and then processed 64 at a time, so late rounds with a few unfinished
+            // streams scattered over the batch are one pass, not one per 64 slots.
+            for (int s0 = 0; s0 < d.B * W; s0 += DK_SCAN)
+            {
                 __syncthreads();
-                if (warp == 0) {  // compact the group's pending items (ballot scan)
-                    int n = 0;
-                    for (int c = 0; c < DK_GROUP; c += 32) {
-                        const int it = g0 + c + lane, b = it / W, wi = it - b * W;
-                        const bool on = it < d.B * W && __ldcg(d.fp + b) + wi < d.nvalid[b];
-                        const unsigned m = __ballot_sync(0xffffffffu, on);
-                        if (on) sm.act[n + __popc(m & ((1u << lane) - 1u))] = it;
-                        n += __popc(m);
-                    }
-                    if (lane == 0) sm.n_act = n;
+                const int it_ = s0 + 32 * warp + lane, b_ = it_ / W, wi_ = it_ - b_ * W;
+                const bool on_ = it_ < d.B * W && __ldcg(d.fp + b_) + wi_ < d.nvalid[b_];
+                const unsigned m_ = __ballot_sync(0xffffffffu, on_);
+                if (lane == 0) sm.cmask[warp] = m_;
+                __syncthreads();
+                int base_ = 0, total = 0;
+#pragma unroll
+                for (int w2 = 0; w2 < 8; w2++) {
+                    const int c2 = __popc(sm.cmask[w2]);
+                    if (w2 < warp) base_ += c2;
+                    total += c2;
                 }
-                __syncthreads();
-                const int n_act = sm.n_act;
+                if (on_) sm.act[base_ + __popc(m_ & ((1u << lane) - 1u))] = it_;
+            for (int a0 = 0; a0 < total; a0 += DK_GROUP) {
+                __syncthreads();  // the list is complete; the previous group's tiles and partial sums are consumed
+                const int n_act = min(DK_GROUP, total - a0);
+                const int* act = sm.act + a0;
                 unsigned long long u0 = tr ? now() : 0;
-                if (n_act == 0) continue;  // uniform
                 const int n_mt = (n_act + 15) >> 4;                      // 16-item MMA tiles in use
                 const int mtp = n_mt <= 1 ? 1 : (n_mt <= 2 ? 2 : 4);      // warps are split (item tile, K slice): 1x8, 2x4 or 4x2
                 const int n_pad = n_mt * 16;
                 for (int i = t; i < n_pad * (JOINT / 4); i += 256) {  // all of a thread's 16-byte pieces in flight at once (L2 only)
                     const int q = i / (JOINT / 4), k = (i - q * (JOINT / 4)) * 4;
                     float* dst = &sm.xs[(size_t)q * DK_LDH + k];
-                    if (q < n_act) cp_async16(dst, d.hid + (size_t)sm.act[q] * JOINT + k);
+                    if (q < n_act) cp_async16(dst, d.hid + (size_t)act[q] * JOINT + k);
                     else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
                 }
                 asm volatile("cp.async.commit_group;" ::: "memory");
@@ -559,10 +568,11 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                             if (x > best) { second = best; best = x; besti = v0 + i; }
                             else if (x > second) second = x;
                         }
-                        partial[(size_t)sm.act[t] * G + cta] = make_float4(best, second, __int_as_float(besti), 0.0f);
+                        partial[(size_t)act[t] * G + cta] = make_float4(best, second, __int_as_float(besti), 0.0f);
                     }
                 }
                 if (tr) { const unsigned long long u2 = now(); acc[4] += u0 - tg; acc[5] += u1 - u0; acc[6] += u2 - u1; tg = u2; }
+            }
             }
         }
         unsigned long long t1 = tr ? now() : 0;

@@ -654,7 +654,7 @@ void alloc_state(nb200_model* m) {
     // decode window (frames evaluated per stream and round, decoder.cu window mode): 2 for the streaming step. Measured at 64
     // streams x 14 frames, all-blank decoding: 258 / 211 / 197 us per chunk at 1 / 2 / 4; 2 keeps the speculative extra work small
     // when tokens are frequent. NB200_DECODE_WINDOW overrides (1 = one symbol step per round, the checker).
-    m->dec_window = 2;
+    m->dec_window = 3;  // frames of a stream evaluated per decode round (decoder.cu window mode; measured 2 / 3 / 4: 587 / 560 / 577 us per chunk)
     if (const char* e = getenv("NB200_DECODE_WINDOW")) m->dec_window = std::max(1, std::min(8, atoi(e)));
     m->ws_partial = m->alloc<float>((size_t)decode_partial_floats(B) * m->dec_window);
     m->ws_hid = m->alloc<float>((size_t)B * JOINT * m->dec_window);
