@@ -343,21 +343,24 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
     __syncthreads();
     if (t < 4 * nu) sm.rows[t] = (t / nu) * DEC + u0 + (t % nu);  // the same gate rows in both layers; rows[0..nu) = u0.. are also joint.pred's
     __syncthreads();
-    dk_stage_rows(wsm, DK_LDX, w.wcat_s[0], 2 * DEC, sm.rows, 4 * nu);
+    dk_stage_rows(wsm, DK_LDH, w.whh0_s, DEC, sm.rows, 4 * nu);
     for (int layer = 0; layer < 2; layer++) {
         for (int e0 = 0; e0 < E; e0 += DK_TS) {
             __syncthreads();
             if (t < DK_TS) dk_tile_item(s, d, sm, list, e0, E, t);
             __syncthreads();
-            // x = [embed[prev] | h0] for layer 0, [h0' | h1] for layer 1 (h0' = this round's new layer-0 output): all 20 16-byte
-            // pieces of a thread are in flight at once (cp.async; L2 only, the state was written by other CTAs of this launch)
-            for (int i = t; i < DK_TS * (2 * DEC / 4); i += 256) {
-                const int q = i / (2 * DEC / 4), k = (i - q * (2 * DEC / 4)) * 4, slot = sm.sl[q];
+            // layer 0: x = h0 (the input half W_ih0 . embed[prev] + b is the token's row of the table w.t0); layer 1: x = [h0' | h1]
+            // (h0' = this round's new layer-0 output). Every 16-byte piece of a thread is in flight at once (cp.async; L2 only, the
+            // state was written by other CTAs of this launch)
+            const int kx = layer == 0 ? DEC : 2 * DEC;
+            for (int i = t; i < DK_TS * (kx / 4); i += 256) {
+                const int q = i / (kx / 4), k = (i - q * (kx / 4)) * 4, slot = sm.sl[q];
                 float* dst = &sm.xs[q * DK_LDX + k];
                 if (slot >= 0) {
                     const float* src;
-                    if (k < DEC) src = layer == 0 ? w.embed + (size_t)sm.tok[q] * DEC + k : s.pend_h + (size_t)slot * 2 * DEC + k;
-                    else src = s.h + (size_t)slot * 2 * DEC + (size_t)layer * DEC + (k - DEC);
+                    if (layer == 0) src = s.h + (size_t)slot * 2 * DEC + k;
+                    else if (k < DEC) src = s.pend_h + (size_t)slot * 2 * DEC + k;
+                    else src = s.h + (size_t)slot * 2 * DEC + DEC + (k - DEC);
                     cp_async16(dst, src);
                 } else {
                     *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -369,7 +372,11 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
             if (tr) { q1 = now(); acc[7] += q1 - q0; q0 = q1; }
             float c_old = 0.0f;  // the gate threads' cell state, requested now so that it is there when the MMAs are done
             if (t < DK_TS * nu && sm.sl[t / nu] >= 0) c_old = __ldcg(s.c + (size_t)sm.sl[t / nu] * 2 * DEC + (size_t)layer * DEC + u0 + t % nu);
-            dk_tile_rows<2 * DEC>(sm, sm.xs, DK_LDX, wsm, DK_LDX, 4 * nu, [&](int q, int r, float v) { sm.gs[q][r] = v + w.bcat[layer][sm.rows[r]]; });
+            if (layer == 0)
+                dk_tile_rows<DEC>(sm, sm.xs, DK_LDX, wsm, DK_LDH, 4 * nu,
+                                  [&](int q, int r, float v) { sm.gs[q][r] = sm.sl[q] >= 0 ? v + __ldg(w.t0 + (size_t)sm.tok[q] * 4 * DEC + sm.rows[r]) : 0.0f; });
+            else
+                dk_tile_rows<2 * DEC>(sm, sm.xs, DK_LDX, wsm, DK_LDX, 4 * nu, [&](int q, int r, float v) { sm.gs[q][r] = v + w.bcat[1][sm.rows[r]]; });
             __syncthreads();
             if (tr) { q1 = now(); acc[8] += q1 - q0; q0 = q1; }
             if (e0 + DK_TS >= E) {  // last tile: the rows are dead, fetch the next phase's while the gates and the barrier run

@@ -367,7 +367,11 @@ void build_model(nb200_model* m, const std::string& path, int flags, const char*
         if (!m->wc_in->open(cp, src_size, src_mtime)) {
             m->wc_in.reset();
             m->wc_out.reset(new WeightCacheWriter());
-            m->wc_out->open(cp, src_size, src_mtime);
+            try {
+                m->wc_out->open(cp, src_size, src_mtime);
+            } catch (const Error&) {  // read-only directory, disk full ...: the model still loads from the GGUF, just without writing the cache
+                m->wc_out.reset();
+            }
         }
     }
     nb200_info& hp = m->info;
@@ -532,6 +536,16 @@ void build_model(nb200_model* m, const std::string& path, int flags, const char*
             for (int r = 0; r < 4 * DEC; r++) bc[r] = bih[r] + bhh[r];
             m->dec.bcat[l] = m->upload(bc);
         }
+        {   // layer 0: recurrent half for the kernel, input half folded into the per-token table t0 (kernels.cuh DecodeWeights::t0)
+            m->dec.whh0_s = m->upload_cached<float>(d + "dec_rnn.lstm.l0#hh#hilo", (size_t)4 * DEC * DEC,
+                                                    [&] { return split_f16_pairs(load_f32(g, d + "dec_rnn.lstm.weight_hh_l0", (int64_t)4 * DEC * DEC)); });
+            float* wih = m->alloc<float>((size_t)4 * DEC * DEC, false);  // dense [2560][640] copy of the left half of wcat[0]
+            CUDA_CHECK(cudaMemcpy2D(wih, DEC * sizeof(float), m->dec.wcat[0], 2 * DEC * sizeof(float), DEC * sizeof(float), 4 * DEC, cudaMemcpyDeviceToDevice));
+            float* t0 = m->alloc<float>((size_t)VOCAB * 4 * DEC);
+            launch_sgemm(m->st, m->dec.embed, wih, m->dec.bcat[0], t0, VOCAB, 4 * DEC, DEC, 4 * DEC, nullptr);
+            CUDA_CHECK(cudaStreamSynchronize(m->st));
+            m->dec.t0 = t0;
+        }
         m->dec.wpred = m->upload(load_f32(g, "joint.pred.weight", (int64_t)JOINT * DEC));
         m->dec.wpred_s = m->upload_cached<float>("joint.pred.weight#hilo", (size_t)JOINT * DEC, [&] { return split_f16_pairs(load_f32(g, "joint.pred.weight", (int64_t)JOINT * DEC)); });
         m->dec.bpred = m->upload(load_f32(g, "joint.pred.bias", JOINT));
@@ -580,7 +594,10 @@ void build_model(nb200_model* m, const std::string& path, int flags, const char*
         throw Error("prompt_kernel weights present but nemo.num_prompts is 0");
     }
     if (m->wc_out) {
-        m->wc_out->commit();
+        try {
+            m->wc_out->commit();
+        } catch (const Error&) {  // the partial file is removed by the writer; loading does not depend on it
+        }
         m->wc_out.reset();
     }
     m->wc_in.reset();  // unmap: everything is on the device now

@@ -154,6 +154,11 @@ struct DecodeWeights {
     const float* wcat_s[2];
     const float* wpred_s;
     const float* wout_s;
+    // Layer 0 of the LSTM sees x = embed[prev]: its input half W_ih0 . embed[tok] + (b_ih0 + b_hh0) only depends on the token, so
+    // it is a table [1025][2560] built at load (fp32 SGEMM); the kernel then multiplies only the recurrent half W_hh0 . h0
+    // (K = 640 instead of 1280: half the staging and half the MMAs of that phase) and adds the token's row.
+    const float* t0;           // [1025][2560]
+    const float* whh0_s;       // [2560][640] W_hh of layer 0, pre-split like wcat_s
 };
 // all greedy rounds of one batched chunk (src/nemo-stream.cpp:840-930, 1106-1118) as one persistent launch
 void launch_decode_chunk(cudaStream_t st, const DecodeWeights& w, const DecodeState& s, const DecodeBatch& b);

@@ -104,9 +104,13 @@ void WeightCacheWriter::add(const std::string& key, const void* data, uint64_t b
     if (!f_) return;
     static const uint8_t zeros[ALIGN] = {0};
     const uint64_t pad = (ALIGN - pos_ % ALIGN) % ALIGN;
-    if (pad && fwrite(zeros, 1, pad, f_) != pad) throw Error("weight cache: write failed");
+    if ((pad && fwrite(zeros, 1, pad, f_) != pad) || (bytes && fwrite(data, 1, bytes, f_) != bytes)) {
+        fclose(f_);  // disk full ...: give the cache up (commit() then does nothing), the load itself goes on
+        f_ = nullptr;
+        unlink(tmp_.c_str());
+        return;
+    }
     pos_ += pad;
-    if (bytes && fwrite(data, 1, bytes, f_) != bytes) throw Error("weight cache: write failed (disk full?)");
     entries_.push_back({key, pos_, bytes});
     pos_ += bytes;
 }
