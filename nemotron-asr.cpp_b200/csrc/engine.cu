@@ -40,12 +40,6 @@ struct LayerW {
     F16Matrix ff1_w1, ff1_w2, wqkv, wpos, wout, pw1, pw2, ff2_w1, ff2_w2;
 };
 
-struct ModeCtx {
-    Mode mode;
-    __half* pos_tab = nullptr;  // [L][npos][1024] fp16 linear_pos(PE(p)), p = -(T-1) .. 70+T-1
-    explicit ModeCtx(int rc) : mode(rc) {}
-};
-
 template <typename T>
 struct PinnedBuf {
     T* p = nullptr;
@@ -58,6 +52,23 @@ struct PinnedBuf {
     }
     ~PinnedBuf() {
         if (p) cudaFreeHost(p);
+    }
+};
+
+// Per latency mode: the precomputed positional table and the host side of a batched step of that mode (pinned metadata and
+// result buffers, events), so that the groups of a step with streams in several modes are all launched before any is waited
+// for (round 1 completed every group but the last synchronously inside nb200_step_begin).
+struct ModeCtx {
+    Mode mode;
+    __half* pos_tab = nullptr;  // [L][npos][1024] fp16 linear_pos(PE(p)), p = -(T-1) .. 70+T-1
+    PinnedBuf<int> h_meta;
+    PinnedBuf<long long> h_meta64;
+    PinnedBuf<int> h_tok;
+    cudaEvent_t ev[4]{};
+    explicit ModeCtx(int rc) : mode(rc) {}
+    ~ModeCtx() {
+        for (auto& e : ev)
+            if (e) cudaEventDestroy(e);
     }
 };
 
@@ -198,8 +209,7 @@ struct nb200_model {
     struct Inflight {
         bool active = false;
         int total = 0;
-        ModeCtx* mc = nullptr;
-        std::vector<BatchItem> items;
+        std::vector<std::pair<ModeCtx*, std::vector<BatchItem>>> groups;  // one batched chunk per latency mode, in launch order
     } inflight;
     // slots waiting for their state reset (apply_resets), the pinned / device copies of that list
     std::vector<int> reset_queue;
@@ -688,9 +698,6 @@ void alloc_state(nb200_model* m) {
         m->d_stage = m->alloc<int16_t>(cap, false);
         m->d_segs = m->alloc<UploadSeg>(MAX_UPLOAD_SEGS, false);
     }
-    m->h_meta.reserve((size_t)META_ROWS * B);
-    m->h_meta64.reserve((size_t)3 * B);
-    m->h_tok.reserve((size_t)B * (MAX_T * MAX_SYMBOLS + 2) + 8);
     for (auto& e : m->ev) CUDA_CHECK(cudaEventCreate(&e));
     for (auto& e : m->tev) CUDA_CHECK(cudaEventCreate(&e));
 }
@@ -702,6 +709,10 @@ ModeCtx* get_mode(nb200_model* m, int rc) {
     if (it != m->modes.end()) return it->second.get();
     auto ctx = std::make_unique<ModeCtx>(rc);
     const Mode& md = ctx->mode;
+    ctx->h_meta.reserve((size_t)META_ROWS * m->cap_B);
+    ctx->h_meta64.reserve((size_t)3 * m->cap_B);
+    ctx->h_tok.reserve((size_t)m->cap_B * (MAX_T * MAX_SYMBOLS + 2) + 8);
+    for (auto& e : ctx->ev) CUDA_CHECK(cudaEventCreate(&e));
     ctx->pos_tab = m->alloc<__half>((size_t)m->n_layers * md.npos * D_MODEL);
     launch_pos_emb(m->st, m->ws_posf, -(md.T - 1), md.npos);
     launch_cast_f16(m->st, m->ws_posf, m->ws_pos16, m->act_quant ? 1 : 0, md.npos, D_MODEL);
@@ -1160,8 +1171,8 @@ void run_batch_launch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
     LaunchCount lc(m);
 
     // ---- per-item metadata (the audio itself is already resident in the slots' device PCM rings) ----
-    int* meta = m->h_meta.p;
-    long long* meta64 = m->h_meta64.p;
+    int* meta = mc->h_meta.p;
+    long long* meta64 = mc->h_meta64.p;
     bool taps = false;
     for (int b = 0; b < B; b++) {
         nb200_stream* s = items[b].s;
@@ -1178,7 +1189,7 @@ void run_batch_launch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
         meta64[1 * capB + b] = (long long)HOP * md.shift * s->chunks_done - 257;
         meta64[2 * capB + b] = s->fed;
     }
-    CUDA_CHECK(cudaEventRecord(m->ev[0], st));
+    CUDA_CHECK(cudaEventRecord(mc->ev[0], st));
     CUDA_CHECK(cudaMemcpyAsync(m->ws_meta, meta, (size_t)META_ROWS * capB * sizeof(int), cudaMemcpyHostToDevice, st));
     CUDA_CHECK(cudaMemcpyAsync(m->ws_meta64, meta64, (size_t)3 * capB * sizeof(long long), cudaMemcpyHostToDevice, st));
     m->stats.h2d_bytes += (long long)META_ROWS * capB * sizeof(int) + (long long)3 * capB * sizeof(long long);
@@ -1187,29 +1198,29 @@ void run_batch_launch(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
     const bool allow_graph = m->use_graphs && !taps && !g_prof_on;
     StepCtx ctx{m, mc, B, taps, &items};
     run_graphed(m, m->enc_graphs, (long long)md.rc * 1000003 + B, allow_graph, [&] { enqueue_encoder(ctx); });
-    CUDA_CHECK(cudaEventRecord(m->ev[2], st));
+    CUDA_CHECK(cudaEventRecord(mc->ev[2], st));
 
     // The greedy rounds (src/nemo-stream.cpp:1106-1118, 840-930) ran inside the same graph as one persistent launch.
     // pinned result buffer: [0..7] = decode counters 6..13 (streams left unfinished, rounds run, barrier word, -, the kernel's
     // start / end globaltimer stamps), then token counts [capB], margins [capB], tokens [B][T*MAX_SYMBOLS]: three copies
-    int* h_unf = m->h_tok.p;
-    int* h_cnt = m->h_tok.p + 8;
+    int* h_unf = mc->h_tok.p;
+    int* h_cnt = mc->h_tok.p + 8;
     int* h_toks = h_cnt + 2 * capB;
     CUDA_CHECK(cudaMemcpyAsync(h_unf, m->ws_unfinished + 6, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaMemcpyAsync(h_cnt, m->ws_tokcnt, sizeof(int) * 2 * capB, cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaMemcpyAsync(h_toks, m->ws_tok, sizeof(int) * (size_t)B * T * MAX_SYMBOLS, cudaMemcpyDeviceToHost, st));
-    CUDA_CHECK(cudaEventRecord(m->ev[3], st));
+    CUDA_CHECK(cudaEventRecord(mc->ev[3], st));
 }
 
 // Waits for the batch launched by run_batch_launch and does the host bookkeeping (tokens, cache positions, statistics).
 void run_batch_finish(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items) {
     const Mode& md = mc->mode;
     const int B = (int)items.size(), T = md.T, capB = m->cap_B;
-    int* h_unf = m->h_tok.p;
-    int* h_cnt = m->h_tok.p + 8;
+    int* h_unf = mc->h_tok.p;
+    int* h_cnt = mc->h_tok.p + 8;
     int* h_margin = h_cnt + capB;
     int* h_toks = h_cnt + 2 * capB;
-    CUDA_CHECK(cudaEventSynchronize(m->ev[3]));
+    CUDA_CHECK(cudaEventSynchronize(mc->ev[3]));
     m->stats.d2h_bytes += (long long)sizeof(int) * ((size_t)2 * capB + (size_t)B * T * MAX_SYMBOLS + 8);
     if (h_unf[0] != 0) throw Error("decode loop did not terminate");
     if (getenv("NB200_DK_TRACE")) {
@@ -1246,8 +1257,8 @@ void run_batch_finish(nb200_model* m, ModeCtx* mc, std::vector<BatchItem>& items
         m->stats.audio_seconds += (double)items[b].n_frames * HOP / 16000.0;
     }
     float ms02 = 0, ms23 = 0;
-    CUDA_CHECK(cudaEventElapsedTime(&ms02, m->ev[0], m->ev[2]));
-    CUDA_CHECK(cudaEventElapsedTime(&ms23, m->ev[2], m->ev[3]));
+    CUDA_CHECK(cudaEventElapsedTime(&ms02, mc->ev[0], mc->ev[2]));
+    CUDA_CHECK(cudaEventElapsedTime(&ms23, mc->ev[2], mc->ev[3]));
     m->stats.steps++;
     m->stats.chunks += B;
     m->stats.frames += frames;
@@ -1534,7 +1545,21 @@ int nb200_stream_ready_chunks(const nb200_stream* s) {
 static int finish_inflight(nb200_model* m) {
     if (!m->inflight.active) return 0;
     m->inflight.active = false;  // cleared first: a failure below must not leave a half-finished step behind
-    run_batch_finish(m, m->inflight.mc, m->inflight.items);
+    std::vector<std::pair<ModeCtx*, std::vector<BatchItem>>> groups = std::move(m->inflight.groups);
+    m->inflight.groups.clear();
+    double gpu_ms = 0.0, enc_ms = 0.0, dec_ms = 0.0;
+    for (auto& g : groups) {
+        run_batch_finish(m, g.first, g.second);
+        gpu_ms += m->stats.last_step_gpu_ms;
+        enc_ms += m->stats.last_encoder_ms;
+        dec_ms += m->stats.last_decoder_ms;
+    }
+    if (groups.size() > 1) {  // the "last step" figures cover all of the step's groups
+        m->stats.last_step_gpu_ms = gpu_ms;
+        m->stats.last_encoder_ms = enc_ms;
+        m->stats.last_decoder_ms = dec_ms;
+        m->stats.steps -= (long long)groups.size() - 1;
+    }
     return m->inflight.total;
 }
 
@@ -1564,19 +1589,16 @@ int nb200_step_begin(nb200_model* m) {
         CUDA_CHECK(cudaStreamWaitEvent(m->st, m->upload_ev, 0));
         m->upload_wait = false;
     }
+    // One batched chunk per latency mode, all enqueued before any is waited for: the modes share the device workspace, which the
+    // stream orders; metadata and results have their own pinned buffers per mode (ModeCtx).
     int total = 0;
-    size_t left = groups.size();
+    m->inflight.groups.clear();
     for (auto& kv : groups) {
         ModeCtx* mc = get_mode(m, kv.first);
         total += (int)kv.second.size();
         run_batch_launch(m, mc, kv.second);
-        if (--left > 0) {  // the latency modes share one workspace: all but the last group complete here
-            run_batch_finish(m, mc, kv.second);
-        } else {
-            m->inflight.active = true;
-            m->inflight.mc = mc;
-            m->inflight.items = std::move(kv.second);
-        }
+        m->inflight.active = true;
+        m->inflight.groups.emplace_back(mc, std::move(kv.second));
     }
     m->inflight.total = total;
     return total;
