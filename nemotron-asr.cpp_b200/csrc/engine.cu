@@ -171,6 +171,7 @@ struct nb200_model {
     std::map<std::string, NamedMatrix> by_name;
     // per-slot state
     __half *k_ring = nullptr, *v_ring = nullptr;  // [L][slots][RING][1024] fp16
+    int16_t* off_pcm = nullptr;  // offline path: the utterance's PCM (persistent, sized for 512 encoder frames)
     float* conv_cache = nullptr;                  // [L][slots][2][8][1024] (two buffers, flipped every chunk)
     float* mel_overlap = nullptr;                                      // [slots][9][128]
     DecodeState dstate{};
@@ -1859,8 +1860,11 @@ int nb200_encode_audio(nb200_model* m, const int16_t* pcm, int n_samples, int32_
 
     // audio + metadata of the one "stream" (b = 0)
     const int ring = 1 << 30;  // the mel kernel indexes a ring: make it larger than any utterance
-    DevBufs bufs;
-    int16_t* d_pcm = bufs.get<int16_t>((size_t)n_samples + 8);
+    // the utterance's PCM lives in a persistent device buffer (no cudaMalloc per call; a stable pointer for the per-length graphs below)
+    const size_t pcm_cap = ((size_t)ATTN_FULL_MAX_T * 8 + 32) * HOP + 1024;
+    if ((size_t)n_samples + 8 > pcm_cap) throw Error("offline path: utterance longer than 512 encoder frames");
+    if (!m->off_pcm) m->off_pcm = m->alloc<int16_t>(pcm_cap, false);
+    int16_t* d_pcm = m->off_pcm;
     std::vector<int> meta((size_t)META_ROWS * capB, 0);
     std::vector<long long> meta64((size_t)3 * capB, 0);
     meta[0 * capB] = slot;      // slot (scratch: zeroed caches)
@@ -1876,6 +1880,20 @@ int nb200_encode_audio(nb200_model* m, const int16_t* pcm, int n_samples, int32_
     CUDA_CHECK(cudaMemcpyAsync(m->ws_meta64, meta64.data(), meta64.size() * sizeof(long long), cudaMemcpyHostToDevice, st));
     int* d_zero_slot = m->ws_meta + 7 * capB;  // spare meta row: the mel kernel's ring slot index (0: d_pcm is the whole "ring")
     CUDA_CHECK(cudaMemcpyAsync(d_zero_slot, &zero, sizeof(int), cudaMemcpyHostToDevice, st));
+    // Everything from the log-mel to the decode kernel depends on the utterance only through its frame count (the audio, its length
+    // and the scratch slot travel in device buffers): one CUDA graph per mel-frame count, captured on the second utterance of that
+    // length and replayed afterwards (~470 launches; eager launches cost ~2 ms of host time per call). A small cache: cleared when full.
+    const float* enc = nullptr;
+    if (m->dec_graphs.size() > 24) {
+        for (auto& kv : m->dec_graphs)
+            if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+        m->dec_graphs.clear();
+    }
+    const int win_off = [&] {
+        static const int win_env = getenv("NB200_OFFLINE_WINDOW") ? atoi(getenv("NB200_OFFLINE_WINDOW")) : 0;
+        return std::max(1, std::min(win_env > 0 ? win_env : 32, std::min(capB, 64)));
+    }();
+    run_graphed(m, m->dec_graphs, (long long)nf, m->use_graphs && !g_prof_on, [&] {
     {
         MelBatch mb{d_pcm, ring, d_zero_slot, m->ws_meta + 4 * capB, m->ws_meta64 + 1 * capB, m->ws_meta64 + 2 * capB, m->ws_meta64 + 0 * capB};
         launch_mel(st, m->mel_tb, mb, m->ws_mel, 1, nf);
@@ -1893,23 +1911,23 @@ int nb200_encode_audio(nb200_model* m, const int16_t* pcm, int n_samples, int32_
         eo.kind = EPI_STORE; eo.bias = m->sub_bout; eo.out_f32 = m->ws_x; eo.ldo = D_MODEL;
         gemm(st, m->op_a6h, m->sub_wout.op, T, eo, m->simt);
     }
-    const float* enc = enqueue_layers(m, 1, T, [&](int l) {
+    enc = enqueue_layers(m, 1, T, [&](int l) {
         LayerW& L = m->layers[l];
         AttnFullArgs at{};
         at.qkv = m->ws_qkv16; at.pos = m->off_pos_tab + (size_t)l * npos * D_MODEL;
         at.bias_u = L.pos_u; at.bias_v = L.pos_v; at.out = m->ws_a16; at.T = T; at.act_quant = aq;
         launch_attention_full(st, at);
     });
+    enqueue_joint_enc(m, enc, T);
+    // greedy_decode (src/nemo-ggml.cpp:1233-1380) from the fresh state; one utterance is the whole batch, so a round evaluates a
+    // window of consecutive frames (decoder.cu, window mode): blank runs cost one round per window instead of one per frame
+    launch_decode_chunk(st, m->dec, m->dstate, decode_batch(m, 1, T, win_off));
+    });
+    if (enc == nullptr) enc = m->num_prompts > 0 ? m->ws_g : m->ws_x;  // a replayed graph: enqueue_layers' (fixed) output buffer
     if (enc_out) {
         if (enc_cap_floats < (int64_t)T * D_MODEL) throw Error("encoder output buffer too small");
         CUDA_CHECK(cudaMemcpyAsync(enc_out, enc, (size_t)T * D_MODEL * sizeof(float), cudaMemcpyDeviceToHost, st));
     }
-    enqueue_joint_enc(m, enc, T);
-    // greedy_decode (src/nemo-ggml.cpp:1233-1380) from the fresh state; one utterance is the whole batch, so a round evaluates a
-    // window of consecutive frames (decoder.cu, window mode): blank runs cost one round per window instead of one per frame
-    static const int win_env = getenv("NB200_OFFLINE_WINDOW") ? atoi(getenv("NB200_OFFLINE_WINDOW")) : 0;
-    const int win = std::max(1, std::min(win_env > 0 ? win_env : 32, std::min(capB, 64)));
-    launch_decode_chunk(st, m->dec, m->dstate, decode_batch(m, 1, T, win));
     int counters[8], n_tok = 0;
     CUDA_CHECK(cudaMemcpyAsync(counters, m->ws_unfinished + 6, sizeof(counters), cudaMemcpyDeviceToHost, st));
     CUDA_CHECK(cudaMemcpyAsync(&n_tok, m->ws_tokcnt, sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -397,6 +397,24 @@ def test_offline_edge_cases(nb, model_f32):
         model_f32.encode_audio(pcm)  # 20 s = 251 frames > 8 streams * 14
 
 
+def test_offline_graph_replay_is_identical(nb, model_f32):
+    """The offline path is captured into one CUDA graph per utterance length on the second utterance of that length and replayed
+    from the third on: eager, captured and replayed runs must give bit-identical encoder output and (token, frame) pairs, also
+    when another length was run in between and when the audio of the same length differs."""
+    a, b = inputs.pcm(41, 3.0), inputs.pcm(43, 3.0)
+    other = inputs.pcm(42, 1.7)
+    first = model_f32.encode_audio(a, want_enc=True)
+    ref_b = None
+    for k in range(4):
+        got = model_f32.encode_audio(a, want_enc=True)
+        assert got[0] == first[0] and got[1] == first[1] and np.array_equal(got[2], first[2]), k
+        model_f32.encode_audio(other)
+        gb = model_f32.encode_audio(b, want_enc=True)
+        if ref_b is None:
+            ref_b = gb
+        assert gb[0] == ref_b[0] and np.array_equal(gb[2], ref_b[2]) and not np.array_equal(gb[2], first[2])
+
+
 def test_decode_window_invariance(nb, model_f32, gguf_f32):
     """The decode kernel's window mode (W frames of a stream per round) must not change a single token or frame stamp: the
     same two streams (one per latency mode, token-heavy random decoder) run in fresh processes at NB200_DECODE_WINDOW = 1
