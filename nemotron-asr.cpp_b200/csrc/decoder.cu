@@ -362,9 +362,7 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
                     else if (k < DEC) src = s.pend_h + (size_t)slot * 2 * DEC + k;
                     else src = s.h + (size_t)slot * 2 * DEC + DEC + (k - DEC);
                     cp_async16(dst, src);
-                } else {
-                    *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
-                }
+                }  // absent streams' rows are left as they are (their output rows are not read)
             }
             asm volatile("cp.async.commit_group;" ::: "memory");
             dk_stage_wait();  // this layer's rows (requested before the previous barrier) and the input tile, my copies ...
@@ -409,7 +407,6 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
             const int q = i / (DEC / 4), k = (i - q * (DEC / 4)) * 4, slot = sm.sl[q];
             float* dst = &sm.xs[q * DK_LDX + k];
             if (slot >= 0) cp_async16(dst, s.pend_h + (size_t)slot * 2 * DEC + DEC + k);
-            else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
         dk_stage_wait();
@@ -549,12 +546,11 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                 unsigned long long u0 = tr ? now() : 0;
                 const int n_mt = (n_act + 15) >> 4;                      // 16-item MMA tiles in use
                 const int mtp = n_mt <= 1 ? 1 : (n_mt <= 2 ? 2 : 4);      // warps are split (item tile, K slice): 1x8, 2x4 or 4x2
-                const int n_pad = n_mt * 16;
-                for (int i = t; i < n_pad * (JOINT / 4); i += 256) {  // all of a thread's 16-byte pieces in flight at once (L2 only)
+                for (int i = t; i < n_act * (JOINT / 4); i += 256) {  // all of a thread's 16-byte pieces in flight at once (L2 only)
                     const int q = i / (JOINT / 4), k = (i - q * (JOINT / 4)) * 4;
                     float* dst = &sm.xs[(size_t)q * DK_LDH + k];
-                    if (q < n_act) cp_async16(dst, d.hid + (size_t)act[q] * JOINT + k);
-                    else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (q < n_act) cp_async16(dst, d.hid + (size_t)act[q] * JOINT + k);  // rows >= n_act keep whatever the buffer holds: an MMA
+                                                                                         // output row depends on its own A row only, and those rows are never read back
                 }
                 asm volatile("cp.async.commit_group;" ::: "memory");
                 dk_stage_wait();
