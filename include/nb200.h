@@ -73,6 +73,9 @@ nb200_model* nb200_model_load(const char* gguf_path, int device, int max_streams
  * fp32 tensors). nb200_model_cache_stats: how many big operands came from the cache / were built from the GGUF. */
 nb200_model* nb200_model_load_cached(const char* gguf_path, const char* cache_path, int device, int max_streams, int flags);
 int nb200_model_cache_stats(const nb200_model* m, int64_t* from_cache, int64_t* from_gguf);
+/* Host-only round trip of the native weight file format (no GPU needed): write, mmap-read, reject foreign stamps and truncated files.
+ * Uses `path` (and path + ".trunc") as scratch files and removes them. NB200_OK or <0 with nb200_last_error(). */
+int nb200_weight_cache_selftest(const char* path);
 /* Host-only check of a GGUF file (no GPU needed): parses the container exactly like nb200_model_load — header, KVs, tensor
  * table with the bounds of every tensor inside the file, the vocabulary (tokenizer.vocab_list, or the legacy 8-byte-piece blob
  * tokenizer.vocab, src/nemo-ggml.cpp:149-169) — and writes a JSON summary {"tensors", "tensor_bytes", "vocab_source",

@@ -1330,6 +1330,64 @@ int nb200_gguf_check(const char* gguf_path, char* json_out, int cap) {
     NB_CATCH(NB200_ERR)
 }
 
+// Host-only round trip of the native weight file format (no GPU needed): writes a few blobs, reads them back through the mmap
+// reader, and checks that a wrong source stamp, a wrong size request and a truncated file are all rejected.
+int nb200_weight_cache_selftest(const char* path) {
+    NB_TRY
+    if (!path) throw Error("null path");
+    const std::string p = path;
+    std::vector<float> a(1000), b(77);
+    std::vector<uint8_t> c(5);
+    for (size_t i = 0; i < a.size(); i++) a[i] = (float)i * 0.5f;
+    for (size_t i = 0; i < b.size(); i++) b[i] = -(float)i;
+    for (size_t i = 0; i < c.size(); i++) c[i] = (uint8_t)(i + 1);
+    {
+        WeightCacheWriter w;
+        w.open(p, 1234, 5678);
+        w.add("first", a.data(), a.size() * sizeof(float));
+        w.add("second#tag", b.data(), b.size() * sizeof(float));
+        w.add("", c.data(), c.size());
+        w.commit();
+    }
+    {
+        WeightCacheReader r;
+        if (!r.open(p, 1234, 5678) || r.entries() != 3) throw Error("selftest: cache did not open");
+        const WeightCacheBlob* x = r.find("first", a.size() * sizeof(float));
+        const WeightCacheBlob* y = r.find("second#tag", b.size() * sizeof(float));
+        const WeightCacheBlob* z = r.find("", c.size());
+        if (!x || !y || !z || memcmp(x->data, a.data(), x->bytes) || memcmp(y->data, b.data(), y->bytes) || memcmp(z->data, c.data(), z->bytes))
+            throw Error("selftest: blobs differ");
+        if (((uintptr_t)x->data & 255) || ((uintptr_t)y->data & 255)) throw Error("selftest: blobs are not 256-byte aligned");
+        if (r.find("first", 4) || r.find("missing", 4)) throw Error("selftest: a wrong size / key was accepted");
+    }
+    {
+        WeightCacheReader r;
+        if (r.open(p, 1234, 5679) || r.open(p, 1235, 5678)) throw Error("selftest: a foreign source stamp was accepted");
+    }
+    {   // truncated at every interesting length: must be rejected, never read out of bounds
+        FILE* f = fopen(p.c_str(), "rb");
+        if (!f) throw Error("selftest: cannot reopen");
+        std::vector<uint8_t> all;
+        uint8_t buf[4096];
+        size_t n;
+        while ((n = fread(buf, 1, sizeof buf, f)) > 0) all.insert(all.end(), buf, buf + n);
+        fclose(f);
+        const std::string t = p + ".trunc";
+        for (size_t len : {(size_t)0, (size_t)7, (size_t)39, (size_t)40, all.size() / 2, all.size() - 9, all.size() - 1}) {
+            FILE* g = fopen(t.c_str(), "wb");
+            if (!g) throw Error("selftest: cannot write");
+            fwrite(all.data(), 1, len, g);
+            fclose(g);
+            WeightCacheReader r;
+            if (r.open(t, 1234, 5678)) throw Error("selftest: a truncated cache (" + std::to_string(len) + " bytes) was accepted");
+        }
+        remove(t.c_str());
+    }
+    remove(p.c_str());
+    return NB200_OK;
+    NB_CATCH(NB200_ERR)
+}
+
 static nb200_model* model_load_impl(const char* gguf_path, const char* cache_path, int device, int max_streams, int flags) {
     nb200_model* m = nullptr;
     try {

@@ -49,6 +49,7 @@ SYMBOLS = {
     "nb200_model_token": (C.c_char_p, [C.c_void_p, C.c_int32]),
     "nb200_model_load_cached": (C.c_void_p, [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int]),
     "nb200_model_cache_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "nb200_weight_cache_selftest": (C.c_int, [C.c_char_p]),
     "nb200_bench_mma_peak": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]),
     "nb200_tokens_to_text": (C.c_int, [C.c_void_p, _I32P, C.c_int, C.c_char_p, C.c_int]),
     "nb200_tokens_to_text_timed": (C.c_int, [C.c_void_p, _I32P, _I64P, C.c_int, C.c_char_p, C.c_int]),

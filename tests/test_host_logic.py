@@ -234,3 +234,13 @@ def test_bench_decoder_profile():
         n += k
     print(f"stationary decoder on synthetic encoder frames: {n / frames:.3f} tokens/frame, histogram {hist.tolist()}")
     assert 0.03 < n / frames < 1.0 and hist[4:].sum() <= 0.02 * frames and hist[10] <= 2
+
+
+def test_weight_cache_format_round_trip(lib_built, tmp_path):
+    """The native weight file (csrc/weight_cache.cpp) without a GPU: blobs written by the writer come back
+    bit-identical and 256-byte aligned through the mmap reader; a foreign source stamp, a wrong size request and files truncated
+    at the header, inside a blob, inside the index and one byte short are all rejected."""
+    import nb200
+    rc = nb200.lib().nb200_weight_cache_selftest(os.fsencode(str(tmp_path / "selftest.nb200w")))
+    assert rc == 0, nb200._err()
+    assert not (tmp_path / "selftest.nb200w").exists()
