@@ -204,6 +204,7 @@ def main():
     ap.add_argument("--layers", type=int, default=24)
     ap.add_argument("--variant", default="q8_0", choices=("q8_0", "f32dq", "f16"),
                     help="weight format of the GGUF: q8_0 (headline), f16 (the reference converter's 16-bit format; it has no BF16, scripts/convert_to_gguf.py:322-336), f32dq")
+    ap.add_argument("--bf16", action="store_true", help="bf16 instead of fp16 operands in the layers' GEMMs (NB200_FLAG_BF16; needs --variant f16 or f32dq)")
     ap.add_argument("--no-latency-path", action="store_true", help="skip the config-3 leg (80 ms chunks, 128 streams per GPU)")
     ap.add_argument("--latency-steps", type=int, default=200)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -283,7 +284,10 @@ def main():
     os.environ["NB200_PCM_RING_LOG2"] = str(max(17, int(np.ceil(np.log2(need)))))
     my_ids = shard.shard_streams(a.streams * world, world, rank)
     assert len(my_ids) == a.streams
-    model = nb200.Model(gguf, device=local, max_streams=max(a.streams, 0 if a.no_latency_path else LATENCY_STREAMS))
+    if a.bf16 and a.variant == "q8_0":
+        raise SystemExit("--bf16 is for --variant f16 / f32dq (the Q8_0 activation grid does not fit bf16)")
+    model = nb200.Model(gguf, device=local, max_streams=max(a.streams, 0 if a.no_latency_path else LATENCY_STREAMS),
+                        flags=(nb200.FLAG_ACT_QUANT_OFF | nb200.FLAG_BF16) if a.bf16 else 0)
     streams = [model.stream(a.rc) for _ in my_ids]
     pcm = build_pcm(a.streams, n_total_steps * cs, my_ids[0])
     base_ptr, row_bytes = pcm.data_ptr(), pcm.stride(0) * 2
@@ -506,7 +510,8 @@ def main():
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms_max / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f16 operands, f32 accumulate (Q8_0 weights dequantised; ggml's int8 activation re-quantisation emulated)",
+            "dtype": ("bf16 operands, f32 accumulate" if a.bf16 else
+                      "f16 operands, f32 accumulate" + (" (Q8_0 weights dequantised; ggml's int8 activation re-quantisation emulated)" if a.variant == "q8_0" else "")),
             "data": "synthetic", "config": config, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
             "latency_ms": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)), "what": "feed+step+poll of one batched chunk, in sequence (wall clock)"},
             "decode_steps_per_frame": steps_per_frame, "decode_rounds_per_step": rounds_per_step, "tokens_emitted": int(tokens),

@@ -33,6 +33,9 @@ typedef struct nb200_stream nb200_stream; /* replaces struct nemo_stream_context
 #define NB200_FLAG_ACT_QUANT_ON 2   /* always                                                                      */
 #define NB200_FLAG_GEMM_SIMT 16     /* debug: CUDA-core GEMM instead of the tcgen05 kernel (same operands/epilogues) */
 #define NB200_FLAG_NO_GRAPHS 32     /* debug: launch every kernel eagerly instead of replaying per-shape CUDA graphs */
+#define NB200_FLAG_BF16 64          /* bf16 instead of fp16 operands in the 24 layers' GEMMs (weights converted at load, activations stored as bf16
+                                     * by the producing kernels; SURVEY section 8(d) "F32 -> bf16 at load"). For F32 / F16 files: not together with
+                                     * the Q8_0 activation re-quantisation. */
 
 typedef struct nb200_info {
     int32_t n_mels, d_model, n_heads, d_head, d_ff, n_layers, kernel_size;

@@ -278,10 +278,9 @@ __global__ void __launch_bounds__(AT_THREADS, 2) attention_f16_kernel(AttnArgs a
             v.z = fake_quant(v.z, amax);
             v.w = fake_quant(v.w, amax);
         }
-        const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
         uint2 u;
-        u.x = *reinterpret_cast<const uint32_t*>(&lo);
-        u.y = *reinterpret_cast<const uint32_t*>(&hi);
+        u.x = pack_operand2(v.x, v.y, a.out_bf16);
+        u.y = pack_operand2(v.z, v.w, a.out_bf16);
         *reinterpret_cast<uint2*>(a.out + ((size_t)(b * T + i)) * D_MODEL + h * D_HEAD + d) = u;
     }
 }
@@ -527,10 +526,9 @@ __global__ void __launch_bounds__(AT_THREADS, 4) attention_f16s_kernel(AttnArgs 
             v.z = fake_quant(v.z, amax);
             v.w = fake_quant(v.w, amax);
         }
-        const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
         uint2 u;
-        u.x = *reinterpret_cast<const uint32_t*>(&lo);
-        u.y = *reinterpret_cast<const uint32_t*>(&hi);
+        u.x = pack_operand2(v.x, v.y, a.out_bf16);
+        u.y = pack_operand2(v.z, v.w, a.out_bf16);
         *reinterpret_cast<uint2*>(a.out + ((size_t)(b * T + i)) * D_MODEL + h * D_HEAD + d) = u;
     }
 }
@@ -759,9 +757,9 @@ __global__ void __launch_bounds__(128) attention_stream_kernel(AttnArgs a) {
             for (int e = 0; e < 8; e++) acc[i][e] = fake_quant(acc[i][e], amax);
         }
         if (hw == 0 && i < T) {
-            __half2 o[4];
+            uint32_t o[4];
 #pragma unroll
-            for (int e = 0; e < 4; e++) o[e] = __floats2half2_rn(acc[i][2 * e], acc[i][2 * e + 1]);
+            for (int e = 0; e < 4; e++) o[e] = pack_operand2(acc[i][2 * e], acc[i][2 * e + 1], a.out_bf16);
             *reinterpret_cast<uint4*>(a.out + ((size_t)(b * T + i)) * D_MODEL + h * D_HEAD + c * 8) = *reinterpret_cast<const uint4*>(o);
         }
     }
@@ -845,10 +843,9 @@ __global__ void __launch_bounds__(256) attention_simt_kernel(AttnArgs a) {
             acc.z = fake_quant(acc.z, amax);
             acc.w = fake_quant(acc.w, amax);
         }
-        const __half2 lo = __floats2half2_rn(acc.x, acc.y), hi = __floats2half2_rn(acc.z, acc.w);
         uint2 u;
-        u.x = *reinterpret_cast<const uint32_t*>(&lo);
-        u.y = *reinterpret_cast<const uint32_t*>(&hi);
+        u.x = pack_operand2(acc.x, acc.y, a.out_bf16);
+        u.y = pack_operand2(acc.z, acc.w, a.out_bf16);
         *reinterpret_cast<uint2*>(a.out + ((size_t)(b * T + i)) * D_MODEL + h * D_HEAD + d) = u;
     }
 }
@@ -965,10 +962,9 @@ __global__ void __launch_bounds__(256) attention_full_kernel(AttnFullArgs a) {
             v.z = fake_quant(v.z, amax);
             v.w = fake_quant(v.w, amax);
         }
-        const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
         uint2 u;
-        u.x = *reinterpret_cast<const uint32_t*>(&lo);
-        u.y = *reinterpret_cast<const uint32_t*>(&hi);
+        u.x = pack_operand2(v.x, v.y, a.out_bf16);
+        u.y = pack_operand2(v.z, v.w, a.out_bf16);
         *reinterpret_cast<uint2*>(a.out + (size_t)i * D_MODEL + h * D_HEAD + 4 * lane) = u;
     }
 }
@@ -1179,10 +1175,9 @@ __global__ void __launch_bounds__(128) attention_full_mma_kernel(AttnFullArgs a)
             v.w = fake_quant(v.w, amax);
         }
         if (i0 + i < T) {
-            const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
             uint2 u;
-            u.x = *reinterpret_cast<const uint32_t*>(&lo);
-            u.y = *reinterpret_cast<const uint32_t*>(&hi);
+            u.x = pack_operand2(v.x, v.y, a.out_bf16);
+            u.y = pack_operand2(v.z, v.w, a.out_bf16);
             *reinterpret_cast<uint2*>(a.out + (size_t)(i0 + i) * D_MODEL + h * D_HEAD + d) = u;
         }
     }

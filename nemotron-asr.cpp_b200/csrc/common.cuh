@@ -1,5 +1,6 @@
 // common.cuh — shared definitions for libnemob200 (sm_100a only).
 #pragma once
+#include <cuda_bf16.h>
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <cstdint>
@@ -173,6 +174,16 @@ __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
+}
+// Two fp32 values -> one 32-bit word of the GEMM operand type: fp16 (default) or bf16 (models loaded with NB200_FLAG_BF16: the
+// encoder GEMMs then run kind::f16 with A = B = bf16, so every kernel that produces an A operand stores bf16).
+__device__ __forceinline__ uint32_t pack_operand2(float a, float b, int bf16) {
+    if (bf16) {
+        const __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+        return *reinterpret_cast<const uint32_t*>(&v);
+    }
+    const __half2 v = __floats2half2_rn(a, b);
+    return *reinterpret_cast<const uint32_t*>(&v);
 }
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + expf(-x)); }
 __device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + expf(-x)); }

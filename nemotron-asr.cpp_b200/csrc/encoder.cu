@@ -27,7 +27,7 @@ __device__ __forceinline__ float group8_max(float v) {
     return v;
 }
 
-__device__ __forceinline__ void store_f16x4(__half* dst, float4 v, int act_quant) {
+__device__ __forceinline__ void store_f16x4(__half* dst, float4 v, int act_quant, int bf16 = 0) {
     if (act_quant) {
         float amax = group8_max(fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
         v.x = fake_quant(v.x, amax);
@@ -35,10 +35,9 @@ __device__ __forceinline__ void store_f16x4(__half* dst, float4 v, int act_quant
         v.z = fake_quant(v.z, amax);
         v.w = fake_quant(v.w, amax);
     }
-    __half2 a = __floats2half2_rn(v.x, v.y), b = __floats2half2_rn(v.z, v.w);
     uint2 u;
-    u.x = *reinterpret_cast<uint32_t*>(&a);
-    u.y = *reinterpret_cast<uint32_t*>(&b);
+    u.x = pack_operand2(v.x, v.y, bf16);
+    u.y = pack_operand2(v.z, v.w, bf16);
     *reinterpret_cast<uint2*>(dst) = u;
 }
 
@@ -65,7 +64,7 @@ template <int NS>
 __global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, const float* __restrict__ g1,
                                                         const float* __restrict__ b1, float* __restrict__ out_f32,
                                                         const float* __restrict__ g2, const float* __restrict__ b2,
-                                                        __half* __restrict__ out_f16, int act_quant, ResidualIn rin) {
+                                                        __half* __restrict__ out_f16, int act_quant, ResidualIn rin, int out_bf16) {
     pdl_prologue();
     __shared__ float red[32];
     const size_t off = (size_t)blockIdx.x * D_MODEL + threadIdx.x * 4;
@@ -85,17 +84,17 @@ __global__ void __launch_bounds__(256) layernorm_kernel(float* __restrict__ x, c
     v = ln_1024(v, g1, b1, red);
     if (out_f32) *reinterpret_cast<float4*>(out_f32 + off) = v;
     if (g2) v = ln_1024(v, g2, b2, red + 16);
-    if (out_f16) store_f16x4(out_f16 + off, v, act_quant);
+    if (out_f16) store_f16x4(out_f16 + off, v, act_quant, out_bf16);
 }
 
 template <int NS>
 static void launch_ln_ns(cudaStream_t st, float* x, const float* g1, const float* b1, float* out_f32, const float* g2, const float* b2,
-                         __half* out_f16, int act_quant, int M, const ResidualIn& rin) {
-    launch_k(layernorm_kernel<NS>, dim3(M), dim3(256), 0, st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, rin);
+                         __half* out_f16, int act_quant, int M, const ResidualIn& rin, int out_bf16) {
+    launch_k(layernorm_kernel<NS>, dim3(M), dim3(256), 0, st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, rin, out_bf16);
 }
 
 void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b1, float* out_f32, const float* g2,
-                      const float* b2, __half* out_f16, int act_quant, int M, const ResidualIn& rin) {
+                      const float* b2, __half* out_f16, int act_quant, int M, const ResidualIn& rin, int out_bf16) {
     if (M <= 0) return;
     ProfScope ps(st, "layernorm", (double)M * D_MODEL * 8,
                  (double)M * D_MODEL * (4 + (out_f32 ? 4 : 0) + (out_f16 ? 2 : 0) + (rin.partials ? 4.0 * rin.nsplit + (out_f32 != x ? 4 : 0) : 0)));
@@ -103,15 +102,15 @@ void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b
     if (ns < 0 || ns > 8) throw Error("layernorm: at most 8 split-K partials");
     for (int rep = dup_family("layernorm") ? 2 : 1; rep > 0; rep--) {
         switch (ns) {
-            case 0: launch_ln_ns<0>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
-            case 1: launch_ln_ns<1>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
-            case 2: launch_ln_ns<2>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
-            case 3: launch_ln_ns<3>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
-            case 4: launch_ln_ns<4>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
-            case 5: launch_ln_ns<5>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
-            case 6: launch_ln_ns<6>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
-            case 7: launch_ln_ns<7>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
-            default: launch_ln_ns<8>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin); break;
+            case 0: launch_ln_ns<0>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin, out_bf16); break;
+            case 1: launch_ln_ns<1>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin, out_bf16); break;
+            case 2: launch_ln_ns<2>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin, out_bf16); break;
+            case 3: launch_ln_ns<3>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin, out_bf16); break;
+            case 4: launch_ln_ns<4>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin, out_bf16); break;
+            case 5: launch_ln_ns<5>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin, out_bf16); break;
+            case 6: launch_ln_ns<6>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin, out_bf16); break;
+            case 7: launch_ln_ns<7>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin, out_bf16); break;
+            default: launch_ln_ns<8>(st, x, g1, b1, out_f32, g2, b2, out_f16, act_quant, M, rin, out_bf16); break;
         }
     }
     NB_KERNEL_CHECK();
@@ -154,7 +153,7 @@ __global__ void __launch_bounds__(256) dwconv_kernel(ConvArgs a) {
     }
     float4 v = ln_1024(acc, a.ln_g, a.ln_b, red);
     v.x = silu_f(v.x); v.y = silu_f(v.y); v.z = silu_f(v.z); v.w = silu_f(v.w);
-    store_f16x4(a.out + ((size_t)(b * T + t)) * D_MODEL + c, v, a.act_quant);
+    store_f16x4(a.out + ((size_t)(b * T + t)) * D_MODEL + c, v, a.act_quant, a.out_bf16);
 }
 
 void launch_dwconv(cudaStream_t st, const ConvArgs& a) {
@@ -215,17 +214,17 @@ void launch_split_f16x3(cudaStream_t st, const float* x, __half* out, int M, int
     NB_KERNEL_CHECK();
 }
 
-__global__ void __launch_bounds__(256) cast_f16_kernel(const float* __restrict__ x, __half* __restrict__ out, int act_quant, int cols) {
+__global__ void __launch_bounds__(256) cast_f16_kernel(const float* __restrict__ x, __half* __restrict__ out, int act_quant, int cols, int out_bf16) {
     pdl_prologue();
     const size_t row = blockIdx.x;
     for (int c = threadIdx.x * 4; c < cols; c += 1024) {
         float4 v = *reinterpret_cast<const float4*>(x + row * cols + c);
-        store_f16x4(out + row * cols + c, v, act_quant);
+        store_f16x4(out + row * cols + c, v, act_quant, out_bf16);
     }
 }
-void launch_cast_f16(cudaStream_t st, const float* x, __half* out, int act_quant, int rows, int cols) {
+void launch_cast_f16(cudaStream_t st, const float* x, __half* out, int act_quant, int rows, int cols, int out_bf16) {
     if (cols % 1024 != 0) throw Error("cast_f16: cols must be a multiple of 1024");
-    launch_k(cast_f16_kernel, dim3(rows), dim3(256), 0, st, x, out, act_quant, cols);
+    launch_k(cast_f16_kernel, dim3(rows), dim3(256), 0, st, x, out, act_quant, cols, out_bf16);
     NB_KERNEL_CHECK();
 }
 

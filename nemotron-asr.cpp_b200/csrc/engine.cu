@@ -171,6 +171,7 @@ struct nb200_model {
     std::map<std::string, NamedMatrix> by_name;
     // per-slot state
     __half *k_ring = nullptr, *v_ring = nullptr;  // [L][slots][RING][1024] fp16
+    bool bf16 = false;           // NB200_FLAG_BF16: the layers' GEMM operands are bf16
     int16_t* off_pcm = nullptr;  // offline path: the utterance's PCM (persistent, sized for 512 encoder frames)
     float* conv_cache = nullptr;                  // [L][slots][2][8][1024] (two buffers, flipped every chunk)
     float* mel_overlap = nullptr;                                      // [slots][9][128]
@@ -294,12 +295,17 @@ std::vector<float> load_f32(const GgufFile& g, const std::string& name, int64_t 
 
 // fp32 [rows][K] (from `produce`) -> the fp16 GEMM operand on the device, through the weight cache under `key`
 template <typename F>
-void make_f16(nb200_model* m, F16Matrix& dst, const std::string& key, int rows, int K, F&& produce, const std::string& name = "") {
-    dst.ptr = m->upload_cached<__half>(key, (size_t)rows * K, [&] {
+void make_f16(nb200_model* m, F16Matrix& dst, const std::string& key, int rows, int K, F&& produce, const std::string& name = "", bool as_bf16 = false) {
+    dst.ptr = m->upload_cached<__half>(key + (as_bf16 ? "#bf16" : ""), (size_t)rows * K, [&] {
         const std::vector<float> w = produce();
         if (w.size() != (size_t)rows * K) throw Error("weight layout: " + key + " has the wrong size");
         std::vector<__half> h(w.size());
-        for (size_t i = 0; i < h.size(); i++) h[i] = __float2half_rn(w[i]);
+        if (as_bf16) {  // bf16 bit patterns in the 16-bit container (NB200_FLAG_BF16)
+            uint16_t* bits = reinterpret_cast<uint16_t*>(h.data());
+            for (size_t i = 0; i < h.size(); i++) bits[i] = __bfloat16_as_ushort(__float2bfloat16_rn(w[i]));
+        } else {
+            for (size_t i = 0; i < h.size(); i++) h[i] = __float2half_rn(w[i]);
+        }
         return h;
     });
     operand_init(dst.op, dst.ptr, rows, K);
@@ -341,8 +347,8 @@ void make_split3(nb200_model* m, F16Matrix& dst, const std::string& key, int row
     });
 }
 
-void load_matrix(nb200_model* m, const GgufFile& g, F16Matrix& dst, const std::string& name, int rows, int K) {
-    make_f16(m, dst, name, rows, K, [&] { return load_f32(g, name, (int64_t)rows * K); }, name);
+void load_matrix(nb200_model* m, const GgufFile& g, F16Matrix& dst, const std::string& name, int rows, int K, bool as_bf16 = false) {
+    make_f16(m, dst, name, rows, K, [&] { return load_f32(g, name, (int64_t)rows * K); }, name, as_bf16);
 }
 
 uint32_t kv_u32(const GgufFile& g, const char* key, uint32_t dflt) {
@@ -418,6 +424,9 @@ void build_model(nb200_model* m, const std::string& path, int flags, const char*
     m->act_quant = aq == NB200_FLAG_ACT_QUANT_ON || (aq == NB200_FLAG_ACT_QUANT_AUTO && hp.weights_quantized);
     hp.act_quant = m->act_quant;
     m->simt = (flags & NB200_FLAG_GEMM_SIMT) != 0;
+    m->bf16 = (flags & NB200_FLAG_BF16) != 0;
+    if (m->bf16 && m->act_quant) throw Error("NB200_FLAG_BF16 is for F32 / F16 files (or NB200_FLAG_ACT_QUANT_OFF): the int8 activation grid does not fit bf16's 8 mantissa bits");
+    if (m->bf16 && m->simt) throw Error("NB200_FLAG_BF16 cannot be combined with the CUDA-core GEMM checker");
     m->use_graphs = !(flags & NB200_FLAG_NO_GRAPHS) && !getenv("NB200_NO_GRAPHS");
 
     // ---- mel tables (src/preprocessor.cpp:80-110, 270-307) ----
@@ -490,13 +499,13 @@ void build_model(nb200_model* m, const std::string& path, int flags, const char*
         L.bn_g = vec("conv.batch_norm.weight", D_MODEL);        L.bn_b = vec("conv.batch_norm.bias", D_MODEL);
         L.pos_u = vec("self_attn.pos_bias_u", D_MODEL);         L.pos_v = vec("self_attn.pos_bias_v", D_MODEL);
         L.w_dw = vec("conv.depthwise_conv.weight", (int64_t)KERNEL * D_MODEL);
-        load_matrix(m, g, L.ff1_w1, p + "feed_forward1.linear1.weight", D_FF, D_MODEL);
-        load_matrix(m, g, L.ff1_w2, p + "feed_forward1.linear2.weight", D_MODEL, D_FF);
-        load_matrix(m, g, L.ff2_w1, p + "feed_forward2.linear1.weight", D_FF, D_MODEL);
-        load_matrix(m, g, L.ff2_w2, p + "feed_forward2.linear2.weight", D_MODEL, D_FF);
-        load_matrix(m, g, L.wpos, p + "self_attn.linear_pos.weight", D_MODEL, D_MODEL);
-        load_matrix(m, g, L.wout, p + "self_attn.linear_out.weight", D_MODEL, D_MODEL);
-        load_matrix(m, g, L.pw2, p + "conv.pointwise_conv2.weight", D_MODEL, D_MODEL);
+        load_matrix(m, g, L.ff1_w1, p + "feed_forward1.linear1.weight", D_FF, D_MODEL, m->bf16);
+        load_matrix(m, g, L.ff1_w2, p + "feed_forward1.linear2.weight", D_MODEL, D_FF, m->bf16);
+        load_matrix(m, g, L.ff2_w1, p + "feed_forward2.linear1.weight", D_FF, D_MODEL, m->bf16);
+        load_matrix(m, g, L.ff2_w2, p + "feed_forward2.linear2.weight", D_MODEL, D_FF, m->bf16);
+        load_matrix(m, g, L.wpos, p + "self_attn.linear_pos.weight", D_MODEL, D_MODEL, m->bf16);
+        load_matrix(m, g, L.wout, p + "self_attn.linear_out.weight", D_MODEL, D_MODEL, m->bf16);
+        load_matrix(m, g, L.pw2, p + "conv.pointwise_conv2.weight", D_MODEL, D_MODEL, m->bf16);
         {   // q|k|v stacked: one N=3072 GEMM over the same (re-quantised) LN output
             const char* nm[3] = {"self_attn.linear_q.weight", "self_attn.linear_k.weight", "self_attn.linear_v.weight"};
             make_f16(m, L.wqkv, p + "self_attn.qkv", 3 * D_MODEL, D_MODEL, [&] {
@@ -506,7 +515,7 @@ void build_model(nb200_model* m, const std::string& path, int flags, const char*
                     std::copy(part.begin(), part.end(), w.begin() + (size_t)i * D_MODEL * D_MODEL);
                 }
                 return w;
-            });
+            }, "", m->bf16);
             for (int i = 0; i < 3; i++) m->by_name[p + nm[i]] = {L.wqkv.ptr + (size_t)i * D_MODEL * D_MODEL, D_MODEL, D_MODEL, false};
             m->by_name[p + "self_attn.qkv"] = {L.wqkv.ptr, 3 * D_MODEL, D_MODEL, false};  // the stacked matrix the step multiplies by (debug entry points)
         }
@@ -519,7 +528,7 @@ void build_model(nb200_model* m, const std::string& path, int flags, const char*
                               wi.begin() + (size_t)(2 * j + 1) * D_MODEL);
                 }
                 return wi;
-            });
+            }, "", m->bf16);
             m->by_name[p + "conv.pointwise_conv1.weight"] = {L.pw1.ptr, 2 * D_MODEL, D_MODEL, true};
         }
     }
@@ -716,12 +725,13 @@ ModeCtx* get_mode(nb200_model* m, int rc) {
     for (auto& e : ctx->ev) CUDA_CHECK(cudaEventCreate(&e));
     ctx->pos_tab = m->alloc<__half>((size_t)m->n_layers * md.npos * D_MODEL);
     launch_pos_emb(m->st, m->ws_posf, -(md.T - 1), md.npos);
-    launch_cast_f16(m->st, m->ws_posf, m->ws_pos16, m->act_quant ? 1 : 0, md.npos, D_MODEL);
+    launch_cast_f16(m->st, m->ws_posf, m->ws_pos16, m->act_quant ? 1 : 0, md.npos, D_MODEL, m->bf16 ? 1 : 0);
     for (int l = 0; l < m->n_layers; l++) {
         EpiParams ep;
         ep.kind = EPI_STORE_F16;
-        ep.out_f16 = ctx->pos_tab + (size_t)l * md.npos * D_MODEL;
+        ep.out_f16 = ctx->pos_tab + (size_t)l * md.npos * D_MODEL;  // fp16 also for bf16 models: the attention kernels read it
         ep.ldo = D_MODEL;
+        ep.ab_bf16 = m->bf16 ? 1 : 0;
         gemm(m->st, m->op_pos16, m->layers[l].wpos.op, md.npos, ep, m->simt);
     }
     CUDA_CHECK(cudaStreamSynchronize(m->st));
@@ -923,14 +933,15 @@ const float* enqueue_layers(nb200_model* m, int B, int T, AttnFn&& attn, bool kv
     const int* d_parity = m->ws_meta + 5 * capB;
     // 24 cache-aware conformer layers (src/nemo-stream.cpp:605-690)
     const size_t S = (size_t)m->max_streams;
-    launch_layernorm(st, m->ws_x, m->layers[0].ln_ff1_g, m->layers[0].ln_ff1_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M);
+    const int bf = m->bf16 ? 1 : 0;  // bf16 GEMM operands: every kernel that writes an A operand stores bf16
+    launch_layernorm(st, m->ws_x, m->layers[0].ln_ff1_g, m->layers[0].ln_ff1_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, ResidualIn(), bf);
     for (int l = 0; l < m->n_layers; l++) {
         LayerW& L = m->layers[l];
         EpiParams up;  // linear1 + SiLU (+ re-quantise) -> fp16 [M,4096]
-        up.kind = EPI_STORE_F16; up.act = ACT_SILU; up.act_quant = aq; up.out_f16 = m->ws_h16; up.ldo = D_FF;
+        up.kind = EPI_STORE_F16; up.act = ACT_SILU; up.act_quant = aq; up.out_f16 = m->ws_h16; up.ldo = D_FF; up.out_bf16 = bf; up.ab_bf16 = bf;
         // The four residual GEMMs (N = 1024) write split-K partials; the LayerNorm that follows adds them to x.
         EpiParams part;
-        part.kind = EPI_PARTIAL; part.out_f32 = m->ws_part; part.ldo = D_MODEL; part.split_stride = m->part_rows * D_MODEL;
+        part.kind = EPI_PARTIAL; part.out_f32 = m->ws_part; part.ldo = D_MODEL; part.split_stride = m->part_rows * D_MODEL; part.ab_bf16 = bf;
         ResidualIn rin;
         rin.partials = m->ws_part; rin.stride = part.split_stride;
         // every GEMM asks for the NEXT GEMM's weights to be brought into L2 while its own main loop runs (EpiParams::pf_ptr)
@@ -956,9 +967,9 @@ const float* enqueue_layers(nb200_model* m, int B, int T, AttnFn&& attn, bool kv
         part.pf2_base = nullptr;
         rin.alpha = 0.5f;  // x += 0.5 * FFN1
         // self-attention
-        launch_layernorm(st, m->ws_x, L.ln_att_g, L.ln_att_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin);
+        launch_layernorm(st, m->ws_x, L.ln_att_g, L.ln_att_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin, bf);
         EpiParams qkv;  // q | k | v of the chunk's frames, dense fp16; the attention kernel appends k, v to the stream rings
-        qkv.kind = EPI_STORE_F16; qkv.out_f16 = m->ws_qkv16; qkv.ldo = 3 * D_MODEL;
+        qkv.kind = EPI_STORE_F16; qkv.out_f16 = m->ws_qkv16; qkv.ldo = 3 * D_MODEL; qkv.ab_bf16 = bf;  // q | k | v stay fp16: the attention kernels' type
         next_w(qkv, &L.wout);
         gemm(st, m->op_a16, L.wqkv.op, M, qkv, simt);
         attn(l);  // q | k | v in ws_qkv16 -> context in ws_a16 (cached streaming attention, or full-sequence attention offline)
@@ -966,26 +977,26 @@ const float* enqueue_layers(nb200_model* m, int B, int T, AttnFn&& attn, bool kv
         rin.nsplit = gemm(st, m->op_a16, L.wout.op, M, part, simt, m->part_max_splits);
         rin.alpha = 1.0f;  // x += attention
         // convolution module
-        launch_layernorm(st, m->ws_x, L.ln_conv_g, L.ln_conv_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin);
+        launch_layernorm(st, m->ws_x, L.ln_conv_g, L.ln_conv_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin, bf);
         EpiParams glu;
-        glu.kind = EPI_GLU; glu.out_f32 = m->ws_g; glu.ldo = D_MODEL;
+        glu.kind = EPI_GLU; glu.out_f32 = m->ws_g; glu.ldo = D_MODEL; glu.ab_bf16 = bf;
         next_w(glu, &L.pw2);
         gemm(st, m->op_a16, L.pw1.op, M, glu, simt);
         ConvArgs cv{};
         cv.g = m->ws_g; cv.conv_cache = m->conv_cache + (size_t)l * S * 2 * CONV_CACHE * D_MODEL; cv.parity = d_parity; cv.w_dw = L.w_dw;
-        cv.ln_g = L.bn_g; cv.ln_b = L.bn_b; cv.slot = d_slot; cv.out = m->ws_a16; cv.B = B; cv.T = T; cv.act_quant = aq;
+        cv.ln_g = L.bn_g; cv.ln_b = L.bn_b; cv.slot = d_slot; cv.out = m->ws_a16; cv.B = B; cv.T = T; cv.act_quant = aq; cv.out_bf16 = bf;
         launch_dwconv(st, cv);
         next_w(part, &L.ff2_w1);
         rin.nsplit = gemm(st, m->op_a16, L.pw2.op, M, part, simt, m->part_max_splits);
         // FFN2 and the layer's output norm (fused with the next layer's first norm)
-        launch_layernorm(st, m->ws_x, L.ln_ff2_g, L.ln_ff2_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin);  // x += conv module
+        launch_layernorm(st, m->ws_x, L.ln_ff2_g, L.ln_ff2_b, nullptr, nullptr, nullptr, m->ws_a16, aq, M, rin, bf);  // x += conv module
         next_w(up, &L.ff2_w2);
         gemm(st, m->op_a16, L.ff2_w1.op, M, up, simt);
         next_w(part, l + 1 < m->n_layers ? &m->layers[l + 1].ff1_w1 : nullptr);
         rin.nsplit = gemm(st, m->op_h16, L.ff2_w2.op, M, part, simt, m->part_max_splits);
         rin.alpha = 0.5f;  // x += 0.5 * FFN2, then x = LN_out(x)
         if (l + 1 < m->n_layers)
-            launch_layernorm(st, m->ws_x, L.ln_out_g, L.ln_out_b, m->ws_x, m->layers[l + 1].ln_ff1_g, m->layers[l + 1].ln_ff1_b, m->ws_a16, aq, M, rin);
+            launch_layernorm(st, m->ws_x, L.ln_out_g, L.ln_out_b, m->ws_x, m->layers[l + 1].ln_ff1_g, m->layers[l + 1].ln_ff1_b, m->ws_a16, aq, M, rin, bf);
         else
             launch_layernorm(st, m->ws_x, L.ln_out_g, L.ln_out_b, m->ws_x, nullptr, nullptr, nullptr, 0, M, rin);
     }
@@ -1110,7 +1121,7 @@ void enqueue_encoder(const StepCtx& c) {
         at.qkv = m->ws_qkv16; at.k_ring = m->k_ring + (size_t)l * S * RING * D_MODEL; at.v_ring = m->v_ring + (size_t)l * S * RING * D_MODEL;
         at.pos = mc->pos_tab + (size_t)l * md.npos * D_MODEL;
         at.bias_u = L.pos_u; at.bias_v = L.pos_v; at.slot = d_slot; at.wpos = d_wpos; at.valid = d_valid;
-        at.out = m->ws_a16; at.B = B; at.T = T; at.act_quant = aq;
+        at.out = m->ws_a16; at.B = B; at.T = T; at.act_quant = aq; at.out_bf16 = m->bf16 ? 1 : 0;
         launch_attention(st, at);
     }, /*kv_prefetch=*/true);
     if (c.taps) {
@@ -1905,12 +1916,13 @@ int nb200_encode_audio(nb200_model* m, const int16_t* pcm, int n_samples, int32_
     const int npos = 2 * T - 1;
     if (m->off_pos_T != T) {
         launch_pos_emb(st, m->off_posf, -(T - 1), npos);
-        launch_cast_f16(st, m->off_posf, m->off_pos16, aq, npos, D_MODEL);
+        launch_cast_f16(st, m->off_posf, m->off_pos16, aq, npos, D_MODEL, m->bf16 ? 1 : 0);
         for (int l = 0; l < m->n_layers; l++) {
             EpiParams ep;
             ep.kind = EPI_STORE_F16;
             ep.out_f16 = m->off_pos_tab + (size_t)l * npos * D_MODEL;
             ep.ldo = D_MODEL;
+            ep.ab_bf16 = m->bf16 ? 1 : 0;
             gemm(st, m->op_off_pos16, m->layers[l].wpos.op, npos, ep, m->simt);
         }
         m->off_pos_T = T;
@@ -1973,7 +1985,7 @@ int nb200_encode_audio(nb200_model* m, const int16_t* pcm, int n_samples, int32_
         LayerW& L = m->layers[l];
         AttnFullArgs at{};
         at.qkv = m->ws_qkv16; at.pos = m->off_pos_tab + (size_t)l * npos * D_MODEL;
-        at.bias_u = L.pos_u; at.bias_v = L.pos_v; at.out = m->ws_a16; at.T = T; at.act_quant = aq;
+        at.bias_u = L.pos_u; at.bias_v = L.pos_v; at.out = m->ws_a16; at.T = T; at.act_quant = aq; at.out_bf16 = m->bf16 ? 1 : 0;
         launch_attention_full(st, at);
     });
     enqueue_joint_enc(m, enc, T);
@@ -2168,13 +2180,14 @@ int nb200_debug_matmul(nb200_model* m, const char* tensor_name, const float* x, 
     float* dy = bufs.get<float>((size_t)M * N);
     CUDA_CHECK(cudaMemsetAsync(dx16, 0, (size_t)Mp * K * sizeof(__half), m->st));
     CUDA_CHECK(cudaMemcpyAsync(dx, x, (size_t)M * K * sizeof(float), cudaMemcpyHostToDevice, m->st));
-    launch_cast_f16(m->st, dx, dx16, m->act_quant ? 1 : 0, M, K);
+    launch_cast_f16(m->st, dx, dx16, m->act_quant ? 1 : 0, M, K, m->bf16 ? 1 : 0);
     Operand A;
     operand_init(A, dx16, Mp, K);
     EpiParams ep;
     ep.kind = EPI_STORE;
     ep.out_f32 = dy;
     ep.ldo = N;
+    ep.ab_bf16 = m->bf16 ? 1 : 0;
     gemm(m->st, A, W, M, ep, m->simt);
     if (it->second.glu_interleaved) {  // undo the load-time row interleave so y is in the tensor's own row order
         std::vector<float> tmp((size_t)M * N);
@@ -2200,6 +2213,7 @@ int nb200_debug_gemm(nb200_model* m, const char* tensor_name, const float* x, in
     if (!m || !tensor_name || !x || !y || M <= 0) throw Error("bad argument");
     CUDA_CHECK(cudaSetDevice(m->device));
     if (finish_inflight(m) < 0) return NB200_ERR;
+    if (m->bf16) throw Error("debug_gemm reads its fp16 results back as fp16: not available for NB200_FLAG_BF16 models (use debug_matmul)");
     auto it = m->by_name.find(tensor_name);
     if (it == m->by_name.end()) throw Error(std::string("no such encoder matrix: ") + tensor_name);
     Operand W;

@@ -268,7 +268,7 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
         }
     } else if (warp == 1) {
         if (lane == 0 && rank == 0) {  // ===== MMA issuer (the leader CTA issues for the pair) =====
-            constexpr uint32_t idesc = make_idesc_f16(TC_BM * CG, BN);
+            const uint32_t idesc = make_idesc_f16(TC_BM * CG, BN) | (epi.ab_bf16 ? ((1u << 7) | (1u << 10)) : 0u);  // A = B = bf16
             for (int kb = 0; kb < num_k; kb++) {
                 const int s = kb % STAGES;
                 const uint32_t ph = (kb / STAGES) & 1;
@@ -578,6 +578,7 @@ int gemm(cudaStream_t st, const Operand& A, const Operand& W, int M, const EpiPa
     const double out_b = epi.kind == EPI_RESID ? 8.0 : (epi.kind == EPI_STORE_F16 ? 2.0 : (epi.kind == EPI_GLU ? 2.0 : 4.0));
     const double bytes = 2.0 * ((double)M * A.K + (double)N * A.K) + out_b * M * (double)N;
     if (use_simt) {
+        if (epi.ab_bf16) throw Error("GEMM: the CUDA-core checker reads fp16 operands; not available for bf16 models");
         ProfScope ps(st, "gemm_simt", flops, bytes);
         dim3 grid(N / 64, cdiv(M, 64));
         launch_k(gemm_simt_kernel, dim3(grid), dim3(128), 0, st, A.ptr, W.ptr, M, N, A.K, epi);

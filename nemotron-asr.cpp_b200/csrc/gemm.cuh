@@ -30,6 +30,8 @@ struct EpiParams {
     int kind = EPI_STORE;
     int act = ACT_NONE;
     int act_quant = 0;          // EPI_STORE_F16: emulate Q8_0 re-quantisation of the output row blocks
+    int out_bf16 = 0;           // EPI_STORE_F16: store bf16 (the output is the A operand of a bf16 GEMM)
+    int ab_bf16 = 0;            // the operands A and W hold bf16 (kind::f16 with A = B = bf16; NB200_FLAG_BF16 models)
     float alpha = 1.0f;         // EPI_RESID
     const float* bias = nullptr;  // [N] or null
     float* out_f32 = nullptr;   // EPI_STORE / EPI_RESID / EPI_GLU / EPI_QKV(q)
@@ -84,8 +86,7 @@ __device__ __forceinline__ int epilogue_transform(const EpiParams& p, int m, int
         }
 #pragma unroll
         for (int j = 0; j < 16; j++) {
-            __half2 h = __floats2half2_rn(acc[2 * j], acc[2 * j + 1]);
-            w[j] = *reinterpret_cast<uint32_t*>(&h);
+            w[j] = pack_operand2(acc[2 * j], acc[2 * j + 1], p.out_bf16);
         }
         dst = reinterpret_cast<char*>(p.out_f16 + (size_t)m * p.ldo + n0);
         return 16;

@@ -54,7 +54,7 @@ struct ResidualIn {
 // h[m][n] = relu(h[m][n] + w_lang[lang[m / T]][n]) over [M][2048]: the one-hot half of prompt_kernel.0 (src/nemo-ggml.cpp:1097-1101)
 void launch_prompt_add_relu(cudaStream_t st, float* h, const float* w_lang, const int* lang, int T, int M);
 void launch_layernorm(cudaStream_t st, float* x, const float* g1, const float* b1, float* out_f32, const float* g2,
-                      const float* b2, __half* out_f16, int act_quant, int M, const ResidualIn& rin = ResidualIn());
+                      const float* b2, __half* out_f16, int act_quant, int M, const ResidualIn& rin = ResidualIn(), int out_bf16 = 0);
 
 struct AttnArgs {
     const __half* qkv;     // [M][3072] fp16: q | k | v of this chunk's frames (row m = b*T + i), written by the QKV GEMM
@@ -68,6 +68,7 @@ struct AttnArgs {
     const int* valid;      // [B] cache_valid_len before this chunk
     __half* out;           // [M][1024] fp16 context (fq per 32 features when act_quant)
     int B, T, act_quant;
+    int out_bf16 = 0;      // store the context as bf16 (NB200_FLAG_BF16 models)
 };
 void launch_attention(cudaStream_t st, const AttnArgs& a);
 
@@ -80,6 +81,7 @@ struct AttnFullArgs {
     const float* bias_v;
     __half* out;           // [T][1024] fp16 context (fq per 32 features when act_quant)
     int T, act_quant;
+    int out_bf16 = 0;
 };
 constexpr int ATTN_FULL_MAX_T = 512;  // the reference's positional table covers 512 frames (src/nemo-ggml.cpp:233,1061)
 void launch_attention_full(cudaStream_t st, const AttnFullArgs& a);
@@ -94,13 +96,14 @@ struct ConvArgs {
     const int* slot;
     __half* out;           // [M][1024] fp16 = fq(silu(LN(dwconv)))
     int B, T, act_quant;
+    int out_bf16 = 0;
 };
 void launch_dwconv(cudaStream_t st, const ConvArgs& a);  // out = fq(silu(LN(dwconv([cache ; g])))), other cache buffer = last 8 of [cache ; g]
 
 // fp32 [rows][1024] -> fp16 with optional fake-quant per 32 (used to prepare the positional table GEMM input)
 // out[m] = (fp16(x), fp16(x - fp16(x)), fp16(x)) over [M][3 * cols]: A operand of the split-precision GEMMs (joint.enc, prompt kernel)
 void launch_split_f16x3(cudaStream_t st, const float* x, __half* out, int M, int cols = D_MODEL);
-void launch_cast_f16(cudaStream_t st, const float* x, __half* out, int act_quant, int rows, int cols);
+void launch_cast_f16(cudaStream_t st, const float* x, __half* out, int act_quant, int rows, int cols, int out_bf16 = 0);
 // sinusoid rows for relative positions p0 .. p0+n-1 (src/nemo-ggml.cpp:17-32) -> fp32 [n][1024]
 void launch_pos_emb(cudaStream_t st, float* out, int p0, int n);
 

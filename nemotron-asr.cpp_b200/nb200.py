@@ -19,6 +19,7 @@ _HERE = Path(__file__).resolve().parent
 LIB_PATH = _HERE / "libnemob200.so"
 
 FLAG_ACT_QUANT_AUTO, FLAG_ACT_QUANT_OFF, FLAG_ACT_QUANT_ON, FLAG_GEMM_SIMT = 0, 1, 2, 16
+FLAG_NO_GRAPHS, FLAG_BF16 = 32, 64
 TAP_MEL, TAP_ENC = 1, 2
 
 
