@@ -185,7 +185,7 @@ struct DkSmem {
     float wrow[DK_MAXR][DK_LDH];       // this CTA's joint.out rows (rows >= nr are zero)
     float red[8][16][24];              // per-warp partial tiles [item][row]
     float gs[DK_TS][4 * DK_MAXU];      // gate pre-activations of the tile
-    int sl[DK_TS], bq[DK_TS], tok[DK_TS], rows[4 * DK_MAXU];
+    int sl[DK_TS], bq[DK_TS], tok[DK_TS], fpq[DK_TS], nvq[DK_TS], rows[4 * DK_MAXU];
     float bias[DK_MAXR];               // joint.out bias of my rows
     int act[DK_SCAN];                  // L: item indices (stream * W + window offset) of the pending symbol steps of up to 256 item slots
     unsigned cmask[8];                 // L: per-warp ballot of the scan
@@ -309,13 +309,13 @@ __device__ __forceinline__ void dk_tile_rows(DkSmem& sm, const float* xs, int ld
 }
 
 // Item q of an LSTM tile: (batch index, slot, previous token) of emitting stream e0 + q — one 16-byte record written by the
-// argmax phase (no dependent slot / prev look-ups) — or, for a refresh of streams 0..E-1, from the batch arrays.
+// argmax phase: (batch index, slot, token | next frame << 16, frames of the chunk) (no dependent slot / prev / frame look-ups) — or, for a refresh of streams 0..E-1, from the batch arrays.
 __device__ __forceinline__ void dk_tile_item(const DecodeState& s, const DecodeBatch& d, DkSmem& sm, const int4* list, int e0, int E, int q) {
-    int b = -1, slot = -1, tok = 0;
+    int b = -1, slot = -1, tok = 0, fp = 0, nv = 0;
     if (e0 + q < E) {
         if (list) {
             const int4 r = __ldcg(list + e0 + q);
-            b = r.x; slot = r.y; tok = r.z;
+            b = r.x; slot = r.y; tok = r.z & 0xffff; fp = r.z >> 16; nv = r.w;
         } else {
             b = e0 + q;
             slot = d.slot[b];
@@ -325,6 +325,8 @@ __device__ __forceinline__ void dk_tile_item(const DecodeState& s, const DecodeB
     sm.bq[q] = b;
     sm.sl[q] = slot;
     sm.tok[q] = tok;
+    sm.fpq[q] = fp;  // the stream's frame pointer after the emission and its frame count: joint.pred stages the next hid from them
+    sm.nvq[q] = nv;
 }
 
 // Recomputes pend_h / pend_c / pend_p of the E streams listed in `list` (batch indices; nullptr = 0..E-1), 16 streams per tile.
@@ -417,9 +419,16 @@ __device__ void dk_lstm_update(const DecodeWeights& w, const DecodeState& s, con
             const float v = acc + w.bpred[u0 + r];
             s.pend_p[(size_t)sm.sl[q] * JOINT + u0 + r] = v;
             if (list) {  // the stream's next symbol step: hid = relu(joint.enc(frame fp) + new pending pred), my rows
-                const int b = sm.bq[q], fp = __ldcg(d.fp + b), nv = d.nvalid[b];
-                for (int wi = 0; wi < d.W && fp + wi < nv; wi++)
-                    d.hid[(size_t)(b * d.W + wi) * JOINT + u0 + r] = fmaxf(d.e[((size_t)(b * d.T + fp + wi)) * JOINT + u0 + r] + v, 0.0f);
+                const int b = sm.bq[q], fp = sm.fpq[q], n_w = min(d.W, sm.nvq[q] - fp);
+                for (int w0 = 0; w0 < n_w; w0 += 4) {  // loads before stores (the pointers may alias as far as the compiler knows)
+                    float ev[4];
+#pragma unroll
+                    for (int j = 0; j < 4; j++)
+                        if (w0 + j < n_w) ev[j] = d.e[((size_t)(b * d.T + fp + w0 + j)) * JOINT + u0 + r];
+#pragma unroll
+                    for (int j = 0; j < 4; j++)
+                        if (w0 + j < n_w) d.hid[(size_t)(b * d.W + w0 + j) * JOINT + u0 + r] = fmaxf(ev[j] + v, 0.0f);
+                }
             }
         });
         if (tr) { q1 = now(); acc[12] += q1 - q0; q0 = q1; }
@@ -589,6 +598,9 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                 const int fp = __ldcg(d.fp + b);
                 if (fp >= nvalid) continue;  // uniform
                 const int nw = min(W, nvalid - fp);
+                int sy0 = 0, tc0 = 0;  // the state machine's counters, requested beside the partial maxima (one round trip, not three)
+                float mg0 = 0.0f;
+                if (t == 0) { sy0 = d.sym[b]; mg0 = d.min_margin[b]; tc0 = d.tok_cnt[b]; }
                 for (int wi = warp; wi < nw; wi += 8) {
                     float best = -INFINITY, second = -INFINITY;
                     int besti = 0x7fffffff;
@@ -610,8 +622,8 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                 }
                 __syncthreads();
                 if (t == 0) {
-                    int f = fp, sy = d.sym[b], emit = 0;
-                    float mg = d.min_margin[b];
+                    int f = fp, sy = sy0, emit = 0;
+                    float mg = mg0;
                     for (int wi = 0; wi < nw; wi++) {
                         mg = fminf(mg, sm.wbest[wi] - sm.wsecond[wi]);
                         const int besti = sm.widx[wi];
@@ -619,14 +631,14 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                             f++;
                             sy = 0;
                         } else {
-                            const int n = d.tok_cnt[b];
+                            const int n = tc0;
                             d.tok_out[(size_t)b * d.T * MAX_SYMBOLS + n] = besti | (f << 16);
                             d.tok_cnt[b] = n + 1;
                             s.prev[slot] = besti;
                             emit = 1;
-                            d.emit_list[atomicAdd(emit_count + cs, 1)] = make_int4(b, slot, besti, 0);
                             sy++;
                             if (sy >= MAX_SYMBOLS) { f++; sy = 0; }
+                            d.emit_list[atomicAdd(emit_count + cs, 1)] = make_int4(b, slot, besti | (f << 16), nvalid);
                             break;  // the later items of the window were formed with the old prediction: discarded
                         }
                     }
@@ -680,9 +692,9 @@ __global__ void __launch_bounds__(256) decode_persistent_kernel(DecodeWeights w,
                     d.tok_cnt[b] = n + 1;
                     s.prev[slot] = besti;
                     emit = 1;
-                    d.emit_list[atomicAdd(emit_count + cs, 1)] = make_int4(b, slot, besti, 0);  // order is irrelevant: the streams are independent
                     sy++;
                     if (sy >= MAX_SYMBOLS) { f++; sy = 0; }
+                    d.emit_list[atomicAdd(emit_count + cs, 1)] = make_int4(b, slot, besti | (f << 16), nvalid);  // order is irrelevant: the streams are independent
                 }
                 d.fp[b] = f;
                 d.sym[b] = sy;
