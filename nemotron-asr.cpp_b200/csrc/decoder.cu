@@ -148,9 +148,11 @@ void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* 
 
 // ---- the greedy loop: one persistent launch per batched chunk -------------------------------------------------------
 // G CTAs (one per SM) stay resident for all symbol rounds of the chunk and meet at grid-wide barriers. A round:
-//   L  logits: CTA j owns vocabulary rows [j*R, j*R+R) of joint.out (kept in shared memory for the whole launch). For
-//      every tile of 8 streams it stages hid = relu(joint.enc(frame fp) + pending pred) (src/nemo-ggml.cpp:1215-1217),
-//      one warp per row forms the 8 dot products, and the slice's (first max, runner-up, index) goes to partial[b][j].
+//   L  logits: CTA j owns vocabulary rows [j*R, j*R+R) of joint.out (kept in shared memory for the whole launch, pre-split).
+//      The pending items (stream, window offset) are compacted once per round; for every group of up to 64 of them it stages
+//      hid = relu(joint.enc(frame fp) + pending pred) (src/nemo-ggml.cpp:1215-1217) with cp.async, the 8 warps form the
+//      [items x my rows] products as MMA tiles of 16 items (K split over the warps), and the slice's (first max, runner-up,
+//      index) goes to partial[item][j].
 //   -- barrier --
 //   A  argmax: one warp per stream merges the G partials (ties -> lowest index = the reference's strict '>' scan,
 //      src/nemo-stream.cpp:899-906) and runs its state machine (:907-926): blank -> next frame, state untouched;
@@ -159,8 +161,9 @@ void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* 
 //   E  only if some stream emitted (a blank leaves (prev, h, c) untouched, so the pending state stays valid): the
 //      pending LSTM / joint.pred state of the streams in emit_list is recomputed: layer 0, layer 1, joint.pred, each
 //      followed by a barrier (every hidden unit of the previous one is needed); CTA j owns 4-5 hidden units (= the i,f,
-//      g,o gate rows of those units, src/nemo-ggml.cpp:601-618) and loops over the emitting streams in tiles of 8.
-// Window mode (DecodeBatch::W > 1, used by the offline path where one utterance is the whole batch): a blank leaves the
+//      g,o gate rows of those units, src/nemo-ggml.cpp:601-618) and loops over the emitting streams in tiles of 16. Layer 0
+//      multiplies only its recurrent half: W_ih0 . embed[prev] + b is a per-token table built at load (DecodeWeights::t0).
+// Window mode (DecodeBatch::W > 1: 3 in the streaming step, 32 in the offline path where one utterance is the whole batch): a blank leaves the
 // decoder state untouched, so the logits of the next W frames can all be formed with the same pending prediction; a round
 // evaluates W consecutive frames of the stream as W items, the argmax phase walks them in order up to the first non-blank
 // one (everything before it is a blank step, everything after it is discarded), and a round advances up to W frames instead
@@ -171,8 +174,8 @@ void launch_sgemm(cudaStream_t st, const float* A, const float* W, const float* 
 // accumulation): every fp32 operand is hi + lo / 2048 with hi = fp16(x), lo = fp16((x - hi) * 2048), and hi*hi + (hi*lo + lo*hi) /
 // 2048 is accumulated in fp32 (weights pre-split at load, activations split in the loop); the dropped lo*lo term and the
 // rounding of the lo parts are ~2^-22 relative per product, the same class as the fp32 summation-order noise of a CUDA-core
-// dot product. (3xTF32 on m16n8k8 gave the same results at twice the MMA count: the legacy tensor path is the limiter.) (the reference keeps these weights and this math in F32,
-// src/nemo-ggml.cpp:580-619,1186-1224). M = 16 items (streams / symbol steps), N = 8 weight rows per tile; a CTA's 8 warps
+// dot product (3xTF32 on m16n8k8 gave the same results at twice the MMA count: the legacy tensor path is the limiter). The
+// reference keeps these weights and this math in F32 (src/nemo-ggml.cpp:580-619,1186-1224). M = 16 items (streams / symbol steps), N = 8 weight rows per tile; a CTA's 8 warps
 // split K and their partial tiles are summed in warp order through shared memory (fixed order: deterministic).
 // The CUDA-core version this replaces was bound by shared-memory bandwidth (every warp re-read the whole item tile for 3
 // weight rows): 9.7 us of dot products per round in the logits phase and ~1.5 us per 8 emitting streams and LSTM layer.
