@@ -113,7 +113,13 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
 // (BN/2 rows), so the L2 -> SM operand traffic per output element drops by a third to a half — the main loop of the
 // single-CTA kernel is bound by exactly that traffic (measured ~70 B/clk/SM, ~8.3 KB/clk chip-wide).
 // ------------------------------------------------------------------------------------------------
-constexpr int TC_BM = 128, TC_BK = 64, TC_EPI_WARPS = 16, TC_THREADS = 64 + 32 * TC_EPI_WARPS;  // warp 0 TMA, warp 1 MMA, warps 2-17 epilogue
+constexpr int TC_BM = 128, TC_BK = 64, TC_EPI_WARPS_MAX = 16;
+// Epilogue warps per epilogue class: the SiLU + re-quantise transform is bound by instruction issue (16 instructions per element)
+// and wants all 16 warps; the store-only classes (split-K partial, plain fp16, generic) and GLU finish sooner with 8 — fewer
+// warps to start, to synchronise and to drain; tiles of at most 64 columns (the 80 ms path's M = 128 GEMMs) take 4, one per TMEM lane
+// quadrant, whatever the class (measured: step 3.54 -> 3.50 ms, 80 ms path 2.24 -> 2.16 ms).
+__host__ __device__ constexpr int tc_epi_warps(int ec, int bn) { return (ec == 1 /*EC_SILU_F16*/ && bn >= 128) ? 16 : (bn <= 64 ? 4 : 8); }  // narrow tiles: little to transform
+__host__ __device__ constexpr int tc_threads(int ec, int bn) { return 64 + 32 * tc_epi_warps(ec, bn); }  // warp 0 TMA, warp 1 MMA, the rest epilogue
 
 template <int BN, int STAGES, int CG>
 struct TcSmem {
@@ -122,7 +128,7 @@ struct TcSmem {
     static constexpr int B_BYTES = B_ROWS * TC_BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
-    static_assert(STAGES * STAGE_BYTES >= TC_EPI_WARPS * 8192, "the epilogue staging tiles reuse the operand ring");
+    static_assert(STAGES * STAGE_BYTES >= TC_EPI_WARPS_MAX * 8192, "the epilogue staging tiles reuse the operand ring");
     static_assert(B_BYTES % 1024 == 0, "stage sub-buffers must keep the 1024-byte swizzle alignment");
 };
 
@@ -179,7 +185,7 @@ __device__ __forceinline__ void tmem_dealloc_cg(uint32_t taddr, uint32_t ncols) 
 }
 
 template <int BN, int STAGES, int CG, int EC>
-__global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
+__global__ void __launch_bounds__(tc_threads(EC, BN)) gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a,
                                                             const __grid_constant__ CUtensorMap map_w,
                                                             const __grid_constant__ CUtensorMap map_out, int M, int kb_total,
                                                             EpiParams epi_in) {
@@ -292,7 +298,7 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
             else umma_commit(accum_bar);
         }
     } else {
-        // ===== epilogue warps 2..17: warp w reads TMEM lanes 32*(w%4) .. +31 (the hardware's lane-quadrant rule); the four
+        // ===== epilogue warps 2 .. 1 + tc_epi_warps(EC, BN): warp w reads TMEM lanes 32*(w%4) .. +31 (the hardware's lane-quadrant rule); the four
         // warps of a quadrant alternate over the tile's column groups. Per group: tcgen05.ld (thread = row, 32 columns) ->
         // bias / activation / re-quantisation in registers -> a 32-row x 128-byte staging tile in shared memory (128B-swizzled,
         // so the 16-byte row pieces of 8 lanes land in 8 different bank groups) -> one TMA tensor store. Rows >= M are
@@ -330,7 +336,7 @@ __global__ void __launch_bounds__(TC_THREADS) gemm_tc_kernel(const __grid_consta
         const int sw = lane & 7;
         int buf = 0;
 #pragma unroll 1
-        for (int c = half * acc_cols; c < BN; c += (TC_EPI_WARPS / 4) * acc_cols, buf ^= 1) {
+        for (int c = half * acc_cols; c < BN; c += (tc_epi_warps(EC, BN) / 4) * acc_cols, buf ^= 1) {
             if (lane == 0) bulk_wait_read<1>();  // the store that last read this staging tile has drained it
             __syncwarp();
             uint8_t* row_ptr = stg + buf * 4096 + lane * 128;
@@ -498,7 +504,7 @@ static void launch_tc_ec(cudaStream_t st, const Operand& A, const Operand& W, co
     static PerDeviceOnce once;
     if (once.first()) CUDA_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<BN, STAGES, CG, EC>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
     dim3 grid(CG * (W.rows / BN), cdiv(M, TC_BM * CG), splits);
-    launch_kc(gemm_tc_kernel<BN, STAGES, CG, EC>, grid, dim3(TC_THREADS), (size_t)S::TOTAL, st, CG, A.box(128), W.box(S::B_ROWS), omap, M,
+    launch_kc(gemm_tc_kernel<BN, STAGES, CG, EC>, grid, dim3(tc_threads(EC, BN)), (size_t)S::TOTAL, st, CG, A.box(128), W.box(S::B_ROWS), omap, M,
               A.K / TC_BK, epi);
     NB_KERNEL_CHECK();
 }

@@ -3,7 +3,7 @@
 // Two kernels share one set of fused epilogues:
 //   gemm_tc_kernel   tcgen05.mma (kind::f16, M=128 x N=BN x K=16 per instruction) with the accumulator in TMEM,
 //                    operands staged by TMA (cp.async.bulk.tensor, 128-byte swizzle) through an mbarrier ring;
-//                    warp 0 = TMA producer, warp 1 = MMA issuer + TMEM allocator, warps 2-5 = epilogue (tcgen05.ld).
+//                    warp 0 = TMA producer, warp 1 = MMA issuer + TMEM allocator, then 4 / 8 / 16 epilogue warps (tcgen05.ld) by tile width and epilogue class.
 //   gemm_simt_kernel CUDA-core checker/debug path (NB200_FLAG_GEMM_SIMT), identical operands and epilogues.
 //
 // Epilogues (what the reference does as separate ggml nodes, src/nemo-stream.cpp:593-690):
