@@ -21,9 +21,9 @@ def main():
         for name, N, K, kind in SHAPES:
             auto = m.bench_gemm(M, N, K, kind, 0, 1)
             row = {"M": M, "shape": name, "N": N, "K": K, "auto": auto, "sweep": []}
-            for bn in (1256, 1192, 1128, 256, 128, 64):
+            for bn in (1256, 1192, 1128, 256, 128, 64, 32):
                 for sp in ((1, 2, 3, 4, 5, 6, 8) if kind == 5 else (1,)):
-                    if N % (bn % 1000):
+                    if N % (bn % 1000) or (bn == 32 and kind in (1, 4, 6)) or (bn >= 1000 and M <= 128):
                         continue
                     r = m.bench_gemm(M, N, K, kind, bn, sp)
                     row["sweep"].append({"bn": bn, "splits": sp, "us": round(r["us"], 2), "tflops": round(r["tflops"], 1)})
