@@ -237,6 +237,18 @@ int nb200_trace_gemm(nb200_model* m, int M, int N, int K, int epi_kind, int bn, 
 int nb200_bench_mma_peak(nb200_model* m, int kind, int ctas, int iters, const uint8_t* a_bytes, const uint8_t* b_bytes,
                          uint32_t* check_out, double* tops_out);
 
+/* nb200_mel_batch without any allocation. No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it). Same
+ * arguments and results as nb200_mel_batch (host pcm [n_streams][n_samples] in, host mel [n_streams][n_frames][128] out, returns
+ * n_frames), same kernel; the device scratch (PCM rings, metadata, the mel output before its copy to the host) is a fixed
+ * file-scope device array of 5.2 MiB that every GPU holds while the library is loaded. Limits: n_streams <=
+ * NB200_NOALLOC_MAX_STREAMS and n_samples <= NB200_NOALLOC_MAX_SAMPLES, anything larger is rejected with an error (use
+ * nb200_mel_batch). Calls no cudaMalloc / cudaFree and no allocating library routine. All calls share the scratch: calls on one
+ * model are ordered by its stream; calls that overlap on the GPU (two models on one device, two threads) race. */
+#define NB200_NOALLOC_MAX_STREAMS 16
+#define NB200_NOALLOC_MAX_SAMPLES 65536
+int nb200_mel_batch_noalloc(nb200_model* m, const int16_t* pcm, int n_streams, int n_samples, float* mel_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -2312,4 +2312,84 @@ int nb200_bench_mma_peak(nb200_model* m, int kind, int ctas, int iters, const ui
     NB_CATCH(NB200_ERR)
 }
 
+// ---- allocation-free variant of nb200_mel_batch (no counterpart in the reference) ----
+// For callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it):
+// the device-side scratch nb200_mel_batch allocates per call (PCM rings, per-stream metadata, the log-mel output before it is
+// copied to the host) lives in ONE file-scope device array of fixed size instead. Every GPU that loads the library holds the
+// array until exit. Limits: NB200_NOALLOC_MAX_STREAMS signals of at most NB200_NOALLOC_MAX_SAMPLES samples each.
+// All calls share the array and it keeps the last call's contents. Nothing has to start at zero: every word the kernel reads is
+// written by the same call first (samples beyond n_samples are masked by the n_avail bound, all n_streams * n_frames * 128 outputs
+// are written before they are copied out). Calls that overlap on the GPU (two models on one device stepping from two threads)
+// race on it; calls on one model are ordered by the model's stream.
+}  // extern "C" (the array below has file scope)
+
+constexpr int NA_MAX_STREAMS = NB200_NOALLOC_MAX_STREAMS, NA_MAX_SAMPLES = NB200_NOALLOC_MAX_SAMPLES;  // 16 x 65536 (4.096 s at 16 kHz)
+constexpr int NA_MAX_FRAMES = (256 + NA_MAX_SAMPLES - 512) / 160 + 1;                                   // 409
+constexpr size_t NA_PCM_BYTES = (size_t)NA_MAX_STREAMS * NA_MAX_SAMPLES * sizeof(int16_t);              // 2 MiB: one 65536-sample "ring" per signal
+constexpr size_t NA_MEL_BYTES = (size_t)NA_MAX_STREAMS * NA_MAX_FRAMES * nb::N_MELS * sizeof(float);    // 3.2 MiB
+constexpr size_t NA_META_BYTES = 1024;                                                                  // 2 x 16 ints + 3 x 16 long longs
+constexpr size_t NA_TOTAL_BYTES = NA_PCM_BYTES + NA_MEL_BYTES + NA_META_BYTES;                          // 5.2 MiB per GPU
+static_assert(NA_PCM_BYTES % 256 == 0 && NA_MEL_BYTES % 256 == 0, "sub-buffers keep the 256-byte alignment");
+static_assert((NA_MAX_SAMPLES & (NA_MAX_SAMPLES - 1)) == 0, "the mel kernel indexes the PCM buffer as a power-of-two ring");
+static_assert(2 * NA_MAX_STREAMS * sizeof(int) + 3 * NA_MAX_STREAMS * sizeof(long long) <= NA_META_BYTES, "metadata region");
+
+static __device__ __align__(256) unsigned char nb200_noalloc_scratch[NA_TOTAL_BYTES];
+
+// In host code the array's name is only a stand-in for the symbol: its device address comes from cudaGetSymbolAddress, once per
+// device, with that device current.
+static unsigned char* noalloc_scratch_ptr() {
+    static unsigned char* ptr[64] = {};
+    static nb::PerDeviceOnce once;
+    int dev = 0;
+    CUDA_CHECK(cudaGetDevice(&dev));
+    dev &= 63;
+    if (once.first() || ptr[dev] == nullptr) {
+        void* p = nullptr;
+        CUDA_CHECK(cudaGetSymbolAddress(&p, nb200_noalloc_scratch));
+        if (p == nullptr) throw nb::Error("cudaGetSymbolAddress returned a null address for the no-alloc scratch");
+        ptr[dev] = static_cast<unsigned char*>(p);
+    }
+    return ptr[dev];
+}
+
+extern "C" {
+
+int nb200_mel_batch_noalloc(nb200_model* m, const int16_t* pcm, int n_streams, int n_samples, float* mel_out) {
+    NB_TRY
+    if (!m || !pcm || !mel_out) throw Error("null argument");
+    if (n_streams > NA_MAX_STREAMS || n_samples > NA_MAX_SAMPLES)
+        throw Error("nb200_mel_batch_noalloc: at most " + std::to_string(NA_MAX_STREAMS) + " signals of at most " + std::to_string(NA_MAX_SAMPLES) +
+                    " samples fit its fixed device scratch (got " + std::to_string(n_streams) + " x " + std::to_string(n_samples) +
+                    "); use nb200_mel_batch for larger batches");
+    CUDA_CHECK(cudaSetDevice(m->device));
+    const int nf = (int)frames_available(n_samples);
+    if (nf <= 0 || n_streams <= 0) return 0;
+    unsigned char* base = noalloc_scratch_ptr();
+    int16_t* d_pcm = reinterpret_cast<int16_t*>(base);
+    float* d_mel = reinterpret_cast<float*>(base + NA_PCM_BYTES);
+    int* d_i = reinterpret_cast<int*>(base + NA_PCM_BYTES + NA_MEL_BYTES);
+    long long* d_l = reinterpret_cast<long long*>(base + NA_PCM_BYTES + NA_MEL_BYTES + 2 * NA_MAX_STREAMS * sizeof(int));
+    int h_i[2 * NA_MAX_STREAMS];          // slot | n_frames (host metadata on the stack: no host allocation either)
+    long long h_l[3 * NA_MAX_STREAMS];    // out_off | a0 | n_avail
+    for (int b = 0; b < n_streams; b++) {
+        h_i[b] = b;
+        h_i[NA_MAX_STREAMS + b] = nf;
+        h_l[0 * NA_MAX_STREAMS + b] = (long long)b * nf * N_MELS;
+        h_l[1 * NA_MAX_STREAMS + b] = -257;  // 256 zeros of centre padding + the pre-emphasis sample
+        h_l[2 * NA_MAX_STREAMS + b] = n_samples;
+    }
+    LaunchCount lc(m);
+    cudaStream_t st = m->st;
+    CUDA_CHECK(cudaMemcpy2DAsync(d_pcm, (size_t)NA_MAX_SAMPLES * sizeof(int16_t), pcm, (size_t)n_samples * sizeof(int16_t),
+                                 (size_t)n_samples * sizeof(int16_t), n_streams, cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(d_i, h_i, sizeof h_i, cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(d_l, h_l, sizeof h_l, cudaMemcpyHostToDevice, st));
+    MelBatch mb{d_pcm, NA_MAX_SAMPLES, d_i, d_i + NA_MAX_STREAMS, d_l + NA_MAX_STREAMS, d_l + 2 * NA_MAX_STREAMS, d_l};
+    launch_mel(st, m->mel_tb, mb, d_mel, n_streams, nf);
+    CUDA_CHECK(cudaMemcpyAsync(mel_out, d_mel, (size_t)n_streams * nf * N_MELS * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));  // h_i / h_l / the caller's buffers are in use until here
+    return nf;
+    NB_CATCH(NB200_ERR)
+}
+
 }  // extern "C"

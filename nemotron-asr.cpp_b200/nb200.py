@@ -48,6 +48,7 @@ SYMBOLS = {
     "nb200_model_free": (None, [C.c_void_p]),
     "nb200_model_info": (C.c_int, [C.c_void_p, C.POINTER(Info)]),
     "nb200_model_token": (C.c_char_p, [C.c_void_p, C.c_int32]),
+    "nb200_mel_batch_noalloc": (C.c_int, [C.c_void_p, _I16P, C.c_int, C.c_int, _F32P]),
     "nb200_model_load_cached": (C.c_void_p, [C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int]),
     "nb200_model_cache_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "nb200_weight_cache_selftest": (C.c_int, [C.c_char_p]),
