@@ -231,7 +231,9 @@ int nb200_trace_gemm(nb200_model* m, int M, int N, int K, int epi_kind, int bn, 
 /* Tensor-pipe peak of one tcgen05.mma kind on this device (measurement only: the int8 question of SURVEY section 8d; ggml's Q8_0
  * arithmetic is ggml/src/ggml-cpu/quants.c:451-478). Every CTA keeps a 128 x 256 operand pair resident in shared memory and
  * issues iters k-blocks of 128 bytes of K (4 MMAs) into one TMEM accumulator. kind 0 = kind::f16 (fp16 x fp16 -> fp32), 1 =
- * kind::i8 (s8 x s8 -> s32). *tops_out = 1e-12 * 2 * 128 * 256 * K_total * ctas / device time (TFLOP/s or TOP/s).
+ * kind::i8 (s8 x s8 -> s32), 2 = kind::i8 with ggml's Q8_0 block scales: ONE K = 32 MMA per iteration into one of two TMEM
+ * accumulators, read out by 16 epilogue warps and added as d_x[m][blk] * d_w[n][blk] * acc into fp32 running sums (synthetic scale
+ * tables; check_out then holds fp32 sums over 8 blocks). *tops_out = 1e-12 * 2 * 128 * 256 * K_total * ctas / device time (TFLOP/s or TOP/s).
  * a_bytes [128][128] / b_bytes [256][128] (host, K-major rows of 128 bytes) are the operands; check_out (host, [128][256] 32-bit
  * words, may be NULL) receives CTA 0's accumulator of a SEPARATE one-k-block launch, for an arithmetic check. */
 int nb200_bench_mma_peak(nb200_model* m, int kind, int ctas, int iters, const uint8_t* a_bytes, const uint8_t* b_bytes,

@@ -2289,7 +2289,7 @@ int nb200_debug_gemm(nb200_model* m, const char* tensor_name, const float* x, in
 int nb200_bench_mma_peak(nb200_model* m, int kind, int ctas, int iters, const uint8_t* a_bytes, const uint8_t* b_bytes, uint32_t* check_out,
                          double* tops_out) {
     NB_TRY
-    if (!m || !a_bytes || !b_bytes || !tops_out || (kind != 0 && kind != 1) || ctas <= 0 || iters <= 0) throw Error("bad argument");
+    if (!m || !a_bytes || !b_bytes || !tops_out || (kind < 0 || kind > 2) || ctas <= 0 || iters <= 0) throw Error("bad argument");
     CUDA_CHECK(cudaSetDevice(m->device));
     if (finish_inflight(m) < 0) return NB200_ERR;
     DevBufs bufs;
@@ -2300,13 +2300,13 @@ int nb200_bench_mma_peak(nb200_model* m, int kind, int ctas, int iters, const ui
     CUDA_CHECK(cudaMemcpyAsync(da, a_bytes, 128 * 128, cudaMemcpyHostToDevice, st));
     CUDA_CHECK(cudaMemcpyAsync(db, b_bytes, 256 * 128, cudaMemcpyHostToDevice, st));
     if (check_out) {
-        mma_peak_run(st, kind, 1, 1, da, db, dc);
+        mma_peak_run(st, kind, 1, kind == 2 ? 8 : 1, da, db, dc);  // kind 2: 8 blocks (4 distinct K slices of the operands, twice)
         CUDA_CHECK(cudaMemcpyAsync(check_out, dc, 128 * 256 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
         CUDA_CHECK(cudaStreamSynchronize(st));
     }
     mma_peak_run(st, kind, ctas, std::min(iters, 64), da, db, nullptr);  // warm-up
     const float ms = mma_peak_run(st, kind, ctas, iters, da, db, nullptr);
-    const double k_total = (double)iters * (kind == 0 ? 64.0 : 128.0);
+    const double k_total = (double)iters * (kind == 0 ? 64.0 : (kind == 1 ? 128.0 : 32.0));
     *tops_out = 2.0 * 128.0 * 256.0 * k_total * ctas / (ms * 1e-3) * 1e-12;
     return NB200_OK;
     NB_CATCH(NB200_ERR)

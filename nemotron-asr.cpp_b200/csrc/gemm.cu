@@ -717,15 +717,126 @@ __global__ void __launch_bounds__(192) mma_peak_kernel(int iters, const uint8_t*
     }
 }
 
+// kind 2: what ggml's Q8_0 arithmetic (ggml-cpu/quants.c:451-478) costs on kind::i8 — the int32 accumulator of ONE MMA (K = 32 = one
+// quantisation block) must be scaled by d_w[n][block] * d_x[m][block] before it may be added to the running sum. Best-case design:
+// two TMEM accumulators (MMA of block i + 1 runs while block i is read out), 16 epilogue warps, thread = (row, 64 columns) with its
+// 64 fp32 running sums in registers; per block and thread 2 x tcgen05.ld.x32, 64 I2F, 64 scale products, 64 FMAs. Scales are
+// synthetic tables in shared memory (8 blocks deep, cycled). The result goes to check_out as fp32.
+__device__ __forceinline__ void tmem_ld32_raw(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
+
+constexpr int I8S_EPI_WARPS = 16, I8S_THREADS = 64 + 32 * I8S_EPI_WARPS;
+__global__ void __launch_bounds__(I8S_THREADS, 1) mma_i8_block_scaled_kernel(int iters, const uint8_t* __restrict__ a_bytes, const uint8_t* __restrict__ b_bytes,
+                                                                         float* __restrict__ check_out) {
+    constexpr int BN = 256, A_BYTES = 128 * 128, B_BYTES = BN * 128;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t base = (raw + 1023u) & ~1023u;
+    uint8_t* smem = smem_raw + (base - raw);
+    const uint32_t bars = base + A_BYTES + B_BYTES;  // full[2], empty[2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + A_BYTES + B_BYTES + 32);
+    float* sw = reinterpret_cast<float*>(smem + A_BYTES + B_BYTES + 64);  // d_w [8 blocks][256 columns]
+    float* sx = sw + 8 * BN;                                              // d_x [8 blocks][128 rows]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < (A_BYTES + B_BYTES) / 16; i += blockDim.x) {
+        const bool is_b = i >= A_BYTES / 16;
+        const int j = is_b ? i - A_BYTES / 16 : i, row = j >> 3, chunk = j & 7;
+        const uint8_t* src = (is_b ? b_bytes : a_bytes) + (size_t)row * 128 + chunk * 16;
+        uint8_t* dst = smem + (is_b ? A_BYTES : 0) + (row >> 3) * 1024 + (row & 7) * 128 + ((chunk ^ (row & 7)) * 16);
+        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+    }
+    for (int i = threadIdx.x; i < 8 * BN; i += blockDim.x) sw[i] = 0.5f + 0.001f * (float)((i * 7) % 31);
+    for (int i = threadIdx.x; i < 8 * 128; i += blockDim.x) sx[i] = 0.25f + 0.002f * (float)((i * 5) % 29);
+    if (threadIdx.x == 0) {
+        mbar_init(bars, 1);
+        mbar_init(bars + 8, 1);
+        mbar_init(bars + 16, I8S_EPI_WARPS);
+        mbar_init(bars + 24, I8S_EPI_WARPS);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), 512);
+    fence_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    if (warp == 1) {
+        if (lane == 0) {
+            const uint64_t adesc = make_smem_desc(base), bdesc = make_smem_desc(base + A_BYTES);
+            for (int it = 0; it < iters; it++) {
+                const int buf = it & 1;
+                mbar_wait(bars + 16 + 8 * buf, ((it >> 1) & 1) ^ 1);  // the accumulator's previous contents have been read out
+                tc_fence_after();
+                umma_i8(tmem_base + 256u * buf, adesc + 2 * (it & 3), bdesc + 2 * (it & 3), make_idesc_i8(128, BN), 0u);  // ONE K = 32 block
+                umma_commit(bars + 8 * buf);
+            }
+        }
+    } else if (warp >= 2) {
+        const int ew = warp - 2, quad = warp & 3, cg = ew >> 2;  // TMEM lane quadrant, 64-column group
+        const int row = quad * 32 + lane;
+        float acc[64];
+#pragma unroll
+        for (int j = 0; j < 64; j++) acc[j] = 0.0f;
+#pragma unroll 1
+        for (int it = 0; it < iters; it++) {
+            const int buf = it & 1, blk = it & 7;
+            mbar_wait(bars + 8 * buf, (it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t ta = tmem_base + 256u * buf + ((uint32_t)(quad * 32) << 16) + (uint32_t)(cg * 64);
+            const float dx = sx[blk * 128 + row];
+            const float* dw = sw + blk * BN + cg * 64;
+            uint32_t v[32];
+            tmem_ld32_raw(ta, v);
+#pragma unroll
+            for (int j = 0; j < 32; j++) acc[j] = fmaf((float)(int)v[j], dx * dw[j], acc[j]);
+            tmem_ld32_raw(ta + 32, v);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bars + 16 + 8 * buf);  // the MMA of block it + 2 may overwrite this accumulator
+#pragma unroll
+            for (int j = 0; j < 32; j++) acc[32 + j] = fmaf((float)(int)v[j], dx * dw[32 + j], acc[32 + j]);
+        }
+        if (check_out != nullptr && blockIdx.x == 0) {
+#pragma unroll
+            for (int j = 0; j < 64; j++) check_out[(size_t)row * BN + cg * 64 + j] = acc[j];
+        } else {  // keep the sums alive
+            float s = 0.0f;
+#pragma unroll
+            for (int j = 0; j < 64; j++) s += acc[j];
+            if (s == 1.2345e-30f) sw[0] = s;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
 float mma_peak_run(cudaStream_t st, int kind, int ctas, int iters, const uint8_t* a_bytes, const uint8_t* b_bytes, uint32_t* check_out) {
-    const int smem = 128 * 128 + 256 * 128 + 1024 + 64;
+    const int smem = 128 * 128 + 256 * 128 + 1024 + 64 + (kind == 2 ? 8 * (256 + 128) * 4 : 0);
     auto kern = kind == 0 ? mma_peak_kernel<0> : mma_peak_kernel<1>;
-    CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    if (kind == 2) CUDA_CHECK(cudaFuncSetAttribute(mma_i8_block_scaled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    else CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     cudaEvent_t e0, e1;
     CUDA_CHECK(cudaEventCreate(&e0));
     CUDA_CHECK(cudaEventCreate(&e1));
     CUDA_CHECK(cudaEventRecord(e0, st));
-    kern<<<ctas, 192, smem, st>>>(iters, a_bytes, b_bytes, check_out);
+    if (kind == 2) mma_i8_block_scaled_kernel<<<ctas, I8S_THREADS, smem, st>>>(iters, a_bytes, b_bytes, reinterpret_cast<float*>(check_out));
+    else kern<<<ctas, 192, smem, st>>>(iters, a_bytes, b_bytes, check_out);
     CUDA_CHECK(cudaEventRecord(e1, st));
     CUDA_CHECK(cudaEventSynchronize(e1));
     NB_KERNEL_CHECK();
