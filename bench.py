@@ -414,13 +414,18 @@ def main():
     except Exception:
         pass
     traffic = None
+    traffic_own = None
     try:  # DRAM bytes per launch of the dominant GEMM from this round's ncu --set full capture (profiles/ncu_traffic.json)
         if a.streams == 64 and a.rc == 13:
-            traffic = json.loads((ROOT / "profiles" / "ncu_traffic.json").read_text()).get("gemm_tc_128x256", {}).get("traffic")
+            tj = json.loads((ROOT / "profiles" / "ncu_traffic.json").read_text()).get("gemm_tc_128x256", {})
+            traffic, traffic_own = tj.get("traffic"), tj.get("own_operand_bytes")
     except Exception:
         traffic = None
+    traffic_note = ("dram bytes per launch of the 128x256 GEMMs (W1 / W2) under ncu --set full: the kernel's own operands (traffic_own_operands: weights + A, no "
+                    "re-reads) plus the NEXT GEMM's weights and the layer's K / V slabs that its epilogue warps prefetch into L2; ncu serialises "
+                    "kernels with cold caches, so it counts the prefetched bytes here and again in the next kernel, in a step they replace that kernel's reads")
     roofline = {"kernel": "gemm_tc_kernel (all tcgen05 GEMM launches of the step)", "bound": "tensor", "achieved": ach, "peak": pk["tflops"],
-                "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": traffic, "algorithmic": gemm_flops_step / max(gemm_launches_step, 1),
+                "unit": "TFLOP/s", "frac": ach / pk["tflops"], "traffic": traffic, "traffic_own_operands": traffic_own, "traffic_note": traffic_note, "algorithmic": gemm_flops_step / max(gemm_launches_step, 1),
                 "launches_per_step": gemm_launches_step, "avg_launch_us": gemm_ms_step / max(gemm_launches_step, 1) * 1e3,
                 "gemm_ms_per_step": gemm_ms_step, "share_of_step": gemm_ms_step / (ms_dev / a.steps), "peak_source": pk["source"],
                 "timing": "in-graph marginal cost: K steps with every GEMM launched twice minus the K timed steps (CUDA events on the library's "
