@@ -943,7 +943,7 @@ np.savez(%r, **out)
 """
 
 CHECKER_PATHS = ("NB200_ATTN_SIMT", "NB200_ATTN_STAGED", "NB200_ATTN_MMA_ONLY", "NB200_ATTN_FULL_SIMT", "NB200_JOINT_SGEMM", "NB200_MEL_RADIX2",
-                 "NB200_NO_PDL", "NB200_DECODE_NO_COOP", "NB200_NO_GRAPHS", "NB200_GEMM_GENERIC_EPILOGUE", "NB200_NO_LN_FUSION")
+                 "NB200_NO_PDL", "NB200_DECODE_NO_COOP", "NB200_NO_GRAPHS", "NB200_GEMM_GENERIC_EPILOGUE", "NB200_NO_WEIGHT_PREFETCH")
 
 
 @pytest.fixture(scope="module")
@@ -984,7 +984,8 @@ def test_checker_paths_agree_with_fast_paths(nb, ab_runner, env_name):
     assert r < 2e-3, (env_name, "offline", r)
     n = min(len(base["off_tok"]), len(alt["off_tok"]), 20)
     assert np.array_equal(base["off_tok"][:n], alt["off_tok"][:n]) and np.array_equal(base["off_fr"][:n], alt["off_fr"][:n])
-    if env_name in ("NB200_NO_PDL", "NB200_DECODE_NO_COOP", "NB200_NO_GRAPHS", "NB200_MEL_RADIX2", "NB200_GEMM_GENERIC_EPILOGUE"):
+    if env_name in ("NB200_NO_PDL", "NB200_DECODE_NO_COOP", "NB200_NO_GRAPHS", "NB200_MEL_RADIX2", "NB200_GEMM_GENERIC_EPILOGUE",
+                    "NB200_NO_WEIGHT_PREFETCH"):
         # launch modes and bit-identical kernels: nothing may change at all
         for k in base.files:
             assert np.array_equal(base[k], alt[k]), (env_name, k)
